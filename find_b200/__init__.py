@@ -1,0 +1,10 @@
+"""find_b200 — B200-native (sm_100a) implementation of FIND's field + Chamfer training hot path.
+
+Public surface mirrors the reference's names:
+  chamfer_distance, knn_points, Pointclouds         (PyTorch3D calls at src/model/losses.py:77-88)
+  NeuralDisplacementField, LatentVector, FourierFeatureTransform, DisplacementLoss   (src/model/model.py, losses.py)
+All compute goes through libfindb200.so (include/find_b200.h); there is no CPU fallback.
+"""
+from .chamfer import Pointclouds, chamfer_distance, knn_points  # noqa: F401
+
+__all__ = ["chamfer_distance", "knn_points", "Pointclouds"]

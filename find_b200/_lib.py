@@ -1,0 +1,93 @@
+"""find_b200/_lib.py — loads libfindb200.so (the C ABI in include/find_b200.h) through ctypes.
+
+There is NO fallback: if the CUDA library is missing or a call fails, a RuntimeError is raised.  torch is
+used only as the owner of device memory and streams; every pointer handed to the library is a raw
+``data_ptr()`` and every call is enqueued on torch's current CUDA stream.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+from typing import Optional
+
+import torch
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libfindb200.so")
+
+_lib = None
+
+c_void_p, c_int, c_size_t, c_float, c_char_p = (ctypes.c_void_p, ctypes.c_int, ctypes.c_size_t, ctypes.c_float,
+                                                ctypes.c_char_p)
+
+# name -> (restype, argtypes): mirrors include/find_b200.h exactly (checked by tests/test_abi.py)
+SIGNATURES = {
+    "findb200_last_error": (c_char_p, []),
+    "findb200_version": (c_char_p, []),
+    "findb200_knn_workspace_bytes": (c_size_t, [c_int, c_int, c_int]),
+    "findb200_knn1": (c_int, [c_void_p] * 4 + [c_int] * 3 + [c_void_p] * 3 + [c_size_t, c_void_p]),
+    "findb200_knn1_backward": (c_int, [c_void_p] * 6 + [c_int] * 3 + [c_void_p] * 3),
+    "findb200_chamfer_forward": (c_int, [c_void_p] * 4 + [c_int] * 3 + [c_void_p] * 6 + [c_size_t, c_void_p]),
+    "findb200_umma_selftest": (c_int, [c_int, c_void_p, c_void_p, c_void_p, c_void_p]),
+    "findb200_chamfer_backward": (c_int, [c_void_p] * 4 + [c_int] * 3 + [c_void_p] * 3 + [c_float] + [c_void_p] * 3),
+}
+
+
+def load(build_if_missing: bool = True):
+    """Return the ctypes handle of libfindb200.so; raise RuntimeError if it cannot be had."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        if not build_if_missing:
+            raise RuntimeError(f"{LIB_PATH} is missing: run `python -m find_b200.build`")
+        from . import build as _build
+        _build.build()
+    try:
+        lib = ctypes.CDLL(LIB_PATH)
+    except OSError as e:  # pragma: no cover
+        raise RuntimeError(f"cannot load {LIB_PATH}: {e}") from e
+    for name, (res, args) in SIGNATURES.items():
+        try:
+            fn = getattr(lib, name)
+        except AttributeError as e:
+            raise RuntimeError(f"{LIB_PATH} does not export {name}; rebuild with `python -m find_b200.build`") from e
+        fn.restype = res
+        fn.argtypes = args
+    _lib = lib
+    return lib
+
+
+def last_error() -> str:
+    return load().findb200_last_error().decode("utf-8", "replace")
+
+
+def check(rc: int, what: str) -> None:
+    if rc != 0:
+        raise RuntimeError(f"{what} failed (code {rc}): {last_error()}")
+
+
+def ptr(t: Optional[torch.Tensor]):
+    """Raw device pointer (None -> NULL)."""
+    return None if t is None else ctypes.c_void_p(t.data_ptr())
+
+
+def stream_ptr(device: torch.device):
+    return ctypes.c_void_p(torch.cuda.current_stream(device).cuda_stream)
+
+
+def require_cuda(*tensors: Optional[torch.Tensor]) -> torch.device:
+    """The product path has no CPU implementation: refuse loudly instead of silently falling back."""
+    dev = None
+    for t in tensors:
+        if t is None:
+            continue
+        if not t.is_cuda:
+            raise RuntimeError("find_b200 runs on CUDA (sm_100a) only: got a CPU tensor; there is no CPU fallback")
+        if dev is None:
+            dev = t.device
+        elif t.device != dev:
+            raise RuntimeError(f"tensors on different devices: {dev} vs {t.device}")
+    if dev is None:
+        raise RuntimeError("no tensor given")
+    return dev

@@ -1,0 +1,504 @@
+// find_b200/csrc/chamfer.cu — bidirectional Chamfer / 1-NN for sm_100a.
+//
+// Replaces, for FIND's 3-D loss (reference call sites /root/reference/src/model/losses.py:77,85,88 and
+// src/eval/eval_3d.py:151,159,176-177), PyTorch3D's `knn_points(K=1)` + `chamfer_distance` + backward
+// (pytorch3d @ 1706eb82: csrc/knn/knn.cu KNearestNeighborKernelV0-V3 / KNearestNeighborBackwardKernel).
+//
+// Contract (bit-exact vs oracle/chamfer_oracle.c mode 0):
+//   dist(q,t) = fmaf(dz,dz, fmaf(dy,dy, dx*dx)),  d* = q* - t* rounded to fp32; argmin with lowest index on ties.
+//
+// Design (B200):
+//   * clouds are re-laid out once per call as SoA rows padded with +inf to a multiple of 32 (cloud_to_soa),
+//     so target tiles are three contiguous rows that one elected thread moves with cp.async.bulk (TMA engine)
+//     into a double-buffered shared-memory stage guarded by mbarriers;
+//   * each thread keeps Q=4 queries in registers as duplicated fp32x2 pairs and evaluates two targets per
+//     instruction with FADD2/FMUL2/FFMA2 (6 packed ops per 2 pairs) + one FMNMX3 per 2 pairs;
+//   * argmin is two-level: the inner loop only tracks the minimum of each 32-target chunk and the id of the
+//     best chunk (strict <, ascending chunks); the winning chunk is rescanned once at the end for the lowest
+//     index whose distance equals the minimum — so the inner loop carries no per-pair index bookkeeping;
+//   * work items (direction, cloud, 512-query tile, target split) are handed out by a persistent grid through
+//     an atomic counter; splits combine with one 64-bit atomicMin on (dist_bits << 32 | idx), which orders
+//     exactly like (dist, idx) lexicographically because dist >= +0.
+#include "common.cuh"
+#include "../../include/find_b200.h"
+#include <math_constants.h>
+
+namespace fb {
+namespace chamfer {
+
+constexpr int kThreads = 128;
+constexpr int kQ = 4;                      // queries per thread
+constexpr int kQueriesPerItem = kThreads * kQ;
+constexpr int kChunk = 32;                 // targets per argmin chunk
+constexpr int kTile = 1024;                // targets per shared-memory stage (3 rows x 4 KB)
+constexpr int kStages = 2;
+
+struct KnnDir {
+    const float* q_soa;   // [N][3][Pq_pad]
+    const float* t_soa;   // [N][3][Pt_pad]
+    const int64_t* len_q; // nullable
+    const int64_t* len_t; // nullable
+    unsigned long long* keys;  // [N][Pq]
+    int Pq, Pq_pad, Pt, Pt_pad;
+    int n_qtiles, n_splits;
+};
+struct KnnParams {
+    KnnDir dir[2];
+    int ndir, N;
+    int items_dir0, total_items;
+    unsigned int* counter;
+};
+
+__global__ void cloud_to_soa_kernel(const float* __restrict__ aos, const int64_t* __restrict__ lens, int P,
+                                    int Ppad, float* __restrict__ soa) {
+    int n = blockIdx.y;
+    int j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= Ppad) return;
+    int len = lens ? (int)lens[n] : P;
+    float x = CUDART_INF_F, y = CUDART_INF_F, z = CUDART_INF_F;
+    if (j < len) {
+        const float* p = aos + ((size_t)n * P + j) * 3;
+        x = p[0]; y = p[1]; z = p[2];
+    }
+    float* o = soa + (size_t)n * 3 * Ppad;
+    o[j] = x; o[Ppad + j] = y; o[2 * Ppad + j] = z;
+}
+
+FB_DEVINL float dist_exact(float qx, float qy, float qz, float tx, float ty, float tz) {
+    float dx = __fsub_rn(qx, tx), dy = __fsub_rn(qy, ty), dz = __fsub_rn(qz, tz);
+    return __fmaf_rn(dz, dz, __fmaf_rn(dy, dy, __fmul_rn(dx, dx)));
+}
+
+__global__ void __launch_bounds__(kThreads) knn_main_kernel(const KnnParams prm) {
+    __shared__ __align__(128) float s_t[kStages][3][kTile];
+    __shared__ __align__(8) uint64_t s_full[kStages];
+    __shared__ int s_item;
+
+    const int tid = threadIdx.x;
+    if (tid == 0) {
+        for (int s = 0; s < kStages; ++s) mbar_init(&s_full[s], 1);
+        fence_barrier_init();
+    }
+    __syncthreads();
+    uint32_t full_phase = 0;   // bit s = parity to wait for on stage s
+
+    for (;;) {
+        if (tid == 0) s_item = (int)atomicAdd(prm.counter, 1u);
+        __syncthreads();
+        const int item = s_item;
+        __syncthreads();                       // everyone has read s_item before it is overwritten
+        if (item >= prm.total_items) break;
+
+        const int d = item >= prm.items_dir0 ? 1 : 0;
+        const KnnDir& D = prm.dir[d];
+        int r = item - (d ? prm.items_dir0 : 0);
+        const int split = r % D.n_splits; r /= D.n_splits;
+        const int qt = r % D.n_qtiles;
+        const int n = r / D.n_qtiles;
+
+        const int len_q = D.len_q ? (int)D.len_q[n] : D.Pq;
+        const int len_t = D.len_t ? (int)D.len_t[n] : D.Pt;
+        if (qt * kQueriesPerItem >= len_q || len_t <= 0) continue;   // uniform across the block
+
+        // target range of this split, in 32-target chunks
+        const int n_chunks = (len_t + kChunk - 1) / kChunk;
+        const int cps = (n_chunks + D.n_splits - 1) / D.n_splits;
+        const int c_begin = split * cps;
+        const int c_end = min(n_chunks, c_begin + cps);
+        if (c_begin >= c_end) continue;
+        const int t_begin = c_begin * kChunk, t_end = c_end * kChunk;
+        const int n_tiles = (t_end - t_begin + kTile - 1) / kTile;
+        const float* tsoa = D.t_soa + (size_t)n * 3 * D.Pt_pad;
+
+        auto issue_tile = [&](int tile) {
+            const int s = tile % kStages;
+            const int t0 = t_begin + tile * kTile;
+            const int cnt = min(kTile, t_end - t0);
+            mbar_expect_tx(&s_full[s], 3u * cnt * 4u);
+#pragma unroll
+            for (int c = 0; c < 3; ++c) bulk_g2s(&s_t[s][c][0], tsoa + (size_t)c * D.Pt_pad + t0, cnt * 4u, &s_full[s]);
+        };
+        if (tid == 0) {
+            issue_tile(0);
+            if (n_tiles > 1) issue_tile(1);
+        }
+
+        // queries -> registers (duplicated halves so that one packed op serves two targets)
+        const float* qsoa = D.q_soa + (size_t)n * 3 * D.Pq_pad;
+        uint64_t qx[kQ], qy[kQ], qz[kQ];
+        float best[kQ];
+        int bchunk[kQ];
+#pragma unroll
+        for (int q = 0; q < kQ; ++q) {
+            const int i = qt * kQueriesPerItem + q * kThreads + tid;
+            float x = CUDART_INF_F, y = CUDART_INF_F, z = CUDART_INF_F;
+            if (i < D.Pq_pad) { x = qsoa[i]; y = qsoa[D.Pq_pad + i]; z = qsoa[2 * D.Pq_pad + i]; }
+            qx[q] = pack2(x, x); qy[q] = pack2(y, y); qz[q] = pack2(z, z);
+            best[q] = CUDART_INF_F;
+            bchunk[q] = c_begin;
+        }
+
+        for (int tile = 0; tile < n_tiles; ++tile) {
+            const int s = tile % kStages;
+            mbar_wait(&s_full[s], (full_phase >> s) & 1u);
+            full_phase ^= 1u << s;
+            const int t0 = t_begin + tile * kTile;
+            const int chunks = (min(kTile, t_end - t0)) / kChunk;
+            const float4* sx = reinterpret_cast<const float4*>(&s_t[s][0][0]);
+            const float4* sy = reinterpret_cast<const float4*>(&s_t[s][1][0]);
+            const float4* sz = reinterpret_cast<const float4*>(&s_t[s][2][0]);
+            for (int c = 0; c < chunks; ++c) {
+                float cmin[kQ];
+#pragma unroll
+                for (int q = 0; q < kQ; ++q) cmin[q] = CUDART_INF_F;
+#pragma unroll
+                for (int g = 0; g < kChunk / 4; ++g) {
+                    const float4 X = sx[c * (kChunk / 4) + g];
+                    const float4 Y = sy[c * (kChunk / 4) + g];
+                    const float4 Z = sz[c * (kChunk / 4) + g];
+                    const uint64_t x01 = pack2(X.x, X.y), x23 = pack2(X.z, X.w);
+                    const uint64_t y01 = pack2(Y.x, Y.y), y23 = pack2(Y.z, Y.w);
+                    const uint64_t z01 = pack2(Z.x, Z.y), z23 = pack2(Z.z, Z.w);
+#pragma unroll
+                    for (int q = 0; q < kQ; ++q) {
+                        uint64_t dx = sub2(qx[q], x01), dy = sub2(qy[q], y01), dz = sub2(qz[q], z01);
+                        uint64_t dd = fma2(dz, dz, fma2(dy, dy, mul2(dx, dx)));
+                        float lo, hi;
+                        unpack2(dd, lo, hi);
+                        cmin[q] = min3(cmin[q], lo, hi);
+                        dx = sub2(qx[q], x23); dy = sub2(qy[q], y23); dz = sub2(qz[q], z23);
+                        dd = fma2(dz, dz, fma2(dy, dy, mul2(dx, dx)));
+                        unpack2(dd, lo, hi);
+                        cmin[q] = min3(cmin[q], lo, hi);
+                    }
+                }
+                const int cid = (t0 / kChunk) + c;
+#pragma unroll
+                for (int q = 0; q < kQ; ++q) {
+                    if (cmin[q] < best[q]) { best[q] = cmin[q]; bchunk[q] = cid; }
+                }
+            }
+            __syncthreads();                                   // stage s fully consumed by every warp
+            if (tid == 0 && tile + kStages < n_tiles) issue_tile(tile + kStages);
+        }
+
+        // resolve the lowest index inside the winning chunk (exactly the same arithmetic), publish
+#pragma unroll
+        for (int q = 0; q < kQ; ++q) {
+            const int i = qt * kQueriesPerItem + q * kThreads + tid;
+            if (i >= len_q) continue;
+            float x, xd, y, yd, z, zd;
+            unpack2(qx[q], x, xd); unpack2(qy[q], y, yd); unpack2(qz[q], z, zd);
+            const int j0 = bchunk[q] * kChunk;
+            int bj = j0;
+            bool found = false;
+            for (int j = 0; j < kChunk; ++j) {
+                const float tx = tsoa[j0 + j], ty = tsoa[D.Pt_pad + j0 + j], tz = tsoa[2 * D.Pt_pad + j0 + j];
+                const float dd = dist_exact(x, y, z, tx, ty, tz);
+                if (!found && dd == best[q]) { bj = j0 + j; found = true; }
+            }
+            const unsigned long long key =
+                ((unsigned long long)__float_as_uint(best[q]) << 32) | (unsigned long long)(unsigned)bj;
+            unsigned long long* dst = D.keys + (size_t)n * D.Pq + i;
+            if (D.n_splits == 1) *dst = key; else atomicMin(dst, key);
+        }
+    }
+}
+
+// keys -> (dist, idx int64) + deterministic per-cloud sums of dist (double) for the Chamfer reduction.
+// grid (N, ndir), block 256.
+struct FinalizeDir {
+    const unsigned long long* keys;
+    const int64_t* len_q;
+    const int64_t* len_t;
+    float* dists;     // nullable
+    int64_t* idx;     // nullable
+    int32_t* idx32;   // nullable (internal consumers)
+    double* sums;     // nullable, [N]
+    int Pq, Pt;
+};
+struct FinalizeParams { FinalizeDir dir[2]; };
+
+__global__ void __launch_bounds__(256) knn_finalize_kernel(const FinalizeParams prm) {
+    const FinalizeDir& D = prm.dir[blockIdx.y];
+    const int n = blockIdx.x;
+    const int len_q = D.len_q ? (int)D.len_q[n] : D.Pq;
+    const int len_t = D.len_t ? (int)D.len_t[n] : D.Pt;
+    double acc = 0.0;
+    for (int i = threadIdx.x; i < D.Pq; i += blockDim.x) {
+        float dist = 0.f;
+        long long j = 0;
+        if (i < len_q && len_t > 0) {
+            const unsigned long long k = D.keys[(size_t)n * D.Pq + i];
+            dist = __uint_as_float((unsigned)(k >> 32));
+            j = (long long)(k & 0xffffffffull);
+            acc += (double)dist;
+        }
+        if (D.dists) D.dists[(size_t)n * D.Pq + i] = dist;
+        if (D.idx) D.idx[(size_t)n * D.Pq + i] = j;
+        if (D.idx32) D.idx32[(size_t)n * D.Pq + i] = (int32_t)j;
+    }
+    if (D.sums) {
+        __shared__ double s_acc[256];
+        s_acc[threadIdx.x] = acc;
+        __syncthreads();
+        for (int o = 128; o > 0; o >>= 1) {
+            if ((int)threadIdx.x < o) s_acc[threadIdx.x] += s_acc[threadIdx.x + o];
+            __syncthreads();
+        }
+        if (threadIdx.x == 0) D.sums[n] = s_acc[0];
+    }
+}
+
+// loss = ( sum_n sx[n]/max(lx,1) + sum_n sy[n]/max(ly,1) ) / max(N,1)   (chamfer.py mean/mean), one thread.
+__global__ void chamfer_reduce_kernel(const double* sx, const double* sy, const int64_t* lx, const int64_t* ly, int N,
+                                      int P1, int P2, float* loss, float* loss_xy) {
+    if (threadIdx.x || blockIdx.x) return;
+    double cx = 0.0, cy = 0.0;
+    for (int n = 0; n < N; ++n) {
+        long long a = lx ? lx[n] : P1, b = ly ? ly[n] : P2;
+        cx += sx[n] / (double)(a < 1 ? 1 : a);
+        cy += sy[n] / (double)(b < 1 ? 1 : b);
+    }
+    const double div = (double)(N < 1 ? 1 : N);
+    *loss = (float)((cx + cy) / div);
+    if (loss_xy) { loss_xy[0] = (float)(cx / div); loss_xy[1] = (float)(cy / div); }
+}
+
+// ---- backward ---------------------------------------------------------------------------------------
+// knn_points backward (K=1, norm=2): direct term with plain stores, scatter term with fp32 atomics
+// (PyTorch3D's kernel does both with atomicAdd; summation order is unspecified there as well).
+__global__ void knn_bwd_kernel(const float* __restrict__ p1, const float* __restrict__ p2,
+                               const int64_t* __restrict__ len1, const int64_t* __restrict__ len2,
+                               const int64_t* __restrict__ idx, const float* __restrict__ grad_dists, int P1, int P2,
+                               float* __restrict__ grad_p1, float* __restrict__ grad_p2) {
+    const int n = blockIdx.y;
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= P1) return;
+    const int l1 = len1 ? (int)len1[n] : P1, l2 = len2 ? (int)len2[n] : P2;
+    float gx = 0.f, gy = 0.f, gz = 0.f;
+    if (i < l1 && l2 > 0) {
+        const int j = (int)idx[(size_t)n * P1 + i];
+        const float g = grad_dists[(size_t)n * P1 + i];
+        const float* a = p1 + ((size_t)n * P1 + i) * 3;
+        const float* b = p2 + ((size_t)n * P2 + j) * 3;
+        gx = 2.0f * g * (a[0] - b[0]); gy = 2.0f * g * (a[1] - b[1]); gz = 2.0f * g * (a[2] - b[2]);
+        float* o = grad_p2 + ((size_t)n * P2 + j) * 3;
+        atomicAdd(o + 0, -gx); atomicAdd(o + 1, -gy); atomicAdd(o + 2, -gz);
+    }
+    float* o1 = grad_p1 + ((size_t)n * P1 + i) * 3;
+    o1[0] = gx; o1[1] = gy; o1[2] = gz;
+}
+
+// Chamfer backward, step 1: direct terms of both clouds (every element written once, padded rows get 0).
+//   grad_a[n,i] = 2 * g * w_a[n] * (a_i - b_idx_a[i]),   w_a[n] = 1 / (max(len_a,1) * max(N,1))
+__global__ void chamfer_bwd_direct_kernel(const float* __restrict__ a, const float* __restrict__ b,
+                                          const int64_t* __restrict__ len_a, const int64_t* __restrict__ len_b,
+                                          const int64_t* __restrict__ idx_a, const float* __restrict__ grad_loss,
+                                          float grad_scale, int N, int Pa, int Pb, float* __restrict__ grad_a) {
+    const int n = blockIdx.y;
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= Pa) return;
+    const int la = len_a ? (int)len_a[n] : Pa, lb = len_b ? (int)len_b[n] : Pb;
+    float gx = 0.f, gy = 0.f, gz = 0.f;
+    if (i < la && lb > 0) {
+        const float g = (grad_loss ? *grad_loss : 1.0f) * grad_scale;
+        const float w = g / ((float)(la < 1 ? 1 : la) * (float)(N < 1 ? 1 : N));
+        const int j = (int)idx_a[(size_t)n * Pa + i];
+        const float* pa = a + ((size_t)n * Pa + i) * 3;
+        const float* pb = b + ((size_t)n * Pb + j) * 3;
+        gx = 2.0f * w * (pa[0] - pb[0]); gy = 2.0f * w * (pa[1] - pb[1]); gz = 2.0f * w * (pa[2] - pb[2]);
+    }
+    float* o = grad_a + ((size_t)n * Pa + i) * 3;
+    o[0] = gx; o[1] = gy; o[2] = gz;
+}
+// step 2: scatter term: grad_b[n, idx_a[i]] -= 2 * g * w_a[n] * (a_i - b_idx_a[i])
+__global__ void chamfer_bwd_scatter_kernel(const float* __restrict__ a, const float* __restrict__ b,
+                                           const int64_t* __restrict__ len_a, const int64_t* __restrict__ len_b,
+                                           const int64_t* __restrict__ idx_a, const float* __restrict__ grad_loss,
+                                           float grad_scale, int N, int Pa, int Pb, float* __restrict__ grad_b) {
+    const int n = blockIdx.y;
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const int la = len_a ? (int)len_a[n] : Pa, lb = len_b ? (int)len_b[n] : Pb;
+    if (i >= la || lb <= 0) return;
+    const float g = (grad_loss ? *grad_loss : 1.0f) * grad_scale;
+    const float w = g / ((float)(la < 1 ? 1 : la) * (float)(N < 1 ? 1 : N));
+    const int j = (int)idx_a[(size_t)n * Pa + i];
+    const float* pa = a + ((size_t)n * Pa + i) * 3;
+    const float* pb = b + ((size_t)n * Pb + j) * 3;
+    float* o = grad_b + ((size_t)n * Pb + j) * 3;
+    atomicAdd(o + 0, -2.0f * w * (pa[0] - pb[0]));
+    atomicAdd(o + 1, -2.0f * w * (pa[1] - pb[1]));
+    atomicAdd(o + 2, -2.0f * w * (pa[2] - pb[2]));
+}
+
+// ---- host side ------------------------------------------------------------------------------------------
+static inline int round_up(int a, int b) { return (a + b - 1) / b * b; }
+static inline size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }
+
+struct Workspace {
+    unsigned int* counter;
+    unsigned long long *keys_x, *keys_y;
+    float *soa_x, *soa_y;
+    double *sum_x, *sum_y;
+    size_t bytes;
+};
+static Workspace carve(void* base, int N, int P1, int P2) {
+    Workspace w{};
+    const int P1p = round_up(P1 > 0 ? P1 : 1, kChunk), P2p = round_up(P2 > 0 ? P2 : 1, kChunk);
+    size_t off = 0;
+    char* b = (char*)base;
+    w.counter = (unsigned int*)(b + off); off += 256;
+    w.keys_x = (unsigned long long*)(b + off); off += align256((size_t)N * P1 * 8);
+    w.keys_y = (unsigned long long*)(b + off); off += align256((size_t)N * P2 * 8);
+    w.soa_x = (float*)(b + off); off += align256((size_t)N * 3 * P1p * 4);
+    w.soa_y = (float*)(b + off); off += align256((size_t)N * 3 * P2p * 4);
+    w.sum_x = (double*)(b + off); off += align256((size_t)N * 8);
+    w.sum_y = (double*)(b + off); off += align256((size_t)N * 8);
+    w.bytes = off;
+    return w;
+}
+
+static int g_num_sms = 0;
+static int num_sms() {
+    if (!g_num_sms) {
+        int dev = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&g_num_sms, cudaDevAttrMultiProcessorCount, dev);
+        if (g_num_sms <= 0) g_num_sms = 148;
+    }
+    return g_num_sms;
+}
+
+static void fill_dir(KnnDir& D, const float* qsoa, const float* tsoa, const int64_t* lq, const int64_t* lt,
+                     unsigned long long* keys, int Pq, int Pt, int N, int target_items) {
+    D.q_soa = qsoa; D.t_soa = tsoa; D.len_q = lq; D.len_t = lt; D.keys = keys;
+    D.Pq = Pq; D.Pt = Pt; D.Pq_pad = round_up(Pq, kChunk); D.Pt_pad = round_up(Pt, kChunk);
+    D.n_qtiles = (Pq + kQueriesPerItem - 1) / kQueriesPerItem;
+    // split the target range until there are enough items to balance a persistent grid, but keep
+    // at least 2 full tiles of targets per split so the staging pipeline stays amortised
+    int base_items = N * D.n_qtiles;
+    int max_splits = (Pt + 2 * kTile - 1) / (2 * kTile);
+    if (max_splits < 1) max_splits = 1;
+    int s = 1;
+    while (base_items * s < target_items && s * 2 <= max_splits) s *= 2;
+    D.n_splits = s;
+}
+
+// Core: runs 1 or 2 directions.  dir 0: queries x (P1) vs targets y (P2); dir 1: queries y vs targets x.
+static int run_knn(const float* x, const float* y, const int64_t* lx, const int64_t* ly, int N, int P1, int P2,
+                   bool both, void* ws_base, size_t ws_bytes, Workspace& w, cudaStream_t st) {
+    FB_REQUIRE(N >= 0 && P1 >= 0 && P2 >= 0, FINDB200_ERR_SHAPE, "knn: negative size N=%d P1=%d P2=%d", N, P1, P2);
+    w = carve(ws_base, N, P1, P2);
+    FB_REQUIRE(ws_base != nullptr && ws_bytes >= w.bytes, FINDB200_ERR_WORKSPACE,
+               "knn: workspace too small (%zu < %zu bytes)", ws_bytes, w.bytes);
+    if (N == 0 || (P1 == 0 && P2 == 0)) return 0;
+    const int P1p = round_up(P1 > 0 ? P1 : 1, kChunk), P2p = round_up(P2 > 0 ? P2 : 1, kChunk);
+    if (P1 > 0) cloud_to_soa_kernel<<<dim3((P1p + 255) / 256, N), 256, 0, st>>>(x, lx, P1, P1p, w.soa_x);
+    if (P2 > 0) cloud_to_soa_kernel<<<dim3((P2p + 255) / 256, N), 256, 0, st>>>(y, ly, P2, P2p, w.soa_y);
+    // counter = 0, keys = 0xFF.. (identity of atomicMin); one memset each (they are adjacent but differ in value)
+    FB_CUDA(cudaMemsetAsync(w.counter, 0, 256, st));
+    FB_CUDA(cudaMemsetAsync(w.keys_x, 0xFF, (size_t)((char*)w.soa_x - (char*)w.keys_x), st));
+    if (P1 == 0 || P2 == 0) return 0;
+
+    const int sms = num_sms();
+    KnnParams prm{};
+    prm.N = N; prm.counter = w.counter; prm.ndir = both ? 2 : 1;
+    const int target_items = sms * 8;
+    fill_dir(prm.dir[0], w.soa_x, w.soa_y, lx, ly, w.keys_x, P1, P2, N, both ? target_items / 2 : target_items);
+    prm.items_dir0 = N * prm.dir[0].n_qtiles * prm.dir[0].n_splits;
+    prm.total_items = prm.items_dir0;
+    if (both) {
+        fill_dir(prm.dir[1], w.soa_y, w.soa_x, ly, lx, w.keys_y, P2, P1, N, target_items / 2);
+        prm.total_items += N * prm.dir[1].n_qtiles * prm.dir[1].n_splits;
+    }
+    int grid = sms * 4;
+    if (grid > prm.total_items) grid = prm.total_items;
+    knn_main_kernel<<<grid, kThreads, 0, st>>>(prm);
+    FB_CUDA(cudaGetLastError());
+    return 0;
+}
+
+}  // namespace chamfer
+}  // namespace fb
+
+using namespace fb;
+using namespace fb::chamfer;
+
+extern "C" {
+
+size_t findb200_knn_workspace_bytes(int N, int P1, int P2) {
+    if (N < 0 || P1 < 0 || P2 < 0) return 0;
+    return carve(nullptr, N, P1, P2).bytes;
+}
+
+int findb200_knn1(const float* p1, const float* p2, const int64_t* len1, const int64_t* len2, int N, int P1, int P2,
+                  float* dists, int64_t* idx, void* ws, size_t ws_bytes, void* stream) {
+    cudaStream_t st = (cudaStream_t)stream;
+    Workspace w;
+    int rc = run_knn(p1, p2, len1, len2, N, P1, P2, false, ws, ws_bytes, w, st);
+    if (rc) return rc;
+    if (N == 0 || P1 == 0) return 0;
+    FinalizeParams fp{};
+    fp.dir[0] = FinalizeDir{w.keys_x, len1, len2, dists, idx, nullptr, nullptr, P1, P2};
+    knn_finalize_kernel<<<dim3(N, 1), 256, 0, st>>>(fp);
+    FB_CUDA(cudaGetLastError());
+    return 0;
+}
+
+int findb200_knn1_backward(const float* p1, const float* p2, const int64_t* len1, const int64_t* len2,
+                           const int64_t* idx, const float* grad_dists, int N, int P1, int P2, float* grad_p1,
+                           float* grad_p2, void* stream) {
+    cudaStream_t st = (cudaStream_t)stream;
+    FB_REQUIRE(N >= 0 && P1 >= 0 && P2 >= 0, FINDB200_ERR_SHAPE, "knn_backward: negative size");
+    if (N == 0) return 0;
+    if (P2 > 0) FB_CUDA(cudaMemsetAsync(grad_p2, 0, (size_t)N * P2 * 3 * sizeof(float), st));
+    if (P1 > 0) {
+        knn_bwd_kernel<<<dim3((P1 + 255) / 256, N), 256, 0, st>>>(p1, p2, len1, len2, idx, grad_dists, P1, P2, grad_p1,
+                                                                  grad_p2);
+        FB_CUDA(cudaGetLastError());
+    }
+    return 0;
+}
+
+int findb200_chamfer_forward(const float* x, const float* y, const int64_t* x_len, const int64_t* y_len, int N, int P1,
+                             int P2, float* loss, float* dist_x, int64_t* idx_x, float* dist_y, int64_t* idx_y,
+                             void* ws, size_t ws_bytes, void* stream) {
+    cudaStream_t st = (cudaStream_t)stream;
+    FB_REQUIRE(loss != nullptr, FINDB200_ERR_ARG, "chamfer_forward: loss pointer is null");
+    Workspace w;
+    int rc = run_knn(x, y, x_len, y_len, N, P1, P2, true, ws, ws_bytes, w, st);
+    if (rc) return rc;
+    if (N == 0) { FB_CUDA(cudaMemsetAsync(loss, 0, sizeof(float), st)); return 0; }
+    FinalizeParams fp{};
+    fp.dir[0] = FinalizeDir{w.keys_x, x_len, y_len, dist_x, idx_x, nullptr, w.sum_x, P1, P2};
+    fp.dir[1] = FinalizeDir{w.keys_y, y_len, x_len, dist_y, idx_y, nullptr, w.sum_y, P2, P1};
+    knn_finalize_kernel<<<dim3(N, 2), 256, 0, st>>>(fp);
+    chamfer_reduce_kernel<<<1, 32, 0, st>>>(w.sum_x, w.sum_y, x_len, y_len, N, P1, P2, loss, nullptr);
+    FB_CUDA(cudaGetLastError());
+    return 0;
+}
+
+int findb200_chamfer_backward(const float* x, const float* y, const int64_t* x_len, const int64_t* y_len, int N,
+                              int P1, int P2, const int64_t* idx_x, const int64_t* idx_y, const float* grad_loss,
+                              float grad_scale, float* grad_x, float* grad_y, void* stream) {
+    cudaStream_t st = (cudaStream_t)stream;
+    FB_REQUIRE(N >= 0 && P1 >= 0 && P2 >= 0, FINDB200_ERR_SHAPE, "chamfer_backward: negative size");
+    FB_REQUIRE(grad_x != nullptr, FINDB200_ERR_ARG, "chamfer_backward: grad_x is null");
+    if (N == 0) return 0;
+    const dim3 g1((P1 + 255) / 256, N), g2((P2 + 255) / 256, N);
+    if (P1 > 0)
+        chamfer_bwd_direct_kernel<<<g1, 256, 0, st>>>(x, y, x_len, y_len, idx_x, grad_loss, grad_scale, N, P1, P2, grad_x);
+    if (grad_y && P2 > 0)
+        chamfer_bwd_direct_kernel<<<g2, 256, 0, st>>>(y, x, y_len, x_len, idx_y, grad_loss, grad_scale, N, P2, P1, grad_y);
+    if (P1 > 0 && P2 > 0) {
+        // y -> x scatter lands in grad_x; x -> y scatter lands in grad_y
+        chamfer_bwd_scatter_kernel<<<g2, 256, 0, st>>>(y, x, y_len, x_len, idx_y, grad_loss, grad_scale, N, P2, P1, grad_x);
+        if (grad_y)
+            chamfer_bwd_scatter_kernel<<<g1, 256, 0, st>>>(x, y, x_len, y_len, idx_x, grad_loss, grad_scale, N, P1, P2, grad_y);
+    }
+    FB_CUDA(cudaGetLastError());
+    return 0;
+}
+
+}  // extern "C"
