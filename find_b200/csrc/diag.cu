@@ -1,0 +1,93 @@
+// find_b200/csrc/diag.cu — FP32 CUDA-core peak microbenchmarks (roofline denominators for the Chamfer kernel;
+// MEASURED_PEAKS.json carries no fp32 entry).  mode 0: scalar FFMA chains, mode 1: packed FFMA2 chains.
+#include "common.cuh"
+#include "../../include/find_b200.h"
+
+namespace fb {
+template <int MODE>
+__global__ void __launch_bounds__(256) fp32_peak_kernel(int iters, float seed, float* out) {
+    constexpr int ILP = 8;
+    float a[ILP], b = seed, c = 0.5f;
+    uint64_t A[ILP], B2 = pack2(seed, seed), C2 = pack2(0.5f, 0.25f);
+#pragma unroll
+    for (int i = 0; i < ILP; ++i) { a[i] = seed + i; A[i] = pack2(seed + i, seed - i); }
+    for (int it = 0; it < iters; ++it) {
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+#pragma unroll
+            for (int i = 0; i < ILP; ++i) {
+                if (MODE == 0) a[i] = __fmaf_rn(a[i], b, c);
+                else A[i] = fma2(A[i], B2, C2);
+            }
+        }
+    }
+    float s = 0.f;
+#pragma unroll
+    for (int i = 0; i < ILP; ++i) {
+        float lo, hi;
+        unpack2(A[i], lo, hi);
+        s += a[i] + lo + hi;
+    }
+    if (s == 123.456f) out[0] = s;   // never true; keeps the chains alive
+}
+}  // namespace fb
+
+// Launches `blocks` x 256 threads, each doing iters*64 FMA instructions (mode 1: x2 lanes).  Time it outside.
+extern "C" int findb200_fp32_peak(int mode, int blocks, int iters, float* scratch, void* stream) {
+    using namespace fb;
+    FB_REQUIRE(mode == 0 || mode == 1, FINDB200_ERR_ARG, "fp32_peak: mode must be 0 or 1");
+    if (mode == 0) fp32_peak_kernel<0><<<blocks, 256, 0, (cudaStream_t)stream>>>(iters, 1.0001f, scratch);
+    else fp32_peak_kernel<1><<<blocks, 256, 0, (cudaStream_t)stream>>>(iters, 1.0001f, scratch);
+    FB_CUDA(cudaGetLastError());
+    return 0;
+}
+
+// ---- L2 -> shared-memory bulk-copy bandwidth probe ------------------------------------------------------
+// Every CTA streams the SAME `region_bytes` of global memory (the way every field CTA streams the same packed
+// weights) with cp.async.bulk; nothing consumes the data.  `issuers` warps each run their own ring of `stages`
+// slots of `chunk` bytes.  Time it outside: bytes moved = blocks * issuers * iters * chunk.
+namespace fb {
+__global__ void __launch_bounds__(128) l2_stream_kernel(const uint8_t* __restrict__ src, uint32_t region_chunks,
+                                                        uint32_t chunk, int iters, int stages, int issuers,
+                                                        float* out) {
+    extern __shared__ uint8_t dsm_raw[];
+    uint8_t* ring0 = (uint8_t*)(((uintptr_t)dsm_raw + 1023) & ~(uintptr_t)1023);
+    __shared__ __align__(8) uint64_t full[4][8];
+    if (threadIdx.x == 0) {
+        for (int w = 0; w < 4; ++w)
+            for (int s = 0; s < 8; ++s) mbar_init(&full[w][s], 1);
+        fence_barrier_init();
+    }
+    __syncthreads();
+    const int w = threadIdx.x >> 5;
+    if ((threadIdx.x & 31) == 0 && w < issuers) {
+        uint8_t* ring = ring0 + (size_t)w * stages * chunk;
+        uint32_t c = (blockIdx.x * 7u + w * 3u) % region_chunks;      // CTAs start at different chunks
+        for (int i = 0; i < iters + stages; ++i) {
+            const int s = i % stages;
+            if (i >= stages) mbar_wait(&full[w][s], ((i / stages) - 1) & 1);
+            if (i < iters) {
+                mbar_expect_tx(&full[w][s], chunk);
+                bulk_g2s(ring + s * chunk, src + (size_t)c * chunk, chunk, &full[w][s]);
+                c = (c + 1 == region_chunks) ? 0 : c + 1;
+            }
+        }
+        if (ring[5] == 77 && iters < 0) out[0] = 1.f;
+    }
+}
+}  // namespace fb
+
+extern "C" int findb200_l2_stream(const void* src, size_t region_bytes, int chunk_bytes, int blocks, int iters,
+                                  int stages, int issuers, float* scratch, void* stream) {
+    using namespace fb;
+    FB_REQUIRE(stages >= 1 && stages <= 8 && issuers >= 1 && issuers <= 4 && chunk_bytes >= 1024 &&
+                   region_bytes >= (size_t)chunk_bytes, FINDB200_ERR_ARG, "l2_stream: bad args");
+    const int smem = issuers * stages * chunk_bytes + 1024;
+    FB_REQUIRE(smem <= 227 * 1024, FINDB200_ERR_ARG, "l2_stream: ring too large");
+    FB_CUDA(cudaFuncSetAttribute(l2_stream_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    l2_stream_kernel<<<blocks, 128, smem, (cudaStream_t)stream>>>((const uint8_t*)src,
+                                                                (uint32_t)(region_bytes / chunk_bytes),
+                                                                (uint32_t)chunk_bytes, iters, stages, issuers, scratch);
+    FB_CUDA(cudaGetLastError());
+    return 0;
+}

@@ -67,6 +67,16 @@ int findb200_chamfer_backward(const float* x, const float* y, const int64_t* x_l
  * ------------------------------------------------------------------------------------------------------ */
 int findb200_umma_selftest(int mode, const void* a_img, const void* b_img, float* d_out, void* stream);
 
+/* FP32 CUDA-core peak probe (roofline denominator of the Chamfer kernel): launches blocks x 256 threads, each
+ * issuing iters*64 dependent-chain FMAs with ILP 8 (mode 0: FFMA, mode 1: packed FFMA2 = 2 lanes/instr). */
+int findb200_fp32_peak(int mode, int blocks, int iters, float* scratch, void* stream);
+
+/* L2 -> shared-memory bulk-copy (cp.async.bulk) bandwidth probe: `blocks` CTAs x `issuers` warps each stream `iters`
+ * chunks of `chunk_bytes` of the same `region_bytes` region through a `stages`-deep ring (how the field CTAs stream
+ * packed weights). */
+int findb200_l2_stream(const void* src, size_t region_bytes, int chunk_bytes, int blocks, int iters, int stages,
+                       int issuers, float* scratch, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
