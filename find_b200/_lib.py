@@ -28,6 +28,11 @@ SIGNATURES = {
     "findb200_knn1": (c_int, [c_void_p] * 4 + [c_int] * 3 + [c_void_p] * 3 + [c_size_t, c_void_p]),
     "findb200_knn1_backward": (c_int, [c_void_p] * 6 + [c_int] * 3 + [c_void_p] * 3),
     "findb200_chamfer_forward": (c_int, [c_void_p] * 4 + [c_int] * 3 + [c_void_p] * 6 + [c_size_t, c_void_p]),
+    "findb200_field_workspace_bytes": (c_size_t, [c_int] * 4),
+    "findb200_field_forward": (c_int, [c_void_p] * 2 + [c_int] + [c_void_p] * 4 + [c_int] * 3 + [c_void_p] * 4
+                               + [c_size_t, c_void_p]),
+    "findb200_field_backward": (c_int, [c_void_p] * 2 + [c_int] + [c_void_p] * 4 + [c_int] * 2 + [c_void_p] * 11
+                                + [c_size_t, c_void_p]),
     "findb200_umma_selftest": (c_int, [c_int, c_void_p, c_void_p, c_void_p, c_void_p]),
     "findb200_fp32_peak": (c_int, [c_int, c_int, c_int, c_void_p, c_void_p]),
     "findb200_l2_stream": (c_int, [c_void_p, c_size_t] + [c_int] * 5 + [c_void_p, c_void_p]),

@@ -1,0 +1,695 @@
+// find_b200/csrc/field.cu — host orchestration + small CUDA-core kernels of the displacement field (C ABI in
+// include/find_b200.h).  The tensor-core work is in field_chain.cu (forward / dX chains) and field_dw.cu (dW GEMMs).
+//
+// Step structure (training, template shared by all feet — the get_meshes call site, model.py:473-477):
+//   forward : pack_weights | latent_bias | TRUNK_FWD (once per template tile) | HEAD_FWD (per head, foot, tile)
+//   backward: grad_prep (tanh', registration-transform backward, max |g| for the fp16 gradient scale)
+//             | HEAD_BWD | TRUNK_BWD | dw_kernel (all weight-gradient GEMMs in one launch) | reduce_dw | finish_small
+// With per-foot distinct points (TextureLossGTSpace call site, losses.py:50) the trunk runs per foot as well.
+#include "field.cuh"
+#include "field_dw.cuh"
+#include <math.h>
+#include <string.h>
+
+#include "field_chain_params.cuh"
+
+namespace fb {
+namespace field {
+
+static inline size_t align1k(size_t x) { return (x + 1023) & ~(size_t)1023; }
+static inline int cdiv(int a, int b) { return (a + b - 1) / b; }
+
+static int g_sms = 0;
+static int num_sms() {
+    if (!g_sms) {
+        int dev = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&g_sms, cudaDevAttrMultiProcessorCount, dev);
+        if (g_sms <= 0) g_sms = 148;
+    }
+    return g_sms;
+}
+
+// ---- packed weight layout ---------------------------------------------------------------------------------
+static PackLayout make_layout() {
+    PackLayout L;
+    memset(&L, 0, sizeof(L));
+    uint32_t off = 0;
+    auto put = [&](GemmW& g, int n_chunks, uint32_t chunk_bytes, int N, int k16_last) {
+        g.off = off; g.chunk_bytes = chunk_bytes; g.n_chunks = (uint16_t)n_chunks; g.N = (uint16_t)N;
+        g.k16_last = (uint16_t)k16_last; g.pad = 0;
+        off += (uint32_t)n_chunks * chunk_bytes;
+    };
+    put(L.fwd[P_T0], kEncChunks, kWChunkBytes, 256, 1);          // K = 515 -> 8 chunks + 16 columns of the 9th
+    for (int l = P_T1; l <= P_T4; ++l) put(L.fwd[l], 4, kWChunkBytes, 256, 4);
+    for (int h = 0; h < 2; ++h) {
+        const int b = h ? P_C1 : P_D1;
+        for (int l = 0; l < 3; ++l) put(L.fwd[b + l], 4, kWChunkBytes, 256, 4);
+        put(L.fwd[b + 3], 4, kWSmallChunkBytes, 16, 4);          // 256 -> 3, N padded to 16
+    }
+    for (int l = P_T1; l <= P_T4; ++l) put(L.bwd[l], 4, kWChunkBytes, 256, 4);
+    for (int h = 0; h < 2; ++h) {
+        const int b = h ? P_C1 : P_D1;
+        for (int l = 0; l < 3; ++l) put(L.bwd[b + l], 4, kWChunkBytes, 256, 4);
+        put(L.bwd[b + 3], 1, kWChunkBytes, 256, 1);              // 3 -> 256: one K = 16 step
+    }
+    L.total_bytes = off;
+    return L;
+}
+
+// One thread per 16-B chunk of a weight image.  Image row i, internal k:
+//   forward  images: value = W[i][col0 + k]            (i < rows, k < kcols), K-permuted for base.0
+//   backward images: value = W[k][col0 + i]            (i < kcols, k < rows)
+struct PackJob {
+    const float* src;
+    int ld, rows, kcols, col0, transpose, perm, img_rows, n_chunks;
+    uint32_t dst_off;
+};
+struct PackParams { PackJob j[2 * P_COUNT]; int n; uint8_t* dst; };
+
+__global__ void __launch_bounds__(256) pack_weights_kernel(const __grid_constant__ PackParams P) {
+    const PackJob& J = P.j[blockIdx.y];
+    const int per_chunk = J.img_rows * 8;
+    const int total = per_chunk * J.n_chunks;
+    for (int id = blockIdx.x * blockDim.x + threadIdx.x; id < total; id += gridDim.x * blockDim.x) {
+        const int c = id / per_chunk, r = (id % per_chunk) / 8, ch = id % 8;
+        float v[8];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+            const int k = c * 64 + ch * 8 + e;
+            float x = 0.f;
+            if (!J.transpose) {
+                int kc = J.perm ? enc_ref_col(k) : k;
+                if (r < J.rows && kc >= 0 && kc < J.kcols) x = J.src[(size_t)r * J.ld + J.col0 + kc];
+            } else {
+                if (r < J.kcols && k < J.rows) x = J.src[(size_t)k * J.ld + J.col0 + r];
+            }
+            v[e] = x;
+        }
+        uint4 pk;
+        __half2 h;
+        h = __floats2half2_rn(v[0], v[1]); pk.x = *reinterpret_cast<uint32_t*>(&h);
+        h = __floats2half2_rn(v[2], v[3]); pk.y = *reinterpret_cast<uint32_t*>(&h);
+        h = __floats2half2_rn(v[4], v[5]); pk.z = *reinterpret_cast<uint32_t*>(&h);
+        h = __floats2half2_rn(v[6], v[7]); pk.w = *reinterpret_cast<uint32_t*>(&h);
+        uint8_t* d = P.dst + J.dst_off + (size_t)c * (J.img_rows * 128) + (size_t)r * 128 + ((ch ^ (r & 7)) << 4);
+        *reinterpret_cast<uint4*>(d) = pk;
+    }
+}
+
+// biasfoot[head][b][n] = b1[n] + sum_j W1[n][256 + j] * z_b[j]   (the latent columns of mlp_*.0, model.py:428-437)
+struct LatentBiasParams {
+    const float *Wd, *bd, *Wc, *bc;      // mlp_disp.0 / mlp_col.0
+    const float *z_shape, *z_pose, *z_tex;
+    int S, Pz, T, B;
+    float* out;
+};
+__global__ void __launch_bounds__(256) latent_bias_kernel(const LatentBiasParams P) {
+    const int n = threadIdx.x, b = blockIdx.x, head = blockIdx.y;
+    float acc;
+    if (head == 0) {
+        const int ld = kW + P.S + P.Pz;
+        const float* w = P.Wd + (size_t)n * ld + kW;
+        acc = P.bd[n];
+        for (int j = 0; j < P.S; ++j) acc = fmaf(w[j], P.z_shape[(size_t)b * P.S + j], acc);
+        for (int j = 0; j < P.Pz; ++j) acc = fmaf(w[P.S + j], P.z_pose[(size_t)b * P.Pz + j], acc);
+    } else {
+        const int ld = kW + P.T;
+        const float* w = P.Wc + (size_t)n * ld + kW;
+        acc = P.bc[n];
+        for (int j = 0; j < P.T; ++j) acc = fmaf(w[j], P.z_tex[(size_t)b * P.T + j], acc);
+    }
+    P.out[((size_t)head * P.B + b) * kW + n] = acc;
+}
+
+__device__ __forceinline__ void euler_xyz_d(const float* e, float (&R)[3][3]) {
+    float sa, ca, sb, cb, sc, cc;
+    sincosf(e[0], &sa, &ca); sincosf(e[1], &sb, &cb); sincosf(e[2], &sc, &cc);
+    R[0][0] = cb * cc;                 R[0][1] = -cb * sc;                R[0][2] = sb;
+    R[1][0] = sa * sb * cc + ca * sc;  R[1][1] = -sa * sb * sc + ca * cc; R[1][2] = -sa * cb;
+    R[2][0] = -ca * sb * cc + sa * sc; R[2][1] = ca * sb * sc + sa * cc;  R[2][2] = ca * cb;
+}
+
+// Backward of the output non-linearities and of the registration transform, per (foot, vertex):
+//   g_u = (R g_X) * S  (+ grad_disp),  d(pre-tanh)_disp = g_u * 0.1 * (1 - t^2), t = disp / 0.1
+//   d(pre-tanh)_col = grad_col * 0.5 * (1 - t^2), t = 2 (col - avg) - 1
+// plus per-foot sums for d(reg) and the global max |d(pre-tanh)| that fixes the fp16 gradient scale.
+struct GradPrepParams {
+    const float *pos, *disp, *col, *reg, *avg_col, *grad_disp, *grad_col, *grad_verts;
+    int B, V, shared;
+    float* dovals;       // [2][B][V][4]
+    uint32_t* maxabs;
+    float* regsums;      // [B][12]
+};
+__global__ void __launch_bounds__(256) grad_prep_kernel(const GradPrepParams P) {
+    const int b = blockIdx.y;
+    const int v = blockIdx.x * blockDim.x + threadIdx.x;
+    float sums[12];
+#pragma unroll
+    for (int i = 0; i < 12; ++i) sums[i] = 0.f;
+    float m = 0.f;
+    if (v < P.V) {
+        const size_t o = ((size_t)b * P.V + v) * 3;
+        float g0 = 0.f, g1 = 0.f, g2 = 0.f;
+        if (P.grad_disp) { g0 = P.grad_disp[o]; g1 = P.grad_disp[o + 1]; g2 = P.grad_disp[o + 2]; }
+        if (P.grad_verts) {
+            const float x0 = P.grad_verts[o], x1 = P.grad_verts[o + 1], x2 = P.grad_verts[o + 2];
+            if (P.reg) {
+                const float* rg = P.reg + (size_t)b * 9;
+                float R[3][3];
+                euler_xyz_d(rg + 3, R);
+                const float* pp = P.pos + ((size_t)(P.shared ? 0 : b) * P.V + v) * 3;
+                const float u[3] = {pp[0] + P.disp[o], pp[1] + P.disp[o + 1], pp[2] + P.disp[o + 2]};
+                const float gx[3] = {x0, x1, x2};
+                sums[0] = x0; sums[1] = x1; sums[2] = x2;
+#pragma unroll
+                for (int i = 0; i < 3; ++i)
+#pragma unroll
+                    for (int j = 0; j < 3; ++j) sums[3 + i * 3 + j] = u[i] * gx[j];
+                g0 += rg[6] * (R[0][0] * x0 + R[0][1] * x1 + R[0][2] * x2);
+                g1 += rg[7] * (R[1][0] * x0 + R[1][1] * x1 + R[1][2] * x2);
+                g2 += rg[8] * (R[2][0] * x0 + R[2][1] * x1 + R[2][2] * x2);
+            } else {
+                g0 += x0; g1 += x1; g2 += x2;
+            }
+        }
+        const float t0 = 10.f * P.disp[o], t1 = 10.f * P.disp[o + 1], t2 = 10.f * P.disp[o + 2];
+        float4 dd = make_float4(g0 * 0.1f * (1.f - t0 * t0), g1 * 0.1f * (1.f - t1 * t1), g2 * 0.1f * (1.f - t2 * t2), 0.f);
+        *reinterpret_cast<float4*>(P.dovals + ((size_t)b * P.V + v) * 4) = dd;
+        m = fmaxf(fmaxf(fabsf(dd.x), fabsf(dd.y)), fabsf(dd.z));
+        float4 dc = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (P.grad_col) {
+            const float a0 = P.avg_col ? P.avg_col[0] : 0.f, a1 = P.avg_col ? P.avg_col[1] : 0.f, a2 = P.avg_col ? P.avg_col[2] : 0.f;
+            const float c0 = 2.f * (P.col[o] - a0) - 1.f, c1 = 2.f * (P.col[o + 1] - a1) - 1.f, c2 = 2.f * (P.col[o + 2] - a2) - 1.f;
+            dc = make_float4(P.grad_col[o] * 0.5f * (1.f - c0 * c0), P.grad_col[o + 1] * 0.5f * (1.f - c1 * c1),
+                             P.grad_col[o + 2] * 0.5f * (1.f - c2 * c2), 0.f);
+            m = fmaxf(m, fmaxf(fmaxf(fabsf(dc.x), fabsf(dc.y)), fabsf(dc.z)));
+        }
+        *reinterpret_cast<float4*>(P.dovals + (((size_t)P.B + b) * P.V + v) * 4) = dc;
+    }
+    // block reductions
+    __shared__ float sh[12][8];
+    __shared__ float shm[8];
+    const int lane = threadIdx.x & 31, wp = threadIdx.x >> 5;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
+    if (P.reg && P.grad_verts) {
+#pragma unroll
+        for (int i = 0; i < 12; ++i) {
+            float s = sums[i];
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+            if (lane == 0) sh[i][wp] = s;
+        }
+    }
+    if (lane == 0) shm[wp] = m;
+    __syncthreads();
+    if (threadIdx.x < 12 && P.reg && P.grad_verts) {
+        float s = 0.f;
+        for (int w = 0; w < 8; ++w) s += sh[threadIdx.x][w];
+        atomicAdd(P.regsums + (size_t)b * 12 + threadIdx.x, s);
+    }
+    if (threadIdx.x == 0) {
+        float mm = 0.f;
+        for (int w = 0; w < 8; ++w) mm = fmaxf(mm, shm[w]);
+        if (mm == mm && mm < 3.0e38f) atomicMax(P.maxabs, __float_as_uint(mm));   // non-negative floats order like their bits
+    }
+}
+
+__device__ __forceinline__ float inv_grad_scale(uint32_t maxabs_bits) {
+    const float m = __uint_as_float(maxabs_bits);
+    if (!(m > 0.f) || !(m < 3.0e38f)) return 1.0f;
+    int e;
+    frexpf(m, &e);
+    return ldexpf(1.0f, e - 4);
+}
+
+// dst[r][dst_col(c)] = inv_scale * sum_s partial[s][r][src_col0 + c]      (fixed order => deterministic)
+struct ReduceJob {
+    float* dst;
+    const float* partial;
+    int dst_ld, rows, cols, dst_col0, perm_kbase, ncta, src_col0;   // perm_kbase >= 0: dst col = enc_ref_col(kbase + c)
+};
+constexpr int kMaxReduceJobs = 20;
+struct ReduceParams { ReduceJob j[kMaxReduceJobs]; int n; const uint32_t* maxabs; };
+
+__global__ void __launch_bounds__(256) reduce_dw_kernel(const __grid_constant__ ReduceParams P) {
+    const ReduceJob& J = P.j[blockIdx.y];
+    if (!J.dst) return;
+    const float inv = inv_grad_scale(*P.maxabs);
+    const int total = J.rows * J.cols;
+    for (int id = blockIdx.x * blockDim.x + threadIdx.x; id < total; id += gridDim.x * blockDim.x) {
+        const int r = id / J.cols, c = id % J.cols;
+        float acc = 0.f;
+        const float* p = J.partial + (size_t)r * kW + J.src_col0 + c;
+        for (int s = 0; s < J.ncta; ++s) acc += p[(size_t)s * kW * kW];
+        int dc = J.dst_col0 + c;
+        if (J.perm_kbase >= 0) {
+            dc = enc_ref_col(J.perm_kbase + c);
+            if (dc < 0) continue;
+        }
+        J.dst[(size_t)r * J.dst_ld + dc] = acc * inv;
+    }
+}
+
+// Everything that hangs off the column sums: bias gradients, latent columns of mlp_*.0.weight, latent-code
+// gradients, registration gradients.  grid.x = blocks of 256 threads, grid.y = section.
+struct FinishParams {
+    const uint32_t* maxabs;
+    const float* colsum;          // see Workspace::colsum
+    const float* regsums;         // [B][12]
+    const float *Wd, *Wc;         // mlp_disp.0.weight / mlp_col.0.weight (for the latent-code gradients)
+    const float *z_shape, *z_pose, *z_tex, *reg;
+    int B, S, Pz, T, heads_mask, frozen, have_reg;
+    float* gW[P_COUNT];
+    float* gb[P_COUNT];
+    float *gz_shape, *gz_pose, *gz_tex, *greg;
+};
+// colsum layout (floats)
+__host__ __device__ inline size_t cs_foot(int head, int B) { return (size_t)head * B * kW; }                 // [2][B][256]
+__host__ __device__ inline size_t cs_head(int head, int l, int B) { return (size_t)2 * B * kW + ((size_t)head * 2 + l) * kW; }   // l = 0: layer 2, 1: layer 3
+__host__ __device__ inline size_t cs_out(int head, int B) { return (size_t)2 * B * kW + 4 * kW + (size_t)head * 16; }
+__host__ __device__ inline size_t cs_trunk(int l, int B) { return (size_t)2 * B * kW + 4 * kW + 32 + (size_t)l * kW; }
+__host__ __device__ inline size_t cs_total(int B) { return (size_t)2 * B * kW + 4 * kW + 32 + 5 * kW; }
+
+__global__ void __launch_bounds__(256) finish_small_kernel(const __grid_constant__ FinishParams P) {
+    const float inv = inv_grad_scale(*P.maxabs);
+    const int sec = blockIdx.y;
+    const int id = blockIdx.x * blockDim.x + threadIdx.x;
+    if (sec == 0) {
+        // bias gradients (13 vectors) : id = param * 256 + n
+        if (P.frozen) return;
+        const int prm = id / kW, n = id % kW;
+        if (prm >= P_COUNT || !P.gb[prm]) return;
+        float v = 0.f;
+        if (prm <= P_T4) v = P.colsum[cs_trunk(prm, P.B) + n];
+        else {
+            const int head = prm >= P_C1, l = prm - (head ? P_C1 : P_D1);
+            if (l == 3 && n >= 3) return;
+            if (!(P.heads_mask & (1 << head))) v = 0.f;
+            else if (l == 0) { for (int b = 0; b < P.B; ++b) v += P.colsum[cs_foot(head, P.B) + (size_t)b * kW + n]; }
+            else if (l == 3) v = P.colsum[cs_out(head, P.B) + n];
+            else v = P.colsum[cs_head(head, l - 1, P.B) + n];
+        }
+        P.gb[prm][n] = v * inv;
+    } else if (sec == 1 || sec == 2) {
+        // latent columns of mlp_disp.0.weight (sec 1) / mlp_col.0.weight (sec 2): dW[n][256 + j] = sum_b s_b[n] z_b[j]
+        if (P.frozen) return;
+        const int head = sec - 1;
+        const int L = head ? P.T : P.S + P.Pz;
+        float* g = P.gW[head ? P_C1 : P_D1];
+        if (!g || id >= kW * L) return;
+        const int n = id / L, j = id % L;
+        float v = 0.f;
+        if (P.heads_mask & (1 << head)) {
+            for (int b = 0; b < P.B; ++b) {
+                float z;
+                if (head) z = P.z_tex[(size_t)b * P.T + j];
+                else z = j < P.S ? P.z_shape[(size_t)b * P.S + j] : P.z_pose[(size_t)b * P.Pz + (j - P.S)];
+                v = fmaf(P.colsum[cs_foot(head, P.B) + (size_t)b * kW + n], z, v);
+            }
+        }
+        g[(size_t)n * (kW + L) + kW + j] = v * inv;
+    } else if (sec == 3) {
+        // latent-code gradients: gz[b][j] = sum_n W1[n][256 + j] s_b[n]
+        const int Ld = P.S + P.Pz, Lt = P.T;
+        const int per = Ld + Lt;
+        if (per == 0 || id >= P.B * per) return;
+        const int b = id / per, j = id % per;
+        const int head = j >= Ld;
+        const int jj = head ? j - Ld : j;
+        const float* W = head ? P.Wc : P.Wd;
+        const int ld = kW + (head ? Lt : Ld);
+        float v = 0.f;
+        if (P.heads_mask & (1 << head)) {
+            const float* s = P.colsum + cs_foot(head, P.B) + (size_t)b * kW;
+            for (int n = 0; n < kW; ++n) v = fmaf(W[(size_t)n * ld + kW + jj], s[n], v);
+        }
+        v *= inv;
+        if (head) { if (P.gz_tex) P.gz_tex[(size_t)b * P.T + jj] = v; }
+        else if (jj < P.S) { if (P.gz_shape) P.gz_shape[(size_t)b * P.S + jj] = v; }
+        else { if (P.gz_pose) P.gz_pose[(size_t)b * P.Pz + (jj - P.S)] = v; }
+    } else {
+        // registration gradients (reg = [t(3), euler(3), S(3)], model.py:481-488); not scaled (fp32 path)
+        if (!P.greg || id >= P.B) return;
+        const int b = id;
+        float* g = P.greg + (size_t)b * 9;
+        if (!P.have_reg) { for (int i = 0; i < 9; ++i) g[i] = 0.f; return; }
+        const float* s = P.regsums + (size_t)b * 12;
+        const float* rg = P.reg + (size_t)b * 9;
+        float sa, ca, sb, cb, sc, cc;
+        sincosf(rg[3], &sa, &ca); sincosf(rg[4], &sb, &cb); sincosf(rg[5], &sc, &cc);
+        float R[3][3];
+        euler_xyz_d(rg + 3, R);
+        const float dRa[3][3] = {{0.f, 0.f, 0.f}, {-R[2][0], -R[2][1], -R[2][2]}, {R[1][0], R[1][1], R[1][2]}};
+        const float dRb[3][3] = {{-sb * cc, sb * sc, cb}, {sa * cb * cc, -sa * cb * sc, sa * sb}, {-ca * cb * cc, ca * cb * sc, -ca * sb}};
+        const float dRc[3][3] = {{R[0][1], -R[0][0], 0.f}, {R[1][1], -R[1][0], 0.f}, {R[2][1], -R[2][0], 0.f}};
+        float ga = 0.f, gbb = 0.f, gc = 0.f, gS[3];
+        for (int i = 0; i < 3; ++i) {
+            float acc = 0.f;
+            for (int j = 0; j < 3; ++j) {
+                const float Q = s[3 + i * 3 + j];
+                acc += R[i][j] * Q;
+                const float M = rg[6 + i] * Q;
+                ga += M * dRa[i][j]; gbb += M * dRb[i][j]; gc += M * dRc[i][j];
+            }
+            gS[i] = acc;
+        }
+        g[0] = s[0]; g[1] = s[1]; g[2] = s[2];
+        g[3] = ga; g[4] = gbb; g[5] = gc;
+        g[6] = gS[0]; g[7] = gS[1]; g[8] = gS[2];
+    }
+}
+
+// ---- workspace --------------------------------------------------------------------------------------------
+static Workspace carve(int B, int V, int shared, int for_backward) {
+    Workspace w;
+    memset(&w, 0, sizeof(w));
+    const PackLayout L = make_layout();
+    w.tpf = cdiv(V > 0 ? V : 1, kTile);
+    w.tpf2 = (w.tpf + 1) & ~1;
+    w.trunk_feet = shared ? 1 : B;
+    w.trunk_tiles = w.trunk_feet * w.tpf2;
+    const size_t head_tiles = (size_t)B * w.tpf2;
+    size_t off = 0;
+    auto take = [&](size_t bytes) { size_t o = off; off = align1k(off + bytes); return o; };
+    w.wpack = take(L.total_bytes);
+    w.biasfoot = take((size_t)2 * B * kW * 4);
+    w.tact = take((size_t)5 * w.trunk_tiles * kTileBytes);
+    w.scal = take(1024);
+    if (for_backward) {
+        w.enc = take((size_t)w.trunk_tiles * kEncTileBytes);
+        w.hact = take((size_t)2 * 3 * head_tiles * kTileBytes);
+        w.hdz = take((size_t)2 * 3 * head_tiles * kTileBytes);
+        w.doimg = take((size_t)2 * head_tiles * kImgBytes);
+        w.tdz = take((size_t)5 * w.trunk_tiles * kTileBytes);
+        w.dovals = take((size_t)2 * B * V * 16);
+        w.regsums = take((size_t)B * 12 * 4);
+        w.colsum = take(cs_total(B) * 4);
+        w.n_partials = kMaxDwCtas;
+        w.partial = take((size_t)w.n_partials * kW * kW * 4);
+    }
+    w.total = off;
+    return w;
+}
+
+struct Sizes { int S, Pz, T; };
+
+static int check_common(const findb200_field_params* p, int B, int V) {
+    FB_REQUIRE(p != nullptr, FINDB200_ERR_ARG, "field: params is null");
+    FB_REQUIRE(B >= 1 && V >= 1, FINDB200_ERR_SHAPE, "field: need nfeet >= 1 and V >= 1 (got %d, %d)", B, V);
+    FB_REQUIRE((long long)B * V < (1ll << 31) / 16, FINDB200_ERR_SHAPE, "field: nfeet * V too large");
+    for (int i = 0; i < P_COUNT; ++i)
+        FB_REQUIRE(p->weight[i] && p->bias[i], FINDB200_ERR_ARG, "field: weight/bias %d is null", i);
+    FB_REQUIRE(p->fourier_B != nullptr, FINDB200_ERR_ARG, "field: fourier_B is null");
+    FB_REQUIRE(p->shapevec_size >= 0 && p->posevec_size >= 0 && p->texvec_size >= 0, FINDB200_ERR_SHAPE,
+               "field: negative latent size");
+    return 0;
+}
+
+static void fill_chain_common(ChainParams& C, const findb200_field_params* p, const Workspace& w, uint8_t* ws, int B, int V,
+                              int shared) {
+    memset(&C, 0, sizeof(C));
+    C.wpack = ws + w.wpack;
+    C.lay = make_layout();
+    C.B = B; C.V = V; C.tpf = w.tpf; C.tpf2 = w.tpf2; C.trunk_feet = w.trunk_feet; C.trunk_tiles = w.trunk_tiles;
+    C.shared = shared;
+    C.Bmat = p->fourier_B;
+    for (int i = 0; i < P_COUNT; ++i) C.bias[i] = p->bias[i];
+    C.biasfoot = (const float*)(ws + w.biasfoot);
+    C.enc = ws + w.enc; C.tact = ws + w.tact; C.hact = ws + w.hact; C.hdz = ws + w.hdz; C.doimg = ws + w.doimg;
+    C.tdz = ws + w.tdz;
+    C.avg_col = p->avg_col;
+    C.dovals = (const float*)(ws + w.dovals);
+    C.maxabs = (const uint32_t*)(ws + w.scal);
+}
+
+static int run_pack(const findb200_field_params* p, const Workspace& w, uint8_t* ws, cudaStream_t st) {
+    const PackLayout L = make_layout();
+    PackParams PP;
+    memset(&PP, 0, sizeof(PP));
+    PP.dst = ws + w.wpack;
+    const int in_dims[P_COUNT] = {kEnc, kW, kW, kW, kW, kW + p->shapevec_size + p->posevec_size, kW, kW, kW,
+                                  kW + p->texvec_size, kW, kW, kW};
+    const int out_dims[P_COUNT] = {kW, kW, kW, kW, kW, kW, kW, kW, 3, kW, kW, kW, 3};
+    int n = 0;
+    for (int i = 0; i < P_COUNT; ++i) {
+        PackJob& J = PP.j[n++];
+        J.src = p->weight[i]; J.ld = in_dims[i]; J.rows = out_dims[i]; J.kcols = (i == P_T0) ? kEnc : kW; J.col0 = 0;
+        J.transpose = 0; J.perm = (i == P_T0); J.img_rows = L.fwd[i].N; J.n_chunks = L.fwd[i].n_chunks; J.dst_off = L.fwd[i].off;
+    }
+    for (int i = 0; i < P_COUNT; ++i) {
+        if (i == P_T0) continue;
+        PackJob& J = PP.j[n++];
+        J.src = p->weight[i]; J.ld = in_dims[i]; J.rows = out_dims[i]; J.kcols = kW; J.col0 = 0;
+        J.transpose = 1; J.perm = 0; J.img_rows = 256; J.n_chunks = L.bwd[i].n_chunks; J.dst_off = L.bwd[i].off;
+    }
+    PP.n = n;
+    pack_weights_kernel<<<dim3(36, n), 256, 0, st>>>(PP);
+    FB_CUDA(cudaGetLastError());
+    return 0;
+}
+
+}  // namespace field
+}  // namespace fb
+
+using namespace fb;
+using namespace fb::field;
+
+extern "C" {
+
+size_t findb200_field_workspace_bytes(int nfeet, int V, int pos_shared, int for_backward) {
+    if (nfeet < 1 || V < 1) return 0;
+    return carve(nfeet, V, pos_shared, for_backward).total;
+}
+
+int findb200_field_forward(const findb200_field_params* p, const float* pos, int pos_shared, const float* z_shape,
+                           const float* z_pose, const float* z_tex, const float* reg, int nfeet, int V,
+                           int save_for_backward, float* disp, float* col, float* verts, void* ws_, size_t ws_bytes,
+                           void* stream) {
+    cudaStream_t st = (cudaStream_t)stream;
+    const int B = nfeet;
+    int rc = check_common(p, B, V);
+    if (rc) return rc;
+    FB_REQUIRE(pos && disp, FINDB200_ERR_ARG, "field_forward: pos/disp is null");
+    FB_REQUIRE((p->shapevec_size == 0 || z_shape) && (p->posevec_size == 0 || z_pose) && (p->texvec_size == 0 || z_tex),
+               FINDB200_ERR_ARG, "field_forward: a latent block has non-zero size but a null pointer");
+    const Workspace w = carve(B, V, pos_shared, save_for_backward);
+    FB_REQUIRE(ws_ && ws_bytes >= w.total, FINDB200_ERR_WORKSPACE, "field_forward: workspace too small (%zu < %zu bytes)",
+               ws_bytes, w.total);
+    uint8_t* ws = (uint8_t*)ws_;
+    const int sms = num_sms();
+
+    rc = run_pack(p, w, ws, st);
+    if (rc) return rc;
+    LatentBiasParams LB{p->weight[P_D1], p->bias[P_D1], p->weight[P_C1], p->bias[P_C1], z_shape, z_pose, z_tex,
+                        p->shapevec_size, p->posevec_size, p->texvec_size, B, (float*)(ws + w.biasfoot)};
+    latent_bias_kernel<<<dim3(B, 2), 256, 0, st>>>(LB);
+    FB_CUDA(cudaGetLastError());
+
+    ChainParams C;
+    fill_chain_common(C, p, w, ws, B, V, pos_shared);
+    C.save = save_for_backward;
+    C.pos = pos;
+    C.disp = disp; C.col = col; C.verts = verts; C.reg = reg;
+    // trunk: one tile per CTA while that still fills the machine poorly (latency), two when there are many tiles
+    {
+        const int nt = (w.trunk_tiles <= 2 * sms) ? 1 : 2;
+        C.n_items = w.trunk_tiles / nt;
+        rc = launch_chain(0, nt, C, sms, st);
+        if (rc) return rc;
+    }
+    {
+        C.heads_mask = col ? 3 : 1;
+        C.n_heads = col ? 2 : 1;
+        const int nt = 2;
+        C.n_items = C.n_heads * B * (w.tpf2 / nt);
+        rc = launch_chain(1, nt, C, sms, st);
+        if (rc) return rc;
+    }
+    return 0;
+}
+
+int findb200_field_backward(const findb200_field_params* p, const float* pos, int pos_shared, const float* z_shape,
+                            const float* z_pose, const float* z_tex, const float* reg, int nfeet, int V,
+                            const float* disp, const float* col, const float* grad_disp, const float* grad_col,
+                            const float* grad_verts, const findb200_field_grads* gw, float* gz_shape, float* gz_pose,
+                            float* gz_tex, float* greg, void* ws_, size_t ws_bytes, void* stream) {
+    cudaStream_t st = (cudaStream_t)stream;
+    const int B = nfeet;
+    int rc = check_common(p, B, V);
+    if (rc) return rc;
+    FB_REQUIRE(pos && disp, FINDB200_ERR_ARG, "field_backward: pos/disp is null");
+    FB_REQUIRE(!grad_col || col, FINDB200_ERR_ARG, "field_backward: grad_col given without col");
+    const Workspace w = carve(B, V, pos_shared, 1);
+    FB_REQUIRE(ws_ && ws_bytes >= w.total, FINDB200_ERR_WORKSPACE, "field_backward: workspace too small (%zu < %zu bytes)",
+               ws_bytes, w.total);
+    uint8_t* ws = (uint8_t*)ws_;
+    const int sms = num_sms();
+    const int frozen = gw == nullptr;
+    const int heads_mask = 1 | (grad_col ? 2 : 0);
+    const int n_heads = grad_col ? 2 : 1;
+    const size_t head_tiles = (size_t)B * w.tpf2;
+
+    // scalars, per-foot sums, column sums, d(pre-tanh) images start from zero
+    FB_CUDA(cudaMemsetAsync(ws + w.scal, 0, 1024, st));
+    FB_CUDA(cudaMemsetAsync(ws + w.regsums, 0, (size_t)B * 12 * 4, st));
+    FB_CUDA(cudaMemsetAsync(ws + w.colsum, 0, cs_total(B) * 4, st));
+    FB_CUDA(cudaMemsetAsync(ws + w.doimg, 0, (size_t)2 * head_tiles * kImgBytes, st));
+
+    GradPrepParams GP{pos, disp, col, reg, p->avg_col, grad_disp, grad_col, grad_verts, B, V, pos_shared,
+                      (float*)(ws + w.dovals), (uint32_t*)(ws + w.scal), (float*)(ws + w.regsums)};
+    grad_prep_kernel<<<dim3(cdiv(V, 256), B), 256, 0, st>>>(GP);
+    FB_CUDA(cudaGetLastError());
+
+    ChainParams C;
+    fill_chain_common(C, p, w, ws, B, V, pos_shared);
+    C.pos = pos; C.reg = reg;
+    C.heads_mask = heads_mask; C.n_heads = n_heads;
+    {
+        const int nt = 2;
+        C.n_items = n_heads * B * (w.tpf2 / nt);
+        rc = launch_chain(2, nt, C, sms, st);
+        if (rc) return rc;
+    }
+    float* colsum = (float*)(ws + w.colsum);
+    float* partial = (float*)(ws + w.partial);
+
+    DwParams D;
+    memset(&D, 0, sizeof(D));
+    int ng = 0;
+    int gemm_param[kMaxDwGemms];     // which parameter the GEMM feeds, and which K block of base.0
+    int gemm_kblock[kMaxDwGemms];
+    long long cost[kMaxDwGemms];
+    auto add = [&](const uint8_t* A, uint32_t atb, int a_imgs, const uint8_t* Bm, uint32_t btb, uint32_t boff, int b_imgs,
+                   int mh, int N, int feet, int afs, int bfs, float* cs, int csmode, int cscols, int prm, int kblock) {
+        DwGemm& g = D.g[ng];
+        g.A = A; g.Bm = Bm; g.a_tile_bytes = atb; g.b_tile_bytes = btb; g.b_img_off = boff; g.a_imgs = a_imgs; g.b_imgs = b_imgs;
+        g.mhalves = mh; g.N = N; g.feet = feet; g.tpf = w.tpf; g.a_foot_stride = afs; g.b_foot_stride = bfs;
+        g.colsum = cs; g.colsum_mode = csmode; g.colsum_cols = cscols;
+        gemm_param[ng] = prm; gemm_kblock[ng] = kblock;
+        cost[ng] = (long long)feet * w.tpf * (mh * 4 * (N >= 256 ? 4 : 1) + 4);
+        ++ng;
+    };
+    if (!frozen) {
+        rc = 0;
+        C.n_items = w.trunk_tiles / ((w.trunk_tiles <= 2 * sms) ? 1 : 2);
+        rc = launch_chain(3, (w.trunk_tiles <= 2 * sms) ? 1 : 2, C, sms, st);
+        if (rc) return rc;
+    }
+    for (int head = 0; head < 2; ++head) {
+        if (!(heads_mask & (1 << head))) continue;
+        const int base = head ? P_C1 : P_D1;
+        uint8_t* hact = ws + w.hact + (size_t)head * 3 * head_tiles * kTileBytes;
+        uint8_t* hdz = ws + w.hdz + (size_t)head * 3 * head_tiles * kTileBytes;
+        uint8_t* doimg = ws + w.doimg + (size_t)head * head_tiles * kImgBytes;
+        const uint8_t* h5 = ws + w.tact + (size_t)4 * w.trunk_tiles * kTileBytes;
+        if (frozen) {
+            // only the per-foot column sums of dZ1 are needed (latent-code gradients): stream A alone
+            add(hdz, kTileBytes, 4, h5, kTileBytes, 0, 0, 0, 256, B, w.tpf2, pos_shared ? 0 : w.tpf2,
+                colsum + cs_foot(head, B), 2, 256, -1, 0);
+            continue;
+        }
+        // layer 1: dZ1^T h5 (+ per-foot column sums)
+        add(hdz, kTileBytes, 4, h5, kTileBytes, 0, 4, 2, 256, B, w.tpf2, pos_shared ? 0 : w.tpf2, colsum + cs_foot(head, B), 2, 256,
+            base, 0);
+        // layers 2, 3: dZ_l^T a_{l-1}
+        for (int l = 1; l <= 2; ++l)
+            add(hdz + (size_t)l * head_tiles * kTileBytes, kTileBytes, 4, hact + (size_t)(l - 1) * head_tiles * kTileBytes,
+                kTileBytes, 0, 4, 2, 256, B, w.tpf2, w.tpf2, colsum + cs_head(head, l - 1, B), 1, 256, base + l, 0);
+        // output layer: do^T a3 (A = the 16-column d(pre-tanh) image, M' = 128 with rows 3.. ignored)
+        add(doimg, kImgBytes, 1, hact + (size_t)2 * head_tiles * kTileBytes, kTileBytes, 0, 4, 1, 256, B, w.tpf2, w.tpf2,
+            colsum + cs_out(head, B), 1, 16, base + 3, 0);
+    }
+    if (!frozen) {
+        uint8_t* tact = ws + w.tact;
+        uint8_t* tdz = ws + w.tdz;
+        uint8_t* enc = ws + w.enc;
+        for (int l = 4; l >= 1; --l)
+            add(tdz + (size_t)l * w.trunk_tiles * kTileBytes, kTileBytes, 4, tact + (size_t)(l - 1) * w.trunk_tiles * kTileBytes,
+                kTileBytes, 0, 4, 2, 256, w.trunk_feet, w.tpf2, w.tpf2, colsum + cs_trunk(l, B), 1, 256, P_T0 + l, 0);
+        for (int kb = 0; kb < 3; ++kb)
+            add(tdz, kTileBytes, 4, enc, kEncTileBytes, (uint32_t)kb * 4 * kImgBytes, kb < 2 ? 4 : 1, 2, kb < 2 ? 256 : 64,
+                w.trunk_feet, w.tpf2, w.tpf2, kb == 0 ? colsum + cs_trunk(0, B) : nullptr, kb == 0 ? 1 : 0, 256, P_T0, kb);
+    }
+    D.n_gemms = ng;
+    // CTA allocation proportional to cost, every GEMM at least one, at most kMaxDwCtas in total
+    long long total_cost = 0;
+    for (int i = 0; i < ng; ++i) total_cost += cost[i];
+    int budget = sms < kMaxDwCtas ? sms : kMaxDwCtas;
+    int n_ctas = 0;
+    for (int i = 0; i < ng; ++i) {
+        int n = total_cost > 0 ? (int)((cost[i] * budget) / total_cost) : 1;
+        const int units = D.g[i].feet * D.g[i].tpf;
+        if (n > units) n = units;
+        if (n < 1) n = 1;
+        D.g[i].ncta = n;
+        n_ctas += n;
+    }
+    while (n_ctas > kMaxDwCtas) {            // cannot happen with budget <= kMaxDwCtas - ng, kept as a guard
+        int big = 0;
+        for (int i = 1; i < ng; ++i) if (D.g[i].ncta > D.g[big].ncta) big = i;
+        FB_REQUIRE(D.g[big].ncta > 1, FINDB200_ERR_UNSUPPORTED, "field_backward: too many weight-gradient GEMMs");
+        --D.g[big].ncta; --n_ctas;
+    }
+    int c0 = 0;
+    for (int i = 0; i < ng; ++i) {
+        D.g[i].cta0 = c0;
+        D.g[i].partial = partial + (size_t)c0 * kW * kW;
+        c0 += D.g[i].ncta;
+    }
+    rc = launch_dw(D, n_ctas, st);
+    if (rc) return rc;
+
+    if (!frozen) {
+        ReduceParams R;
+        memset(&R, 0, sizeof(R));
+        R.maxabs = (const uint32_t*)(ws + w.scal);
+        const int in_dims[P_COUNT] = {kEnc, kW, kW, kW, kW, kW + p->shapevec_size + p->posevec_size, kW, kW, kW,
+                                      kW + p->texvec_size, kW, kW, kW};
+        int nj = 0;
+        for (int i = 0; i < ng; ++i) {
+            const int prm = gemm_param[i];
+            if (prm < 0) continue;
+            ReduceJob& J = R.j[nj++];
+            J.dst = gw->weight[prm]; J.partial = D.g[i].partial; J.dst_ld = in_dims[prm]; J.ncta = D.g[i].ncta;
+            J.rows = (prm == P_D4 || prm == P_C4) ? 3 : kW;
+            J.cols = kW; J.dst_col0 = 0; J.perm_kbase = -1; J.src_col0 = 0;
+            if (prm == P_T0) { J.perm_kbase = gemm_kblock[i] * 256; J.cols = gemm_kblock[i] < 2 ? 256 : 3; }
+        }
+        // parameters of a head that received no gradient: write zeros (ncta = 0 sums nothing)
+        for (int head = 0; head < 2; ++head) {
+            if (heads_mask & (1 << head)) continue;
+            const int base = head ? P_C1 : P_D1;
+            for (int l = 0; l < 4; ++l) {
+                ReduceJob& J = R.j[nj++];
+                J.dst = gw->weight[base + l]; J.partial = partial; J.dst_ld = in_dims[base + l]; J.ncta = 0;
+                J.rows = l == 3 ? 3 : kW; J.cols = kW; J.dst_col0 = 0; J.perm_kbase = -1; J.src_col0 = 0;
+            }
+        }
+        R.n = nj;
+        reduce_dw_kernel<<<dim3(64, nj), 256, 0, st>>>(R);
+        FB_CUDA(cudaGetLastError());
+    }
+
+    FinishParams F;
+    memset(&F, 0, sizeof(F));
+    F.maxabs = (const uint32_t*)(ws + w.scal);
+    F.colsum = colsum; F.regsums = (const float*)(ws + w.regsums);
+    F.Wd = p->weight[P_D1]; F.Wc = p->weight[P_C1];
+    F.z_shape = z_shape; F.z_pose = z_pose; F.z_tex = z_tex; F.reg = reg;
+    F.B = B; F.S = p->shapevec_size; F.Pz = p->posevec_size; F.T = p->texvec_size;
+    F.heads_mask = heads_mask; F.frozen = frozen; F.have_reg = (reg && grad_verts) ? 1 : 0;
+    if (gw) for (int i = 0; i < P_COUNT; ++i) { F.gW[i] = gw->weight[i]; F.gb[i] = gw->bias[i]; }
+    F.gz_shape = gz_shape; F.gz_pose = gz_pose; F.gz_tex = gz_tex; F.greg = greg;
+    int maxid = P_COUNT * kW;
+    const int Lmax = (F.S + F.Pz > F.T ? F.S + F.Pz : F.T);
+    if (kW * Lmax > maxid) maxid = kW * Lmax;
+    if (B * (F.S + F.Pz + F.T) > maxid) maxid = B * (F.S + F.Pz + F.T);
+    if (B > maxid) maxid = B;
+    finish_small_kernel<<<dim3(cdiv(maxid, 256), 5), 256, 0, st>>>(F);
+    FB_CUDA(cudaGetLastError());
+    return 0;
+}
+
+}  // extern "C"

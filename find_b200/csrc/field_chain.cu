@@ -1,0 +1,511 @@
+// find_b200/csrc/field_chain.cu — the "chain" kernels of the displacement field: a tile of 128 (or 2 x 128) rows
+// is pushed through a sequence of 256-wide GEMMs without leaving the SM.
+//
+//   TRUNK_FWD : encode xyz (Fourier features, fp32 sincos -> fp16) -> base.0 .. base.8 (+ReLU)      model.py:421-426
+//   HEAD_FWD  : trunk feature tile -> mlp_disp / mlp_col (latents folded into a per-foot bias)     model.py:428-451
+//               -> tanh epilogue, registration transform                                          model.py:481-488
+//   HEAD_BWD  : d(pre-tanh) -> dZ3 -> dZ2 -> dZ1 of one head (ReLU masks re-read from the saved activations)
+//   TRUNK_BWD : sum over feet/heads of dZ1 -> x W1h^T -> dZ of base.8 .. base.0
+//
+// Per CTA: warp 0 = weight/input producer (cp.async.bulk into a 3 x 32 KB ring), warp 1 = tcgen05.mma issuer,
+// warps 2.. = epilogue (4 warps per tile: TMEM -> registers -> bias/ReLU/mask -> fp16 tile image in shared memory,
+// which is the A operand of the next GEMM and is also bulk-stored to HBM for the weight-gradient kernel).
+// Activations of a tile live in shared memory (64 KB per tile, overwritten in place layer by layer) and the
+// accumulator [128 x 256] fp32 in TMEM (256 columns per tile).
+#include "field.cuh"
+#include "field_chain_params.cuh"
+
+namespace fb {
+namespace field {
+
+FB_DEVINL void named_bar_sync(int id, int count) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(count) : "memory"); }
+
+// power-of-two gradient scale that puts max |d(pre-tanh)| into [8, 16): fp16 operands keep full precision
+FB_DEVINL float grad_scale_from(uint32_t maxabs_bits) {
+    const float m = __uint_as_float(maxabs_bits);
+    if (!(m > 0.f) || !(m < 3.0e38f)) return 1.0f;
+    int e;
+    frexpf(m, &e);                       // m = f * 2^e, f in [0.5, 1)
+    return ldexpf(1.0f, 4 - e);          // m * scale in [8, 16)
+}
+
+FB_DEVINL uint32_t pack_h2(float a, float b) {
+    __half2 h = __floats2half2_rn(a, b);
+    return *reinterpret_cast<uint32_t*>(&h);
+}
+
+// ---- producer: stream one weight operand through the ring ------------------------------------------------
+FB_DEVINL void produce_gemm(const ChainParams& P, const GemmW& g, uint8_t* ring, uint64_t* bar_full, uint64_t* bar_empty,
+                            uint32_t& pcount, int c0, int c1) {
+    for (int c = c0; c < c1; ++c) {
+        const uint32_t s = pcount % kRing, use = pcount / kRing;
+        if (use > 0) mbar_wait(&bar_empty[s], (use - 1) & 1);
+        mbar_expect_tx(&bar_full[s], g.chunk_bytes);
+        bulk_g2s(ring + s * kWChunkBytes, P.wpack + g.off + (size_t)c * g.chunk_bytes, g.chunk_bytes, &bar_full[s]);
+        ++pcount;
+    }
+}
+
+// ---- MMA issuer: D[tile] (+)= A[tile](smem images) * W(ring) for chunks [c0, c1) ------------------------------
+template <int NT>
+FB_DEVINL void mma_gemm(const GemmW& g, uint32_t act_s, uint32_t ring_s, uint32_t tmem, uint64_t* bar_full,
+                        uint64_t* bar_empty, uint32_t& ccount, int c0, int c1, bool acc_init) {
+    const uint32_t idesc = umma_idesc_f16(128, g.N, false, false);
+    for (int c = c0; c < c1; ++c) {
+        const uint32_t s = ccount % kRing, use = ccount / kRing;
+        mbar_wait(&bar_full[s], use & 1);
+        tc_fence_after();
+        const int nk = (c == g.n_chunks - 1) ? g.k16_last : 4;
+#pragma unroll
+        for (int t = 0; t < NT; ++t) {
+            for (int k = 0; k < nk; ++k) {
+                const uint64_t ad = umma_desc(act_s + t * kTileBytes + (c - c0) * kImgBytes + k * 32, 16, 1024);
+                const uint64_t bd = umma_desc(ring_s + s * kWChunkBytes + k * 32, 16, 1024);
+                umma_f16(tmem + t * 256, ad, bd, idesc, (acc_init || c > c0 || k > 0) ? 1u : 0u);
+            }
+        }
+        umma_commit(&bar_empty[s]);
+        ++ccount;
+    }
+}
+
+// ---- epilogues (one thread = one row of the tile) ---------------------------------------------------------
+FB_DEVINL uint32_t img_row_off(int chunk32, int row) {   // byte offset of 16-B chunk `chunk32` (0..31) of `row`
+    return (uint32_t)(chunk32 >> 3) * kImgBytes + (uint32_t)row * 128u + (uint32_t)(((chunk32 & 7) ^ (row & 7)) << 4);
+}
+
+FB_DEVINL void epi_relu(uint32_t taddr, uint8_t* act_tile, int row, const float* __restrict__ bias) {
+#pragma unroll 1
+    for (int cc = 0; cc < 8; ++cc) {
+        uint32_t v[32];
+        tmem_ld32(taddr + cc * 32, v);
+        tmem_ld_wait();
+        const float4* b4 = reinterpret_cast<const float4*>(bias + cc * 32);
+#pragma unroll
+        for (int g = 0; g < 4; ++g) {
+            const float4 b0 = __ldg(b4 + g * 2), b1 = __ldg(b4 + g * 2 + 1);
+            uint4 pk;
+            pk.x = pack_h2(fmaxf(__uint_as_float(v[g * 8 + 0]) + b0.x, 0.f), fmaxf(__uint_as_float(v[g * 8 + 1]) + b0.y, 0.f));
+            pk.y = pack_h2(fmaxf(__uint_as_float(v[g * 8 + 2]) + b0.z, 0.f), fmaxf(__uint_as_float(v[g * 8 + 3]) + b0.w, 0.f));
+            pk.z = pack_h2(fmaxf(__uint_as_float(v[g * 8 + 4]) + b1.x, 0.f), fmaxf(__uint_as_float(v[g * 8 + 5]) + b1.y, 0.f));
+            pk.w = pack_h2(fmaxf(__uint_as_float(v[g * 8 + 6]) + b1.z, 0.f), fmaxf(__uint_as_float(v[g * 8 + 7]) + b1.w, 0.f));
+            *reinterpret_cast<uint4*>(act_tile + img_row_off(cc * 4 + g, row)) = pk;
+        }
+    }
+}
+
+FB_DEVINL uint32_t mask_pack(uint32_t a, float lo, float hi) {   // a = two saved fp16 activations (>= 0)
+    const float l = (a & 0x00007fffu) ? lo : 0.f;
+    const float h = (a & 0x7fff0000u) ? hi : 0.f;
+    return pack_h2(l, h);
+}
+
+// dZ = dA * [a > 0]; a is the saved forward activation tile (global, same image layout)
+FB_DEVINL void epi_mask(uint32_t taddr, uint8_t* act_tile, int row, const uint8_t* __restrict__ a_tile) {
+#pragma unroll 1
+    for (int cc = 0; cc < 8; ++cc) {
+        uint4 a[4];
+#pragma unroll
+        for (int g = 0; g < 4; ++g) a[g] = __ldg(reinterpret_cast<const uint4*>(a_tile + img_row_off(cc * 4 + g, row)));
+        uint32_t v[32];
+        tmem_ld32(taddr + cc * 32, v);
+        tmem_ld_wait();
+#pragma unroll
+        for (int g = 0; g < 4; ++g) {
+            uint4 pk;
+            pk.x = mask_pack(a[g].x, __uint_as_float(v[g * 8 + 0]), __uint_as_float(v[g * 8 + 1]));
+            pk.y = mask_pack(a[g].y, __uint_as_float(v[g * 8 + 2]), __uint_as_float(v[g * 8 + 3]));
+            pk.z = mask_pack(a[g].z, __uint_as_float(v[g * 8 + 4]), __uint_as_float(v[g * 8 + 5]));
+            pk.w = mask_pack(a[g].w, __uint_as_float(v[g * 8 + 6]), __uint_as_float(v[g * 8 + 7]));
+            *reinterpret_cast<uint4*>(act_tile + img_row_off(cc * 4 + g, row)) = pk;
+        }
+    }
+}
+
+// Fourier features of one row for encoded-input chunk c (64 internal columns), written to image slot `slot`.
+// chunk c < 8: [sin(2 pi r_f) f = 32c..32c+31 | cos(2 pi r_f) same f],  r_f = x.B[:,f]; chunk 8: [x, y, z, 0...]
+FB_DEVINL void encode_chunk(int c, float x, float y, float z, const float* __restrict__ Bm, uint8_t* slot_img, int row,
+                            uint8_t* g_img) {
+    if (c < 8) {
+#pragma unroll 1
+        for (int g = 0; g < 4; ++g) {
+            float s[8], co[8];
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                const int f = c * 32 + g * 8 + j;
+                const float r = fmaf(z, __ldg(Bm + 512 + f), fmaf(y, __ldg(Bm + 256 + f), x * __ldg(Bm + f)));
+                const float fr = r - rintf(r);                    // exact; |fr| <= 0.5
+                const float a = fr * 6.28318530717958647692f;
+                s[j] = __sinf(a);
+                co[j] = __cosf(a);
+            }
+            uint4 ps, pc;
+            ps.x = pack_h2(s[0], s[1]); ps.y = pack_h2(s[2], s[3]); ps.z = pack_h2(s[4], s[5]); ps.w = pack_h2(s[6], s[7]);
+            pc.x = pack_h2(co[0], co[1]); pc.y = pack_h2(co[2], co[3]); pc.z = pack_h2(co[4], co[5]); pc.w = pack_h2(co[6], co[7]);
+            const uint32_t os = (uint32_t)row * 128u + (uint32_t)((g ^ (row & 7)) << 4);
+            const uint32_t oc = (uint32_t)row * 128u + (uint32_t)(((g + 4) ^ (row & 7)) << 4);
+            *reinterpret_cast<uint4*>(slot_img + os) = ps;
+            *reinterpret_cast<uint4*>(slot_img + oc) = pc;
+            if (g_img) {
+                *reinterpret_cast<uint4*>(g_img + os) = ps;
+                *reinterpret_cast<uint4*>(g_img + oc) = pc;
+            }
+        }
+    } else {
+#pragma unroll
+        for (int g = 0; g < 8; ++g) {
+            uint4 p = make_uint4(0, 0, 0, 0);
+            if (g == 0) { p.x = pack_h2(x, y); p.y = pack_h2(z, 0.f); }
+            const uint32_t o = (uint32_t)row * 128u + (uint32_t)((g ^ (row & 7)) << 4);
+            *reinterpret_cast<uint4*>(slot_img + o) = p;
+            if (g_img) *reinterpret_cast<uint4*>(g_img + o) = p;
+        }
+    }
+}
+
+FB_DEVINL void add8(float (&acc)[8], uint4 x) {
+    const __half2* h = reinterpret_cast<const __half2*>(&x);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const float2 f = __half22float2(h[i]);
+        acc[2 * i] += f.x;
+        acc[2 * i + 1] += f.y;
+    }
+}
+
+// rotation of the registration transform: R = Rx(e0) Ry(e1) Rz(e2) (PyTorch3D euler_angles_to_matrix 'XYZ')
+FB_DEVINL void euler_xyz(const float* e, float (&R)[3][3]) {
+    float sa, ca, sb, cb, sc, cc;
+    sincosf(e[0], &sa, &ca); sincosf(e[1], &sb, &cb); sincosf(e[2], &sc, &cc);
+    R[0][0] = cb * cc;                 R[0][1] = -cb * sc;                R[0][2] = sb;
+    R[1][0] = sa * sb * cc + ca * sc;  R[1][1] = -sa * sb * sc + ca * cc; R[1][2] = -sa * cb;
+    R[2][0] = -ca * sb * cc + sa * sc; R[2][1] = ca * sb * sc + sa * cc;  R[2][2] = ca * cb;
+}
+
+template <int MODE, int NT>
+__global__ void __launch_bounds__(64 + 128 * NT, 1) chain_kernel(const __grid_constant__ ChainParams P) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+    uint8_t* act = smem;
+    uint8_t* ring = smem + NT * kTileBytes;
+    __shared__ __align__(8) uint64_t bar_full[kRing], bar_empty[kRing];
+    __shared__ __align__(8) uint64_t bar_act_ready, bar_acc_ready, bar_in_full, bar_act_free;
+    __shared__ uint32_t tmem_base_s;
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    if (tid == 0) {
+        for (int s = 0; s < kRing; ++s) { mbar_init(&bar_full[s], 1); mbar_init(&bar_empty[s], 1); }
+        mbar_init(&bar_act_ready, 128 * NT);
+        mbar_init(&bar_acc_ready, 1);
+        mbar_init(&bar_in_full, 1);
+        mbar_init(&bar_act_free, 1 + 128 * NT);
+        fence_barrier_init();
+    }
+    if (warp == 0) tmem_alloc(&tmem_base_s, NT * 256);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = tmem_base_s;
+    const int groups_per_foot = P.tpf2 / NT;
+    const int items_per_head = P.B * groups_per_foot;
+
+    // decode an item -> head, foot, first tile (heads) or first trunk tile (trunk)
+    auto decode = [&](int it, int& head, int& b, int& t0) {
+        if (MODE == TRUNK_FWD || MODE == TRUNK_BWD) {
+            head = 0; b = (it * NT) / P.tpf2; t0 = (it * NT) % P.tpf2;
+        } else {
+            const int hsel = it / items_per_head;
+            head = (P.heads_mask == 2) ? 1 : hsel;       // mask 1: disp only, 2: col only, 3: both (hsel = head)
+            const int r = it % items_per_head;
+            b = r / groups_per_foot; t0 = (r % groups_per_foot) * NT;
+        }
+    };
+
+    if (warp == 0) {
+        // ===================================== producer ===========================================
+        if (lane == 0) {
+            uint32_t pcount = 0, icount = 0;
+            for (int it = blockIdx.x; it < P.n_items; it += gridDim.x, ++icount) {
+                int head, b, t0;
+                decode(it, head, b, t0);
+                if (MODE == TRUNK_FWD) {
+                    for (int l = 0; l < 5; ++l) produce_gemm(P, P.lay.fwd[P_T0 + l], ring, bar_full, bar_empty, pcount, 0, P.lay.fwd[P_T0 + l].n_chunks);
+                } else if (MODE == HEAD_FWD) {
+                    if (icount > 0) mbar_wait(&bar_act_free, (icount - 1) & 1);
+                    mbar_expect_tx(&bar_in_full, NT * kTileBytes);
+                    for (int t = 0; t < NT; ++t) {
+                        const size_t tt = (size_t)(P.shared ? 0 : b) * P.tpf2 + t0 + t;
+                        bulk_g2s(act + t * kTileBytes, P.tact + ((size_t)4 * P.trunk_tiles + tt) * kTileBytes, kTileBytes, &bar_in_full);
+                    }
+                    const int base = head ? P_C1 : P_D1;
+                    for (int l = 0; l < 4; ++l) produce_gemm(P, P.lay.fwd[base + l], ring, bar_full, bar_empty, pcount, 0, P.lay.fwd[base + l].n_chunks);
+                } else if (MODE == HEAD_BWD) {
+                    const int base = head ? P_C1 : P_D1;
+                    for (int l = 3; l >= 1; --l) produce_gemm(P, P.lay.bwd[base + l], ring, bar_full, bar_empty, pcount, 0, P.lay.bwd[base + l].n_chunks);
+                } else {
+                    if (P.heads_mask & 1) produce_gemm(P, P.lay.bwd[P_D1], ring, bar_full, bar_empty, pcount, 0, 4);
+                    if (P.heads_mask & 2) produce_gemm(P, P.lay.bwd[P_C1], ring, bar_full, bar_empty, pcount, 0, 4);
+                    for (int l = 4; l >= 1; --l) produce_gemm(P, P.lay.bwd[P_T0 + l], ring, bar_full, bar_empty, pcount, 0, 4);
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ===================================== MMA issuer =========================================
+        if (lane == 0) {
+            uint32_t ccount = 0, n_act = 0, icount = 0;
+            const uint32_t act_s = smem_u32(act), ring_s = smem_u32(ring);
+            auto wait_act = [&]() { mbar_wait(&bar_act_ready, n_act & 1); ++n_act; tc_fence_after(); };
+            for (int it = blockIdx.x; it < P.n_items; it += gridDim.x, ++icount) {
+                int head, b, t0;
+                decode(it, head, b, t0);
+                if (MODE == TRUNK_FWD) {
+                    for (int p = 0; p < 3; ++p) {
+                        wait_act();
+                        mma_gemm<NT>(P.lay.fwd[P_T0], act_s, ring_s, tmem, bar_full, bar_empty, ccount, 4 * p, min(4 * p + 4, kEncChunks), p > 0);
+                        umma_commit(&bar_acc_ready);
+                    }
+                    for (int l = 1; l < 5; ++l) {
+                        wait_act();
+                        mma_gemm<NT>(P.lay.fwd[P_T0 + l], act_s, ring_s, tmem, bar_full, bar_empty, ccount, 0, 4, false);
+                        umma_commit(&bar_acc_ready);
+                    }
+                } else if (MODE == HEAD_FWD) {
+                    const int base = head ? P_C1 : P_D1;
+                    mbar_wait(&bar_in_full, icount & 1);
+                    tc_fence_after();
+                    for (int l = 0; l < 4; ++l) {
+                        if (l > 0) wait_act();
+                        mma_gemm<NT>(P.lay.fwd[base + l], act_s, ring_s, tmem, bar_full, bar_empty, ccount, 0, 4, false);
+                        umma_commit(&bar_acc_ready);
+                    }
+                    umma_commit(&bar_act_free);
+                } else if (MODE == HEAD_BWD) {
+                    const int base = head ? P_C1 : P_D1;
+                    for (int l = 3; l >= 1; --l) {
+                        wait_act();
+                        mma_gemm<NT>(P.lay.bwd[base + l], act_s, ring_s, tmem, bar_full, bar_empty, ccount, 0, P.lay.bwd[base + l].n_chunks, false);
+                        umma_commit(&bar_acc_ready);
+                    }
+                } else {
+                    bool first = true;
+                    if (P.heads_mask & 1) {
+                        wait_act();
+                        mma_gemm<NT>(P.lay.bwd[P_D1], act_s, ring_s, tmem, bar_full, bar_empty, ccount, 0, 4, false);
+                        umma_commit(&bar_acc_ready);
+                        first = false;
+                    }
+                    if (P.heads_mask & 2) {
+                        wait_act();
+                        mma_gemm<NT>(P.lay.bwd[P_C1], act_s, ring_s, tmem, bar_full, bar_empty, ccount, 0, 4, !first);
+                        umma_commit(&bar_acc_ready);
+                    }
+                    for (int l = 4; l >= 1; --l) {
+                        wait_act();
+                        mma_gemm<NT>(P.lay.bwd[P_T0 + l], act_s, ring_s, tmem, bar_full, bar_empty, ccount, 0, 4, false);
+                        umma_commit(&bar_acc_ready);
+                    }
+                }
+            }
+        }
+    } else {
+        // ===================================== epilogue warps =====================================
+        const int ew = warp - 2;
+        const int tl = ew >> 2;                      // tile of the group this warp serves
+        const int q = warp & 3;                      // TMEM lane quadrant this warp may touch
+        const int row = q * 32 + lane;
+        const int gt = (ew & 3) * 32 + lane;         // thread index inside the tile's 128-thread group
+        const bool leader = gt == 0;
+        uint8_t* act_tile = act + tl * kTileBytes;
+        const uint32_t taddr = tmem + ((uint32_t)(q * 32) << 16) + tl * 256;
+        uint32_t n_acc = 0;
+        auto wait_acc = [&]() { mbar_wait(&bar_acc_ready, n_acc & 1); ++n_acc; tc_fence_after(); };
+        auto before_overwrite = [&]() {              // pending bulk store of this tile must have read smem
+            if (leader) bulk_wait_read0();
+            named_bar_sync(1 + tl, 128);
+        };
+        auto publish = [&](uint8_t* gdst) {          // tile image complete: hand to the MMA proxy, store to HBM
+            fence_proxy_async();
+            if (gdst) {
+                named_bar_sync(1 + tl, 128);
+                if (leader) { bulk_s2g(gdst, act_tile, kTileBytes); bulk_commit(); }
+            }
+        };
+        auto signal_act = [&]() { tc_fence_before(); mbar_arrive(&bar_act_ready); };
+
+        for (int it = blockIdx.x; it < P.n_items; it += gridDim.x) {
+            int head, b, t0;
+            decode(it, head, b, t0);
+            const int t = t0 + tl;                   // tile inside the foot
+            const int vrow = t * kTile + row;        // vertex index of this thread's row
+            const bool valid = vrow < P.V;
+
+            if (MODE == TRUNK_FWD) {
+                const size_t tt = (size_t)b * P.tpf2 + t;
+                float x = 0.f, y = 0.f, z = 0.f;
+                if (valid) {
+                    const float* pp = P.pos + ((size_t)b * P.V + vrow) * 3;
+                    x = pp[0]; y = pp[1]; z = pp[2];
+                }
+                for (int p = 0; p < 3; ++p) {
+                    if (p == 0) before_overwrite(); else wait_acc();
+                    for (int c = 4 * p; c < min(4 * p + 4, kEncChunks); ++c)
+                        encode_chunk(c, x, y, z, P.Bmat, act_tile + (c - 4 * p) * kImgBytes, row,
+                                     P.save ? P.enc + tt * kEncTileBytes + (size_t)c * kImgBytes : nullptr);
+                    fence_proxy_async();
+                    signal_act();
+                }
+                for (int l = 0; l < 5; ++l) {
+                    wait_acc();
+                    before_overwrite();
+                    epi_relu(taddr, act_tile, row, P.bias[P_T0 + l]);
+                    publish((P.save || l == 4) ? P.tact + ((size_t)l * P.trunk_tiles + tt) * kTileBytes : nullptr);
+                    if (l < 4) signal_act();
+                }
+            } else if (MODE == HEAD_FWD) {
+                const int base = head ? P_C1 : P_D1;
+                const size_t ht = (size_t)b * P.tpf2 + t;
+                for (int l = 0; l < 3; ++l) {
+                    wait_acc();
+                    before_overwrite();
+                    epi_relu(taddr, act_tile, row, l == 0 ? P.biasfoot + ((size_t)head * P.B + b) * kW : P.bias[base + l]);
+                    publish(P.save ? P.hact + (((size_t)head * 3 + l) * P.B * P.tpf2 + ht) * kTileBytes : nullptr);
+                    signal_act();
+                }
+                wait_acc();
+                if (leader) bulk_wait_read0();
+                uint32_t v[32];
+                tmem_ld32(taddr, v);
+                tmem_ld_wait();
+                tc_fence_before();
+                mbar_arrive(&bar_act_free);          // act buffer and TMEM of this item are free for the next one
+                if (valid) {
+                    const float* bo = P.bias[base + 3];
+                    const float t0v = tanhf(__uint_as_float(v[0]) + __ldg(bo + 0));
+                    const float t1v = tanhf(__uint_as_float(v[1]) + __ldg(bo + 1));
+                    const float t2v = tanhf(__uint_as_float(v[2]) + __ldg(bo + 2));
+                    const size_t o = ((size_t)b * P.V + vrow) * 3;
+                    if (head == 0) {
+                        const float d0 = 0.1f * t0v, d1 = 0.1f * t1v, d2 = 0.1f * t2v;     // model.py:444
+                        P.disp[o] = d0; P.disp[o + 1] = d1; P.disp[o + 2] = d2;
+                        if (P.verts) {
+                            const float* pp = P.pos + ((size_t)(P.shared ? 0 : b) * P.V + vrow) * 3;
+                            float u0 = pp[0] + d0, u1 = pp[1] + d1, u2 = pp[2] + d2;
+                            if (P.reg) {                                                   // model.py:481-488
+                                const float* rg = P.reg + (size_t)b * 9;
+                                float R[3][3];
+                                euler_xyz(rg + 3, R);
+                                u0 *= rg[6]; u1 *= rg[7]; u2 *= rg[8];
+                                const float X0 = u0 * R[0][0] + u1 * R[1][0] + u2 * R[2][0] + rg[0];
+                                const float X1 = u0 * R[0][1] + u1 * R[1][1] + u2 * R[2][1] + rg[1];
+                                const float X2 = u0 * R[0][2] + u1 * R[1][2] + u2 * R[2][2] + rg[2];
+                                u0 = X0; u1 = X1; u2 = X2;
+                            }
+                            P.verts[o] = u0; P.verts[o + 1] = u1; P.verts[o + 2] = u2;
+                        }
+                    } else {
+                        const float a0 = P.avg_col ? P.avg_col[0] : 0.f, a1 = P.avg_col ? P.avg_col[1] : 0.f,
+                                    a2 = P.avg_col ? P.avg_col[2] : 0.f;
+                        P.col[o] = a0 + 0.5f * (1.f + t0v);                                // model.py:446,449-451
+                        P.col[o + 1] = a1 + 0.5f * (1.f + t1v);
+                        P.col[o + 2] = a2 + 0.5f * (1.f + t2v);
+                    }
+                }
+            } else if (MODE == HEAD_BWD) {
+                const size_t ht = (size_t)b * P.tpf2 + t;
+                // prologue: scaled d(pre-tanh) -> columns 0..2 of image 0 (K = 16 GEMM) and the dW operand image
+                before_overwrite();
+                {
+                    const float sc = grad_scale_from(*P.maxabs);
+                    float d0 = 0.f, d1 = 0.f, d2 = 0.f;
+                    if (valid) {
+                        const float4 dv = *reinterpret_cast<const float4*>(P.dovals + (((size_t)head * P.B + b) * P.V + vrow) * 4);
+                        d0 = dv.x * sc; d1 = dv.y * sc; d2 = dv.z * sc;
+                    }
+                    uint4 c0 = make_uint4(pack_h2(d0, d1), pack_h2(d2, 0.f), 0, 0), c1 = make_uint4(0, 0, 0, 0);
+                    const uint32_t o0 = (uint32_t)row * 128u + (uint32_t)((0 ^ (row & 7)) << 4);
+                    const uint32_t o1 = (uint32_t)row * 128u + (uint32_t)((1 ^ (row & 7)) << 4);
+                    *reinterpret_cast<uint4*>(act_tile + o0) = c0;
+                    *reinterpret_cast<uint4*>(act_tile + o1) = c1;
+                    uint8_t* gi = P.doimg + ((size_t)head * P.B * P.tpf2 + ht) * kImgBytes;
+                    *reinterpret_cast<uint4*>(gi + o0) = c0;
+                    *reinterpret_cast<uint4*>(gi + o1) = c1;
+                    fence_proxy_async();
+                    signal_act();
+                }
+                for (int l = 2; l >= 0; --l) {       // l indexes a_{l+1} / dZ_{l+1}
+                    wait_acc();
+                    before_overwrite();
+                    const size_t off = (((size_t)head * 3 + l) * P.B * P.tpf2 + ht) * kTileBytes;
+                    epi_mask(taddr, act_tile, row, P.hact + off);
+                    publish(P.hdz + off);
+                    if (l > 0) signal_act();
+                }
+            } else {   // TRUNK_BWD
+                const size_t tt = (size_t)b * P.tpf2 + t;
+                const int f0 = P.shared ? 0 : b, f1 = P.shared ? P.B : b + 1;
+                auto fill_sum = [&](int hd) {        // A = sum over feet of dZ1 of head hd (elementwise on images)
+                    for (int j = gt; j < kTileBytes / 16; j += 128) {
+                        float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+                        for (int f = f0; f < f1; ++f) {
+                            const uint8_t* src = P.hdz + (((size_t)hd * 3 + 0) * P.B * P.tpf2 + (size_t)f * P.tpf2 + t) * kTileBytes;
+                            add8(acc, __ldg(reinterpret_cast<const uint4*>(src) + j));
+                        }
+                        uint4 pk = make_uint4(pack_h2(acc[0], acc[1]), pack_h2(acc[2], acc[3]), pack_h2(acc[4], acc[5]), pack_h2(acc[6], acc[7]));
+                        *(reinterpret_cast<uint4*>(act_tile) + j) = pk;
+                    }
+                    fence_proxy_async();
+                };
+                bool filled = false;
+                for (int hd = 0; hd < 2; ++hd) {
+                    if (!(P.heads_mask & (1 << hd))) continue;
+                    if (!filled) before_overwrite(); else { wait_acc(); named_bar_sync(1 + tl, 128); }
+                    fill_sum(hd);
+                    signal_act();
+                    filled = true;
+                }
+                for (int l = 4; l >= 0; --l) {
+                    wait_acc();
+                    before_overwrite();
+                    const size_t off = ((size_t)l * P.trunk_tiles + tt) * kTileBytes;
+                    epi_mask(taddr, act_tile, row, P.tact + off);
+                    publish(P.tdz + off);
+                    if (l > 0) signal_act();
+                }
+            }
+        }
+        if (leader) bulk_wait0();
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 0) tmem_dealloc(tmem, NT * 256);
+}
+
+// ---- launch ---------------------------------------------------------------------------------------------
+template <int MODE, int NT>
+static int launch_chain_t(const ChainParams& P, int sms, cudaStream_t st) {
+    const int smem = NT * kTileBytes + kRing * kWChunkBytes + 1024;
+    FB_CUDA(cudaFuncSetAttribute(chain_kernel<MODE, NT>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    int grid = P.n_items < sms ? P.n_items : sms;
+    if (grid <= 0) return 0;
+    chain_kernel<MODE, NT><<<grid, 64 + 128 * NT, smem, st>>>(P);
+    FB_CUDA(cudaGetLastError());
+    return 0;
+}
+
+int launch_chain(int mode, int nt, const ChainParams& P, int sms, cudaStream_t st) {
+    switch (mode * 2 + (nt - 1)) {
+        case 0: return launch_chain_t<TRUNK_FWD, 1>(P, sms, st);
+        case 1: return launch_chain_t<TRUNK_FWD, 2>(P, sms, st);
+        case 2: return launch_chain_t<HEAD_FWD, 1>(P, sms, st);
+        case 3: return launch_chain_t<HEAD_FWD, 2>(P, sms, st);
+        case 4: return launch_chain_t<HEAD_BWD, 1>(P, sms, st);
+        case 5: return launch_chain_t<HEAD_BWD, 2>(P, sms, st);
+        case 6: return launch_chain_t<TRUNK_BWD, 1>(P, sms, st);
+        case 7: return launch_chain_t<TRUNK_BWD, 2>(P, sms, st);
+    }
+    set_error("launch_chain: bad mode %d nt %d", mode, nt);
+    return FINDB200_ERR_ARG;
+}
+
+}  // namespace field
+}  // namespace fb

@@ -61,6 +61,51 @@ int findb200_chamfer_backward(const float* x, const float* y, const int64_t* x_l
                               float grad_scale, float* grad_x, float* grad_y, void* stream);
 
 /* ------------------------------------------------------------------------------------------------------
+ * Neural displacement field   (replaces NeuralDisplacementField.forward + its autograd,
+ *   src/model/model.py:393-453, the latent concat model.py:428-437, and the registration transform of
+ *   get_meshes, model.py:481-491; called from ModelWithLoss.forward model.py:1009 and TextureLossGTSpace
+ *   src/model/losses.py:50).  fp16 tensor-core GEMMs (tcgen05, fp32 accumulate), fp32 everywhere else.
+ *
+ * Parameter order in weight[] / bias[]: base.0,2,4,6,8 | mlp_disp.0,2,4,6 | mlp_col.0,2,4,6, each an
+ * nn.Linear weight [out,in] / bias [out] exactly as in the reference state_dict (model.py:250-257,351-371).
+ * mlp_disp.0 has in = 256 + shapevec_size + posevec_size, mlp_col.0 has in = 256 + texvec_size.
+ * ------------------------------------------------------------------------------------------------------ */
+typedef struct findb200_field_params {
+    const float* weight[13];
+    const float* bias[13];
+    const float* fourier_B;   /* [3,256] Gaussian matrix of FourierFeatureTransform (fourier_feature_transform.py:23-26) */
+    const float* avg_col;     /* [3] added to col, or NULL (model.py:449-451) */
+    int shapevec_size, posevec_size, texvec_size;   /* widths of the latent blocks (0 = block absent) */
+} findb200_field_params;
+
+typedef struct findb200_field_grads {   /* same order and shapes as findb200_field_params; every entry is overwritten */
+    float* weight[13];
+    float* bias[13];
+} findb200_field_grads;
+
+/* Scratch + saved-for-backward storage.  A forward with save_for_backward = 1 fills it; the matching backward
+ * must be given the same, untouched buffer. */
+size_t findb200_field_workspace_bytes(int nfeet, int V, int pos_shared, int for_backward);
+
+/* pos: [V,3] if pos_shared (template shared by all feet, model.py:404-406,473-477) else [nfeet,V,3].
+ * z_*: [nfeet, size] latent rows.  reg: [nfeet,9] = [t(3), euler XYZ(3), scale(3)] or NULL.
+ * Outputs [nfeet,V,3]: disp = 0.1 tanh(.), col = 0.5 (1 + tanh(.)) (+avg_col) (NULL: colour head skipped),
+ * verts = ((pos + disp) * scale) @ R + t (NULL: skipped; without reg: pos + disp). */
+int findb200_field_forward(const findb200_field_params* p, const float* pos, int pos_shared, const float* z_shape,
+                           const float* z_pose, const float* z_tex, const float* reg, int nfeet, int V,
+                           int save_for_backward, float* disp, float* col, float* verts, void* workspace,
+                           size_t workspace_bytes, void* stream);
+
+/* Gradients of sum(grad_disp*disp) + sum(grad_col*col) + sum(grad_verts*verts) (each grad_* may be NULL).
+ * disp / col: the forward outputs.  gw NULL = frozen MLP (latent-code fitting, src/train/train.py:218-224):
+ * only gz_* and greg are produced.  gz_*: [nfeet,size]; greg: [nfeet,9]; NULL outputs are skipped. */
+int findb200_field_backward(const findb200_field_params* p, const float* pos, int pos_shared, const float* z_shape,
+                            const float* z_pose, const float* z_tex, const float* reg, int nfeet, int V,
+                            const float* disp, const float* col, const float* grad_disp, const float* grad_col,
+                            const float* grad_verts, const findb200_field_grads* gw, float* gz_shape, float* gz_pose,
+                            float* gz_tex, float* greg, void* workspace, size_t workspace_bytes, void* stream);
+
+/* ------------------------------------------------------------------------------------------------------
  * Diagnostics: one-CTA tcgen05 self-test of the shared-memory image / descriptor / TMEM conventions used by
  * the field kernels (mode 0: K-major operands, forward and dX shape; mode 1: MN-major operands, dW shape).
  * a_img / b_img are fp16 swizzled tile images (see csrc/umma_selftest.cu); d_out is fp32 [128][256].

@@ -48,18 +48,39 @@ def fourier_encode(x: torch.Tensor, B: torch.Tensor) -> torch.Tensor:
     return out.reshape(*shp[:-1], out.shape[-1])
 
 
-def _mlp(x, p, names):
-    for i, n in enumerate(names):
-        x = torch.nn.functional.linear(x, p[n + ".weight"], p[n + ".bias"])
-        if i < len(names) - 1:
-            x = torch.relu(x)
-    return x
+def _q(x: torch.Tensor, operand_dtype) -> torch.Tensor:
+    """Round a GEMM operand to `operand_dtype` with a straight-through gradient (identity when None).
+
+    operand_dtype=torch.float16 restates what the sm_100a kernels feed the tensor cores (fp16 operands, fp32
+    accumulate; csrc/field_chain.cu): the "rounding-matched" oracle used to check the backward kernels exactly,
+    because ReLU masks of a reduced-precision forward legitimately differ from the fp32 forward's near z = 0."""
+    if operand_dtype is None:
+        return x
+    return x + (x.to(operand_dtype).to(x.dtype) - x).detach()
+
+
+def _lin(x, p, n, od):
+    return torch.nn.functional.linear(_q(x, od), _q(p[n + ".weight"], od), p[n + ".bias"])
+
+
+def _head(x, lat, p, names, od):
+    """mlp_disp / mlp_col on cat([x, lat]) (model.py:428-440); the latent columns stay fp32 in the kernels."""
+    W = p[names[0] + ".weight"]
+    h = torch.nn.functional.linear(_q(x, od), _q(W[:, :x.shape[-1]], od), p[names[0] + ".bias"])
+    if lat is not None:
+        h = h + torch.nn.functional.linear(lat, W[:, x.shape[-1]:])
+    h = torch.relu(h)
+    for n in names[1:-1]:
+        h = torch.relu(_lin(h, p, n, od))
+    return _lin(h, p, names[-1], od)
 
 
 def field_forward(p: Dict[str, torch.Tensor], B: torch.Tensor, pos: torch.Tensor,
                   shapevec: Optional[torch.Tensor] = None, texvec: Optional[torch.Tensor] = None,
-                  posevec: Optional[torch.Tensor] = None, avg_col: Optional[torch.Tensor] = None):
-    """model.py:393-453.  pos [B or 1, V, 3]; latents [B, 100] or None -> {'disp','col'} [B,V,3]."""
+                  posevec: Optional[torch.Tensor] = None, avg_col: Optional[torch.Tensor] = None,
+                  operand_dtype=None):
+    """model.py:393-453.  pos [B or 1, V, 3]; latents [B, 100] or None -> {'disp','col'} [B,V,3].
+    operand_dtype=None is the reference arithmetic (fp32 / whatever dtype the inputs have); see _q."""
     batch, npts, _ = pos.shape
     if batch == 1 and shapevec is not None:
         batch = shapevec.shape[0]
@@ -68,17 +89,11 @@ def field_forward(p: Dict[str, torch.Tensor], B: torch.Tensor, pos: torch.Tensor
     shapevec, posevec, texvec = ex(shapevec), ex(posevec), ex(texvec)
     x = fourier_encode(pos, B)
     for n in TRUNK:                                         # every trunk Linear is followed by ReLU
-        x = torch.relu(torch.nn.functional.linear(x, p[n + ".weight"], p[n + ".bias"]))
-    disp_in = x
-    if shapevec is not None:
-        disp_in = torch.cat([disp_in, shapevec], dim=-1)
-    if posevec is not None:
-        disp_in = torch.cat([disp_in, posevec], dim=-1)
-    col_in = x
-    if texvec is not None:
-        col_in = torch.cat([col_in, texvec], dim=-1)
-    disp = 0.1 * torch.tanh(_mlp(disp_in, p, DISP))
-    col = 0.5 * (1 + torch.tanh(_mlp(col_in, p, COL)))
+        x = torch.relu(_lin(x, p, n, operand_dtype))
+    lat_d = [z for z in (shapevec, posevec) if z is not None]    # disp_in = [x, shape, pose] (model.py:428-433)
+    lat_d = torch.cat(lat_d, dim=-1) if lat_d else None
+    disp = 0.1 * torch.tanh(_head(x, lat_d, p, DISP, operand_dtype))
+    col = 0.5 * (1 + torch.tanh(_head(x, texvec, p, COL, operand_dtype)))   # col_in = [x, tex] (model.py:435-437)
     if avg_col is not None:
         col = avg_col[None, None, :] + col
     return {"disp": disp, "col": col}
@@ -153,4 +168,42 @@ def random_params(seed: int = 0, dtype=torch.float32) -> Dict[str, torch.Tensor]
         p[n + ".weight"] = ((torch.rand(o, i, generator=g) * 2 - 1) * k).to(dtype)
         p[n + ".bias"] = ((torch.rand(o, generator=g) * 2 - 1) * k).to(dtype)
     p["mlp_disp.6.weight"] = (torch.randn(3, 256, generator=g) * 0.05).to(dtype)
+    return p
+
+
+def kinkfree_params(seed: int, Bmat: torch.Tensor, pos: torch.Tensor, shapevec, posevec, texvec,
+                    sigma: float = 0.2, margin: float = 6.0) -> Dict[str, torch.Tensor]:
+    """Parameters for which NO ReLU pre-activation of the given inputs is near zero (every unit sits `margin`
+    standard deviations on one side), so that a reduced-precision forward has exactly the masks of the fp32 forward
+    and gradients can be compared at rounding-error level.  (With ordinary weights ~1e-4 of the pre-activations
+    change sign under fp16/tf32/bf16 operand rounding and each flip changes a gradient term by 100 %.)"""
+    p = random_params(seed)
+    g = torch.Generator().manual_seed(seed + 1)
+    npts = pos.shape[1]
+    nb = shapevec.shape[0]
+    ex = lambda z: z.unsqueeze(1).expand(-1, npts, -1)
+    x = fourier_encode(pos.expand(nb, -1, -1), Bmat)
+
+    def fix(name, inp):
+        W = p[name + ".weight"]
+        z = torch.nn.functional.linear(inp, W)
+        s = z.reshape(-1, z.shape[-1]).std(0).clamp_min(1e-6)
+        W = W * (sigma / s)[:, None]
+        z = torch.nn.functional.linear(inp, W)
+        mu = z.reshape(-1, z.shape[-1]).mean(0)
+        sign = (torch.rand(W.shape[0], generator=g) < 0.5).float() * 2 - 1
+        p[name + ".weight"] = W.contiguous()
+        p[name + ".bias"] = (sign * margin * sigma - mu).contiguous()
+        return torch.relu(z + p[name + ".bias"])
+
+    for n in TRUNK:
+        x = fix(n, x)
+    for names, lat in ((DISP, torch.cat([ex(shapevec), ex(posevec)], -1)), (COL, ex(texvec))):
+        h = fix(names[0], torch.cat([x, lat], -1))
+        for n in names[1:-1]:
+            h = fix(n, h)
+        W = p[names[-1] + ".weight"]
+        z = torch.nn.functional.linear(h, W)
+        p[names[-1] + ".weight"] = (W * (0.5 / z.std().clamp_min(1e-6))).contiguous()
+        p[names[-1] + ".bias"] = (-torch.nn.functional.linear(h, p[names[-1] + ".weight"]).reshape(-1, 3).mean(0)).contiguous()
     return p
