@@ -1,0 +1,407 @@
+#!/usr/bin/env python
+"""bench.py — FIND field + Chamfer train-step throughput on B200 (BASELINE.json metric), one process per GPU.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload cfg2] [--impl reference]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port P \
+           bench.py --gpus N --steps K --warmup W
+
+A "step" = latent-row gather -> field forward on the shared template -> registration transform -> bidirectional Chamfer
+against the target clouds (+ colour MSE) -> backward of all of it incl. dW / latent / reg gradients -> (N > 1) one
+allreduce of the flat MLP-gradient bucket.  Optimiser excluded.  Weak scaling: every rank owns
+`feet_per_gpu` feet of the global batch.  Prints ONE JSON line on rank 0 (contract in the task statement):
+  value      foot-vertices/s, inputs resident in HBM, CUDA events per step, L2 flushed between steps, max over ranks
+  e2e        same metric through the public host-facing call (TrainStep.step_from_host): pinned-host inputs copied
+             H2D and the loss read back D2H inside the timed region, every step
+  roofline   the dominant kernel of the step, timed live with CUDA events by the library's launch profiler
+  cpu_baseline  the CPU oracle port (oracle/step_oracle.py) timed on this box's host cores on a bounded sample
+`--impl reference` times that CPU port as its own arm (the reference is pure Python + PyTorch3D and cannot travel to
+the GPU box; see DESIGN.md "Reference arm").
+"""
+from __future__ import annotations
+
+import argparse
+import ctypes
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+import torch  # noqa: E402
+
+METRIC = "field+Chamfer train-step foot-vertices/s"
+UNIT = "vertices/s"
+
+WORKLOADS = {
+    # name: (feet per GPU, V, P2, frozen_mlp)   — BASELINE.json configs
+    "cfg2": dict(feet=8, V=10242, P2=10000, frozen=False, desc="FIND field fwd+bwd+Chamfer, batch 8 feet, 10k verts, 1xB200"),
+    "cfg3": dict(feet=8, V=10242, P2=20000, frozen=False, desc="batch 64 feet, 10k verts, 20k target points, foot-batch sharded (8 feet/GPU)"),
+    "cfg4": dict(feet=4, V=50000, P2=100000, frozen=False, desc="high-res template 50k verts, 100k target points, batch 32 (4 feet/GPU)"),
+    "cfg5": dict(feet=32, V=10242, P2=10000, frozen=True, desc="latent-code fitting (frozen MLP), batch 256 feet (32 feet/GPU)"),
+}
+
+# algorithmic MACs of the tensor-core kernels (the latent columns of mlp_*.0 are folded into
+# a per-foot bias and x.B is done with FMAs, so neither is credited)
+MAC_TRUNK_FWD = 515 * 256 + 4 * 65536            # per template vertex
+MAC_HEAD_FWD = 3 * 65536 + 768                   # per foot-vertex per head
+MAC_HEAD_BWD = 768 + 2 * 65536                   # dX chain of one head
+MAC_TRUNK_BWD = 2 * 65536 + 4 * 65536            # both heads' dX into the trunk + 4 trunk layers
+MAC_DW_HEAD = 3 * 65536 + 768                    # per foot-vertex per head
+MAC_DW_TRUNK = 4 * 65536 + 515 * 256             # per template vertex
+FLOP_PER_PAIR = 8                                # 3 sub + 1 mul + 2 fma(=4) ... counted as 8 flop / pair-evaluation (§8(d))
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md recipe)."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.index, self.proc, self.lines = index, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"], stdout=subprocess.PIPE,
+                                         stderr=subprocess.DEVNULL, text=True)
+            self.th = threading.Thread(target=self._read, daemon=True)
+            self.th.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
+        sm, smax, reasons, power = [], [], set(), []
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                sm.append(float(f[0])); smax.append(float(f[1])); power.append(float(f[2]))
+            except ValueError:
+                continue
+            for n, v in zip(names, f[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        # "under load" = samples in the upper half of the observed clock range (idle samples sit at 120-300 MHz)
+        load = [c for c in sm if c >= 0.5 * max(sm)] if sm else []
+        return {"sm_mhz": statistics.median(load) if load else None, "sm_max_mhz": max(smax) if smax else None,
+                "power_w_max": max(power) if power else None, "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def load_peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        with open(path) as fh:
+            d = json.load(fh)
+        return dict(hbm_gbs=d["hbm_gbs"], bf16_burst=d["bf16_tflops"], bf16_sustained=d["bf16_tflops_sustained"],
+                    source="measured (MEASURED_PEAKS.json)")
+    return dict(hbm_gbs=6650.0, bf16_burst=1590.0, bf16_sustained=1400.0, source="fallback (B200_PROFILING.md)")
+
+
+# ---------------------------------------------------------------------------------------------------------------
+def build_job(wl, rank, world, device):
+    """Model + TrainStep + this rank's host-side inputs (pinned)."""
+    from find_b200 import synthetic as syn
+    from find_b200.field import NeuralDisplacementField
+    from find_b200.step import TrainStep
+    feet, V, P2 = wl["feet"], wl["V"], wl["P2"]
+    global_feet = feet * world
+    foot0 = rank * feet
+    model = NeuralDisplacementField(use_shapevec=True, use_texvec=True, use_posevec=True, train_size=global_feet,
+                                    val_size=1, shapevec_size=100, texvec_size=100, posevec_size=100, device=device)
+    tv, tf = syn.make_template(V)
+    model.set_template(tv, tf)
+    syn.randomise_last_disp_layer(model.mlp_disp[-1], seed=0)
+    lat = syn.make_latents(feet, foot0)
+    with torch.no_grad():
+        for k in ("shapevec", "posevec", "texvec", "reg"):
+            getattr(model, k).data[foot0:foot0 + feet] = lat[k].to(device)
+    step = TrainStep(model, feet, P2, with_colour=True, frozen_mlp=wl["frozen"])
+    host = dict(idx=torch.arange(foot0, foot0 + feet, dtype=torch.int64).pin_memory(),
+                target=syn.make_targets(feet, P2, foot0).pin_memory(),
+                col_target=syn.make_col_target(feet, V, foot0).pin_memory())
+    return model, step, host
+
+
+def kernel_flops(name, wl, tpf_pad_rows=None):
+    """Algorithmic FLOPs of ONE launch of a named kernel for this rank's workload (None: not a math kernel)."""
+    B, V, P2 = wl["feet"], wl["V"], wl["P2"]
+    fv = B * V
+    if name == "trunk_fwd": return 2.0 * MAC_TRUNK_FWD * V
+    if name == "head_fwd": return 2.0 * MAC_HEAD_FWD * fv * 2
+    if name == "head_bwd": return 2.0 * MAC_HEAD_BWD * fv * 2
+    if name == "trunk_bwd": return 2.0 * MAC_TRUNK_BWD * V
+    if name == "dw_gemms":
+        return 2.0 * (MAC_DW_HEAD * fv * 2 + MAC_DW_TRUNK * V) if not wl["frozen"] else None
+    if name == "knn_main": return float(FLOP_PER_PAIR) * 2.0 * B * V * P2
+    return None
+
+
+def run_ours(args, wl, rank, world, local_rank):
+    import torch.distributed as dist
+    from find_b200 import _lib
+    from find_b200.parallel import ShardedTrainStep
+    device = torch.device("cuda", local_rank)
+    torch.cuda.set_device(device)
+    lib = _lib.load()
+    peaks = load_peaks()
+    model, step, host = build_job(wl, rank, world, device)
+    sharded = ShardedTrainStep(step, wl["feet"] * world)
+    feet, V, P2 = wl["feet"], wl["V"], wl["P2"]
+    fv_global = feet * world * V
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=device)     # > 126 MB L2
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize(device)
+
+    def max_over_ranks(x: float) -> float:
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device=device)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    step.load_inputs(host["idx"], host["target"], host["col_target"])
+    for _ in range(max(args.warmup, 3)):
+        sharded.run()
+    barrier()
+
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+
+    # ---- (1) device-resident: K steps, CUDA events around each, L2 flushed between ------------------------------
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    barrier()
+    t_wall0 = time.perf_counter()
+    for a, b in ev:
+        flush.zero_()
+        a.record()
+        sharded.run()
+        b.record()
+    barrier()
+    t_wall = time.perf_counter() - t_wall0
+    ms_dev = sum(a.elapsed_time(b) for a, b in ev)
+    ms_dev = max_over_ranks(ms_dev)
+    ms_per_step = ms_dev / args.steps
+    loss3 = step.loss3.tolist()
+
+    # ---- (2) end to end through the public host-facing call: H2D inputs + D2H loss inside the timed region ------
+    for _ in range(2):
+        step.step_from_host(host["idx"], host["target"], host["col_target"])
+    barrier()
+    e2e_s = 0.0
+    for _ in range(args.steps):
+        flush.zero_()
+        torch.cuda.synchronize(device)
+        t0 = time.perf_counter()
+        step.load_inputs(host["idx"], host["target"], host["col_target"])
+        sharded.run()
+        losses = step.loss3.tolist()              # D2H + sync (trainer.py:128-130 reads the losses every step)
+        e2e_s += time.perf_counter() - t0
+    barrier()
+    e2e_s = max_over_ranks(e2e_s)
+    h2d = host["idx"].numel() * 8 + host["target"].numel() * 4 + host["col_target"].numel() * 4
+    clocks = sampler.stop() if rank == 0 else None
+
+    # ---- (3) live per-kernel timing (library launch profiler, non-graph enqueue, L2 flushed between steps) -----
+    step.use_graph = False
+    n_prof = 5
+    lib.findb200_profile_enable(1)
+    for _ in range(n_prof):
+        flush.zero_()
+        sharded.run()
+    torch.cuda.synchronize(device)
+    buf = ctypes.create_string_buffer(1 << 16)
+    nbytes = lib.findb200_profile_read(buf, len(buf))
+    lib.findb200_profile_enable(0)
+    step.use_graph = True
+    kernels = []
+    for ln in buf.value.decode().splitlines() if nbytes > 0 else []:
+        name, cnt, tot = ln.split(",")
+        kernels.append(dict(name=name, launches_per_step=int(cnt) / n_prof, ms_per_step=float(tot) / n_prof))
+    launches = int(round(sum(k["launches_per_step"] for k in kernels)))
+    prof_total = sum(k["ms_per_step"] for k in kernels) or 1.0
+    fp32_peak = None
+    try:
+        scratch = torch.zeros(16, device=device)
+        blocks, iters = torch.cuda.get_device_properties(device).multi_processor_count * 8, 2048
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        lib.findb200_fp32_peak(1, blocks, iters, _lib.ptr(scratch), _lib.stream_ptr(device))
+        e0.record()
+        lib.findb200_fp32_peak(1, blocks, iters, _lib.ptr(scratch), _lib.stream_ptr(device))
+        e1.record()
+        torch.cuda.synchronize(device)
+        fp32_peak = blocks * 256 * iters * 64 * 2 * 2 / (e0.elapsed_time(e1) * 1e-3) / 1e12
+    except Exception:
+        pass
+    for k in kernels:
+        k["share"] = k["ms_per_step"] / prof_total
+        fl = kernel_flops(k["name"], wl)
+        if fl is not None and k["ms_per_step"] > 0:
+            k["tflops"] = fl / (k["ms_per_step"] * 1e-3) / 1e12
+            if k["name"] == "knn_main":
+                k["bound"], k["peak"] = "fp32", fp32_peak
+            else:
+                k["bound"], k["peak"] = "tensor", peaks["bf16_sustained"]
+            k["frac"] = k["tflops"] / k["peak"] if k["peak"] else None
+    math_k = [k for k in kernels if "tflops" in k]
+    dom = max(math_k, key=lambda k: k["ms_per_step"]) if math_k else None
+    roofline = None
+    if dom is not None:
+        roofline = dict(kernel=dom["name"], bound=dom["bound"], achieved=round(dom["tflops"], 2), peak=dom["peak"],
+                        unit="TFLOP/s", frac=round(dom["frac"], 4) if dom["frac"] else None, traffic=None,
+                        kernel_ms=round(dom["ms_per_step"], 4), share_of_step=round(dom["share"], 3),
+                        peak_source=("findb200_fp32_peak FFMA2 probe, same run" if dom["bound"] == "fp32"
+                                     else peaks["source"] + " bf16_tflops_sustained (fp16 operands, same tensor rate)"))
+
+    out = {
+        "metric": METRIC, "value": fv_global / (ms_per_step * 1e-3), "unit": UNIT, "n_gpus": world,
+        "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms_per_step, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "fp16 tensor-core operands / fp32 accumulate (field), fp32 (Chamfer)",
+        "data": "synthetic", "impl": "find_b200",
+        "config": {"workload": f"{args.workload}: {wl['desc']}", "feet_per_gpu": feet, "global_feet": feet * world,
+                   "verts": V, "target_points": P2, "frozen_mlp": wl["frozen"], "parallelism": f"dp{world} (foot-batch sharding)",
+                   "l2": "flushed between steps (256 MiB memset outside the event pairs)", "cuda_graph": True,
+                   "loss": "1e4*chamfer(verts,target) + 1*mse(col,col_target)"},
+        "e2e": {"value": fv_global / (e2e_s / args.steps), "unit": UNIT, "h2d_bytes_per_step": h2d,
+                "d2h_bytes_per_step": 12, "ms_per_step": e2e_s / args.steps * 1e3,
+                "api": "find_b200.step.TrainStep.step_from_host (pinned host -> H2D -> graph replay -> D2H loss)"},
+        "gpu_launches": launches * args.steps,
+        "gpu_launches_per_step": launches,
+        "roofline": roofline,
+        "kernels": [{k2: (round(v, 4) if isinstance(v, float) else v) for k2, v in k.items()} for k in kernels],
+        "loss": {"total": loss3[0], "chamfer": loss3[1], "colour_mse": loss3[2]},
+        "wall_s_timed_region": t_wall,
+        "clocks": clocks,
+    }
+    if rank == 0 and world == 1 and not args.skip_cpu_baseline:
+        out["cpu_baseline"] = cpu_baseline(wl, budget_s=args.cpu_budget)
+    return out
+
+
+# ---------------------------------------------------------------------------------------------------------------
+def cpu_step_fn(wl, feet_sample):
+    """-> (callable running one CPU step on `feet_sample` feet of the workload, threads used)."""
+    from find_b200 import synthetic as syn
+    from oracle import field_oracle as fo
+    from oracle import step_oracle as so
+    from oracle import chamfer_oracle as co
+    V, P2 = wl["V"], wl["P2"]
+    threads = os.cpu_count() or 1
+    torch.set_num_threads(threads)
+    Bm = fo.fourier_B()
+    p = fo.random_params(0)
+    tv, _ = syn.make_template(V)
+    lat = syn.make_latents(feet_sample, 0)
+    tables = {k: lat[k] for k in ("shapevec", "posevec", "texvec", "reg")}
+    idx = torch.arange(feet_sample)
+    target = syn.make_targets(feet_sample, P2, 0)
+    colt = syn.make_col_target(feet_sample, V, 0)
+    co.build()
+
+    def run():
+        return so.train_step(p, Bm, tv, tables, idx, target, colt, threads=threads, need_param_grads=not wl["frozen"])
+    return run, threads
+
+
+def cpu_baseline(wl, budget_s=20.0, steps=None, warmup=1):
+    feet_sample = 1 if wl["V"] <= 20000 else 1
+    run, threads = cpu_step_fn(wl, feet_sample)
+    for _ in range(warmup):
+        run()
+    times = []
+    t_start = time.perf_counter()
+    while True:
+        t0 = time.perf_counter()
+        run()
+        times.append(time.perf_counter() - t0)
+        if steps is not None and len(times) >= steps:
+            break
+        if steps is None and (time.perf_counter() - t_start > budget_s or len(times) >= 20):
+            break
+    med = statistics.median(times)
+    return {"value": feet_sample * wl["V"] / med, "unit": UNIT, "cores": threads, "kind": "port",
+            "sample": f"{feet_sample} foot of the {wl['V']}-vertex / {wl['P2']}-target workload per step "
+                      f"(same per-foot work as the GPU arm), median of {len(times)} steps after {warmup} warm-up; "
+                      f"oracle/step_oracle.py: torch CPU autograd (field) + OpenMP C Chamfer",
+            "s_per_step": med}
+
+
+def run_reference(args, wl, rank, world):
+    """The reference arm: the CPU port of the reference's path on the host cores (rank 0 only)."""
+    if rank != 0:
+        return None
+    base = cpu_baseline(wl, steps=args.steps, warmup=max(1, min(args.warmup, 2)))
+    return {"metric": METRIC, "value": base["value"], "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": base["s_per_step"] * 1e3, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "fp32", "data": "synthetic", "impl": "reference",
+            "config": {"workload": f"{args.workload}: {wl['desc']}", "feet_per_step": 1, "verts": wl["V"],
+                       "target_points": wl["P2"], "frozen_mlp": wl["frozen"]},
+            "cpu_baseline": base,
+            "e2e": {"value": base["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0,
+            "note": "reference = pure Python on torch + PyTorch3D (absent, not installable offline): timed arm is the "
+                    "oracle port of its algorithm on the host cores"}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="find_b200", choices=["find_b200", "reference"])
+    ap.add_argument("--workload", default=None, choices=sorted(WORKLOADS))
+    ap.add_argument("--skip-cpu-baseline", action="store_true")
+    ap.add_argument("--cpu-budget", type=float, default=20.0)
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.workload is None:
+        args.workload = "cfg2" if world == 1 else "cfg3"
+    wl = WORKLOADS[args.workload]
+
+    if args.impl == "reference":
+        if args.steps > 5:
+            args.steps = 5                      # each CPU step is seconds: keep the arm within minutes
+        out = run_reference(args, wl, rank, world)
+        if out is not None:
+            print(json.dumps(out), flush=True)
+        return
+
+    import torch.distributed as dist
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    try:
+        out = run_ours(args, wl, rank, world, local_rank)
+        if rank == 0:
+            print(json.dumps(out), flush=True)
+    finally:
+        if world > 1:
+            dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -33,6 +33,12 @@ SIGNATURES = {
                                + [c_size_t, c_void_p]),
     "findb200_field_backward": (c_int, [c_void_p] * 2 + [c_int] + [c_void_p] * 4 + [c_int] * 2 + [c_void_p] * 11
                                 + [c_size_t, c_void_p]),
+    "findb200_train_step_workspace_bytes": (c_size_t, [c_int] * 3),
+    "findb200_train_step": (c_int, [c_void_p] * 9 + [c_int] * 3 + [c_float] * 2 + [c_void_p] * 10 + [c_size_t, c_void_p]),
+    "findb200_gather_rows": (c_int, [c_void_p, c_int, c_int, c_void_p, c_int, c_void_p, c_void_p]),
+    "findb200_scatter_add_rows": (c_int, [c_void_p, c_int, c_int, c_void_p, c_int, c_void_p, c_void_p]),
+    "findb200_profile_enable": (c_int, [c_int]),
+    "findb200_profile_read": (c_int, [c_char_p, c_size_t]),
     "findb200_umma_selftest": (c_int, [c_int, c_void_p, c_void_p, c_void_p, c_void_p]),
     "findb200_fp32_peak": (c_int, [c_int, c_int, c_int, c_void_p, c_void_p]),
     "findb200_l2_stream": (c_int, [c_void_p, c_size_t] + [c_int] * 5 + [c_void_p, c_void_p]),

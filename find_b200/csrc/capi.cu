@@ -3,6 +3,7 @@
 #include "../../include/find_b200.h"
 #include <cstdarg>
 #include <cstdio>
+#include <cstring>
 
 namespace fb {
 
@@ -21,9 +22,64 @@ int check_cuda(cudaError_t e, const char* what) {
     return FINDB200_ERR_CUDA;
 }
 
+// ---- launch profiler ----------------------------------------------------------------------------------------
+constexpr int kProfMax = 8192;
+static bool g_prof_on = false;
+static int g_prof_n = 0;
+static cudaEvent_t g_prof_ev[kProfMax];
+static const char* g_prof_name[kProfMax];
+static int g_prof_created = 0;
+
+void prof_mark(const char* name, cudaStream_t st) {
+    if (!g_prof_on || g_prof_n >= kProfMax) return;
+    if (g_prof_n >= g_prof_created) {
+        if (cudaEventCreate(&g_prof_ev[g_prof_created]) != cudaSuccess) return;
+        ++g_prof_created;
+    }
+    cudaEventRecord(g_prof_ev[g_prof_n], st);
+    g_prof_name[g_prof_n] = name;
+    ++g_prof_n;
+}
+
 }  // namespace fb
 
 extern "C" {
+int findb200_profile_enable(int on) {
+    fb::g_prof_on = on != 0;
+    if (on) fb::g_prof_n = 0;
+    return 0;
+}
+
+// Synchronises on the recorded events and writes one "name,launches,total_ms" line per kernel name (first-appearance
+// order) into buf; returns the number of bytes written (0 if nothing was recorded), negative on error.
+int findb200_profile_read(char* buf, size_t cap) {
+    using namespace fb;
+    if (!buf || cap < 2) return FINDB200_ERR_ARG;
+    buf[0] = 0;
+    const int n = g_prof_n;
+    if (n < 2) return 0;
+    if (cudaEventSynchronize(g_prof_ev[n - 1]) != cudaSuccess) return FINDB200_ERR_CUDA;
+    const char* names[256];
+    double tot[256];
+    int cnt[256], nn = 0;
+    for (int i = 0; i + 1 < n; ++i) {
+        if (!g_prof_name[i]) continue;
+        float ms = 0.f;
+        if (cudaEventElapsedTime(&ms, g_prof_ev[i], g_prof_ev[i + 1]) != cudaSuccess) continue;
+        int k = 0;
+        while (k < nn && strcmp(names[k], g_prof_name[i]) != 0) ++k;
+        if (k == nn) { if (nn == 256) continue; names[nn] = g_prof_name[i]; tot[nn] = 0; cnt[nn] = 0; ++nn; }
+        tot[k] += ms; cnt[k] += 1;
+    }
+    size_t off = 0;
+    for (int k = 0; k < nn; ++k) {
+        int w = snprintf(buf + off, cap - off, "%s,%d,%.6f\n", names[k], cnt[k], tot[k]);
+        if (w < 0 || (size_t)w >= cap - off) break;
+        off += (size_t)w;
+    }
+    g_prof_n = 0;
+    return (int)off;
+}
 const char* findb200_last_error(void) { return fb::g_err; }
 const char* findb200_version(void) { return "find_b200 0.1 (sm_100a)"; }
 }

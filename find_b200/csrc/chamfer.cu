@@ -394,6 +394,7 @@ static int run_knn(const float* x, const float* y, const int64_t* lx, const int6
                "knn: workspace too small (%zu < %zu bytes)", ws_bytes, w.bytes);
     if (N == 0 || (P1 == 0 && P2 == 0)) return 0;
     const int P1p = round_up(P1 > 0 ? P1 : 1, kChunk), P2p = round_up(P2 > 0 ? P2 : 1, kChunk);
+    FB_MARK("chamfer_prep", st);
     if (P1 > 0) cloud_to_soa_kernel<<<dim3((P1p + 255) / 256, N), 256, 0, st>>>(x, lx, P1, P1p, w.soa_x);
     if (P2 > 0) cloud_to_soa_kernel<<<dim3((P2p + 255) / 256, N), 256, 0, st>>>(y, ly, P2, P2p, w.soa_y);
     // counter = 0, keys = 0xFF.. (identity of atomicMin); one memset each (they are adjacent but differ in value)
@@ -414,6 +415,7 @@ static int run_knn(const float* x, const float* y, const int64_t* lx, const int6
     }
     int grid = sms * 4;
     if (grid > prm.total_items) grid = prm.total_items;
+    FB_MARK("knn_main", st);
     knn_main_kernel<<<grid, kThreads, 0, st>>>(prm);
     FB_CUDA(cudaGetLastError());
     return 0;
@@ -441,8 +443,10 @@ int findb200_knn1(const float* p1, const float* p2, const int64_t* len1, const i
     if (N == 0 || P1 == 0) return 0;
     FinalizeParams fp{};
     fp.dir[0] = FinalizeDir{w.keys_x, len1, len2, dists, idx, nullptr, nullptr, P1, P2};
+    FB_MARK("knn_finalize", st);
     knn_finalize_kernel<<<dim3(N, 1), 256, 0, st>>>(fp);
     FB_CUDA(cudaGetLastError());
+    FB_MARK_END(st);
     return 0;
 }
 
@@ -454,6 +458,7 @@ int findb200_knn1_backward(const float* p1, const float* p2, const int64_t* len1
     if (N == 0) return 0;
     if (P2 > 0) FB_CUDA(cudaMemsetAsync(grad_p2, 0, (size_t)N * P2 * 3 * sizeof(float), st));
     if (P1 > 0) {
+        FB_MARK("knn_bwd", st);
         knn_bwd_kernel<<<dim3((P1 + 255) / 256, N), 256, 0, st>>>(p1, p2, len1, len2, idx, grad_dists, P1, P2, grad_p1,
                                                                   grad_p2);
         FB_CUDA(cudaGetLastError());
@@ -473,9 +478,12 @@ int findb200_chamfer_forward(const float* x, const float* y, const int64_t* x_le
     FinalizeParams fp{};
     fp.dir[0] = FinalizeDir{w.keys_x, x_len, y_len, dist_x, idx_x, nullptr, w.sum_x, P1, P2};
     fp.dir[1] = FinalizeDir{w.keys_y, y_len, x_len, dist_y, idx_y, nullptr, w.sum_y, P2, P1};
+    FB_MARK("knn_finalize", st);
     knn_finalize_kernel<<<dim3(N, 2), 256, 0, st>>>(fp);
+    FB_MARK("chamfer_reduce", st);
     chamfer_reduce_kernel<<<1, 32, 0, st>>>(w.sum_x, w.sum_y, x_len, y_len, N, P1, P2, loss, nullptr);
     FB_CUDA(cudaGetLastError());
+    FB_MARK_END(st);
     return 0;
 }
 
@@ -487,6 +495,7 @@ int findb200_chamfer_backward(const float* x, const float* y, const int64_t* x_l
     FB_REQUIRE(grad_x != nullptr, FINDB200_ERR_ARG, "chamfer_backward: grad_x is null");
     if (N == 0) return 0;
     const dim3 g1((P1 + 255) / 256, N), g2((P2 + 255) / 256, N);
+    FB_MARK("chamfer_bwd", st);
     if (P1 > 0)
         chamfer_bwd_direct_kernel<<<g1, 256, 0, st>>>(x, y, x_len, y_len, idx_x, grad_loss, grad_scale, N, P1, P2, grad_x);
     if (grad_y && P2 > 0)
@@ -498,6 +507,7 @@ int findb200_chamfer_backward(const float* x, const float* y, const int64_t* x_l
             chamfer_bwd_scatter_kernel<<<g1, 256, 0, st>>>(x, y, x_len, y_len, idx_x, grad_loss, grad_scale, N, P1, P2, grad_y);
     }
     FB_CUDA(cudaGetLastError());
+    FB_MARK_END(st);
     return 0;
 }
 

@@ -25,6 +25,12 @@ int  check_cuda(cudaError_t e, const char* what);
         if (!(cond)) { fb::set_error(__VA_ARGS__); return (code); }        \
     } while (0)
 
+// Launch profiler (off by default): FB_MARK("kernel") before a launch records a CUDA event on the launching stream;
+// the time to the next mark is attributed to that name.  FB_MARK_END closes a C-ABI call.  See capi.cu.
+void prof_mark(const char* name, cudaStream_t st);
+#define FB_MARK(name, st) fb::prof_mark((name), (st))
+#define FB_MARK_END(st) fb::prof_mark(nullptr, (st))
+
 // ------------------------------------------------------------------------------------------------
 FB_DEVINL uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 

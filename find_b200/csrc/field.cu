@@ -445,6 +445,7 @@ static int run_pack(const findb200_field_params* p, const Workspace& w, uint8_t*
         J.transpose = 1; J.perm = 0; J.img_rows = 256; J.n_chunks = L.bwd[i].n_chunks; J.dst_off = L.bwd[i].off;
     }
     PP.n = n;
+    FB_MARK("pack_weights", st);
     pack_weights_kernel<<<dim3(36, n), 256, 0, st>>>(PP);
     FB_CUDA(cudaGetLastError());
     return 0;
@@ -484,6 +485,7 @@ int findb200_field_forward(const findb200_field_params* p, const float* pos, int
     if (rc) return rc;
     LatentBiasParams LB{p->weight[P_D1], p->bias[P_D1], p->weight[P_C1], p->bias[P_C1], z_shape, z_pose, z_tex,
                         p->shapevec_size, p->posevec_size, p->texvec_size, B, (float*)(ws + w.biasfoot)};
+    FB_MARK("latent_bias", st);
     latent_bias_kernel<<<dim3(B, 2), 256, 0, st>>>(LB);
     FB_CUDA(cudaGetLastError());
 
@@ -507,6 +509,7 @@ int findb200_field_forward(const findb200_field_params* p, const float* pos, int
         rc = launch_chain(1, nt, C, sms, st);
         if (rc) return rc;
     }
+    FB_MARK_END(st);
     return 0;
 }
 
@@ -532,6 +535,7 @@ int findb200_field_backward(const findb200_field_params* p, const float* pos, in
     const size_t head_tiles = (size_t)B * w.tpf2;
 
     // scalars, per-foot sums, column sums, d(pre-tanh) images start from zero
+    FB_MARK("bwd_memsets", st);
     FB_CUDA(cudaMemsetAsync(ws + w.scal, 0, 1024, st));
     FB_CUDA(cudaMemsetAsync(ws + w.regsums, 0, (size_t)B * 12 * 4, st));
     FB_CUDA(cudaMemsetAsync(ws + w.colsum, 0, cs_total(B) * 4, st));
@@ -539,6 +543,7 @@ int findb200_field_backward(const findb200_field_params* p, const float* pos, in
 
     GradPrepParams GP{pos, disp, col, reg, p->avg_col, grad_disp, grad_col, grad_verts, B, V, pos_shared,
                       (float*)(ws + w.dovals), (uint32_t*)(ws + w.scal), (float*)(ws + w.regsums)};
+    FB_MARK("grad_prep", st);
     grad_prep_kernel<<<dim3(cdiv(V, 256), B), 256, 0, st>>>(GP);
     FB_CUDA(cudaGetLastError());
 
@@ -668,6 +673,7 @@ int findb200_field_backward(const findb200_field_params* p, const float* pos, in
             }
         }
         R.n = nj;
+        FB_MARK("reduce_dw", st);
         reduce_dw_kernel<<<dim3(64, nj), 256, 0, st>>>(R);
         FB_CUDA(cudaGetLastError());
     }
@@ -687,8 +693,10 @@ int findb200_field_backward(const findb200_field_params* p, const float* pos, in
     if (kW * Lmax > maxid) maxid = kW * Lmax;
     if (B * (F.S + F.Pz + F.T) > maxid) maxid = B * (F.S + F.Pz + F.T);
     if (B > maxid) maxid = B;
+    FB_MARK("finish_small", st);
     finish_small_kernel<<<dim3(cdiv(maxid, 256), 5), 256, 0, st>>>(F);
     FB_CUDA(cudaGetLastError());
+    FB_MARK_END(st);
     return 0;
 }
 

@@ -484,9 +484,15 @@ __global__ void __launch_bounds__(64 + 128 * NT, 1) chain_kernel(const __grid_co
 template <int MODE, int NT>
 static int launch_chain_t(const ChainParams& P, int sms, cudaStream_t st) {
     const int smem = NT * kTileBytes + kRing * kWChunkBytes + 1024;
-    FB_CUDA(cudaFuncSetAttribute(chain_kernel<MODE, NT>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    static bool attr_set = false;      // one process drives one GPU (one rank per GPU)
+    if (!attr_set) {
+        FB_CUDA(cudaFuncSetAttribute(chain_kernel<MODE, NT>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        attr_set = true;
+    }
     int grid = P.n_items < sms ? P.n_items : sms;
     if (grid <= 0) return 0;
+    static const char* const kNames[4] = {"trunk_fwd", "head_fwd", "head_bwd", "trunk_bwd"};
+    FB_MARK(kNames[MODE], st);
     chain_kernel<MODE, NT><<<grid, 64 + 128 * NT, smem, st>>>(P);
     FB_CUDA(cudaGetLastError());
     return 0;

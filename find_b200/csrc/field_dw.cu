@@ -152,7 +152,12 @@ __global__ void __launch_bounds__(kDwThreads, 1) dw_kernel(const __grid_constant
 int launch_dw(const DwParams& P, int n_ctas, cudaStream_t st) {
     if (n_ctas <= 0) return 0;
     const int smem = kDwStages * kDwStageBytes + 1024;
-    FB_CUDA(cudaFuncSetAttribute(dw_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    static bool attr_set = false;
+    if (!attr_set) {
+        FB_CUDA(cudaFuncSetAttribute(dw_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        attr_set = true;
+    }
+    FB_MARK("dw_gemms", st);
     dw_kernel<<<n_ctas, kDwThreads, smem, st>>>(P);
     FB_CUDA(cudaGetLastError());
     return 0;

@@ -1,0 +1,165 @@
+// find_b200/csrc/step.cu — one host call that enqueues FIND's whole 3-D training step (no host sync, graph-capturable):
+//   field forward on the shared template + registration transform     model.py:1009 -> 455-504
+//   bidirectional Chamfer of the deformed vertices vs the target cloud losses.py:87-88 (plain branch)
+//   colour MSE against per-vertex targets (stand-in for TextureLossGTSpace, losses.py:22-57; optional)
+//   loss = w_chamf * chamfer + w_tex * mse                             model.py:1157-1158, opts.py:97-99
+//   backward of all of it: d/d(MLP weights), d/d(latent rows), d/d(reg rows)   trainer.py:121
+// It only composes the entry points of chamfer.cu / field.cu; the kernels are theirs.
+#include "common.cuh"
+#include "../../include/find_b200.h"
+
+namespace fb {
+namespace step {
+
+static inline size_t align1k(size_t x) { return (x + 1023) & ~(size_t)1023; }
+
+struct Carve {
+    size_t field, knn, idx_x, idx_y, grad_verts, grad_col, sums, total;
+    size_t field_bytes, knn_bytes;
+};
+static Carve carve(int B, int V, int P2) {
+    Carve c{};
+    size_t off = 0;
+    auto take = [&](size_t bytes) { size_t o = off; off = align1k(off + bytes); return o; };
+    c.field_bytes = findb200_field_workspace_bytes(B, V, 1, 1);
+    c.knn_bytes = findb200_knn_workspace_bytes(B, V, P2);
+    c.field = take(c.field_bytes);
+    c.knn = take(c.knn_bytes);
+    c.idx_x = take((size_t)B * V * 8);
+    c.idx_y = take((size_t)B * P2 * 8);
+    c.grad_verts = take((size_t)B * V * 12);
+    c.grad_col = take((size_t)B * V * 12);
+    c.sums = take(1024);
+    c.total = off;
+    return c;
+}
+
+// grad_col = 2 w (col - target) / n ; per-block partial sums of (col - target)^2 -> one double atomic per block
+__global__ void __launch_bounds__(256) col_mse_kernel(const float* __restrict__ col, const float* __restrict__ tgt, size_t n,
+                                                      float w_over_n, float* __restrict__ grad_col, double* sum) {
+    double acc = 0.0;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+        const float d = col[i] - tgt[i];
+        grad_col[i] = 2.0f * w_over_n * d;
+        acc += (double)d * (double)d;
+    }
+    __shared__ double sh[256];
+    sh[threadIdx.x] = acc;
+    __syncthreads();
+    for (int o = 128; o > 0; o >>= 1) {
+        if ((int)threadIdx.x < o) sh[threadIdx.x] += sh[threadIdx.x + o];
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) atomicAdd(sum, sh[0]);
+}
+
+__global__ void combine_loss_kernel(const float* chamf, const double* mse_sum, double n, float w_chamf, float w_tex,
+                                    float* loss3) {
+    if (threadIdx.x || blockIdx.x) return;
+    const float c = *chamf;
+    const float t = mse_sum ? (float)(*mse_sum / n) : 0.f;
+    loss3[0] = w_chamf * c + w_tex * t;
+    loss3[1] = c;
+    loss3[2] = t;
+}
+
+}  // namespace step
+}  // namespace fb
+
+using namespace fb;
+using namespace fb::step;
+
+extern "C" {
+
+size_t findb200_train_step_workspace_bytes(int nfeet, int V, int P2) {
+    if (nfeet < 1 || V < 1 || P2 < 0) return 0;
+    return carve(nfeet, V, P2).total;
+}
+
+int findb200_train_step(const findb200_field_params* p, const float* template_pos, const float* z_shape,
+                        const float* z_pose, const float* z_tex, const float* reg, const float* target,
+                        const int64_t* target_len, const float* col_target, int nfeet, int V, int P2, float w_chamf,
+                        float w_tex, float* loss3, float* disp, float* col, float* verts,
+                        const findb200_field_grads* gw, float* gz_shape, float* gz_pose, float* gz_tex, float* greg,
+                        void* workspace, size_t workspace_bytes, void* stream) {
+    cudaStream_t st = (cudaStream_t)stream;
+    FB_REQUIRE(p && template_pos && target && loss3 && disp && col && verts, FINDB200_ERR_ARG,
+               "train_step: a required pointer is null");
+    FB_REQUIRE(nfeet >= 1 && V >= 1 && P2 >= 1, FINDB200_ERR_SHAPE, "train_step: bad sizes nfeet=%d V=%d P2=%d", nfeet, V, P2);
+    const Carve c = carve(nfeet, V, P2);
+    FB_REQUIRE(workspace && workspace_bytes >= c.total, FINDB200_ERR_WORKSPACE,
+               "train_step: workspace too small (%zu < %zu bytes)", workspace_bytes, c.total);
+    uint8_t* ws = (uint8_t*)workspace;
+    int64_t* idx_x = (int64_t*)(ws + c.idx_x);
+    int64_t* idx_y = (int64_t*)(ws + c.idx_y);
+    float* grad_verts = (float*)(ws + c.grad_verts);
+    float* grad_col = (float*)(ws + c.grad_col);
+    double* mse_sum = (double*)(ws + c.sums);
+    float* chamf = (float*)(ws + c.sums + 64);
+
+    int rc = findb200_field_forward(p, template_pos, 1, z_shape, z_pose, z_tex, reg, nfeet, V, 1, disp, col, verts,
+                                    ws + c.field, c.field_bytes, stream);
+    if (rc) return rc;
+    rc = findb200_chamfer_forward(verts, target, nullptr, target_len, nfeet, V, P2, chamf, nullptr, idx_x, nullptr, idx_y,
+                                  ws + c.knn, c.knn_bytes, stream);
+    if (rc) return rc;
+    rc = findb200_chamfer_backward(verts, target, nullptr, target_len, nfeet, V, P2, idx_x, idx_y, nullptr, w_chamf,
+                                   grad_verts, nullptr, stream);
+    if (rc) return rc;
+    const size_t n = (size_t)nfeet * V * 3;
+    const bool tex = col_target != nullptr && w_tex != 0.f;
+    if (tex) {
+        FB_MARK("col_mse", st);
+        FB_CUDA(cudaMemsetAsync(mse_sum, 0, 8, st));
+        int blocks = (int)((n + 255) / 256);
+        if (blocks > 1184) blocks = 1184;
+        col_mse_kernel<<<blocks, 256, 0, st>>>(col, col_target, n, w_tex / (float)n, grad_col, mse_sum);
+        FB_CUDA(cudaGetLastError());
+    }
+    FB_MARK("combine_loss", st);
+    combine_loss_kernel<<<1, 32, 0, st>>>(chamf, tex ? mse_sum : nullptr, (double)n, w_chamf, tex ? w_tex : 0.f, loss3);
+    FB_CUDA(cudaGetLastError());
+    return findb200_field_backward(p, template_pos, 1, z_shape, z_pose, z_tex, reg, nfeet, V, disp, col, nullptr,
+                                   tex ? grad_col : nullptr, grad_verts, gw, gz_shape, gz_pose, gz_tex, greg,
+                                   ws + c.field, c.field_bytes, stream);
+}
+
+}  // extern "C"
+
+// ---- latent-table row gather / gradient scatter (LatentVector.__getitem__, model.py:130-152, and its autograd) ----
+namespace fb {
+namespace step {
+__global__ void gather_rows_kernel(const float* __restrict__ table, int width, const int64_t* __restrict__ idx, int B,
+                                   float* __restrict__ out) {
+    const int b = blockIdx.x;
+    const float* src = table + (size_t)idx[b] * width;
+    for (int j = threadIdx.x; j < width; j += blockDim.x) out[(size_t)b * width + j] = src[j];
+}
+__global__ void scatter_add_rows_kernel(float* __restrict__ grad_table, int width, const int64_t* __restrict__ idx, int B,
+                                        const float* __restrict__ g) {
+    const int b = blockIdx.x;
+    float* dst = grad_table + (size_t)idx[b] * width;
+    for (int j = threadIdx.x; j < width; j += blockDim.x) atomicAdd(dst + j, g[(size_t)b * width + j]);   // duplicates accumulate
+}
+}  // namespace step
+}  // namespace fb
+
+extern "C" {
+int findb200_gather_rows(const float* table, int n_rows, int width, const int64_t* idx, int B, float* out, void* stream) {
+    FB_REQUIRE(table && idx && out && n_rows >= 1 && width >= 1 && B >= 1, FINDB200_ERR_ARG, "gather_rows: bad argument");
+    FB_MARK("gather_rows", (cudaStream_t)stream);
+    fb::step::gather_rows_kernel<<<B, 128, 0, (cudaStream_t)stream>>>(table, width, idx, B, out);
+    FB_CUDA(cudaGetLastError());
+    FB_MARK_END((cudaStream_t)stream);
+    return 0;
+}
+int findb200_scatter_add_rows(float* grad_table, int n_rows, int width, const int64_t* idx, int B, const float* g,
+                              void* stream) {
+    FB_REQUIRE(grad_table && idx && g && n_rows >= 1 && width >= 1 && B >= 1, FINDB200_ERR_ARG, "scatter_add_rows: bad argument");
+    FB_MARK("scatter_add_rows", (cudaStream_t)stream);
+    fb::step::scatter_add_rows_kernel<<<B, 128, 0, (cudaStream_t)stream>>>(grad_table, width, idx, B, g);
+    FB_CUDA(cudaGetLastError());
+    FB_MARK_END((cudaStream_t)stream);
+    return 0;
+}
+}

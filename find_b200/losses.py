@@ -1,0 +1,78 @@
+"""find_b200/losses.py — the 3-D loss of FIND's training step on the sm_100a Chamfer kernels.
+
+Mirrors /root/reference/src/model/losses.py:59-90 (``DisplacementLoss``) and the weighting of
+``ModelWithLoss.forward`` (/root/reference/src/model/model.py:1026-1030,1157-1158; weights opts.py:97-99).
+
+The reference draws 5000 random surface samples from both meshes with PyTorch3D's ``sample_points_from_meshes``
+before Chamfer (losses.py:63,67).  BASELINE.json's configurations take Chamfer directly between the deformed template
+vertices and a target point cloud, so here ``num_samples=None`` (default) means "use the points as given":
+  * prediction = ``res['verts']`` ([B,V,3], what ``res['meshes'].verts_padded()`` holds),
+  * target     = ``batch['points']`` ([B,P,3] tensor or ``Pointclouds``), else ``batch['mesh'].verts_padded()``.
+Surface sampling is SURVEY.md §8(f) row 1 ("next"); asking for it (``num_samples`` an int) raises until it lands.
+"""
+from __future__ import annotations
+
+import torch
+from torch import nn
+
+from .chamfer import Pointclouds, chamfer_distance
+
+CHAMF_WEIGHT = 1e4      # opts.py:97  (--weight_chamf default)
+TEX_WEIGHT = 1.0        # opts.py:99
+
+
+def _target_points(batch):
+    if "points" in batch:
+        return batch["points"]
+    mesh = batch["mesh"]
+    if hasattr(mesh, "verts_padded"):
+        return mesh.verts_padded()
+    raise RuntimeError("DisplacementLoss: batch needs 'points' ([B,P,3] or Pointclouds) or 'mesh' with verts_padded()")
+
+
+class DisplacementLoss(nn.Module):
+    """losses.py:59-90 -> dict(loss=chamfer).  All three z-cutoff variants are kept (ragged clouds)."""
+
+    def forward(self, model, res, batch, epoch=0, num_samples=None, z_cutoff=None, gt_z_cutoff=None):
+        if num_samples is not None:
+            raise NotImplementedError("surface sampling (sample_points_from_meshes) is not on the CUDA path yet; "
+                                      "pass num_samples=None to take Chamfer on the vertices / given points")
+        gt_samples = _target_points(batch)
+        pred_samples = res["verts"] if "verts" in res else res["meshes"].verts_padded()
+
+        if z_cutoff is not None:                                   # losses.py:69-77
+            gt_pad = gt_samples.points_padded() if isinstance(gt_samples, Pointclouds) else gt_samples
+            pred_verts, gt_verts = [], []
+            for b in range(len(pred_samples)):
+                pred_verts.append(pred_samples[b][pred_samples[b, :, 2] <= z_cutoff])
+                gt_verts.append(gt_pad[b][gt_pad[b, :, 2] <= z_cutoff])
+            chamf_loss, _ = chamfer_distance(Pointclouds(pred_verts), Pointclouds(gt_verts))
+        elif gt_z_cutoff is not None:                              # losses.py:79-85
+            gt_pad = gt_samples.points_padded() if isinstance(gt_samples, Pointclouds) else gt_samples
+            gt_verts = [gt_pad[b][gt_pad[b, :, 2] <= gt_z_cutoff] for b in range(len(gt_pad))]
+            chamf_loss, _ = chamfer_distance(pred_samples, Pointclouds(gt_verts))
+        else:                                                      # losses.py:87-88 (what training uses)
+            chamf_loss, _ = chamfer_distance(pred_samples, gt_samples)
+        return dict(loss=chamf_loss)
+
+
+class FieldChamferObjective(nn.Module):
+    """The bench / training objective of SURVEY.md §8(d): ``1e4 * Chamfer(verts, target) + 1 * MSE(col, col_target)``
+    (the colour term stands in for TextureLossGTSpace, losses.py:22-57, so that both heads carry gradient)."""
+
+    def __init__(self, weight_chamf: float = CHAMF_WEIGHT, weight_tex: float = TEX_WEIGHT):
+        super().__init__()
+        self.disp_loss = DisplacementLoss()
+        self.weight_chamf, self.weight_tex = weight_chamf, weight_tex
+
+    def forward(self, model, batch, is_train=True):
+        res = model.get_meshes_from_batch(batch, is_train=is_train)
+        losses = {"chamf": self.disp_loss(model, res, batch, 0)["loss"]}
+        total = self.weight_chamf * losses["chamf"]
+        if "col_target" in batch and self.weight_tex:
+            losses["tex"] = torch.nn.functional.mse_loss(res["col"], batch["col_target"])
+            total = total + self.weight_tex * losses["tex"]
+        return total, losses
+
+
+__all__ = ["DisplacementLoss", "FieldChamferObjective", "CHAMF_WEIGHT", "TEX_WEIGHT"]

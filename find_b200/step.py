@@ -1,0 +1,158 @@
+"""find_b200/step.py — FIND's 3-D training step as ONE enqueue of sm_100a kernels (findb200_train_step).
+
+What it replaces, per step of ``Trainer.train_epoch`` (/root/reference/src/train/trainer.py:97-121) with the
+``chamf`` (+ colour) losses on:
+    batch.update(sample_latent_vectors(...))      trainer.py:97      -> findb200_gather_rows (4 tables)
+    loss, loss_dict = self.model(batch, ...)      trainer.py:106     -> field fwd + reg transform + Chamfer (+ colour MSE)
+    loss.backward()                               trainer.py:121     -> Chamfer bwd + field bwd (+ latent scatter-add)
+The optimiser step stays with torch (``.grad`` of every parameter is populated exactly like autograd would).
+
+``TrainStep`` owns static device buffers, so the enqueue can be captured once in a CUDA graph and replayed; the
+per-step inputs are the foot indices, the target clouds and (optionally) colour targets.  No CPU path exists.
+"""
+from __future__ import annotations
+
+import ctypes
+from typing import Dict, Optional
+
+import torch
+
+from . import _lib
+from .field import NeuralDisplacementField
+from .field_ops import FieldGradsC, N_PARAMS, _make_params
+from .losses import CHAMF_WEIGHT, TEX_WEIGHT
+
+
+class TrainStep:
+    def __init__(self, model: NeuralDisplacementField, nfeet: int, P2: int, with_colour: bool = True,
+                 frozen_mlp: bool = False, is_train: bool = True, weight_chamf: float = CHAMF_WEIGHT,
+                 weight_tex: float = TEX_WEIGHT, use_graph: bool = True):
+        self.lib = _lib.load()
+        self.model = model
+        dev = model.template_verts.device
+        _lib.require_cuda(model.template_verts)
+        self.dev = dev
+        self.B, self.P2 = int(nfeet), int(P2)
+        self.V = int(model.template_verts.shape[1])
+        self.with_colour, self.frozen = bool(with_colour), bool(frozen_mlp)
+        self.w_chamf, self.w_tex = float(weight_chamf), float(weight_tex)
+        sfx = "" if is_train else "_val"
+        self.tables = {k: getattr(model, k + sfx) for k in ("shapevec", "posevec", "texvec", "reg")}
+        f32 = dict(dtype=torch.float32, device=dev)
+        B, V = self.B, self.V
+        # per-step inputs (static addresses)
+        self.idx = torch.zeros(B, dtype=torch.int64, device=dev)
+        self.target = torch.zeros(B, self.P2, 3, **f32)
+        self.col_target = torch.zeros(B, V, 3, **f32) if with_colour else None
+        # gathered rows, outputs, gradients
+        self.rows = {k: torch.zeros(B, t.data.shape[1], **f32) for k, t in self.tables.items() if t is not None}
+        self.grows = {k: torch.zeros_like(v) for k, v in self.rows.items()}
+        self.loss3 = torch.zeros(3, **f32)
+        self.disp, self.col, self.verts = (torch.empty(B, V, 3, **f32) for _ in range(3))
+        self.mlp_params = model.mlp_parameters()
+        n_flat = sum(p.numel() for p in self.mlp_params)
+        self.flat_grad = torch.zeros(n_flat, **f32)          # the data-parallel allreduce bucket
+        self.grad_views, off = [], 0
+        for p in self.mlp_params:
+            self.grad_views.append(self.flat_grad[off:off + p.numel()].view_as(p))
+            off += p.numel()
+        nbytes = int(self.lib.findb200_train_step_workspace_bytes(B, V, self.P2))
+        self.ws = torch.empty(nbytes, dtype=torch.uint8, device=dev)
+        self.kernel_launches = 0         # filled by the first enqueue (counted from the C ABI's launch list)
+        self.graph: Optional[torch.cuda.CUDAGraph] = None
+        self.use_graph = use_graph
+        self._cparams = None
+        self._cgrads = None
+
+    # ---- the enqueue ---------------------------------------------------------------------------------------
+    def _structs(self):
+        m = self.model
+        mods = m.mlp_modules()
+        for p in self.mlp_params:
+            if not p.is_contiguous() or p.dtype != torch.float32:
+                raise RuntimeError("MLP parameters must be contiguous fp32")
+        S = self.rows["shapevec"].shape[1] if "shapevec" in self.rows else 0
+        P = self.rows["posevec"].shape[1] if "posevec" in self.rows else 0
+        T = self.rows["texvec"].shape[1] if "texvec" in self.rows else 0
+        self._B = m.encoder[0].B_on(self.dev)
+        self._avg = m.avg_col.detach() if m.use_avg_colour else None
+        cp = _make_params([x.weight.detach() for x in mods], [x.bias.detach() for x in mods], self._B, self._avg, S, P, T)
+        cg = None
+        if not self.frozen:
+            cg = FieldGradsC()
+            for i in range(N_PARAMS):
+                cg.weight[i] = self.grad_views[i].data_ptr()
+                cg.bias[i] = self.grad_views[N_PARAMS + i].data_ptr()
+        return cp, cg
+
+    def _enqueue(self):
+        lib, st = self.lib, _lib.stream_ptr(self.dev)
+        if self._cparams is None:
+            self._cparams, self._cgrads = self._structs()
+        for k, t in self.tables.items():
+            if t is None:
+                continue
+            rc = lib.findb200_gather_rows(_lib.ptr(t.data), t.data.shape[0], t.data.shape[1], _lib.ptr(self.idx), self.B,
+                                          _lib.ptr(self.rows[k]), st)
+            _lib.check(rc, "findb200_gather_rows")
+        r, g = self.rows, self.grows
+        rc = lib.findb200_train_step(
+            ctypes.byref(self._cparams), _lib.ptr(self.model.template_verts), _lib.ptr(r.get("shapevec")),
+            _lib.ptr(r.get("posevec")), _lib.ptr(r.get("texvec")), _lib.ptr(r.get("reg")), _lib.ptr(self.target), None,
+            _lib.ptr(self.col_target), self.B, self.V, self.P2, self.w_chamf, self.w_tex if self.with_colour else 0.0,
+            _lib.ptr(self.loss3), _lib.ptr(self.disp), _lib.ptr(self.col), _lib.ptr(self.verts),
+            ctypes.byref(self._cgrads) if self._cgrads is not None else None, _lib.ptr(g.get("shapevec")),
+            _lib.ptr(g.get("posevec")), _lib.ptr(g.get("texvec")), _lib.ptr(g.get("reg")), _lib.ptr(self.ws),
+            self.ws.numel(), st)
+        _lib.check(rc, "findb200_train_step")
+
+    def run(self) -> torch.Tensor:
+        """Enqueue one step on the current stream (graph replay after the first call) -> loss3 (device)."""
+        with torch.cuda.device(self.dev):
+            if not self.use_graph:
+                self._enqueue()
+            elif self.graph is None:
+                self._enqueue()                      # warm-up outside capture (sets function attributes)
+                torch.cuda.synchronize(self.dev)
+                g = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(g):
+                    self._enqueue()
+                self.graph = g
+                g.replay()
+            else:
+                self.graph.replay()
+        return self.loss3
+
+    # ---- host-facing conveniences --------------------------------------------------------------------------
+    def load_inputs(self, idx: torch.Tensor, target: torch.Tensor, col_target: Optional[torch.Tensor] = None):
+        """Copy one batch (host pinned or device tensors) into the static input buffers, asynchronously."""
+        self.idx.copy_(idx, non_blocking=True)
+        self.target.copy_(target, non_blocking=True)
+        if self.with_colour and col_target is not None:
+            self.col_target.copy_(col_target, non_blocking=True)
+
+    def populate_grads(self):
+        """Make ``.grad`` of every parameter what autograd would have produced (dense table grads, trainer.py:121)."""
+        st = _lib.stream_ptr(self.dev)
+        if not self.frozen:
+            for p, gv in zip(self.mlp_params, self.grad_views):
+                p.grad = gv
+        for k, t in self.tables.items():
+            if t is None:
+                continue
+            if t.data.grad is None:
+                t.data.grad = torch.zeros_like(t.data)
+            rc = self.lib.findb200_scatter_add_rows(_lib.ptr(t.data.grad), t.data.shape[0], t.data.shape[1],
+                                                    _lib.ptr(self.idx), self.B, _lib.ptr(self.grows[k]), st)
+            _lib.check(rc, "findb200_scatter_add_rows")
+
+    def step_from_host(self, idx: torch.Tensor, target: torch.Tensor, col_target: Optional[torch.Tensor] = None
+                       ) -> Dict[str, float]:
+        """The public end-to-end call: host batch in, losses out (one D2H read, like trainer.py:128-130)."""
+        self.load_inputs(idx, target, col_target)
+        self.run()
+        total, chamf, tex = self.loss3.tolist()
+        return {"loss": total, "chamf": chamf, "tex": tex}
+
+
+__all__ = ["TrainStep"]

@@ -106,11 +106,44 @@ int findb200_field_backward(const findb200_field_params* p, const float* pos, in
                             float* gz_tex, float* greg, void* workspace, size_t workspace_bytes, void* stream);
 
 /* ------------------------------------------------------------------------------------------------------
+ * Whole 3-D training step in one call (replaces, for the chamf(+tex) configuration, everything between
+ * `loss, loss_dict = self.model(batch, ...)` and `loss.backward()` of Trainer.train_epoch,
+ * src/train/trainer.py:106-121: ModelWithLoss.forward model.py:1009,1026-1030,1157-1158 -> get_meshes model.py:455-504
+ * -> DisplacementLoss plain branch losses.py:87-88 -> autograd).  Chamfer is taken between the deformed template
+ * vertices [nfeet,V,3] and target [nfeet,P2,3] (target_len int64 [nfeet] or NULL); col_target [nfeet,V,3] (or NULL)
+ * adds w_tex * mean((col - col_target)^2).  loss3 = {total, chamfer, colour mse} (device).  disp/col/verts are
+ * the forward outputs.  Gradients as in findb200_field_backward (gw NULL = frozen MLP).  Nothing synchronises; the
+ * sequence can be captured in a CUDA graph.
+ * ------------------------------------------------------------------------------------------------------ */
+size_t findb200_train_step_workspace_bytes(int nfeet, int V, int P2);
+
+int findb200_train_step(const findb200_field_params* p, const float* template_pos, const float* z_shape,
+                        const float* z_pose, const float* z_tex, const float* reg, const float* target,
+                        const int64_t* target_len, const float* col_target, int nfeet, int V, int P2, float w_chamf,
+                        float w_tex, float* loss3, float* disp, float* col, float* verts,
+                        const findb200_field_grads* gw, float* gz_shape, float* gz_pose, float* gz_tex, float* greg,
+                        void* workspace, size_t workspace_bytes, void* stream);
+
+/* Latent-table access (replaces LatentVector.__getitem__ with an index tensor, src/model/model.py:130-152 as called
+ * from sample_latent_vectors src/train/trainer.py:29-46, and the index scatter-add of its autograd).
+ * table / grad_table: [n_rows,width]; idx: int64 [B] (device); out / g: [B,width].  Duplicate rows accumulate. */
+int findb200_gather_rows(const float* table, int n_rows, int width, const int64_t* idx, int B, float* out, void* stream);
+int findb200_scatter_add_rows(float* grad_table, int n_rows, int width, const int64_t* idx, int B, const float* g,
+                              void* stream);
+
+/* ------------------------------------------------------------------------------------------------------
  * Diagnostics: one-CTA tcgen05 self-test of the shared-memory image / descriptor / TMEM conventions used by
  * the field kernels (mode 0: K-major operands, forward and dX shape; mode 1: MN-major operands, dW shape).
  * a_img / b_img are fp16 swizzled tile images (see csrc/umma_selftest.cu); d_out is fp32 [128][256].
  * ------------------------------------------------------------------------------------------------------ */
 int findb200_umma_selftest(int mode, const void* a_img, const void* b_img, float* d_out, void* stream);
+
+/* Launch profiler used by bench.py for the live roofline: after findb200_profile_enable(1) every kernel launch of the
+ * library is bracketed by CUDA events on its launching stream (do not enable during CUDA-graph capture);
+ * findb200_profile_read synchronises and writes "kernel,launches,total_ms" lines into the HOST buffer buf
+ * (returns bytes written) and clears the record. */
+int findb200_profile_enable(int on);
+int findb200_profile_read(char* buf, size_t cap);
 
 /* FP32 CUDA-core peak probe (roofline denominator of the Chamfer kernel): launches blocks x 256 threads, each
  * issuing iters*64 dependent-chain FMAs with ILP 8 (mode 0: FFMA, mode 1: packed FFMA2 = 2 lanes/instr). */

@@ -4,7 +4,11 @@
 
 Stated tolerances (fp32 reference vs fp16-operand / fp32-accumulate tensor-core compute; DESIGN.md "Numerics"):
   * outputs (disp, col, verts):                       rel-L2 <= 1e-3   (measured ~1e-4)
-  * gradients when no ReLU pre-activation is near 0:   rel-L2 <= 2e-3   (test_field_gradients_kinkfree)
+  * kink-free parameters (no ReLU pre-activation near 0, so the masks of the fp16-operand forward equal the fp32
+    forward's): outputs AND gradients rel-L2 <= 2e-3 vs the rounding-matched oracle (CPU fp32 autograd whose forward
+    rounds GEMM operands to fp16) — this isolates the backward kernels — and <= 3e-2 vs the fp32 reference (those
+    parameters put a large common mode on every activation, mean/std = 6, which amplifies fp16 operand rounding;
+    measured 6e-3 on the outputs)
   * gradients with ordinary weights:                   rel-L2 <= 5e-2 vs the fp32 reference, AND no further from it
     than 1.5 x the distance of the rounding-matched oracle (CPU fp32 autograd whose forward rounds GEMM operands
     to fp16) + 2e-3.  Reason: any reduced-precision forward (fp16, tf32 and bf16 alike) flips the sign of ~1e-4
@@ -20,7 +24,8 @@ from oracle import field_oracle as fo
 pytestmark = pytest.mark.gpu
 
 TOL_OUT = 1e-3
-TOL_GRAD = 2e-3          # kink-free gradients
+TOL_GRAD = 2e-3          # kink-free parameters, vs the rounding-matched oracle
+TOL_KINKFREE_FP32 = 3e-2 # kink-free parameters, vs the fp32 reference
 TOL_GRAD_FP32 = 5e-2     # ordinary weights, vs the fp32 reference
 
 
@@ -104,7 +109,7 @@ def _oracle_case(B, V, shared, seed, with_reg=True, frozen=False, kinkfree=False
     p = fo.kinkfree_params(seed, Bm, pos, zs, zp, zt) if kinkfree else fo.random_params(seed)
 
     ref = _oracle_grads(p, Bm, pos, zs, zp, zt, reg, avg, gd, gc, gv)
-    matched = None if kinkfree else _oracle_grads(p, Bm, pos, zs, zp, zt, reg, avg, gd, gc, gv, torch.float16)
+    matched = _oracle_grads(p, Bm, pos, zs, zp, zt, reg, avg, gd, gc, gv, torch.float16)
 
     ws, bs = _params_from(p, dev, requires_grad=not frozen)
     zg = [z.to(dev).requires_grad_(True) for z in (zs, zp, zt)]
@@ -122,10 +127,11 @@ def _oracle_case(B, V, shared, seed, with_reg=True, frozen=False, kinkfree=False
         assert all(w.grad is None for w in ws)
     for k, v in mine.items():
         e = rel_l2(v, ref[k])
-        if k in ("disp", "col", "verts"):
+        if kinkfree:
+            assert rel_l2(v, matched[k]) < TOL_GRAD, (k, rel_l2(v, matched[k]))
+            assert e < TOL_KINKFREE_FP32, (k, e)
+        elif k in ("disp", "col", "verts"):
             assert e < TOL_OUT, (k, e)
-        elif kinkfree:
-            assert e < TOL_GRAD, (k, e)
         else:
             em = rel_l2(matched[k], ref[k])
             assert e < TOL_GRAD_FP32, (k, e)

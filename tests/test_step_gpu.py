@@ -1,0 +1,159 @@
+"""GPU parity: the fused training step (findb200_train_step through find_b200.step.TrainStep) and the module-level
+path (NeuralDisplacementField.get_meshes_from_batch + DisplacementLoss + autograd) against the CPU oracle of the
+whole step (oracle/step_oracle.py) on the same seeded inputs.
+
+Tolerances: loss / verts rel <= 1e-3 (fp16-operand forward, measured ~1e-4); Chamfer NN indices of the fused step are
+bit-exact against the oracle evaluated ON THE GPU's own vertices (the index contract is a property of the Chamfer
+kernel; vertices differ from the fp32 oracle's by forward rounding); gradients <= 5e-2 vs the fp32 oracle (ReLU-mask
+flips of any reduced-precision forward, see tests/test_field_gpu.py) and <= 1e-4 between the two GPU paths.
+"""
+import numpy as np
+import pytest
+import torch
+
+from oracle import chamfer_oracle as co
+from oracle import field_oracle as fo
+from oracle import step_oracle as so
+
+pytestmark = pytest.mark.gpu
+
+
+def rel_l2(a, b):
+    a = torch.as_tensor(a).detach().double().cpu().reshape(-1)
+    b = torch.as_tensor(b).detach().double().cpu().reshape(-1)
+    return float((a - b).norm() / b.norm().clamp_min(1e-30))
+
+
+def _setup(B, V, P2, n_rows, seed, frozen=False):
+    from find_b200 import synthetic as syn
+    from find_b200.field import NeuralDisplacementField
+    dev = torch.device("cuda:0")
+    model = NeuralDisplacementField(use_shapevec=True, use_texvec=True, use_posevec=True, train_size=n_rows, val_size=1,
+                                    shapevec_size=100, texvec_size=100, posevec_size=100, device=dev)
+    p = fo.random_params(seed)
+    sd = model.state_dict()
+    with torch.no_grad():
+        for k, v in p.items():
+            sd[k].copy_(v)
+    tv, tf = syn.make_template(V)
+    model.set_template(tv, tf)
+    lat = syn.make_latents(n_rows, 0)
+    with torch.no_grad():
+        for k in ("shapevec", "posevec", "texvec", "reg"):
+            getattr(model, k).data.copy_(lat[k])
+    g = torch.Generator().manual_seed(seed)
+    idx = torch.randperm(n_rows, generator=g)[:B]
+    target = syn.make_targets(B, P2, 0)
+    colt = syn.make_col_target(B, V, 0)
+    tables = {k: lat[k] for k in ("shapevec", "posevec", "texvec", "reg")}
+    return dev, model, p, tv, tables, idx, target, colt
+
+
+def _check_against_oracle(step, model, ref, p, idx, n_rows, frozen):
+    total, chamf, tex = step.loss3.tolist()
+    assert abs(chamf - ref["chamf"]) <= 1e-3 * ref["chamf"]
+    assert abs(tex - ref["tex"]) <= 1e-3 * ref["tex"]
+    assert abs(total - ref["loss"]) <= 1e-3 * ref["loss"]
+    assert rel_l2(step.verts, ref["verts"]) < 1e-3
+    assert rel_l2(step.col, ref["col"]) < 1e-3
+    step.populate_grads()
+    torch.cuda.synchronize()
+    for k in ("shapevec", "posevec", "texvec", "reg"):
+        g = getattr(model, k).data.grad
+        assert rel_l2(g, ref["table_grads"][k]) < 5e-2, k
+        untouched = torch.ones(n_rows, dtype=torch.bool)
+        untouched[idx] = False
+        assert float(g[untouched.to(g.device)].abs().max()) == 0.0
+    if not frozen:
+        for name, prm in model.named_parameters():
+            if name in p:
+                assert rel_l2(prm.grad, ref["grads"][name]) < 5e-2, name
+
+
+@pytest.mark.parametrize("use_graph", [False, True])
+def test_train_step_matches_cpu_oracle(use_graph):
+    from find_b200.step import TrainStep
+    B, V, P2, n_rows = 3, 700, 600, 5
+    dev, model, p, tv, tables, idx, target, colt = _setup(B, V, P2, n_rows, seed=31)
+    ref = so.train_step(p, fo.fourier_B(), tv, tables, idx, target, colt)
+    step = TrainStep(model, B, P2, with_colour=True, use_graph=use_graph)
+    step.load_inputs(idx, target, colt)
+    step.run()
+    if use_graph:
+        step.run()                                   # a replay must give the same answer as the capture run
+    torch.cuda.synchronize()
+    _check_against_oracle(step, model, ref, p, idx, n_rows, frozen=False)
+    # Chamfer index contract on the GPU's own vertices: bit-exact vs the C oracle (FMA-chain mode)
+    ch = co.chamfer(step.verts.cpu().numpy(), target.numpy(), with_grad=False)
+    ws = step.ws
+    from find_b200 import knn_points
+    k1 = knn_points(step.verts, target.to(dev))
+    k2 = knn_points(target.to(dev), step.verts)
+    assert np.array_equal(k1.idx[..., 0].cpu().numpy(), ch["idx_x"])
+    assert np.array_equal(k2.idx[..., 0].cpu().numpy(), ch["idx_y"])
+    assert np.array_equal(k1.dists[..., 0].cpu().numpy(), ch["dist_x"])
+
+
+def test_train_step_frozen_mlp_latent_fitting():
+    from find_b200.step import TrainStep
+    B, V, P2, n_rows = 4, 300, 256, 4
+    dev, model, p, tv, tables, idx, target, colt = _setup(B, V, P2, n_rows, seed=32)
+    ref = so.train_step(p, fo.fourier_B(), tv, tables, idx, target, colt, need_param_grads=False)
+    step = TrainStep(model, B, P2, with_colour=True, frozen_mlp=True, use_graph=False)
+    step.load_inputs(idx, target, colt)
+    step.run()
+    torch.cuda.synchronize()
+    _check_against_oracle(step, model, ref, p, idx, n_rows, frozen=True)
+    assert all(prm.grad is None for n, prm in model.named_parameters() if n in p)
+
+
+def test_module_path_equals_fused_step():
+    """model.get_meshes_from_batch + DisplacementLoss + autograd (the reference-shaped API) == findb200_train_step."""
+    from find_b200.field import sample_latent_vectors
+    from find_b200.losses import FieldChamferObjective
+    from find_b200.step import TrainStep
+    B, V, P2, n_rows = 3, 515, 400, 6
+    dev, model, p, tv, tables, idx, target, colt = _setup(B, V, P2, n_rows, seed=33)
+    step = TrainStep(model, B, P2, with_colour=True, use_graph=False)
+    step.load_inputs(idx, target, colt)
+    step.run()
+    step.populate_grads()
+    torch.cuda.synchronize()
+    fused = {n: prm.grad.clone() for n, prm in model.named_parameters() if prm.grad is not None}
+    fused_loss = step.loss3.tolist()
+    model.zero_grad(set_to_none=True)
+
+    batch = {"idx": idx.to(dev), "points": target.to(dev), "col_target": colt.to(dev)}
+    batch.update(sample_latent_vectors(batch, model.latent_vectors_train))
+    loss, losses = FieldChamferObjective()(model, batch, is_train=True)
+    loss.backward()
+    assert abs(float(loss) - fused_loss[0]) <= 1e-5 * abs(fused_loss[0])
+    assert abs(float(losses["chamf"]) - fused_loss[1]) <= 1e-6 * abs(fused_loss[1])
+    for n, prm in model.named_parameters():
+        if n in fused:
+            assert prm.grad is not None, n
+            assert rel_l2(prm.grad, fused[n]) < 1e-4, n
+
+
+def test_displacement_loss_z_cutoff_variants_run_ragged():
+    from find_b200.losses import DisplacementLoss
+    from find_b200 import Pointclouds, chamfer_distance
+    dev = torch.device("cuda:0")
+    g = torch.Generator().manual_seed(5)
+    verts = (torch.randn(2, 300, 3, generator=g) * 0.05).to(dev)
+    pts = (torch.randn(2, 250, 3, generator=g) * 0.05).to(dev)
+    L = DisplacementLoss()
+    full = L(None, {"verts": verts}, {"points": pts}, 0)["loss"]
+    ref = co.chamfer(verts.cpu().numpy(), pts.cpu().numpy(), with_grad=False)["loss"]
+    assert abs(float(full) - ref) <= 1e-6 * ref
+    cut = L(None, {"verts": verts}, {"points": pts}, 0, gt_z_cutoff=0.0)["loss"]
+    lens = (pts[..., 2] <= 0).sum(1)
+    padded = torch.zeros_like(pts)
+    for b in range(2):
+        padded[b, : int(lens[b])] = pts[b][pts[b, :, 2] <= 0]
+    ref2 = co.chamfer(verts.cpu().numpy(), padded.cpu().numpy(), y_lengths=lens.cpu().numpy(), with_grad=False)["loss"]
+    assert abs(float(cut) - ref2) <= 1e-6 * ref2
+    both = L(None, {"verts": verts}, {"points": pts}, 0, z_cutoff=0.0)["loss"]
+    assert torch.isfinite(both)
+    with pytest.raises(NotImplementedError):
+        L(None, {"verts": verts}, {"points": pts}, 0, num_samples=5000)
