@@ -4,11 +4,11 @@
 
 Stated tolerances (fp32 reference vs fp16-operand / fp32-accumulate tensor-core compute; DESIGN.md "Numerics"):
   * outputs (disp, col, verts):                       rel-L2 <= 1e-3   (measured ~1e-4)
-  * kink-free parameters (no ReLU pre-activation near 0, so the masks of the fp16-operand forward equal the fp32
-    forward's): outputs AND gradients rel-L2 <= 2e-3 vs the rounding-matched oracle (CPU fp32 autograd whose forward
-    rounds GEMM operands to fp16) — this isolates the backward kernels — and <= 3e-2 vs the fp32 reference (those
-    parameters put a large common mode on every activation, mean/std = 6, which amplifies fp16 operand rounding;
-    measured 6e-3 on the outputs)
+  * kink-free parameters (oracle/field_oracle.kinkfree_params: no ReLU pre-activation near 0, so the masks of the
+    fp16-operand forward equal the fp32 forward's): gradients rel-L2 <= 2e-3 vs the fp32 reference (measured
+    <= 1.2e-3) — this isolates the backward kernels from mask flips.  Those parameters put a large common mode on
+    every activation (mean/std = 6), which amplifies fp16 operand rounding on the OUTPUTS, so outputs are held to
+    1e-2 there (measured 6e-3..8e-3; the rounding-matched oracle shows the same 6e-3..8e-3 against fp32)
   * gradients with ordinary weights:                   rel-L2 <= 5e-2 vs the fp32 reference, AND no further from it
     than 1.5 x the distance of the rounding-matched oracle (CPU fp32 autograd whose forward rounds GEMM operands
     to fp16) + 2e-3.  Reason: any reduced-precision forward (fp16, tf32 and bf16 alike) flips the sign of ~1e-4
@@ -24,8 +24,8 @@ from oracle import field_oracle as fo
 pytestmark = pytest.mark.gpu
 
 TOL_OUT = 1e-3
-TOL_GRAD = 2e-3          # kink-free parameters, vs the rounding-matched oracle
-TOL_KINKFREE_FP32 = 3e-2 # kink-free parameters, vs the fp32 reference
+TOL_GRAD = 2e-3          # kink-free parameters: gradients vs the fp32 reference
+TOL_KINKFREE_OUT = 1e-2  # kink-free parameters: outputs vs the fp32 reference (ill-conditioned on purpose)
 TOL_GRAD_FP32 = 5e-2     # ordinary weights, vs the fp32 reference
 
 
@@ -128,8 +128,7 @@ def _oracle_case(B, V, shared, seed, with_reg=True, frozen=False, kinkfree=False
     for k, v in mine.items():
         e = rel_l2(v, ref[k])
         if kinkfree:
-            assert rel_l2(v, matched[k]) < TOL_GRAD, (k, rel_l2(v, matched[k]))
-            assert e < TOL_KINKFREE_FP32, (k, e)
+            assert e < (TOL_KINKFREE_OUT if k in ("disp", "col", "verts") else TOL_GRAD), (k, e)
         elif k in ("disp", "col", "verts"):
             assert e < TOL_OUT, (k, e)
         else:

@@ -63,7 +63,8 @@ def _check_against_oracle(step, model, ref, p, idx, n_rows, frozen):
         assert rel_l2(g, ref["table_grads"][k]) < 5e-2, k
         untouched = torch.ones(n_rows, dtype=torch.bool)
         untouched[idx] = False
-        assert float(g[untouched.to(g.device)].abs().max()) == 0.0
+        if untouched.any():
+            assert float(g[untouched.to(g.device)].abs().max()) == 0.0
     if not frozen:
         for name, prm in model.named_parameters():
             if name in p:
@@ -96,7 +97,7 @@ def test_train_step_matches_cpu_oracle(use_graph):
 
 def test_train_step_frozen_mlp_latent_fitting():
     from find_b200.step import TrainStep
-    B, V, P2, n_rows = 4, 300, 256, 4
+    B, V, P2, n_rows = 4, 300, 256, 6
     dev, model, p, tv, tables, idx, target, colt = _setup(B, V, P2, n_rows, seed=32)
     ref = so.train_step(p, fo.fourier_B(), tv, tables, idx, target, colt, need_param_grads=False)
     step = TrainStep(model, B, P2, with_colour=True, frozen_mlp=True, use_graph=False)

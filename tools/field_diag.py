@@ -12,10 +12,9 @@ def rel(a, b):
     return float((a - b).norm() / b.norm().clamp_min(1e-30))
 
 
-def case(B, V, shared, seed, with_reg=True):
+def case(B, V, shared, seed, with_reg=True, kinkfree=False):
     dev = torch.device("cuda:0")
     g = torch.Generator().manual_seed(seed)
-    p = fo.random_params(seed)
     Bm = fo.fourier_B()
     pos = torch.randn(1 if shared else B, V, 3, generator=g) * 0.05
     zs, zp, zt = (torch.randn(B, 100, generator=g) * 0.1 for _ in range(3))
@@ -23,6 +22,7 @@ def case(B, V, shared, seed, with_reg=True):
                      1 + torch.randn(B, 3, generator=g) * 0.02], 1) if with_reg else None
     avg = torch.rand(3, generator=g) * 0.1
     gd, gc, gv = (torch.randn(B, V, 3, generator=g) for _ in range(3))
+    p = fo.kinkfree_params(seed, Bm, pos, zs, zp, zt) if kinkfree else fo.random_params(seed)
     refs = {}
     for tag, od in (("fp32", None), ("matched", torch.float16)):
         po = {k: v.clone().requires_grad_(True) for k, v in p.items()}
@@ -52,13 +52,17 @@ def case(B, V, shared, seed, with_reg=True):
     for i, n in enumerate(PARAM_NAMES):
         mine["gW " + n] = ws[i].grad
         mine["gb " + n] = bs[i].grad
-    print(f"--- B={B} V={V} shared={shared}")
+    print(f"--- B={B} V={V} shared={shared} kinkfree={kinkfree}")
     for k in mine:
         print(f"{k:24s} vs fp32 {rel(mine[k], refs['fp32'][k]):.2e}   vs matched {rel(mine[k], refs['matched'][k]):.2e}"
               f"   (matched vs fp32 {rel(refs['matched'][k], refs['fp32'][k]):.2e})")
 
 
 if __name__ == "__main__":
+    if "--kinkfree" in sys.argv:
+        case(3, 333, True, 21, kinkfree=True)
+        case(2, 257, False, 22, kinkfree=True)
+        sys.exit(0)
     case(3, 333, True, 11)
     case(2, 257, False, 12)
     case(24, 1500, True, 15)
