@@ -379,7 +379,7 @@ def main():
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     if args.workload is None:
-        args.workload = "cfg2" if world == 1 else "cfg3"
+        args.workload = "cfg2"        # same per-GPU shape at every N (weak scaling: 8 feet / GPU)
     wl = WORKLOADS[args.workload]
 
     if args.impl == "reference":
