@@ -22,6 +22,7 @@
 #include "common.cuh"
 #include "../../include/find_b200.h"
 #include <math_constants.h>
+#include <cstdlib>
 
 namespace fb {
 namespace chamfer {
@@ -68,6 +69,12 @@ FB_DEVINL float dist_exact(float qx, float qy, float qz, float tx, float ty, flo
     float dx = __fsub_rn(qx, tx), dy = __fsub_rn(qy, ty), dz = __fsub_rn(qz, tz);
     return __fmaf_rn(dz, dz, __fmaf_rn(dy, dy, __fmul_rn(dx, dx)));
 }
+
+}  // namespace chamfer
+}  // namespace fb
+#include "knn_cull.cuh"
+namespace fb {
+namespace chamfer {
 
 __global__ void __launch_bounds__(kThreads) knn_main_kernel(const KnnParams prm) {
     __shared__ __align__(128) float s_t[kStages][3][kTile];
@@ -337,22 +344,31 @@ static inline int round_up(int a, int b) { return (a + b - 1) / b * b; }
 static inline size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }
 
 struct Workspace {
-    unsigned int* counter;
+    unsigned int* counter;            // [0] work queue; stats (2 x u64) live 64 bytes further
+    unsigned long long* stats;
     unsigned long long *keys_x, *keys_y;
     float *soa_x, *soa_y;
+    int *perm_x, *perm_y;
+    float *box_x, *box_y;
     double *sum_x, *sum_y;
+    int P1p, P2p, C1p, C2p;
     size_t bytes;
 };
 static Workspace carve(void* base, int N, int P1, int P2) {
     Workspace w{};
-    const int P1p = round_up(P1 > 0 ? P1 : 1, kChunk), P2p = round_up(P2 > 0 ? P2 : 1, kChunk);
+    w.P1p = round_up(P1 > 0 ? P1 : 1, kChunk); w.P2p = round_up(P2 > 0 ? P2 : 1, kChunk);
+    w.C1p = round_up(w.P1p / kChunk, 32); w.C2p = round_up(w.P2p / kChunk, 32);
     size_t off = 0;
     char* b = (char*)base;
-    w.counter = (unsigned int*)(b + off); off += 256;
+    w.counter = (unsigned int*)(b + off); w.stats = (unsigned long long*)(b + off + 64); off += 256;
     w.keys_x = (unsigned long long*)(b + off); off += align256((size_t)N * P1 * 8);
     w.keys_y = (unsigned long long*)(b + off); off += align256((size_t)N * P2 * 8);
-    w.soa_x = (float*)(b + off); off += align256((size_t)N * 3 * P1p * 4);
-    w.soa_y = (float*)(b + off); off += align256((size_t)N * 3 * P2p * 4);
+    w.soa_x = (float*)(b + off); off += align256((size_t)N * 3 * w.P1p * 4);
+    w.soa_y = (float*)(b + off); off += align256((size_t)N * 3 * w.P2p * 4);
+    w.perm_x = (int*)(b + off); off += align256((size_t)N * w.P1p * 4);
+    w.perm_y = (int*)(b + off); off += align256((size_t)N * w.P2p * 4);
+    w.box_x = (float*)(b + off); off += align256((size_t)N * 6 * w.C1p * 4);
+    w.box_y = (float*)(b + off); off += align256((size_t)N * 6 * w.C2p * 4);
     w.sum_x = (double*)(b + off); off += align256((size_t)N * 8);
     w.sum_y = (double*)(b + off); off += align256((size_t)N * 8);
     w.bytes = off;
@@ -385,23 +401,24 @@ static void fill_dir(KnnDir& D, const float* qsoa, const float* tsoa, const int6
     D.n_splits = s;
 }
 
-// Core: runs 1 or 2 directions.  dir 0: queries x (P1) vs targets y (P2); dir 1: queries y vs targets x.
-static int run_knn(const float* x, const float* y, const int64_t* lx, const int64_t* ly, int N, int P1, int P2,
-                   bool both, void* ws_base, size_t ws_bytes, Workspace& w, cudaStream_t st) {
-    FB_REQUIRE(N >= 0 && P1 >= 0 && P2 >= 0, FINDB200_ERR_SHAPE, "knn: negative size N=%d P1=%d P2=%d", N, P1, P2);
-    w = carve(ws_base, N, P1, P2);
-    FB_REQUIRE(ws_base != nullptr && ws_bytes >= w.bytes, FINDB200_ERR_WORKSPACE,
-               "knn: workspace too small (%zu < %zu bytes)", ws_bytes, w.bytes);
-    if (N == 0 || (P1 == 0 && P2 == 0)) return 0;
-    const int P1p = round_up(P1 > 0 ? P1 : 1, kChunk), P2p = round_up(P2 > 0 ? P2 : 1, kChunk);
-    FB_MARK("chamfer_prep", st);
-    if (P1 > 0) cloud_to_soa_kernel<<<dim3((P1p + 255) / 256, N), 256, 0, st>>>(x, lx, P1, P1p, w.soa_x);
-    if (P2 > 0) cloud_to_soa_kernel<<<dim3((P2p + 255) / 256, N), 256, 0, st>>>(y, ly, P2, P2p, w.soa_y);
-    // counter = 0, keys = 0xFF.. (identity of atomicMin); one memset each (they are adjacent but differ in value)
-    FB_CUDA(cudaMemsetAsync(w.counter, 0, 256, st));
-    FB_CUDA(cudaMemsetAsync(w.keys_x, 0xFF, (size_t)((char*)w.soa_x - (char*)w.keys_x), st));
-    if (P1 == 0 || P2 == 0) return 0;
+// 0 = culled (default), 1 = brute-force tile kernel (kept for A/B measurement: FINDB200_KNN_MODE=1 or findb200_set_knn_mode)
+static int g_knn_mode = -1;
+static int knn_mode() {
+    if (g_knn_mode < 0) {
+        const char* e = getenv("FINDB200_KNN_MODE");
+        g_knn_mode = (e && e[0] == '1') ? 1 : 0;
+    }
+    return g_knn_mode;
+}
+static int g_cull_kq = 0;   // 0 = heuristic
 
+static int grid_log2(int P) { return P < 2048 ? 3 : (P < 40000 ? 4 : 5); }
+
+static int run_knn_brute(const float* x, const float* y, const int64_t* lx, const int64_t* ly, int N, int P1, int P2,
+                         bool both, Workspace& w, cudaStream_t st) {
+    FB_MARK("chamfer_prep", st);
+    cloud_to_soa_kernel<<<dim3((w.P1p + 255) / 256, N), 256, 0, st>>>(x, lx, P1, w.P1p, w.soa_x);
+    cloud_to_soa_kernel<<<dim3((w.P2p + 255) / 256, N), 256, 0, st>>>(y, ly, P2, w.P2p, w.soa_y);
     const int sms = num_sms();
     KnnParams prm{};
     prm.N = N; prm.counter = w.counter; prm.ndir = both ? 2 : 1;
@@ -421,6 +438,65 @@ static int run_knn(const float* x, const float* y, const int64_t* lx, const int6
     return 0;
 }
 
+template <int kQ>
+static int launch_cull(CullParams& prm, int N, int P1, int P2, bool both, cudaStream_t st) {
+    prm.dir[0].n_groups = (P1 + 32 * kQ - 1) / (32 * kQ);
+    prm.dir[1].n_groups = (P2 + 32 * kQ - 1) / (32 * kQ);
+    prm.items_dir0 = N * prm.dir[0].n_groups;
+    prm.total_items = prm.items_dir0 + (both ? N * prm.dir[1].n_groups : 0);
+    int grid = (prm.total_items + 3) / 4;
+    const int cap = num_sms() * 8;
+    if (grid > cap) grid = cap;
+    FB_MARK("knn_main", st);
+    knn_cull_kernel<kQ><<<grid, 128, 0, st>>>(prm);
+    FB_CUDA(cudaGetLastError());
+    return 0;
+}
+
+static int run_knn_cull(const float* x, const float* y, const int64_t* lx, const int64_t* ly, int N, int P1, int P2,
+                        bool both, Workspace& w, cudaStream_t st) {
+    SortParams sp{};
+    sp.set[0] = SortSet{x, lx, w.soa_x, w.perm_x, w.box_x, P1, w.P1p, w.C1p, grid_log2(P1)};
+    sp.set[1] = SortSet{y, ly, w.soa_y, w.perm_y, w.box_y, P2, w.P2p, w.C2p, grid_log2(P2)};
+    const int gl = sp.set[0].glog2 > sp.set[1].glog2 ? sp.set[0].glog2 : sp.set[1].glog2;
+    const size_t smem = (size_t)4 << (3 * gl);
+    static bool attr_done = false;
+    if (!attr_done) {
+        FB_CUDA(cudaFuncSetAttribute(sort_cloud_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 4 << 15));
+        attr_done = true;
+    }
+    FB_MARK("chamfer_prep", st);
+    sort_cloud_kernel<<<dim3(N, 2), kSortThreads, smem, st>>>(sp);
+    FB_CUDA(cudaGetLastError());
+
+    CullParams prm{};
+    prm.N = N; prm.counter = w.counter; prm.stats = w.stats; prm.ndir = both ? 2 : 1;
+    prm.dir[0] = CullDir{w.soa_x, w.perm_x, w.soa_y, w.perm_y, w.box_y, lx, ly, w.keys_x, P1, w.P1p, P2, w.P2p, w.C2p, 0};
+    prm.dir[1] = CullDir{w.soa_y, w.perm_y, w.soa_x, w.perm_x, w.box_x, ly, lx, w.keys_y, P2, w.P2p, P1, w.P1p, w.C1p, 0};
+    int kq = g_cull_kq;
+    if (!kq) {
+        const long long q = (long long)N * (P1 + (both ? P2 : 0));
+        kq = q / 128 >= (long long)num_sms() * 32 ? 4 : 2;
+    }
+    return kq == 4 ? launch_cull<4>(prm, N, P1, P2, both, st) : launch_cull<2>(prm, N, P1, P2, both, st);
+}
+
+// Core: runs 1 or 2 directions.  dir 0: queries x (P1) vs targets y (P2); dir 1: queries y vs targets x.
+static int run_knn(const float* x, const float* y, const int64_t* lx, const int64_t* ly, int N, int P1, int P2,
+                   bool both, void* ws_base, size_t ws_bytes, Workspace& w, cudaStream_t st) {
+    FB_REQUIRE(N >= 0 && P1 >= 0 && P2 >= 0, FINDB200_ERR_SHAPE, "knn: negative size N=%d P1=%d P2=%d", N, P1, P2);
+    w = carve(ws_base, N, P1, P2);
+    FB_REQUIRE(ws_base != nullptr && ws_bytes >= w.bytes, FINDB200_ERR_WORKSPACE,
+               "knn: workspace too small (%zu < %zu bytes)", ws_bytes, w.bytes);
+    if (N == 0 || (P1 == 0 && P2 == 0)) return 0;
+    // queue counter + stats = 0, keys = 0xFF.. (identity of atomicMin; also what an unreachable query keeps)
+    FB_CUDA(cudaMemsetAsync(w.counter, 0, 256, st));
+    FB_CUDA(cudaMemsetAsync(w.keys_x, 0xFF, (size_t)((char*)w.soa_x - (char*)w.keys_x), st));
+    if (P1 == 0 || P2 == 0) return 0;
+    return knn_mode() == 1 ? run_knn_brute(x, y, lx, ly, N, P1, P2, both, w, st)
+                           : run_knn_cull(x, y, lx, ly, N, P1, P2, both, w, st);
+}
+
 }  // namespace chamfer
 }  // namespace fb
 
@@ -428,6 +504,19 @@ using namespace fb;
 using namespace fb::chamfer;
 
 extern "C" {
+
+int findb200_set_knn_mode(int mode, int kq) {
+    FB_REQUIRE((mode == 0 || mode == 1) && (kq == 0 || kq == 2 || kq == 4), FINDB200_ERR_ARG, "set_knn_mode: mode 0/1, kq 0/2/4");
+    g_knn_mode = mode; g_cull_kq = kq;
+    return 0;
+}
+
+int findb200_knn_stats(const void* workspace, unsigned long long* out4_host, void* stream) {
+    FB_REQUIRE(workspace && out4_host, FINDB200_ERR_ARG, "knn_stats: null argument");
+    FB_CUDA(cudaMemcpyAsync(out4_host, (const char*)workspace + 64, 32, cudaMemcpyDeviceToHost, (cudaStream_t)stream));
+    FB_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
+    return 0;
+}
 
 size_t findb200_knn_workspace_bytes(int N, int P1, int P2) {
     if (N < 0 || P1 < 0 || P2 < 0) return 0;

@@ -60,6 +60,15 @@ int findb200_chamfer_backward(const float* x, const float* y, const int64_t* x_l
                               int P1, int P2, const int64_t* idx_x, const int64_t* idx_y, const float* grad_loss,
                               float grad_scale, float* grad_x, float* grad_y, void* stream);
 
+/* Measurement hooks for the kNN kernel.  mode 0 (default): exact search with bounding-box culling over spatially
+ * binned clouds; mode 1: the plain brute-force tile kernel (every pair evaluated), kept for A/B timing.  kq = queries
+ * per lane of the culled kernel (0 = heuristic, 2 or 4).  Results are bit-identical in every mode.
+ * findb200_knn_stats copies {pair evaluations executed, queries that took the cross-chunk-tie path, most chunk
+ * evaluations done for one query group, query groups} of the LAST culled call that used `workspace` into four host
+ * uint64 (synchronises `stream`). */
+int findb200_set_knn_mode(int mode, int kq);
+int findb200_knn_stats(const void* workspace, unsigned long long* out4_host, void* stream);
+
 /* ------------------------------------------------------------------------------------------------------
  * Neural displacement field   (replaces NeuralDisplacementField.forward + its autograd,
  *   src/model/model.py:393-453, the latent concat model.py:428-437, and the registration transform of

@@ -7,6 +7,24 @@ import torch
 pytestmark = pytest.mark.gpu
 
 
+@pytest.fixture(params=["cull_kq2", "cull_kq4", "brute"], autouse=True)
+def knn_mode(request):
+    """Every test runs on the culled kernel (2 and 4 queries per lane) and on the brute-force tile kernel."""
+    from find_b200 import _lib
+    mode, kq = {"cull_kq2": (0, 2), "cull_kq4": (0, 4), "brute": (1, 0)}[request.param]
+    assert _lib.load().findb200_set_knn_mode(mode, kq) == 0
+    yield request.param
+    _lib.load().findb200_set_knn_mode(0, 0)
+
+
+def _surface(seed, n, p, radii=(0.125, 0.05, 0.05), jitter=2e-4):
+    """Points on an ellipsoid shell: the spatial structure the training clouds have (culling is exercised hard)."""
+    g = torch.Generator().manual_seed(seed)
+    u = torch.randn(n, p, 3, generator=g)
+    u = u / u.norm(dim=-1, keepdim=True).clamp_min(1e-12)
+    return u * torch.tensor(radii) * (1 + 0.05 * torch.randn(n, 1, 1, generator=g)) + jitter * torch.randn(n, p, 3, generator=g)
+
+
 def _cloud(seed, n, p, scale=0.1):
     g = torch.Generator().manual_seed(seed)
     return torch.randn(n, p, 3, generator=g) * scale
@@ -40,6 +58,22 @@ def test_knn_ragged_empty_and_ties():
     # lattice queries vs lattice targets: massive exact ties
     g = torch.stack(torch.meshgrid(*[torch.arange(8.0)] * 3, indexing="ij"), -1).reshape(1, -1, 3)
     _check_knn(g + 0.5, g)
+
+
+@pytest.mark.parametrize("n,p1,p2", [(2, 10242, 10000), (1, 20000, 50000), (3, 777, 31)])
+def test_knn_surface_clouds_bit_exact(n, p1, p2):
+    _check_knn(_surface(20, n, p1), _surface(21, n, p2))
+
+
+def test_knn_cross_chunk_ties_and_degenerate_clouds():
+    # the same target set repeated far apart in index order: equal distances in different chunks -> lowest ORIGINAL index
+    t = _surface(22, 1, 2000)
+    _check_knn(_surface(23, 1, 3000), torch.cat([t, t.flip(1), t], 1))
+    # every target identical; all points on a line; a single cell
+    _check_knn(_cloud(24, 1, 200), torch.ones(1, 500, 3) * 0.3)
+    line = torch.linspace(-1, 1, 4000).view(1, -1, 1) * torch.tensor([1.0, 0.0, 0.0])
+    _check_knn(line[:, ::3] + 1e-3, line)
+    _check_knn(torch.zeros(2, 65, 3), torch.zeros(2, 97, 3))
 
 
 def test_knn_split_target_path():
