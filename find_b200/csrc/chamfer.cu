@@ -226,13 +226,20 @@ struct FinalizeDir {
 };
 struct FinalizeParams { FinalizeDir dir[2]; };
 
+constexpr int kFinSlice = 2048;   // points per finalize block
+static inline int fin_blocks(int P) { return P > 0 ? (P + kFinSlice - 1) / kFinSlice : 1; }
+
+// grid (ceil(maxPq/kFinSlice), N, ndir), block 256: unpack keys, write dists / idx, one partial sum per block.
 __global__ void __launch_bounds__(256) knn_finalize_kernel(const FinalizeParams prm) {
-    const FinalizeDir& D = prm.dir[blockIdx.y];
-    const int n = blockIdx.x;
+    const FinalizeDir& D = prm.dir[blockIdx.z];
+    const int n = blockIdx.y;
+    const int nblk = (D.Pq + kFinSlice - 1) / kFinSlice;
+    if ((int)blockIdx.x >= nblk) return;
     const int len_q = D.len_q ? (int)D.len_q[n] : D.Pq;
     const int len_t = D.len_t ? (int)D.len_t[n] : D.Pt;
+    const int i_end = min(D.Pq, ((int)blockIdx.x + 1) * kFinSlice);
     double acc = 0.0;
-    for (int i = threadIdx.x; i < D.Pq; i += blockDim.x) {
+    for (int i = blockIdx.x * kFinSlice + threadIdx.x; i < i_end; i += 256) {
         float dist = 0.f;
         long long j = 0;
         if (i < len_q && len_t > 0) {
@@ -245,31 +252,45 @@ __global__ void __launch_bounds__(256) knn_finalize_kernel(const FinalizeParams 
         if (D.idx) D.idx[(size_t)n * D.Pq + i] = j;
         if (D.idx32) D.idx32[(size_t)n * D.Pq + i] = (int32_t)j;
     }
-    if (D.sums) {
-        __shared__ double s_acc[256];
-        s_acc[threadIdx.x] = acc;
+    if (D.sums) {   // fixed-shape tree: deterministic
+        __shared__ double s_acc[8];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+        if ((threadIdx.x & 31) == 0) s_acc[threadIdx.x >> 5] = acc;
         __syncthreads();
-        for (int o = 128; o > 0; o >>= 1) {
-            if ((int)threadIdx.x < o) s_acc[threadIdx.x] += s_acc[threadIdx.x + o];
-            __syncthreads();
+        if (threadIdx.x == 0) {
+            double t = 0.0;
+            for (int w = 0; w < 8; ++w) t += s_acc[w];
+            D.sums[(size_t)n * nblk + blockIdx.x] = t;
         }
-        if (threadIdx.x == 0) D.sums[n] = s_acc[0];
     }
 }
 
-// loss = ( sum_n sx[n]/max(lx,1) + sum_n sy[n]/max(ly,1) ) / max(N,1)   (chamfer.py mean/mean), one thread.
+// loss = ( sum_n sx[n]/max(lx,1) + sum_n sy[n]/max(ly,1) ) / max(N,1)   (chamfer.py mean/mean); sx[n] = ordered sum
+// of the cloud's block partials.  One warp, lane = cloud (strided), fixed-order combination.
 __global__ void chamfer_reduce_kernel(const double* sx, const double* sy, const int64_t* lx, const int64_t* ly, int N,
                                       int P1, int P2, float* loss, float* loss_xy) {
-    if (threadIdx.x || blockIdx.x) return;
+    const int lane = threadIdx.x;
+    const int nb1 = (P1 + kFinSlice - 1) / kFinSlice, nb2 = (P2 + kFinSlice - 1) / kFinSlice;
     double cx = 0.0, cy = 0.0;
-    for (int n = 0; n < N; ++n) {
-        long long a = lx ? lx[n] : P1, b = ly ? ly[n] : P2;
-        cx += sx[n] / (double)(a < 1 ? 1 : a);
-        cy += sy[n] / (double)(b < 1 ? 1 : b);
+    for (int n = lane; n < N; n += 32) {
+        double a = 0.0, b = 0.0;
+        for (int k = 0; k < nb1; ++k) a += sx[(size_t)n * nb1 + k];
+        for (int k = 0; k < nb2; ++k) b += sy[(size_t)n * nb2 + k];
+        const long long la = lx ? lx[n] : P1, lb = ly ? ly[n] : P2;
+        cx += a / (double)(la < 1 ? 1 : la);
+        cy += b / (double)(lb < 1 ? 1 : lb);
     }
-    const double div = (double)(N < 1 ? 1 : N);
-    *loss = (float)((cx + cy) / div);
-    if (loss_xy) { loss_xy[0] = (float)(cx / div); loss_xy[1] = (float)(cy / div); }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        cx += __shfl_xor_sync(0xffffffffu, cx, o);
+        cy += __shfl_xor_sync(0xffffffffu, cy, o);
+    }
+    if (lane == 0) {
+        const double div = (double)(N < 1 ? 1 : N);
+        *loss = (float)((cx + cy) / div);
+        if (loss_xy) { loss_xy[0] = (float)(cx / div); loss_xy[1] = (float)(cy / div); }
+    }
 }
 
 // ---- backward ---------------------------------------------------------------------------------------
@@ -343,34 +364,49 @@ __global__ void chamfer_bwd_scatter_kernel(const float* __restrict__ a, const fl
 static inline int round_up(int a, int b) { return (a + b - 1) / b * b; }
 static inline size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }
 
+static int grid_log2(int P) { return P < 2048 ? 3 : (P < 40000 ? 4 : 5); }
+
+// Layout: [counter+stats 256 B | bb_max | hist]  zeroed by one memset;  [bb_min | keys_x | keys_y]  set to 0xFF by one
+// memset; then the sorted clouds, permutations, chunk boxes, sort scratch and the per-cloud sums.
 struct Workspace {
-    unsigned int* counter;            // [0] work queue; stats (2 x u64) live 64 bytes further
+    unsigned int* counter;            // [0] work queue; stats (4 x u64) live 64 bytes further
     unsigned long long* stats;
+    unsigned *bbmax_x, *bbmax_y, *bbmin_x, *bbmin_y;
+    int *hist_x, *hist_y;
     unsigned long long *keys_x, *keys_y;
     float *soa_x, *soa_y;
     int *perm_x, *perm_y;
-    float *box_x, *box_y;
+    float *box_x, *box_y, *sbox_x, *sbox_y;
+    int *cell_x, *cell_y, *rank_x, *rank_y;
     double *sum_x, *sum_y;
-    int P1p, P2p, C1p, C2p;
+    int P1p, P2p, C1p, C2p, S1p, S2p, gl1, gl2;
+    size_t zero_bytes, ff_bytes;      // memset extents starting at counter / bbmin_x
     size_t bytes;
 };
 static Workspace carve(void* base, int N, int P1, int P2) {
     Workspace w{};
     w.P1p = round_up(P1 > 0 ? P1 : 1, kChunk); w.P2p = round_up(P2 > 0 ? P2 : 1, kChunk);
     w.C1p = round_up(w.P1p / kChunk, 32); w.C2p = round_up(w.P2p / kChunk, 32);
+    w.S1p = round_up(w.C1p / 32, 32); w.S2p = round_up(w.C2p / 32, 32);
+    w.gl1 = grid_log2(P1); w.gl2 = grid_log2(P2);
     size_t off = 0;
     char* b = (char*)base;
-    w.counter = (unsigned int*)(b + off); w.stats = (unsigned long long*)(b + off + 64); off += 256;
-    w.keys_x = (unsigned long long*)(b + off); off += align256((size_t)N * P1 * 8);
-    w.keys_y = (unsigned long long*)(b + off); off += align256((size_t)N * P2 * 8);
-    w.soa_x = (float*)(b + off); off += align256((size_t)N * 3 * w.P1p * 4);
-    w.soa_y = (float*)(b + off); off += align256((size_t)N * 3 * w.P2p * 4);
-    w.perm_x = (int*)(b + off); off += align256((size_t)N * w.P1p * 4);
-    w.perm_y = (int*)(b + off); off += align256((size_t)N * w.P2p * 4);
-    w.box_x = (float*)(b + off); off += align256((size_t)N * 6 * w.C1p * 4);
-    w.box_y = (float*)(b + off); off += align256((size_t)N * 6 * w.C2p * 4);
-    w.sum_x = (double*)(b + off); off += align256((size_t)N * 8);
-    w.sum_y = (double*)(b + off); off += align256((size_t)N * 8);
+    auto take = [&](size_t bytes) { char* p = b + off; off += align256(bytes); return p; };
+    w.counter = (unsigned int*)take(256); w.stats = (unsigned long long*)((char*)w.counter + 64);
+    w.bbmax_x = (unsigned*)take((size_t)N * 12); w.bbmax_y = (unsigned*)take((size_t)N * 12);
+    w.hist_x = (int*)take(((size_t)N << (3 * w.gl1)) * 4); w.hist_y = (int*)take(((size_t)N << (3 * w.gl2)) * 4);
+    w.zero_bytes = off;
+    w.bbmin_x = (unsigned*)take((size_t)N * 12); w.bbmin_y = (unsigned*)take((size_t)N * 12);
+    w.keys_x = (unsigned long long*)take((size_t)N * P1 * 8);
+    w.keys_y = (unsigned long long*)take((size_t)N * P2 * 8);
+    w.ff_bytes = off - w.zero_bytes;
+    w.soa_x = (float*)take((size_t)N * 3 * w.P1p * 4); w.soa_y = (float*)take((size_t)N * 3 * w.P2p * 4);
+    w.perm_x = (int*)take((size_t)N * w.P1p * 4); w.perm_y = (int*)take((size_t)N * w.P2p * 4);
+    w.box_x = (float*)take((size_t)N * 6 * w.C1p * 4); w.box_y = (float*)take((size_t)N * 6 * w.C2p * 4);
+    w.sbox_x = (float*)take((size_t)N * 6 * w.S1p * 4); w.sbox_y = (float*)take((size_t)N * 6 * w.S2p * 4);
+    w.cell_x = (int*)take((size_t)N * P1 * 4); w.cell_y = (int*)take((size_t)N * P2 * 4);
+    w.rank_x = (int*)take((size_t)N * P1 * 4); w.rank_y = (int*)take((size_t)N * P2 * 4);
+    w.sum_x = (double*)take((size_t)N * fin_blocks(P1) * 8); w.sum_y = (double*)take((size_t)N * fin_blocks(P2) * 8);
     w.bytes = off;
     return w;
 }
@@ -411,8 +447,6 @@ static int knn_mode() {
     return g_knn_mode;
 }
 static int g_cull_kq = 0;   // 0 = heuristic
-
-static int grid_log2(int P) { return P < 2048 ? 3 : (P < 40000 ? 4 : 5); }
 
 static int run_knn_brute(const float* x, const float* y, const int64_t* lx, const int64_t* ly, int N, int P1, int P2,
                          bool both, Workspace& w, cudaStream_t st) {
@@ -456,28 +490,30 @@ static int launch_cull(CullParams& prm, int N, int P1, int P2, bool both, cudaSt
 static int run_knn_cull(const float* x, const float* y, const int64_t* lx, const int64_t* ly, int N, int P1, int P2,
                         bool both, Workspace& w, cudaStream_t st) {
     SortParams sp{};
-    sp.set[0] = SortSet{x, lx, w.soa_x, w.perm_x, w.box_x, P1, w.P1p, w.C1p, grid_log2(P1)};
-    sp.set[1] = SortSet{y, ly, w.soa_y, w.perm_y, w.box_y, P2, w.P2p, w.C2p, grid_log2(P2)};
-    const int gl = sp.set[0].glog2 > sp.set[1].glog2 ? sp.set[0].glog2 : sp.set[1].glog2;
-    const size_t smem = (size_t)4 << (3 * gl);
-    static bool attr_done = false;
-    if (!attr_done) {
-        FB_CUDA(cudaFuncSetAttribute(sort_cloud_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 4 << 15));
-        attr_done = true;
-    }
-    FB_MARK("chamfer_prep", st);
-    sort_cloud_kernel<<<dim3(N, 2), kSortThreads, smem, st>>>(sp);
+    sp.set[0] = SortSet{x, lx, w.soa_x, w.perm_x, w.box_x, w.sbox_x, w.bbmin_x, w.bbmax_x, w.hist_x, w.cell_x, w.rank_x,
+                        P1, w.P1p, w.C1p, w.S1p, w.gl1};
+    sp.set[1] = SortSet{y, ly, w.soa_y, w.perm_y, w.box_y, w.sbox_y, w.bbmin_y, w.bbmax_y, w.hist_y, w.cell_y, w.rank_y,
+                        P2, w.P2p, w.C2p, w.S2p, w.gl2};
+    const int Pm = P1 > P2 ? P1 : P2, Ppm = w.P1p > w.P2p ? w.P1p : w.P2p;
+    FB_MARK("sort_bbox", st);
+    cloud_bbox_kernel<<<dim3((Pm + 1023) / 1024, N, 2), 256, 0, st>>>(sp);
+    FB_MARK("sort_hist", st);
+    cloud_hist_kernel<<<dim3((Pm + 255) / 256, N, 2), 256, 0, st>>>(sp);
+    FB_MARK("sort_scatter", st);
+    cloud_scan_kernel<<<dim3(N, 2), 1024, 0, st>>>(sp);
+    FB_MARK("sort_scatter2", st);
+    cloud_scatter_kernel<<<dim3((Ppm + 255) / 256, N, 2), 256, 0, st>>>(sp);
+    FB_MARK("sort_boxes", st);
+    cloud_boxes_kernel<<<dim3((Ppm / kCullChunk + 7) / 8, N, 2), 256, 0, st>>>(sp);
+    cloud_superboxes_kernel<<<dim3((Ppm / kCullChunk / 32 + 8) / 8, N, 2), 256, 0, st>>>(sp);
     FB_CUDA(cudaGetLastError());
 
     CullParams prm{};
     prm.N = N; prm.counter = w.counter; prm.stats = w.stats; prm.ndir = both ? 2 : 1;
-    prm.dir[0] = CullDir{w.soa_x, w.perm_x, w.soa_y, w.perm_y, w.box_y, lx, ly, w.keys_x, P1, w.P1p, P2, w.P2p, w.C2p, 0};
-    prm.dir[1] = CullDir{w.soa_y, w.perm_y, w.soa_x, w.perm_x, w.box_x, ly, lx, w.keys_y, P2, w.P2p, P1, w.P1p, w.C1p, 0};
-    int kq = g_cull_kq;
-    if (!kq) {
-        const long long q = (long long)N * (P1 + (both ? P2 : 0));
-        kq = q / 128 >= (long long)num_sms() * 32 ? 4 : 2;
-    }
+    prm.dir[0] = CullDir{w.soa_x, w.perm_x, w.soa_y, w.perm_y, w.box_y, w.sbox_y, lx, ly, w.keys_x, P1, w.P1p, P2, w.P2p, w.C2p, w.S2p, 0};
+    prm.dir[1] = CullDir{w.soa_y, w.perm_y, w.soa_x, w.perm_x, w.box_x, w.sbox_x, ly, lx, w.keys_y, P2, w.P2p, P1, w.P1p, w.C1p, w.S1p, 0};
+    const int kq = g_cull_kq ? g_cull_kq : 2;   // 2 queries per lane measured best on cfg2-cfg4 shapes (tools/knn_bench.py)
+    if (kq == 1) return launch_cull<1>(prm, N, P1, P2, both, st);
     return kq == 4 ? launch_cull<4>(prm, N, P1, P2, both, st) : launch_cull<2>(prm, N, P1, P2, both, st);
 }
 
@@ -490,8 +526,9 @@ static int run_knn(const float* x, const float* y, const int64_t* lx, const int6
                "knn: workspace too small (%zu < %zu bytes)", ws_bytes, w.bytes);
     if (N == 0 || (P1 == 0 && P2 == 0)) return 0;
     // queue counter + stats = 0, keys = 0xFF.. (identity of atomicMin; also what an unreachable query keeps)
-    FB_CUDA(cudaMemsetAsync(w.counter, 0, 256, st));
-    FB_CUDA(cudaMemsetAsync(w.keys_x, 0xFF, (size_t)((char*)w.soa_x - (char*)w.keys_x), st));
+    FB_MARK("knn_memsets", st);
+    FB_CUDA(cudaMemsetAsync(w.counter, 0, w.zero_bytes, st));
+    FB_CUDA(cudaMemsetAsync(w.bbmin_x, 0xFF, w.ff_bytes, st));
     if (P1 == 0 || P2 == 0) return 0;
     return knn_mode() == 1 ? run_knn_brute(x, y, lx, ly, N, P1, P2, both, w, st)
                            : run_knn_cull(x, y, lx, ly, N, P1, P2, both, w, st);
@@ -506,7 +543,7 @@ using namespace fb::chamfer;
 extern "C" {
 
 int findb200_set_knn_mode(int mode, int kq) {
-    FB_REQUIRE((mode == 0 || mode == 1) && (kq == 0 || kq == 2 || kq == 4), FINDB200_ERR_ARG, "set_knn_mode: mode 0/1, kq 0/2/4");
+    FB_REQUIRE((mode == 0 || mode == 1) && (kq == 0 || kq == 1 || kq == 2 || kq == 4), FINDB200_ERR_ARG, "set_knn_mode: mode 0/1, kq 0/1/2/4");
     g_knn_mode = mode; g_cull_kq = kq;
     return 0;
 }
@@ -533,7 +570,7 @@ int findb200_knn1(const float* p1, const float* p2, const int64_t* len1, const i
     FinalizeParams fp{};
     fp.dir[0] = FinalizeDir{w.keys_x, len1, len2, dists, idx, nullptr, nullptr, P1, P2};
     FB_MARK("knn_finalize", st);
-    knn_finalize_kernel<<<dim3(N, 1), 256, 0, st>>>(fp);
+    knn_finalize_kernel<<<dim3(fin_blocks(P1), N, 1), 256, 0, st>>>(fp);
     FB_CUDA(cudaGetLastError());
     FB_MARK_END(st);
     return 0;
@@ -568,7 +605,7 @@ int findb200_chamfer_forward(const float* x, const float* y, const int64_t* x_le
     fp.dir[0] = FinalizeDir{w.keys_x, x_len, y_len, dist_x, idx_x, nullptr, w.sum_x, P1, P2};
     fp.dir[1] = FinalizeDir{w.keys_y, y_len, x_len, dist_y, idx_y, nullptr, w.sum_y, P2, P1};
     FB_MARK("knn_finalize", st);
-    knn_finalize_kernel<<<dim3(N, 2), 256, 0, st>>>(fp);
+    knn_finalize_kernel<<<dim3(fin_blocks(P1 > P2 ? P1 : P2), N, 2), 256, 0, st>>>(fp);
     FB_MARK("chamfer_reduce", st);
     chamfer_reduce_kernel<<<1, 32, 0, st>>>(w.sum_x, w.sum_y, x_len, y_len, N, P1, P2, loss, nullptr);
     FB_CUDA(cudaGetLastError());

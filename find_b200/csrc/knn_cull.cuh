@@ -3,18 +3,19 @@
 // Same contract as the brute-force tile kernel (dist = fmaf(dz,dz,fmaf(dy,dy,dx*dx)), lowest ORIGINAL index on ties,
 // bit-exact vs oracle/chamfer_oracle.c), but most (query group, target chunk) pairs are never evaluated:
 //
-//   1. sort_cloud_kernel: one CTA per cloud bins the points into a cubic grid (G^3 cells over the cloud's bounding
-//      box, Morton cell order, counting sort in shared memory) and writes them as SoA rows padded with +inf to a
-//      multiple of 32, the permutation back to original indices, and the bounding box of every 32-point chunk.
+//   1. cloud_{bbox,hist,scan,scatter,boxes}_kernel: a counting sort of every cloud into the cells of a cubic grid (G^3 cells
+//      over the cloud's bounding box, Hilbert-curve cell order), written as SoA rows padded with +inf to a multiple of
+//      32, plus the permutation back to original indices and the bounding box of every 32-point chunk.
 //   2. knn_cull_kernel: persistent warps.  A warp owns 32*kQ consecutive sorted queries (spatially compact), kQ per
 //      lane in registers.  It evaluates the chunk nearest to the group first, then walks the chunk boxes 32 at a time
-//      (one box per lane), and evaluates a chunk only if LB(group box, chunk box) <= U, U = max over the group's
-//      queries of their current best distance.  Chunk evaluation is the packed-fp32x2 brute-force inner loop.
+//      (one box per lane): a chunk survives level 1 if LB(group box, chunk box) <= U, U = max over the group's queries
+//      of their current best distance, and is evaluated if, at level 2, LB(query, chunk box) <= best[query] for some
+//      query of the group.  Chunk evaluation is the packed-fp32x2 brute-force inner loop.
 //
 // Why the cull is exact: LB is computed with the SAME operation sequence as the distance, on the per-axis gaps
 // g = max(0, tlo - qhi, qlo - thi).  Round-to-nearest subtraction, multiplication and fma are monotone, so for every
 // query in the group box and every target in the chunk box the COMPUTED fp32 distance is >= LB.  A chunk is skipped
-// only when LB > U >= best[q] for all q, so it holds neither a closer point nor a tie.  Ties across chunks (equal
+// only when LB > best[q] for all q, so it holds neither a closer point nor a tie.  Ties across chunks (equal
 // distance, lower original index elsewhere) set a per-query flag in the hot loop and take a slow exact path.
 #pragma once
 #include "common.cuh"
@@ -24,17 +25,29 @@ namespace fb {
 namespace chamfer {
 
 constexpr int kCullChunk = 32;
-constexpr int kSortThreads = 1024;
 
+// One cloud set (x or y): [N] clouds of up to P points.
 struct SortSet {
     const float* aos;       // [N][P][3]
     const int64_t* len;     // nullable
-    float* soa;             // [N][3][Ppad]
-    int* perm;              // [N][Ppad]   sorted position -> original index
-    float* box;             // [N][6][Cpad]  lo xyz, hi xyz per 32-point chunk
-    int P, Ppad, Cpad, glog2;
+    float* soa;             // [N][3][Ppad]   sorted, padded with +inf
+    int* perm;              // [N][Ppad]      sorted position -> original index
+    float* box;             // [N][6][Cpad]   lo xyz, hi xyz per 32-point chunk
+    float* sbox;            // [N][6][Spad]   lo xyz, hi xyz per 32-chunk super-chunk
+    unsigned* bb_min;       // [N][3]  order-encoded floats, identity 0xFFFFFFFF
+    unsigned* bb_max;       // [N][3]  order-encoded floats, identity 0
+    int* hist;              // [N][ncell]     zeroed by the host
+    int* cell;              // [N][P]         cell of point i
+    int* rank;              // [N][P]         arrival rank of point i inside its cell
+    int P, Ppad, Cpad, Spad, glog2;
 };
 struct SortParams { SortSet set[2]; };
+
+FB_DEVINL unsigned enc_ord(float f) {       // monotone float -> uint
+    const unsigned u = __float_as_uint(f);
+    return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+}
+FB_DEVINL float dec_ord(unsigned e) { return __uint_as_float((e & 0x80000000u) ? (e & 0x7fffffffu) : ~e); }
 
 FB_DEVINL uint32_t spread3(uint32_t v) {   // 10 bits -> every third bit
     v = (v | (v << 16)) & 0x030000FFu;
@@ -43,39 +56,59 @@ FB_DEVINL uint32_t spread3(uint32_t v) {   // 10 bits -> every third bit
     v = (v | (v << 2)) & 0x09249249u;
     return v;
 }
+// Hilbert index of an integer cell (bits per axis = b): consecutive indices are face-adjacent cells, so a run of the
+// sorted order is a compact blob (no Morton jumps).  Skilling's axes-to-transpose, then bit interleave.
+FB_DEVINL uint32_t hilbert3(uint32_t x, uint32_t y, uint32_t z, int b) {
+    uint32_t X[3] = {x, y, z};
+    const uint32_t M = 1u << (b - 1);
+    for (uint32_t Q = M; Q > 1; Q >>= 1) {
+        const uint32_t Pm = Q - 1;
+#pragma unroll
+        for (int i = 0; i < 3; ++i) {
+            if (X[i] & Q) X[0] ^= Pm;
+            else { const uint32_t t = (X[0] ^ X[i]) & Pm; X[0] ^= t; X[i] ^= t; }
+        }
+    }
+    X[1] ^= X[0]; X[2] ^= X[1];
+    uint32_t t = 0;
+    for (uint32_t Q = M; Q > 1; Q >>= 1)
+        if (X[2] & Q) t ^= Q - 1;
+    X[0] ^= t; X[1] ^= t; X[2] ^= t;
+    return (spread3(X[0]) << 2) | (spread3(X[1]) << 1) | spread3(X[2]);
+}
 FB_DEVINL int cell_coord(float p, float lo, float inv_h, int G) {
     const float f = (p - lo) * inv_h;
     int c = 0;
     if (f >= 0.f) c = f < (float)G ? (int)f : G - 1;   // NaN -> 0
     return c;
 }
-
-// grid (N, nsets), block kSortThreads, dynamic smem = (1 << 3*glog2) * 4 bytes
-__global__ void __launch_bounds__(kSortThreads) sort_cloud_kernel(const SortParams prm) {
-    extern __shared__ int s_hist[];
-    __shared__ float s_red[32][6];
-    __shared__ float s_bb[6];
-    __shared__ int s_wsum[32];
-
-    const SortSet& S = prm.set[blockIdx.y];
-    const int n = blockIdx.x, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
-    if (S.P <= 0) return;
+FB_DEVINL int set_len(const SortSet& S, int n) {
     int len = S.len ? (int)S.len[n] : S.P;
-    len = len < 0 ? 0 : (len > S.P ? S.P : len);
-    const float* aos = S.aos + (size_t)n * S.P * 3;
-    float* soa = S.soa + (size_t)n * 3 * S.Ppad;
-    int* perm = S.perm + (size_t)n * S.Ppad;
-    float* box = S.box + (size_t)n * 6 * S.Cpad;
-    const int G = 1 << S.glog2, ncell = 1 << (3 * S.glog2);
+    return len < 0 ? 0 : (len > S.P ? S.P : len);
+}
 
-    // 1. bounding box of the cloud (NaNs ignored by fminf/fmaxf)
+// 1. bounding box per cloud.  grid (ceil(maxP/1024), N, 2), block 256, 4 points per thread.
+__global__ void __launch_bounds__(256) cloud_bbox_kernel(const SortParams prm) {
+    const SortSet& S = prm.set[blockIdx.z];
+    const int n = blockIdx.y;
+    const int len = set_len(S, n);
+    const int i0 = blockIdx.x * 1024;
+    if (i0 >= len) return;
+    const float* aos = S.aos + (size_t)n * S.P * 3;
     float lo[3] = {CUDART_INF_F, CUDART_INF_F, CUDART_INF_F}, hi[3] = {-CUDART_INF_F, -CUDART_INF_F, -CUDART_INF_F};
-    for (int i = tid; i < len; i += kSortThreads) {
 #pragma unroll
-        for (int k = 0; k < 3; ++k) { const float v = aos[(size_t)i * 3 + k]; lo[k] = fminf(lo[k], v); hi[k] = fmaxf(hi[k], v); }
+    for (int r = 0; r < 4; ++r) {
+        const int i = i0 + r * 256 + threadIdx.x;
+        if (i < len) {
+#pragma unroll
+            for (int k = 0; k < 3; ++k) { const float v = aos[(size_t)i * 3 + k]; lo[k] = fminf(lo[k], v); hi[k] = fmaxf(hi[k], v); }
+        }
     }
+    __shared__ float s_red[8][6];
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
 #pragma unroll
     for (int k = 0; k < 3; ++k)
+#pragma unroll
         for (int o = 16; o > 0; o >>= 1) {
             lo[k] = fminf(lo[k], __shfl_xor_sync(0xffffffffu, lo[k], o));
             hi[k] = fmaxf(hi[k], __shfl_xor_sync(0xffffffffu, hi[k], o));
@@ -84,98 +117,159 @@ __global__ void __launch_bounds__(kSortThreads) sort_cloud_kernel(const SortPara
 #pragma unroll
         for (int k = 0; k < 3; ++k) { s_red[wid][k] = lo[k]; s_red[wid][3 + k] = hi[k]; }
     }
-    for (int c = tid; c < ncell; c += kSortThreads) s_hist[c] = 0;
+    __syncthreads();
+    if (threadIdx.x < 6) {
+        const int k = threadIdx.x;
+        float v = s_red[0][k];
+        for (int w = 1; w < 8; ++w) v = k < 3 ? fminf(v, s_red[w][k]) : fmaxf(v, s_red[w][k]);
+        if (k < 3) { if (v < CUDART_INF_F) atomicMin(S.bb_min + n * 3 + k, enc_ord(v)); }
+        else if (v > -CUDART_INF_F) atomicMax(S.bb_max + n * 3 + (k - 3), enc_ord(v));
+    }
+}
+
+struct CloudGrid { float lo[3]; float inv_h; };
+FB_DEVINL CloudGrid cloud_grid(const SortSet& S, int n) {
+    CloudGrid g;
+    float ext = 0.f;
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        const unsigned a = S.bb_min[n * 3 + k], b = S.bb_max[n * 3 + k];
+        const float lo = a == 0xFFFFFFFFu ? 0.f : dec_ord(a), hi = b == 0u ? 0.f : dec_ord(b);
+        g.lo[k] = lo;
+        ext = fmaxf(ext, hi - lo);
+    }
+    const int G = 1 << S.glog2;
+    g.inv_h = (ext > 0.f && ext < CUDART_INF_F) ? (float)G / ext : 0.f;     // cubic cells; degenerate cloud -> one cell
+    if (!(g.inv_h < CUDART_INF_F)) g.inv_h = 0.f;
+    return g;
+}
+
+// 2. cell + arrival rank of every point.  grid (ceil(maxP/256), N, 2), block 256.
+__global__ void __launch_bounds__(256) cloud_hist_kernel(const SortParams prm) {
+    const SortSet& S = prm.set[blockIdx.z];
+    const int n = blockIdx.y;
+    const int len = set_len(S, n);
+    const int i = blockIdx.x * 256 + threadIdx.x;
+    if (i >= len) return;
+    const CloudGrid g = cloud_grid(S, n);
+    const int G = 1 << S.glog2;
+    const float* p = S.aos + ((size_t)n * S.P + i) * 3;
+    const uint32_t cx = cell_coord(p[0], g.lo[0], g.inv_h, G), cy = cell_coord(p[1], g.lo[1], g.inv_h, G),
+                   cz = cell_coord(p[2], g.lo[2], g.inv_h, G);
+    const int cell = (int)hilbert3(cx, cy, cz, S.glog2);
+    S.cell[(size_t)n * S.P + i] = cell;
+    S.rank[(size_t)n * S.P + i] = atomicAdd(S.hist + ((size_t)n << (3 * S.glog2)) + cell, 1);
+}
+
+// 3. in-place exclusive scan of every cloud's histogram.  grid (N, 2), block 1024: warp w owns the contiguous segment
+//    [w*seg, (w+1)*seg) and walks it in coalesced 32-entry rows.
+__global__ void __launch_bounds__(1024) cloud_scan_kernel(const SortParams prm) {
+    __shared__ int s_wsum[32];
+    const SortSet& S = prm.set[blockIdx.y];
+    if (S.P <= 0) return;
+    const int n = blockIdx.x, lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const int ncell = 1 << (3 * S.glog2), seg = ncell / 32;
+    int* hist = S.hist + ((size_t)n << (3 * S.glog2)) + wid * seg;
+    int tot = 0;
+    for (int r = lane; r < seg; r += 32) tot += hist[r];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) tot += __shfl_xor_sync(0xffffffffu, tot, o);
+    if (lane == 0) s_wsum[wid] = tot;
     __syncthreads();
     if (wid == 0) {
+        const int v = s_wsum[lane];
+        int w = v;
 #pragma unroll
-        for (int k = 0; k < 3; ++k) {
-            float a = s_red[lane][k], b = s_red[lane][3 + k];
-            for (int o = 16; o > 0; o >>= 1) {
-                a = fminf(a, __shfl_xor_sync(0xffffffffu, a, o));
-                b = fmaxf(b, __shfl_xor_sync(0xffffffffu, b, o));
-            }
-            if (lane == 0) { s_bb[k] = a; s_bb[3 + k] = b; }
-        }
-    }
-    __syncthreads();
-    const float blo[3] = {s_bb[0], s_bb[1], s_bb[2]};
-    float ext = fmaxf(fmaxf(s_bb[3] - s_bb[0], s_bb[4] - s_bb[1]), s_bb[5] - s_bb[2]);
-    float inv_h = (ext > 0.f && ext < CUDART_INF_F) ? (float)G / ext : 0.f;   // cubic cells; degenerate cloud -> one cell
-    if (!(inv_h < CUDART_INF_F)) inv_h = 0.f;
-
-    auto cell_of = [&](int i) -> int {
-        const float x = aos[(size_t)i * 3], y = aos[(size_t)i * 3 + 1], z = aos[(size_t)i * 3 + 2];
-        const uint32_t cx = cell_coord(x, blo[0], inv_h, G), cy = cell_coord(y, blo[1], inv_h, G),
-                       cz = cell_coord(z, blo[2], inv_h, G);
-        return (int)(spread3(cx) | (spread3(cy) << 1) | (spread3(cz) << 2));
-    };
-
-    // 2. histogram
-    for (int i = tid; i < len; i += kSortThreads) atomicAdd(&s_hist[cell_of(i)], 1);
-    __syncthreads();
-
-    // 3. exclusive scan over cells (each thread owns `per` consecutive cells)
-    {
-        const int per = ncell >= kSortThreads ? ncell / kSortThreads : 1;
-        const int c0 = tid * per;
-        int sum = 0;
-        if (c0 < ncell)
-            for (int j = 0; j < per; ++j) sum += s_hist[c0 + j];
-        int inc = sum;
         for (int o = 1; o < 32; o <<= 1) {
-            const int v = __shfl_up_sync(0xffffffffu, inc, o);
-            if (lane >= o) inc += v;
+            const int u = __shfl_up_sync(0xffffffffu, w, o);
+            if (lane >= o) w += u;
         }
-        if (lane == 31) s_wsum[wid] = inc;
-        __syncthreads();
-        if (wid == 0) {
-            int w = s_wsum[lane];
-            for (int o = 1; o < 32; o <<= 1) {
-                const int v = __shfl_up_sync(0xffffffffu, w, o);
-                if (lane >= o) w += v;
-            }
-            s_wsum[lane] = w;   // inclusive over warps
-        }
-        __syncthreads();
-        int run = inc - sum + (wid ? s_wsum[wid - 1] : 0);
-        if (c0 < ncell)
-            for (int j = 0; j < per; ++j) { const int h = s_hist[c0 + j]; s_hist[c0 + j] = run; run += h; }
+        s_wsum[lane] = w - v;   // exclusive over warps
     }
     __syncthreads();
-
-    // 4. scatter into cell order (order inside a cell is arbitrary; results do not depend on it)
-    for (int i = tid; i < len; i += kSortThreads) {
-        const int pos = atomicAdd(&s_hist[cell_of(i)], 1);
-        soa[pos] = aos[(size_t)i * 3];
-        soa[S.Ppad + pos] = aos[(size_t)i * 3 + 1];
-        soa[2 * S.Ppad + pos] = aos[(size_t)i * 3 + 2];
-        perm[pos] = i;
+    int carry = s_wsum[wid];
+    for (int r0 = 0; r0 < seg; r0 += 32) {
+        const int r = r0 + lane;
+        const int v = r < seg ? hist[r] : 0;
+        int inc = v;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int u = __shfl_up_sync(0xffffffffu, inc, o);
+            if (lane >= o) inc += u;
+        }
+        if (r < seg) hist[r] = carry + inc - v;
+        carry += __shfl_sync(0xffffffffu, inc, 31);
     }
-    for (int i = len + tid; i < S.Ppad; i += kSortThreads) {
+}
+
+// 4. scatter into curve order: pos = start[cell] + rank.  grid (ceil(maxPpad/256), N, 2), block 256.
+__global__ void __launch_bounds__(256) cloud_scatter_kernel(const SortParams prm) {
+    const SortSet& S = prm.set[blockIdx.z];
+    const int n = blockIdx.y;
+    const int len = set_len(S, n);
+    const int i = blockIdx.x * 256 + threadIdx.x;
+    if (i >= S.Ppad || S.P <= 0) return;
+    float* soa = S.soa + (size_t)n * 3 * S.Ppad;
+    int* perm = S.perm + (size_t)n * S.Ppad;
+    if (i < len) {
+        const float* p = S.aos + ((size_t)n * S.P + i) * 3;
+        const int pos = S.hist[((size_t)n << (3 * S.glog2)) + S.cell[(size_t)n * S.P + i]] + S.rank[(size_t)n * S.P + i];
+        soa[pos] = p[0]; soa[S.Ppad + pos] = p[1]; soa[2 * S.Ppad + pos] = p[2];
+        perm[pos] = i;
+    } else {
         soa[i] = CUDART_INF_F; soa[S.Ppad + i] = CUDART_INF_F; soa[2 * S.Ppad + i] = CUDART_INF_F;
         perm[i] = 0;
     }
-    __syncthreads();
+}
 
-    // 5. chunk boxes (plain loads: written by this block just above)
-    const int nchunk = (len + kCullChunk - 1) / kCullChunk;
-    for (int c = wid; c < nchunk; c += kSortThreads / 32) {
-        const int i = c * kCullChunk + lane;
-        float v[3], a[3], b[3];
+// 5. bounding box of every 32-point chunk of the sorted cloud.  grid (ceil(maxC/8), N, 2), block 256 (warp per chunk).
+__global__ void __launch_bounds__(256) cloud_boxes_kernel(const SortParams prm) {
+    const SortSet& S = prm.set[blockIdx.z];
+    const int n = blockIdx.y, lane = threadIdx.x & 31;
+    const int len = set_len(S, n);
+    const int c = blockIdx.x * 8 + (threadIdx.x >> 5);
+    if (c * kCullChunk >= len) return;
+    const float* soa = S.soa + (size_t)n * 3 * S.Ppad;
+    float* box = S.box + (size_t)n * 6 * S.Cpad;
+    const int i = c * kCullChunk + lane;
+    float a[3], b[3];
 #pragma unroll
-        for (int k = 0; k < 3; ++k) {
-            v[k] = soa[k * S.Ppad + i];
-            a[k] = i < len ? v[k] : CUDART_INF_F;
-            b[k] = i < len ? v[k] : -CUDART_INF_F;
-            for (int o = 16; o > 0; o >>= 1) {
-                a[k] = fminf(a[k], __shfl_xor_sync(0xffffffffu, a[k], o));
-                b[k] = fmaxf(b[k], __shfl_xor_sync(0xffffffffu, b[k], o));
-            }
-        }
-        if (lane == 0) {
+    for (int k = 0; k < 3; ++k) {
+        const float v = soa[k * S.Ppad + i];
+        a[k] = i < len ? v : CUDART_INF_F;
+        b[k] = i < len ? v : -CUDART_INF_F;
 #pragma unroll
-            for (int k = 0; k < 3; ++k) { box[k * S.Cpad + c] = a[k]; box[(3 + k) * S.Cpad + c] = b[k]; }
+        for (int o = 16; o > 0; o >>= 1) {
+            a[k] = fminf(a[k], __shfl_xor_sync(0xffffffffu, a[k], o));
+            b[k] = fmaxf(b[k], __shfl_xor_sync(0xffffffffu, b[k], o));
         }
+    }
+    if (lane == 0) {
+#pragma unroll
+        for (int k = 0; k < 3; ++k) { box[k * S.Cpad + c] = a[k]; box[(3 + k) * S.Cpad + c] = b[k]; }
+    }
+}
+
+// 6. bounding box of every super-chunk (32 chunks).  grid (ceil(maxS/8), N, 2), block 256 (warp per super-chunk).
+__global__ void __launch_bounds__(256) cloud_superboxes_kernel(const SortParams prm) {
+    const SortSet& S = prm.set[blockIdx.z];
+    const int n = blockIdx.y, lane = threadIdx.x & 31;
+    const int nchunk = (set_len(S, n) + kCullChunk - 1) / kCullChunk;
+    const int sc = blockIdx.x * 8 + (threadIdx.x >> 5);
+    if (sc * 32 >= nchunk) return;
+    const float* box = S.box + (size_t)n * 6 * S.Cpad;
+    float* sbox = S.sbox + (size_t)n * 6 * S.Spad;
+    const int c = sc * 32 + lane;
+#pragma unroll
+    for (int k = 0; k < 6; ++k) {
+        float v = k < 3 ? CUDART_INF_F : -CUDART_INF_F;
+        if (c < nchunk) v = box[k * S.Cpad + c];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            const float u = __shfl_xor_sync(0xffffffffu, v, o);
+            v = k < 3 ? fminf(v, u) : fmaxf(v, u);
+        }
+        if (lane == 0) sbox[k * S.Spad + sc] = v;
     }
 }
 
@@ -186,10 +280,11 @@ struct CullDir {
     const float* t_soa;   // sorted [N][3][Pt_pad]
     const int* t_perm;    // [N][Pt_pad]
     const float* t_box;   // [N][6][Ct_pad]
+    const float* t_sbox;  // [N][6][St_pad]   boxes of 32-chunk super-chunks
     const int64_t* len_q; // nullable
     const int64_t* len_t; // nullable
     unsigned long long* keys;   // [N][Pq], original query order
-    int Pq, Pq_pad, Pt, Pt_pad, Ct_pad, n_groups;
+    int Pq, Pq_pad, Pt, Pt_pad, Ct_pad, St_pad, n_groups;
 };
 struct CullParams {
     CullDir dir[2];
@@ -211,11 +306,14 @@ FB_DEVINL float warp_min(float v) {
 FB_DEVINL float gap(float alo, float ahi, float blo, float bhi) {   // distance between intervals, rounded like d = q - t
     return fmaxf(0.f, fmaxf(__fsub_rn(blo, ahi), __fsub_rn(alo, bhi)));
 }
+FB_DEVINL void prefetch_l1(const void* p) { asm volatile("prefetch.global.L1 [%0];" ::"l"(p)); }
 FB_DEVINL float lb_dist(float gx, float gy, float gz) { return __fmaf_rn(gz, gz, __fmaf_rn(gy, gy, __fmul_rn(gx, gx))); }
 
 template <int kQ>
 __global__ void __launch_bounds__(128) knn_cull_kernel(const CullParams prm) {
+    __shared__ float4 s_stage[4][24];      // per warp: one target chunk (x row | y row | z row)
     const int lane = threadIdx.x & 31;
+    float4* stage = s_stage[threadIdx.x >> 5];
     unsigned long long n_eval = 0, n_slow = 0, n_eval_max = 0, n_items = 0;
 
     for (;;) {
@@ -261,17 +359,25 @@ __global__ void __launch_bounds__(128) knn_cull_kernel(const CullParams prm) {
 
         const unsigned long long n_eval_before = n_eval;
         ++n_items;
-        float U = CUDART_INF_F;
-        auto evaluate = [&](int c) {
-            const float4* sx = reinterpret_cast<const float4*>(tsoa + (size_t)c * kCullChunk);
-            const float4* sy = reinterpret_cast<const float4*>(tsoa + D.Pt_pad + (size_t)c * kCullChunk);
-            const float4* sz = reinterpret_cast<const float4*>(tsoa + 2 * (size_t)D.Pt_pad + (size_t)c * kCullChunk);
+        // a chunk travels global -> one float4 per lane (24 lanes) -> the warp's shared-memory stage -> broadcast reads:
+        // one LDG per chunk, issued one chunk ahead of its use
+        auto load_part = [&](int c) -> float4 {
+            float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (lane < 24)
+                v = __ldg(reinterpret_cast<const float4*>(tsoa + (size_t)(lane >> 3) * D.Pt_pad + (size_t)c * kCullChunk) + (lane & 7));
+            return v;
+        };
+        auto evaluate = [&](int c, const float4& part) {
+            __syncwarp();
+            if (lane < 24) stage[lane] = part;
+            __syncwarp();
+            const float4 *sx = stage, *sy = stage + 8, *sz = stage + 16;
             float cmin[kQ];
 #pragma unroll
             for (int q = 0; q < kQ; ++q) cmin[q] = CUDART_INF_F;
 #pragma unroll
             for (int g = 0; g < kCullChunk / 4; ++g) {
-                const float4 X = __ldg(sx + g), Y = __ldg(sy + g), Z = __ldg(sz + g);
+                const float4 X = sx[g], Y = sy[g], Z = sz[g];
                 const uint64_t x01 = pack2(X.x, X.y), x23 = pack2(X.z, X.w);
                 const uint64_t y01 = pack2(Y.x, Y.y), y23 = pack2(Y.z, Y.w);
                 const uint64_t z01 = pack2(Z.x, Z.y), z23 = pack2(Z.z, Z.w);
@@ -288,26 +394,24 @@ __global__ void __launch_bounds__(128) knn_cull_kernel(const CullParams prm) {
                     cmin[q] = min3(cmin[q], lo, hi);
                 }
             }
-            float m = 0.f;
 #pragma unroll
             for (int q = 0; q < kQ; ++q) {
                 if (cmin[q] < best[q]) { best[q] = cmin[q]; bchunk[q] = c; tie &= ~(1u << q); }
                 else if (cmin[q] == best[q]) tie |= 1u << q;
-                m = fmaxf(m, best[q]);
             }
-            U = warp_max(m);
             ++n_eval;
         };
 
-        // seed: the chunk whose box centre is nearest to the group's centre
-        int seed = 0;
-        {
+        // seed: nearest super-chunk (32 chunks) by box centre, then the nearest chunk inside it
+        const float* sbox = D.t_sbox + (size_t)n * 6 * D.St_pad;
+        const int nsuper = (nchunk + 31) / 32;
+        auto nearest = [&](const float* bxs, int pad, int first, int last) -> int {
             const float cx = 0.5f * (glo[0] + ghi[0]), cy = 0.5f * (glo[1] + ghi[1]), cz = 0.5f * (glo[2] + ghi[2]);
             unsigned long long bk = ~0ull;
-            for (int c = lane; c < nchunk; c += 32) {
-                const float dx = 0.5f * (box[c] + box[3 * D.Ct_pad + c]) - cx;
-                const float dy = 0.5f * (box[D.Ct_pad + c] + box[4 * D.Ct_pad + c]) - cy;
-                const float dz = 0.5f * (box[2 * D.Ct_pad + c] + box[5 * D.Ct_pad + c]) - cz;
+            for (int c = first + lane; c < last; c += 32) {
+                const float dx = 0.5f * (bxs[c] + bxs[3 * pad + c]) - cx;
+                const float dy = 0.5f * (bxs[pad + c] + bxs[4 * pad + c]) - cy;
+                const float dz = 0.5f * (bxs[2 * pad + c] + bxs[5 * pad + c]) - cz;
                 const float k2 = dx * dx + dy * dy + dz * dz;        // >= 0 or NaN
                 const unsigned long long key = ((unsigned long long)__float_as_uint(k2) << 32) | (unsigned)c;
                 if (k2 >= 0.f && key < bk) bk = key;
@@ -317,41 +421,81 @@ __global__ void __launch_bounds__(128) knn_cull_kernel(const CullParams prm) {
                 const unsigned long long other = __shfl_xor_sync(0xffffffffu, bk, o);
                 bk = other < bk ? other : bk;
             }
-            if (bk != ~0ull) seed = (int)(bk & 0xffffffffu);
-        }
-        evaluate(seed);
+            return bk != ~0ull ? (int)(bk & 0xffffffffu) : first;
+        };
+        const int seed_super = nearest(sbox, D.St_pad, 0, nsuper);
+        const int seed = nearest(box, D.Ct_pad, seed_super * 32, min(nchunk, seed_super * 32 + 32));
+        evaluate(seed, load_part(seed));
 
-        // cull pass: one chunk box per lane.  Level 1: group box vs chunk box against U (one test per chunk, lane
-        // parallel).  Level 2, for the survivors in ascending chunk order: every lane tests its own kQ queries against
-        // the chunk box (point-to-box bound vs that query's best); the chunk is evaluated if any query may gain or tie.
-        for (int c0 = 0; c0 < nchunk; c0 += 32) {
-            const int c = c0 + lane;
-            float lb = CUDART_INF_F;
-            float bx[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-            if (c < nchunk && c != seed) {
+        // cull passes over a two-level box hierarchy (super-chunk = 32 chunks = 1024 targets; chunk = 32 targets), one box
+        // per lane at either level.  Level 1 tests the group's box: pass 0 takes the chunks whose box overlaps it (LB == 0:
+        // where the neighbours almost always are), pass 1 the remaining chunks with LB <= U, U = max over the group's
+        // queries of their best so far; a super-chunk is opened when its own box passes the same test.  Level 2, for the
+        // level-1 survivors in ascending chunk order: every lane tests its own kQ queries against the chunk box
+        // (point-to-box bound vs that query's best); the chunk is evaluated if any query may gain or tie.
+        // Survivors' box rows and target rows are prefetched into L1 while the tests run.
+        auto group_U = [&]() -> float {
+            float mb = 0.f;
 #pragma unroll
-                for (int k = 0; k < 6; ++k) bx[k] = box[k * D.Ct_pad + c];
-                lb = lb_dist(gap(glo[0], ghi[0], bx[0], bx[3]), gap(glo[1], ghi[1], bx[1], bx[4]),
-                             gap(glo[2], ghi[2], bx[2], bx[5]));
-                if (!(lb >= 0.f)) lb = 0.f;          // NaN box -> always a candidate
-            }
-            uint32_t m = __ballot_sync(0xffffffffu, lb <= U);
-            while (m) {
-                const int b = __ffs(m) - 1;
-                m &= m - 1;
-                const float lbc = __shfl_sync(0xffffffffu, lb, b);
-                if (lbc > U) continue;
-                float cb[6];
-#pragma unroll
-                for (int k = 0; k < 6; ++k) cb[k] = __shfl_sync(0xffffffffu, bx[k], b);
-                bool want = false;
-#pragma unroll
-                for (int q = 0; q < kQ; ++q) {
-                    const float lq = lb_dist(gap(fx[q], fx[q], cb[0], cb[3]), gap(fy[q], fy[q], cb[1], cb[4]),
-                                             gap(fz[q], fz[q], cb[2], cb[5]));
-                    want |= !(lq > best[q]);           // NaN -> evaluate
+            for (int q = 0; q < kQ; ++q) mb = fmaxf(mb, best[q]);
+            return warp_max(mb);
+        };
+#pragma unroll 1
+        for (int pass = 0; pass < 2; ++pass) {
+#pragma unroll 1
+            for (int s0 = 0; s0 < nsuper; s0 += 32) {
+                const int sidx = s0 + lane;
+                float slb = CUDART_INF_F;
+                if (sidx < nsuper) {
+                    slb = lb_dist(gap(glo[0], ghi[0], sbox[sidx], sbox[3 * D.St_pad + sidx]),
+                                  gap(glo[1], ghi[1], sbox[D.St_pad + sidx], sbox[4 * D.St_pad + sidx]),
+                                  gap(glo[2], ghi[2], sbox[2 * D.St_pad + sidx], sbox[5 * D.St_pad + sidx]));
+                    if (!(slb >= 0.f)) slb = 0.f;
                 }
-                if (__any_sync(0xffffffffu, want)) evaluate(c0 + b);
+                bool scand = slb == 0.f;
+                if (pass) { const float U = group_U(); scand = slb <= U; }
+                uint32_t ms = __ballot_sync(0xffffffffu, scand);
+                if (lane < 6) {
+                    for (uint32_t t = ms; t; t &= t - 1) prefetch_l1(box + lane * D.Ct_pad + (s0 + __ffs(t) - 1) * 32);
+                }
+                while (ms) {
+                    const int sb = __ffs(ms) - 1;
+                    ms &= ms - 1;
+                    const int c0 = (s0 + sb) * 32;
+                    const int c = c0 + lane;
+                    float lb = CUDART_INF_F;
+                    float bx[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+                    if (c < nchunk && c != seed) {
+#pragma unroll
+                        for (int k = 0; k < 6; ++k) bx[k] = box[k * D.Ct_pad + c];
+                        lb = lb_dist(gap(glo[0], ghi[0], bx[0], bx[3]), gap(glo[1], ghi[1], bx[1], bx[4]),
+                                     gap(glo[2], ghi[2], bx[2], bx[5]));
+                        if (!(lb >= 0.f)) lb = 0.f;          // NaN box -> always a candidate
+                    }
+                    bool cand = lb == 0.f;
+                    if (pass) { const float U = group_U(); cand = lb > 0.f && lb <= U; }   // U first: all lanes shuffle
+                    uint32_t m = __ballot_sync(0xffffffffu, cand);
+                    float4 cur = make_float4(0.f, 0.f, 0.f, 0.f);
+                    if (m) cur = load_part(c0 + __ffs(m) - 1);
+                    while (m) {
+                        const int b = __ffs(m) - 1;
+                        m &= m - 1;
+                        float4 nxt = make_float4(0.f, 0.f, 0.f, 0.f);
+                        if (m) nxt = load_part(c0 + __ffs(m) - 1);
+                        float cb[6];
+#pragma unroll
+                        for (int k = 0; k < 6; ++k) cb[k] = __shfl_sync(0xffffffffu, bx[k], b);
+                        bool want = false;
+#pragma unroll
+                        for (int q = 0; q < kQ; ++q) {
+                            const float lq = lb_dist(gap(fx[q], fx[q], cb[0], cb[3]), gap(fy[q], fy[q], cb[1], cb[4]),
+                                                     gap(fz[q], fz[q], cb[2], cb[5]));
+                            want |= !(lq > best[q]);           // NaN -> evaluate
+                        }
+                        if (__any_sync(0xffffffffu, want)) evaluate(c0 + b, cur);
+                        cur = nxt;
+                    }
+                }
             }
         }
 

@@ -62,7 +62,7 @@ int findb200_chamfer_backward(const float* x, const float* y, const int64_t* x_l
 
 /* Measurement hooks for the kNN kernel.  mode 0 (default): exact search with bounding-box culling over spatially
  * binned clouds; mode 1: the plain brute-force tile kernel (every pair evaluated), kept for A/B timing.  kq = queries
- * per lane of the culled kernel (0 = heuristic, 2 or 4).  Results are bit-identical in every mode.
+ * per lane of the culled kernel (0 = heuristic, 1, 2 or 4).  Results are bit-identical in every mode.
  * findb200_knn_stats copies {pair evaluations executed, queries that took the cross-chunk-tie path, most chunk
  * evaluations done for one query group, query groups} of the LAST culled call that used `workspace` into four host
  * uint64 (synchronises `stream`). */

@@ -7,11 +7,11 @@ import torch
 pytestmark = pytest.mark.gpu
 
 
-@pytest.fixture(params=["cull_kq2", "cull_kq4", "brute"], autouse=True)
+@pytest.fixture(params=["cull_kq1", "cull_kq2", "cull_kq4", "brute"], autouse=True)
 def knn_mode(request):
     """Every test runs on the culled kernel (2 and 4 queries per lane) and on the brute-force tile kernel."""
     from find_b200 import _lib
-    mode, kq = {"cull_kq2": (0, 2), "cull_kq4": (0, 4), "brute": (1, 0)}[request.param]
+    mode, kq = {"cull_kq1": (0, 1), "cull_kq2": (0, 2), "cull_kq4": (0, 4), "brute": (1, 0)}[request.param]
     assert _lib.load().findb200_set_knn_mode(mode, kq) == 0
     yield request.param
     _lib.load().findb200_set_knn_mode(0, 0)

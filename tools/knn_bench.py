@@ -11,7 +11,7 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from find_b200 import _lib, synthetic as syn  # noqa: E402
 
 
-def run(B, V, P2, mode, kq, iters=20):
+def run(B, V, P2, mode, kq, iters=int(os.environ.get('KB_ITERS', '20'))):
     lib = _lib.load()
     dev = torch.device("cuda:0")
     lib.findb200_set_knn_mode(mode, kq)
@@ -61,5 +61,6 @@ if __name__ == "__main__":
         a = [int(v) for v in sys.argv[1:]]
         shapes = [tuple(a[i:i + 3]) for i in range(0, len(a), 3)]
     for s in shapes:
-        for mode, kq in ((1, 0), (0, 2), (0, 4)):
+        modes = [tuple(int(v) for v in m.split(':')) for m in os.environ.get('KB_MODES', '1:0,0:1,0:2,0:4').split(',')]
+        for mode, kq in modes:
             print(json.dumps(run(*s, mode, kq)), flush=True)
