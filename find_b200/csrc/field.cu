@@ -381,6 +381,8 @@ static Workspace carve(int B, int V, int shared, int for_backward) {
         w.enc = take((size_t)w.trunk_tiles * kEncTileBytes);
         w.hact = take((size_t)2 * 3 * head_tiles * kTileBytes);
         w.hdz = take((size_t)2 * 3 * head_tiles * kTileBytes);
+        w.hmask = take((size_t)2 * 3 * head_tiles * kMaskTileBytes);
+        w.tmask = take((size_t)5 * w.trunk_tiles * kMaskTileBytes);
         w.doimg = take((size_t)2 * head_tiles * kImgBytes);
         w.tdz = take((size_t)5 * w.trunk_tiles * kTileBytes);
         w.dovals = take((size_t)2 * B * V * 16);
@@ -419,6 +421,7 @@ static void fill_chain_common(ChainParams& C, const findb200_field_params* p, co
     C.biasfoot = (const float*)(ws + w.biasfoot);
     C.enc = ws + w.enc; C.tact = ws + w.tact; C.hact = ws + w.hact; C.hdz = ws + w.hdz; C.doimg = ws + w.doimg;
     C.tdz = ws + w.tdz;
+    C.hmask = (uint32_t*)(ws + w.hmask); C.tmask = (uint32_t*)(ws + w.tmask);
     C.avg_col = p->avg_col;
     C.dovals = (const float*)(ws + w.dovals);
     C.maxabs = (const uint32_t*)(ws + w.scal);

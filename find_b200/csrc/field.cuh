@@ -25,6 +25,7 @@ constexpr int kTile = 128;              // rows per tile (= UMMA M)
 constexpr int kImgBytes = 16384;        // [128 x 64] fp16
 constexpr int kTileBytes = 65536;       // 4 images
 constexpr int kEncTileBytes = kEncChunks * kImgBytes;
+constexpr int kMaskTileBytes = 4096;     // ReLU sign bits of one tile: [128 rows][8 words], see epi_relu / epi_mask
 constexpr int kWChunkBytes = 32768;     // [256 x 64] fp16
 constexpr int kWSmallChunkBytes = 2048; // [16 x 64] fp16 (the 256 -> 3 output layers, N padded to 16)
 constexpr int kRing = 3;                // weight ring stages in the chain kernels
@@ -67,6 +68,8 @@ struct Workspace {
     size_t tact;         // trunk: a0..a4 tiles                 [5][trunk_tiles]
     size_t hact;         // heads: a1..a3 tiles                 [2][3][B*tpf2]
     size_t hdz;          // heads: dZ3,dZ2,dZ1 tiles            [2][3][B*tpf2]
+    size_t hmask;        // heads: ReLU bit masks of a1..a3     [2][3][B*tpf2] x 4 KB
+    size_t tmask;        // trunk: ReLU bit masks of a0..a4     [5][trunk_tiles] x 4 KB
     size_t doimg;        // heads: d(pre-tanh) images           [2][B*tpf2] x 16 KB
     size_t tdz;          // trunk: dZ4..dZ0 tiles               [5][trunk_tiles]
     size_t dovals;       // float [2][B][V][4]: unscaled d(pre-tanh) values

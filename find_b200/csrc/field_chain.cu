@@ -47,7 +47,6 @@ FB_DEVINL void produce_gemm(const ChainParams& P, const GemmW& g, uint8_t* ring,
 }
 
 // ---- MMA issuer: D[tile] (+)= A[tile](smem images) * W(ring) for chunks [c0, c1) ------------------------------
-template <int NT>
 FB_DEVINL void mma_gemm(const GemmW& g, uint32_t act_s, uint32_t ring_s, uint32_t tmem, uint64_t* bar_full,
                         uint64_t* bar_empty, uint32_t& ccount, int c0, int c1, bool acc_init) {
     const uint32_t idesc = umma_idesc_f16(128, g.N, false, false);
@@ -56,13 +55,10 @@ FB_DEVINL void mma_gemm(const GemmW& g, uint32_t act_s, uint32_t ring_s, uint32_
         mbar_wait(&bar_full[s], use & 1);
         tc_fence_after();
         const int nk = (c == g.n_chunks - 1) ? g.k16_last : 4;
-#pragma unroll
-        for (int t = 0; t < NT; ++t) {
-            for (int k = 0; k < nk; ++k) {
-                const uint64_t ad = umma_desc(act_s + t * kTileBytes + (c - c0) * kImgBytes + k * 32, 16, 1024);
-                const uint64_t bd = umma_desc(ring_s + s * kWChunkBytes + k * 32, 16, 1024);
-                umma_f16(tmem + t * 256, ad, bd, idesc, (acc_init || c > c0 || k > 0) ? 1u : 0u);
-            }
+        for (int k = 0; k < nk; ++k) {
+            const uint64_t ad = umma_desc(act_s + (c - c0) * kImgBytes + k * 32, 16, 1024);
+            const uint64_t bd = umma_desc(ring_s + s * kWChunkBytes + k * 32, 16, 1024);
+            umma_f16(tmem, ad, bd, idesc, (acc_init || c > c0 || k > 0) ? 1u : 0u);
         }
         umma_commit(&bar_empty[s]);
         ++ccount;
@@ -74,52 +70,85 @@ FB_DEVINL uint32_t img_row_off(int chunk32, int row) {   // byte offset of 16-B 
     return (uint32_t)(chunk32 >> 3) * kImgBytes + (uint32_t)row * 128u + (uint32_t)(((chunk32 & 7) ^ (row & 7)) << 4);
 }
 
-FB_DEVINL void epi_relu(uint32_t taddr, uint8_t* act_tile, int row, const float* __restrict__ bias) {
-#pragma unroll 1
-    for (int cc = 0; cc < 8; ++cc) {
-        uint32_t v[32];
-        tmem_ld32(taddr + cc * 32, v);
-        tmem_ld_wait();
-        const float4* b4 = reinterpret_cast<const float4*>(bias + cc * 32);
+// 32 accumulator columns of one row: + bias (shared memory), ReLU, fp16, into the tile image; returns the ReLU sign
+// bits of the 32 columns: column 2j -> bit 15-j, column 2j+1 -> bit 31-j (j = 0..15), i.e. of packed word j.
+FB_DEVINL uint32_t relu_chunk(const uint32_t (&v)[32], int cc, uint8_t* act_tile, int row, const float* bias_s) {
+    const float4* b4 = reinterpret_cast<const float4*>(bias_s + cc * 32);
+    uint32_t bits = 0;
 #pragma unroll
-        for (int g = 0; g < 4; ++g) {
-            const float4 b0 = __ldg(b4 + g * 2), b1 = __ldg(b4 + g * 2 + 1);
-            uint4 pk;
-            pk.x = pack_h2(fmaxf(__uint_as_float(v[g * 8 + 0]) + b0.x, 0.f), fmaxf(__uint_as_float(v[g * 8 + 1]) + b0.y, 0.f));
-            pk.y = pack_h2(fmaxf(__uint_as_float(v[g * 8 + 2]) + b0.z, 0.f), fmaxf(__uint_as_float(v[g * 8 + 3]) + b0.w, 0.f));
-            pk.z = pack_h2(fmaxf(__uint_as_float(v[g * 8 + 4]) + b1.x, 0.f), fmaxf(__uint_as_float(v[g * 8 + 5]) + b1.y, 0.f));
-            pk.w = pack_h2(fmaxf(__uint_as_float(v[g * 8 + 6]) + b1.z, 0.f), fmaxf(__uint_as_float(v[g * 8 + 7]) + b1.w, 0.f));
-            *reinterpret_cast<uint4*>(act_tile + img_row_off(cc * 4 + g, row)) = pk;
-        }
+    for (int g = 0; g < 4; ++g) {
+        const float4 b0 = b4[g * 2], b1 = b4[g * 2 + 1];
+        uint4 pk;
+        pk.x = pack_h2(fmaxf(__uint_as_float(v[g * 8 + 0]) + b0.x, 0.f), fmaxf(__uint_as_float(v[g * 8 + 1]) + b0.y, 0.f));
+        pk.y = pack_h2(fmaxf(__uint_as_float(v[g * 8 + 2]) + b0.z, 0.f), fmaxf(__uint_as_float(v[g * 8 + 3]) + b0.w, 0.f));
+        pk.z = pack_h2(fmaxf(__uint_as_float(v[g * 8 + 4]) + b1.x, 0.f), fmaxf(__uint_as_float(v[g * 8 + 5]) + b1.y, 0.f));
+        pk.w = pack_h2(fmaxf(__uint_as_float(v[g * 8 + 6]) + b1.z, 0.f), fmaxf(__uint_as_float(v[g * 8 + 7]) + b1.w, 0.f));
+        *reinterpret_cast<uint4*>(act_tile + img_row_off(cc * 4 + g, row)) = pk;
+        // a packed half >= +0 is non-zero iff adding 0x7fff carries into its top bit (no carry crosses the halves)
+        bits |= ((pk.x + 0x7fff7fffu) & 0x80008000u) >> (g * 4 + 0);
+        bits |= ((pk.y + 0x7fff7fffu) & 0x80008000u) >> (g * 4 + 1);
+        bits |= ((pk.z + 0x7fff7fffu) & 0x80008000u) >> (g * 4 + 2);
+        bits |= ((pk.w + 0x7fff7fffu) & 0x80008000u) >> (g * 4 + 3);
+    }
+    return bits;
+}
+
+// a = relu(acc + bias) for one row of the tile; TMEM loads run one 32-column chunk ahead of the arithmetic.
+// mask_row: global [8] words for this row's sign bits (saved for the backward pass), or null.
+FB_DEVINL void epi_relu(uint32_t taddr, uint8_t* act_tile, int row, const float* bias_s, uint32_t* mask_row) {
+    uint32_t va[32], vb[32], m[8];
+    tmem_ld32(taddr, va);
+#pragma unroll
+    for (int cc = 0; cc < 8; cc += 2) {
+        tmem_ld_wait();
+        tmem_ld32(taddr + (cc + 1) * 32, vb);
+        m[cc] = relu_chunk(va, cc, act_tile, row, bias_s);
+        tmem_ld_wait();
+        if (cc + 2 < 8) tmem_ld32(taddr + (cc + 2) * 32, va);
+        m[cc + 1] = relu_chunk(vb, cc + 1, act_tile, row, bias_s);
+    }
+    if (mask_row) {
+        reinterpret_cast<uint4*>(mask_row)[0] = make_uint4(m[0], m[1], m[2], m[3]);
+        reinterpret_cast<uint4*>(mask_row)[1] = make_uint4(m[4], m[5], m[6], m[7]);
     }
 }
 
-FB_DEVINL uint32_t mask_pack(uint32_t a, float lo, float hi) {   // a = two saved fp16 activations (>= 0)
-    const float l = (a & 0x00007fffu) ? lo : 0.f;
-    const float h = (a & 0x7fff0000u) ? hi : 0.f;
+FB_DEVINL uint32_t mask_pack(uint32_t bits, int j, float lo, float hi) {   // sign bits of packed word j, see relu_chunk
+    const float l = (bits & (0x00008000u >> j)) ? lo : 0.f;
+    const float h = (bits & (0x80000000u >> j)) ? hi : 0.f;
     return pack_h2(l, h);
 }
 
-// dZ = dA * [a > 0]; a is the saved forward activation tile (global, same image layout)
-FB_DEVINL void epi_mask(uint32_t taddr, uint8_t* act_tile, int row, const uint8_t* __restrict__ a_tile) {
-#pragma unroll 1
-    for (int cc = 0; cc < 8; ++cc) {
-        uint4 a[4];
+FB_DEVINL void mask_chunk(const uint32_t (&v)[32], int cc, uint8_t* act_tile, int row, uint32_t bits) {
 #pragma unroll
-        for (int g = 0; g < 4; ++g) a[g] = __ldg(reinterpret_cast<const uint4*>(a_tile + img_row_off(cc * 4 + g, row)));
-        uint32_t v[32];
-        tmem_ld32(taddr + cc * 32, v);
-        tmem_ld_wait();
-#pragma unroll
-        for (int g = 0; g < 4; ++g) {
-            uint4 pk;
-            pk.x = mask_pack(a[g].x, __uint_as_float(v[g * 8 + 0]), __uint_as_float(v[g * 8 + 1]));
-            pk.y = mask_pack(a[g].y, __uint_as_float(v[g * 8 + 2]), __uint_as_float(v[g * 8 + 3]));
-            pk.z = mask_pack(a[g].z, __uint_as_float(v[g * 8 + 4]), __uint_as_float(v[g * 8 + 5]));
-            pk.w = mask_pack(a[g].w, __uint_as_float(v[g * 8 + 6]), __uint_as_float(v[g * 8 + 7]));
-            *reinterpret_cast<uint4*>(act_tile + img_row_off(cc * 4 + g, row)) = pk;
-        }
+    for (int g = 0; g < 4; ++g) {
+        uint4 pk;
+        pk.x = mask_pack(bits, g * 4 + 0, __uint_as_float(v[g * 8 + 0]), __uint_as_float(v[g * 8 + 1]));
+        pk.y = mask_pack(bits, g * 4 + 1, __uint_as_float(v[g * 8 + 2]), __uint_as_float(v[g * 8 + 3]));
+        pk.z = mask_pack(bits, g * 4 + 2, __uint_as_float(v[g * 8 + 4]), __uint_as_float(v[g * 8 + 5]));
+        pk.w = mask_pack(bits, g * 4 + 3, __uint_as_float(v[g * 8 + 6]), __uint_as_float(v[g * 8 + 7]));
+        *reinterpret_cast<uint4*>(act_tile + img_row_off(cc * 4 + g, row)) = pk;
     }
+}
+
+// dZ = dA * [a > 0]; m = the row's 8 sign words saved by the forward epilogue (loaded by the caller before it waits)
+FB_DEVINL void epi_mask(uint32_t taddr, uint8_t* act_tile, int row, const uint32_t (&m)[8]) {
+    uint32_t va[32], vb[32];
+    tmem_ld32(taddr, va);
+#pragma unroll
+    for (int cc = 0; cc < 8; cc += 2) {
+        tmem_ld_wait();
+        tmem_ld32(taddr + (cc + 1) * 32, vb);
+        mask_chunk(va, cc, act_tile, row, m[cc]);
+        tmem_ld_wait();
+        if (cc + 2 < 8) tmem_ld32(taddr + (cc + 2) * 32, va);
+        mask_chunk(vb, cc + 1, act_tile, row, m[cc + 1]);
+    }
+}
+
+FB_DEVINL void load_mask_row(const uint32_t* mask_row, uint32_t (&m)[8]) {
+    const uint4 a = __ldg(reinterpret_cast<const uint4*>(mask_row)), b = __ldg(reinterpret_cast<const uint4*>(mask_row) + 1);
+    m[0] = a.x; m[1] = a.y; m[2] = a.z; m[3] = a.w; m[4] = b.x; m[5] = b.y; m[6] = b.z; m[7] = b.w;
 }
 
 // Fourier features of one row for encoded-input chunk c (64 internal columns), written to image slot `slot`.
@@ -184,21 +213,32 @@ FB_DEVINL void euler_xyz(const float* e, float (&R)[3][3]) {
 
 template <int MODE, int NT>
 __global__ void __launch_bounds__(64 + 128 * NT, 1) chain_kernel(const __grid_constant__ ChainParams P) {
-    extern __shared__ uint8_t smem_raw[];
-    uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+    // dynamic shared memory only (no static __shared__), so the window starts 1024-aligned as SWIZZLE_128B needs:
+    // [NT activation tiles 64 KB][weight ring 3 x 32 KB][NT x 256 fp32 bias of the layer in flight][mbarriers]
+    extern __shared__ __align__(1024) uint8_t smem[];
     uint8_t* act = smem;
     uint8_t* ring = smem + NT * kTileBytes;
-    __shared__ __align__(8) uint64_t bar_full[kRing], bar_empty[kRing];
-    __shared__ __align__(8) uint64_t bar_act_ready, bar_acc_ready, bar_in_full, bar_act_free;
-    __shared__ uint32_t tmem_base_s;
+    float* bias_sm = reinterpret_cast<float*>(ring + kRing * kWChunkBytes);
+    uint64_t* bars = reinterpret_cast<uint64_t*>(bias_sm + NT * kW);
+    uint64_t* bar_full = bars;                    // [kRing]
+    uint64_t* bar_empty = bars + kRing;           // [kRing]
+    // per tile slot: the NT tiles of a CTA run half a layer out of phase (tile t's epilogue overlaps tile t^1's MMAs)
+    uint64_t* bar_act_ready = bars + 2 * kRing;   // [NT]
+    uint64_t* bar_acc_ready = bar_act_ready + NT; // [NT]
+    uint64_t* bar_in_full = bar_acc_ready + NT;   // [NT]
+    uint64_t* bar_act_free = bar_in_full + NT;    // [NT]
+    uint32_t& tmem_base_s = *reinterpret_cast<uint32_t*>(bar_act_free + NT);
+    if ((smem_u32(smem) & 1023u) != 0u) __trap();
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     if (tid == 0) {
         for (int s = 0; s < kRing; ++s) { mbar_init(&bar_full[s], 1); mbar_init(&bar_empty[s], 1); }
-        mbar_init(&bar_act_ready, 128 * NT);
-        mbar_init(&bar_acc_ready, 1);
-        mbar_init(&bar_in_full, 1);
-        mbar_init(&bar_act_free, 1 + 128 * NT);
+        for (int t = 0; t < NT; ++t) {
+            mbar_init(&bar_act_ready[t], 128);
+            mbar_init(&bar_acc_ready[t], 1);
+            mbar_init(&bar_in_full[t], 1);
+            mbar_init(&bar_act_free[t], 1 + 128);
+        }
         fence_barrier_init();
     }
     if (warp == 0) tmem_alloc(&tmem_base_s, NT * 256);
@@ -228,82 +268,88 @@ __global__ void __launch_bounds__(64 + 128 * NT, 1) chain_kernel(const __grid_co
             for (int it = blockIdx.x; it < P.n_items; it += gridDim.x, ++icount) {
                 int head, b, t0;
                 decode(it, head, b, t0);
+                // weights are streamed once per (layer, tile), in the order the MMA warp consumes them
                 if (MODE == TRUNK_FWD) {
-                    for (int l = 0; l < 5; ++l) produce_gemm(P, P.lay.fwd[P_T0 + l], ring, bar_full, bar_empty, pcount, 0, P.lay.fwd[P_T0 + l].n_chunks);
+                    for (int l = 0; l < 5; ++l)
+                        for (int t = 0; t < NT; ++t)
+                            produce_gemm(P, P.lay.fwd[P_T0 + l], ring, bar_full, bar_empty, pcount, 0, P.lay.fwd[P_T0 + l].n_chunks);
                 } else if (MODE == HEAD_FWD) {
-                    if (icount > 0) mbar_wait(&bar_act_free, (icount - 1) & 1);
-                    mbar_expect_tx(&bar_in_full, NT * kTileBytes);
                     for (int t = 0; t < NT; ++t) {
+                        if (icount > 0) mbar_wait(&bar_act_free[t], (icount - 1) & 1);
+                        mbar_expect_tx(&bar_in_full[t], kTileBytes);
                         const size_t tt = (size_t)(P.shared ? 0 : b) * P.tpf2 + t0 + t;
-                        bulk_g2s(act + t * kTileBytes, P.tact + ((size_t)4 * P.trunk_tiles + tt) * kTileBytes, kTileBytes, &bar_in_full);
+                        bulk_g2s(act + t * kTileBytes, P.tact + ((size_t)4 * P.trunk_tiles + tt) * kTileBytes, kTileBytes, &bar_in_full[t]);
                     }
                     const int base = head ? P_C1 : P_D1;
-                    for (int l = 0; l < 4; ++l) produce_gemm(P, P.lay.fwd[base + l], ring, bar_full, bar_empty, pcount, 0, P.lay.fwd[base + l].n_chunks);
+                    for (int l = 0; l < 4; ++l)
+                        for (int t = 0; t < NT; ++t)
+                            produce_gemm(P, P.lay.fwd[base + l], ring, bar_full, bar_empty, pcount, 0, P.lay.fwd[base + l].n_chunks);
                 } else if (MODE == HEAD_BWD) {
                     const int base = head ? P_C1 : P_D1;
-                    for (int l = 3; l >= 1; --l) produce_gemm(P, P.lay.bwd[base + l], ring, bar_full, bar_empty, pcount, 0, P.lay.bwd[base + l].n_chunks);
+                    for (int l = 3; l >= 1; --l)
+                        for (int t = 0; t < NT; ++t)
+                            produce_gemm(P, P.lay.bwd[base + l], ring, bar_full, bar_empty, pcount, 0, P.lay.bwd[base + l].n_chunks);
                 } else {
-                    if (P.heads_mask & 1) produce_gemm(P, P.lay.bwd[P_D1], ring, bar_full, bar_empty, pcount, 0, 4);
-                    if (P.heads_mask & 2) produce_gemm(P, P.lay.bwd[P_C1], ring, bar_full, bar_empty, pcount, 0, 4);
-                    for (int l = 4; l >= 1; --l) produce_gemm(P, P.lay.bwd[P_T0 + l], ring, bar_full, bar_empty, pcount, 0, 4);
+                    if (P.heads_mask & 1) for (int t = 0; t < NT; ++t) produce_gemm(P, P.lay.bwd[P_D1], ring, bar_full, bar_empty, pcount, 0, 4);
+                    if (P.heads_mask & 2) for (int t = 0; t < NT; ++t) produce_gemm(P, P.lay.bwd[P_C1], ring, bar_full, bar_empty, pcount, 0, 4);
+                    for (int l = 4; l >= 1; --l)
+                        for (int t = 0; t < NT; ++t) produce_gemm(P, P.lay.bwd[P_T0 + l], ring, bar_full, bar_empty, pcount, 0, 4);
                 }
             }
         }
     } else if (warp == 1) {
         // ===================================== MMA issuer =========================================
         if (lane == 0) {
-            uint32_t ccount = 0, n_act = 0, icount = 0;
+            uint32_t ccount = 0, icount = 0;
+            uint32_t n_act[NT];
+            for (int t = 0; t < NT; ++t) n_act[t] = 0;
             const uint32_t act_s = smem_u32(act), ring_s = smem_u32(ring);
-            auto wait_act = [&]() { mbar_wait(&bar_act_ready, n_act & 1); ++n_act; tc_fence_after(); };
+            auto wait_act = [&](int t) { mbar_wait(&bar_act_ready[t], n_act[t] & 1); ++n_act[t]; tc_fence_after(); };
+            // one layer of one tile; then straight on to the other tile while this one's epilogue runs
+            auto gemm = [&](int t, const GemmW& g, int c0, int c1, bool acc_init) {
+                mma_gemm(g, act_s + t * kTileBytes, ring_s, tmem + t * 256, bar_full, bar_empty, ccount, c0, c1, acc_init);
+                umma_commit(&bar_acc_ready[t]);
+            };
             for (int it = blockIdx.x; it < P.n_items; it += gridDim.x, ++icount) {
                 int head, b, t0;
                 decode(it, head, b, t0);
                 if (MODE == TRUNK_FWD) {
-                    for (int p = 0; p < 3; ++p) {
-                        wait_act();
-                        mma_gemm<NT>(P.lay.fwd[P_T0], act_s, ring_s, tmem, bar_full, bar_empty, ccount, 4 * p, min(4 * p + 4, kEncChunks), p > 0);
-                        umma_commit(&bar_acc_ready);
-                    }
-                    for (int l = 1; l < 5; ++l) {
-                        wait_act();
-                        mma_gemm<NT>(P.lay.fwd[P_T0 + l], act_s, ring_s, tmem, bar_full, bar_empty, ccount, 0, 4, false);
-                        umma_commit(&bar_acc_ready);
-                    }
+                    for (int p = 0; p < 3; ++p)
+                        for (int t = 0; t < NT; ++t) {
+                            wait_act(t);
+                            gemm(t, P.lay.fwd[P_T0], 4 * p, min(4 * p + 4, kEncChunks), p > 0);
+                        }
+                    for (int l = 1; l < 5; ++l)
+                        for (int t = 0; t < NT; ++t) {
+                            wait_act(t);
+                            gemm(t, P.lay.fwd[P_T0 + l], 0, 4, false);
+                        }
                 } else if (MODE == HEAD_FWD) {
                     const int base = head ? P_C1 : P_D1;
-                    mbar_wait(&bar_in_full, icount & 1);
-                    tc_fence_after();
-                    for (int l = 0; l < 4; ++l) {
-                        if (l > 0) wait_act();
-                        mma_gemm<NT>(P.lay.fwd[base + l], act_s, ring_s, tmem, bar_full, bar_empty, ccount, 0, 4, false);
-                        umma_commit(&bar_acc_ready);
-                    }
-                    umma_commit(&bar_act_free);
+                    for (int l = 0; l < 4; ++l)
+                        for (int t = 0; t < NT; ++t) {
+                            if (l == 0) { mbar_wait(&bar_in_full[t], icount & 1); tc_fence_after(); }
+                            else wait_act(t);
+                            gemm(t, P.lay.fwd[base + l], 0, 4, false);
+                            if (l == 3) umma_commit(&bar_act_free[t]);
+                        }
                 } else if (MODE == HEAD_BWD) {
                     const int base = head ? P_C1 : P_D1;
-                    for (int l = 3; l >= 1; --l) {
-                        wait_act();
-                        mma_gemm<NT>(P.lay.bwd[base + l], act_s, ring_s, tmem, bar_full, bar_empty, ccount, 0, P.lay.bwd[base + l].n_chunks, false);
-                        umma_commit(&bar_acc_ready);
-                    }
+                    for (int l = 3; l >= 1; --l)
+                        for (int t = 0; t < NT; ++t) {
+                            wait_act(t);
+                            gemm(t, P.lay.bwd[base + l], 0, P.lay.bwd[base + l].n_chunks, false);
+                        }
                 } else {
                     bool first = true;
                     if (P.heads_mask & 1) {
-                        wait_act();
-                        mma_gemm<NT>(P.lay.bwd[P_D1], act_s, ring_s, tmem, bar_full, bar_empty, ccount, 0, 4, false);
-                        umma_commit(&bar_acc_ready);
+                        for (int t = 0; t < NT; ++t) { wait_act(t); gemm(t, P.lay.bwd[P_D1], 0, 4, false); }
                         first = false;
                     }
-                    if (P.heads_mask & 2) {
-                        wait_act();
-                        mma_gemm<NT>(P.lay.bwd[P_C1], act_s, ring_s, tmem, bar_full, bar_empty, ccount, 0, 4, !first);
-                        umma_commit(&bar_acc_ready);
-                    }
-                    for (int l = 4; l >= 1; --l) {
-                        wait_act();
-                        mma_gemm<NT>(P.lay.bwd[P_T0 + l], act_s, ring_s, tmem, bar_full, bar_empty, ccount, 0, 4, false);
-                        umma_commit(&bar_acc_ready);
-                    }
+                    if (P.heads_mask & 2)
+                        for (int t = 0; t < NT; ++t) { wait_act(t); gemm(t, P.lay.bwd[P_C1], 0, 4, !first); }
+                    for (int l = 4; l >= 1; --l)
+                        for (int t = 0; t < NT; ++t) { wait_act(t); gemm(t, P.lay.bwd[P_T0 + l], 0, 4, false); }
                 }
             }
         }
@@ -318,19 +364,22 @@ __global__ void __launch_bounds__(64 + 128 * NT, 1) chain_kernel(const __grid_co
         uint8_t* act_tile = act + tl * kTileBytes;
         const uint32_t taddr = tmem + ((uint32_t)(q * 32) << 16) + tl * 256;
         uint32_t n_acc = 0;
-        auto wait_acc = [&]() { mbar_wait(&bar_acc_ready, n_acc & 1); ++n_acc; tc_fence_after(); };
+        auto wait_acc = [&]() { mbar_wait(&bar_acc_ready[tl], n_acc & 1); ++n_acc; tc_fence_after(); };
         auto before_overwrite = [&]() {              // pending bulk store of this tile must have read smem
             if (leader) bulk_wait_read0();
             named_bar_sync(1 + tl, 128);
         };
         auto publish = [&](uint8_t* gdst) {          // tile image complete: hand to the MMA proxy, store to HBM
             fence_proxy_async();
-            if (gdst) {
-                named_bar_sync(1 + tl, 128);
-                if (leader) { bulk_s2g(gdst, act_tile, kTileBytes); bulk_commit(); }
-            }
+            named_bar_sync(1 + tl, 128);             // also: every thread is done with bias_s of this layer
+            if (gdst && leader) { bulk_s2g(gdst, act_tile, kTileBytes); bulk_commit(); }
         };
-        auto signal_act = [&]() { tc_fence_before(); mbar_arrive(&bar_act_ready); };
+        float* bias_s = bias_sm + tl * kW;
+        // bias of the next layer: global -> registers before the accumulator wait, -> shared memory after it (the
+        // barrier in before_overwrite() publishes it to the tile's 128 threads)
+        auto bias_fetch = [&](const float* gb) -> float2 { return __ldg(reinterpret_cast<const float2*>(gb) + gt); };
+        auto bias_put = [&](float2 v) { reinterpret_cast<float2*>(bias_s)[gt] = v; };
+        auto signal_act = [&]() { tc_fence_before(); mbar_arrive(&bar_act_ready[tl]); };
 
         for (int it = blockIdx.x; it < P.n_items; it += gridDim.x) {
             int head, b, t0;
@@ -355,9 +404,12 @@ __global__ void __launch_bounds__(64 + 128 * NT, 1) chain_kernel(const __grid_co
                     signal_act();
                 }
                 for (int l = 0; l < 5; ++l) {
+                    const float2 bv = bias_fetch(P.bias[P_T0 + l]);
                     wait_acc();
+                    bias_put(bv);
                     before_overwrite();
-                    epi_relu(taddr, act_tile, row, P.bias[P_T0 + l]);
+                    epi_relu(taddr, act_tile, row, bias_s,
+                             P.save ? P.tmask + (((size_t)l * P.trunk_tiles + tt) * kTile + row) * 8 : nullptr);
                     publish((P.save || l == 4) ? P.tact + ((size_t)l * P.trunk_tiles + tt) * kTileBytes : nullptr);
                     if (l < 4) signal_act();
                 }
@@ -365,10 +417,13 @@ __global__ void __launch_bounds__(64 + 128 * NT, 1) chain_kernel(const __grid_co
                 const int base = head ? P_C1 : P_D1;
                 const size_t ht = (size_t)b * P.tpf2 + t;
                 for (int l = 0; l < 3; ++l) {
+                    const float2 bv = bias_fetch(l == 0 ? P.biasfoot + ((size_t)head * P.B + b) * kW : P.bias[base + l]);
                     wait_acc();
+                    bias_put(bv);
                     before_overwrite();
-                    epi_relu(taddr, act_tile, row, l == 0 ? P.biasfoot + ((size_t)head * P.B + b) * kW : P.bias[base + l]);
-                    publish(P.save ? P.hact + (((size_t)head * 3 + l) * P.B * P.tpf2 + ht) * kTileBytes : nullptr);
+                    const size_t slot = ((size_t)head * 3 + l) * P.B * P.tpf2 + ht;
+                    epi_relu(taddr, act_tile, row, bias_s, P.save ? P.hmask + (slot * kTile + row) * 8 : nullptr);
+                    publish(P.save ? P.hact + slot * kTileBytes : nullptr);
                     signal_act();
                 }
                 wait_acc();
@@ -377,7 +432,7 @@ __global__ void __launch_bounds__(64 + 128 * NT, 1) chain_kernel(const __grid_co
                 tmem_ld32(taddr, v);
                 tmem_ld_wait();
                 tc_fence_before();
-                mbar_arrive(&bar_act_free);          // act buffer and TMEM of this item are free for the next one
+                mbar_arrive(&bar_act_free[tl]);      // act buffer and TMEM of this item are free for the next one
                 if (valid) {
                     const float* bo = P.bias[base + 3];
                     const float t0v = tanhf(__uint_as_float(v[0]) + __ldg(bo + 0));
@@ -433,11 +488,13 @@ __global__ void __launch_bounds__(64 + 128 * NT, 1) chain_kernel(const __grid_co
                     signal_act();
                 }
                 for (int l = 2; l >= 0; --l) {       // l indexes a_{l+1} / dZ_{l+1}
+                    const size_t slot = ((size_t)head * 3 + l) * P.B * P.tpf2 + ht;
+                    uint32_t m[8];
+                    load_mask_row(P.hmask + (slot * kTile + row) * 8, m);
                     wait_acc();
                     before_overwrite();
-                    const size_t off = (((size_t)head * 3 + l) * P.B * P.tpf2 + ht) * kTileBytes;
-                    epi_mask(taddr, act_tile, row, P.hact + off);
-                    publish(P.hdz + off);
+                    epi_mask(taddr, act_tile, row, m);
+                    publish(P.hdz + slot * kTileBytes);
                     if (l > 0) signal_act();
                 }
             } else {   // TRUNK_BWD
@@ -464,11 +521,13 @@ __global__ void __launch_bounds__(64 + 128 * NT, 1) chain_kernel(const __grid_co
                     filled = true;
                 }
                 for (int l = 4; l >= 0; --l) {
+                    const size_t slot = (size_t)l * P.trunk_tiles + tt;
+                    uint32_t m[8];
+                    load_mask_row(P.tmask + (slot * kTile + row) * 8, m);
                     wait_acc();
                     before_overwrite();
-                    const size_t off = ((size_t)l * P.trunk_tiles + tt) * kTileBytes;
-                    epi_mask(taddr, act_tile, row, P.tact + off);
-                    publish(P.tdz + off);
+                    epi_mask(taddr, act_tile, row, m);
+                    publish(P.tdz + slot * kTileBytes);
                     if (l > 0) signal_act();
                 }
             }
@@ -483,7 +542,7 @@ __global__ void __launch_bounds__(64 + 128 * NT, 1) chain_kernel(const __grid_co
 // ---- launch ---------------------------------------------------------------------------------------------
 template <int MODE, int NT>
 static int launch_chain_t(const ChainParams& P, int sms, cudaStream_t st) {
-    const int smem = NT * kTileBytes + kRing * kWChunkBytes + 1024;
+    const int smem = NT * kTileBytes + kRing * kWChunkBytes + NT * kW * 4 + (2 * kRing + 4 * NT + 1) * 8;
     static bool attr_set = false;      // one process drives one GPU (one rank per GPU)
     if (!attr_set) {
         FB_CUDA(cudaFuncSetAttribute(chain_kernel<MODE, NT>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
