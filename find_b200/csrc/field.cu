@@ -361,6 +361,39 @@ __global__ void __launch_bounds__(256) finish_small_kernel(const __grid_constant
     }
 }
 
+// Shared template: the trunk sees the SUM over feet of the heads' layer-1 gradients (the template rows are the same
+// vertices for every foot).  Elementwise over tile images: out[hd][tile] = sum_f dZ1[hd][f][tile], fp32 accumulate.
+// grid (trunk_tiles * 16, heads), block 256; one uint4 (8 halves) per thread.
+__global__ void __launch_bounds__(256) sum_feet_kernel(const uint8_t* __restrict__ hdz, uint8_t* __restrict__ hsum, int B,
+                                                       int tpf2, int heads_mask) {
+    const int hd = (heads_mask == 2) ? 1 : blockIdx.y;
+    const size_t j = (size_t)blockIdx.x * 256 + threadIdx.x;            // uint4 index inside [tpf2 tiles]
+    const size_t per_foot = (size_t)tpf2 * (kTileBytes / 16);
+    const uint4* src = reinterpret_cast<const uint4*>(hdz + (size_t)hd * 3 * B * tpf2 * kTileBytes) + j;
+    float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    for (int f0 = 0; f0 < B; f0 += 8) {
+        uint4 v[8];
+#pragma unroll
+        for (int f = 0; f < 8; ++f)
+            v[f] = (f0 + f < B) ? __ldg(src + (size_t)(f0 + f) * per_foot) : make_uint4(0, 0, 0, 0);
+#pragma unroll
+        for (int f = 0; f < 8; ++f) {
+            const __half2* h = reinterpret_cast<const __half2*>(&v[f]);
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const float2 x = __half22float2(h[i]);
+                acc[2 * i] += x.x;
+                acc[2 * i + 1] += x.y;
+            }
+        }
+    }
+    uint4 o;
+    __half2* oh = reinterpret_cast<__half2*>(&o);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) oh[i] = __floats2half2_rn(acc[2 * i], acc[2 * i + 1]);
+    reinterpret_cast<uint4*>(hsum + (size_t)hd * tpf2 * kTileBytes)[j] = o;
+}
+
 // ---- workspace --------------------------------------------------------------------------------------------
 static Workspace carve(int B, int V, int shared, int for_backward) {
     Workspace w;
@@ -381,6 +414,7 @@ static Workspace carve(int B, int V, int shared, int for_backward) {
         w.enc = take((size_t)w.trunk_tiles * kEncTileBytes);
         w.hact = take((size_t)2 * 3 * head_tiles * kTileBytes);
         w.hdz = take((size_t)2 * 3 * head_tiles * kTileBytes);
+        w.hsum = take(shared ? (size_t)2 * w.trunk_tiles * kTileBytes : 0);
         w.hmask = take((size_t)2 * 3 * head_tiles * kMaskTileBytes);
         w.tmask = take((size_t)5 * w.trunk_tiles * kMaskTileBytes);
         w.doimg = take((size_t)2 * head_tiles * kImgBytes);
@@ -581,6 +615,15 @@ int findb200_field_backward(const findb200_field_params* p, const float* pos, in
     };
     if (!frozen) {
         rc = 0;
+        if (pos_shared && B > 1) {
+            FB_MARK("sum_feet", st);
+            sum_feet_kernel<<<dim3(w.tpf2 * (kTileBytes / 16) / 256, n_heads), 256, 0, st>>>(ws + w.hdz, ws + w.hsum, B, w.tpf2,
+                                                                                             heads_mask);
+            FB_CUDA(cudaGetLastError());
+            for (int hd = 0; hd < 2; ++hd) C.tsrc[hd] = ws + w.hsum + (size_t)hd * w.trunk_tiles * kTileBytes;
+        } else {
+            for (int hd = 0; hd < 2; ++hd) C.tsrc[hd] = ws + w.hdz + (size_t)hd * 3 * head_tiles * kTileBytes;
+        }
         C.n_items = w.trunk_tiles / ((w.trunk_tiles <= 2 * sms) ? 1 : 2);
         rc = launch_chain(3, (w.trunk_tiles <= 2 * sms) ? 1 : 2, C, sms, st);
         if (rc) return rc;

@@ -68,6 +68,7 @@ struct Workspace {
     size_t tact;         // trunk: a0..a4 tiles                 [5][trunk_tiles]
     size_t hact;         // heads: a1..a3 tiles                 [2][3][B*tpf2]
     size_t hdz;          // heads: dZ3,dZ2,dZ1 tiles            [2][3][B*tpf2]
+    size_t hsum;         // heads: sum over feet of dZ1         [2][trunk_tiles] (shared template only)
     size_t hmask;        // heads: ReLU bit masks of a1..a3     [2][3][B*tpf2] x 4 KB
     size_t tmask;        // trunk: ReLU bit masks of a0..a4     [5][trunk_tiles] x 4 KB
     size_t doimg;        // heads: d(pre-tanh) images           [2][B*tpf2] x 16 KB

@@ -192,16 +192,6 @@ FB_DEVINL void encode_chunk(int c, float x, float y, float z, const float* __res
     }
 }
 
-FB_DEVINL void add8(float (&acc)[8], uint4 x) {
-    const __half2* h = reinterpret_cast<const __half2*>(&x);
-#pragma unroll
-    for (int i = 0; i < 4; ++i) {
-        const float2 f = __half22float2(h[i]);
-        acc[2 * i] += f.x;
-        acc[2 * i + 1] += f.y;
-    }
-}
-
 // rotation of the registration transform: R = Rx(e0) Ry(e1) Rz(e2) (PyTorch3D euler_angles_to_matrix 'XYZ')
 FB_DEVINL void euler_xyz(const float* e, float (&R)[3][3]) {
     float sa, ca, sb, cb, sc, cc;
@@ -237,7 +227,7 @@ __global__ void __launch_bounds__(64 + 128 * NT, 1) chain_kernel(const __grid_co
             mbar_init(&bar_act_ready[t], 128);
             mbar_init(&bar_acc_ready[t], 1);
             mbar_init(&bar_in_full[t], 1);
-            mbar_init(&bar_act_free[t], 1 + 128);
+            mbar_init(&bar_act_free[t], MODE == TRUNK_BWD ? 1 : 1 + 128);
         }
         fence_barrier_init();
     }
@@ -265,6 +255,8 @@ __global__ void __launch_bounds__(64 + 128 * NT, 1) chain_kernel(const __grid_co
         // ===================================== producer ===========================================
         if (lane == 0) {
             uint32_t pcount = 0, icount = 0;
+            uint32_t n_free[NT];
+            for (int t = 0; t < NT; ++t) n_free[t] = 0;
             for (int it = blockIdx.x; it < P.n_items; it += gridDim.x, ++icount) {
                 int head, b, t0;
                 decode(it, head, b, t0);
@@ -290,8 +282,18 @@ __global__ void __launch_bounds__(64 + 128 * NT, 1) chain_kernel(const __grid_co
                         for (int t = 0; t < NT; ++t)
                             produce_gemm(P, P.lay.bwd[base + l], ring, bar_full, bar_empty, pcount, 0, P.lay.bwd[base + l].n_chunks);
                 } else {
-                    if (P.heads_mask & 1) for (int t = 0; t < NT; ++t) produce_gemm(P, P.lay.bwd[P_D1], ring, bar_full, bar_empty, pcount, 0, 4);
-                    if (P.heads_mask & 2) for (int t = 0; t < NT; ++t) produce_gemm(P, P.lay.bwd[P_C1], ring, bar_full, bar_empty, pcount, 0, 4);
+                    // A operand of the first GEMM(s): sum over feet of dZ1 of each head (P.tsrc, made by sum_feet_kernel), bulk
+                    // loaded into the tile's activation buffer once the buffer's previous reader is done
+                    for (int hd = 0; hd < 2; ++hd) {
+                        if (!(P.heads_mask & (1 << hd))) continue;
+                        for (int t = 0; t < NT; ++t) {
+                            if (n_free[t] > 0) mbar_wait(&bar_act_free[t], (n_free[t] - 1) & 1);   // every load but the first
+                            ++n_free[t];
+                            mbar_expect_tx(&bar_in_full[t], kTileBytes);
+                            bulk_g2s(act + t * kTileBytes, P.tsrc[hd] + ((size_t)b * P.tpf2 + t0 + t) * kTileBytes, kTileBytes, &bar_in_full[t]);
+                            produce_gemm(P, P.lay.bwd[hd ? P_C1 : P_D1], ring, bar_full, bar_empty, pcount, 0, 4);
+                        }
+                    }
                     for (int l = 4; l >= 1; --l)
                         for (int t = 0; t < NT; ++t) produce_gemm(P, P.lay.bwd[P_T0 + l], ring, bar_full, bar_empty, pcount, 0, 4);
                 }
@@ -301,8 +303,8 @@ __global__ void __launch_bounds__(64 + 128 * NT, 1) chain_kernel(const __grid_co
         // ===================================== MMA issuer =========================================
         if (lane == 0) {
             uint32_t ccount = 0, icount = 0;
-            uint32_t n_act[NT];
-            for (int t = 0; t < NT; ++t) n_act[t] = 0;
+            uint32_t n_act[NT], n_in[NT];
+            for (int t = 0; t < NT; ++t) n_act[t] = n_in[t] = 0;
             const uint32_t act_s = smem_u32(act), ring_s = smem_u32(ring);
             auto wait_act = [&](int t) { mbar_wait(&bar_act_ready[t], n_act[t] & 1); ++n_act[t]; tc_fence_after(); };
             // one layer of one tile; then straight on to the other tile while this one's epilogue runs
@@ -341,13 +343,18 @@ __global__ void __launch_bounds__(64 + 128 * NT, 1) chain_kernel(const __grid_co
                             gemm(t, P.lay.bwd[base + l], 0, P.lay.bwd[base + l].n_chunks, false);
                         }
                 } else {
-                    bool first = true;
-                    if (P.heads_mask & 1) {
-                        for (int t = 0; t < NT; ++t) { wait_act(t); gemm(t, P.lay.bwd[P_D1], 0, 4, false); }
-                        first = false;
+                    const int last_hd = (P.heads_mask & 2) ? 1 : 0;
+                    for (int hd = 0; hd < 2; ++hd) {
+                        if (!(P.heads_mask & (1 << hd))) continue;
+                        for (int t = 0; t < NT; ++t) {
+                            mbar_wait(&bar_in_full[t], n_in[t] & 1); ++n_in[t];
+                            tc_fence_after();
+                            mma_gemm(P.lay.bwd[hd ? P_C1 : P_D1], act_s + t * kTileBytes, ring_s, tmem + t * 256, bar_full, bar_empty,
+                                     ccount, 0, 4, hd == 1 && (P.heads_mask & 1));
+                            // not the last head: the buffer goes back to the producer; last: the accumulator to the epilogue
+                            umma_commit(hd == last_hd ? &bar_acc_ready[t] : &bar_act_free[t]);
+                        }
                     }
-                    if (P.heads_mask & 2)
-                        for (int t = 0; t < NT; ++t) { wait_act(t); gemm(t, P.lay.bwd[P_C1], 0, 4, !first); }
                     for (int l = 4; l >= 1; --l)
                         for (int t = 0; t < NT; ++t) { wait_act(t); gemm(t, P.lay.bwd[P_T0 + l], 0, 4, false); }
                 }
@@ -499,27 +506,6 @@ __global__ void __launch_bounds__(64 + 128 * NT, 1) chain_kernel(const __grid_co
                 }
             } else {   // TRUNK_BWD
                 const size_t tt = (size_t)b * P.tpf2 + t;
-                const int f0 = P.shared ? 0 : b, f1 = P.shared ? P.B : b + 1;
-                auto fill_sum = [&](int hd) {        // A = sum over feet of dZ1 of head hd (elementwise on images)
-                    for (int j = gt; j < kTileBytes / 16; j += 128) {
-                        float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-                        for (int f = f0; f < f1; ++f) {
-                            const uint8_t* src = P.hdz + (((size_t)hd * 3 + 0) * P.B * P.tpf2 + (size_t)f * P.tpf2 + t) * kTileBytes;
-                            add8(acc, __ldg(reinterpret_cast<const uint4*>(src) + j));
-                        }
-                        uint4 pk = make_uint4(pack_h2(acc[0], acc[1]), pack_h2(acc[2], acc[3]), pack_h2(acc[4], acc[5]), pack_h2(acc[6], acc[7]));
-                        *(reinterpret_cast<uint4*>(act_tile) + j) = pk;
-                    }
-                    fence_proxy_async();
-                };
-                bool filled = false;
-                for (int hd = 0; hd < 2; ++hd) {
-                    if (!(P.heads_mask & (1 << hd))) continue;
-                    if (!filled) before_overwrite(); else { wait_acc(); named_bar_sync(1 + tl, 128); }
-                    fill_sum(hd);
-                    signal_act();
-                    filled = true;
-                }
                 for (int l = 4; l >= 0; --l) {
                     const size_t slot = (size_t)l * P.trunk_tiles + tt;
                     uint32_t m[8];
@@ -530,6 +516,7 @@ __global__ void __launch_bounds__(64 + 128 * NT, 1) chain_kernel(const __grid_co
                     publish(P.tdz + slot * kTileBytes);
                     if (l > 0) signal_act();
                 }
+                if (leader) { bulk_wait_read0(); mbar_arrive(&bar_act_free[tl]); }   // buffer free for the next item's load
             }
         }
         if (leader) bulk_wait0();

@@ -17,6 +17,7 @@ struct ChainParams {
     const float* bias[P_COUNT];
     const float* biasfoot;       // [2][B][256]
     uint8_t *enc, *tact, *hact, *hdz, *doimg, *tdz;
+    const uint8_t* tsrc[2];      // TRUNK_BWD input per head: [trunk_tiles] tiles = sum over feet of dZ1 (or dZ1 itself)
     uint32_t *hmask, *tmask;     // ReLU sign bits saved by the forward epilogues, [..tile..][128 rows][8 words]
     float *disp, *col, *verts;   // [B][V][3]
     const float* reg;            // [B][9] or null
