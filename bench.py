@@ -58,14 +58,32 @@ FLOP_PER_PAIR = 8                                # 3 sub + 1 mul + 2 fma(=4) ...
 
 
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md recipe)."""
+    """SM clock / throttle reasons / power sampled DURING the timed region (B200_PROFILING.md's clocks line).  The timed
+    region is short (tens of ms), so the sampler reads NVML in-process every ~2 ms (nvidia_ml_py); `nvidia-smi -lms 100`
+    is the fallback when NVML cannot be loaded."""
     Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
     def __init__(self, index: int):
         self.index, self.proc, self.lines = index, None, []
+        self.samples, self.stop_flag, self.h, self.nv = [], False, None, None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            try:
+                uuid = str(torch.cuda.get_device_properties(index).uuid)
+                self.h = pynvml.nvmlDeviceGetHandleByUUID(("GPU-" + uuid) if not uuid.startswith("GPU-") else uuid)
+            except Exception:
+                self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.nv = pynvml
+        except Exception:
+            self.nv = None
 
     def start(self):
+        if self.nv is not None:
+            self.th = threading.Thread(target=self._poll, daemon=True)
+            self.th.start()
+            return
         try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
                                           "--format=csv,noheader,nounits", "-lms", "100"], stdout=subprocess.PIPE,
@@ -75,35 +93,71 @@ class ClockSampler:
         except OSError:
             self.proc = None
 
+    def _poll(self):
+        nv, h = self.nv, self.h
+        bits = {"hw_slowdown": nv.nvmlClocksEventReasonHwSlowdown if hasattr(nv, "nvmlClocksEventReasonHwSlowdown") else 0x8,
+                "hw_thermal_slowdown": 0x40, "sw_thermal_slowdown": 0x20, "sw_power_cap": 0x4}
+        smax = None
+        try:
+            smax = float(nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM))
+        except Exception:
+            pass
+        while not self.stop_flag:
+            try:
+                sm = float(nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM))
+                try:
+                    mask = int(nv.nvmlDeviceGetCurrentClocksEventReasons(h))
+                except Exception:
+                    mask = int(nv.nvmlDeviceGetCurrentClocksThrottleReasons(h))
+                try:
+                    pw = nv.nvmlDeviceGetPowerUsage(h) / 1e3
+                except Exception:
+                    pw = None
+                self.samples.append((sm, smax, pw, [n for n, b in bits.items() if mask & b]))
+            except Exception:
+                break
+            time.sleep(0.002)
+
     def _read(self):
         for line in self.proc.stdout:
             self.lines.append(line.strip())
 
     def stop(self):
-        if self.proc is None:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        self.proc.terminate()
-        try:
-            self.proc.wait(timeout=5)
-        except subprocess.TimeoutExpired:
-            self.proc.kill()
         sm, smax, reasons, power = [], [], set(), []
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for ln in self.lines:
-            f = [x.strip() for x in ln.split(",")]
-            if len(f) < 7:
-                continue
+        if self.nv is not None:
+            self.stop_flag = True
+            self.th.join(timeout=2)
+            for c, m, pw, rs in self.samples:
+                sm.append(c)
+                if m: smax.append(m)
+                if pw is not None: power.append(pw)
+                reasons.update(rs)
+            how = "nvml in-process, 2 ms cadence"
+        else:
+            if self.proc is None:
+                return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+            self.proc.terminate()
             try:
-                sm.append(float(f[0])); smax.append(float(f[1])); power.append(float(f[2]))
-            except ValueError:
-                continue
-            for n, v in zip(names, f[3:7]):
-                if v.lower().startswith("active"):
-                    reasons.add(n)
+                self.proc.wait(timeout=5)
+            except subprocess.TimeoutExpired:
+                self.proc.kill()
+            names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+            for ln in self.lines:
+                f = [x.strip() for x in ln.split(",")]
+                if len(f) < 7:
+                    continue
+                try:
+                    sm.append(float(f[0])); smax.append(float(f[1])); power.append(float(f[2]))
+                except ValueError:
+                    continue
+                for n, v in zip(names, f[3:7]):
+                    if v.lower().startswith("active"):
+                        reasons.add(n)
+            how = "nvidia-smi -lms 100"
         # "under load" = samples in the upper half of the observed clock range (idle samples sit at 120-300 MHz)
         load = [c for c in sm if c >= 0.5 * max(sm)] if sm else []
         return {"sm_mhz": statistics.median(load) if load else None, "sm_max_mhz": max(smax) if smax else None,
-                "power_w_max": max(power) if power else None, "samples": len(sm), "reasons": sorted(reasons)}
+                "power_w_max": max(power) if power else None, "samples": len(sm), "reasons": sorted(reasons), "how": how}
 
 
 def load_peaks():
@@ -255,22 +309,38 @@ def run_ours(args, wl, rank, world, local_rank):
         fp32_peak = blocks * 256 * iters * 64 * 2 * 2 / (e0.elapsed_time(e1) * 1e-3) / 1e12
     except Exception:
         pass
+    # pair evaluations the culled kNN kernel really executed in the last step (kernel counter, not an estimate)
+    knn_stats = (ctypes.c_ulonglong * 4)()
+    rc = lib.findb200_train_step_knn_stats(_lib.ptr(step.ws), feet, V, P2, knn_stats, _lib.stream_ptr(device))
+    pairs_exec = int(knn_stats[0]) if rc == 0 and knn_stats[0] else None
     for k in kernels:
         k["share"] = k["ms_per_step"] / prof_total
         fl = kernel_flops(k["name"], wl)
         if fl is not None and k["ms_per_step"] > 0:
-            k["tflops"] = fl / (k["ms_per_step"] * 1e-3) / 1e12
             if k["name"] == "knn_main":
+                # only EXECUTED pair evaluations are credited against the FP32 peak; the brute-force-equivalent rate
+                # (what the reference's knn_points would have to sustain for the same time) is reported beside it
+                k["tflops_bruteforce_equiv"] = fl / (k["ms_per_step"] * 1e-3) / 1e12
+                k["pairs_algorithmic"], k["pairs_executed"] = int(fl / FLOP_PER_PAIR), pairs_exec
+                if pairs_exec is not None:
+                    fl = float(FLOP_PER_PAIR) * pairs_exec
                 k["bound"], k["peak"] = "fp32", fp32_peak
             else:
                 k["bound"], k["peak"] = "tensor", peaks["bf16_sustained"]
+            k["tflops"] = fl / (k["ms_per_step"] * 1e-3) / 1e12
             k["frac"] = k["tflops"] / k["peak"] if k["peak"] else None
     math_k = [k for k in kernels if "tflops" in k]
     dom = max(math_k, key=lambda k: k["ms_per_step"]) if math_k else None
     roofline = None
+    traffic = None
+    try:       # dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed `ncu --set full` capture
+        with open(os.path.join(ROOT, "profiles", "ncu_traffic.json")) as fh:
+            traffic = json.load(fh).get(args.workload, {}).get(dom["name"] if dom else "", None)
+    except (OSError, ValueError):
+        pass
     if dom is not None:
         roofline = dict(kernel=dom["name"], bound=dom["bound"], achieved=round(dom["tflops"], 2), peak=dom["peak"],
-                        unit="TFLOP/s", frac=round(dom["frac"], 4) if dom["frac"] else None, traffic=None,
+                        unit="TFLOP/s", frac=round(dom["frac"], 4) if dom["frac"] else None, traffic=traffic,
                         kernel_ms=round(dom["ms_per_step"], 4), share_of_step=round(dom["share"], 3),
                         peak_source=("findb200_fp32_peak FFMA2 probe, same run" if dom["bound"] == "fp32"
                                      else peaks["source"] + " bf16_tflops_sustained (fp16 operands, same tensor rate)"))
@@ -368,7 +438,7 @@ def run_reference(args, wl, rank, world):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--steps", type=int, default=100)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="find_b200", choices=["find_b200", "reference"])
     ap.add_argument("--workload", default=None, choices=sorted(WORKLOADS))

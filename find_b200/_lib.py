@@ -44,6 +44,7 @@ SIGNATURES = {
     "findb200_l2_stream": (c_int, [c_void_p, c_size_t] + [c_int] * 5 + [c_void_p, c_void_p]),
     "findb200_set_knn_mode": (c_int, [c_int, c_int]),
     "findb200_knn_stats": (c_int, [c_void_p, c_void_p, c_void_p]),
+    "findb200_train_step_knn_stats": (c_int, [c_void_p, c_int, c_int, c_int, c_void_p, c_void_p]),
     "findb200_chamfer_backward": (c_int, [c_void_p] * 4 + [c_int] * 3 + [c_void_p] * 3 + [c_float] + [c_void_p] * 3),
 }
 

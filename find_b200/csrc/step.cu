@@ -124,6 +124,13 @@ int findb200_train_step(const findb200_field_params* p, const float* template_po
                                    ws + c.field, c.field_bytes, stream);
 }
 
+
+int findb200_train_step_knn_stats(const void* workspace, int nfeet, int V, int P2, unsigned long long* out4_host,
+                                  void* stream) {
+    FB_REQUIRE(workspace && out4_host && nfeet >= 1 && V >= 1 && P2 >= 1, FINDB200_ERR_ARG, "train_step_knn_stats: bad argument");
+    return findb200_knn_stats((const uint8_t*)workspace + carve(nfeet, V, P2).knn, out4_host, stream);
+}
+
 }  // extern "C"
 
 // ---- latent-table row gather / gradient scatter (LatentVector.__getitem__, model.py:130-152, and its autograd) ----

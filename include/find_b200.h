@@ -133,6 +133,11 @@ int findb200_train_step(const findb200_field_params* p, const float* template_po
                         const findb200_field_grads* gw, float* gz_shape, float* gz_pose, float* gz_tex, float* greg,
                         void* workspace, size_t workspace_bytes, void* stream);
 
+/* Kernel counters of the last findb200_train_step that used this workspace: same four numbers as findb200_knn_stats
+ * ({pair evaluations executed, cross-chunk-tie queries, most chunk evaluations of one group, groups}); synchronises. */
+int findb200_train_step_knn_stats(const void* workspace, int nfeet, int V, int P2, unsigned long long* out4_host,
+                                  void* stream);
+
 /* Latent-table access (replaces LatentVector.__getitem__ with an index tensor, src/model/model.py:130-152 as called
  * from sample_latent_vectors src/train/trainer.py:29-46, and the index scatter-add of its autograd).
  * table / grad_table: [n_rows,width]; idx: int64 [B] (device); out / g: [B,width].  Duplicate rows accumulate. */
