@@ -44,6 +44,17 @@ SIGNATURES = {
     "findb200_l2_stream": (c_int, [c_void_p, c_size_t] + [c_int] * 5 + [c_void_p, c_void_p]),
     "findb200_set_knn_mode": (c_int, [c_int, c_int]),
     "findb200_knn_stats": (c_int, [c_void_p, c_void_p, c_void_p]),
+    "findb200_sample_workspace_bytes": (c_size_t, [c_int, c_int]),
+    "findb200_sample_points_forward": (c_int, [c_void_p, c_int, c_void_p, c_int, c_void_p] + [c_int] * 4 + [ctypes.c_ulonglong]
+                                       + [c_void_p] * 6 + [c_int, c_int, c_void_p, c_void_p, c_size_t, c_void_p]),
+    "findb200_sample_points_backward": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_void_p] + [c_int] * 4
+                                        + [c_float, c_int, c_void_p, c_void_p]),
+    "findb200_mesh_smooth_workspace_bytes": (c_size_t, [c_int] * 3),
+    "findb200_mesh_smooth": (c_int, [c_void_p, c_int, c_int, c_void_p, c_int, c_void_p, c_int, c_void_p, c_void_p, c_void_p,
+                                     c_int, c_float, c_float, c_float, c_void_p, c_void_p, c_void_p, c_int, c_void_p,
+                                     c_size_t, c_void_p]),
+    "findb200_adam_step": (c_int, [c_void_p, c_int] + [c_float] * 5 + [c_void_p, c_void_p]),
+    "findb200_sgd_momentum_step": (c_int, [c_void_p, c_int] + [c_float] * 3 + [c_void_p, c_void_p]),
     "findb200_train_step_knn_stats": (c_int, [c_void_p, c_int, c_int, c_int, c_void_p, c_void_p]),
     "findb200_chamfer_backward": (c_int, [c_void_p] * 4 + [c_int] * 3 + [c_void_p] * 3 + [c_float] + [c_void_p] * 3),
 }

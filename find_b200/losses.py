@@ -8,7 +8,8 @@ before Chamfer (losses.py:63,67).  BASELINE.json's configurations take Chamfer d
 vertices and a target point cloud, so here ``num_samples=None`` (default) means "use the points as given":
   * prediction = ``res['verts']`` ([B,V,3], what ``res['meshes'].verts_padded()`` holds),
   * target     = ``batch['points']`` ([B,P,3] tensor or ``Pointclouds``), else ``batch['mesh'].verts_padded()``.
-Surface sampling is SURVEY.md §8(f) row 1 ("next"); asking for it (``num_samples`` an int) raises until it lands.
+``num_samples=<int>`` reproduces the reference: both meshes are surface-sampled on the GPU first (find_b200.mesh,
+SURVEY.md §8(f) row 1; same distribution as PyTorch3D's sampler, its own Philox stream — ``seed`` makes it repeatable).
 """
 from __future__ import annotations
 
@@ -33,12 +34,17 @@ def _target_points(batch):
 class DisplacementLoss(nn.Module):
     """losses.py:59-90 -> dict(loss=chamfer).  All three z-cutoff variants are kept (ragged clouds)."""
 
-    def forward(self, model, res, batch, epoch=0, num_samples=None, z_cutoff=None, gt_z_cutoff=None):
-        if num_samples is not None:
-            raise NotImplementedError("surface sampling (sample_points_from_meshes) is not on the CUDA path yet; "
-                                      "pass num_samples=None to take Chamfer on the vertices / given points")
-        gt_samples = _target_points(batch)
-        pred_samples = res["verts"] if "verts" in res else res["meshes"].verts_padded()
+    def forward(self, model, res, batch, epoch=0, num_samples=None, z_cutoff=None, gt_z_cutoff=None, seed=None):
+        if num_samples is not None:                                # losses.py:63,67: 5000 surface samples of both meshes
+            from .mesh import sample_points_from_meshes
+            s_gt = None if seed is None else 2 * int(seed)
+            s_pr = None if seed is None else 2 * int(seed) + 1
+            gt_samples = (sample_points_from_meshes(batch["mesh"], num_samples=num_samples, seed=s_gt)
+                          if "mesh" in batch and hasattr(batch["mesh"], "faces_padded") else _target_points(batch))
+            pred_samples = sample_points_from_meshes(res["meshes"], num_samples=num_samples, seed=s_pr)
+        else:
+            gt_samples = _target_points(batch)
+            pred_samples = res["verts"] if "verts" in res else res["meshes"].verts_padded()
 
         if z_cutoff is not None:                                   # losses.py:69-77
             gt_pad = gt_samples.points_padded() if isinstance(gt_samples, Pointclouds) else gt_samples

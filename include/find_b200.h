@@ -133,6 +133,59 @@ int findb200_train_step(const findb200_field_params* p, const float* template_po
                         const findb200_field_grads* gw, float* gz_shape, float* gz_pose, float* gz_tex, float* greg,
                         void* workspace, size_t workspace_bytes, void* stream);
 
+/* ------------------------------------------------------------------------------------------------------
+ * Mesh side of the 3-D loss.  faces / edges / incidence lists are int32 device arrays.
+ * ------------------------------------------------------------------------------------------------------ */
+
+/* pytorch3d.ops.sample_points_from_meshes(meshes, num_samples, return_textures)  — src/model/losses.py:39,63,67,
+ * src/eval/eval_3d.py:149-150.  verts [N,V,3] (verts_shared: one [V,3] array for all meshes), faces [N,F,3] or shared
+ * [F,3]; num_faces [N] int64 valid faces per mesh (NULL = F).  The draw: Philox4x32-10 keyed by `seed` over an integer
+ * area CDF (see csrc/mesh.cu); pass face_idx_in [N,S] (mesh-local) and uv_in [2,N,S] (PyTorch3D's
+ * _rand_barycentric_coords layout) to inject a draw instead.  Outputs: samples [N,S,3]; face_idx [N,S] and bary [N,S,3]
+ * (optional, needed by the backward); attr_out [N,S,C] = barycentric interpolation of vert_attr [N,V,C] (optional:
+ * TexturesVertex colours for return_textures=True).  Workspace only needed when the draw is made here. */
+size_t findb200_sample_workspace_bytes(int N, int F);
+int findb200_sample_points_forward(const float* verts, int verts_shared, const int32_t* faces, int faces_shared,
+                                   const int64_t* num_faces, int N, int V, int F, int S, unsigned long long seed,
+                                   const int64_t* face_idx_in, const float* uv_in, float* samples, int64_t* face_idx,
+                                   float* bary, const float* vert_attr, int attr_shared, int C, float* attr_out,
+                                   void* workspace, size_t workspace_bytes, void* stream);
+/* autograd of the interpolation: grad_verts[n, faces[f][k]] += bary[k] * grad_scale * grad_samples[n,s]
+ * (grad_verts [N,V,3]; zeroed first unless accumulate != 0) */
+int findb200_sample_points_backward(const float* grad_samples, const int32_t* faces, int faces_shared,
+                                    const int64_t* face_idx, const float* bary, int N, int V, int F, int S,
+                                    float grad_scale, int accumulate, float* grad_verts, void* stream);
+
+/* MeshSmoothnessLoss (src/model/losses.py:93-99) = w_lap * mesh_laplacian_smoothing(meshes, "cot") +
+ * w_edge * mesh_edge_loss(meshes, target_length) on N meshes sharing one topology (the deformed template):
+ * faces [F,3], unique edges [E,2], vertex -> (face, corner) incidence in CSR form (vf_ptr [V+1], vf_face / vf_corner [nnz]).
+ * loss2[0] = edge loss, loss2[1] = laplacian loss (unweighted, device).  grad_verts (optional, [N,V,3]) receives
+ * w_edge * d edge + w_lap * d laplacian (added when accumulate != 0).  grad_loss must be NULL (fold it into the weights). */
+size_t findb200_mesh_smooth_workspace_bytes(int N, int V, int nnz);
+int findb200_mesh_smooth(const float* verts, int N, int V, const int32_t* faces, int F, const int32_t* edges, int E,
+                         const int32_t* vf_ptr, const int32_t* vf_face, const int32_t* vf_corner, int nnz,
+                         float target_length, float w_edge, float w_lap, const float* grad_loss, float* loss2,
+                         float* grad_verts, int accumulate, void* workspace, size_t workspace_bytes, void* stream);
+
+/* ------------------------------------------------------------------------------------------------------
+ * Optimiser updates: torch.optim.Adam(main_params / latent_params) and
+ * torch.optim.SGD(reg_params, momentum=0.9) as stepped at src/train/train.py:161-168, src/train/trainer.py:122-123.
+ * One launch updates every tensor of the table (dense updates, like torch on dense .grad).  `tensors` is a HOST array of
+ * device pointers; step_dev is a device int64 holding the number of steps taken so far (read, then incremented on the
+ * stream), which keeps the call legal inside a captured CUDA graph.
+ * ------------------------------------------------------------------------------------------------------ */
+typedef struct findb200_optim_tensor {
+    float* param;         /* updated in place */
+    const float* grad;
+    float* m;             /* Adam exp_avg / SGD momentum_buffer */
+    float* v;             /* Adam exp_avg_sq (unused by SGD, may be NULL) */
+    long long numel;
+} findb200_optim_tensor;
+int findb200_adam_step(const findb200_optim_tensor* tensors, int n_tensors, float lr, float beta1, float beta2, float eps,
+                       float weight_decay, long long* step_dev, void* stream);
+int findb200_sgd_momentum_step(const findb200_optim_tensor* tensors, int n_tensors, float lr, float momentum, float weight_decay,
+                               long long* step_dev, void* stream);
+
 /* Kernel counters of the last findb200_train_step that used this workspace: same four numbers as findb200_knn_stats
  * ({pair evaluations executed, cross-chunk-tie queries, most chunk evaluations of one group, groups}); synchronises. */
 int findb200_train_step_knn_stats(const void* workspace, int nfeet, int V, int P2, unsigned long long* out4_host,
