@@ -37,15 +37,17 @@ FB_DEVINL int find_tensor(const Table& t, long long grp) {
 
 // mode 0: Adam;  mode 1: SGD with momentum (m = momentum buffer; first step: buf = grad)
 template <int MODE>
-__global__ void __launch_bounds__(256) optim_kernel(const __grid_constant__ Table t, float lr, float b1, float b2, float eps, float wd,
+__global__ void __launch_bounds__(256) optim_kernel(const __grid_constant__ Table t, double lr_d, double b1_d, double b2_d, float eps, float wd,
                                                     const long long* __restrict__ step_dev) {
+    // hyper-parameters arrive as doubles, as torch holds them: 1 - beta is formed in double and rounded once
+    const float lr = (float)lr_d, b1 = (float)b1_d, b2 = (float)b2_d, omb1 = (float)(1.0 - b1_d), omb2 = (float)(1.0 - b2_d);
     const long long total = t.start[t.n];
     const long long step = *step_dev + 1;
     float step_size = lr, inv_sqrt_bc2 = 1.f;
     if (MODE == 0) {
-        const double bc1 = 1.0 - pow((double)b1, (double)step), bc2 = 1.0 - pow((double)b2, (double)step);
-        step_size = (float)((double)lr / bc1);
-        inv_sqrt_bc2 = (float)(1.0 / sqrt(bc2));
+        const double bc1 = 1.0 - pow(b1_d, (double)step), bc2 = 1.0 - pow(b2_d, (double)step);
+        step_size = (float)(lr_d / bc1);
+        inv_sqrt_bc2 = 1.f / (float)sqrt(bc2);        // torch divides by the scalar through its fp32 reciprocal
     }
     for (long long grp = (long long)blockIdx.x * blockDim.x + threadIdx.x; grp < total; grp += (long long)gridDim.x * blockDim.x) {
         const int k = find_tensor(t, grp);
@@ -62,10 +64,10 @@ __global__ void __launch_bounds__(256) optim_kernel(const __grid_constant__ Tabl
             float gj = g[j], pj = p[j];
             if (wd != 0.f) gj = gj + wd * pj;
             if (MODE == 0) {
-                const float mj = m[j] + (gj - m[j]) * (1.f - b1);              // exp_avg.lerp_(grad, 1 - beta1)
-                const float vj = v[j] * b2 + (1.f - b2) * gj * gj;             // exp_avg_sq.mul_(b2).addcmul_(g, g, 1 - b2)
+                const float mj = m[j] + (gj - m[j]) * omb1;                    // exp_avg.lerp_(grad, 1 - beta1)
+                const float vj = v[j] * b2 + omb2 * gj * gj;                   // exp_avg_sq.mul_(b2).addcmul_(g, g, 1 - b2)
                 const float denom = sqrtf(vj) * inv_sqrt_bc2 + eps;
-                p[j] = pj - step_size * (mj / denom);
+                p[j] = pj + (-step_size * mj) / denom;                          // addcdiv_(exp_avg, denom, value=-step_size)
                 m[j] = mj; v[j] = vj;
             } else {
                 const float mj = step == 1 ? gj : m[j] * b1 + gj;              // b1 = momentum
@@ -84,8 +86,8 @@ __global__ void bump_step_kernel(long long* step) { *step += 1; }
 using namespace fb;
 using namespace fb::optim;
 
-static int launch_optim(int mode, const findb200_optim_tensor* tensors, int n_tensors, float lr, float b1, float b2, float eps,
-                        float wd, long long* step_dev, cudaStream_t st) {
+static int launch_optim(int mode, const findb200_optim_tensor* tensors, int n_tensors, double lr, double b1, double b2, double eps,
+                        double wd, long long* step_dev, cudaStream_t st) {
     FB_REQUIRE(tensors && step_dev, FINDB200_ERR_ARG, "optim: null argument");
     FB_REQUIRE(n_tensors >= 1 && n_tensors <= kMaxTensors, FINDB200_ERR_SHAPE, "optim: 1..%d tensors per call (got %d)", kMaxTensors,
                n_tensors);
@@ -107,9 +109,9 @@ static int launch_optim(int mode, const findb200_optim_tensor* tensors, int n_te
     if (blocks > 148 * 8) blocks = 148 * 8;
     FB_MARK(mode == 0 ? "adam" : "sgd_momentum", st);
     if (mode == 0)
-        optim_kernel<0><<<(int)blocks, 256, 0, st>>>(t, lr, b1, b2, eps, wd, step_dev);
+        optim_kernel<0><<<(int)blocks, 256, 0, st>>>(t, lr, b1, b2, (float)eps, (float)wd, step_dev);
     else
-        optim_kernel<1><<<(int)blocks, 256, 0, st>>>(t, lr, b1, 0.f, 0.f, wd, step_dev);
+        optim_kernel<1><<<(int)blocks, 256, 0, st>>>(t, lr, b1, 0.0, 0.f, (float)wd, step_dev);
     FB_CUDA(cudaGetLastError());
     bump_step_kernel<<<1, 1, 0, st>>>(step_dev);
     FB_CUDA(cudaGetLastError());
@@ -119,14 +121,14 @@ static int launch_optim(int mode, const findb200_optim_tensor* tensors, int n_te
 
 extern "C" {
 
-int findb200_adam_step(const findb200_optim_tensor* tensors, int n_tensors, float lr, float beta1, float beta2, float eps,
-                       float weight_decay, long long* step_dev, void* stream) {
+int findb200_adam_step(const findb200_optim_tensor* tensors, int n_tensors, double lr, double beta1, double beta2, double eps,
+                       double weight_decay, long long* step_dev, void* stream) {
     return launch_optim(0, tensors, n_tensors, lr, beta1, beta2, eps, weight_decay, step_dev, (cudaStream_t)stream);
 }
 
-int findb200_sgd_momentum_step(const findb200_optim_tensor* tensors, int n_tensors, float lr, float momentum, float weight_decay,
+int findb200_sgd_momentum_step(const findb200_optim_tensor* tensors, int n_tensors, double lr, double momentum, double weight_decay,
                                long long* step_dev, void* stream) {
-    return launch_optim(1, tensors, n_tensors, lr, momentum, 0.f, 0.f, weight_decay, step_dev, (cudaStream_t)stream);
+    return launch_optim(1, tensors, n_tensors, lr, momentum, 0.0, 0.0, weight_decay, step_dev, (cudaStream_t)stream);
 }
 
 }  // extern "C"

@@ -181,9 +181,9 @@ typedef struct findb200_optim_tensor {
     float* v;             /* Adam exp_avg_sq (unused by SGD, may be NULL) */
     long long numel;
 } findb200_optim_tensor;
-int findb200_adam_step(const findb200_optim_tensor* tensors, int n_tensors, float lr, float beta1, float beta2, float eps,
-                       float weight_decay, long long* step_dev, void* stream);
-int findb200_sgd_momentum_step(const findb200_optim_tensor* tensors, int n_tensors, float lr, float momentum, float weight_decay,
+int findb200_adam_step(const findb200_optim_tensor* tensors, int n_tensors, double lr, double beta1, double beta2, double eps,
+                       double weight_decay, long long* step_dev, void* stream);
+int findb200_sgd_momentum_step(const findb200_optim_tensor* tensors, int n_tensors, double lr, double momentum, double weight_decay,
                                long long* step_dev, void* stream);
 
 /* Kernel counters of the last findb200_train_step that used this workspace: same four numbers as findb200_knn_stats
