@@ -35,6 +35,8 @@ SIGNATURES = {
                                 + [c_size_t, c_void_p]),
     "findb200_train_step_workspace_bytes": (c_size_t, [c_int] * 3),
     "findb200_train_step": (c_int, [c_void_p] * 9 + [c_int] * 3 + [c_float] * 2 + [c_void_p] * 10 + [c_size_t, c_void_p]),
+    "findb200_train_step_mesh_workspace_bytes": (c_size_t, [c_int] * 6),
+    "findb200_train_step_mesh": (c_int, [c_void_p] * 9 + [c_int] * 3 + [c_float] * 2 + [c_void_p] * 11 + [c_size_t, c_void_p]),
     "findb200_gather_rows": (c_int, [c_void_p, c_int, c_int, c_void_p, c_int, c_void_p, c_void_p]),
     "findb200_scatter_add_rows": (c_int, [c_void_p, c_int, c_int, c_void_p, c_int, c_void_p, c_void_p]),
     "findb200_profile_enable": (c_int, [c_int]),
@@ -46,7 +48,7 @@ SIGNATURES = {
     "findb200_knn_stats": (c_int, [c_void_p, c_void_p, c_void_p]),
     "findb200_sample_workspace_bytes": (c_size_t, [c_int, c_int]),
     "findb200_sample_points_forward": (c_int, [c_void_p, c_int, c_void_p, c_int, c_void_p] + [c_int] * 4 + [ctypes.c_ulonglong]
-                                       + [c_void_p] * 6 + [c_int, c_int, c_void_p, c_void_p, c_size_t, c_void_p]),
+                                       + [c_void_p] * 7 + [c_int, c_int, c_void_p, c_void_p, c_size_t, c_void_p]),
     "findb200_sample_points_backward": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_void_p] + [c_int] * 4
                                         + [c_float, c_int, c_void_p, c_void_p]),
     "findb200_mesh_smooth_workspace_bytes": (c_size_t, [c_int] * 3),

@@ -12,7 +12,8 @@
 // here in a way a CPU oracle can restate bit for bit (oracle/mesh_oracle.py):
 //   area_f  = 0.5 * sqrt(|e1 x e2|^2) with every fp32 operation individually rounded (no FMA contraction);
 //   q_f     = floor(double(area_f) / double(max_f area_f) * 2^32)  as uint64  -> integer CDF, order independent;
-//   r0..r3  = Philox4x32-10(counter = (sample, mesh, 0, 0), key = seed);  target = mulhi64(r0:r1, total);
+//   r0..r3  = Philox4x32-10(counter = (sample, mesh, draw_lo, draw_hi), key = seed), draw = *draw_counter (0 if NULL):
+//             a device counter so that a captured CUDA graph draws fresh samples on every replay;  target = mulhi64(r0:r1, total);
 //   face    = first f with cdf_incl[f] > target;   u = (r2 >> 8) 2^-24,  v = (r3 >> 8) 2^-24.
 // Callers that need PyTorch3D's exact draw pass face indices and (u, v) in; the interpolation then follows the same
 // operation order as PyTorch3D's `w0*a + w1*b + w2*c` (each product and sum rounded once).
@@ -127,12 +128,16 @@ struct SampleOut {
 
 __global__ void sample_points_kernel(const SampleGeom g, const unsigned long long* __restrict__ cdf,
                                      const int64_t* __restrict__ face_in, const float* __restrict__ uv_in, int S,
-                                     unsigned long long seed, const SampleOut o) {
+                                     unsigned long long seed, const unsigned long long* __restrict__ draw_counter,
+                                     const SampleOut o) {
     const int n = blockIdx.y;
     const int s = blockIdx.x * blockDim.x + threadIdx.x;
     if (s >= S) return;
     uint32_t r[4] = {0u, 0u, 0u, 0u};
-    if (!face_in || !uv_in) philox4x32_10((uint32_t)s, (uint32_t)n, 0u, 0u, (uint32_t)seed, (uint32_t)(seed >> 32), r);
+    if (!face_in || !uv_in) {
+        const unsigned long long draw = draw_counter ? *draw_counter : 0ull;
+        philox4x32_10((uint32_t)s, (uint32_t)n, (uint32_t)draw, (uint32_t)(draw >> 32), (uint32_t)seed, (uint32_t)(seed >> 32), r);
+    }
     int f;
     if (face_in) {
         const long long fi = face_in[(size_t)n * S + s];
@@ -360,6 +365,7 @@ size_t findb200_sample_workspace_bytes(int N, int F) {
 
 int findb200_sample_points_forward(const float* verts, int verts_shared, const int32_t* faces, int faces_shared,
                                    const int64_t* num_faces, int N, int V, int F, int S, unsigned long long seed,
+                                   const unsigned long long* draw_counter,
                                    const int64_t* face_idx_in, const float* uv_in, float* samples, int64_t* face_idx,
                                    float* bary, const float* vert_attr, int attr_shared, int C, float* attr_out,
                                    void* workspace, size_t workspace_bytes, void* stream) {
@@ -390,7 +396,7 @@ int findb200_sample_points_forward(const float* verts, int verts_shared, const i
     SampleOut o{samples, face_idx, bary, C > 0 ? vert_attr : nullptr, C > 0 ? attr_out : nullptr,
                 attr_shared ? 0ll : (long long)V * C, C};
     FB_MARK("sample_points", st);
-    sample_points_kernel<<<dim3((S + 127) / 128, N), 128, 0, st>>>(g, cdf, face_idx_in, uv_in, S, seed, o);
+    sample_points_kernel<<<dim3((S + 127) / 128, N), 128, 0, st>>>(g, cdf, face_idx_in, uv_in, S, seed, draw_counter, o);
     FB_CUDA(cudaGetLastError());
     FB_MARK_END(st);
     return 0;

@@ -16,20 +16,37 @@ static inline size_t align1k(size_t x) { return (x + 1023) & ~(size_t)1023; }
 struct Carve {
     size_t field, knn, idx_x, idx_y, grad_verts, grad_col, sums, total;
     size_t field_bytes, knn_bytes;
+    // mesh terms (findb200_train_step_mesh): surface samples of the deformed template and the smoothness workspace
+    size_t samples, fidx, bary, grad_samples, sample_ws, smooth_ws, smooth2;
+    size_t sample_ws_bytes, smooth_ws_bytes;
 };
-static Carve carve(int B, int V, int P2) {
+static Carve carve(int B, int V, int P2, int S = 0, int nnz = 0, int F = 0) {
     Carve c{};
     size_t off = 0;
     auto take = [&](size_t bytes) { size_t o = off; off = align1k(off + bytes); return o; };
+    const int P1 = S > 0 ? S : V;
     c.field_bytes = findb200_field_workspace_bytes(B, V, 1, 1);
-    c.knn_bytes = findb200_knn_workspace_bytes(B, V, P2);
+    c.knn_bytes = findb200_knn_workspace_bytes(B, P1, P2);
     c.field = take(c.field_bytes);
     c.knn = take(c.knn_bytes);
-    c.idx_x = take((size_t)B * V * 8);
+    c.idx_x = take((size_t)B * P1 * 8);
     c.idx_y = take((size_t)B * P2 * 8);
     c.grad_verts = take((size_t)B * V * 12);
     c.grad_col = take((size_t)B * V * 12);
     c.sums = take(1024);
+    if (S > 0) {
+        c.samples = take((size_t)B * S * 12);
+        c.fidx = take((size_t)B * S * 8);
+        c.bary = take((size_t)B * S * 12);
+        c.grad_samples = take((size_t)B * S * 12);
+        c.sample_ws_bytes = findb200_sample_workspace_bytes(B, F);
+        c.sample_ws = take(c.sample_ws_bytes);
+    }
+    if (nnz > 0) {
+        c.smooth_ws_bytes = findb200_mesh_smooth_workspace_bytes(B, V, nnz);
+        c.smooth_ws = take(c.smooth_ws_bytes);
+        c.smooth2 = take(64);
+    }
     c.total = off;
     return c;
 }
@@ -54,14 +71,21 @@ __global__ void __launch_bounds__(256) col_mse_kernel(const float* __restrict__ 
 }
 
 __global__ void combine_loss_kernel(const float* chamf, const double* mse_sum, double n, float w_chamf, float w_tex,
-                                    float* loss3) {
+                                    const float* smooth2, float w_smooth, float* loss3, float* loss_extra) {
     if (threadIdx.x || blockIdx.x) return;
     const float c = *chamf;
     const float t = mse_sum ? (float)(*mse_sum / n) : 0.f;
-    loss3[0] = w_chamf * c + w_tex * t;
+    float sm = 0.f;
+    if (smooth2) {                         // MeshSmoothnessLoss, losses.py:97: 0.1 * laplacian + 10 * edge
+        sm = 0.1f * smooth2[1] + 10.f * smooth2[0];
+        if (loss_extra) { loss_extra[0] = smooth2[0]; loss_extra[1] = smooth2[1]; }
+    }
+    loss3[0] = w_chamf * c + w_tex * t + w_smooth * sm;
     loss3[1] = c;
     loss3[2] = t;
 }
+
+__global__ void bump_counter_kernel(unsigned long long* c) { *c += 1ull; }
 
 }  // namespace step
 }  // namespace fb
@@ -76,17 +100,31 @@ size_t findb200_train_step_workspace_bytes(int nfeet, int V, int P2) {
     return carve(nfeet, V, P2).total;
 }
 
-int findb200_train_step(const findb200_field_params* p, const float* template_pos, const float* z_shape,
-                        const float* z_pose, const float* z_tex, const float* reg, const float* target,
-                        const int64_t* target_len, const float* col_target, int nfeet, int V, int P2, float w_chamf,
-                        float w_tex, float* loss3, float* disp, float* col, float* verts,
-                        const findb200_field_grads* gw, float* gz_shape, float* gz_pose, float* gz_tex, float* greg,
-                        void* workspace, size_t workspace_bytes, void* stream) {
+size_t findb200_train_step_mesh_workspace_bytes(int nfeet, int V, int P2, int num_samples, int nnz, int F) {
+    if (nfeet < 1 || V < 1 || P2 < 0 || num_samples < 0 || nnz < 0 || F < 0) return 0;
+    return carve(nfeet, V, P2, num_samples, nnz, F).total;
+}
+
+}  // extern "C"
+
+static int run_step(const findb200_field_params* p, const float* template_pos, const float* z_shape, const float* z_pose,
+                    const float* z_tex, const float* reg, const float* target, const int64_t* target_len,
+                    const float* col_target, int nfeet, int V, int P2, float w_chamf, float w_tex, float* loss3, float* disp,
+                    float* col, float* verts, const findb200_field_grads* gw, float* gz_shape, float* gz_pose, float* gz_tex,
+                    float* greg, const findb200_mesh_terms* mt, void* workspace, size_t workspace_bytes, void* stream) {
     cudaStream_t st = (cudaStream_t)stream;
     FB_REQUIRE(p && template_pos && target && loss3 && disp && col && verts, FINDB200_ERR_ARG,
                "train_step: a required pointer is null");
     FB_REQUIRE(nfeet >= 1 && V >= 1 && P2 >= 1, FINDB200_ERR_SHAPE, "train_step: bad sizes nfeet=%d V=%d P2=%d", nfeet, V, P2);
-    const Carve c = carve(nfeet, V, P2);
+    const int S = mt ? mt->num_samples : 0;
+    const bool smooth = mt && mt->w_smooth != 0.f;
+    if (mt) {
+        FB_REQUIRE(S >= 0, FINDB200_ERR_SHAPE, "train_step_mesh: num_samples < 0");
+        FB_REQUIRE(!(S > 0) || (mt->faces && mt->F >= 1), FINDB200_ERR_ARG, "train_step_mesh: sampling needs the template faces");
+        FB_REQUIRE(!smooth || (mt->faces && mt->edges && mt->vf_ptr && mt->vf_face && mt->vf_corner && mt->F >= 1 && mt->E >= 1 &&
+                               mt->nnz >= 1), FINDB200_ERR_ARG, "train_step_mesh: smoothness needs faces, edges and the incidence list");
+    }
+    const Carve c = carve(nfeet, V, P2, S, smooth ? mt->nnz : 0, S > 0 ? mt->F : 0);
     FB_REQUIRE(workspace && workspace_bytes >= c.total, FINDB200_ERR_WORKSPACE,
                "train_step: workspace too small (%zu < %zu bytes)", workspace_bytes, c.total);
     uint8_t* ws = (uint8_t*)workspace;
@@ -100,12 +138,44 @@ int findb200_train_step(const findb200_field_params* p, const float* template_po
     int rc = findb200_field_forward(p, template_pos, 1, z_shape, z_pose, z_tex, reg, nfeet, V, 1, disp, col, verts,
                                     ws + c.field, c.field_bytes, stream);
     if (rc) return rc;
-    rc = findb200_chamfer_forward(verts, target, nullptr, target_len, nfeet, V, P2, chamf, nullptr, idx_x, nullptr, idx_y,
-                                  ws + c.knn, c.knn_bytes, stream);
-    if (rc) return rc;
-    rc = findb200_chamfer_backward(verts, target, nullptr, target_len, nfeet, V, P2, idx_x, idx_y, nullptr, w_chamf,
-                                   grad_verts, nullptr, stream);
-    if (rc) return rc;
+    if (S > 0) {
+        // losses.py:67: Chamfer is taken on S area-weighted surface samples of the deformed template
+        float* samples = (float*)(ws + c.samples);
+        int64_t* fidx = (int64_t*)(ws + c.fidx);
+        float* bary = (float*)(ws + c.bary);
+        float* grad_samples = (float*)(ws + c.grad_samples);
+        rc = findb200_sample_points_forward(verts, 0, mt->faces, 1, nullptr, nfeet, V, mt->F, S, mt->seed, mt->draw_counter, nullptr,
+                                            nullptr, samples, fidx, bary, nullptr, 0, 0, nullptr, ws + c.sample_ws,
+                                            c.sample_ws_bytes, stream);
+        if (rc) return rc;
+        if (mt->draw_counter) {
+            bump_counter_kernel<<<1, 1, 0, st>>>(mt->draw_counter);
+            FB_CUDA(cudaGetLastError());
+        }
+        rc = findb200_chamfer_forward(samples, target, nullptr, target_len, nfeet, S, P2, chamf, nullptr, idx_x, nullptr, idx_y,
+                                      ws + c.knn, c.knn_bytes, stream);
+        if (rc) return rc;
+        rc = findb200_chamfer_backward(samples, target, nullptr, target_len, nfeet, S, P2, idx_x, idx_y, nullptr, w_chamf,
+                                       grad_samples, nullptr, stream);
+        if (rc) return rc;
+        rc = findb200_sample_points_backward(grad_samples, mt->faces, 1, fidx, bary, nfeet, V, mt->F, S, 1.0f, 0, grad_verts, stream);
+        if (rc) return rc;
+    } else {
+        rc = findb200_chamfer_forward(verts, target, nullptr, target_len, nfeet, V, P2, chamf, nullptr, idx_x, nullptr, idx_y,
+                                      ws + c.knn, c.knn_bytes, stream);
+        if (rc) return rc;
+        rc = findb200_chamfer_backward(verts, target, nullptr, target_len, nfeet, V, P2, idx_x, idx_y, nullptr, w_chamf,
+                                       grad_verts, nullptr, stream);
+        if (rc) return rc;
+    }
+    float* smooth2 = nullptr;
+    if (smooth) {                          // model.py:1032-1033 on the deformed template; weights losses.py:97
+        smooth2 = (float*)(ws + c.smooth2);
+        rc = findb200_mesh_smooth(verts, nfeet, V, mt->faces, mt->F, mt->edges, mt->E, mt->vf_ptr, mt->vf_face, mt->vf_corner,
+                                  mt->nnz, 0.f, 10.f * mt->w_smooth, 0.1f * mt->w_smooth, nullptr, smooth2, grad_verts, 1,
+                                  ws + c.smooth_ws, c.smooth_ws_bytes, stream);
+        if (rc) return rc;
+    }
     const size_t n = (size_t)nfeet * V * 3;
     const bool tex = col_target != nullptr && w_tex != 0.f;
     if (tex) {
@@ -117,13 +187,36 @@ int findb200_train_step(const findb200_field_params* p, const float* template_po
         FB_CUDA(cudaGetLastError());
     }
     FB_MARK("combine_loss", st);
-    combine_loss_kernel<<<1, 32, 0, st>>>(chamf, tex ? mse_sum : nullptr, (double)n, w_chamf, tex ? w_tex : 0.f, loss3);
+    combine_loss_kernel<<<1, 32, 0, st>>>(chamf, tex ? mse_sum : nullptr, (double)n, w_chamf, tex ? w_tex : 0.f, smooth2,
+                                          smooth ? mt->w_smooth : 0.f, loss3, mt ? mt->loss_extra : nullptr);
     FB_CUDA(cudaGetLastError());
     return findb200_field_backward(p, template_pos, 1, z_shape, z_pose, z_tex, reg, nfeet, V, disp, col, nullptr,
                                    tex ? grad_col : nullptr, grad_verts, gw, gz_shape, gz_pose, gz_tex, greg,
                                    ws + c.field, c.field_bytes, stream);
 }
 
+extern "C" {
+
+int findb200_train_step(const findb200_field_params* p, const float* template_pos, const float* z_shape,
+                        const float* z_pose, const float* z_tex, const float* reg, const float* target,
+                        const int64_t* target_len, const float* col_target, int nfeet, int V, int P2, float w_chamf,
+                        float w_tex, float* loss3, float* disp, float* col, float* verts,
+                        const findb200_field_grads* gw, float* gz_shape, float* gz_pose, float* gz_tex, float* greg,
+                        void* workspace, size_t workspace_bytes, void* stream) {
+    return run_step(p, template_pos, z_shape, z_pose, z_tex, reg, target, target_len, col_target, nfeet, V, P2, w_chamf, w_tex,
+                    loss3, disp, col, verts, gw, gz_shape, gz_pose, gz_tex, greg, nullptr, workspace, workspace_bytes, stream);
+}
+
+int findb200_train_step_mesh(const findb200_field_params* p, const float* template_pos, const float* z_shape,
+                             const float* z_pose, const float* z_tex, const float* reg, const float* target,
+                             const int64_t* target_len, const float* col_target, int nfeet, int V, int P2, float w_chamf,
+                             float w_tex, float* loss3, float* disp, float* col, float* verts,
+                             const findb200_field_grads* gw, float* gz_shape, float* gz_pose, float* gz_tex, float* greg,
+                             const findb200_mesh_terms* mesh_terms, void* workspace, size_t workspace_bytes, void* stream) {
+    FB_REQUIRE(mesh_terms, FINDB200_ERR_ARG, "train_step_mesh: mesh_terms is null");
+    return run_step(p, template_pos, z_shape, z_pose, z_tex, reg, target, target_len, col_target, nfeet, V, P2, w_chamf, w_tex,
+                    loss3, disp, col, verts, gw, gz_shape, gz_pose, gz_tex, greg, mesh_terms, workspace, workspace_bytes, stream);
+}
 
 int findb200_train_step_knn_stats(const void* workspace, int nfeet, int V, int P2, unsigned long long* out4_host,
                                   void* stream) {

@@ -167,7 +167,7 @@ class _SamplePoints(torch.autograd.Function):
         with torch.cuda.device(dev):
             rc = lib.findb200_sample_points_forward(
                 _lib.ptr(vc), int(verts_shared), _lib.ptr(faces_i32), int(faces_shared), _lib.ptr(num_faces), N, V, F, S,
-                seed, _lib.ptr(face_idx_in), _lib.ptr(uv_in), _lib.ptr(samples), _lib.ptr(fidx), _lib.ptr(bary), _lib.ptr(ac),
+                seed, None, _lib.ptr(face_idx_in), _lib.ptr(uv_in), _lib.ptr(samples), _lib.ptr(fidx), _lib.ptr(bary), _lib.ptr(ac),
                 int(attr_shared), C, _lib.ptr(attr_out), _lib.ptr(ws), ws.numel() if ws is not None else 0, _lib.stream_ptr(dev))
         _lib.check(rc, "findb200_sample_points_forward")
         ctx.save_for_backward(faces_i32, fidx, bary)

@@ -22,11 +22,25 @@ from .field import NeuralDisplacementField
 from .field_ops import FieldGradsC, N_PARAMS, _make_params
 from .losses import CHAMF_WEIGHT, TEX_WEIGHT
 
+SMOOTH_WEIGHT = 1000.0   # opts.py:97 (--weight_smooth default)
+
+
+class MeshTermsC(ctypes.Structure):             # findb200_mesh_terms (include/find_b200.h)
+    _fields_ = [("faces", ctypes.c_void_p), ("F", ctypes.c_int), ("edges", ctypes.c_void_p), ("E", ctypes.c_int),
+                ("vf_ptr", ctypes.c_void_p), ("vf_face", ctypes.c_void_p), ("vf_corner", ctypes.c_void_p), ("nnz", ctypes.c_int),
+                ("num_samples", ctypes.c_int), ("seed", ctypes.c_ulonglong), ("draw_counter", ctypes.c_void_p),
+                ("w_smooth", ctypes.c_float), ("loss_extra", ctypes.c_void_p)]
+
 
 class TrainStep:
     def __init__(self, model: NeuralDisplacementField, nfeet: int, P2: int, with_colour: bool = True,
                  frozen_mlp: bool = False, is_train: bool = True, weight_chamf: float = CHAMF_WEIGHT,
-                 weight_tex: float = TEX_WEIGHT, use_graph: bool = True):
+                 weight_tex: float = TEX_WEIGHT, use_graph: bool = True, num_samples: Optional[int] = None,
+                 weight_smooth: float = 0.0, seed: int = 0):
+        """``num_samples``: Chamfer on that many surface samples of the deformed template (losses.py:67; None = on the
+        vertices, BASELINE.json's configuration).  ``weight_smooth``: weight of MeshSmoothnessLoss (opts.py:97 default
+        1000 when --smooth_loss is on, cfgs/train_3d.yaml:21; 0 = off).  ``seed``: key of the sample draw; a device
+        counter advances the draw every step, also under graph replay."""
         self.lib = _lib.load()
         self.model = model
         dev = model.template_verts.device
@@ -56,7 +70,27 @@ class TrainStep:
         for p in self.mlp_params:
             self.grad_views.append(self.flat_grad[off:off + p.numel()].view_as(p))
             off += p.numel()
-        nbytes = int(self.lib.findb200_train_step_workspace_bytes(B, V, self.P2))
+        self.S = int(num_samples) if num_samples else 0
+        self.w_smooth = float(weight_smooth)
+        self.mesh_terms = None
+        if self.S > 0 or self.w_smooth != 0.0:
+            from .mesh import MeshTopology
+            faces = model.template_faces.reshape(-1, 3)
+            if faces.shape[0] < 2:
+                raise RuntimeError("surface sampling / smoothness need the template faces (model.set_template(verts, faces))")
+            self.topo = MeshTopology(faces.to(dev), V)
+            self.draw_counter = torch.zeros(1, dtype=torch.int64, device=dev)
+            self.loss_extra = torch.zeros(2, **f32)
+            t, mt = self.topo, MeshTermsC()
+            mt.faces, mt.F, mt.edges, mt.E = t.faces.data_ptr(), t.F, t.edges.data_ptr(), t.E
+            mt.vf_ptr, mt.vf_face, mt.vf_corner, mt.nnz = t.vf_ptr.data_ptr(), t.vf_face.data_ptr(), t.vf_corner.data_ptr(), t.nnz
+            mt.num_samples, mt.seed, mt.draw_counter = self.S, int(seed) & (2 ** 64 - 1), self.draw_counter.data_ptr()
+            mt.w_smooth, mt.loss_extra = self.w_smooth, self.loss_extra.data_ptr()
+            self.mesh_terms = mt
+            nbytes = int(self.lib.findb200_train_step_mesh_workspace_bytes(B, V, self.P2, self.S,
+                                                                           t.nnz if self.w_smooth != 0.0 else 0, t.F))
+        else:
+            nbytes = int(self.lib.findb200_train_step_workspace_bytes(B, V, self.P2))
         self.ws = torch.empty(nbytes, dtype=torch.uint8, device=dev)
         self.kernel_launches = 0         # filled by the first enqueue (counted from the C ABI's launch list)
         self.graph: Optional[torch.cuda.CUDAGraph] = None
@@ -96,15 +130,18 @@ class TrainStep:
                                           _lib.ptr(self.rows[k]), st)
             _lib.check(rc, "findb200_gather_rows")
         r, g = self.rows, self.grows
-        rc = lib.findb200_train_step(
-            ctypes.byref(self._cparams), _lib.ptr(self.model.template_verts), _lib.ptr(r.get("shapevec")),
-            _lib.ptr(r.get("posevec")), _lib.ptr(r.get("texvec")), _lib.ptr(r.get("reg")), _lib.ptr(self.target), None,
-            _lib.ptr(self.col_target), self.B, self.V, self.P2, self.w_chamf, self.w_tex if self.with_colour else 0.0,
-            _lib.ptr(self.loss3), _lib.ptr(self.disp), _lib.ptr(self.col), _lib.ptr(self.verts),
-            ctypes.byref(self._cgrads) if self._cgrads is not None else None, _lib.ptr(g.get("shapevec")),
-            _lib.ptr(g.get("posevec")), _lib.ptr(g.get("texvec")), _lib.ptr(g.get("reg")), _lib.ptr(self.ws),
-            self.ws.numel(), st)
-        _lib.check(rc, "findb200_train_step")
+        args = (ctypes.byref(self._cparams), _lib.ptr(self.model.template_verts), _lib.ptr(r.get("shapevec")),
+                _lib.ptr(r.get("posevec")), _lib.ptr(r.get("texvec")), _lib.ptr(r.get("reg")), _lib.ptr(self.target), None,
+                _lib.ptr(self.col_target), self.B, self.V, self.P2, self.w_chamf, self.w_tex if self.with_colour else 0.0,
+                _lib.ptr(self.loss3), _lib.ptr(self.disp), _lib.ptr(self.col), _lib.ptr(self.verts),
+                ctypes.byref(self._cgrads) if self._cgrads is not None else None, _lib.ptr(g.get("shapevec")),
+                _lib.ptr(g.get("posevec")), _lib.ptr(g.get("texvec")), _lib.ptr(g.get("reg")))
+        if self.mesh_terms is None:
+            rc = lib.findb200_train_step(*args, _lib.ptr(self.ws), self.ws.numel(), st)
+            _lib.check(rc, "findb200_train_step")
+        else:
+            rc = lib.findb200_train_step_mesh(*args, ctypes.byref(self.mesh_terms), _lib.ptr(self.ws), self.ws.numel(), st)
+            _lib.check(rc, "findb200_train_step_mesh")
 
     def run(self) -> torch.Tensor:
         """Enqueue one step on the current stream (graph replay after the first call) -> loss3 (device)."""

@@ -140,14 +140,15 @@ int findb200_train_step(const findb200_field_params* p, const float* template_po
 /* pytorch3d.ops.sample_points_from_meshes(meshes, num_samples, return_textures)  — src/model/losses.py:39,63,67,
  * src/eval/eval_3d.py:149-150.  verts [N,V,3] (verts_shared: one [V,3] array for all meshes), faces [N,F,3] or shared
  * [F,3]; num_faces [N] int64 valid faces per mesh (NULL = F).  The draw: Philox4x32-10 keyed by `seed` over an integer
- * area CDF (see csrc/mesh.cu); pass face_idx_in [N,S] (mesh-local) and uv_in [2,N,S] (PyTorch3D's
+ * area CDF (see csrc/mesh.cu), counter words 2-3 = *draw_counter (device uint64, NULL = 0: lets a captured graph draw
+ * fresh samples per replay); pass face_idx_in [N,S] (mesh-local) and uv_in [2,N,S] (PyTorch3D's
  * _rand_barycentric_coords layout) to inject a draw instead.  Outputs: samples [N,S,3]; face_idx [N,S] and bary [N,S,3]
  * (optional, needed by the backward); attr_out [N,S,C] = barycentric interpolation of vert_attr [N,V,C] (optional:
  * TexturesVertex colours for return_textures=True).  Workspace only needed when the draw is made here. */
 size_t findb200_sample_workspace_bytes(int N, int F);
 int findb200_sample_points_forward(const float* verts, int verts_shared, const int32_t* faces, int faces_shared,
                                    const int64_t* num_faces, int N, int V, int F, int S, unsigned long long seed,
-                                   const int64_t* face_idx_in, const float* uv_in, float* samples, int64_t* face_idx,
+                                   const unsigned long long* draw_counter, const int64_t* face_idx_in, const float* uv_in, float* samples, int64_t* face_idx,
                                    float* bary, const float* vert_attr, int attr_shared, int C, float* attr_out,
                                    void* workspace, size_t workspace_bytes, void* stream);
 /* autograd of the interpolation: grad_verts[n, faces[f][k]] += bary[k] * grad_scale * grad_samples[n,s]
@@ -185,6 +186,34 @@ int findb200_adam_step(const findb200_optim_tensor* tensors, int n_tensors, doub
                        double weight_decay, long long* step_dev, void* stream);
 int findb200_sgd_momentum_step(const findb200_optim_tensor* tensors, int n_tensors, double lr, double momentum, double weight_decay,
                                long long* step_dev, void* stream);
+
+/* The shipped 3-D configuration (cfgs/train_3d.yaml: chamf + smooth + tex) in one call: findb200_train_step plus
+ *   - Chamfer on num_samples area-weighted surface samples of the deformed template instead of its vertices
+ *     (DisplacementLoss, src/model/losses.py:67,88; 0 = on the vertices), gradient gathered back to the vertices;
+ *   - w_smooth * MeshSmoothnessLoss(deformed template) (src/model/model.py:1032-1033, losses.py:93-99; opts.py:97 default
+ *     weight 1000; 0 = off).
+ * The target cloud is given as points (the GT-mesh samples of losses.py:63 are drawn by findb200_sample_points_forward on
+ * the data side).  loss3[0] includes the smoothness term; loss_extra (optional) = {edge loss, laplacian loss}. */
+typedef struct findb200_mesh_terms {
+    const int32_t* faces; int F;               /* template topology (device, int32): faces [F,3]            */
+    const int32_t* edges; int E;               /* unique edges [E,2]                       (smoothness only) */
+    const int32_t* vf_ptr;                     /* [V+1] CSR of vertex -> (face, corner)    (smoothness only) */
+    const int32_t* vf_face;
+    const int32_t* vf_corner;
+    int nnz;
+    int num_samples;
+    unsigned long long seed;
+    unsigned long long* draw_counter;          /* device uint64, bumped after every draw (NULL: same draw every call) */
+    float w_smooth;
+    float* loss_extra;                         /* device [2] or NULL */
+} findb200_mesh_terms;
+size_t findb200_train_step_mesh_workspace_bytes(int nfeet, int V, int P2, int num_samples, int nnz, int F);
+int findb200_train_step_mesh(const findb200_field_params* p, const float* template_pos, const float* z_shape,
+                             const float* z_pose, const float* z_tex, const float* reg, const float* target,
+                             const int64_t* target_len, const float* col_target, int nfeet, int V, int P2, float w_chamf,
+                             float w_tex, float* loss3, float* disp, float* col, float* verts,
+                             const findb200_field_grads* gw, float* gz_shape, float* gz_pose, float* gz_tex, float* greg,
+                             const findb200_mesh_terms* mesh_terms, void* workspace, size_t workspace_bytes, void* stream);
 
 /* Kernel counters of the last findb200_train_step that used this workspace: same four numbers as findb200_knn_stats
  * ({pair evaluations executed, cross-chunk-tie queries, most chunk evaluations of one group, groups}); synchronises. */

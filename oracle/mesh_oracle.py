@@ -59,10 +59,11 @@ def area_cdf(area: np.ndarray) -> np.ndarray:
     return np.cumsum(q, dtype=np.uint64)
 
 
-def draw(cdf: np.ndarray, mesh: int, S: int, seed: int):
+def draw(cdf: np.ndarray, mesh: int, S: int, seed: int, counter: int = 0):
     """-> face [S] int64, u [S] f32, v [S] f32 for mesh index `mesh`."""
     s = np.arange(S, dtype=np.uint64)
-    r0, r1, r2, r3 = philox4x32_10(s, np.full(S, mesh, np.uint64), np.zeros(S, np.uint64), np.zeros(S, np.uint64),
+    r0, r1, r2, r3 = philox4x32_10(s, np.full(S, mesh, np.uint64), np.full(S, counter & 0xFFFFFFFF, np.uint64),
+                                   np.full(S, (counter >> 32) & 0xFFFFFFFF, np.uint64),
                                    seed & 0xFFFFFFFF, (seed >> 32) & 0xFFFFFFFF)
     total = int(cdf[-1])
     r64 = [(int(a) << 32) | int(b) for a, b in zip(r0, r1)]
@@ -89,7 +90,7 @@ def interpolate(values: np.ndarray, faces: np.ndarray, face: np.ndarray, w0, w1,
 
 
 def sample_points(verts: np.ndarray, faces, num_samples: int, seed: int = 0, face_idx=None, uv=None, num_faces=None,
-                  attr=None):
+                  attr=None, counter: int = 0):
     """verts [N,V,3]; faces [F,3] shared or [N,F,3]; -> dict(samples [N,S,3], face_idx [N,S], bary [N,S,3], attr [N,S,C])."""
     N = verts.shape[0]
     out = dict(samples=[], face_idx=[], bary=[], attr=[])
@@ -100,7 +101,7 @@ def sample_points(verts: np.ndarray, faces, num_samples: int, seed: int = 0, fac
             area = face_areas(verts[n], fc)
             if num_faces is not None:
                 area[int(num_faces[n]):] = 0
-            f_d, u_d, v_d = draw(area_cdf(area), n, num_samples, seed)
+            f_d, u_d, v_d = draw(area_cdf(area), n, num_samples, seed, counter)
         f = np.clip(np.asarray(face_idx[n]).astype(np.int64), 0, F - 1) if face_idx is not None else f_d
         u, v = (np.asarray(uv[0][n]), np.asarray(uv[1][n])) if uv is not None else (u_d, v_d)
         w0, w1, w2 = barycentric(u, v)

@@ -156,5 +156,64 @@ def test_displacement_loss_z_cutoff_variants_run_ragged():
     assert abs(float(cut) - ref2) <= 1e-6 * ref2
     both = L(None, {"verts": verts}, {"points": pts}, 0, z_cutoff=0.0)["loss"]
     assert torch.isfinite(both)
-    with pytest.raises(NotImplementedError):
-        L(None, {"verts": verts}, {"points": pts}, 0, num_samples=5000)
+
+
+@pytest.mark.parametrize("use_graph", [False, True])
+def test_train_step_mesh_terms_match_cpu_oracle(use_graph):
+    """The shipped 3-D configuration (cfgs/train_3d.yaml: chamf on surface samples + smooth + tex) through
+    findb200_train_step_mesh vs the CPU oracle of the same step.  The oracle makes its draw from the GPU's own vertices
+    (draw parity itself is bit-exact, tests/test_mesh_gpu.py); the second run checks that the device draw counter advanced."""
+    from find_b200 import synthetic as syn
+    from find_b200.step import TrainStep
+    B, V, P2, n_rows, S = 3, 642, 600, 5, 500
+    dev, model, p, tv, tables, idx, target, colt = _setup(B, V, P2, n_rows, seed=41)
+    _, tf = syn.make_template(V)
+    step = TrainStep(model, B, P2, with_colour=True, use_graph=use_graph, num_samples=S, weight_smooth=1000.0, seed=77)
+    step.load_inputs(idx, target, colt)
+    for it in range(2):
+        step.run()
+        torch.cuda.synchronize()
+        # the draw that produced the current outputs (the first graph-mode run() executes a warm-up enqueue and a replay)
+        counter = int(step.draw_counter.item()) - 1
+        assert counter == (it + 1 if use_graph else it)
+        ref = so.train_step(p, fo.fourier_B(), tv, tables, idx, target, colt, faces=tf.numpy(), num_samples=S, seed=77,
+                            counter=counter, w_smooth=1000.0, draw_from_verts=step.verts.cpu().numpy())
+        total, chamf, tex = step.loss3.tolist()
+        edge, lap = step.loss_extra.tolist()
+        assert abs(chamf - ref["chamf"]) <= 1e-3 * ref["chamf"], counter
+        assert abs(edge - ref["smooth_edge"]) <= 1e-3 * ref["smooth_edge"]
+        assert abs(lap - ref["smooth_lap"]) <= 1e-3 * ref["smooth_lap"]
+        assert abs(total - ref["loss"]) <= 1e-3 * ref["loss"]
+    model.zero_grad(set_to_none=True)
+    step.populate_grads()
+    torch.cuda.synchronize()
+    for k in ("shapevec", "posevec", "texvec", "reg"):
+        assert rel_l2(getattr(model, k).data.grad, ref["table_grads"][k]) < 5e-2, k
+    for name, prm in model.named_parameters():
+        if name in p:
+            assert rel_l2(prm.grad, ref["grads"][name]) < 5e-2, name
+
+
+def test_train_step_smooth_only_and_sampling_only():
+    from find_b200 import synthetic as syn
+    from find_b200.step import TrainStep
+    B, V, P2, n_rows = 2, 642, 500, 4
+    dev, model, p, tv, tables, idx, target, colt = _setup(B, V, P2, n_rows, seed=42)
+    _, tf = syn.make_template(V)
+    base = TrainStep(model, B, P2, with_colour=True, use_graph=False)
+    base.load_inputs(idx, target, colt); base.run()
+    sm = TrainStep(model, B, P2, with_colour=True, use_graph=False, weight_smooth=1000.0)
+    sm.load_inputs(idx, target, colt); sm.run()
+    torch.cuda.synchronize()
+    b, s = base.loss3.tolist(), sm.loss3.tolist()
+    e, l = sm.loss_extra.tolist()
+    assert s[1] == b[1] and s[2] == b[2]                       # same Chamfer / colour terms, bit for bit
+    assert abs(s[0] - (b[0] + 1000.0 * (0.1 * l + 10.0 * e))) <= 1e-5 * abs(s[0])
+    ref = so.train_step(p, fo.fourier_B(), tv, tables, idx, target, colt, faces=tf.numpy(), w_smooth=1000.0, forward_only=True)
+    assert abs(e - ref["smooth_edge"]) <= 1e-3 * ref["smooth_edge"] and abs(l - ref["smooth_lap"]) <= 1e-3 * ref["smooth_lap"]
+    sp = TrainStep(model, B, P2, with_colour=False, use_graph=False, num_samples=2000, seed=5)
+    sp.load_inputs(idx, target); sp.run()
+    torch.cuda.synchronize()
+    ref2 = so.train_step(p, fo.fourier_B(), tv, tables, idx, target, None, faces=tf.numpy(), num_samples=2000, seed=5,
+                         forward_only=True, draw_from_verts=sp.verts.cpu().numpy())
+    assert abs(sp.loss3[1].item() - ref2["chamf"]) <= 1e-3 * ref2["chamf"]
