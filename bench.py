@@ -382,9 +382,56 @@ def run_ours(args, wl, rank, world, local_rank):
         "wall_s_timed_region": t_wall,
         "clocks": clocks,
     }
+    if world == 1 and not wl["frozen"]:
+        out["shipped_3d_step"] = measure_shipped_step(model, step, wl, host, device, flush, min(args.steps, 50))
     if rank == 0 and world == 1 and not args.skip_cpu_baseline:
         out["cpu_baseline"] = cpu_baseline(wl, budget_s=args.cpu_budget)
     return out
+
+
+def measure_shipped_step(model, base_step, wl, host, device, flush, steps):
+    """Secondary figure (not the headline metric): the reference's shipped 3-D configuration (cfgs/train_3d.yaml: chamf on
+    5000 surface samples + smooth + tex) through findb200_train_step_mesh, followed by the optimiser updates of
+    train.py:161-168 (FusedAdam on the MLP and the latent tables, FusedSGD momentum on reg) — one full training iteration."""
+    from find_b200.optim import FusedAdam, FusedSGD
+    from find_b200.step import TrainStep
+    del base_step
+    step = TrainStep(model, wl["feet"], wl["P2"], with_colour=True, num_samples=5000, weight_smooth=1000.0, seed=1)
+    step.load_inputs(host["idx"], host["target"], host["col_target"])
+    tables = [t.data for t in step.tables.values() if t is not None]
+    lat = [model.shapevec.data, model.posevec.data, model.texvec.data]
+    opt_net = FusedAdam(step.mlp_params, lr=0.0)              # lr 0: the timed updates must not drift the benchmark weights
+    opt_lat = FusedAdam(lat, lr=0.0)
+    opt_reg = FusedSGD([model.reg.data], lr=0.0, momentum=0.9)
+
+    def iteration():
+        step.run()
+        for t in tables:
+            if t.grad is not None:
+                t.grad.zero_()
+        step.populate_grads()
+        opt_net.step(); opt_lat.step(); opt_reg.step()
+
+    for _ in range(3):
+        iteration()
+    torch.cuda.synchronize(device)
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
+    for a, b in ev:
+        flush.zero_()
+        a.record(); iteration(); b.record()
+    torch.cuda.synchronize(device)
+    ms = sorted(a.elapsed_time(b) for a, b in ev)[len(ev) // 2]
+    total, chamf, tex = step.loss3.tolist()
+    edge, lap = step.loss_extra.tolist()
+    for t in tables:
+        t.grad = None
+    for p_ in step.mlp_params:
+        p_.grad = None
+    return {"ms_per_iteration_median": ms, "vertices_per_s": wl["feet"] * wl["V"] / (ms * 1e-3),
+            "what": "findb200_train_step_mesh (Chamfer on 5000 surface samples/foot + 1000*MeshSmoothnessLoss + colour) + "
+                    "latent-grad scatter + FusedAdam(MLP) + FusedAdam(latents) + FusedSGD(reg); step is a graph replay, "
+                    "optimiser launches are eager",
+            "loss": {"total": total, "chamfer": chamf, "colour_mse": tex, "edge": edge, "laplacian": lap}}
 
 
 # ---------------------------------------------------------------------------------------------------------------

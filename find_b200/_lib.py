@@ -38,6 +38,7 @@ SIGNATURES = {
     "findb200_train_step_mesh_workspace_bytes": (c_size_t, [c_int] * 6),
     "findb200_train_step_mesh": (c_int, [c_void_p] * 9 + [c_int] * 3 + [c_float] * 2 + [c_void_p] * 11 + [c_size_t, c_void_p]),
     "findb200_gather_rows": (c_int, [c_void_p, c_int, c_int, c_void_p, c_int, c_void_p, c_void_p]),
+    "findb200_gather_rows_multi": (c_int, [c_void_p, c_int, c_void_p, c_int, c_void_p]),
     "findb200_scatter_add_rows": (c_int, [c_void_p, c_int, c_int, c_void_p, c_int, c_void_p, c_void_p]),
     "findb200_profile_enable": (c_int, [c_int]),
     "findb200_profile_read": (c_int, [c_char_p, c_size_t]),

@@ -7,6 +7,7 @@
 //             | HEAD_BWD | TRUNK_BWD | dw_kernel (all weight-gradient GEMMs in one launch) | reduce_dw | finish_small
 // With per-foot distinct points (TextureLossGTSpace call site, losses.py:50) the trunk runs per foot as well.
 #include "field.cuh"
+#include <cstdlib>
 #include "field_dw.cuh"
 #include <math.h>
 #include <string.h>
@@ -104,22 +105,25 @@ struct LatentBiasParams {
     int S, Pz, T, B;
     float* out;
 };
+// one warp per output row n: lanes stride over the latent columns (coalesced weight reads), shuffle-reduce
 __global__ void __launch_bounds__(256) latent_bias_kernel(const LatentBiasParams P) {
-    const int n = threadIdx.x, b = blockIdx.x, head = blockIdx.y;
-    float acc;
-    if (head == 0) {
-        const int ld = kW + P.S + P.Pz;
-        const float* w = P.Wd + (size_t)n * ld + kW;
-        acc = P.bd[n];
-        for (int j = 0; j < P.S; ++j) acc = fmaf(w[j], P.z_shape[(size_t)b * P.S + j], acc);
-        for (int j = 0; j < P.Pz; ++j) acc = fmaf(w[P.S + j], P.z_pose[(size_t)b * P.Pz + j], acc);
-    } else {
-        const int ld = kW + P.T;
-        const float* w = P.Wc + (size_t)n * ld + kW;
-        acc = P.bc[n];
-        for (int j = 0; j < P.T; ++j) acc = fmaf(w[j], P.z_tex[(size_t)b * P.T + j], acc);
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const int b = blockIdx.x, head = blockIdx.y;
+    for (int n = blockIdx.z * 8 + wid; n < kW; n += gridDim.z * 8) {
+        float acc = 0.f;
+        if (head == 0) {
+            const int L = P.S + P.Pz;
+            const float* w = P.Wd + (size_t)n * (kW + L) + kW;
+            for (int j = lane; j < L; j += 32)
+                acc = fmaf(w[j], j < P.S ? P.z_shape[(size_t)b * P.S + j] : P.z_pose[(size_t)b * P.Pz + (j - P.S)], acc);
+        } else {
+            const float* w = P.Wc + (size_t)n * (kW + P.T) + kW;
+            for (int j = lane; j < P.T; j += 32) acc = fmaf(w[j], P.z_tex[(size_t)b * P.T + j], acc);
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+        if (lane == 0) P.out[((size_t)head * P.B + b) * kW + n] = acc + (head ? P.bc[n] : P.bd[n]);
     }
-    P.out[((size_t)head * P.B + b) * kW + n] = acc;
 }
 
 __device__ __forceinline__ void euler_xyz_d(const float* e, float (&R)[3][3]) {
@@ -323,7 +327,16 @@ __global__ void __launch_bounds__(256) finish_small_kernel(const __grid_constant
         float v = 0.f;
         if (P.heads_mask & (1 << head)) {
             const float* s = P.colsum + cs_foot(head, P.B) + (size_t)b * kW;
-            for (int n = 0; n < kW; ++n) v = fmaf(W[(size_t)n * ld + kW + jj], s[n], v);
+            float v0 = 0.f, v1 = 0.f, v2 = 0.f, v3 = 0.f;          // four chains: the 256 loads overlap instead of serialising
+            const float* Wj = W + kW + jj;
+#pragma unroll 4
+            for (int n = 0; n < kW; n += 4) {
+                v0 = fmaf(Wj[(size_t)n * ld], s[n], v0);
+                v1 = fmaf(Wj[(size_t)(n + 1) * ld], s[n + 1], v1);
+                v2 = fmaf(Wj[(size_t)(n + 2) * ld], s[n + 2], v2);
+                v3 = fmaf(Wj[(size_t)(n + 3) * ld], s[n + 3], v3);
+            }
+            v = (v0 + v1) + (v2 + v3);
         }
         v *= inv;
         if (head) { if (P.gz_tex) P.gz_tex[(size_t)b * P.T + jj] = v; }
@@ -411,6 +424,9 @@ static Workspace carve(int B, int V, int shared, int for_backward) {
     w.tact = take((size_t)5 * w.trunk_tiles * kTileBytes);
     w.scal = take(1024);
     if (for_backward) {
+        // scal | regsums | colsum are adjacent: the backward zeroes them with ONE memset node
+        w.regsums = take((size_t)B * 12 * 4);
+        w.colsum = take(cs_total(B) * 4);
         w.enc = take((size_t)w.trunk_tiles * kEncTileBytes);
         w.hact = take((size_t)2 * 3 * head_tiles * kTileBytes);
         w.hdz = take((size_t)2 * 3 * head_tiles * kTileBytes);
@@ -420,8 +436,6 @@ static Workspace carve(int B, int V, int shared, int for_backward) {
         w.doimg = take((size_t)2 * head_tiles * kImgBytes);
         w.tdz = take((size_t)5 * w.trunk_tiles * kTileBytes);
         w.dovals = take((size_t)2 * B * V * 16);
-        w.regsums = take((size_t)B * 12 * 4);
-        w.colsum = take(cs_total(B) * 4);
         w.n_partials = kMaxDwCtas;
         w.partial = take((size_t)w.n_partials * kW * kW * 4);
     }
@@ -523,7 +537,7 @@ int findb200_field_forward(const findb200_field_params* p, const float* pos, int
     LatentBiasParams LB{p->weight[P_D1], p->bias[P_D1], p->weight[P_C1], p->bias[P_C1], z_shape, z_pose, z_tex,
                         p->shapevec_size, p->posevec_size, p->texvec_size, B, (float*)(ws + w.biasfoot)};
     FB_MARK("latent_bias", st);
-    latent_bias_kernel<<<dim3(B, 2), 256, 0, st>>>(LB);
+    latent_bias_kernel<<<dim3(B, 2, 8), 256, 0, st>>>(LB);
     FB_CUDA(cudaGetLastError());
 
     ChainParams C;
@@ -573,10 +587,10 @@ int findb200_field_backward(const findb200_field_params* p, const float* pos, in
 
     // scalars, per-foot sums, column sums, d(pre-tanh) images start from zero
     FB_MARK("bwd_memsets", st);
-    FB_CUDA(cudaMemsetAsync(ws + w.scal, 0, 1024, st));
-    FB_CUDA(cudaMemsetAsync(ws + w.regsums, 0, (size_t)B * 12 * 4, st));
-    FB_CUDA(cudaMemsetAsync(ws + w.colsum, 0, cs_total(B) * 4, st));
-    FB_CUDA(cudaMemsetAsync(ws + w.doimg, 0, (size_t)2 * head_tiles * kImgBytes, st));
+    // one memset: global max | per-foot reg sums | column sums (adjacent in the workspace).  The d(pre-tanh) images need no
+    // clearing: head_bwd rewrites columns 0..15 of every row each step, and whatever sits in columns 16..63 only reaches
+    // rows >= 16 of the 256 -> 3 layers' dW partial, which reduce_dw never reads (J.rows = 3).
+    FB_CUDA(cudaMemsetAsync(ws + w.scal, 0, (w.colsum - w.scal) + cs_total(B) * 4, st));
 
     GradPrepParams GP{pos, disp, col, reg, p->avg_col, grad_disp, grad_col, grad_verts, B, V, pos_shared,
                       (float*)(ws + w.dovals), (uint32_t*)(ws + w.scal), (float*)(ws + w.regsums)};
@@ -664,24 +678,38 @@ int findb200_field_backward(const findb200_field_params* p, const float* pos, in
                 w.trunk_feet, w.tpf2, w.tpf2, kb == 0 ? colsum + cs_trunk(0, B) : nullptr, kb == 0 ? 1 : 0, 256, P_T0, kb);
     }
     D.n_gemms = ng;
-    // CTA allocation proportional to cost, every GEMM at least one, at most kMaxDwCtas in total
-    long long total_cost = 0;
-    for (int i = 0; i < ng; ++i) total_cost += cost[i];
+    // CTA allocation: the launch is HBM-bound (profiles/r1_math_kernels_ncu_full.md), so the cost of a GEMM is the bytes it
+    // streams; one CTA per SM, every GEMM at least one, then each further CTA goes to the GEMM whose CTAs carry the most
+    // bytes (greedy min-max), so that all CTAs finish together.
+    long long bytes[kMaxDwGemms];
+    // operands that were written by the kernels just before this one (the trunk's activations / dZ, 5 MB each) or that are
+    // re-read by every foot (the shared trunk output h5) mostly hit the 126 MB L2: they cost a fraction of an HBM byte
+    static float l2w = -1.f;
+    if (l2w < 0.f) { const char* e = getenv("FINDB200_DW_L2W"); l2w = e ? (float)atof(e) : 0.6f; }
+    for (int i = 0; i < ng; ++i) {
+        const DwGemm& g = D.g[i];
+        const bool trunk = g.feet == w.trunk_feet && g.A >= ws + w.tdz && g.A < ws + w.tdz + (size_t)5 * w.trunk_tiles * kTileBytes;
+        const float fa = trunk ? l2w : 1.f;
+        const float fb = (trunk || (g.b_foot_stride == 0 && g.feet > 1)) ? l2w : 1.f;
+        bytes[i] = (long long)((double)g.feet * g.tpf * ((double)g.a_imgs * fa + (double)g.b_imgs * fb) * kImgBytes);
+        if (bytes[i] < 1) bytes[i] = 1;
+    }
+    (void)cost;
     int budget = sms < kMaxDwCtas ? sms : kMaxDwCtas;
     int n_ctas = 0;
-    for (int i = 0; i < ng; ++i) {
-        int n = total_cost > 0 ? (int)((cost[i] * budget) / total_cost) : 1;
-        const int units = D.g[i].feet * D.g[i].tpf;
-        if (n > units) n = units;
-        if (n < 1) n = 1;
-        D.g[i].ncta = n;
-        n_ctas += n;
-    }
-    while (n_ctas > kMaxDwCtas) {            // cannot happen with budget <= kMaxDwCtas - ng, kept as a guard
-        int big = 0;
-        for (int i = 1; i < ng; ++i) if (D.g[i].ncta > D.g[big].ncta) big = i;
-        FB_REQUIRE(D.g[big].ncta > 1, FINDB200_ERR_UNSUPPORTED, "field_backward: too many weight-gradient GEMMs");
-        --D.g[big].ncta; --n_ctas;
+    for (int i = 0; i < ng; ++i) { D.g[i].ncta = 1; ++n_ctas; }
+    FB_REQUIRE(n_ctas <= kMaxDwCtas, FINDB200_ERR_UNSUPPORTED, "field_backward: too many weight-gradient GEMMs");
+    while (n_ctas < budget) {
+        int big = -1;
+        double worst = 0.0;
+        for (int i = 0; i < ng; ++i) {
+            const int units = D.g[i].feet * D.g[i].tpf;
+            if (D.g[i].ncta >= units) continue;
+            const double per = (double)bytes[i] / D.g[i].ncta;
+            if (per > worst) { worst = per; big = i; }
+        }
+        if (big < 0) break;
+        ++D.g[big].ncta; ++n_ctas;
     }
     int c0 = 0;
     for (int i = 0; i < ng; ++i) {

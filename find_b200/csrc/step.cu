@@ -244,7 +244,34 @@ __global__ void scatter_add_rows_kernel(float* __restrict__ grad_table, int widt
 }  // namespace step
 }  // namespace fb
 
+namespace fb {
+namespace step {
+struct GatherJobs { const float* table[8]; float* out[8]; int width[8]; };
+__global__ void gather_rows_multi_kernel(const GatherJobs J, const int64_t* __restrict__ idx) {
+    const int b = blockIdx.x, k = blockIdx.y;
+    const int width = J.width[k];
+    const float* src = J.table[k] + (size_t)idx[b] * width;
+    float* dst = J.out[k] + (size_t)b * width;
+    for (int j = threadIdx.x; j < width; j += blockDim.x) dst[j] = src[j];
+}
+}  // namespace step
+}  // namespace fb
+
 extern "C" {
+int findb200_gather_rows_multi(const findb200_gather_job* jobs, int n_jobs, const int64_t* idx, int B, void* stream) {
+    FB_REQUIRE(jobs && idx && n_jobs >= 1 && n_jobs <= 8 && B >= 1, FINDB200_ERR_ARG, "gather_rows_multi: bad argument (1..8 jobs)");
+    fb::step::GatherJobs J{};
+    for (int k = 0; k < n_jobs; ++k) {
+        FB_REQUIRE(jobs[k].table && jobs[k].out && jobs[k].width >= 1 && jobs[k].n_rows >= 1, FINDB200_ERR_ARG,
+                   "gather_rows_multi: job %d is incomplete", k);
+        J.table[k] = jobs[k].table; J.out[k] = jobs[k].out; J.width[k] = jobs[k].width;
+    }
+    FB_MARK("gather_rows", (cudaStream_t)stream);
+    fb::step::gather_rows_multi_kernel<<<dim3(B, n_jobs), 128, 0, (cudaStream_t)stream>>>(J, idx);
+    FB_CUDA(cudaGetLastError());
+    FB_MARK_END((cudaStream_t)stream);
+    return 0;
+}
 int findb200_gather_rows(const float* table, int n_rows, int width, const int64_t* idx, int B, float* out, void* stream) {
     FB_REQUIRE(table && idx && out && n_rows >= 1 && width >= 1 && B >= 1, FINDB200_ERR_ARG, "gather_rows: bad argument");
     FB_MARK("gather_rows", (cudaStream_t)stream);

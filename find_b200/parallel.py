@@ -74,14 +74,41 @@ class ShardedTrainStep:
         self.global_feet = int(global_feet)
         self.world = dist.get_world_size(group) if dist.is_initialized() else 1
         self.weight = step.B / float(self.global_feet)
+        self.graph: Optional[torch.cuda.CUDAGraph] = None
+
+    def _collective(self):
+        """weight * flat_grad summed over ranks, in place.  An even split is NCCL's AVG (one kernel, no pre-scale)."""
+        fg = self.step.flat_grad
+        if fg.is_cuda and abs(self.weight * self.world - 1.0) < 1e-12:
+            dist.all_reduce(fg, op=dist.ReduceOp.AVG, group=self.group)
+            return
+        if self.weight != 1.0:
+            fg.mul_(self.weight)
+        dist.all_reduce(fg, op=dist.ReduceOp.SUM, group=self.group)
 
     def run(self):
-        loss3 = self.step.run()
-        if self.world > 1 and not self.step.frozen:
-            if self.weight != 1.0:
-                self.step.flat_grad.mul_(self.weight)
-            allreduce_flat_grad(self.step.flat_grad, self.group)
-        return loss3
+        """One step of this rank's shard + the gradient allreduce.  With ``step.use_graph`` the kernels of the step AND
+        the NCCL allreduce are captured in ONE CUDA graph (a single replay per step: no host launch between the last
+        backward kernel and the collective)."""
+        step = self.step
+        if self.world == 1 or step.frozen:
+            return step.run()
+        if not step.use_graph:
+            step.run()
+            self._collective()
+            return step.loss3
+        with torch.cuda.device(step.dev):
+            if self.graph is None:
+                step._enqueue()                      # warm-up outside capture: function attributes, NCCL communicator
+                self._collective()
+                torch.cuda.synchronize(step.dev)
+                g = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(g):
+                    step._enqueue()
+                    self._collective()
+                self.graph = g
+            self.graph.replay()
+        return step.loss3
 
     def scale_local_grads(self):
         """Latent / reg row gradients are rank-local; scale them to the global mean as well."""

@@ -25,6 +25,10 @@ from .losses import CHAMF_WEIGHT, TEX_WEIGHT
 SMOOTH_WEIGHT = 1000.0   # opts.py:97 (--weight_smooth default)
 
 
+class GatherJobC(ctypes.Structure):             # findb200_gather_job (include/find_b200.h)
+    _fields_ = [("table", ctypes.c_void_p), ("n_rows", ctypes.c_int), ("width", ctypes.c_int), ("out", ctypes.c_void_p)]
+
+
 class MeshTermsC(ctypes.Structure):             # findb200_mesh_terms (include/find_b200.h)
     _fields_ = [("faces", ctypes.c_void_p), ("F", ctypes.c_int), ("edges", ctypes.c_void_p), ("E", ctypes.c_int),
                 ("vf_ptr", ctypes.c_void_p), ("vf_face", ctypes.c_void_p), ("vf_corner", ctypes.c_void_p), ("nnz", ctypes.c_int),
@@ -97,6 +101,7 @@ class TrainStep:
         self.use_graph = use_graph
         self._cparams = None
         self._cgrads = None
+        self._gather = None
 
     # ---- the enqueue ---------------------------------------------------------------------------------------
     def _structs(self):
@@ -123,12 +128,16 @@ class TrainStep:
         lib, st = self.lib, _lib.stream_ptr(self.dev)
         if self._cparams is None:
             self._cparams, self._cgrads = self._structs()
-        for k, t in self.tables.items():
-            if t is None:
-                continue
-            rc = lib.findb200_gather_rows(_lib.ptr(t.data), t.data.shape[0], t.data.shape[1], _lib.ptr(self.idx), self.B,
-                                          _lib.ptr(self.rows[k]), st)
-            _lib.check(rc, "findb200_gather_rows")
+        if self._gather is None:
+            live = [(k, t) for k, t in self.tables.items() if t is not None]
+            jobs = (GatherJobC * len(live))()
+            for j, (k, t) in enumerate(live):
+                jobs[j].table, jobs[j].n_rows, jobs[j].width = t.data.data_ptr(), t.data.shape[0], t.data.shape[1]
+                jobs[j].out = self.rows[k].data_ptr()
+            self._gather = (jobs, len(live))
+        if self._gather[1]:
+            rc = lib.findb200_gather_rows_multi(self._gather[0], self._gather[1], _lib.ptr(self.idx), self.B, st)
+            _lib.check(rc, "findb200_gather_rows_multi")
         r, g = self.rows, self.grows
         args = (ctypes.byref(self._cparams), _lib.ptr(self.model.template_verts), _lib.ptr(r.get("shapevec")),
                 _lib.ptr(r.get("posevec")), _lib.ptr(r.get("texvec")), _lib.ptr(r.get("reg")), _lib.ptr(self.target), None,

@@ -226,6 +226,10 @@ int findb200_train_step_knn_stats(const void* workspace, int nfeet, int V, int P
 int findb200_gather_rows(const float* table, int n_rows, int width, const int64_t* idx, int B, float* out, void* stream);
 int findb200_scatter_add_rows(float* grad_table, int n_rows, int width, const int64_t* idx, int B, const float* g,
                               void* stream);
+/* the same gather for up to 8 tables in one launch (shapevec / posevec / texvec / reg rows of a batch) */
+typedef struct findb200_gather_job { const float* table; int n_rows; int width; float* out; } findb200_gather_job;
+int findb200_gather_rows_multi(const findb200_gather_job* jobs, int n_jobs, const int64_t* idx, int B, void* stream);
+
 
 /* ------------------------------------------------------------------------------------------------------
  * Diagnostics: one-CTA tcgen05 self-test of the shared-memory image / descriptor / TMEM conventions used by
