@@ -528,13 +528,28 @@ def main():
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    rc = 0
     try:
         out = run_ours(args, wl, rank, world, local_rank)
         if rank == 0:
             print(json.dumps(out), flush=True)
-    finally:
-        if world > 1:
-            dist.destroy_process_group()
+    except BaseException:                       # noqa: BLE001 — report, then leave with a non-zero code
+        import traceback
+        traceback.print_exc()
+        rc = 1
+    if world > 1:
+        # leave without tearing NCCL down: the communicator is referenced by a live CUDA graph (the captured allreduce) and
+        # destroy_process_group() on such a communicator can block.  Everything is flushed and synchronised first.
+        try:
+            if rc == 0:
+                dist.barrier()
+                torch.cuda.synchronize()
+        finally:
+            sys.stdout.flush()
+            sys.stderr.flush()
+            os._exit(rc)
+    if rc:
+        sys.exit(rc)
 
 
 if __name__ == "__main__":

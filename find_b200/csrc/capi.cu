@@ -1,4 +1,5 @@
 // find_b200/csrc/capi.cu — error plumbing of the C ABI (include/find_b200.h).
+#include <cstdlib>
 #include "common.cuh"
 #include "../../include/find_b200.h"
 #include <cstdarg>
@@ -6,6 +7,13 @@
 #include <cstring>
 
 namespace fb {
+
+bool pdl_enabled() {
+    static int on = -1;
+    if (on < 0) { const char* e = getenv("FINDB200_PDL"); on = (e && e[0] == '0') ? 0 : 1; }
+    return on != 0;
+}
+
 
 static thread_local char g_err[512] = "";
 

@@ -52,6 +52,7 @@ struct KnnParams {
 
 __global__ void cloud_to_soa_kernel(const float* __restrict__ aos, const int64_t* __restrict__ lens, int P,
                                     int Ppad, float* __restrict__ soa) {
+    fb::pdl_wait_trigger();
     int n = blockIdx.y;
     int j = blockIdx.x * blockDim.x + threadIdx.x;
     if (j >= Ppad) return;
@@ -77,6 +78,7 @@ namespace fb {
 namespace chamfer {
 
 __global__ void __launch_bounds__(kThreads) knn_main_kernel(const KnnParams prm) {
+    fb::pdl_wait_trigger();
     __shared__ __align__(128) float s_t[kStages][3][kTile];
     __shared__ __align__(8) uint64_t s_full[kStages];
     __shared__ int s_item;
@@ -231,6 +233,7 @@ static inline int fin_blocks(int P) { return P > 0 ? (P + kFinSlice - 1) / kFinS
 
 // grid (ceil(maxPq/kFinSlice), N, ndir), block 256: unpack keys, write dists / idx, one partial sum per block.
 __global__ void __launch_bounds__(256) knn_finalize_kernel(const FinalizeParams prm) {
+    fb::pdl_wait_trigger();
     const FinalizeDir& D = prm.dir[blockIdx.z];
     const int n = blockIdx.y;
     const int nblk = (D.Pq + kFinSlice - 1) / kFinSlice;
@@ -270,6 +273,7 @@ __global__ void __launch_bounds__(256) knn_finalize_kernel(const FinalizeParams 
 // of the cloud's block partials.  One warp, lane = cloud (strided), fixed-order combination.
 __global__ void chamfer_reduce_kernel(const double* sx, const double* sy, const int64_t* lx, const int64_t* ly, int N,
                                       int P1, int P2, float* loss, float* loss_xy) {
+    fb::pdl_wait_trigger();
     const int lane = threadIdx.x;
     const int nb1 = (P1 + kFinSlice - 1) / kFinSlice, nb2 = (P2 + kFinSlice - 1) / kFinSlice;
     double cx = 0.0, cy = 0.0;
@@ -300,6 +304,7 @@ __global__ void knn_bwd_kernel(const float* __restrict__ p1, const float* __rest
                                const int64_t* __restrict__ len1, const int64_t* __restrict__ len2,
                                const int64_t* __restrict__ idx, const float* __restrict__ grad_dists, int P1, int P2,
                                float* __restrict__ grad_p1, float* __restrict__ grad_p2) {
+    fb::pdl_wait_trigger();
     const int n = blockIdx.y;
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= P1) return;
@@ -324,6 +329,7 @@ __global__ void chamfer_bwd_direct_kernel(const float* __restrict__ a, const flo
                                           const int64_t* __restrict__ len_a, const int64_t* __restrict__ len_b,
                                           const int64_t* __restrict__ idx_a, const float* __restrict__ grad_loss,
                                           float grad_scale, int N, int Pa, int Pb, float* __restrict__ grad_a) {
+    fb::pdl_wait_trigger();
     const int n = blockIdx.y;
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= Pa) return;
@@ -345,6 +351,7 @@ __global__ void chamfer_bwd_scatter_kernel(const float* __restrict__ a, const fl
                                            const int64_t* __restrict__ len_a, const int64_t* __restrict__ len_b,
                                            const int64_t* __restrict__ idx_a, const float* __restrict__ grad_loss,
                                            float grad_scale, int N, int Pa, int Pb, float* __restrict__ grad_b) {
+    fb::pdl_wait_trigger();
     const int n = blockIdx.y;
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     const int la = len_a ? (int)len_a[n] : Pa, lb = len_b ? (int)len_b[n] : Pb;
@@ -451,8 +458,8 @@ static int g_cull_kq = 0;   // 0 = heuristic
 static int run_knn_brute(const float* x, const float* y, const int64_t* lx, const int64_t* ly, int N, int P1, int P2,
                          bool both, Workspace& w, cudaStream_t st) {
     FB_MARK("chamfer_prep", st);
-    cloud_to_soa_kernel<<<dim3((w.P1p + 255) / 256, N), 256, 0, st>>>(x, lx, P1, w.P1p, w.soa_x);
-    cloud_to_soa_kernel<<<dim3((w.P2p + 255) / 256, N), 256, 0, st>>>(y, ly, P2, w.P2p, w.soa_y);
+    FB_CUDA(fb::launch_pdl(cloud_to_soa_kernel, dim3((w.P1p + 255) / 256, N), 256, 0, st, x, lx, P1, w.P1p, w.soa_x));
+    FB_CUDA(fb::launch_pdl(cloud_to_soa_kernel, dim3((w.P2p + 255) / 256, N), 256, 0, st, y, ly, P2, w.P2p, w.soa_y));
     const int sms = num_sms();
     KnnParams prm{};
     prm.N = N; prm.counter = w.counter; prm.ndir = both ? 2 : 1;
@@ -467,7 +474,7 @@ static int run_knn_brute(const float* x, const float* y, const int64_t* lx, cons
     int grid = sms * 4;
     if (grid > prm.total_items) grid = prm.total_items;
     FB_MARK("knn_main", st);
-    knn_main_kernel<<<grid, kThreads, 0, st>>>(prm);
+    FB_CUDA(fb::launch_pdl(knn_main_kernel, grid, kThreads, 0, st, prm));
     FB_CUDA(cudaGetLastError());
     return 0;
 }
@@ -482,7 +489,7 @@ static int launch_cull(CullParams& prm, int N, int P1, int P2, bool both, cudaSt
     const int cap = num_sms() * 8;
     if (grid > cap) grid = cap;
     FB_MARK("knn_main", st);
-    knn_cull_kernel<kQ><<<grid, 128, 0, st>>>(prm);
+    FB_CUDA(fb::launch_pdl(knn_cull_kernel<kQ>, grid, 128, 0, st, prm));
     FB_CUDA(cudaGetLastError());
     return 0;
 }
@@ -496,16 +503,16 @@ static int run_knn_cull(const float* x, const float* y, const int64_t* lx, const
                         P2, w.P2p, w.C2p, w.S2p, w.gl2};
     const int Pm = P1 > P2 ? P1 : P2, Ppm = w.P1p > w.P2p ? w.P1p : w.P2p;
     FB_MARK("sort_bbox", st);
-    cloud_bbox_kernel<<<dim3((Pm + 1023) / 1024, N, 2), 256, 0, st>>>(sp);
+    FB_CUDA(fb::launch_pdl(cloud_bbox_kernel, dim3((Pm + 1023) / 1024, N, 2), 256, 0, st, sp));
     FB_MARK("sort_hist", st);
-    cloud_hist_kernel<<<dim3((Pm + 255) / 256, N, 2), 256, 0, st>>>(sp);
+    FB_CUDA(fb::launch_pdl(cloud_hist_kernel, dim3((Pm + 255) / 256, N, 2), 256, 0, st, sp));
     FB_MARK("sort_scatter", st);
-    cloud_scan_kernel<<<dim3(N, 2), 1024, 0, st>>>(sp);
+    FB_CUDA(fb::launch_pdl(cloud_scan_kernel, dim3(N, 2), 1024, 0, st, sp));
     FB_MARK("sort_scatter2", st);
-    cloud_scatter_kernel<<<dim3((Ppm + 255) / 256, N, 2), 256, 0, st>>>(sp);
+    FB_CUDA(fb::launch_pdl(cloud_scatter_kernel, dim3((Ppm + 255) / 256, N, 2), 256, 0, st, sp));
     FB_MARK("sort_boxes", st);
-    cloud_boxes_kernel<<<dim3((Ppm / kCullChunk + 7) / 8, N, 2), 256, 0, st>>>(sp);
-    cloud_superboxes_kernel<<<dim3((Ppm / kCullChunk / 32 + 8) / 8, N, 2), 256, 0, st>>>(sp);
+    FB_CUDA(fb::launch_pdl(cloud_boxes_kernel, dim3((Ppm / kCullChunk + 7) / 8, N, 2), 256, 0, st, sp));
+    FB_CUDA(fb::launch_pdl(cloud_superboxes_kernel, dim3((Ppm / kCullChunk / 32 + 8) / 8, N, 2), 256, 0, st, sp));
     FB_CUDA(cudaGetLastError());
 
     CullParams prm{};
@@ -570,7 +577,7 @@ int findb200_knn1(const float* p1, const float* p2, const int64_t* len1, const i
     FinalizeParams fp{};
     fp.dir[0] = FinalizeDir{w.keys_x, len1, len2, dists, idx, nullptr, nullptr, P1, P2};
     FB_MARK("knn_finalize", st);
-    knn_finalize_kernel<<<dim3(fin_blocks(P1), N, 1), 256, 0, st>>>(fp);
+    FB_CUDA(fb::launch_pdl(knn_finalize_kernel, dim3(fin_blocks(P1), N, 1), 256, 0, st, fp));
     FB_CUDA(cudaGetLastError());
     FB_MARK_END(st);
     return 0;
@@ -585,8 +592,8 @@ int findb200_knn1_backward(const float* p1, const float* p2, const int64_t* len1
     if (P2 > 0) FB_CUDA(cudaMemsetAsync(grad_p2, 0, (size_t)N * P2 * 3 * sizeof(float), st));
     if (P1 > 0) {
         FB_MARK("knn_bwd", st);
-        knn_bwd_kernel<<<dim3((P1 + 255) / 256, N), 256, 0, st>>>(p1, p2, len1, len2, idx, grad_dists, P1, P2, grad_p1,
-                                                                  grad_p2);
+        FB_CUDA(fb::launch_pdl(knn_bwd_kernel, dim3((P1 + 255) / 256, N), 256, 0, st, p1, p2, len1, len2, idx, grad_dists, P1, P2, grad_p1,
+                                                                  grad_p2));
         FB_CUDA(cudaGetLastError());
     }
     return 0;
@@ -605,9 +612,9 @@ int findb200_chamfer_forward(const float* x, const float* y, const int64_t* x_le
     fp.dir[0] = FinalizeDir{w.keys_x, x_len, y_len, dist_x, idx_x, nullptr, w.sum_x, P1, P2};
     fp.dir[1] = FinalizeDir{w.keys_y, y_len, x_len, dist_y, idx_y, nullptr, w.sum_y, P2, P1};
     FB_MARK("knn_finalize", st);
-    knn_finalize_kernel<<<dim3(fin_blocks(P1 > P2 ? P1 : P2), N, 2), 256, 0, st>>>(fp);
+    FB_CUDA(fb::launch_pdl(knn_finalize_kernel, dim3(fin_blocks(P1 > P2 ? P1 : P2), N, 2), 256, 0, st, fp));
     FB_MARK("chamfer_reduce", st);
-    chamfer_reduce_kernel<<<1, 32, 0, st>>>(w.sum_x, w.sum_y, x_len, y_len, N, P1, P2, loss, nullptr);
+    FB_CUDA(fb::launch_pdl(chamfer_reduce_kernel, 1, 32, 0, st, w.sum_x, w.sum_y, x_len, y_len, N, P1, P2, loss, nullptr));
     FB_CUDA(cudaGetLastError());
     FB_MARK_END(st);
     return 0;
@@ -623,14 +630,14 @@ int findb200_chamfer_backward(const float* x, const float* y, const int64_t* x_l
     const dim3 g1((P1 + 255) / 256, N), g2((P2 + 255) / 256, N);
     FB_MARK("chamfer_bwd", st);
     if (P1 > 0)
-        chamfer_bwd_direct_kernel<<<g1, 256, 0, st>>>(x, y, x_len, y_len, idx_x, grad_loss, grad_scale, N, P1, P2, grad_x);
+        FB_CUDA(fb::launch_pdl(chamfer_bwd_direct_kernel, g1, 256, 0, st, x, y, x_len, y_len, idx_x, grad_loss, grad_scale, N, P1, P2, grad_x));
     if (grad_y && P2 > 0)
-        chamfer_bwd_direct_kernel<<<g2, 256, 0, st>>>(y, x, y_len, x_len, idx_y, grad_loss, grad_scale, N, P2, P1, grad_y);
+        FB_CUDA(fb::launch_pdl(chamfer_bwd_direct_kernel, g2, 256, 0, st, y, x, y_len, x_len, idx_y, grad_loss, grad_scale, N, P2, P1, grad_y));
     if (P1 > 0 && P2 > 0) {
         // y -> x scatter lands in grad_x; x -> y scatter lands in grad_y
-        chamfer_bwd_scatter_kernel<<<g2, 256, 0, st>>>(y, x, y_len, x_len, idx_y, grad_loss, grad_scale, N, P2, P1, grad_x);
+        FB_CUDA(fb::launch_pdl(chamfer_bwd_scatter_kernel, g2, 256, 0, st, y, x, y_len, x_len, idx_y, grad_loss, grad_scale, N, P2, P1, grad_x));
         if (grad_y)
-            chamfer_bwd_scatter_kernel<<<g1, 256, 0, st>>>(x, y, x_len, y_len, idx_x, grad_loss, grad_scale, N, P1, P2, grad_y);
+            FB_CUDA(fb::launch_pdl(chamfer_bwd_scatter_kernel, g1, 256, 0, st, x, y, x_len, y_len, idx_x, grad_loss, grad_scale, N, P1, P2, grad_y));
     }
     FB_CUDA(cudaGetLastError());
     FB_MARK_END(st);

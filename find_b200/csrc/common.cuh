@@ -32,6 +32,28 @@ void prof_mark(const char* name, cudaStream_t st);
 #define FB_MARK_END(st) fb::prof_mark(nullptr, (st))
 
 // ------------------------------------------------------------------------------------------------
+// Programmatic dependent launch: every kernel of the step starts with pdl_wait_trigger() and is launched through
+// launch_pdl(), so kernel N+1 is scheduled (launch latency, CTA ramp) while kernel N drains.  griddepcontrol.wait blocks
+// until the previous grid has COMPLETED and its memory is visible, so data hazards are exactly those of plain stream
+// order; launch_dependents comes after the wait, which keeps at most two kernels of the chain resident.
+FB_DEVINL void pdl_wait_trigger() {
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+}
+bool pdl_enabled();     // capi.cu: FINDB200_PDL=0 turns the launch attribute off (A/B measurement)
+template <typename... KP, typename... A>
+inline cudaError_t launch_pdl(void (*kernel)(KP...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, A&&... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = pdl_enabled() ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, kernel, static_cast<KP>(args)...);
+}
+
+// ------------------------------------------------------------------------------------------------
 FB_DEVINL uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
 FB_DEVINL bool elect_one() {

@@ -69,6 +69,7 @@ struct PackJob {
 struct PackParams { PackJob j[2 * P_COUNT]; int n; uint8_t* dst; };
 
 __global__ void __launch_bounds__(256) pack_weights_kernel(const __grid_constant__ PackParams P) {
+    fb::pdl_wait_trigger();
     const PackJob& J = P.j[blockIdx.y];
     const int per_chunk = J.img_rows * 8;
     const int total = per_chunk * J.n_chunks;
@@ -107,6 +108,7 @@ struct LatentBiasParams {
 };
 // one warp per output row n: lanes stride over the latent columns (coalesced weight reads), shuffle-reduce
 __global__ void __launch_bounds__(256) latent_bias_kernel(const LatentBiasParams P) {
+    fb::pdl_wait_trigger();
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     const int b = blockIdx.x, head = blockIdx.y;
     for (int n = blockIdx.z * 8 + wid; n < kW; n += gridDim.z * 8) {
@@ -146,6 +148,7 @@ struct GradPrepParams {
     float* regsums;      // [B][12]
 };
 __global__ void __launch_bounds__(256) grad_prep_kernel(const GradPrepParams P) {
+    fb::pdl_wait_trigger();
     const int b = blockIdx.y;
     const int v = blockIdx.x * blockDim.x + threadIdx.x;
     float sums[12];
@@ -238,9 +241,35 @@ constexpr int kMaxReduceJobs = 20;
 struct ReduceParams { ReduceJob j[kMaxReduceJobs]; int n; const uint32_t* maxabs; };
 
 __global__ void __launch_bounds__(256) reduce_dw_kernel(const __grid_constant__ ReduceParams P) {
+    fb::pdl_wait_trigger();
     const ReduceJob& J = P.j[blockIdx.y];
     if (!J.dst) return;
     const float inv = inv_grad_scale(*P.maxabs);
+    if ((J.cols & 3) == 0 && (J.src_col0 & 3) == 0) {
+        // four columns per thread: one 16-byte load per partial, all of them independent (the launch is a pure HBM read)
+        const int c4n = J.cols >> 2, total4 = J.rows * c4n;
+        for (int id = blockIdx.x * blockDim.x + threadIdx.x; id < total4; id += gridDim.x * blockDim.x) {
+            const int r = id / c4n, c = (id % c4n) << 2;
+            const float4* p = reinterpret_cast<const float4*>(J.partial + (size_t)r * kW + J.src_col0 + c);
+            float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll 8
+            for (int s = 0; s < J.ncta; ++s) {
+                const float4 v = __ldg(p + (size_t)s * (kW * kW / 4));
+                acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
+            }
+            const float a[4] = {acc.x, acc.y, acc.z, acc.w};
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+                int dc = J.dst_col0 + c + e;
+                if (J.perm_kbase >= 0) {
+                    dc = enc_ref_col(J.perm_kbase + c + e);
+                    if (dc < 0) continue;
+                }
+                J.dst[(size_t)r * J.dst_ld + dc] = a[e] * inv;
+            }
+        }
+        return;
+    }
     const int total = J.rows * J.cols;
     for (int id = blockIdx.x * blockDim.x + threadIdx.x; id < total; id += gridDim.x * blockDim.x) {
         const int r = id / J.cols, c = id % J.cols;
@@ -277,6 +306,7 @@ __host__ __device__ inline size_t cs_trunk(int l, int B) { return (size_t)2 * B 
 __host__ __device__ inline size_t cs_total(int B) { return (size_t)2 * B * kW + 4 * kW + 32 + 5 * kW; }
 
 __global__ void __launch_bounds__(256) finish_small_kernel(const __grid_constant__ FinishParams P) {
+    fb::pdl_wait_trigger();
     const float inv = inv_grad_scale(*P.maxabs);
     const int sec = blockIdx.y;
     const int id = blockIdx.x * blockDim.x + threadIdx.x;
@@ -315,22 +345,26 @@ __global__ void __launch_bounds__(256) finish_small_kernel(const __grid_constant
         }
         g[(size_t)n * (kW + L) + kW + j] = v * inv;
     } else if (sec == 3) {
-        // latent-code gradients: gz[b][j] = sum_n W1[n][256 + j] s_b[n]
+        // latent-code gradients: gz[b][j] = sum_n W1[n][256 + j] s_b[n].  A block owns 32 consecutive (b, j) pairs; its
+        // 8 warps split the 256 rows, so every thread issues 32 independent coalesced loads, then a shared-memory fold.
+        __shared__ float part[8][33];
         const int Ld = P.S + P.Pz, Lt = P.T;
         const int per = Ld + Lt;
-        if (per == 0 || id >= P.B * per) return;
-        const int b = id / per, j = id % per;
+        const int lane = threadIdx.x & 31, wq = threadIdx.x >> 5;
+        const int pid = blockIdx.x * 32 + lane;
+        const bool live = per > 0 && pid < P.B * per;
+        const int b = live ? pid / per : 0, j = live ? pid % per : 0;
         const int head = j >= Ld;
         const int jj = head ? j - Ld : j;
-        const float* W = head ? P.Wc : P.Wd;
-        const int ld = kW + (head ? Lt : Ld);
         float v = 0.f;
-        if (P.heads_mask & (1 << head)) {
-            const float* s = P.colsum + cs_foot(head, P.B) + (size_t)b * kW;
-            float v0 = 0.f, v1 = 0.f, v2 = 0.f, v3 = 0.f;          // four chains: the 256 loads overlap instead of serialising
-            const float* Wj = W + kW + jj;
-#pragma unroll 4
-            for (int n = 0; n < kW; n += 4) {
+        if (live && (P.heads_mask & (1 << head))) {
+            const float* W = head ? P.Wc : P.Wd;
+            const int ld = kW + (head ? Lt : Ld);
+            const float* s = P.colsum + cs_foot(head, P.B) + (size_t)b * kW + wq * 32;
+            const float* Wj = W + (size_t)(wq * 32) * ld + kW + jj;
+            float v0 = 0.f, v1 = 0.f, v2 = 0.f, v3 = 0.f;
+#pragma unroll
+            for (int n = 0; n < 32; n += 4) {
                 v0 = fmaf(Wj[(size_t)n * ld], s[n], v0);
                 v1 = fmaf(Wj[(size_t)(n + 1) * ld], s[n + 1], v1);
                 v2 = fmaf(Wj[(size_t)(n + 2) * ld], s[n + 2], v2);
@@ -338,10 +372,17 @@ __global__ void __launch_bounds__(256) finish_small_kernel(const __grid_constant
             }
             v = (v0 + v1) + (v2 + v3);
         }
-        v *= inv;
-        if (head) { if (P.gz_tex) P.gz_tex[(size_t)b * P.T + jj] = v; }
-        else if (jj < P.S) { if (P.gz_shape) P.gz_shape[(size_t)b * P.S + jj] = v; }
-        else { if (P.gz_pose) P.gz_pose[(size_t)b * P.Pz + (jj - P.S)] = v; }
+        part[wq][lane] = v;
+        __syncthreads();
+        if (wq == 0 && live) {
+            float t = 0.f;
+#pragma unroll
+            for (int q = 0; q < 8; ++q) t += part[q][lane];
+            t *= inv;
+            if (head) { if (P.gz_tex) P.gz_tex[(size_t)b * P.T + jj] = t; }
+            else if (jj < P.S) { if (P.gz_shape) P.gz_shape[(size_t)b * P.S + jj] = t; }
+            else { if (P.gz_pose) P.gz_pose[(size_t)b * P.Pz + (jj - P.S)] = t; }
+        }
     } else {
         // registration gradients (reg = [t(3), euler(3), S(3)], model.py:481-488); not scaled (fp32 path)
         if (!P.greg || id >= P.B) return;
@@ -379,6 +420,7 @@ __global__ void __launch_bounds__(256) finish_small_kernel(const __grid_constant
 // grid (trunk_tiles * 16, heads), block 256; one uint4 (8 halves) per thread.
 __global__ void __launch_bounds__(256) sum_feet_kernel(const uint8_t* __restrict__ hdz, uint8_t* __restrict__ hsum, int B,
                                                        int tpf2, int heads_mask) {
+    fb::pdl_wait_trigger();
     const int hd = (heads_mask == 2) ? 1 : blockIdx.y;
     const size_t j = (size_t)blockIdx.x * 256 + threadIdx.x;            // uint4 index inside [tpf2 tiles]
     const size_t per_foot = (size_t)tpf2 * (kTileBytes / 16);
@@ -497,7 +539,7 @@ static int run_pack(const findb200_field_params* p, const Workspace& w, uint8_t*
     }
     PP.n = n;
     FB_MARK("pack_weights", st);
-    pack_weights_kernel<<<dim3(36, n), 256, 0, st>>>(PP);
+    FB_CUDA(fb::launch_pdl(pack_weights_kernel, dim3(36, n), 256, 0, st, PP));
     FB_CUDA(cudaGetLastError());
     return 0;
 }
@@ -537,7 +579,7 @@ int findb200_field_forward(const findb200_field_params* p, const float* pos, int
     LatentBiasParams LB{p->weight[P_D1], p->bias[P_D1], p->weight[P_C1], p->bias[P_C1], z_shape, z_pose, z_tex,
                         p->shapevec_size, p->posevec_size, p->texvec_size, B, (float*)(ws + w.biasfoot)};
     FB_MARK("latent_bias", st);
-    latent_bias_kernel<<<dim3(B, 2, 8), 256, 0, st>>>(LB);
+    FB_CUDA(fb::launch_pdl(latent_bias_kernel, dim3(B, 2, 8), 256, 0, st, LB));
     FB_CUDA(cudaGetLastError());
 
     ChainParams C;
@@ -595,7 +637,7 @@ int findb200_field_backward(const findb200_field_params* p, const float* pos, in
     GradPrepParams GP{pos, disp, col, reg, p->avg_col, grad_disp, grad_col, grad_verts, B, V, pos_shared,
                       (float*)(ws + w.dovals), (uint32_t*)(ws + w.scal), (float*)(ws + w.regsums)};
     FB_MARK("grad_prep", st);
-    grad_prep_kernel<<<dim3(cdiv(V, 256), B), 256, 0, st>>>(GP);
+    FB_CUDA(fb::launch_pdl(grad_prep_kernel, dim3(cdiv(V, 256), B), 256, 0, st, GP));
     FB_CUDA(cudaGetLastError());
 
     ChainParams C;
@@ -631,8 +673,8 @@ int findb200_field_backward(const findb200_field_params* p, const float* pos, in
         rc = 0;
         if (pos_shared && B > 1) {
             FB_MARK("sum_feet", st);
-            sum_feet_kernel<<<dim3(w.tpf2 * (kTileBytes / 16) / 256, n_heads), 256, 0, st>>>(ws + w.hdz, ws + w.hsum, B, w.tpf2,
-                                                                                             heads_mask);
+            FB_CUDA(fb::launch_pdl(sum_feet_kernel, dim3(w.tpf2 * (kTileBytes / 16) / 256, n_heads), 256, 0, st, ws + w.hdz, ws + w.hsum, B, w.tpf2,
+                                                                                             heads_mask));
             FB_CUDA(cudaGetLastError());
             for (int hd = 0; hd < 2; ++hd) C.tsrc[hd] = ws + w.hsum + (size_t)hd * w.trunk_tiles * kTileBytes;
         } else {
@@ -748,7 +790,7 @@ int findb200_field_backward(const findb200_field_params* p, const float* pos, in
         }
         R.n = nj;
         FB_MARK("reduce_dw", st);
-        reduce_dw_kernel<<<dim3(64, nj), 256, 0, st>>>(R);
+        FB_CUDA(fb::launch_pdl(reduce_dw_kernel, dim3(64, nj), 256, 0, st, R));
         FB_CUDA(cudaGetLastError());
     }
 
@@ -765,10 +807,10 @@ int findb200_field_backward(const findb200_field_params* p, const float* pos, in
     int maxid = P_COUNT * kW;
     const int Lmax = (F.S + F.Pz > F.T ? F.S + F.Pz : F.T);
     if (kW * Lmax > maxid) maxid = kW * Lmax;
-    if (B * (F.S + F.Pz + F.T) > maxid) maxid = B * (F.S + F.Pz + F.T);
+    if (B * (F.S + F.Pz + F.T) * 8 > maxid) maxid = B * (F.S + F.Pz + F.T) * 8;     // section 3: 32 (b, j) pairs per block
     if (B > maxid) maxid = B;
     FB_MARK("finish_small", st);
-    finish_small_kernel<<<dim3(cdiv(maxid, 256), 5), 256, 0, st>>>(F);
+    FB_CUDA(fb::launch_pdl(finish_small_kernel, dim3(cdiv(maxid, 256), 5), 256, 0, st, F));
     FB_CUDA(cudaGetLastError());
     FB_MARK_END(st);
     return 0;

@@ -203,6 +203,7 @@ FB_DEVINL void euler_xyz(const float* e, float (&R)[3][3]) {
 
 template <int MODE, int NT>
 __global__ void __launch_bounds__(64 + 128 * NT, 1) chain_kernel(const __grid_constant__ ChainParams P) {
+    fb::pdl_wait_trigger();
     // dynamic shared memory only (no static __shared__), so the window starts 1024-aligned as SWIZZLE_128B needs:
     // [NT activation tiles 64 KB][weight ring 3 x 32 KB][NT x 256 fp32 bias of the layer in flight][mbarriers]
     extern __shared__ __align__(1024) uint8_t smem[];
@@ -539,7 +540,7 @@ static int launch_chain_t(const ChainParams& P, int sms, cudaStream_t st) {
     if (grid <= 0) return 0;
     static const char* const kNames[4] = {"trunk_fwd", "head_fwd", "head_bwd", "trunk_bwd"};
     FB_MARK(kNames[MODE], st);
-    chain_kernel<MODE, NT><<<grid, 64 + 128 * NT, smem, st>>>(P);
+    FB_CUDA(fb::launch_pdl(chain_kernel<MODE, NT>, grid, 64 + 128 * NT, smem, st, P));
     FB_CUDA(cudaGetLastError());
     return 0;
 }

@@ -18,6 +18,7 @@ constexpr int kDwStageBytes = 65536;   // A half-tile (<= 4 x 8 KB) | B half-til
 constexpr int kDwThreads = 192;        // warp 0 producer, warp 1 MMA, warps 2..5 column sums + final epilogue
 
 __global__ void __launch_bounds__(kDwThreads, 1) dw_kernel(const __grid_constant__ DwParams P) {
+    fb::pdl_wait_trigger();
     extern __shared__ uint8_t smem_raw[];
     uint8_t* ring = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
     __shared__ __align__(8) uint64_t bar_full[kDwStages], bar_empty[kDwStages], bar_done;
@@ -158,7 +159,7 @@ int launch_dw(const DwParams& P, int n_ctas, cudaStream_t st) {
         attr_set = true;
     }
     FB_MARK("dw_gemms", st);
-    dw_kernel<<<n_ctas, kDwThreads, smem, st>>>(P);
+    FB_CUDA(fb::launch_pdl(dw_kernel, n_ctas, kDwThreads, smem, st, P));
     FB_CUDA(cudaGetLastError());
     return 0;
 }

@@ -89,6 +89,7 @@ FB_DEVINL int set_len(const SortSet& S, int n) {
 
 // 1. bounding box per cloud.  grid (ceil(maxP/1024), N, 2), block 256, 4 points per thread.
 __global__ void __launch_bounds__(256) cloud_bbox_kernel(const SortParams prm) {
+    fb::pdl_wait_trigger();
     const SortSet& S = prm.set[blockIdx.z];
     const int n = blockIdx.y;
     const int len = set_len(S, n);
@@ -146,6 +147,7 @@ FB_DEVINL CloudGrid cloud_grid(const SortSet& S, int n) {
 
 // 2. cell + arrival rank of every point.  grid (ceil(maxP/256), N, 2), block 256.
 __global__ void __launch_bounds__(256) cloud_hist_kernel(const SortParams prm) {
+    fb::pdl_wait_trigger();
     const SortSet& S = prm.set[blockIdx.z];
     const int n = blockIdx.y;
     const int len = set_len(S, n);
@@ -164,6 +166,7 @@ __global__ void __launch_bounds__(256) cloud_hist_kernel(const SortParams prm) {
 // 3. in-place exclusive scan of every cloud's histogram.  grid (N, 2), block 1024: warp w owns the contiguous segment
 //    [w*seg, (w+1)*seg) and walks it in coalesced 32-entry rows.
 __global__ void __launch_bounds__(1024) cloud_scan_kernel(const SortParams prm) {
+    fb::pdl_wait_trigger();
     __shared__ int s_wsum[32];
     const SortSet& S = prm.set[blockIdx.y];
     if (S.P <= 0) return;
@@ -204,6 +207,7 @@ __global__ void __launch_bounds__(1024) cloud_scan_kernel(const SortParams prm) 
 
 // 4. scatter into curve order: pos = start[cell] + rank.  grid (ceil(maxPpad/256), N, 2), block 256.
 __global__ void __launch_bounds__(256) cloud_scatter_kernel(const SortParams prm) {
+    fb::pdl_wait_trigger();
     const SortSet& S = prm.set[blockIdx.z];
     const int n = blockIdx.y;
     const int len = set_len(S, n);
@@ -224,6 +228,7 @@ __global__ void __launch_bounds__(256) cloud_scatter_kernel(const SortParams prm
 
 // 5. bounding box of every 32-point chunk of the sorted cloud.  grid (ceil(maxC/8), N, 2), block 256 (warp per chunk).
 __global__ void __launch_bounds__(256) cloud_boxes_kernel(const SortParams prm) {
+    fb::pdl_wait_trigger();
     const SortSet& S = prm.set[blockIdx.z];
     const int n = blockIdx.y, lane = threadIdx.x & 31;
     const int len = set_len(S, n);
@@ -252,6 +257,7 @@ __global__ void __launch_bounds__(256) cloud_boxes_kernel(const SortParams prm) 
 
 // 6. bounding box of every super-chunk (32 chunks).  grid (ceil(maxS/8), N, 2), block 256 (warp per super-chunk).
 __global__ void __launch_bounds__(256) cloud_superboxes_kernel(const SortParams prm) {
+    fb::pdl_wait_trigger();
     const SortSet& S = prm.set[blockIdx.z];
     const int n = blockIdx.y, lane = threadIdx.x & 31;
     const int nchunk = (set_len(S, n) + kCullChunk - 1) / kCullChunk;
@@ -311,6 +317,7 @@ FB_DEVINL float lb_dist(float gx, float gy, float gz) { return __fmaf_rn(gz, gz,
 
 template <int kQ>
 __global__ void __launch_bounds__(128) knn_cull_kernel(const CullParams prm) {
+    fb::pdl_wait_trigger();
     __shared__ float4 s_stage[4][24];      // per warp: one target chunk (x row | y row | z row)
     const int lane = threadIdx.x & 31;
     float4* stage = s_stage[threadIdx.x >> 5];

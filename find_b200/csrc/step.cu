@@ -54,6 +54,7 @@ static Carve carve(int B, int V, int P2, int S = 0, int nnz = 0, int F = 0) {
 // grad_col = 2 w (col - target) / n ; per-block partial sums of (col - target)^2 -> one double atomic per block
 __global__ void __launch_bounds__(256) col_mse_kernel(const float* __restrict__ col, const float* __restrict__ tgt, size_t n,
                                                       float w_over_n, float* __restrict__ grad_col, double* sum) {
+    fb::pdl_wait_trigger();
     double acc = 0.0;
     for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
         const float d = col[i] - tgt[i];
@@ -72,6 +73,7 @@ __global__ void __launch_bounds__(256) col_mse_kernel(const float* __restrict__ 
 
 __global__ void combine_loss_kernel(const float* chamf, const double* mse_sum, double n, float w_chamf, float w_tex,
                                     const float* smooth2, float w_smooth, float* loss3, float* loss_extra) {
+    fb::pdl_wait_trigger();
     if (threadIdx.x || blockIdx.x) return;
     const float c = *chamf;
     const float t = mse_sum ? (float)(*mse_sum / n) : 0.f;
@@ -85,7 +87,7 @@ __global__ void combine_loss_kernel(const float* chamf, const double* mse_sum, d
     loss3[2] = t;
 }
 
-__global__ void bump_counter_kernel(unsigned long long* c) { *c += 1ull; }
+__global__ void bump_counter_kernel(unsigned long long* c) { fb::pdl_wait_trigger(); *c += 1ull; }
 
 }  // namespace step
 }  // namespace fb
@@ -149,7 +151,7 @@ static int run_step(const findb200_field_params* p, const float* template_pos, c
                                             c.sample_ws_bytes, stream);
         if (rc) return rc;
         if (mt->draw_counter) {
-            bump_counter_kernel<<<1, 1, 0, st>>>(mt->draw_counter);
+            FB_CUDA(fb::launch_pdl(bump_counter_kernel, 1, 1, 0, st, mt->draw_counter));
             FB_CUDA(cudaGetLastError());
         }
         rc = findb200_chamfer_forward(samples, target, nullptr, target_len, nfeet, S, P2, chamf, nullptr, idx_x, nullptr, idx_y,
@@ -183,12 +185,12 @@ static int run_step(const findb200_field_params* p, const float* template_pos, c
         FB_CUDA(cudaMemsetAsync(mse_sum, 0, 8, st));
         int blocks = (int)((n + 255) / 256);
         if (blocks > 1184) blocks = 1184;
-        col_mse_kernel<<<blocks, 256, 0, st>>>(col, col_target, n, w_tex / (float)n, grad_col, mse_sum);
+        FB_CUDA(fb::launch_pdl(col_mse_kernel, blocks, 256, 0, st, col, col_target, n, w_tex / (float)n, grad_col, mse_sum));
         FB_CUDA(cudaGetLastError());
     }
     FB_MARK("combine_loss", st);
-    combine_loss_kernel<<<1, 32, 0, st>>>(chamf, tex ? mse_sum : nullptr, (double)n, w_chamf, tex ? w_tex : 0.f, smooth2,
-                                          smooth ? mt->w_smooth : 0.f, loss3, mt ? mt->loss_extra : nullptr);
+    FB_CUDA(fb::launch_pdl(combine_loss_kernel, 1, 32, 0, st, chamf, tex ? mse_sum : nullptr, (double)n, w_chamf, tex ? w_tex : 0.f, smooth2,
+                                          smooth ? mt->w_smooth : 0.f, loss3, mt ? mt->loss_extra : nullptr));
     FB_CUDA(cudaGetLastError());
     return findb200_field_backward(p, template_pos, 1, z_shape, z_pose, z_tex, reg, nfeet, V, disp, col, nullptr,
                                    tex ? grad_col : nullptr, grad_verts, gw, gz_shape, gz_pose, gz_tex, greg,
@@ -231,12 +233,14 @@ namespace fb {
 namespace step {
 __global__ void gather_rows_kernel(const float* __restrict__ table, int width, const int64_t* __restrict__ idx, int B,
                                    float* __restrict__ out) {
+    fb::pdl_wait_trigger();
     const int b = blockIdx.x;
     const float* src = table + (size_t)idx[b] * width;
     for (int j = threadIdx.x; j < width; j += blockDim.x) out[(size_t)b * width + j] = src[j];
 }
 __global__ void scatter_add_rows_kernel(float* __restrict__ grad_table, int width, const int64_t* __restrict__ idx, int B,
                                         const float* __restrict__ g) {
+    fb::pdl_wait_trigger();
     const int b = blockIdx.x;
     float* dst = grad_table + (size_t)idx[b] * width;
     for (int j = threadIdx.x; j < width; j += blockDim.x) atomicAdd(dst + j, g[(size_t)b * width + j]);   // duplicates accumulate
@@ -248,6 +252,7 @@ namespace fb {
 namespace step {
 struct GatherJobs { const float* table[8]; float* out[8]; int width[8]; };
 __global__ void gather_rows_multi_kernel(const GatherJobs J, const int64_t* __restrict__ idx) {
+    fb::pdl_wait_trigger();
     const int b = blockIdx.x, k = blockIdx.y;
     const int width = J.width[k];
     const float* src = J.table[k] + (size_t)idx[b] * width;
@@ -267,7 +272,7 @@ int findb200_gather_rows_multi(const findb200_gather_job* jobs, int n_jobs, cons
         J.table[k] = jobs[k].table; J.out[k] = jobs[k].out; J.width[k] = jobs[k].width;
     }
     FB_MARK("gather_rows", (cudaStream_t)stream);
-    fb::step::gather_rows_multi_kernel<<<dim3(B, n_jobs), 128, 0, (cudaStream_t)stream>>>(J, idx);
+    FB_CUDA(fb::launch_pdl(fb::step::gather_rows_multi_kernel, dim3(B, n_jobs), 128, 0, (cudaStream_t)stream, J, idx));
     FB_CUDA(cudaGetLastError());
     FB_MARK_END((cudaStream_t)stream);
     return 0;
@@ -275,7 +280,7 @@ int findb200_gather_rows_multi(const findb200_gather_job* jobs, int n_jobs, cons
 int findb200_gather_rows(const float* table, int n_rows, int width, const int64_t* idx, int B, float* out, void* stream) {
     FB_REQUIRE(table && idx && out && n_rows >= 1 && width >= 1 && B >= 1, FINDB200_ERR_ARG, "gather_rows: bad argument");
     FB_MARK("gather_rows", (cudaStream_t)stream);
-    fb::step::gather_rows_kernel<<<B, 128, 0, (cudaStream_t)stream>>>(table, width, idx, B, out);
+    FB_CUDA(fb::launch_pdl(fb::step::gather_rows_kernel, B, 128, 0, (cudaStream_t)stream, table, width, idx, B, out));
     FB_CUDA(cudaGetLastError());
     FB_MARK_END((cudaStream_t)stream);
     return 0;
@@ -284,7 +289,7 @@ int findb200_scatter_add_rows(float* grad_table, int n_rows, int width, const in
                               void* stream) {
     FB_REQUIRE(grad_table && idx && g && n_rows >= 1 && width >= 1 && B >= 1, FINDB200_ERR_ARG, "scatter_add_rows: bad argument");
     FB_MARK("scatter_add_rows", (cudaStream_t)stream);
-    fb::step::scatter_add_rows_kernel<<<B, 128, 0, (cudaStream_t)stream>>>(grad_table, width, idx, B, g);
+    FB_CUDA(fb::launch_pdl(fb::step::scatter_add_rows_kernel, B, 128, 0, (cudaStream_t)stream, grad_table, width, idx, B, g));
     FB_CUDA(cudaGetLastError());
     FB_MARK_END((cudaStream_t)stream);
     return 0;
