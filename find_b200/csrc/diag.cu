@@ -91,3 +91,11 @@ extern "C" int findb200_l2_stream(const void* src, size_t region_bytes, int chun
     FB_CUDA(cudaGetLastError());
     return 0;
 }
+
+// Diagnostics: dev_buf (>= 256 x u64, zeroed by the caller) receives %globaltimer stamps of CTA 0's first head_fwd item
+// (slots: field_chain.cu dbg_stamp call sites); NULL turns the trace off.
+namespace fb { namespace field { extern unsigned long long* g_chain_dbg; } }
+extern "C" int findb200_chain_trace(void* dev_buf) {
+    fb::field::g_chain_dbg = (unsigned long long*)dev_buf;
+    return 0;
+}

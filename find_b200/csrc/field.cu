@@ -515,6 +515,7 @@ static void fill_chain_common(ChainParams& C, const findb200_field_params* p, co
     C.avg_col = p->avg_col;
     C.dovals = (const float*)(ws + w.dovals);
     C.maxabs = (const uint32_t*)(ws + w.scal);
+    C.dbg = g_chain_dbg;
 }
 
 static int run_pack(const findb200_field_params* p, const Workspace& w, uint8_t* ws, cudaStream_t st) {

@@ -18,6 +18,16 @@
 namespace fb {
 namespace field {
 
+unsigned long long* g_chain_dbg = nullptr;
+
+FB_DEVINL void dbg_stamp(const ChainParams& P, bool first, int slot) {
+    if (P.dbg && first && blockIdx.x == 0) {
+        unsigned long long t;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+        P.dbg[slot] = t;
+    }
+}
+
 FB_DEVINL void named_bar_sync(int id, int count) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(count) : "memory"); }
 
 // power-of-two gradient scale that puts max |d(pre-tanh)| into [8, 16): fp16 operands keep full precision
@@ -42,23 +52,57 @@ FB_DEVINL void produce_gemm(const ChainParams& P, const GemmW& g, uint8_t* ring,
         if (use > 0) mbar_wait(&bar_empty[s], (use - 1) & 1);
         mbar_expect_tx(&bar_full[s], g.chunk_bytes);
         bulk_g2s(ring + s * kWChunkBytes, P.wpack + g.off + (size_t)c * g.chunk_bytes, g.chunk_bytes, &bar_full[s]);
+        dbg_stamp(P, pcount < 32, 64 + (int)pcount);
         ++pcount;
     }
 }
 
 // ---- MMA issuer: D[tile] (+)= A[tile](smem images) * W(ring) for chunks [c0, c1) ------------------------------
 FB_DEVINL void mma_gemm(const GemmW& g, uint32_t act_s, uint32_t ring_s, uint32_t tmem, uint64_t* bar_full,
-                        uint64_t* bar_empty, uint32_t& ccount, int c0, int c1, bool acc_init) {
+                        uint64_t* bar_empty, uint32_t& ccount, int c0, int c1, bool acc_init, const ChainParams* dbgP = nullptr) {
     const uint32_t idesc = umma_idesc_f16(128, g.N, false, false);
     for (int c = c0; c < c1; ++c) {
         const uint32_t s = ccount % kRing, use = ccount / kRing;
         mbar_wait(&bar_full[s], use & 1);
         tc_fence_after();
+        if (dbgP) dbg_stamp(*dbgP, ccount < 32, 96 + (int)ccount);
         const int nk = (c == g.n_chunks - 1) ? g.k16_last : 4;
         for (int k = 0; k < nk; ++k) {
             const uint64_t ad = umma_desc(act_s + (c - c0) * kImgBytes + k * 32, 16, 1024);
             const uint64_t bd = umma_desc(ring_s + s * kWChunkBytes + k * 32, 16, 1024);
             umma_f16(tmem, ad, bd, idesc, (acc_init || c > c0 || k > 0) ? 1u : 0u);
+        }
+        umma_commit(&bar_empty[s]);
+        ++ccount;
+    }
+}
+
+// ---- two tiles, ONE pass over the weight chunks: every chunk that lands in the ring feeds both tiles' accumulators ------
+// The chain kernels are bound by the arrival rate of weight chunks (one 32 KB chunk per ~0.5 us per SM with 3 ring slots
+// and ~0.8 us L2 latency, measured with findb200_chain_trace), not by the tensor pipe (0.28 us of MMA per chunk and tile),
+// so halving the number of chunks per layer matters more than overlapping one tile's epilogue with the other tile's MMAs.
+// Measured (tools/chain_trace.py, profiles/r1_chain_trace.md): sharing is SLOWER than the per-tile ping-pong (head_fwd 110 -> 128 us):
+// a slot is held for two tiles' MMAs, so chunks arrive every 0.75-0.9 us instead of 0.5 us and the two epilogues no longer
+// hide behind the other tile's MMAs.  Kept behind kShareChunks = false as the record of that experiment.
+constexpr bool kShareChunks = false;
+template <typename WaitT1>
+FB_DEVINL void mma_gemm2(const GemmW& g, uint32_t act_s, uint32_t ring_s, uint32_t tmem, uint64_t* bar_full, uint64_t* bar_empty,
+                         uint32_t& ccount, WaitT1&& wait_tile1, const ChainParams* dbgP = nullptr) {
+    const uint32_t idesc = umma_idesc_f16(128, g.N, false, false);
+    for (int c = 0; c < g.n_chunks; ++c) {
+        const uint32_t s = ccount % kRing, use = ccount / kRing;
+        mbar_wait(&bar_full[s], use & 1);
+        tc_fence_after();
+        if (dbgP) dbg_stamp(*dbgP, ccount < 32, 96 + (int)ccount);
+        const int nk = (c == g.n_chunks - 1) ? g.k16_last : 4;
+#pragma unroll
+        for (int t = 0; t < 2; ++t) {
+            if (t == 1 && c == 0) wait_tile1();          // tile 1's operand is only needed now: tile 0 starts earlier
+            for (int k = 0; k < nk; ++k) {
+                const uint64_t ad = umma_desc(act_s + t * kTileBytes + c * kImgBytes + k * 32, 16, 1024);
+                const uint64_t bd = umma_desc(ring_s + s * kWChunkBytes + k * 32, 16, 1024);
+                umma_f16(tmem + t * 256, ad, bd, idesc, (c > 0 || k > 0) ? 1u : 0u);
+            }
         }
         umma_commit(&bar_empty[s]);
         ++ccount;
@@ -275,12 +319,12 @@ __global__ void __launch_bounds__(64 + 128 * NT, 1) chain_kernel(const __grid_co
                     }
                     const int base = head ? P_C1 : P_D1;
                     for (int l = 0; l < 4; ++l)
-                        for (int t = 0; t < NT; ++t)
+                        for (int t = 0; t < ((NT == 2 && kShareChunks) ? 1 : NT); ++t)
                             produce_gemm(P, P.lay.fwd[base + l], ring, bar_full, bar_empty, pcount, 0, P.lay.fwd[base + l].n_chunks);
                 } else if (MODE == HEAD_BWD) {
                     const int base = head ? P_C1 : P_D1;
                     for (int l = 3; l >= 1; --l)
-                        for (int t = 0; t < NT; ++t)
+                        for (int t = 0; t < ((NT == 2 && kShareChunks) ? 1 : NT); ++t)
                             produce_gemm(P, P.lay.bwd[base + l], ring, bar_full, bar_empty, pcount, 0, P.lay.bwd[base + l].n_chunks);
                 } else {
                     // A operand of the first GEMM(s): sum over feet of dZ1 of each head (P.tsrc, made by sum_feet_kernel), bulk
@@ -310,7 +354,7 @@ __global__ void __launch_bounds__(64 + 128 * NT, 1) chain_kernel(const __grid_co
             auto wait_act = [&](int t) { mbar_wait(&bar_act_ready[t], n_act[t] & 1); ++n_act[t]; tc_fence_after(); };
             // one layer of one tile; then straight on to the other tile while this one's epilogue runs
             auto gemm = [&](int t, const GemmW& g, int c0, int c1, bool acc_init) {
-                mma_gemm(g, act_s + t * kTileBytes, ring_s, tmem + t * 256, bar_full, bar_empty, ccount, c0, c1, acc_init);
+                mma_gemm(g, act_s + t * kTileBytes, ring_s, tmem + t * 256, bar_full, bar_empty, ccount, c0, c1, acc_init, MODE == HEAD_FWD ? &P : nullptr);
                 umma_commit(&bar_acc_ready[t]);
             };
             for (int it = blockIdx.x; it < P.n_items; it += gridDim.x, ++icount) {
@@ -329,20 +373,47 @@ __global__ void __launch_bounds__(64 + 128 * NT, 1) chain_kernel(const __grid_co
                         }
                 } else if (MODE == HEAD_FWD) {
                     const int base = head ? P_C1 : P_D1;
-                    for (int l = 0; l < 4; ++l)
-                        for (int t = 0; t < NT; ++t) {
-                            if (l == 0) { mbar_wait(&bar_in_full[t], icount & 1); tc_fence_after(); }
-                            else wait_act(t);
-                            gemm(t, P.lay.fwd[base + l], 0, 4, false);
-                            if (l == 3) umma_commit(&bar_act_free[t]);
+                    if (NT == 2 && kShareChunks) {
+                        for (int l = 0; l < 4; ++l) {
+                            auto wait_in = [&](int t) {
+                                if (l == 0) { mbar_wait(&bar_in_full[t], icount & 1); tc_fence_after(); }
+                                else wait_act(t);
+                            };
+                            wait_in(0);
+                            dbg_stamp(P, icount == 0, l * 4);
+                            mma_gemm2(P.lay.fwd[base + l], act_s, ring_s, tmem, bar_full, bar_empty, ccount, [&]() { wait_in(1); }, &P);
+                            umma_commit(&bar_acc_ready[0]);
+                            umma_commit(&bar_acc_ready[1]);
+                            if (l == 3) { umma_commit(&bar_act_free[0]); umma_commit(&bar_act_free[1]); }
+                            dbg_stamp(P, icount == 0, l * 4 + 1);
                         }
+                    } else {
+                        for (int l = 0; l < 4; ++l)
+                            for (int t = 0; t < NT; ++t) {
+                                if (l == 0) { mbar_wait(&bar_in_full[t], icount & 1); tc_fence_after(); }
+                                else wait_act(t);
+                                dbg_stamp(P, icount == 0, (l * 2 + t) * 2);
+                                gemm(t, P.lay.fwd[base + l], 0, 4, false);
+                                dbg_stamp(P, icount == 0, (l * 2 + t) * 2 + 1);
+                                if (l == 3) umma_commit(&bar_act_free[t]);
+                            }
+                    }
                 } else if (MODE == HEAD_BWD) {
                     const int base = head ? P_C1 : P_D1;
-                    for (int l = 3; l >= 1; --l)
-                        for (int t = 0; t < NT; ++t) {
-                            wait_act(t);
-                            gemm(t, P.lay.bwd[base + l], 0, P.lay.bwd[base + l].n_chunks, false);
+                    if (NT == 2 && kShareChunks) {
+                        for (int l = 3; l >= 1; --l) {
+                            wait_act(0);
+                            mma_gemm2(P.lay.bwd[base + l], act_s, ring_s, tmem, bar_full, bar_empty, ccount, [&]() { wait_act(1); });
+                            umma_commit(&bar_acc_ready[0]);
+                            umma_commit(&bar_acc_ready[1]);
                         }
+                    } else {
+                        for (int l = 3; l >= 1; --l)
+                            for (int t = 0; t < NT; ++t) {
+                                wait_act(t);
+                                gemm(t, P.lay.bwd[base + l], 0, P.lay.bwd[base + l].n_chunks, false);
+                            }
+                    }
                 } else {
                     const int last_hd = (P.heads_mask & 2) ? 1 : 0;
                     for (int hd = 0; hd < 2; ++hd) {
@@ -426,13 +497,18 @@ __global__ void __launch_bounds__(64 + 128 * NT, 1) chain_kernel(const __grid_co
                 const size_t ht = (size_t)b * P.tpf2 + t;
                 for (int l = 0; l < 3; ++l) {
                     const float2 bv = bias_fetch(l == 0 ? P.biasfoot + ((size_t)head * P.B + b) * kW : P.bias[base + l]);
+                    const bool first = leader && it == (int)blockIdx.x;
                     wait_acc();
+                    dbg_stamp(P, first, 32 + (tl * 3 + l) * 4);
                     bias_put(bv);
                     before_overwrite();
+                    dbg_stamp(P, first, 32 + (tl * 3 + l) * 4 + 1);
                     const size_t slot = ((size_t)head * 3 + l) * P.B * P.tpf2 + ht;
                     epi_relu(taddr, act_tile, row, bias_s, P.save ? P.hmask + (slot * kTile + row) * 8 : nullptr);
+                    dbg_stamp(P, first, 32 + (tl * 3 + l) * 4 + 2);
                     publish(P.save ? P.hact + slot * kTileBytes : nullptr);
                     signal_act();
+                    dbg_stamp(P, first, 32 + (tl * 3 + l) * 4 + 3);
                 }
                 wait_acc();
                 if (leader) bulk_wait_read0();

@@ -24,7 +24,10 @@ struct ChainParams {
     const float* avg_col;        // [3] or null
     const float* dovals;         // [2][B][V][4]
     const uint32_t* maxabs;      // bits of max |d(pre-tanh)|
+    unsigned long long* dbg;     // optional timeline of CTA 0's first item (findb200_chain_trace; diagnostics only)
 };
+
+extern unsigned long long* g_chain_dbg;
 
 
 int launch_chain(int mode, int nt, const ChainParams& P, int sms, cudaStream_t st);

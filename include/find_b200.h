@@ -242,6 +242,7 @@ int findb200_umma_selftest(int mode, const void* a_img, const void* b_img, float
  * library is bracketed by CUDA events on its launching stream (do not enable during CUDA-graph capture);
  * findb200_profile_read synchronises and writes "kernel,launches,total_ms" lines into the HOST buffer buf
  * (returns bytes written) and clears the record. */
+int findb200_chain_trace(void* dev_buf_256_u64);   /* diagnostics: timeline of one head_fwd item (csrc/diag.cu) */
 int findb200_profile_enable(int on);
 int findb200_profile_read(char* buf, size_t cap);
 

@@ -217,3 +217,52 @@ def test_train_step_smooth_only_and_sampling_only():
     ref2 = so.train_step(p, fo.fourier_B(), tv, tables, idx, target, None, faces=tf.numpy(), num_samples=2000, seed=5,
                          forward_only=True, draw_from_verts=sp.verts.cpu().numpy())
     assert abs(sp.loss3[1].item() - ref2["chamf"]) <= 1e-3 * ref2["chamf"]
+
+
+def test_cfg1_full_size_forward_chamfer_matches_cpu_oracle():
+    """BASELINE.json configs[0]: field forward + Chamfer, 1 synthetic foot, 10 242-vertex template vs 10 000 target points,
+    at full size against the CPU oracle (the reference's own CPU-runnable case)."""
+    from find_b200.step import TrainStep
+    B, V, P2, n_rows = 1, 10242, 10000, 2
+    dev, model, p, tv, tables, idx, target, colt = _setup(B, V, P2, n_rows, seed=51)
+    ref = so.train_step(p, fo.fourier_B(), tv, tables, idx, target, colt, forward_only=True, threads=8)
+    step = TrainStep(model, B, P2, with_colour=True, use_graph=False)
+    step.load_inputs(idx, target, colt)
+    step.run()
+    torch.cuda.synchronize()
+    total, chamf, tex = step.loss3.tolist()
+    assert abs(chamf - ref["chamf"]) <= 1e-3 * ref["chamf"]
+    assert abs(tex - ref["tex"]) <= 1e-3 * ref["tex"]
+    assert rel_l2(step.verts, ref["verts"]) < 1e-3 and rel_l2(step.disp, ref["disp"]) < 1e-3
+    ch = co.chamfer(step.verts.cpu().numpy(), target.numpy(), with_grad=False, threads=8)
+    from find_b200 import knn_points
+    k1 = knn_points(step.verts, target.to(dev))
+    assert np.array_equal(k1.idx[..., 0].cpu().numpy(), ch["idx_x"])
+    assert np.array_equal(k1.dists[..., 0].cpu().numpy(), ch["dist_x"])
+
+
+def test_cfg2_full_size_batch_additivity():
+    """Size-independent property at BASELINE.json configs[1] (8 feet x 10 242 vertices x 10 000 targets): the loss is a mean
+    over feet, so the MLP-gradient bucket of the 8-foot step equals the mean of the buckets of its two 4-foot halves, and the
+    per-foot latent gradients of a half are those of the full step times 2 (fp32 summation order only)."""
+    from find_b200.step import TrainStep
+    B, V, P2 = 8, 10242, 10000
+    dev, model, p, tv, tables, idx, target, colt = _setup(B, V, P2, B, seed=52)
+    idx = torch.arange(B)
+    full = TrainStep(model, B, P2, with_colour=True, use_graph=False)
+    full.load_inputs(idx, target, colt)
+    full.run()
+    half = TrainStep(model, 4, P2, with_colour=True, use_graph=False)
+    acc, rows = torch.zeros_like(full.flat_grad), []
+    for h in range(2):
+        sl = slice(4 * h, 4 * h + 4)
+        half.load_inputs(idx[sl], target[sl], colt[sl])
+        half.run()
+        acc += half.flat_grad
+        rows.append(half.grows["shapevec"].clone())
+        l_half = half.loss3.clone()
+        assert torch.isfinite(l_half).all()
+    torch.cuda.synchronize()
+    assert rel_l2(acc / 2, full.flat_grad) < 2e-3          # fp16 gradient scale differs between the runs (global max)
+    assert rel_l2(torch.cat(rows) / 2, full.grows["shapevec"]) < 2e-3
+    assert torch.isfinite(full.loss3).all() and float(full.loss3[1]) > 0
