@@ -38,7 +38,7 @@ static PackLayout make_layout() {
     uint32_t off = 0;
     auto put = [&](GemmW& g, int n_chunks, uint32_t chunk_bytes, int N, int k16_last) {
         g.off = off; g.chunk_bytes = chunk_bytes; g.n_chunks = (uint16_t)n_chunks; g.N = (uint16_t)N;
-        g.k16_last = (uint16_t)k16_last; g.pad = 0;
+        g.k16_last = (uint16_t)k16_last; g.group = 1;
         off += (uint32_t)n_chunks * chunk_bytes;
     };
     put(L.fwd[P_T0], kEncChunks, kWChunkBytes, 256, 1);          // K = 515 -> 8 chunks + 16 columns of the 9th
@@ -47,6 +47,7 @@ static PackLayout make_layout() {
         const int b = h ? P_C1 : P_D1;
         for (int l = 0; l < 3; ++l) put(L.fwd[b + l], 4, kWChunkBytes, 256, 4);
         put(L.fwd[b + 3], 4, kWSmallChunkBytes, 16, 4);          // 256 -> 3, N padded to 16
+        L.fwd[b + 3].group = 4;                                  // 4 x 2 KB in one slot: one ring round trip, not four
     }
     for (int l = P_T1; l <= P_T4; ++l) put(L.bwd[l], 4, kWChunkBytes, 256, 4);
     for (int h = 0; h < 2; ++h) {

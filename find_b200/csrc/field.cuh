@@ -51,7 +51,7 @@ struct GemmW {            // one streamed weight operand (a run of chunk images 
     uint16_t n_chunks;    // K / 64
     uint16_t k16_last;    // 16-wide K steps in the last chunk (1..4); all other chunks use 4
     uint16_t N;           // UMMA N (256 or 16)
-    uint16_t pad;
+    uint16_t group;       // chunks that travel in ONE ring slot (1; 4 for the 2 KB chunks of the N=16 output layers)
 };
 
 struct PackLayout {

@@ -47,11 +47,13 @@ FB_DEVINL uint32_t pack_h2(float a, float b) {
 // ---- producer: stream one weight operand through the ring ------------------------------------------------
 FB_DEVINL void produce_gemm(const ChainParams& P, const GemmW& g, uint8_t* ring, uint64_t* bar_full, uint64_t* bar_empty,
                             uint32_t& pcount, int c0, int c1) {
-    for (int c = c0; c < c1; ++c) {
+    const int grp = g.group ? g.group : 1;
+    for (int c = c0; c < c1; c += grp) {
         const uint32_t s = pcount % kRing, use = pcount / kRing;
+        const uint32_t bytes = (uint32_t)min(grp, c1 - c) * g.chunk_bytes;
         if (use > 0) mbar_wait(&bar_empty[s], (use - 1) & 1);
-        mbar_expect_tx(&bar_full[s], g.chunk_bytes);
-        bulk_g2s(ring + s * kWChunkBytes, P.wpack + g.off + (size_t)c * g.chunk_bytes, g.chunk_bytes, &bar_full[s]);
+        mbar_expect_tx(&bar_full[s], bytes);
+        bulk_g2s(ring + s * kWChunkBytes, P.wpack + g.off + (size_t)c * g.chunk_bytes, bytes, &bar_full[s]);
         dbg_stamp(P, pcount < 32, 64 + (int)pcount);
         ++pcount;
     }
@@ -61,16 +63,20 @@ FB_DEVINL void produce_gemm(const ChainParams& P, const GemmW& g, uint8_t* ring,
 FB_DEVINL void mma_gemm(const GemmW& g, uint32_t act_s, uint32_t ring_s, uint32_t tmem, uint64_t* bar_full,
                         uint64_t* bar_empty, uint32_t& ccount, int c0, int c1, bool acc_init, const ChainParams* dbgP = nullptr) {
     const uint32_t idesc = umma_idesc_f16(128, g.N, false, false);
-    for (int c = c0; c < c1; ++c) {
+    const int grp = g.group ? g.group : 1;
+    for (int c = c0; c < c1; c += grp) {
         const uint32_t s = ccount % kRing, use = ccount / kRing;
         mbar_wait(&bar_full[s], use & 1);
         tc_fence_after();
         if (dbgP) dbg_stamp(*dbgP, ccount < 32, 96 + (int)ccount);
-        const int nk = (c == g.n_chunks - 1) ? g.k16_last : 4;
-        for (int k = 0; k < nk; ++k) {
-            const uint64_t ad = umma_desc(act_s + (c - c0) * kImgBytes + k * 32, 16, 1024);
-            const uint64_t bd = umma_desc(ring_s + s * kWChunkBytes + k * 32, 16, 1024);
-            umma_f16(tmem, ad, bd, idesc, (acc_init || c > c0 || k > 0) ? 1u : 0u);
+        for (int sub = 0; sub < grp && c + sub < c1; ++sub) {
+            const int cc = c + sub;
+            const int nk = (cc == g.n_chunks - 1) ? g.k16_last : 4;
+            for (int k = 0; k < nk; ++k) {
+                const uint64_t ad = umma_desc(act_s + (cc - c0) * kImgBytes + k * 32, 16, 1024);
+                const uint64_t bd = umma_desc(ring_s + s * kWChunkBytes + sub * g.chunk_bytes + k * 32, 16, 1024);
+                umma_f16(tmem, ad, bd, idesc, (acc_init || cc > c0 || k > 0) ? 1u : 0u);
+            }
         }
         umma_commit(&bar_empty[s]);
         ++ccount;
