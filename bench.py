@@ -368,7 +368,7 @@ def run_ours(args, wl, rank, world, local_rank):
         "scaling": "weak", "vs_baseline": None, "dtype": "fp16 tensor-core operands / fp32 accumulate (field), fp32 (Chamfer)",
         "data": "synthetic", "impl": "find_b200",
         "config": {"workload": f"{args.workload}: {wl['desc']}", "feet_per_gpu": feet, "global_feet": feet * world,
-                   "verts": V, "target_points": P2, "frozen_mlp": wl["frozen"], "parallelism": f"dp{world} (foot-batch sharding)",
+                   "verts": V, "target_points": P2, "frozen_mlp": wl["frozen"], "parallelism": f"dp{world} (foot-batch sharding)", "collective": sharded.collective,
                    "l2": "flushed between steps (256 MiB memset outside the event pairs)", "cuda_graph": True,
                    "loss": "1e4*chamfer(verts,target) + 1*mse(col,col_target)"},
         "e2e": {"value": fv_global / (e2e_s / args.steps), "unit": UNIT, "h2d_bytes_per_step": h2d,

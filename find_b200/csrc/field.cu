@@ -590,7 +590,8 @@ int findb200_field_forward(const findb200_field_params* p, const float* pos, int
     C.pos = pos;
     C.disp = disp; C.col = col; C.verts = verts; C.reg = reg;
     // trunk: one tile per CTA while that still fills the machine poorly (latency), two when there are many tiles
-    {
+    C.enc_cached = (save_for_backward && (p->flags & FINDB200_FIELD_ENC_CACHED)) ? 1 : 0;
+    if (!(save_for_backward && (p->flags & FINDB200_FIELD_TRUNK_CACHED))) {
         const int nt = (w.trunk_tiles <= 2 * sms) ? 1 : 2;
         C.n_items = w.trunk_tiles / nt;
         rc = launch_chain(0, nt, C, sms, st);

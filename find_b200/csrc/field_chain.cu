@@ -254,6 +254,7 @@ FB_DEVINL void euler_xyz(const float* e, float (&R)[3][3]) {
 template <int MODE, int NT>
 __global__ void __launch_bounds__(64 + 128 * NT, 1) chain_kernel(const __grid_constant__ ChainParams P) {
     fb::pdl_wait_trigger();
+    if (threadIdx.x == 0) dbg_stamp(P, true, 200 + MODE * 2);
     // dynamic shared memory only (no static __shared__), so the window starts 1024-aligned as SWIZZLE_128B needs:
     // [NT activation tiles 64 KB][weight ring 3 x 32 KB][NT x 256 fp32 bias of the layer in flight][mbarriers]
     extern __shared__ __align__(1024) uint8_t smem[];
@@ -370,12 +371,16 @@ __global__ void __launch_bounds__(64 + 128 * NT, 1) chain_kernel(const __grid_co
                     for (int p = 0; p < 3; ++p)
                         for (int t = 0; t < NT; ++t) {
                             wait_act(t);
+                            dbg_stamp(P, icount == 0 && t == 0, 128 + p * 2);
                             gemm(t, P.lay.fwd[P_T0], 4 * p, min(4 * p + 4, kEncChunks), p > 0);
+                            dbg_stamp(P, icount == 0 && t == 0, 128 + p * 2 + 1);
                         }
                     for (int l = 1; l < 5; ++l)
                         for (int t = 0; t < NT; ++t) {
                             wait_act(t);
+                            dbg_stamp(P, icount == 0 && t == 0, 128 + (2 + l) * 2);
                             gemm(t, P.lay.fwd[P_T0 + l], 0, 4, false);
+                            dbg_stamp(P, icount == 0 && t == 0, 128 + (2 + l) * 2 + 1);
                         }
                 } else if (MODE == HEAD_FWD) {
                     const int base = head ? P_C1 : P_D1;
@@ -448,7 +453,7 @@ __global__ void __launch_bounds__(64 + 128 * NT, 1) chain_kernel(const __grid_co
         const bool leader = gt == 0;
         uint8_t* act_tile = act + tl * kTileBytes;
         const uint32_t taddr = tmem + ((uint32_t)(q * 32) << 16) + tl * 256;
-        uint32_t n_acc = 0;
+        uint32_t n_acc = 0, n_enc = 0;
         auto wait_acc = [&]() { mbar_wait(&bar_acc_ready[tl], n_acc & 1); ++n_acc; tc_fence_after(); };
         auto before_overwrite = [&]() {              // pending bulk store of this tile must have read smem
             if (leader) bulk_wait_read0();
@@ -480,23 +485,53 @@ __global__ void __launch_bounds__(64 + 128 * NT, 1) chain_kernel(const __grid_co
                     const float* pp = P.pos + ((size_t)b * P.V + vrow) * 3;
                     x = pp[0]; y = pp[1]; z = pp[2];
                 }
+                const bool first = leader && tl == 0 && it == (int)blockIdx.x;
                 for (int p = 0; p < 3; ++p) {
-                    if (p == 0) before_overwrite(); else wait_acc();
-                    for (int c = 4 * p; c < min(4 * p + 4, kEncChunks); ++c)
-                        encode_chunk(c, x, y, z, P.Bmat, act_tile + (c - 4 * p) * kImgBytes, row,
-                                     P.save ? P.enc + tt * kEncTileBytes + (size_t)c * kImgBytes : nullptr);
+                    if (p > 0) wait_acc();
+                    before_overwrite();                  // the previous bulk store of this buffer has read it
+                    dbg_stamp(P, first, 160 + p * 2);
+                    const int c_lo = 4 * p, c_hi = min(4 * p + 4, kEncChunks);
+                    if (P.enc_cached) {
+                        // the template is constant: an earlier forward left these images in the workspace, one bulk load
+                        // replaces 128 sin/cos pairs per row and pass
+                        if (leader) {
+                            const uint32_t bytes = (uint32_t)(c_hi - c_lo) * kImgBytes;
+                            mbar_expect_tx(&bar_in_full[tl], bytes);
+                            bulk_g2s(act_tile, P.enc + tt * kEncTileBytes + (size_t)c_lo * kImgBytes, bytes, &bar_in_full[tl]);
+                        }
+                        mbar_wait(&bar_in_full[tl], n_enc & 1);
+                        ++n_enc;
+                        signal_act();
+                        dbg_stamp(P, first, 160 + p * 2 + 1);
+                        continue;
+                    }
+                    for (int c = c_lo; c < c_hi; ++c)
+                        encode_chunk(c, x, y, z, P.Bmat, act_tile + (c - c_lo) * kImgBytes, row, nullptr);
+                    // the saved copy for the dW kernel leaves as ONE bulk store of the finished images (the per-thread
+                    // 16-byte global stores it replaces touched 32 lines per warp instruction: 4 us per pass)
                     fence_proxy_async();
+                    if (P.save) {
+                        named_bar_sync(1 + tl, 128);
+                        if (leader) {
+                            bulk_s2g(P.enc + tt * kEncTileBytes + (size_t)c_lo * kImgBytes, act_tile, (uint32_t)(c_hi - c_lo) * kImgBytes);
+                            bulk_commit();
+                        }
+                    }
                     signal_act();
+                    dbg_stamp(P, first, 160 + p * 2 + 1);
                 }
                 for (int l = 0; l < 5; ++l) {
+                    dbg_stamp(P, first, 170 + l * 3);
                     const float2 bv = bias_fetch(P.bias[P_T0 + l]);
                     wait_acc();
+                    dbg_stamp(P, first, 170 + l * 3 + 1);
                     bias_put(bv);
                     before_overwrite();
                     epi_relu(taddr, act_tile, row, bias_s,
                              P.save ? P.tmask + (((size_t)l * P.trunk_tiles + tt) * kTile + row) * 8 : nullptr);
                     publish((P.save || l == 4) ? P.tact + ((size_t)l * P.trunk_tiles + tt) * kTileBytes : nullptr);
                     if (l < 4) signal_act();
+                    dbg_stamp(P, first, 170 + l * 3 + 2);
                 }
             } else if (MODE == HEAD_FWD) {
                 const int base = head ? P_C1 : P_D1;
@@ -607,6 +642,7 @@ __global__ void __launch_bounds__(64 + 128 * NT, 1) chain_kernel(const __grid_co
     tc_fence_before();
     __syncthreads();
     if (warp == 0) tmem_dealloc(tmem, NT * 256);
+    if (threadIdx.x == 0) dbg_stamp(P, true, 200 + MODE * 2 + 1);
 }
 
 // ---- launch ---------------------------------------------------------------------------------------------

@@ -12,6 +12,7 @@ struct ChainParams {
     PackLayout lay;
     int B, V, tpf, tpf2, trunk_feet, trunk_tiles, shared;
     int n_items, save, heads_mask, n_heads;
+    int enc_cached;              // TRUNK_FWD: load the encoded tiles from `enc` instead of computing them
     const float* pos;            // [trunk_feet][V][3]
     const float* Bmat;           // [3][256]
     const float* bias[P_COUNT];

@@ -25,7 +25,11 @@ ENC = 515
 class FieldParamsC(ctypes.Structure):
     _fields_ = [("weight", ctypes.c_void_p * N_PARAMS), ("bias", ctypes.c_void_p * N_PARAMS),
                 ("fourier_B", ctypes.c_void_p), ("avg_col", ctypes.c_void_p),
-                ("shapevec_size", ctypes.c_int), ("posevec_size", ctypes.c_int), ("texvec_size", ctypes.c_int)]
+                ("shapevec_size", ctypes.c_int), ("posevec_size", ctypes.c_int), ("texvec_size", ctypes.c_int),
+                ("flags", ctypes.c_int)]
+
+
+FIELD_ENC_CACHED, FIELD_TRUNK_CACHED = 1, 2
 
 
 class FieldGradsC(ctypes.Structure):
@@ -62,6 +66,7 @@ def _make_params(weights: Sequence[torch.Tensor], biases: Sequence[torch.Tensor]
     c.fourier_B = fourier_B.data_ptr()
     c.avg_col = None if avg_col is None else avg_col.data_ptr()
     c.shapevec_size, c.posevec_size, c.texvec_size = S, P, T
+    c.flags = 0
     return c
 
 

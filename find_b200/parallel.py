@@ -61,6 +61,49 @@ def allreduce_flat_grad(flat_grad: torch.Tensor, group=None, average: bool = Fal
     return None
 
 
+class P2PAllReduce:
+    """The MLP-gradient bucket in symmetric memory + findb200_allreduce_p2p (csrc/allreduce.cu): ONE kernel over NVLink /
+    NVSwitch peer memory instead of an NCCL call.  torch's symmetric-memory rendezvous is used only to allocate the bucket and
+    to exchange the peer mappings (plumbing); the reduction itself is the library's kernel.  ``bucket`` is the fp32 view of
+    length ``n`` the step writes its gradients into."""
+
+    def __init__(self, n: int, device: torch.device, group=None, n_ctas: int = 128):
+        import ctypes
+        import torch.distributed._symmetric_memory as symm_mem
+        from . import _lib
+        self.lib = _lib.load()
+        self._lib_mod = _lib
+        group = group if group is not None else dist.group.WORLD
+        self.world, self.rank = dist.get_world_size(group), dist.get_rank(group)
+        self.n, self.n_pad = int(n), (int(n) + 3) // 4 * 4
+        self.dev, self.n_ctas = device, int(n_ctas)
+        flag_words = int(self.lib.findb200_allreduce_p2p_flag_bytes()) // 4
+        with torch.cuda.device(device):
+            self.buf = symm_mem.empty(self.n_pad, dtype=torch.float32, device=device)
+            self.flags = symm_mem.empty(flag_words, dtype=torch.int32, device=device)
+            self.buf.zero_()
+            self.flags.zero_()
+            torch.cuda.synchronize(device)
+            self._h_buf = symm_mem.rendezvous(self.buf, group)
+            self._h_flags = symm_mem.rendezvous(self.flags, group)
+        bp, fp = list(self._h_buf.buffer_ptrs), list(self._h_flags.buffer_ptrs)
+        if len(bp) != self.world or len(fp) != self.world or not all(bp) or not all(fp):
+            raise RuntimeError("symmetric-memory rendezvous did not map every peer")
+        self._bufs = (ctypes.c_void_p * self.world)(*bp)
+        self._flags = (ctypes.c_void_p * self.world)(*fp)
+        self.epoch = torch.zeros(2, dtype=torch.int32, device=device)
+        self.bucket = self.buf[: self.n]
+        dist.barrier(group)                       # every rank's flag page is zero before anyone signals
+        torch.cuda.synchronize(device)
+
+    def enqueue(self, scale: float = 1.0):
+        """bucket <- scale * sum over ranks (in place, on the current stream; graph-capturable)."""
+        _lib = self._lib_mod
+        rc = self.lib.findb200_allreduce_p2p(self._bufs, self._flags, self.rank, self.world, self.n_pad, float(scale),
+                                             _lib.ptr(self.epoch), self.n_ctas, _lib.stream_ptr(self.dev))
+        _lib.check(rc, "findb200_allreduce_p2p")
+
+
 class ShardedTrainStep:
     """TrainStep over this rank's slice of a global foot batch + the gradient allreduce.
 
@@ -68,16 +111,51 @@ class ShardedTrainStep:
     ``local_feet`` and the bucket is combined with weights ``local_feet / global_feet`` (a plain average when the
     split is even), which reproduces the single-rank gradient of the concatenated batch."""
 
-    def __init__(self, step, global_feet: int, group=None):
+    def __init__(self, step, global_feet: int, group=None, collective: str = "auto"):
+        """``collective``: "p2p" = the library's own peer-memory allreduce kernel (csrc/allreduce.cu), "nccl" =
+        torch.distributed.all_reduce, "auto" = p2p when every rank can map its peers (symmetric memory), else nccl."""
         self.step = step
         self.group = group
         self.global_feet = int(global_feet)
         self.world = dist.get_world_size(group) if dist.is_initialized() else 1
         self.weight = step.B / float(self.global_feet)
         self.graph: Optional[torch.cuda.CUDAGraph] = None
+        self.p2p: Optional[P2PAllReduce] = None
+        self.collective = "none"
+        if self.world > 1 and not step.frozen:
+            self.collective = "nccl"
+            if collective in ("auto", "p2p") and step.flat_grad.is_cuda:
+                err = None
+                try:
+                    self.p2p = P2PAllReduce(step.flat_grad.numel(), step.dev, group)
+                except Exception as e:              # noqa: BLE001 — no peer mapping on this box: NCCL carries the exchange
+                    err = e
+                ok = torch.tensor([1 if self.p2p is not None else 0], device=step.dev)
+                dist.all_reduce(ok, op=dist.ReduceOp.MIN, group=group)
+                if int(ok.item()) == 1:
+                    self._adopt_bucket()
+                    self.collective = "p2p"
+                else:
+                    self.p2p = None
+                    if collective == "p2p":
+                        raise RuntimeError(f"peer-memory allreduce unavailable: {err}")
+
+    def _adopt_bucket(self):
+        """Make the step write its MLP gradients straight into the symmetric bucket (must happen before its first enqueue)."""
+        step = self.step
+        if step._cparams is not None:
+            raise RuntimeError("ShardedTrainStep must wrap a TrainStep before its first run")
+        step.flat_grad = self.p2p.bucket
+        step.grad_views, off = [], 0
+        for prm in step.mlp_params:
+            step.grad_views.append(step.flat_grad[off:off + prm.numel()].view_as(prm))
+            off += prm.numel()
 
     def _collective(self):
         """weight * flat_grad summed over ranks, in place.  An even split is NCCL's AVG (one kernel, no pre-scale)."""
+        if self.p2p is not None:
+            self.p2p.enqueue(self.weight)
+            return
         fg = self.step.flat_grad
         if fg.is_cuda and abs(self.weight * self.world - 1.0) < 1e-12:
             dist.all_reduce(fg, op=dist.ReduceOp.AVG, group=self.group)
@@ -98,7 +176,8 @@ class ShardedTrainStep:
             self._collective()
             return step.loss3
         with torch.cuda.device(step.dev):
-            if self.graph is None:
+            if self.graph is None or (step._cache_key is not None and step._cache_key != step._current_cache_key()):
+                step._cache_key = None               # template changed: recompute the cached tiles, re-capture
                 step._enqueue()                      # warm-up outside capture: function attributes, NCCL communicator
                 self._collective()
                 torch.cuda.synchronize(step.dev)
@@ -117,4 +196,4 @@ class ShardedTrainStep:
                 g.mul_(self.weight)
 
 
-__all__ = ["shard_range", "owner_by_label", "shard_by_label", "allreduce_flat_grad", "ShardedTrainStep"]
+__all__ = ["shard_range", "owner_by_label", "shard_by_label", "allreduce_flat_grad", "ShardedTrainStep", "P2PAllReduce"]

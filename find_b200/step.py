@@ -19,7 +19,7 @@ import torch
 
 from . import _lib
 from .field import NeuralDisplacementField
-from .field_ops import FieldGradsC, N_PARAMS, _make_params
+from .field_ops import FIELD_ENC_CACHED, FIELD_TRUNK_CACHED, FieldGradsC, N_PARAMS, _make_params
 from .losses import CHAMF_WEIGHT, TEX_WEIGHT
 
 SMOOTH_WEIGHT = 1000.0   # opts.py:97 (--weight_smooth default)
@@ -102,6 +102,7 @@ class TrainStep:
         self._cparams = None
         self._cgrads = None
         self._gather = None
+        self._cache_key = None           # what the cached tiles in the workspace were computed from
 
     # ---- the enqueue ---------------------------------------------------------------------------------------
     def _structs(self):
@@ -138,6 +139,15 @@ class TrainStep:
         if self._gather[1]:
             rc = lib.findb200_gather_rows_multi(self._gather[0], self._gather[1], _lib.ptr(self.idx), self.B, st)
             _lib.check(rc, "findb200_gather_rows_multi")
+        # Workspace caches (include/find_b200.h FINDB200_FIELD_*): the template never changes during training, so after the
+        # first enqueue the Fourier-encoded tiles are reused; with a frozen MLP the whole trunk output is.  Any in-place
+        # change of the template (or of the frozen weights) is seen through the tensors' version counters.
+        key = self._current_cache_key()
+        flags = 0
+        if self._cache_key == key:
+            flags = FIELD_ENC_CACHED | (FIELD_TRUNK_CACHED if self.frozen else 0)
+        self._cparams.flags = flags
+        self._cache_key = None                   # set again below, once the enqueue has succeeded
         r, g = self.rows, self.grows
         args = (ctypes.byref(self._cparams), _lib.ptr(self.model.template_verts), _lib.ptr(r.get("shapevec")),
                 _lib.ptr(r.get("posevec")), _lib.ptr(r.get("texvec")), _lib.ptr(r.get("reg")), _lib.ptr(self.target), None,
@@ -151,13 +161,22 @@ class TrainStep:
         else:
             rc = lib.findb200_train_step_mesh(*args, ctypes.byref(self.mesh_terms), _lib.ptr(self.ws), self.ws.numel(), st)
             _lib.check(rc, "findb200_train_step_mesh")
+        self._cache_key = key
+
+    def _current_cache_key(self):
+        tv = self.model.template_verts
+        key = (tv.data_ptr(), tv._version)
+        if self.frozen:
+            key = key + tuple((p.data_ptr(), p._version) for p in self.mlp_params)
+        return key
 
     def run(self) -> torch.Tensor:
         """Enqueue one step on the current stream (graph replay after the first call) -> loss3 (device)."""
         with torch.cuda.device(self.dev):
             if not self.use_graph:
                 self._enqueue()
-            elif self.graph is None:
+            elif self.graph is None or (self._cache_key is not None and self._cache_key != self._current_cache_key()):
+                self._cache_key = None               # template (or frozen weights) changed: recompute, then re-capture
                 self._enqueue()                      # warm-up outside capture (sets function attributes)
                 torch.cuda.synchronize(self.dev)
                 g = torch.cuda.CUDAGraph()

@@ -85,7 +85,15 @@ typedef struct findb200_field_params {
     const float* fourier_B;   /* [3,256] Gaussian matrix of FourierFeatureTransform (fourier_feature_transform.py:23-26) */
     const float* avg_col;     /* [3] added to col, or NULL (model.py:449-451) */
     int shapevec_size, posevec_size, texvec_size;   /* widths of the latent blocks (0 = block absent) */
+    int flags;                /* FINDB200_FIELD_* bits; 0 = recompute everything */
 } findb200_field_params;
+/* Caller's promise about the workspace it passes (same workspace, same `pos`, for_backward = 1 in an EARLIER forward):
+ *   ENC_CACHED   the Fourier-encoded tiles of `pos` written by that forward are still there: the trunk loads them instead of
+ *                recomputing 256 sin/cos pairs per vertex (the template is constant over training, model.py:285);
+ *   TRUNK_CACHED also the trunk output is still valid (MLP weights unchanged since: latent-code fitting with a frozen MLP,
+ *                train.py:218-224): the trunk forward is skipped altogether. */
+#define FINDB200_FIELD_ENC_CACHED 1
+#define FINDB200_FIELD_TRUNK_CACHED 2
 
 typedef struct findb200_field_grads {   /* same order and shapes as findb200_field_params; every entry is overwritten */
     float* weight[13];
@@ -214,6 +222,18 @@ int findb200_train_step_mesh(const findb200_field_params* p, const float* templa
                              float w_tex, float* loss3, float* disp, float* col, float* verts,
                              const findb200_field_grads* gw, float* gz_shape, float* gz_pose, float* gz_tex, float* greg,
                              const findb200_mesh_terms* mesh_terms, void* workspace, size_t workspace_bytes, void* stream);
+
+/* ------------------------------------------------------------------------------------------------------
+ * The exchange step of the sharded training step: in-place SUM (times `scale`) of the flat MLP-gradient
+ * bucket over `world` ranks, one kernel over NVLink / NVSwitch peer memory (two-shot, deterministic, bit-identical on
+ * every rank).  peer_bufs / peer_flags: HOST arrays of `world` device pointers — every rank's bucket (n_floats fp32,
+ * multiple of 4, 16-byte aligned) and flag page (findb200_allreduce_p2p_flag_bytes() bytes, zeroed once) as mapped into THIS
+ * process (e.g. torch symmetric memory); epoch_dev: device u32[2], zero-initialised, owned by the call sequence.  Graph-capturable.
+ * Every rank must enqueue the call the same number of times.
+ * ------------------------------------------------------------------------------------------------------ */
+size_t findb200_allreduce_p2p_flag_bytes(void);
+int findb200_allreduce_p2p(void* const* peer_bufs, void* const* peer_flags, int rank, int world, long long n_floats,
+                           float scale, unsigned int* epoch_dev, int n_ctas, void* stream);
 
 /* Kernel counters of the last findb200_train_step that used this workspace: same four numbers as findb200_knn_stats
  * ({pair evaluations executed, cross-chunk-tie queries, most chunk evaluations of one group, groups}); synchronises. */

@@ -266,3 +266,34 @@ def test_cfg2_full_size_batch_additivity():
     assert rel_l2(acc / 2, full.flat_grad) < 2e-3          # fp16 gradient scale differs between the runs (global max)
     assert rel_l2(torch.cat(rows) / 2, full.grows["shapevec"]) < 2e-3
     assert torch.isfinite(full.loss3).all() and float(full.loss3[1]) > 0
+
+
+def test_workspace_caches_match_recompute_and_follow_template_changes():
+    """FINDB200_FIELD_ENC_CACHED / TRUNK_CACHED: the second and later enqueues reuse the encoded template tiles (and, with a
+    frozen MLP, the trunk output) left in the workspace — results must be bit-identical to the first (recomputing) enqueue,
+    and an in-place change of the template must be picked up (version counter) instead of served from the cache."""
+    from find_b200.step import TrainStep
+    for frozen in (False, True):
+        B, V, P2, n_rows = 3, 700, 600, 5
+        dev, model, p, tv, tables, idx, target, colt = _setup(B, V, P2, n_rows, seed=61)
+        step = TrainStep(model, B, P2, with_colour=True, use_graph=False, frozen_mlp=frozen)
+        step.load_inputs(idx, target, colt)
+        step.run(); torch.cuda.synchronize()
+        first = (step.loss3.clone(), step.verts.clone(), step.col.clone(), step.flat_grad.clone(), step.grows["shapevec"].clone())
+        assert step._cparams.flags == 0
+        step.run(); torch.cuda.synchronize()
+        assert step._cparams.flags == (3 if frozen else 1)
+        second = (step.loss3, step.verts, step.col, step.flat_grad, step.grows["shapevec"])
+        for a, b in zip(first[:3], second[:3]):
+            assert torch.equal(a, b)
+        for a, b in zip(first[3:], second[3:]):                  # gradients: fp32 atomics in the column sums
+            assert rel_l2(b, a) < 1e-5
+        with torch.no_grad():
+            model.template_verts.mul_(1.01)                      # in-place edit bumps the version counter
+        step.run(); torch.cuda.synchronize()
+        assert step._cparams.flags == 0
+        fresh = TrainStep(model, B, P2, with_colour=True, use_graph=False, frozen_mlp=frozen)
+        fresh.load_inputs(idx, target, colt)
+        fresh.run(); torch.cuda.synchronize()
+        assert torch.equal(fresh.verts, step.verts) and torch.equal(fresh.loss3, step.loss3)
+        assert not torch.equal(step.verts, first[1])

@@ -36,3 +36,13 @@ for tl in range(2):
         print(f"  T{tl} L{l}: {r(b):7.2f} {r(b+1):7.2f} {r(b+2):7.2f} {r(b+3):7.2f}")
 print("producer chunk issue (us):", " ".join(f"{r(64+i):.2f}" for i in range(32)))
 print("mma chunk full   (us):", " ".join(f"{r(96+i):.2f}" for i in range(32)))
+print("kernel start/end (us): trunk_fwd", r(200), r(201), " head_fwd", r(202), r(203))
+print("trunk_fwd MMA warp (us): [enc pass 0..2, layers 1..4] ready, issued")
+for i in range(7):
+    print(f"  stage {i}: {r(128+i*2):7.2f} {r(128+i*2+1):7.2f}")
+print("trunk_fwd epilogue leader: encode pass start / signalled")
+for p_ in range(3):
+    print(f"  enc {p_}: {r(160+p_*2):7.2f} {r(160+p_*2+1):7.2f}")
+print("trunk_fwd epilogue leader per layer: loop top, acc_ready, published")
+for l in range(5):
+    print(f"  L{l}: {r(170+l*3):7.2f} {r(170+l*3+1):7.2f} {r(170+l*3+2):7.2f}")

@@ -64,7 +64,7 @@ def main():
         full.load_inputs(torch.arange(G), target, colt)
         full.run()
         torch.cuda.synchronize()
-        out = dict(world=world, bucket_rel_l2=rel(flat, full.flat_grad), shapevec_rows_rel_l2=rel(torch.cat(gathered), full.grows["shapevec"]))
+        out = dict(world=world, collective=sh.collective, bucket_rel_l2=rel(flat, full.flat_grad), shapevec_rows_rel_l2=rel(torch.cat(gathered), full.grows["shapevec"]))
     oks = [None] * world
     dist.all_gather_object(oks, same)
     if rank == 0:
