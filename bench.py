@@ -218,7 +218,7 @@ def run_ours(args, wl, rank, world, local_rank):
     lib = _lib.load()
     peaks = load_peaks()
     model, step, host = build_job(wl, rank, world, device)
-    sharded = ShardedTrainStep(step, wl["feet"] * world)
+    sharded = ShardedTrainStep(step, wl["feet"] * world, collective=os.environ.get("FINDB200_COLLECTIVE", "auto"))
     feet, V, P2 = wl["feet"], wl["V"], wl["P2"]
     fv_global = feet * world * V
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=device)     # > 126 MB L2
