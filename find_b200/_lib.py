@@ -57,6 +57,12 @@ SIGNATURES = {
     "findb200_mesh_smooth": (c_int, [c_void_p, c_int, c_int, c_void_p, c_int, c_void_p, c_int, c_void_p, c_void_p, c_void_p,
                                      c_int, c_float, c_float, c_float, c_void_p, c_void_p, c_void_p, c_int, c_void_p,
                                      c_size_t, c_void_p]),
+    "findb200_silhouette_workspace_bytes": (c_size_t, [c_int] * 2),
+    "findb200_silhouette_forward": (c_int, [c_void_p, c_void_p] + [c_int] * 5 + [c_float, c_float, c_int, c_int]
+                                    + [c_void_p] * 4 + [c_size_t, c_void_p]),
+    "findb200_silhouette_backward": (c_int, [c_void_p, c_void_p] + [c_int] * 5 + [c_float, c_float, c_int, c_int]
+                                     + [c_void_p] * 4 + [c_size_t, c_void_p]),
+    "findb200_silhouette_status": (c_int, [c_void_p, c_int, c_int, c_void_p]),
     "findb200_adam_step": (c_int, [c_void_p, c_int] + [ctypes.c_double] * 5 + [c_void_p, c_void_p]),
     "findb200_sgd_momentum_step": (c_int, [c_void_p, c_int] + [ctypes.c_double] * 3 + [c_void_p, c_void_p]),
     "findb200_allreduce_p2p_flag_bytes": (c_size_t, []),

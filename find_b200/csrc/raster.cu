@@ -1,0 +1,458 @@
+// find_b200/csrc/raster.cu — soft-silhouette rasteriser (forward + backward), the first slice of SURVEY.md §8(f) row 4.
+//
+// Replaces, for the silhouette used by FIND's 2-D losses (/root/reference/src/model/renderer.py:122-128, 208-245, 309-311),
+// PyTorch3D's rasterize_meshes (faces_per_pixel = 100, blur_radius = log(1/1e-4 - 1) * sigma, clipped + perspective-correct
+// barycentrics) followed by SoftSilhouetteShader:  alpha = 1 - prod_k (1 - sigmoid(-signed_dist_k / sigma))  over the K
+// candidates of smallest depth.  The arithmetic is restated in oracle/raster_oracle.py (header there lists the rules).
+//
+// Design (no graphics API: plain CUDA):
+//   face_setup_kernel   one thread per (mesh, face): the 9 vertex floats and the blur-grown bounding box, as two float4-
+//                       aligned records; a degenerate or behind-the-camera face gets an empty box
+//   sil_tile_kernel     one CTA per 16 x 16 pixel tile of one mesh, one thread per pixel.  The CTA streams the mesh's boxes
+//                       (coalesced float4), compacts the faces that touch the tile IN FACE ORDER into shared memory and
+//                       evaluates them for all 256 pixels from shared memory.  No global binning pass, no per-pixel lists.
+//                       K truncation is exact and needs no per-pixel heap: a pixel with more than K candidates finds the
+//                       K-th smallest depth by bisection on the float bit pattern over the tile's face list (re-evaluation
+//                       instead of storage), then multiplies the candidates below it and the first ties in face order.
+//   backward            the same tile walk; d alpha / d signed_dist_k = prod * p_k / sigma needs only the saved product.
+//                       Per face the 256 pixels' contributions are reduced in the warp before 6 atomics per warp.
+// Bound: FP32 latency / FMA (about 70 flop per pixel-face evaluation); HBM traffic is 64 B per face per tile row.
+#include "common.cuh"
+#include "../../include/find_b200.h"
+
+namespace fb {
+namespace raster {
+
+constexpr int kTile = 16;
+constexpr int kThreads = kTile * kTile;
+constexpr int kListCap = 4096;           // faces touching one tile that the CTA keeps for the K-truncation passes
+constexpr float kEps = 1e-8f;
+
+struct FaceRec {                          // 48 B, three float4 loads
+    float x0, y0, z0, x1;
+    float y1, z1, x2, y2;
+    float z2, pad0, pad1, pad2;
+};
+
+struct SilParams {
+    const float4* box;                    // [N, F]  (xmin, xmax, ymin, ymax) grown by sqrt(blur_radius); empty when invalid
+    const FaceRec* rec;                   // [N, F]
+    int N, F, H, W;
+    float blur_radius, sigma;
+    int K, perspective;
+    float* alpha;                         // [N, H, W]
+    float* prod;                          // [N, H, W]   prod_k (1 - p_k) of the kept candidates
+    uint2* sel;                           // [N, H, W]   (depth-threshold bits, ties allowed); (0xffffffff, 0) = all kept
+    const float* grad_alpha;              // backward
+    float* grad_verts;                    // [N, V, 3]
+    const int* faces;                     // [F, 3] (backward: vertex ids)
+    int V;
+    unsigned int* overflow;               // device flag: a tile exceeded kListCap while a pixel needed K truncation
+};
+
+__global__ void face_setup_kernel(const float* __restrict__ verts, const int* __restrict__ faces, int N, int V, int F,
+                                  float blur, float4* __restrict__ box, FaceRec* __restrict__ rec) {
+    pdl_wait_trigger();
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= (long long)N * F) return;
+    const int n = (int)(i / F), f = (int)(i - (long long)n * F);
+    const int i0 = faces[3 * f], i1 = faces[3 * f + 1], i2 = faces[3 * f + 2];
+    const float* v = verts + (size_t)n * V * 3;
+    FaceRec r;
+    r.x0 = v[3 * i0]; r.y0 = v[3 * i0 + 1]; r.z0 = v[3 * i0 + 2];
+    r.x1 = v[3 * i1]; r.y1 = v[3 * i1 + 1]; r.z1 = v[3 * i1 + 2];
+    r.x2 = v[3 * i2]; r.y2 = v[3 * i2 + 1]; r.z2 = v[3 * i2 + 2];
+    r.pad0 = r.pad1 = r.pad2 = 0.f;
+    const float area = __fsub_rn(__fmul_rn(r.x2 - r.x0, r.y1 - r.y0), __fmul_rn(r.y2 - r.y0, r.x1 - r.x0));
+    const float zmax = fmaxf(fmaxf(r.z0, r.z1), r.z2);
+    const bool ok = (fabsf(area) > kEps) && (zmax >= 0.f);     // NaN coordinates fail both tests
+    float4 b;
+    if (ok) {
+        b.x = fminf(fminf(r.x0, r.x1), r.x2) - blur; b.y = fmaxf(fmaxf(r.x0, r.x1), r.x2) + blur;
+        b.z = fminf(fminf(r.y0, r.y1), r.y2) - blur; b.w = fmaxf(fmaxf(r.y0, r.y1), r.y2) + blur;
+    } else {
+        b = make_float4(1e30f, -1e30f, 1e30f, -1e30f);
+    }
+    box[i] = b;
+    rec[i] = r;
+}
+
+FB_DEVINL float edge_fn(float px, float py, float ax, float ay, float bx, float by) {
+    return __fsub_rn(__fmul_rn(px - ax, by - ay), __fmul_rn(py - ay, bx - ax));
+}
+
+// squared distance from p to segment ab; also the clamped parameter t (t = 2 marks the degenerate-segment branch)
+FB_DEVINL float seg_dist2(float px, float py, float ax, float ay, float bx, float by, float& t_out) {
+    const float bax = bx - ax, bay = by - ay;
+    const float l2 = __fadd_rn(__fmul_rn(bax, bax), __fmul_rn(bay, bay));
+    if (l2 <= kEps) {
+        t_out = 2.f;
+        const float dx = px - bx, dy = py - by;
+        return __fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy));
+    }
+    float t = __fdiv_rn(__fadd_rn(__fmul_rn(bax, px - ax), __fmul_rn(bay, py - ay)), l2);
+    t = fminf(fmaxf(t, 0.f), 1.f);
+    t_out = t;
+    const float dx = px - __fadd_rn(ax, __fmul_rn(t, bax)), dy = py - __fadd_rn(ay, __fmul_rn(t, bay));
+    return __fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy));
+}
+
+struct Eval {
+    bool cand;          // candidate of this pixel
+    bool inside;
+    float d2;           // squared distance to the nearest edge
+    float pz;           // interpolated depth (>= 0 for a candidate)
+    int edge;           // nearest edge: 0 = v0v1, 1 = v0v2, 2 = v1v2
+    float t;            // its clamped parameter
+};
+
+FB_DEVINL Eval eval_face(const FaceRec& r, float px, float py, float blur, float blur_radius, int perspective) {
+    Eval e;
+    e.cand = false;
+    // bounding-box test of THIS pixel (the tile test only said the face touches the tile)
+    const float xmin = fminf(fminf(r.x0, r.x1), r.x2) - blur, xmax = fmaxf(fmaxf(r.x0, r.x1), r.x2) + blur;
+    const float ymin = fminf(fminf(r.y0, r.y1), r.y2) - blur, ymax = fmaxf(fmaxf(r.y0, r.y1), r.y2) + blur;
+    if (!(px >= xmin && px <= xmax && py >= ymin && py <= ymax)) return e;
+    const float area = edge_fn(r.x2, r.y2, r.x0, r.y0, r.x1, r.y1);
+    const float den = area + kEps;
+    const float w0 = __fdiv_rn(edge_fn(px, py, r.x1, r.y1, r.x2, r.y2), den);
+    const float w1 = __fdiv_rn(edge_fn(px, py, r.x2, r.y2, r.x0, r.y0), den);
+    const float w2 = __fdiv_rn(edge_fn(px, py, r.x0, r.y0, r.x1, r.y1), den);
+    e.inside = (w0 > 0.f) && (w1 > 0.f) && (w2 > 0.f);
+    float b0 = w0, b1 = w1, b2 = w2;
+    if (perspective) {
+        const float t0 = __fmul_rn(__fmul_rn(w0, r.z1), r.z2), t1 = __fmul_rn(__fmul_rn(r.z0, w1), r.z2), t2 = __fmul_rn(__fmul_rn(r.z0, r.z1), w2);
+        const float dn = fmaxf(__fadd_rn(__fadd_rn(t0, t1), t2), kEps);
+        b0 = __fdiv_rn(t0, dn); b1 = __fdiv_rn(t1, dn); b2 = __fdiv_rn(t2, dn);
+    }
+    const float c0 = fminf(fmaxf(b0, 0.f), 1.f), c1 = fminf(fmaxf(b1, 0.f), 1.f), c2 = fminf(fmaxf(b2, 0.f), 1.f);
+    const float cs = fmaxf(__fadd_rn(__fadd_rn(c0, c1), c2), 1e-5f);
+    e.pz = __fdiv_rn(__fadd_rn(__fadd_rn(__fmul_rn(c0, r.z0), __fmul_rn(c1, r.z1)), __fmul_rn(c2, r.z2)), cs);
+    if (!(e.pz >= 0.f)) return e;
+    float t01, t02, t12;
+    const float d01 = seg_dist2(px, py, r.x0, r.y0, r.x1, r.y1, t01);
+    const float d02 = seg_dist2(px, py, r.x0, r.y0, r.x2, r.y2, t02);
+    const float d12 = seg_dist2(px, py, r.x1, r.y1, r.x2, r.y2, t12);
+    e.d2 = d01; e.edge = 0; e.t = t01;
+    if (d02 < e.d2) { e.d2 = d02; e.edge = 1; e.t = t02; }
+    if (d12 < e.d2) { e.d2 = d12; e.edge = 2; e.t = t12; }
+    e.cand = e.inside || (e.d2 < blur_radius);
+    return e;
+}
+
+FB_DEVINL float sigmoidf_(float x) { return __fdiv_rn(1.f, 1.f + __expf(-x)); }
+
+struct TileShared {
+    int ids[kListCap];
+    FaceRec rec[kThreads];
+    int vid[kThreads][3];
+    int wcnt[kThreads / 32];
+    int nlist;
+    int overflow;
+};
+
+// Faces of mesh n whose grown box touches the tile, in face order, into sh.ids.  On overflow of the list the caller's
+// `spill` functor consumes the full list (evaluate what is there) and the list restarts.
+template <typename Spill>
+FB_DEVINL void build_tile_list(const SilParams& P, int n, float txmin, float txmax, float tymin, float tymax, TileShared& sh, Spill spill) {
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (tid == 0) { sh.nlist = 0; sh.overflow = 0; }
+    __syncthreads();
+    const float4* box = P.box + (size_t)n * P.F;
+    for (int base = 0; base < P.F; base += kThreads) {
+        const int f = base + tid;
+        bool hit = false;
+        if (f < P.F) {
+            const float4 b = __ldg(box + f);
+            hit = (b.x <= txmax) && (b.y >= txmin) && (b.z <= tymax) && (b.w >= tymin);
+        }
+        const unsigned m = __ballot_sync(0xffffffffu, hit);
+        if (lane == 0) sh.wcnt[warp] = __popc(m);
+        __syncthreads();
+        int before = 0, total = 0;
+#pragma unroll
+        for (int w = 0; w < kThreads / 32; ++w) { const int c = sh.wcnt[w]; if (w < warp) before += c; total += c; }
+        int nl = sh.nlist;
+        if (nl + total > kListCap) {                 // uniform branch: spill what we have, restart the list
+            __syncthreads();
+            spill(nl);
+            __syncthreads();
+            if (tid == 0) { sh.nlist = 0; sh.overflow = 1; }
+            __syncthreads();
+            nl = 0;
+        }
+        if (hit) sh.ids[nl + before + __popc(m & ((1u << lane) - 1u))] = f;
+        __syncthreads();
+        if (tid == 0) sh.nlist = nl + total;
+        __syncthreads();
+    }
+}
+
+// Evaluate the first `count` faces of the tile list for this thread's pixel: fn(j_in_list, face_id, rec, eval).
+template <bool kNeedVid, typename Fn>
+FB_DEVINL void for_each_listed(const SilParams& P, int n, int count, float px, float py, float blur, bool active, TileShared& sh, Fn fn) {
+    const int tid = threadIdx.x;
+    const FaceRec* rec = P.rec + (size_t)n * P.F;
+    for (int base = 0; base < count; base += kThreads) {
+        __syncthreads();
+        const int m = min(kThreads, count - base);
+        if (tid < m) {
+            const int f = sh.ids[base + tid];
+            const float4* src = reinterpret_cast<const float4*>(rec + f);
+            float4* dst = reinterpret_cast<float4*>(&sh.rec[tid]);
+            dst[0] = __ldg(src); dst[1] = __ldg(src + 1); dst[2] = __ldg(src + 2);
+            if (kNeedVid) { sh.vid[tid][0] = P.faces[3 * f]; sh.vid[tid][1] = P.faces[3 * f + 1]; sh.vid[tid][2] = P.faces[3 * f + 2]; }
+        }
+        __syncthreads();
+        for (int j = 0; j < m; ++j) {
+            Eval e;
+            e.cand = false;
+            if (active) e = eval_face(sh.rec[j], px, py, blur, P.blur_radius, P.perspective);
+            fn(j, sh.rec[j], e);
+        }
+    }
+    __syncthreads();
+}
+
+FB_DEVINL uint32_t depth_bits(float pz) { return __float_as_uint(pz) & 0x7fffffffu; }
+
+__global__ void __launch_bounds__(kThreads) sil_tile_fwd_kernel(const __grid_constant__ SilParams P) {
+    pdl_wait_trigger();
+    __shared__ TileShared sh;
+    const int n = blockIdx.z, tid = threadIdx.x;
+    const int col = blockIdx.x * kTile + (tid & (kTile - 1)), row = blockIdx.y * kTile + (tid >> 4);
+    const bool in_img = (col < P.W) && (row < P.H);
+    const float px = 1.f - __fdiv_rn((float)(2 * col + 1), (float)P.W), py = 1.f - __fdiv_rn((float)(2 * row + 1), (float)P.H);
+    const int c_hi = min(blockIdx.x * kTile + kTile - 1, P.W - 1), r_hi = min(blockIdx.y * kTile + kTile - 1, P.H - 1);
+    const float txmax = 1.f - __fdiv_rn((float)(2 * blockIdx.x * kTile + 1), (float)P.W), txmin = 1.f - __fdiv_rn((float)(2 * c_hi + 1), (float)P.W);
+    const float tymax = 1.f - __fdiv_rn((float)(2 * blockIdx.y * kTile + 1), (float)P.H), tymin = 1.f - __fdiv_rn((float)(2 * r_hi + 1), (float)P.H);
+    const float blur = sqrtf(P.blur_radius), inv_sigma = __fdiv_rn(1.f, P.sigma);
+
+    int cnt = 0;
+    float prod = 1.f;
+    uint32_t zlo = 0xffffffffu, zhi = 0u;           // depth range of this pixel's candidates (bit patterns)
+    auto accumulate = [&](int, const FaceRec&, const Eval& e) {
+        if (e.cand) {
+            ++cnt;
+            prod = __fmul_rn(prod, 1.f - sigmoidf_((e.inside ? e.d2 : -e.d2) * inv_sigma));
+            const uint32_t b = depth_bits(e.pz);
+            zlo = min(zlo, b); zhi = max(zhi, b);
+        }
+    };
+    build_tile_list(P, n, txmin, txmax, tymin, tymax, sh,
+                    [&](int count) { for_each_listed<false>(P, n, count, px, py, blur, in_img, sh, accumulate); });
+    const int nlist = sh.nlist;
+    const bool spilled = sh.overflow != 0;
+    for_each_listed<false>(P, n, nlist, px, py, blur, in_img, sh, accumulate);
+
+    uint2 sel = make_uint2(0xffffffffu, 0u);
+    const bool sat = in_img && cnt > P.K;
+    if (__syncthreads_or(sat)) {
+        if (spilled) {
+            if (sat) atomicExch(P.overflow, 1u);     // cannot truncate exactly: the host reports it (findb200_silhouette_status)
+        } else {
+            // K-th smallest depth of this pixel's candidates: 16-ary search on the bit pattern (non-negative floats order as
+            // uints) inside [zlo, zhi], re-evaluating the tile's faces each round instead of storing per-pixel lists.
+            // Invariant: #(bits < lo) = below < K <= #(bits <= hi).
+            uint32_t lo = zlo, hi = zhi;
+            int below = 0;
+            bool searching = sat && lo < hi;
+            while (__syncthreads_or(searching)) {
+                const uint32_t step = ((hi - lo) >> 4) + 1u;
+                uint32_t t[15];
+                int c[15];
+#pragma unroll
+                for (int i = 0; i < 15; ++i) {
+                    const unsigned long long v = (unsigned long long)lo + (unsigned long long)step * (i + 1) - 1ull;
+                    t[i] = v > hi ? hi : (uint32_t)v;
+                    c[i] = 0;
+                }
+                for_each_listed<false>(P, n, nlist, px, py, blur, searching, sh, [&](int, const FaceRec&, const Eval& e) {
+                    if (!e.cand) return;
+                    const uint32_t b = depth_bits(e.pz);
+                    if (b < lo || b > hi) return;
+#pragma unroll
+                    for (int i = 0; i < 15; ++i) c[i] += (b <= t[i]) ? 1 : 0;
+                });
+                if (searching) {
+                    int k = 15;
+#pragma unroll
+                    for (int i = 14; i >= 0; --i) if (below + c[i] >= P.K) k = i;
+                    uint32_t nlo = lo, nhi = hi;
+                    int add = 0;
+#pragma unroll
+                    for (int i = 0; i < 15; ++i) {
+                        if (k == i) nhi = t[i];
+                        if (k == i + 1) { nlo = t[i] + 1u; add = c[i]; }
+                    }
+                    lo = nlo; hi = nhi; below += add;
+                    searching = lo < hi;
+                }
+            }
+            const uint32_t thr = lo;
+            const int ties = P.K - below;
+            int seen = 0;
+            float prod2 = 1.f;
+            for_each_listed<false>(P, n, nlist, px, py, blur, sat, sh, [&](int, const FaceRec&, const Eval& e) {
+                if (!e.cand) return;
+                const uint32_t b = depth_bits(e.pz);
+                const bool keep = (b < thr) || (b == thr && seen++ < ties);
+                if (keep) prod2 = __fmul_rn(prod2, 1.f - sigmoidf_((e.inside ? e.d2 : -e.d2) * inv_sigma));
+            });
+            if (sat) { prod = prod2; sel = make_uint2(thr, (uint32_t)ties); }
+        }
+    }
+    if (in_img) {
+        const size_t o = ((size_t)n * P.H + row) * P.W + col;
+        P.alpha[o] = 1.f - prod;
+        if (P.prod) P.prod[o] = prod;
+        if (P.sel) P.sel[o] = sel;
+    }
+}
+
+__global__ void __launch_bounds__(kThreads) sil_tile_bwd_kernel(const __grid_constant__ SilParams P) {
+    pdl_wait_trigger();
+    __shared__ TileShared sh;
+    const int n = blockIdx.z, tid = threadIdx.x, lane = tid & 31;
+    const int col = blockIdx.x * kTile + (tid & (kTile - 1)), row = blockIdx.y * kTile + (tid >> 4);
+    const bool in_img = (col < P.W) && (row < P.H);
+    const float px = 1.f - __fdiv_rn((float)(2 * col + 1), (float)P.W), py = 1.f - __fdiv_rn((float)(2 * row + 1), (float)P.H);
+    const int c_hi = min(blockIdx.x * kTile + kTile - 1, P.W - 1), r_hi = min(blockIdx.y * kTile + kTile - 1, P.H - 1);
+    const float txmax = 1.f - __fdiv_rn((float)(2 * blockIdx.x * kTile + 1), (float)P.W), txmin = 1.f - __fdiv_rn((float)(2 * c_hi + 1), (float)P.W);
+    const float tymax = 1.f - __fdiv_rn((float)(2 * blockIdx.y * kTile + 1), (float)P.H), tymin = 1.f - __fdiv_rn((float)(2 * r_hi + 1), (float)P.H);
+    const float blur = sqrtf(P.blur_radius), inv_sigma = __fdiv_rn(1.f, P.sigma);
+
+    float coef = 0.f;                      // grad_alpha * prod / sigma of this pixel
+    uint2 sel = make_uint2(0xffffffffu, 0u);
+    if (in_img) {
+        const size_t o = ((size_t)n * P.H + row) * P.W + col;
+        coef = P.grad_alpha[o] * P.prod[o] * inv_sigma;
+        sel = P.sel[o];
+    }
+    // a tile none of whose pixels carries gradient (far inside or far outside the silhouette) skips the walk
+    if (!__syncthreads_or(coef != 0.f)) return;
+    const bool active = in_img && coef != 0.f;
+    int seen = 0;
+    float* gv = P.grad_verts + (size_t)n * P.V * 3;
+    auto scatter = [&](int j, const FaceRec& r, const Eval& e) {
+        float g[3][2] = {{0.f, 0.f}, {0.f, 0.f}, {0.f, 0.f}};
+        bool contributes = false;
+        if (e.cand) {
+            const uint32_t b = depth_bits(e.pz);
+            const bool keep = (sel.x == 0xffffffffu) || (b < sel.x) || (b == sel.x && seen++ < (int)sel.y);
+            if (keep) {
+                const float p = sigmoidf_((e.inside ? e.d2 : -e.d2) * inv_sigma);
+                const float c = (e.inside ? coef : -coef) * p;          // d alpha / d d2
+                if (c != 0.f) {
+                    const int ia = (e.edge == 2) ? 1 : 0, ib = (e.edge == 0) ? 1 : 2;
+                    const float ax = ia == 0 ? r.x0 : r.x1, ay = ia == 0 ? r.y0 : r.y1;
+                    const float bx = ib == 1 ? r.x1 : r.x2, by = ib == 1 ? r.y1 : r.y2;
+                    const float t = (e.t > 1.5f) ? 1.f : e.t;            // degenerate segment: distance to b
+                    const float rx = px - (ax + t * (bx - ax)), ry = py - (ay + t * (by - ay));
+                    const float ga = -2.f * (1.f - t) * c, gb = -2.f * t * c;
+                    g[ia][0] = ga * rx; g[ia][1] = ga * ry;
+                    g[ib][0] = gb * rx; g[ib][1] = gb * ry;
+                    contributes = true;
+                }
+            }
+        }
+        if (__ballot_sync(0xffffffffu, contributes) == 0u) return;
+#pragma unroll
+        for (int k = 0; k < 3; ++k)
+#pragma unroll
+            for (int d = 0; d < 2; ++d) {
+                float v = g[k][d];
+#pragma unroll
+                for (int s = 16; s > 0; s >>= 1) v += __shfl_xor_sync(0xffffffffu, v, s);
+                if (lane == 0 && v != 0.f) atomicAdd(gv + (size_t)sh.vid[j][k] * 3 + d, v);
+            }
+    };
+    build_tile_list(P, n, txmin, txmax, tymin, tymax, sh,
+                    [&](int count) { for_each_listed<true>(P, n, count, px, py, blur, active, sh, scatter); });
+    for_each_listed<true>(P, n, sh.nlist, px, py, blur, active, sh, scatter);
+}
+
+}  // namespace raster
+}  // namespace fb
+
+using namespace fb;
+using namespace fb::raster;
+
+namespace {
+struct WsLayout { size_t box, rec, flag, total; };
+WsLayout ws_layout(int N, int F) {
+    WsLayout L;
+    size_t o = 0;
+    L.box = o; o += ((size_t)N * F * sizeof(float4) + 255) & ~(size_t)255;
+    L.rec = o; o += ((size_t)N * F * sizeof(FaceRec) + 255) & ~(size_t)255;
+    L.flag = o; o += 256;
+    L.total = o;
+    return L;
+}
+int fill(SilParams& P, void* ws, size_t ws_bytes, int N, int V, int F, int H, int W, float blur_radius, float sigma, int K, int perspective) {
+    FB_REQUIRE(N >= 0 && V >= 1 && F >= 0 && H >= 1 && W >= 1, FINDB200_ERR_SHAPE, "silhouette: bad shape N=%d V=%d F=%d H=%d W=%d", N, V, F, H, W);
+    FB_REQUIRE(N <= 65535, FINDB200_ERR_SHAPE, "silhouette: at most 65535 meshes x views per call (got %d)", N);
+    FB_REQUIRE(blur_radius >= 0.f && sigma > 0.f && K >= 1, FINDB200_ERR_ARG, "silhouette: blur_radius >= 0, sigma > 0 and faces_per_pixel >= 1 required");
+    const WsLayout L = ws_layout(N, F);
+    FB_REQUIRE(ws && ws_bytes >= L.total, FINDB200_ERR_WORKSPACE, "silhouette: workspace too small (%zu < %zu)", ws_bytes, L.total);
+    memset(&P, 0, sizeof(P));
+    P.box = (const float4*)((char*)ws + L.box);
+    P.rec = (const FaceRec*)((char*)ws + L.rec);
+    P.overflow = (unsigned int*)((char*)ws + L.flag);
+    P.N = N; P.F = F; P.H = H; P.W = W; P.V = V;
+    P.blur_radius = blur_radius; P.sigma = sigma; P.K = K; P.perspective = perspective;
+    return 0;
+}
+}  // namespace
+
+extern "C" size_t findb200_silhouette_workspace_bytes(int N, int F) { return ws_layout(N > 0 ? N : 0, F > 0 ? F : 0).total; }
+
+extern "C" int findb200_silhouette_forward(const float* verts_ndc, const int32_t* faces, int N, int V, int F, int H, int W,
+                                           float blur_radius, float sigma, int faces_per_pixel, int perspective_correct,
+                                           float* alpha, float* prod, void* sel, void* ws, size_t ws_bytes, void* stream) {
+    cudaStream_t st = (cudaStream_t)stream;
+    SilParams P;
+    int rc = fill(P, ws, ws_bytes, N, V, F, H, W, blur_radius, sigma, faces_per_pixel, perspective_correct);
+    if (rc) return rc;
+    FB_REQUIRE(verts_ndc && (faces || F == 0) && alpha, FINDB200_ERR_ARG, "silhouette_forward: null argument");
+    if (N == 0) return 0;
+    P.alpha = alpha; P.prod = prod; P.sel = (uint2*)sel;
+    FB_CUDA(cudaMemsetAsync(P.overflow, 0, sizeof(unsigned int), st));
+    if (F > 0) {
+        FB_MARK("face_setup", st);
+        const long long tot = (long long)N * F;
+        FB_CUDA(launch_pdl(face_setup_kernel, dim3((unsigned)((tot + 255) / 256)), dim3(256), 0, st, verts_ndc, faces, N, V, F,
+                           sqrtf(blur_radius), (float4*)P.box, (FaceRec*)P.rec));
+    }
+    FB_MARK("sil_tile_fwd", st);
+    FB_CUDA(launch_pdl(sil_tile_fwd_kernel, dim3((W + kTile - 1) / kTile, (H + kTile - 1) / kTile, N), dim3(kThreads), 0, st, P));
+    FB_MARK_END(st);
+    return 0;
+}
+
+// The workspace must be the one the forward call filled (face records); grad_verts is accumulated into (+=) x and y, z gets none.
+extern "C" int findb200_silhouette_backward(const float* grad_alpha, const int32_t* faces, int N, int V, int F, int H, int W,
+                                            float blur_radius, float sigma, int faces_per_pixel, int perspective_correct,
+                                            const float* prod, const void* sel, float* grad_verts_ndc, void* ws, size_t ws_bytes, void* stream) {
+    cudaStream_t st = (cudaStream_t)stream;
+    SilParams P;
+    int rc = fill(P, ws, ws_bytes, N, V, F, H, W, blur_radius, sigma, faces_per_pixel, perspective_correct);
+    if (rc) return rc;
+    if (N == 0 || F == 0) return 0;
+    FB_REQUIRE(grad_alpha && faces && prod && sel && grad_verts_ndc, FINDB200_ERR_ARG, "silhouette_backward: null argument");
+    P.grad_alpha = grad_alpha; P.prod = (float*)prod; P.sel = (uint2*)sel; P.grad_verts = grad_verts_ndc; P.faces = faces;
+    FB_MARK("sil_tile_bwd", st);
+    FB_CUDA(launch_pdl(sil_tile_bwd_kernel, dim3((W + kTile - 1) / kTile, (H + kTile - 1) / kTile, N), dim3(kThreads), 0, st, P));
+    FB_MARK_END(st);
+    return 0;
+}
+
+// 1 when a tile of the last forward call on this workspace could not apply the K truncation exactly (more than 4096 faces on
+// one 16 x 16 tile AND a pixel with more than faces_per_pixel candidates): alpha there multiplies ALL candidates.  Synchronises.
+extern "C" int findb200_silhouette_status(const void* ws, int N, int F, void* stream) {
+    unsigned int flag = 0;
+    const WsLayout L = ws_layout(N, F);
+    FB_CUDA(cudaMemcpyAsync(&flag, (const char*)ws + L.flag, sizeof(flag), cudaMemcpyDeviceToHost, (cudaStream_t)stream));
+    FB_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
+    return (int)flag;
+}

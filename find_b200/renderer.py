@@ -1,0 +1,179 @@
+"""find_b200/renderer.py — the silhouette half of FIND's differentiable renderer on the sm_100a rasteriser of csrc/raster.cu
+(first slice).
+
+Mirrors /root/reference/src/model/renderer.py:
+  * ``FootRenderer(image_size, device)`` (:107-141), ``sample_views`` (:144-153), ``linspace_views`` (:156-174),
+    ``view_from`` (:176-205), ``combine_views`` (:207-208) — same names, argument meaning and return shapes;
+  * ``FootRenderer.forward(meshes, R, T, return_mask=True, mask_with_grad=True)`` (:247-311): every mesh is rendered from
+    every view by ``FoVPerspectiveCameras(R, T, znear=0.02)`` and the mask is the alpha channel of ``SoftSilhouetteShader``
+    over ``rasterize_meshes(faces_per_pixel=100, blur_radius=log(1/1e-4 - 1) * 1e-4)``; returns ``{'mask': [meshes, views, S, S]}``.
+``return_images`` / ``return_features`` / ``return_depth`` / ``keypoints`` (Phong shading, feature blending, point
+rendering) are NOT built yet and raise NotImplementedError — they never fall back to another renderer.
+
+The camera transform (a 3x3 rotation, a translation and the perspective divide per vertex) is done with torch ops so that
+autograd carries the silhouette gradient from NDC back to world-space vertices; the rasterisation, the blend and their
+backward are libfindb200.so (``findb200_silhouette_forward/backward``).  There is no CPU path (CPU tensors raise).
+"""
+from __future__ import annotations
+
+import math
+
+import numpy as np
+import torch
+from torch import nn
+
+from . import _lib
+from .mesh import Meshes, _as_i32_faces
+
+SIGMA = 1e-4                                            # BlendParams(sigma=1e-4), renderer.py:121
+
+
+def look_at_rotation(eye: torch.Tensor, at=((0.0, 0.0, 0.0),), up=((1.0, 0.0, 0.0),)) -> torch.Tensor:
+    """pytorch3d.renderer.look_at_rotation: [n,3] camera positions -> R [n,3,3] with X_view = X_world @ R + T."""
+    eye = torch.as_tensor(eye, dtype=torch.float32).reshape(-1, 3)
+    at_t = torch.as_tensor(at, dtype=torch.float32).reshape(-1, 3).expand_as(eye)
+    up_t = torch.as_tensor(up, dtype=torch.float32).reshape(-1, 3).expand_as(eye)
+    z = torch.nn.functional.normalize(at_t - eye, eps=1e-5, dim=1)
+    x = torch.nn.functional.normalize(torch.cross(up_t, z, dim=1), eps=1e-5, dim=1)
+    y = torch.nn.functional.normalize(torch.cross(z, x, dim=1), eps=1e-5, dim=1)
+    degenerate = torch.isclose(x, torch.zeros(()), atol=5e-3).all(dim=1, keepdim=True)
+    if degenerate.any():                                # up parallel to the view direction: rebuild x from y and z
+        x = torch.where(degenerate, torch.nn.functional.normalize(torch.cross(y, z, dim=1), eps=1e-5, dim=1), x)
+    return torch.stack([x, y, z], dim=1).transpose(1, 2)
+
+
+def look_at_view_transform(dist=1.0, elev=0.0, azim=0.0, at=((0.0, 0.0, 0.0),), up=((0.0, 1.0, 0.0),)):
+    """pytorch3d.renderer.look_at_view_transform (degrees) -> R [n,3,3], T [n,3]."""
+    d, e, a = (torch.as_tensor(np.asarray(v), dtype=torch.float32).reshape(-1) for v in (dist, elev, azim))
+    n = max(d.numel(), e.numel(), a.numel())
+    d, e, a = d.expand(n), torch.deg2rad(e.expand(n)), torch.deg2rad(a.expand(n))
+    eye = torch.stack([d * torch.cos(e) * torch.sin(a), d * torch.sin(e), d * torch.cos(e) * torch.cos(a)], dim=1)
+    eye = eye + torch.as_tensor(at, dtype=torch.float32).reshape(-1, 3)
+    R = look_at_rotation(eye, at, up)
+    T = -torch.bmm(R.transpose(1, 2), eye[:, :, None])[:, :, 0]
+    return R, T
+
+
+class _Silhouette(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, verts_ndc, faces_i32, H, W, blur_radius, sigma, K, perspective):
+        lib = _lib.load()
+        dev = _lib.require_cuda(verts_ndc)
+        v = verts_ndc.contiguous().float()
+        N, V, F = v.shape[0], v.shape[1], faces_i32.shape[0]
+        alpha = torch.empty(N, H, W, dtype=torch.float32, device=dev)
+        prod = torch.empty_like(alpha)
+        sel = torch.empty(N, H, W, 2, dtype=torch.int32, device=dev)
+        ws = torch.empty(int(lib.findb200_silhouette_workspace_bytes(N, F)), dtype=torch.uint8, device=dev)
+        with torch.cuda.device(dev):
+            rc = lib.findb200_silhouette_forward(_lib.ptr(v), _lib.ptr(faces_i32), N, V, F, H, W, float(blur_radius), float(sigma),
+                                                 int(K), int(bool(perspective)), _lib.ptr(alpha), _lib.ptr(prod), _lib.ptr(sel),
+                                                 _lib.ptr(ws), ws.numel(), _lib.stream_ptr(dev))
+        _lib.check(rc, "findb200_silhouette_forward")
+        ctx.save_for_backward(faces_i32, prod, sel, ws)
+        ctx.cfg = (N, V, F, H, W, float(blur_radius), float(sigma), int(K), int(bool(perspective)))
+        return alpha
+
+    @staticmethod
+    def backward(ctx, g_alpha):
+        lib = _lib.load()
+        faces_i32, prod, sel, ws = ctx.saved_tensors
+        N, V, F, H, W, blur_radius, sigma, K, perspective = ctx.cfg
+        dev = g_alpha.device
+        gv = torch.zeros(N, V, 3, dtype=torch.float32, device=dev)
+        g = g_alpha.contiguous().float()
+        with torch.cuda.device(dev):
+            rc = lib.findb200_silhouette_backward(_lib.ptr(g), _lib.ptr(faces_i32), N, V, F, H, W, blur_radius, sigma, K, perspective,
+                                                  _lib.ptr(prod), _lib.ptr(sel), _lib.ptr(gv), _lib.ptr(ws), ws.numel(),
+                                                  _lib.stream_ptr(dev))
+        _lib.check(rc, "findb200_silhouette_backward")
+        return gv, None, None, None, None, None, None, None
+
+
+def rasterize_silhouette(verts_ndc: torch.Tensor, faces: torch.Tensor, image_size, blur_radius: float = None, sigma: float = SIGMA,
+                         faces_per_pixel: int = 100, perspective_correct: bool = True) -> torch.Tensor:
+    """verts_ndc [N,V,3] (x, y NDC; z view depth), faces [F,3] shared -> alpha [N,H,W]; differentiable w.r.t. x, y."""
+    H, W = (image_size, image_size) if isinstance(image_size, int) else image_size
+    if blur_radius is None:
+        blur_radius = math.log(1.0 / 1e-4 - 1.0) * sigma
+    if faces.dim() != 2 or faces.shape[1] != 3:
+        raise ValueError("faces must be [F,3] (one topology shared by the batch)")
+    f = faces if faces.dtype == torch.int32 else faces.to(torch.int32)
+    return _Silhouette.apply(verts_ndc, f.contiguous(), int(H), int(W), blur_radius, sigma, faces_per_pixel, perspective_correct)
+
+
+class FootRenderer(nn.Module):
+    def __init__(self, image_size, device="cuda", background_color=(1.0, 1.0, 1.0), bin_size=None, z_clip_value=None,
+                 max_faces_per_bin=None):
+        super().__init__()
+        self.image_size = image_size
+        self.device = torch.device(device)
+        self.fov, self.znear, self.zfar = 60.0, 0.02, 100.0          # FoVPerspectiveCameras defaults + renderer.py:258
+        self.sigma = SIGMA
+        self.blur_radius = float(np.log(1.0 / 1e-4 - 1.0) * self.sigma)   # renderer.py:124
+        self.faces_per_pixel = 100                                   # renderer.py:125
+
+    # ---- view helpers (host-side numpy / torch, as in the reference) ---------------------------------------------------
+    def sample_views(self, nviews=1, dist_mean=0.25, dist_std=0.05, elev_min=-90, elev_max=90, azim_min=0, azim_max=360,
+                     seed: int = None):
+        if seed:
+            np.random.seed(seed)
+        distances = np.random.normal(dist_mean, dist_std, (nviews))
+        elev = np.random.uniform(elev_min, elev_max, (nviews))
+        azim = np.random.uniform(azim_min, azim_max, (nviews))
+        return look_at_view_transform(dist=distances, elev=elev, azim=azim, up=((1, 0, 0),))
+
+    def linspace_views(self, nviews=1, dist=0.3, dist_min=None, dist_max=None, elev_min=None, elev_max=None, azim_min=None,
+                       azim_max=None, at=((0, 0, 0),)):
+        if dist_min is not None:
+            dist = np.linspace(dist_min, dist_max, nviews)
+        elev = 0 if elev_min is None else np.linspace(elev_min, elev_max, nviews)
+        azim = 0 if azim_min is None else np.linspace(azim_min, azim_max, nviews)
+        return look_at_view_transform(dist=dist, elev=elev, azim=azim, up=((1, 0, 0),), at=at)
+
+    def view_from(self, view_kw="topdown"):
+        table = {"topdown": (0.3, 0, 0, (0, 0, 0)), "side1": (0.35, 90, 0, (0, 0, 0)), "side2": (0.35, -90, 180, (0, 0, 0)),
+                 "toes": (0.1, 0, 0, (0.1, 0, 0)), "45": (0.35, -45, 0, (0, 0, 0)), "60": (0.35, -60, 0, (0, 0, 0))}
+        if isinstance(view_kw, str):
+            view_kw = [view_kw]
+        Rs, Ts = [], []
+        for v in view_kw:
+            assert v in table, f"View description `{view_kw}` not understood"
+            dist, elev, azim, point = table[v]
+            R, T = look_at_view_transform(dist=dist, elev=elev, azim=azim, up=((1, 0, 0),), at=(point,))
+            Rs.append(R[0]); Ts.append(T[0])
+        return torch.stack(Rs), torch.stack(Ts)
+
+    def combine_views(self, R1, T1, R2, T2):
+        return torch.cat([R1, R2], dim=0), torch.cat([T1, T2], dim=0)
+
+    # ---- camera -------------------------------------------------------------------------------------------------------
+    def project(self, verts: torch.Tensor, R: torch.Tensor, T: torch.Tensor) -> torch.Tensor:
+        """verts [M,V,3] world, R [views,3,3], T [views,3] -> [M*views,V,3]: NDC x, y and view-space depth, mesh-major like
+        ``input_meshes.extend(num_views)`` with ``torch.cat([R]*num_meshes)`` (renderer.py:253-257)."""
+        M, V = verts.shape[0], verts.shape[1]
+        nv = R.shape[0]
+        R = R.to(verts.device, verts.dtype)
+        T = T.to(verts.device, verts.dtype)
+        view = torch.einsum("mvi,kij->mkvj", verts, R) + T[None, :, None, :]
+        s = 1.0 / math.tan(math.radians(self.fov) / 2.0)
+        z = view[..., 2]
+        ndc = torch.stack([s * view[..., 0] / z, s * view[..., 1] / z, z], dim=-1)
+        return ndc.reshape(M * nv, V, 3)
+
+    def forward(self, input_meshes: Meshes, R, T, return_images=False, return_depth=False, return_mask=True, mask_with_grad=True,
+                mask_out_faces=False, masked_faces=None, keypoints=None, keypoints_blend=False, lights=None,
+                return_mask_out_masks=False, return_features=False, features=None) -> dict:
+        if return_images or return_features or return_depth or keypoints is not None or mask_out_faces:
+            raise NotImplementedError("find_b200.renderer: only the soft-silhouette mask (return_mask=True, return_images=False) is "
+                                      "built; Phong / feature / depth / keypoint rendering is the rest of SURVEY.md §8(f) row 4")
+        if not return_mask:
+            return {}
+        verts = input_meshes.verts_padded()
+        faces, shared = _as_i32_faces(input_meshes)
+        if not shared:
+            raise NotImplementedError("find_b200.renderer: the meshes of one call must share their topology (FIND's template)")
+        num_views, num_meshes = R.shape[0], len(input_meshes)
+        ndc = self.project(verts, R, T)
+        alpha = rasterize_silhouette(ndc, faces, self.image_size, self.blur_radius, self.sigma, self.faces_per_pixel, True)
+        return {"mask": alpha.reshape(num_meshes, num_views, self.image_size, self.image_size)}

@@ -177,6 +177,28 @@ int findb200_mesh_smooth(const float* verts, int N, int V, const int32_t* faces,
                          float* grad_verts, int accumulate, void* workspace, size_t workspace_bytes, void* stream);
 
 /* ------------------------------------------------------------------------------------------------------
+ * Soft-silhouette rasteriser (first slice): pytorch3d rasterize_meshes (faces_per_pixel = 100,
+ * blur_radius = log(1/1e-4 - 1) * sigma, clipped perspective-correct barycentrics) + SoftSilhouetteShader as set up at
+ * src/model/renderer.py:122-128 and called at renderer.py:208-245, 309-311 (FootRenderer.forward(return_mask=True)).
+ * verts_ndc [N,V,3] fp32: x, y in PyTorch3D NDC (+x left, +y up), z = view-space depth — what MeshRasterizer.transform
+ * produces; N counts meshes x views.  faces [F,3] int32 shared by all N.  alpha [N,H,W] = 1 - prod_k (1 - sigmoid(-signed
+ * squared distance_k / sigma)) over the faces_per_pixel candidates of smallest depth (earlier face on ties).
+ * prod [N,H,W] fp32 and sel [N,H,W] x 8 bytes are saved for the backward (may be NULL for inference).  The backward ADDS
+ * d alpha / d (x, y) into grad_verts_ndc [N,V,3] (z receives no gradient) and must be given the workspace the forward
+ * filled.  findb200_silhouette_status synchronises and returns 1 if a tile could not apply the K truncation exactly
+ * (> 4096 faces on one 16 x 16 tile together with a pixel of more than faces_per_pixel candidates).
+ * ------------------------------------------------------------------------------------------------------ */
+size_t findb200_silhouette_workspace_bytes(int N, int F);
+int findb200_silhouette_forward(const float* verts_ndc, const int32_t* faces, int N, int V, int F, int H, int W,
+                                float blur_radius, float sigma, int faces_per_pixel, int perspective_correct,
+                                float* alpha, float* prod, void* sel, void* workspace, size_t workspace_bytes, void* stream);
+int findb200_silhouette_backward(const float* grad_alpha, const int32_t* faces, int N, int V, int F, int H, int W,
+                                 float blur_radius, float sigma, int faces_per_pixel, int perspective_correct,
+                                 const float* prod, const void* sel, float* grad_verts_ndc, void* workspace,
+                                 size_t workspace_bytes, void* stream);
+int findb200_silhouette_status(const void* workspace, int N, int F, void* stream);
+
+/* ------------------------------------------------------------------------------------------------------
  * Optimiser updates: torch.optim.Adam(main_params / latent_params) and
  * torch.optim.SGD(reg_params, momentum=0.9) as stepped at src/train/train.py:161-168, src/train/trainer.py:122-123.
  * One launch updates every tensor of the table (dense updates, like torch on dense .grad).  `tensors` is a HOST array of

@@ -1,0 +1,149 @@
+"""oracle/raster_oracle.py — CPU restatement of the soft-silhouette half of FIND's differentiable renderer.  TEST
+INFRASTRUCTURE ONLY: imported by tests/ and __graft_entry__.smoke(); never by the product path.
+
+Follows
+  * /root/reference/src/model/renderer.py:122-128 (silhouette RasterizationSettings: blur_radius = log(1/1e-4 - 1) * sigma,
+    sigma = 1e-4, faces_per_pixel = 100), :208-245 (``rasterize`` -> ``rasterize_meshes`` with clip_barycentric_coords =
+    blur_radius > 0, perspective_correct = cameras.is_perspective()), :309-311 (``SoftSilhouetteShader`` alpha channel);
+  * PyTorch3D @ 1706eb82 (requirements_mac_linux.txt:31, NOT on this box), restated from its published algorithm:
+    renderer/mesh/rasterize_meshes.{py,cu} (pixel (r, c) has NDC centre (1 - (2c+1)/W, 1 - (2r+1)/H); a face is a candidate
+    of a pixel when it is not degenerate (|area| > 1e-8), not entirely behind the camera, the pixel lies inside its
+    bounding box grown by sqrt(blur_radius), the interpolated depth pz (perspective-corrected, clipped barycentrics) is
+    >= 0, and the pixel is inside the face or its SQUARED distance to the nearest edge is < blur_radius; the K candidates
+    of smallest pz are kept, the earlier face on ties), utils/geometry (edge function, point-segment distance) and
+    renderer/blending.py::sigmoid_alpha_blend (alpha = 1 - prod_k (1 - sigmoid(-signed_dist_k / sigma))).
+    Face clipping against z_clip_value (faces that straddle the camera plane) is not restated: FIND's cameras look at a
+    foot from 0.1-0.35 m (renderer.py:146-205) and no face crosses znear / 2.
+
+PARITY UNPINNED against PyTorch3D itself (absent; the reference ships no rendered vectors); pinned by known-answer tests in
+tests/test_oracle_raster.py (one triangle: analytic inside / outside distances, K truncation by depth, fp64 autograd vs
+finite differences).
+"""
+from __future__ import annotations
+
+import math
+
+import torch
+
+K_EPS = 1e-8
+
+
+def blur_radius_for(sigma: float = 1e-4) -> float:
+    """renderer.py:124 — np.log(1. / 1e-4 - 1.) * sigma."""
+    return math.log(1.0 / 1e-4 - 1.0) * sigma
+
+
+def pixel_centres(H: int, W: int, dtype=torch.float32):
+    r = torch.arange(H, dtype=dtype)
+    c = torch.arange(W, dtype=dtype)
+    y = 1.0 - (2.0 * r + 1.0) / H
+    x = 1.0 - (2.0 * c + 1.0) / W
+    return x, y
+
+
+def _edge(px, py, ax, ay, bx, by):
+    return (px - ax) * (by - ay) - (py - ay) * (bx - ax)
+
+
+def _seg_dist2(px, py, ax, ay, bx, by):
+    bax, bay = bx - ax, by - ay
+    l2 = bax * bax + bay * bay
+    safe = torch.where(l2 <= K_EPS, torch.ones_like(l2), l2)
+    t = ((bax * (px - ax) + bay * (py - ay)) / safe).clamp(0.0, 1.0)
+    qx, qy = ax + t * bax, ay + t * bay
+    d_seg = (px - qx) ** 2 + (py - qy) ** 2
+    d_pt = (px - bx) ** 2 + (py - by) ** 2
+    return torch.where(l2 <= K_EPS, d_pt, d_seg)
+
+
+def silhouette(verts: torch.Tensor, faces: torch.Tensor, H: int, W: int, blur_radius: float | None = None,
+               sigma: float = 1e-4, faces_per_pixel: int = 100, perspective_correct: bool = True, return_aux: bool = False):
+    """verts [V,3] in NDC (x left, y up, z depth; any float dtype, autograd flows to x, y), faces [F,3] int64 -> alpha [H,W].
+    Dense [H*W, F] evaluation: small cases only."""
+    if blur_radius is None:
+        blur_radius = blur_radius_for(sigma)
+    dt = verts.dtype
+    fv = verts[faces]                                                   # [F,3,3]
+    x0, y0, z0 = fv[:, 0, 0], fv[:, 0, 1], fv[:, 0, 2]
+    x1, y1, z1 = fv[:, 1, 0], fv[:, 1, 1], fv[:, 1, 2]
+    x2, y2, z2 = fv[:, 2, 0], fv[:, 2, 1], fv[:, 2, 2]
+    xs, ys = pixel_centres(H, W, dt)
+    px = xs[None, :].expand(H, W).reshape(-1, 1)
+    py = ys[:, None].expand(H, W).reshape(-1, 1)
+    area = _edge(x2, y2, x0, y0, x1, y1)                                # [F]
+    blur = math.sqrt(blur_radius)
+    xmin, xmax = torch.minimum(torch.minimum(x0, x1), x2) - blur, torch.maximum(torch.maximum(x0, x1), x2) + blur
+    ymin, ymax = torch.minimum(torch.minimum(y0, y1), y2) - blur, torch.maximum(torch.maximum(y0, y1), y2) + blur
+    zmax = torch.maximum(torch.maximum(z0, z1), z2)
+    face_ok = (area.abs() > K_EPS) & (zmax >= 0)
+    in_box = (px >= xmin) & (px <= xmax) & (py >= ymin) & (py <= ymax)
+    den = area + K_EPS
+    w0 = _edge(px, py, x1, y1, x2, y2) / den
+    w1 = _edge(px, py, x2, y2, x0, y0) / den
+    w2 = _edge(px, py, x0, y0, x1, y1) / den
+    inside = (w0 > 0) & (w1 > 0) & (w2 > 0)
+    if perspective_correct:
+        t0, t1, t2 = w0 * z1 * z2, z0 * w1 * z2, z0 * z1 * w2
+        dn = (t0 + t1 + t2).clamp(min=K_EPS)
+        b0, b1, b2 = t0 / dn, t1 / dn, t2 / dn
+    else:
+        b0, b1, b2 = w0, w1, w2
+    c0, c1, c2 = b0.clamp(0, 1), b1.clamp(0, 1), b2.clamp(0, 1)
+    cs = (c0 + c1 + c2).clamp(min=1e-5)
+    pz = (c0 * z0 + c1 * z1 + c2 * z2) / cs
+    d2 = torch.minimum(torch.minimum(_seg_dist2(px, py, x0, y0, x1, y1), _seg_dist2(px, py, x0, y0, x2, y2)),
+                       _seg_dist2(px, py, x1, y1, x2, y2))
+    cand = face_ok[None, :] & in_box & (pz >= 0) & (inside | (d2 < blur_radius))
+    # the K candidates of smallest depth, earlier face on ties (stable sort)
+    key = torch.where(cand, pz.detach(), torch.full_like(pz, float("inf")))
+    order = torch.sort(key, dim=1, stable=True).indices
+    rank = torch.empty_like(order)
+    rank.scatter_(1, order, torch.arange(order.shape[1]).expand_as(order))
+    keep = cand & (rank < faces_per_pixel)
+    sd = torch.where(inside, -d2, d2)
+    prob = torch.sigmoid(-sd / sigma) * keep.to(dt)
+    prod = torch.prod(1.0 - prob, dim=1)
+    alpha = (1.0 - prod).reshape(H, W)
+    if return_aux:
+        return alpha, dict(count=cand.sum(1).reshape(H, W), keep=keep, prod=prod.reshape(H, W))
+    return alpha
+
+
+def silhouette_batch(verts: torch.Tensor, faces: torch.Tensor, H: int, W: int, **kw) -> torch.Tensor:
+    """verts [N,V,3], shared faces -> [N,H,W]."""
+    return torch.stack([silhouette(verts[n], faces, H, W, **kw) for n in range(verts.shape[0])])
+
+
+# ---- cameras (renderer.py:255-258: FoVPerspectiveCameras(R, T, znear=0.02), PyTorch3D defaults fov = 60 deg, zfar = 100) ---
+def look_at_rotation(eye: torch.Tensor, at=(0.0, 0.0, 0.0), up=(1.0, 0.0, 0.0)) -> torch.Tensor:
+    """PyTorch3D look_at_rotation: rows x, y, z axes of the camera in world coordinates, returned transposed (world -> view is
+    X_view = X_world @ R + T)."""
+    eye = torch.as_tensor(eye, dtype=torch.float64).reshape(-1, 3)
+    at_t = torch.as_tensor(at, dtype=torch.float64).reshape(-1, 3).expand_as(eye)
+    up_t = torch.as_tensor(up, dtype=torch.float64).reshape(-1, 3).expand_as(eye)
+    z = torch.nn.functional.normalize(at_t - eye, dim=1)
+    x = torch.nn.functional.normalize(torch.cross(up_t, z, dim=1), dim=1)
+    y = torch.nn.functional.normalize(torch.cross(z, x, dim=1), dim=1)
+    return torch.stack([x, y, z], dim=1).transpose(1, 2)
+
+
+def look_at_view_transform(dist=1.0, elev=0.0, azim=0.0, at=(0.0, 0.0, 0.0), up=(1.0, 0.0, 0.0)):
+    """PyTorch3D look_at_view_transform (degrees): camera position from (dist, elev, azim), R as above, T = -R^T eye."""
+    d, e, a = (torch.as_tensor(v, dtype=torch.float64).reshape(-1) for v in (dist, elev, azim))
+    n = max(d.numel(), e.numel(), a.numel())
+    d, e, a = d.expand(n), torch.deg2rad(e.expand(n)), torch.deg2rad(a.expand(n))
+    eye = torch.stack([d * torch.cos(e) * torch.sin(a), d * torch.sin(e), d * torch.cos(e) * torch.cos(a)], dim=1)
+    eye = eye + torch.as_tensor(at, dtype=torch.float64).reshape(-1, 3)
+    R = look_at_rotation(eye, at, up)
+    T = -torch.bmm(R.transpose(1, 2), eye[:, :, None])[:, :, 0]
+    return R, T
+
+
+def fov_project(verts_world: torch.Tensor, R: torch.Tensor, T: torch.Tensor, fov_deg: float = 60.0, znear: float = 0.02,
+                zfar: float = 100.0) -> torch.Tensor:
+    """FoVPerspectiveCameras.transform_points as MeshRasterizer.transform uses it: x, y in NDC, z = VIEW-space depth.
+    verts_world [V,3], R [3,3], T [3]."""
+    v = verts_world @ R.to(verts_world.dtype) + T.to(verts_world.dtype)
+    s = 1.0 / math.tan(math.radians(fov_deg) / 2.0)
+    z = v[:, 2]
+    return torch.stack([s * v[:, 0] / z, s * v[:, 1] / z, z], dim=1)

@@ -1,0 +1,98 @@
+"""Known-answer tests that pin oracle/raster_oracle.py (the soft-silhouette restatement; PyTorch3D itself is absent)."""
+import math
+
+import torch
+
+from oracle import raster_oracle as ro
+
+TRI = torch.tensor([[-0.5, -0.5, 1.0], [0.5, -0.5, 1.0], [-0.5, 0.5, 1.0]], dtype=torch.float64)
+FACE = torch.tensor([[0, 1, 2]])
+
+
+def _pix(H, W, x, y):
+    xs, ys = ro.pixel_centres(H, W, torch.float64)
+    c = int(torch.argmin((xs - x).abs())); r = int(torch.argmin((ys - y).abs()))
+    return r, c
+
+
+def test_pixel_centres_follow_pytorch3d_ndc():
+    xs, ys = ro.pixel_centres(4, 4, torch.float64)
+    assert torch.allclose(xs, torch.tensor([0.75, 0.25, -0.25, -0.75], dtype=torch.float64))   # +x is LEFT, +y is UP
+    assert torch.allclose(ys, xs)
+
+
+def test_one_triangle_known_alphas():
+    sigma, blur = 0.1, 1.0
+    for tri in (TRI, TRI[[0, 2, 1]]):                                   # both windings (no back-face culling)
+        a = ro.silhouette(tri, FACE, 4, 4, blur_radius=blur, sigma=sigma)
+        r, c = _pix(4, 4, -0.25, -0.25)                                 # inside: nearest edges at 0.25
+        assert abs(float(a[r, c]) - 1 / (1 + math.exp(-0.0625 / sigma))) < 1e-12
+        r, c = _pix(4, 4, 0.25, 0.25)                                   # outside: hypotenuse x + y = 0 at 0.5 / sqrt 2
+        assert abs(float(a[r, c]) - 1 / (1 + math.exp(0.125 / sigma))) < 1e-12
+        r, c = _pix(4, 4, 0.75, 0.75)                                   # squared distance 1.125 >= blur_radius: not a candidate
+        assert float(a[r, c]) == 0.0
+        r, c = _pix(4, 4, 0.75, -0.75)                                  # nearest point is the vertex (0.5, -0.5)
+        assert abs(float(a[r, c]) - 1 / (1 + math.exp(0.125 / sigma))) < 1e-12
+
+
+def test_blur_radius_is_compared_with_the_squared_distance():
+    # distance 0.25 to the left edge: squared 0.0625; candidate iff blur_radius > 0.0625 (NOT 0.25)
+    r, c = _pix(8, 8, -0.625, -0.125)
+    xs, _ = ro.pixel_centres(8, 8, torch.float64)
+    assert abs(float(xs[c]) + 0.625) < 1e-12
+    tri = TRI.clone(); tri[:, 0] += 0.125                               # left edge at x = -0.375: distance 0.25
+    a_in = ro.silhouette(tri, FACE, 8, 8, blur_radius=0.07, sigma=0.1)
+    a_out = ro.silhouette(tri, FACE, 8, 8, blur_radius=0.06, sigma=0.1)
+    assert float(a_in[r, c]) > 0 and float(a_out[r, c]) == 0.0
+
+
+def test_behind_camera_and_degenerate_faces_are_skipped():
+    behind = TRI.clone(); behind[:, 2] = -1.0
+    assert float(ro.silhouette(behind, FACE, 4, 4, blur_radius=1.0, sigma=0.1).abs().max()) == 0.0
+    line = torch.tensor([[-0.5, -0.5, 1.0], [0.0, 0.0, 1.0], [0.5, 0.5, 1.0]], dtype=torch.float64)
+    assert float(ro.silhouette(line, FACE, 4, 4, blur_radius=1.0, sigma=0.1).abs().max()) == 0.0
+
+
+def test_k_truncation_keeps_the_nearest_faces_and_the_earlier_one_on_ties():
+    near, far = TRI.clone(), TRI.clone() * torch.tensor([0.5, 0.5, 2.0])
+    v = torch.cat([far, near, near + torch.tensor([0.01, 0.0, 0.0])])
+    f = torch.tensor([[0, 1, 2], [3, 4, 5], [6, 7, 8]])
+    kw = dict(blur_radius=1.0, sigma=0.1)
+    a1 = ro.silhouette(v, f, 8, 8, faces_per_pixel=1, **kw)
+    only_near = ro.silhouette(near, FACE, 8, 8, **kw)                    # face 1 wins the depth tie with face 2 (earlier)
+    assert torch.equal(a1, only_near)
+    a2, aux = ro.silhouette(v, f, 8, 8, faces_per_pixel=2, return_aux=True, **kw)
+    two_near = ro.silhouette(v[3:], torch.tensor([[0, 1, 2], [3, 4, 5]]), 8, 8, **kw)
+    assert torch.allclose(a2, two_near, atol=1e-15) and int(aux["count"].max()) == 3
+    a3 = ro.silhouette(v, f, 8, 8, faces_per_pixel=3, **kw)
+    assert float((a3 - a2).abs().max()) > 1e-3
+
+
+def test_gradient_matches_finite_differences_fp64():
+    torch.manual_seed(0)
+    v = torch.rand(12, 3, dtype=torch.float64) * torch.tensor([1.6, 1.6, 1.0]) - torch.tensor([0.8, 0.8, -0.5])
+    f = torch.tensor([[0, 1, 2], [3, 4, 5], [6, 7, 8], [9, 10, 11], [0, 4, 8], [1, 5, 9]])
+    w = torch.rand(10, 10, dtype=torch.float64)
+    v.requires_grad_(True)
+    kw = dict(blur_radius=0.05, sigma=0.02)
+    (ro.silhouette(v, f, 10, 10, **kw) * w).sum().backward()
+    g = v.grad.clone()
+    assert float(g[:, 2].abs().max()) == 0.0                             # depth only orders the candidates
+    with torch.no_grad():
+        for (i, d) in [(0, 0), (4, 1), (7, 0), (10, 1), (5, 0)]:
+            e = torch.zeros_like(v); e[i, d] = 1e-6
+            num = ((ro.silhouette(v + e, f, 10, 10, **kw) * w).sum() - (ro.silhouette(v - e, f, 10, 10, **kw) * w).sum()) / 2e-6
+            assert abs(float(num) - float(g[i, d])) < 1e-5 * max(1.0, abs(float(num)))
+
+
+def test_look_at_view_transform_known_answers():
+    R, T = ro.look_at_view_transform(dist=1.0, elev=0.0, azim=0.0, up=(0.0, 1.0, 0.0))
+    assert torch.allclose(R[0], torch.diag(torch.tensor([-1.0, 1.0, -1.0], dtype=torch.float64)), atol=1e-12)
+    assert torch.allclose(T[0], torch.tensor([0.0, 0.0, 1.0], dtype=torch.float64), atol=1e-12)
+    # the camera sits at `dist` from the target and looks at it: the target maps to (0, 0, dist) in view space
+    R, T = ro.look_at_view_transform(dist=0.35, elev=-45.0, azim=30.0, at=(0.1, 0.0, 0.0), up=(1.0, 0.0, 0.0))
+    at_view = torch.tensor([0.1, 0.0, 0.0], dtype=torch.float64) @ R[0] + T[0]
+    assert torch.allclose(at_view, torch.tensor([0.0, 0.0, 0.35], dtype=torch.float64), atol=1e-12)
+    assert torch.allclose(R[0].T @ R[0], torch.eye(3, dtype=torch.float64), atol=1e-12)
+    p = ro.fov_project(torch.tensor([[0.1, 0.0, 0.0]], dtype=torch.float64), R[0], T[0])
+    assert torch.allclose(p[0], torch.tensor([0.0, 0.0, 0.35], dtype=torch.float64), atol=1e-12)

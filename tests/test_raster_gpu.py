@@ -1,0 +1,160 @@
+"""Soft-silhouette rasteriser (csrc/raster.cu through the C ABI) against oracle/raster_oracle.py, plus the host-side camera
+helpers of find_b200.renderer (CPU).  Tolerances: alpha is fp32 with sigmoid / product rounding -> 2e-5 absolute (a candidate that
+flips at the blur boundary carries p = 1e-4, hence the 3e-4 ceiling on the maximum); gradients rel-L2 1e-3 (fp32 atomics)."""
+import math
+
+import pytest
+import torch
+
+from find_b200 import synthetic as syn
+from find_b200.mesh import Meshes
+from find_b200.renderer import FootRenderer, look_at_view_transform, rasterize_silhouette
+from oracle import raster_oracle as ro
+
+
+def rel_l2(a, b):
+    return float((a.double() - b.double()).norm() / b.double().norm().clamp_min(1e-30))
+
+
+def test_camera_helpers_match_the_oracle_cpu():
+    r = FootRenderer(64, device="cpu")
+    for kw in (dict(dist=0.3, elev=0.0, azim=0.0), dict(dist=0.35, elev=-45.0, azim=0.0), dict(dist=[0.2, 0.3], elev=[10.0, 80.0], azim=[5.0, 200.0])):
+        R, T = look_at_view_transform(up=((1, 0, 0),), **kw)
+        Ro, To = ro.look_at_view_transform(up=(1.0, 0.0, 0.0), **kw)
+        assert torch.allclose(R.double(), Ro, atol=1e-6) and torch.allclose(T.double(), To, atol=1e-6)
+    R, T = r.view_from(["topdown", "side1", "side2", "toes", "45", "60"])
+    assert R.shape == (6, 3, 3) and T.shape == (6, 3)
+    R2, T2 = r.combine_views(R, T, *r.linspace_views(3, dist=0.3, azim_min=0, azim_max=90))
+    assert R2.shape == (9, 3, 3) and T2.shape == (9, 3)
+    Rs, Ts = r.sample_views(4, seed=3)
+    assert Rs.shape == (4, 3, 3) and torch.allclose(torch.linalg.det(Rs), torch.ones(4), atol=1e-5)
+    tv, _ = syn.make_template(162)
+    ndc = r.project(tv[None], R[:2], T[:2])
+    for k in range(2):
+        assert torch.allclose(ndc[k], ro.fov_project(tv, R[k], T[k]), atol=1e-6)
+    with pytest.raises(NotImplementedError):
+        r(Meshes(tv[None], torch.zeros(1, 3, dtype=torch.int64)), R, T, return_images=True)
+
+
+def _scene(V, views, B=1, seed=0):
+    dev = torch.device("cuda")
+    tv, tf = syn.make_template(V)
+    g = torch.Generator().manual_seed(seed)
+    verts = tv[None] + 0.002 * torch.randn(B, tv.shape[0], 3, generator=g)
+    r = FootRenderer(64, device=dev)
+    R, T = r.view_from(views)
+    return dev, verts, tf, r, R, T
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("V,size", [(162, (64, 64)), (642, (96, 96)), (642, (50, 70))])
+def test_silhouette_matches_oracle(V, size):
+    dev, verts, tf, r, R, T = _scene(V, ["topdown", "45"])
+    ndc = r.project(verts, R, T)                                          # [2, V, 3] on CPU
+    H, W = size
+    got = rasterize_silhouette(ndc.to(dev), tf.to(dev), (H, W))
+    want = ro.silhouette_batch(ndc, tf, H, W)
+    err = (got.cpu() - want).abs()
+    assert float(err.max()) < 3e-4 and float(err.mean()) < 2e-6
+    assert float(want.max()) > 0.99 and float(want.min()) == 0.0 and 0.02 < float(want.mean()) < 0.9
+
+
+@pytest.mark.gpu
+def test_silhouette_gradient_matches_oracle_autograd():
+    dev, verts, tf, r, R, T = _scene(162, ["topdown", "side1"], seed=1)
+    H = W = 48
+    w = torch.rand(2, H, W, generator=torch.Generator().manual_seed(5))
+    ndc = r.project(verts, R, T)
+    a = ndc.clone().requires_grad_(True)
+    (ro.silhouette_batch(a, tf, H, W) * w).sum().backward()
+    b = ndc.to(dev).requires_grad_(True)
+    (rasterize_silhouette(b, tf.to(dev), (H, W)) * w.to(dev)).sum().backward()
+    assert float(a.grad.abs().max()) > 0
+    assert rel_l2(b.grad.cpu(), a.grad) < 1e-3
+    assert float(b.grad[..., 2].abs().max()) == 0.0
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("K", [1, 5, 100])
+def test_k_truncation_by_depth_with_ties(K):
+    """150 overlapping triangles at 50 distinct depths (three share each depth): more candidates than K on most pixels."""
+    dev = torch.device("cuda")
+    g = torch.Generator().manual_seed(2)
+    base = torch.tensor([[-0.6, -0.5], [0.6, -0.4], [-0.1, 0.7]])
+    vs, fs = [], []
+    for i in range(150):
+        xy = base + 0.05 * torch.randn(3, 2, generator=g)
+        z = torch.full((3, 1), 0.5 + 0.01 * (i % 50))
+        vs.append(torch.cat([xy, z], 1)); fs.append([3 * i, 3 * i + 1, 3 * i + 2])
+    v = torch.cat(vs)[None]; f = torch.tensor(fs)
+    kw = dict(blur_radius=0.01, sigma=0.3, faces_per_pixel=K)
+    want, aux = ro.silhouette(v[0], f, 32, 32, return_aux=True, **kw)
+    assert int(aux["count"].max()) > 100
+    vg = v.to(dev).requires_grad_(True)
+    got = rasterize_silhouette(vg, f.to(dev), 32, **kw)
+    assert float((got[0].detach().cpu() - want).abs().max()) < 2e-5
+    w = torch.rand(32, 32, generator=g)
+    (got[0] * w.to(dev)).sum().backward()
+    vo = v[0].clone().requires_grad_(True)
+    (ro.silhouette(vo, f, 32, 32, **kw) * w).sum().backward()
+    assert rel_l2(vg.grad[0].cpu(), vo.grad) < 1e-3
+
+
+@pytest.mark.gpu
+def test_empty_and_degenerate_inputs():
+    dev = torch.device("cuda")
+    v = torch.zeros(2, 5, 3, device=dev)
+    a = rasterize_silhouette(v, torch.zeros(0, 3, dtype=torch.int64, device=dev), 20)
+    assert a.shape == (2, 20, 20) and float(a.abs().max()) == 0.0
+    a = rasterize_silhouette(v, torch.tensor([[0, 1, 2]], device=dev), 20)               # zero-area face
+    assert float(a.abs().max()) == 0.0
+    v = torch.tensor([[[-0.5, -0.5, -1.0], [0.5, -0.5, -1.0], [0.0, 0.5, -1.0]]], device=dev)  # behind the camera
+    assert float(rasterize_silhouette(v, torch.tensor([[0, 1, 2]], device=dev), 20).abs().max()) == 0.0
+    with pytest.raises(RuntimeError):
+        rasterize_silhouette(torch.zeros(1, 3, 3), torch.tensor([[0, 1, 2]]), 8)           # CPU tensors: no fallback
+
+
+@pytest.mark.gpu
+def test_foot_renderer_mask_full_size_properties_and_world_gradient():
+    """FootRenderer.forward at the reference's scale (10 242-vertex template, 256 x 256, 3 views x 2 feet): shapes, range,
+    agreement of the soft mask with the hard coverage away from the boundary, and a gradient that reaches world vertices."""
+    dev, verts, tf, _, _, _ = _scene(10242, ["topdown"], B=2, seed=3)
+    r = FootRenderer(256, device=dev)
+    R, T = r.view_from(["topdown", "side1", "45"])
+    vw = verts.to(dev).requires_grad_(True)
+    out = r(Meshes(vw, tf.to(dev)), R, T, return_images=False, return_mask=True)
+    m = out["mask"]
+    assert m.shape == (2, 3, 256, 256) and float(m.min()) >= 0.0 and float(m.max()) <= 1.0
+    frac = (m > 0.5).float().mean(dim=(2, 3))
+    assert float(frac.min()) > 0.03 and float(frac.max()) < 0.8
+    soft = ((m > 1e-3) & (m < 1 - 1e-3)).float().mean()
+    assert 0.0 < float(soft) < 0.1                                        # only a thin boundary band is soft
+    target = torch.roll(m.detach(), shifts=4, dims=3)
+    loss = ((m - target) ** 2).mean()
+    loss.backward()
+    g = vw.grad
+    assert torch.isfinite(g).all() and float(g.abs().max()) > 0
+    # row block against the oracle (full dense evaluation is too large): one view, 24 rows through the middle
+    ndc = r.project(verts[:1], R[:1], T[:1])
+    got = rasterize_silhouette(ndc.to(dev), tf.to(dev), 256)[0, 116:140].cpu()
+    xs, ys = ro.pixel_centres(256, 256)
+    sub = _oracle_rows(ndc[0], tf, 256, 256, 116, 140)
+    assert float((got - sub).abs().max()) < 3e-4
+
+
+def _oracle_rows(ndc, faces, H, W, r0, r1):
+    """oracle on rows [r0, r1) only: restrict to faces whose grown box reaches those rows (the result is identical)."""
+    _, ys = ro.pixel_centres(H, W)
+    blur = math.sqrt(ro.blur_radius_for())
+    fy = ndc[faces][:, :, 1]
+    keep = (fy.max(1).values + blur >= ys[r1 - 1] - 1e-6) & (fy.min(1).values - blur <= ys[r0] + 1e-6)
+    full = torch.zeros(r1 - r0, W)
+    # evaluate the oracle on a shifted image: rows r0..r1 of an H-row image = all rows of a crop with the same pixel centres
+    import oracle.raster_oracle as m
+    orig = m.pixel_centres
+    try:
+        m.pixel_centres = lambda h, w, dtype=torch.float32: (orig(H, W, dtype)[0], orig(H, W, dtype)[1][r0:r1])
+        full = m.silhouette(ndc, faces[keep], r1 - r0, W)
+    finally:
+        m.pixel_centres = orig
+    return full
