@@ -24,7 +24,7 @@ def main():
     ours = OrderedDict()
     other = OrderedDict()
     for n, us in rows:
-        d = other if (n.startswith("at::") or "probe" in n or "peak" in n) else ours
+        d = other if (n.startswith(("at::", "native::", "at_cuda_detail::")) or "probe" in n or "peak" in n) else ours
         d.setdefault(n, []).append(us)
     b = json.loads(open(bench).read().strip().splitlines()[-1])
     step_ms = b["ms_per_step"]
