@@ -47,6 +47,9 @@ struct SilParams {
     float* grad_verts;                    // [N, V, 3]
     const int* faces;                     // [F, 3] (backward: vertex ids)
     int V;
+    uint32_t* cand_bits;                  // [grid][cap][256]  per-pixel candidate depths of the tile a CTA is working on
+    float* cand_fac;                      // [grid][cap][256]  their blend factors 1 - p
+    int cap;
     unsigned int* overflow;               // device flag: a tile exceeded kListCap while a pixel needed K truncation
 };
 
@@ -106,13 +109,11 @@ struct Eval {
     float t;            // its clamped parameter
 };
 
-FB_DEVINL Eval eval_face(const FaceRec& r, float px, float py, float blur, float blur_radius, int perspective) {
+FB_DEVINL Eval eval_face(const FaceRec& r, const float4& bx, float px, float py, float blur_radius, int perspective) {
     Eval e;
     e.cand = false;
-    // bounding-box test of THIS pixel (the tile test only said the face touches the tile)
-    const float xmin = fminf(fminf(r.x0, r.x1), r.x2) - blur, xmax = fmaxf(fmaxf(r.x0, r.x1), r.x2) + blur;
-    const float ymin = fminf(fminf(r.y0, r.y1), r.y2) - blur, ymax = fmaxf(fmaxf(r.y0, r.y1), r.y2) + blur;
-    if (!(px >= xmin && px <= xmax && py >= ymin && py <= ymax)) return e;
+    // bounding-box test of THIS pixel against the grown box of face_setup_kernel (the tile test only said the face touches the tile)
+    if (!(px >= bx.x && px <= bx.y && py >= bx.z && py <= bx.w)) return e;
     const float area = edge_fn(r.x2, r.y2, r.x0, r.y0, r.x1, r.y1);
     const float den = area + kEps;
     const float w0 = __fdiv_rn(edge_fn(px, py, r.x1, r.y1, r.x2, r.y2), den);
@@ -145,6 +146,7 @@ FB_DEVINL float sigmoidf_(float x) { return __fdiv_rn(1.f, 1.f + __expf(-x)); }
 struct TileShared {
     int ids[kListCap];
     FaceRec rec[kThreads];
+    float4 box[kThreads];
     int vid[kThreads][3];
     int wcnt[kThreads / 32];
     int nlist;
@@ -193,6 +195,7 @@ template <bool kNeedVid, typename Fn>
 FB_DEVINL void for_each_listed(const SilParams& P, int n, int count, float px, float py, float blur, bool active, TileShared& sh, Fn fn) {
     const int tid = threadIdx.x;
     const FaceRec* rec = P.rec + (size_t)n * P.F;
+    const bool warp_active = __any_sync(0xffffffffu, active);      // a warp with no pixel to serve only helps staging
     for (int base = 0; base < count; base += kThreads) {
         __syncthreads();
         const int m = min(kThreads, count - base);
@@ -201,15 +204,17 @@ FB_DEVINL void for_each_listed(const SilParams& P, int n, int count, float px, f
             const float4* src = reinterpret_cast<const float4*>(rec + f);
             float4* dst = reinterpret_cast<float4*>(&sh.rec[tid]);
             dst[0] = __ldg(src); dst[1] = __ldg(src + 1); dst[2] = __ldg(src + 2);
+            sh.box[tid] = __ldg(P.box + (size_t)n * P.F + f);
             if (kNeedVid) { sh.vid[tid][0] = P.faces[3 * f]; sh.vid[tid][1] = P.faces[3 * f + 1]; sh.vid[tid][2] = P.faces[3 * f + 2]; }
         }
         __syncthreads();
-        for (int j = 0; j < m; ++j) {
-            Eval e;
-            e.cand = false;
-            if (active) e = eval_face(sh.rec[j], px, py, blur, P.blur_radius, P.perspective);
-            fn(j, sh.rec[j], e);
-        }
+        if (warp_active)
+            for (int j = 0; j < m; ++j) {
+                Eval e;
+                e.cand = false;
+                if (active) e = eval_face(sh.rec[j], sh.box[j], px, py, P.blur_radius, P.perspective);
+                fn(j, sh.rec[j], e);
+            }
     }
     __syncthreads();
 }
@@ -219,23 +224,35 @@ FB_DEVINL uint32_t depth_bits(float pz) { return __float_as_uint(pz) & 0x7ffffff
 __global__ void __launch_bounds__(kThreads) sil_tile_fwd_kernel(const __grid_constant__ SilParams P) {
     pdl_wait_trigger();
     __shared__ TileShared sh;
-    const int n = blockIdx.z, tid = threadIdx.x;
-    const int col = blockIdx.x * kTile + (tid & (kTile - 1)), row = blockIdx.y * kTile + (tid >> 4);
+    const int tid = threadIdx.x;
+    const int tiles_x = (P.W + kTile - 1) / kTile, tiles_y = (P.H + kTile - 1) / kTile;
+    const long long n_tiles = (long long)P.N * tiles_x * tiles_y;
+    const float blur = sqrtf(P.blur_radius), inv_sigma = __fdiv_rn(1.f, P.sigma);
+    // this CTA's slice of the candidate store: [cap][256 pixels] depth bits and blend factors, written once per candidate in the
+    // first walk so that a pixel with more than K candidates selects its K nearest from its own list (no re-evaluation)
+    uint32_t* cbits = P.cand_bits + (size_t)blockIdx.x * P.cap * kThreads;
+    float* cfac = P.cand_fac + (size_t)blockIdx.x * P.cap * kThreads;
+    for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+    const int n = (int)(tile / (tiles_x * tiles_y)), trem = (int)(tile - (long long)n * tiles_x * tiles_y);
+    const int tile_y = trem / tiles_x, tile_x = trem - tile_y * tiles_x;
+    const int col = tile_x * kTile + (tid & (kTile - 1)), row = tile_y * kTile + (tid >> 4);
     const bool in_img = (col < P.W) && (row < P.H);
     const float px = 1.f - __fdiv_rn((float)(2 * col + 1), (float)P.W), py = 1.f - __fdiv_rn((float)(2 * row + 1), (float)P.H);
-    const int c_hi = min(blockIdx.x * kTile + kTile - 1, P.W - 1), r_hi = min(blockIdx.y * kTile + kTile - 1, P.H - 1);
-    const float txmax = 1.f - __fdiv_rn((float)(2 * blockIdx.x * kTile + 1), (float)P.W), txmin = 1.f - __fdiv_rn((float)(2 * c_hi + 1), (float)P.W);
-    const float tymax = 1.f - __fdiv_rn((float)(2 * blockIdx.y * kTile + 1), (float)P.H), tymin = 1.f - __fdiv_rn((float)(2 * r_hi + 1), (float)P.H);
-    const float blur = sqrtf(P.blur_radius), inv_sigma = __fdiv_rn(1.f, P.sigma);
+    const int c_hi = min(tile_x * kTile + kTile - 1, P.W - 1), r_hi = min(tile_y * kTile + kTile - 1, P.H - 1);
+    const float txmax = 1.f - __fdiv_rn((float)(2 * tile_x * kTile + 1), (float)P.W), txmin = 1.f - __fdiv_rn((float)(2 * c_hi + 1), (float)P.W);
+    const float tymax = 1.f - __fdiv_rn((float)(2 * tile_y * kTile + 1), (float)P.H), tymin = 1.f - __fdiv_rn((float)(2 * r_hi + 1), (float)P.H);
 
     int cnt = 0;
     float prod = 1.f;
+    uint2 sel = make_uint2(0xffffffffu, 0u);
     uint32_t zlo = 0xffffffffu, zhi = 0u;           // depth range of this pixel's candidates (bit patterns)
     auto accumulate = [&](int, const FaceRec&, const Eval& e) {
         if (e.cand) {
-            ++cnt;
-            prod = __fmul_rn(prod, 1.f - sigmoidf_((e.inside ? e.d2 : -e.d2) * inv_sigma));
+            const float fac = 1.f - sigmoidf_((e.inside ? e.d2 : -e.d2) * inv_sigma);
             const uint32_t b = depth_bits(e.pz);
+            if (cnt < P.cap) { cbits[(size_t)cnt * kThreads + tid] = b; cfac[(size_t)cnt * kThreads + tid] = fac; }
+            ++cnt;
+            prod = __fmul_rn(prod, fac);
             zlo = min(zlo, b); zhi = max(zhi, b);
         }
     };
@@ -245,8 +262,50 @@ __global__ void __launch_bounds__(kThreads) sil_tile_fwd_kernel(const __grid_con
     const bool spilled = sh.overflow != 0;
     for_each_listed<false>(P, n, nlist, px, py, blur, in_img, sh, accumulate);
 
-    uint2 sel = make_uint2(0xffffffffu, 0u);
-    const bool sat = in_img && cnt > P.K;
+    const bool sat_any = in_img && cnt > P.K;
+    if (sat_any && cnt <= P.cap) {
+        // thread-local: K-th smallest depth of the stored list by 16-ary search on the bit pattern, then the product of the kept
+        uint32_t lo = zlo, hi = zhi;
+        int below = 0;
+        while (lo < hi) {
+            const uint32_t step = ((hi - lo) >> 4) + 1u;
+            uint32_t t[15];
+            int c[15];
+#pragma unroll
+            for (int i = 0; i < 15; ++i) {
+                const unsigned long long v = (unsigned long long)lo + (unsigned long long)step * (i + 1) - 1ull;
+                t[i] = v > hi ? hi : (uint32_t)v;
+                c[i] = 0;
+            }
+            for (int q = 0; q < cnt; ++q) {
+                const uint32_t b = cbits[(size_t)q * kThreads + tid];
+                if (b < lo || b > hi) continue;
+#pragma unroll
+                for (int i = 0; i < 15; ++i) c[i] += (b <= t[i]) ? 1 : 0;
+            }
+            int k = 15;
+#pragma unroll
+            for (int i = 14; i >= 0; --i) if (below + c[i] >= P.K) k = i;
+            uint32_t nlo = lo, nhi = hi;
+            int add = 0;
+#pragma unroll
+            for (int i = 0; i < 15; ++i) {
+                if (k == i) nhi = t[i];
+                if (k == i + 1) { nlo = t[i] + 1u; add = c[i]; }
+            }
+            lo = nlo; hi = nhi; below += add;
+        }
+        const int ties = P.K - below;
+        int seen = 0;
+        float prod2 = 1.f;
+        for (int q = 0; q < cnt; ++q) {
+            const uint32_t b = cbits[(size_t)q * kThreads + tid];
+            const bool keep = (b < lo) || (b == lo && seen++ < ties);
+            if (keep) prod2 = __fmul_rn(prod2, cfac[(size_t)q * kThreads + tid]);
+        }
+        prod = prod2; sel = make_uint2(lo, (uint32_t)ties);
+    }
+    const bool sat = sat_any && cnt > P.cap;             // list did not fit: block-wide search by re-evaluation
     if (__syncthreads_or(sat)) {
         if (spilled) {
             if (sat) atomicExch(P.overflow, 1u);     // cannot truncate exactly: the host reports it (findb200_silhouette_status)
@@ -308,6 +367,8 @@ __global__ void __launch_bounds__(kThreads) sil_tile_fwd_kernel(const __grid_con
         if (P.prod) P.prod[o] = prod;
         if (P.sel) P.sel[o] = sel;
     }
+    __syncthreads();
+    }   // tile loop
 }
 
 __global__ void __launch_bounds__(kThreads) sil_tile_bwd_kernel(const __grid_constant__ SilParams P) {
@@ -379,26 +440,38 @@ using namespace fb;
 using namespace fb::raster;
 
 namespace {
-struct WsLayout { size_t box, rec, flag, total; };
+struct WsLayout { size_t box, rec, flag, cbits, cfac, total; };
+constexpr int kFwdCtas = 148 * 3;
+int cand_cap() {
+    const char* e = getenv("FINDB200_SIL_CAP");          // tests force the re-evaluation path with a small capacity
+    const int c = e ? atoi(e) : 384;
+    return c < 1 ? 1 : (c > 1024 ? 1024 : c);
+}
 WsLayout ws_layout(int N, int F) {
     WsLayout L;
     size_t o = 0;
     L.box = o; o += ((size_t)N * F * sizeof(float4) + 255) & ~(size_t)255;
     L.rec = o; o += ((size_t)N * F * sizeof(FaceRec) + 255) & ~(size_t)255;
     L.flag = o; o += 256;
+    L.cbits = o; o += (size_t)kFwdCtas * cand_cap() * kThreads * sizeof(uint32_t);
+    L.cfac = o; o += (size_t)kFwdCtas * cand_cap() * kThreads * sizeof(float);
     L.total = o;
     return L;
 }
-int fill(SilParams& P, void* ws, size_t ws_bytes, int N, int V, int F, int H, int W, float blur_radius, float sigma, int K, int perspective) {
+int fill(SilParams& P, void* ws, size_t ws_bytes, int N, int V, int F, int H, int W, float blur_radius, float sigma, int K, int perspective, bool scratch) {
     FB_REQUIRE(N >= 0 && V >= 1 && F >= 0 && H >= 1 && W >= 1, FINDB200_ERR_SHAPE, "silhouette: bad shape N=%d V=%d F=%d H=%d W=%d", N, V, F, H, W);
     FB_REQUIRE(N <= 65535, FINDB200_ERR_SHAPE, "silhouette: at most 65535 meshes x views per call (got %d)", N);
     FB_REQUIRE(blur_radius >= 0.f && sigma > 0.f && K >= 1, FINDB200_ERR_ARG, "silhouette: blur_radius >= 0, sigma > 0 and faces_per_pixel >= 1 required");
     const WsLayout L = ws_layout(N, F);
-    FB_REQUIRE(ws && ws_bytes >= L.total, FINDB200_ERR_WORKSPACE, "silhouette: workspace too small (%zu < %zu)", ws_bytes, L.total);
+    const size_t need = scratch ? L.total : L.cbits;
+    FB_REQUIRE(ws && ws_bytes >= need, FINDB200_ERR_WORKSPACE, "silhouette: workspace too small (%zu < %zu)", ws_bytes, need);
     memset(&P, 0, sizeof(P));
     P.box = (const float4*)((char*)ws + L.box);
     P.rec = (const FaceRec*)((char*)ws + L.rec);
     P.overflow = (unsigned int*)((char*)ws + L.flag);
+    P.cand_bits = (uint32_t*)((char*)ws + L.cbits);
+    P.cand_fac = (float*)((char*)ws + L.cfac);
+    P.cap = cand_cap();
     P.N = N; P.F = F; P.H = H; P.W = W; P.V = V;
     P.blur_radius = blur_radius; P.sigma = sigma; P.K = K; P.perspective = perspective;
     return 0;
@@ -406,13 +479,15 @@ int fill(SilParams& P, void* ws, size_t ws_bytes, int N, int V, int F, int H, in
 }  // namespace
 
 extern "C" size_t findb200_silhouette_workspace_bytes(int N, int F) { return ws_layout(N > 0 ? N : 0, F > 0 ? F : 0).total; }
+// the leading part of the workspace the backward reads (face records + status flag): keep this prefix, the rest is scratch
+extern "C" size_t findb200_silhouette_saved_bytes(int N, int F) { return ws_layout(N > 0 ? N : 0, F > 0 ? F : 0).cbits; }
 
 extern "C" int findb200_silhouette_forward(const float* verts_ndc, const int32_t* faces, int N, int V, int F, int H, int W,
                                            float blur_radius, float sigma, int faces_per_pixel, int perspective_correct,
                                            float* alpha, float* prod, void* sel, void* ws, size_t ws_bytes, void* stream) {
     cudaStream_t st = (cudaStream_t)stream;
     SilParams P;
-    int rc = fill(P, ws, ws_bytes, N, V, F, H, W, blur_radius, sigma, faces_per_pixel, perspective_correct);
+    int rc = fill(P, ws, ws_bytes, N, V, F, H, W, blur_radius, sigma, faces_per_pixel, perspective_correct, true);
     if (rc) return rc;
     FB_REQUIRE(verts_ndc && (faces || F == 0) && alpha, FINDB200_ERR_ARG, "silhouette_forward: null argument");
     if (N == 0) return 0;
@@ -425,7 +500,8 @@ extern "C" int findb200_silhouette_forward(const float* verts_ndc, const int32_t
                            sqrtf(blur_radius), (float4*)P.box, (FaceRec*)P.rec));
     }
     FB_MARK("sil_tile_fwd", st);
-    FB_CUDA(launch_pdl(sil_tile_fwd_kernel, dim3((W + kTile - 1) / kTile, (H + kTile - 1) / kTile, N), dim3(kThreads), 0, st, P));
+    const long long n_tiles = (long long)N * ((W + kTile - 1) / kTile) * ((H + kTile - 1) / kTile);
+    FB_CUDA(launch_pdl(sil_tile_fwd_kernel, dim3((unsigned)(n_tiles < kFwdCtas ? n_tiles : kFwdCtas)), dim3(kThreads), 0, st, P));
     FB_MARK_END(st);
     return 0;
 }
@@ -436,7 +512,7 @@ extern "C" int findb200_silhouette_backward(const float* grad_alpha, const int32
                                             const float* prod, const void* sel, float* grad_verts_ndc, void* ws, size_t ws_bytes, void* stream) {
     cudaStream_t st = (cudaStream_t)stream;
     SilParams P;
-    int rc = fill(P, ws, ws_bytes, N, V, F, H, W, blur_radius, sigma, faces_per_pixel, perspective_correct);
+    int rc = fill(P, ws, ws_bytes, N, V, F, H, W, blur_radius, sigma, faces_per_pixel, perspective_correct, false);
     if (rc) return rc;
     if (N == 0 || F == 0) return 0;
     FB_REQUIRE(grad_alpha && faces && prod && sel && grad_verts_ndc, FINDB200_ERR_ARG, "silhouette_backward: null argument");

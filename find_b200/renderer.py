@@ -70,6 +70,8 @@ class _Silhouette(torch.autograd.Function):
                                                  int(K), int(bool(perspective)), _lib.ptr(alpha), _lib.ptr(prod), _lib.ptr(sel),
                                                  _lib.ptr(ws), ws.numel(), _lib.stream_ptr(dev))
         _lib.check(rc, "findb200_silhouette_forward")
+        if ctx.needs_input_grad[0]:                        # the backward reads the face records only: drop the scratch part
+            ws = ws[: int(lib.findb200_silhouette_saved_bytes(N, F))].clone()
         ctx.save_for_backward(faces_i32, prod, sel, ws)
         ctx.cfg = (N, V, F, H, W, float(blur_radius), float(sigma), int(K), int(bool(perspective)))
         return alpha

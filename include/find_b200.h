@@ -189,6 +189,7 @@ int findb200_mesh_smooth(const float* verts, int N, int V, const int32_t* faces,
  * (> 4096 faces on one 16 x 16 tile together with a pixel of more than faces_per_pixel candidates).
  * ------------------------------------------------------------------------------------------------------ */
 size_t findb200_silhouette_workspace_bytes(int N, int F);
+size_t findb200_silhouette_saved_bytes(int N, int F);   /* prefix of the workspace the backward needs; the rest is scratch */
 int findb200_silhouette_forward(const float* verts_ndc, const int32_t* faces, int N, int V, int F, int H, int W,
                                 float blur_radius, float sigma, int faces_per_pixel, int perspective_correct,
                                 float* alpha, float* prod, void* sel, void* workspace, size_t workspace_bytes, void* stream);

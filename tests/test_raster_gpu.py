@@ -158,3 +158,11 @@ def _oracle_rows(ndc, faces, H, W, r0, r1):
     finally:
         m.pixel_centres = orig
     return full
+
+
+@pytest.mark.gpu
+def test_k_truncation_re_evaluation_path(monkeypatch):
+    """FINDB200_SIL_CAP below the candidate count forces the block-wide search that re-evaluates the tile's faces."""
+    monkeypatch.setenv("FINDB200_SIL_CAP", "40")
+    test_k_truncation_by_depth_with_ties(100)
+    test_k_truncation_by_depth_with_ties(5)
