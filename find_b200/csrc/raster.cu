@@ -50,6 +50,7 @@ struct SilParams {
     uint32_t* cand_bits;                  // [grid][cap][256]  per-pixel candidate depths of the tile a CTA is working on
     float* cand_fac;                      // [grid][cap][256]  their blend factors 1 - p
     int cap;
+    unsigned int* tile_counter;           // device: next tile of the forward kernel's queue (zeroed per call)
     unsigned int* overflow;               // device flag: a tile exceeded kListCap while a pixel needed K truncation
 };
 
@@ -116,9 +117,19 @@ FB_DEVINL Eval eval_face(const FaceRec& r, const float4& bx, float px, float py,
     if (!(px >= bx.x && px <= bx.y && py >= bx.z && py <= bx.w)) return e;
     const float area = edge_fn(r.x2, r.y2, r.x0, r.y0, r.x1, r.y1);
     const float den = area + kEps;
-    const float w0 = __fdiv_rn(edge_fn(px, py, r.x1, r.y1, r.x2, r.y2), den);
-    const float w1 = __fdiv_rn(edge_fn(px, py, r.x2, r.y2, r.x0, r.y0), den);
-    const float w2 = __fdiv_rn(edge_fn(px, py, r.x0, r.y0, r.x1, r.y1), den);
+    const float e0 = edge_fn(px, py, r.x1, r.y1, r.x2, r.y2), e1 = edge_fn(px, py, r.x2, r.y2, r.x0, r.y0), e2 = edge_fn(px, py, r.x0, r.y0, r.x1, r.y1);
+    float t01, t02, t12;
+    const float d01 = seg_dist2(px, py, r.x0, r.y0, r.x1, r.y1, t01);
+    const float d02 = seg_dist2(px, py, r.x0, r.y0, r.x2, r.y2, t02);
+    const float d12 = seg_dist2(px, py, r.x1, r.y1, r.x2, r.y2, t12);
+    e.d2 = d01; e.edge = 0; e.t = t01;
+    if (d02 < e.d2) { e.d2 = d02; e.edge = 1; e.t = t02; }
+    if (d12 < e.d2) { e.d2 = d12; e.edge = 2; e.t = t12; }
+    // w_i = e_i / den > 0 needs e_i and den of the same sign: when that already fails and the pixel is beyond the blur
+    // radius, the face cannot be a candidate and the divisions below are skipped (the decision itself is unchanged)
+    const bool maybe_inside = (den > 0.f) ? (e0 > 0.f && e1 > 0.f && e2 > 0.f) : (e0 < 0.f && e1 < 0.f && e2 < 0.f);
+    if (!maybe_inside && !(e.d2 < blur_radius)) return e;
+    const float w0 = __fdiv_rn(e0, den), w1 = __fdiv_rn(e1, den), w2 = __fdiv_rn(e2, den);
     e.inside = (w0 > 0.f) && (w1 > 0.f) && (w2 > 0.f);
     float b0 = w0, b1 = w1, b2 = w2;
     if (perspective) {
@@ -130,13 +141,6 @@ FB_DEVINL Eval eval_face(const FaceRec& r, const float4& bx, float px, float py,
     const float cs = fmaxf(__fadd_rn(__fadd_rn(c0, c1), c2), 1e-5f);
     e.pz = __fdiv_rn(__fadd_rn(__fadd_rn(__fmul_rn(c0, r.z0), __fmul_rn(c1, r.z1)), __fmul_rn(c2, r.z2)), cs);
     if (!(e.pz >= 0.f)) return e;
-    float t01, t02, t12;
-    const float d01 = seg_dist2(px, py, r.x0, r.y0, r.x1, r.y1, t01);
-    const float d02 = seg_dist2(px, py, r.x0, r.y0, r.x2, r.y2, t02);
-    const float d12 = seg_dist2(px, py, r.x1, r.y1, r.x2, r.y2, t12);
-    e.d2 = d01; e.edge = 0; e.t = t01;
-    if (d02 < e.d2) { e.d2 = d02; e.edge = 1; e.t = t02; }
-    if (d12 < e.d2) { e.d2 = d12; e.edge = 2; e.t = t12; }
     e.cand = e.inside || (e.d2 < blur_radius);
     return e;
 }
@@ -148,46 +152,59 @@ struct TileShared {
     FaceRec rec[kThreads];
     float4 box[kThreads];
     int vid[kThreads][3];
-    int wcnt[kThreads / 32];
+    int wcnt[4 * kThreads / 32];
+    int next_tile;
     int nlist;
     int overflow;
 };
 
-// Faces of mesh n whose grown box touches the tile, in face order, into sh.ids.  On overflow of the list the caller's
-// `spill` functor consumes the full list (evaluate what is there) and the list restarts.
+// Faces of mesh n whose grown box touches the tile, in face order, into sh.ids.  kSub x 256 boxes are loaded per round (independent
+// loads, two barriers per round).  On overflow of the list the caller's `spill` functor consumes the full list (evaluate what is
+// there) and the list restarts.
+constexpr int kSub = 4;
 template <typename Spill>
 FB_DEVINL void build_tile_list(const SilParams& P, int n, float txmin, float txmax, float tymin, float tymax, TileShared& sh, Spill spill) {
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    if (tid == 0) { sh.nlist = 0; sh.overflow = 0; }
-    __syncthreads();
+    constexpr int kWarps = kThreads / 32;
+    if (tid == 0) sh.overflow = 0;
+    int nl = 0;                                      // uniform across the CTA
     const float4* box = P.box + (size_t)n * P.F;
-    for (int base = 0; base < P.F; base += kThreads) {
-        const int f = base + tid;
-        bool hit = false;
-        if (f < P.F) {
-            const float4 b = __ldg(box + f);
-            hit = (b.x <= txmax) && (b.y >= txmin) && (b.z <= tymax) && (b.w >= tymin);
-        }
-        const unsigned m = __ballot_sync(0xffffffffu, hit);
-        if (lane == 0) sh.wcnt[warp] = __popc(m);
-        __syncthreads();
-        int before = 0, total = 0;
+    for (int base = 0; base < P.F; base += kThreads * kSub) {
+        float4 b[kSub];
 #pragma unroll
-        for (int w = 0; w < kThreads / 32; ++w) { const int c = sh.wcnt[w]; if (w < warp) before += c; total += c; }
-        int nl = sh.nlist;
+        for (int u = 0; u < kSub; ++u) {
+            const int f = base + u * kThreads + tid;
+            b[u] = (f < P.F) ? __ldg(box + f) : make_float4(1e30f, -1e30f, 1e30f, -1e30f);
+        }
+        unsigned m[kSub];
+        bool hit[kSub];
+#pragma unroll
+        for (int u = 0; u < kSub; ++u) {
+            hit[u] = (b[u].x <= txmax) && (b[u].y >= txmin) && (b[u].z <= tymax) && (b[u].w >= tymin);
+            m[u] = __ballot_sync(0xffffffffu, hit[u]);
+            if (lane == 0) sh.wcnt[u * kWarps + warp] = __popc(m[u]);
+        }
+        __syncthreads();
+        int before[kSub], total = 0;
+#pragma unroll
+        for (int u = 0; u < kSub; ++u) {
+            before[u] = total;
+#pragma unroll
+            for (int w = 0; w < kWarps; ++w) { const int c = sh.wcnt[u * kWarps + w]; if (w < warp) before[u] += c; total += c; }
+        }
         if (nl + total > kListCap) {                 // uniform branch: spill what we have, restart the list
-            __syncthreads();
             spill(nl);
-            __syncthreads();
-            if (tid == 0) { sh.nlist = 0; sh.overflow = 1; }
-            __syncthreads();
+            if (tid == 0) sh.overflow = 1;
             nl = 0;
         }
-        if (hit) sh.ids[nl + before + __popc(m & ((1u << lane) - 1u))] = f;
-        __syncthreads();
-        if (tid == 0) sh.nlist = nl + total;
+#pragma unroll
+        for (int u = 0; u < kSub; ++u)
+            if (hit[u]) sh.ids[nl + before[u] + __popc(m[u] & ((1u << lane) - 1u))] = base + u * kThreads + tid;
+        nl += total;
         __syncthreads();
     }
+    if (tid == 0) sh.nlist = nl;
+    __syncthreads();
 }
 
 // Evaluate the first `count` faces of the tile list for this thread's pixel: fn(j_in_list, face_id, rec, eval).
@@ -221,7 +238,7 @@ FB_DEVINL void for_each_listed(const SilParams& P, int n, int count, float px, f
 
 FB_DEVINL uint32_t depth_bits(float pz) { return __float_as_uint(pz) & 0x7fffffffu; }
 
-__global__ void __launch_bounds__(kThreads) sil_tile_fwd_kernel(const __grid_constant__ SilParams P) {
+__global__ void __launch_bounds__(kThreads, 4) sil_tile_fwd_kernel(const __grid_constant__ SilParams P) {
     pdl_wait_trigger();
     __shared__ TileShared sh;
     const int tid = threadIdx.x;
@@ -232,10 +249,17 @@ __global__ void __launch_bounds__(kThreads) sil_tile_fwd_kernel(const __grid_con
     // first walk so that a pixel with more than K candidates selects its K nearest from its own list (no re-evaluation)
     uint32_t* cbits = P.cand_bits + (size_t)blockIdx.x * P.cap * kThreads;
     float* cfac = P.cand_fac + (size_t)blockIdx.x * P.cap * kThreads;
-    for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+    for (;;) {
+    // dynamic tile queue: tiles on the silhouette boundary cost 10x a background tile, so a static stride leaves a long tail
+    __syncthreads();
+    if (tid == 0) sh.next_tile = (int)atomicAdd(P.tile_counter, 1u);
+    __syncthreads();
+    const long long tile = sh.next_tile;
+    if (tile >= n_tiles) break;
     const int n = (int)(tile / (tiles_x * tiles_y)), trem = (int)(tile - (long long)n * tiles_x * tiles_y);
     const int tile_y = trem / tiles_x, tile_x = trem - tile_y * tiles_x;
-    const int col = tile_x * kTile + (tid & (kTile - 1)), row = tile_y * kTile + (tid >> 4);
+    // a warp covers 8 x 4 pixels (not 16 x 2): fewer faces touch a warp's footprint, so fewer divergent evaluations
+    const int col = tile_x * kTile + ((tid >> 5) & 1) * 8 + (tid & 7), row = tile_y * kTile + (tid >> 6) * 4 + ((tid >> 3) & 3);
     const bool in_img = (col < P.W) && (row < P.H);
     const float px = 1.f - __fdiv_rn((float)(2 * col + 1), (float)P.W), py = 1.f - __fdiv_rn((float)(2 * row + 1), (float)P.H);
     const int c_hi = min(tile_x * kTile + kTile - 1, P.W - 1), r_hi = min(tile_y * kTile + kTile - 1, P.H - 1);
@@ -371,11 +395,11 @@ __global__ void __launch_bounds__(kThreads) sil_tile_fwd_kernel(const __grid_con
     }   // tile loop
 }
 
-__global__ void __launch_bounds__(kThreads) sil_tile_bwd_kernel(const __grid_constant__ SilParams P) {
+__global__ void __launch_bounds__(kThreads, 4) sil_tile_bwd_kernel(const __grid_constant__ SilParams P) {
     pdl_wait_trigger();
     __shared__ TileShared sh;
     const int n = blockIdx.z, tid = threadIdx.x, lane = tid & 31;
-    const int col = blockIdx.x * kTile + (tid & (kTile - 1)), row = blockIdx.y * kTile + (tid >> 4);
+    const int col = blockIdx.x * kTile + ((tid >> 5) & 1) * 8 + (tid & 7), row = blockIdx.y * kTile + (tid >> 6) * 4 + ((tid >> 3) & 3);
     const bool in_img = (col < P.W) && (row < P.H);
     const float px = 1.f - __fdiv_rn((float)(2 * col + 1), (float)P.W), py = 1.f - __fdiv_rn((float)(2 * row + 1), (float)P.H);
     const int c_hi = min(blockIdx.x * kTile + kTile - 1, P.W - 1), r_hi = min(blockIdx.y * kTile + kTile - 1, P.H - 1);
@@ -441,7 +465,15 @@ using namespace fb::raster;
 
 namespace {
 struct WsLayout { size_t box, rec, flag, cbits, cfac, total; };
-constexpr int kFwdCtas = 148 * 3;
+constexpr int kFwdCtas = 148 * 4;             // persistent CTAs of the forward kernel (4 per SM: 64 registers, 36 KB shared)
+int prefer_shared() {                         // 4 x 36 KB of static shared memory per SM needs the larger carve-out
+    static int rc = [] {
+        cudaError_t e = cudaFuncSetAttribute(sil_tile_fwd_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(sil_tile_bwd_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+        return (int)e;
+    }();
+    return rc;
+}
 int cand_cap() {
     const char* e = getenv("FINDB200_SIL_CAP");          // tests force the re-evaluation path with a small capacity
     const int c = e ? atoi(e) : 384;
@@ -460,7 +492,7 @@ WsLayout ws_layout(int N, int F) {
 }
 int fill(SilParams& P, void* ws, size_t ws_bytes, int N, int V, int F, int H, int W, float blur_radius, float sigma, int K, int perspective, bool scratch) {
     FB_REQUIRE(N >= 0 && V >= 1 && F >= 0 && H >= 1 && W >= 1, FINDB200_ERR_SHAPE, "silhouette: bad shape N=%d V=%d F=%d H=%d W=%d", N, V, F, H, W);
-    FB_REQUIRE(N <= 65535, FINDB200_ERR_SHAPE, "silhouette: at most 65535 meshes x views per call (got %d)", N);
+    FB_REQUIRE(N <= 65535 && (long long)N * ((W + 15) / 16) * ((H + 15) / 16) < 2000000000ll, FINDB200_ERR_SHAPE, "silhouette: too many meshes x views x tiles in one call (N=%d)", N);
     FB_REQUIRE(blur_radius >= 0.f && sigma > 0.f && K >= 1, FINDB200_ERR_ARG, "silhouette: blur_radius >= 0, sigma > 0 and faces_per_pixel >= 1 required");
     const WsLayout L = ws_layout(N, F);
     const size_t need = scratch ? L.total : L.cbits;
@@ -469,6 +501,7 @@ int fill(SilParams& P, void* ws, size_t ws_bytes, int N, int V, int F, int H, in
     P.box = (const float4*)((char*)ws + L.box);
     P.rec = (const FaceRec*)((char*)ws + L.rec);
     P.overflow = (unsigned int*)((char*)ws + L.flag);
+    P.tile_counter = P.overflow + 1;
     P.cand_bits = (uint32_t*)((char*)ws + L.cbits);
     P.cand_fac = (float*)((char*)ws + L.cfac);
     P.cap = cand_cap();
@@ -492,13 +525,14 @@ extern "C" int findb200_silhouette_forward(const float* verts_ndc, const int32_t
     FB_REQUIRE(verts_ndc && (faces || F == 0) && alpha, FINDB200_ERR_ARG, "silhouette_forward: null argument");
     if (N == 0) return 0;
     P.alpha = alpha; P.prod = prod; P.sel = (uint2*)sel;
-    FB_CUDA(cudaMemsetAsync(P.overflow, 0, sizeof(unsigned int), st));
+    FB_CUDA(cudaMemsetAsync(P.overflow, 0, 2 * sizeof(unsigned int), st));      // status flag + tile queue
     if (F > 0) {
         FB_MARK("face_setup", st);
         const long long tot = (long long)N * F;
         FB_CUDA(launch_pdl(face_setup_kernel, dim3((unsigned)((tot + 255) / 256)), dim3(256), 0, st, verts_ndc, faces, N, V, F,
                            sqrtf(blur_radius), (float4*)P.box, (FaceRec*)P.rec));
     }
+    FB_CUDA((cudaError_t)prefer_shared());
     FB_MARK("sil_tile_fwd", st);
     const long long n_tiles = (long long)N * ((W + kTile - 1) / kTile) * ((H + kTile - 1) / kTile);
     FB_CUDA(launch_pdl(sil_tile_fwd_kernel, dim3((unsigned)(n_tiles < kFwdCtas ? n_tiles : kFwdCtas)), dim3(kThreads), 0, st, P));
@@ -517,6 +551,7 @@ extern "C" int findb200_silhouette_backward(const float* grad_alpha, const int32
     if (N == 0 || F == 0) return 0;
     FB_REQUIRE(grad_alpha && faces && prod && sel && grad_verts_ndc, FINDB200_ERR_ARG, "silhouette_backward: null argument");
     P.grad_alpha = grad_alpha; P.prod = (float*)prod; P.sel = (uint2*)sel; P.grad_verts = grad_verts_ndc; P.faces = faces;
+    FB_CUDA((cudaError_t)prefer_shared());
     FB_MARK("sil_tile_bwd", st);
     FB_CUDA(launch_pdl(sil_tile_bwd_kernel, dim3((W + kTile - 1) / kTile, (H + kTile - 1) / kTile, N), dim3(kThreads), 0, st, P));
     FB_MARK_END(st);
