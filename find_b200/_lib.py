@@ -60,7 +60,7 @@ SIGNATURES = {
     "findb200_silhouette_workspace_bytes": (c_size_t, [c_int] * 2),
     "findb200_silhouette_saved_bytes": (c_size_t, [c_int] * 2),
     "findb200_silhouette_forward": (c_int, [c_void_p, c_void_p] + [c_int] * 5 + [c_float, c_float, c_int, c_int]
-                                    + [c_void_p] * 4 + [c_size_t, c_void_p]),
+                                    + [c_void_p] * 6 + [c_size_t, c_void_p]),
     "findb200_silhouette_backward": (c_int, [c_void_p, c_void_p] + [c_int] * 5 + [c_float, c_float, c_int, c_int]
                                      + [c_void_p] * 4 + [c_size_t, c_void_p]),
     "findb200_silhouette_status": (c_int, [c_void_p, c_int, c_int, c_void_p]),

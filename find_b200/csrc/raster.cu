@@ -43,6 +43,8 @@ struct SilParams {
     float* alpha;                         // [N, H, W]
     float* prod;                          // [N, H, W]   prod_k (1 - p_k) of the kept candidates
     uint2* sel;                           // [N, H, W]   (depth-threshold bits, ties allowed); (0xffffffff, 0) = all kept
+    int* pix_to_face;                     // [N, H, W]   optional: nearest candidate face of the pixel (per-mesh index), -1 = none
+    float* zbuf;                          // [N, H, W]   optional: its depth, -1 = none
     const float* grad_alpha;              // backward
     float* grad_verts;                    // [N, V, 3]
     const int* faces;                     // [F, 3] (backward: vertex ids)
@@ -66,7 +68,8 @@ __global__ void face_setup_kernel(const float* __restrict__ verts, const int* __
     r.x0 = v[3 * i0]; r.y0 = v[3 * i0 + 1]; r.z0 = v[3 * i0 + 2];
     r.x1 = v[3 * i1]; r.y1 = v[3 * i1 + 1]; r.z1 = v[3 * i1 + 2];
     r.x2 = v[3 * i2]; r.y2 = v[3 * i2 + 1]; r.z2 = v[3 * i2 + 2];
-    r.pad0 = r.pad1 = r.pad2 = 0.f;
+    r.pad0 = __int_as_float(f);              // face id travels with the record (pix_to_face output)
+    r.pad1 = r.pad2 = 0.f;
     const float area = __fsub_rn(__fmul_rn(r.x2 - r.x0, r.y1 - r.y0), __fmul_rn(r.y2 - r.y0, r.x1 - r.x0));
     const float zmax = fmaxf(fmaxf(r.z0, r.z1), r.z2);
     const bool ok = (fabsf(area) > kEps) && (zmax >= 0.f);     // NaN coordinates fail both tests
@@ -270,13 +273,15 @@ __global__ void __launch_bounds__(kThreads, 4) sil_tile_fwd_kernel(const __grid_
     float prod = 1.f;
     uint2 sel = make_uint2(0xffffffffu, 0u);
     uint32_t zlo = 0xffffffffu, zhi = 0u;           // depth range of this pixel's candidates (bit patterns)
-    auto accumulate = [&](int, const FaceRec&, const Eval& e) {
+    int near_face = -1;
+    auto accumulate = [&](int, const FaceRec& r, const Eval& e) {
         if (e.cand) {
             const float fac = 1.f - sigmoidf_((e.inside ? e.d2 : -e.d2) * inv_sigma);
             const uint32_t b = depth_bits(e.pz);
             if (cnt < P.cap) { cbits[(size_t)cnt * kThreads + tid] = b; cfac[(size_t)cnt * kThreads + tid] = fac; }
             ++cnt;
             prod = __fmul_rn(prod, fac);
+            if (b < zlo) near_face = __float_as_int(r.pad0);      // strict: the earlier face wins a depth tie (faces arrive in order)
             zlo = min(zlo, b); zhi = max(zhi, b);
         }
     };
@@ -390,6 +395,8 @@ __global__ void __launch_bounds__(kThreads, 4) sil_tile_fwd_kernel(const __grid_
         P.alpha[o] = 1.f - prod;
         if (P.prod) P.prod[o] = prod;
         if (P.sel) P.sel[o] = sel;
+        if (P.pix_to_face) P.pix_to_face[o] = near_face;
+        if (P.zbuf) P.zbuf[o] = near_face >= 0 ? __uint_as_float(zlo) : -1.f;
     }
     __syncthreads();
     }   // tile loop
@@ -517,14 +524,14 @@ extern "C" size_t findb200_silhouette_saved_bytes(int N, int F) { return ws_layo
 
 extern "C" int findb200_silhouette_forward(const float* verts_ndc, const int32_t* faces, int N, int V, int F, int H, int W,
                                            float blur_radius, float sigma, int faces_per_pixel, int perspective_correct,
-                                           float* alpha, float* prod, void* sel, void* ws, size_t ws_bytes, void* stream) {
+                                           float* alpha, float* prod, void* sel, int32_t* pix_to_face, float* zbuf, void* ws, size_t ws_bytes, void* stream) {
     cudaStream_t st = (cudaStream_t)stream;
     SilParams P;
     int rc = fill(P, ws, ws_bytes, N, V, F, H, W, blur_radius, sigma, faces_per_pixel, perspective_correct, true);
     if (rc) return rc;
     FB_REQUIRE(verts_ndc && (faces || F == 0) && alpha, FINDB200_ERR_ARG, "silhouette_forward: null argument");
     if (N == 0) return 0;
-    P.alpha = alpha; P.prod = prod; P.sel = (uint2*)sel;
+    P.alpha = alpha; P.prod = prod; P.sel = (uint2*)sel; P.pix_to_face = pix_to_face; P.zbuf = zbuf;
     FB_CUDA(cudaMemsetAsync(P.overflow, 0, 2 * sizeof(unsigned int), st));      // status flag + tile queue
     if (F > 0) {
         FB_MARK("face_setup", st);

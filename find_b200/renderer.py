@@ -64,20 +64,23 @@ class _Silhouette(torch.autograd.Function):
         alpha = torch.empty(N, H, W, dtype=torch.float32, device=dev)
         prod = torch.empty_like(alpha)
         sel = torch.empty(N, H, W, 2, dtype=torch.int32, device=dev)
+        p2f = torch.empty(N, H, W, dtype=torch.int32, device=dev)
+        zbuf = torch.empty(N, H, W, dtype=torch.float32, device=dev)
         ws = torch.empty(int(lib.findb200_silhouette_workspace_bytes(N, F)), dtype=torch.uint8, device=dev)
         with torch.cuda.device(dev):
             rc = lib.findb200_silhouette_forward(_lib.ptr(v), _lib.ptr(faces_i32), N, V, F, H, W, float(blur_radius), float(sigma),
                                                  int(K), int(bool(perspective)), _lib.ptr(alpha), _lib.ptr(prod), _lib.ptr(sel),
-                                                 _lib.ptr(ws), ws.numel(), _lib.stream_ptr(dev))
+                                                 _lib.ptr(p2f), _lib.ptr(zbuf), _lib.ptr(ws), ws.numel(), _lib.stream_ptr(dev))
         _lib.check(rc, "findb200_silhouette_forward")
         if ctx.needs_input_grad[0]:                        # the backward reads the face records only: drop the scratch part
             ws = ws[: int(lib.findb200_silhouette_saved_bytes(N, F))].clone()
         ctx.save_for_backward(faces_i32, prod, sel, ws)
         ctx.cfg = (N, V, F, H, W, float(blur_radius), float(sigma), int(K), int(bool(perspective)))
-        return alpha
+        ctx.mark_non_differentiable(p2f, zbuf)
+        return alpha, p2f, zbuf
 
     @staticmethod
-    def backward(ctx, g_alpha):
+    def backward(ctx, g_alpha, _g_p2f, _g_zbuf):
         lib = _lib.load()
         faces_i32, prod, sel, ws = ctx.saved_tensors
         N, V, F, H, W, blur_radius, sigma, K, perspective = ctx.cfg
@@ -93,15 +96,18 @@ class _Silhouette(torch.autograd.Function):
 
 
 def rasterize_silhouette(verts_ndc: torch.Tensor, faces: torch.Tensor, image_size, blur_radius: float = None, sigma: float = SIGMA,
-                         faces_per_pixel: int = 100, perspective_correct: bool = True) -> torch.Tensor:
-    """verts_ndc [N,V,3] (x, y NDC; z view depth), faces [F,3] shared -> alpha [N,H,W]; differentiable w.r.t. x, y."""
+                         faces_per_pixel: int = 100, perspective_correct: bool = True, return_fragments: bool = False):
+    """verts_ndc [N,V,3] (x, y NDC; z view depth), faces [F,3] shared -> alpha [N,H,W]; differentiable w.r.t. x, y.
+    ``return_fragments`` adds (pix_to_face [N,H,W] int32, zbuf [N,H,W]): the nearest candidate face of every pixel (index within
+    the mesh, -1 = none) and its depth — the ``[..., 0]`` slice of PyTorch3D's silhouette Fragments."""
     H, W = (image_size, image_size) if isinstance(image_size, int) else image_size
     if blur_radius is None:
         blur_radius = math.log(1.0 / 1e-4 - 1.0) * sigma
     if faces.dim() != 2 or faces.shape[1] != 3:
         raise ValueError("faces must be [F,3] (one topology shared by the batch)")
     f = faces if faces.dtype == torch.int32 else faces.to(torch.int32)
-    return _Silhouette.apply(verts_ndc, f.contiguous(), int(H), int(W), blur_radius, sigma, faces_per_pixel, perspective_correct)
+    alpha, p2f, zbuf = _Silhouette.apply(verts_ndc, f.contiguous(), int(H), int(W), blur_radius, sigma, faces_per_pixel, perspective_correct)
+    return (alpha, p2f, zbuf) if return_fragments else alpha
 
 
 class FootRenderer(nn.Module):
@@ -166,9 +172,12 @@ class FootRenderer(nn.Module):
     def forward(self, input_meshes: Meshes, R, T, return_images=False, return_depth=False, return_mask=True, mask_with_grad=True,
                 mask_out_faces=False, masked_faces=None, keypoints=None, keypoints_blend=False, lights=None,
                 return_mask_out_masks=False, return_features=False, features=None) -> dict:
-        if return_images or return_features or return_depth or keypoints is not None or mask_out_faces:
+        if return_images or return_features or return_depth or keypoints is not None:
             raise NotImplementedError("find_b200.renderer: only the soft-silhouette mask (return_mask=True, return_images=False) is "
                                       "built; Phong / feature / depth / keypoint rendering is the rest of SURVEY.md §8(f) row 4")
+        if mask_out_faces and masked_faces is None:
+            raise NotImplementedError("find_b200.renderer: mask_out_faces needs masked_faces (the TexturesUV u = v = 0 convention of "
+                                      "renderer.py:337-345 is not built)")
         if not return_mask:
             return {}
         verts = input_meshes.verts_padded()
@@ -176,6 +185,22 @@ class FootRenderer(nn.Module):
         if not shared:
             raise NotImplementedError("find_b200.renderer: the meshes of one call must share their topology (FIND's template)")
         num_views, num_meshes = R.shape[0], len(input_meshes)
+        S = self.image_size
         ndc = self.project(verts, R, T)
-        alpha = rasterize_silhouette(ndc, faces, self.image_size, self.blur_radius, self.sigma, self.faces_per_pixel, True)
-        return {"mask": alpha.reshape(num_meshes, num_views, self.image_size, self.image_size)}
+        alpha, p2f, _ = rasterize_silhouette(ndc, faces, S, self.blur_radius, self.sigma, self.faces_per_pixel, True, return_fragments=True)
+        mask = alpha.reshape(num_meshes, num_views, S, S)
+        out = {}
+        if mask_out_faces:
+            # renderer.py:318-365: the closest face of every pixel; pixels whose closest face is in masked_faces are zeroed
+            p2f = p2f.reshape(num_meshes, num_views, S, S)
+            masks = []
+            mask = mask.clone()
+            for n in range(num_meshes):
+                mf = masked_faces[n] if isinstance(masked_faces, list) else masked_faces
+                mpix = torch.isin(p2f[n], mf.to(p2f.device, p2f.dtype))
+                masks.append(mpix)
+                mask[n, mpix] = 0.0
+            if return_mask_out_masks:
+                out["mask_out_masks"] = torch.stack(masks).reshape(num_meshes, num_views, S, S)
+        out["mask"] = mask
+        return out

@@ -183,7 +183,9 @@ int findb200_mesh_smooth(const float* verts, int N, int V, const int32_t* faces,
  * verts_ndc [N,V,3] fp32: x, y in PyTorch3D NDC (+x left, +y up), z = view-space depth — what MeshRasterizer.transform
  * produces; N counts meshes x views.  faces [F,3] int32 shared by all N.  alpha [N,H,W] = 1 - prod_k (1 - sigmoid(-signed
  * squared distance_k / sigma)) over the faces_per_pixel candidates of smallest depth (earlier face on ties).
- * prod [N,H,W] fp32 and sel [N,H,W] x 8 bytes are saved for the backward (may be NULL for inference).  The backward ADDS
+ * prod [N,H,W] fp32 and sel [N,H,W] x 8 bytes are saved for the backward (may be NULL for inference).  pix_to_face / zbuf
+ * [N,H,W] (optional) receive the nearest candidate face of each pixel (index within the mesh, -1 = none) and its depth: the
+ * [..., 0] slice of the silhouette Fragments that FootRenderer's mask_out_faces reads (renderer.py:318-327).  The backward ADDS
  * d alpha / d (x, y) into grad_verts_ndc [N,V,3] (z receives no gradient) and must be given the workspace the forward
  * filled.  findb200_silhouette_status synchronises and returns 1 if a tile could not apply the K truncation exactly
  * (> 4096 faces on one 16 x 16 tile together with a pixel of more than faces_per_pixel candidates).
@@ -192,7 +194,8 @@ size_t findb200_silhouette_workspace_bytes(int N, int F);
 size_t findb200_silhouette_saved_bytes(int N, int F);   /* prefix of the workspace the backward needs; the rest is scratch */
 int findb200_silhouette_forward(const float* verts_ndc, const int32_t* faces, int N, int V, int F, int H, int W,
                                 float blur_radius, float sigma, int faces_per_pixel, int perspective_correct,
-                                float* alpha, float* prod, void* sel, void* workspace, size_t workspace_bytes, void* stream);
+                                float* alpha, float* prod, void* sel, int32_t* pix_to_face, float* zbuf, void* workspace,
+                                size_t workspace_bytes, void* stream);
 int findb200_silhouette_backward(const float* grad_alpha, const int32_t* faces, int N, int V, int F, int H, int W,
                                  float blur_radius, float sigma, int faces_per_pixel, int perspective_correct,
                                  const float* prod, const void* sel, float* grad_verts_ndc, void* workspace,

@@ -105,7 +105,10 @@ def silhouette(verts: torch.Tensor, faces: torch.Tensor, H: int, W: int, blur_ra
     prod = torch.prod(1.0 - prob, dim=1)
     alpha = (1.0 - prod).reshape(H, W)
     if return_aux:
-        return alpha, dict(count=cand.sum(1).reshape(H, W), keep=keep, prod=prod.reshape(H, W))
+        nearest = torch.where(cand.any(1), order[:, 0], torch.full_like(order[:, 0], -1))       # pix_to_face[..., 0]
+        znear = torch.where(cand.any(1), key.gather(1, order[:, :1])[:, 0], torch.full_like(key[:, 0], -1.0))
+        return alpha, dict(count=cand.sum(1).reshape(H, W), keep=keep, prod=prod.reshape(H, W), pix_to_face=nearest.reshape(H, W),
+                           zbuf=znear.reshape(H, W))
     return alpha
 
 

@@ -123,8 +123,8 @@ def test_foot_renderer_mask_full_size_properties_and_world_gradient():
     R, T = r.view_from(["topdown", "side1", "45"])
     vw = verts.to(dev).requires_grad_(True)
     out = r(Meshes(vw, tf.to(dev)), R, T, return_images=False, return_mask=True)
-    m = out["mask"]
-    assert m.shape == (2, 3, 256, 256) and float(m.min()) >= 0.0 and float(m.max()) <= 1.0
+    m = out["mask"]; md = m.detach()
+    assert m.shape == (2, 3, 256, 256) and float(md.min()) >= 0.0 and float(md.max()) <= 1.0
     frac = (m > 0.5).float().mean(dim=(2, 3))
     assert float(frac.min()) > 0.03 and float(frac.max()) < 0.8
     soft = ((m > 1e-3) & (m < 1 - 1e-3)).float().mean()
@@ -166,3 +166,32 @@ def test_k_truncation_re_evaluation_path(monkeypatch):
     monkeypatch.setenv("FINDB200_SIL_CAP", "40")
     test_k_truncation_by_depth_with_ties(100)
     test_k_truncation_by_depth_with_ties(5)
+
+
+@pytest.mark.gpu
+def test_nearest_face_fragments_and_mask_out_faces():
+    dev, verts, tf, r, R, T = _scene(642, ["topdown", "side1"], B=2, seed=4)
+    S = 64
+    ndc = r.project(verts, R, T)                                          # [4, V, 3]
+    alpha, p2f, zbuf = rasterize_silhouette(ndc.to(dev), tf.to(dev), S, return_fragments=True)
+    for k in range(ndc.shape[0]):
+        _, aux = ro.silhouette(ndc[k], tf, S, S, return_aux=True)
+        same = (p2f[k].cpu().long() == aux["pix_to_face"])
+        assert float(same.float().mean()) > 0.999                        # a depth tie between two faces may resolve differently
+        assert torch.equal(p2f[k].cpu() < 0, aux["pix_to_face"] < 0)
+        assert float((zbuf[k].cpu() - aux["zbuf"].float())[same].abs().max()) < 1e-6
+    # FootRenderer: pixels whose closest face is masked are zeroed, the rest is untouched, gradients still flow
+    masked = torch.arange(0, tf.shape[0], 3, device=dev)
+    vw = verts.to(dev).requires_grad_(True)
+    mesh = Meshes(vw, tf.to(dev))
+    plain = r(mesh, R, T)["mask"]
+    out = r(mesh, R, T, mask_out_faces=True, masked_faces=masked, return_mask_out_masks=True)
+    mm = out["mask_out_masks"]
+    assert mm.shape == (2, 2, S, S) and mm.dtype == torch.bool and 0.05 < float(mm.float().mean()) < 0.5
+    assert float(out["mask"][mm].abs().max()) == 0.0 and torch.equal(out["mask"][~mm], plain[~mm])
+    expect = torch.isin(p2f.reshape(2, 2, S, S), masked.to(torch.int32))
+    assert torch.equal(mm, expect)
+    out["mask"].sum().backward()
+    assert torch.isfinite(vw.grad).all() and float(vw.grad.abs().max()) > 0
+    lst = r(mesh, R, T, mask_out_faces=True, masked_faces=[masked, masked[:5]], return_mask_out_masks=True)
+    assert torch.equal(lst["mask_out_masks"][0], mm[0]) and int(lst["mask_out_masks"][1].sum()) < int(mm[1].sum())
