@@ -211,6 +211,91 @@ class TrainStep:
                                                     _lib.ptr(self.idx), self.B, _lib.ptr(self.grows[k]), st)
             _lib.check(rc, "findb200_scatter_add_rows")
 
+    # ---- pipelined host feed: the NEXT batch crosses PCIe on a copy stream while the current step computes ---------------
+    def prefetch_from_host(self, idx: torch.Tensor, target: torch.Tensor, col_target: Optional[torch.Tensor] = None):
+        """Stage one batch (pinned host tensors) into one of two device staging sets on a side stream.  Pair every call with
+        one ``step_prefetched()``; at most two batches may be staged ahead."""
+        if getattr(self, "_copy_stream", None) is None:
+            self._copy_stream = torch.cuda.Stream(device=self.dev)
+            self._stage = [dict(idx=torch.empty_like(self.idx), target=torch.empty_like(self.target),
+                                col_target=None if self.col_target is None else torch.empty_like(self.col_target)) for _ in range(2)]
+            self._ready = [torch.cuda.Event() for _ in range(2)]
+            self._consumed = [torch.cuda.Event() for _ in range(2)]
+            self._staged, self._stage_next = [], 0
+        if len(self._staged) >= 2:
+            raise RuntimeError("prefetch_from_host: two batches are already staged; call step_prefetched() first")
+        k = self._stage_next
+        st = self._stage[k]
+        with torch.cuda.stream(self._copy_stream):
+            self._copy_stream.wait_event(self._consumed[k])          # the step that last used this set has copied it out
+            st["idx"].copy_(idx, non_blocking=True)
+            st["target"].copy_(target, non_blocking=True)
+            if st["col_target"] is not None and col_target is not None:
+                st["col_target"].copy_(col_target, non_blocking=True)
+            self._ready[k].record(self._copy_stream)
+        self._staged.append(k)
+        self._stage_next = k ^ 1
+
+    def _launch_prefetched(self, runner=None) -> int:
+        """Enqueue one step on the oldest staged batch plus an asynchronous D2H copy of its losses; -> the loss slot to collect."""
+        if not getattr(self, "_staged", None):
+            raise RuntimeError("step_prefetched: nothing staged; call prefetch_from_host() first")
+        if getattr(self, "_loss_host", None) is None:
+            self._loss_host = [torch.empty(3, dtype=torch.float32).pin_memory() for _ in range(2)]
+            self._loss_done = [torch.cuda.Event() for _ in range(2)]
+            self._loss_next = 0
+        k = self._staged.pop(0)
+        st = self._stage[k]
+        cur = torch.cuda.current_stream(self.dev)
+        cur.wait_event(self._ready[k])
+        self.idx.copy_(st["idx"], non_blocking=True)                 # device -> device into the graph's static inputs
+        self.target.copy_(st["target"], non_blocking=True)
+        if st["col_target"] is not None:
+            self.col_target.copy_(st["col_target"], non_blocking=True)
+        self._consumed[k].record(cur)
+        (runner or self).run()
+        j = self._loss_next
+        self._loss_host[j].copy_(self.loss3, non_blocking=True)
+        self._loss_done[j].record(cur)
+        self._loss_next = j ^ 1
+        return j
+
+    def _collect(self, j: int) -> Dict[str, float]:
+        self._loss_done[j].synchronize()
+        total, chamf, tex = self._loss_host[j].tolist()
+        return {"loss": total, "chamf": chamf, "tex": tex}
+
+    def step_prefetched(self, runner=None) -> Dict[str, float]:
+        """Run one step on the oldest staged batch (``runner``: a ShardedTrainStep wrapping this step, default this step)
+        and read the losses back (one D2H read, like trainer.py:128-130)."""
+        return self._collect(self._launch_prefetched(runner))
+
+    def iterate_from_host(self, batches, runner=None, deferred: bool = True):
+        """for losses in step.iterate_from_host(loader): ... — ``batches`` yields (idx, target, col_target) pinned host tensors.
+        Batch k+1 is staged on the copy stream before step k is enqueued, and (``deferred``) the losses of step k are read
+        from pinned memory only after step k+1 has been enqueued, so neither PCIe nor the host's launch work is exposed.
+        Yields one loss dict per batch, in order; gradients / outputs on the device are those of the LAST enqueued step."""
+        it = iter(batches)
+        try:
+            self.prefetch_from_host(*next(it))
+        except StopIteration:
+            return
+        pending = None
+        for nxt in it:
+            self.prefetch_from_host(*nxt)
+            tok = self._launch_prefetched(runner)
+            if pending is not None:
+                yield self._collect(pending)
+                pending = None
+            if deferred:
+                pending = tok
+            else:
+                yield self._collect(tok)
+        tok = self._launch_prefetched(runner)
+        if pending is not None:
+            yield self._collect(pending)
+        yield self._collect(tok)
+
     def step_from_host(self, idx: torch.Tensor, target: torch.Tensor, col_target: Optional[torch.Tensor] = None
                        ) -> Dict[str, float]:
         """The public end-to-end call: host batch in, losses out (one D2H read, like trainer.py:128-130)."""

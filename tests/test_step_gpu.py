@@ -297,3 +297,37 @@ def test_workspace_caches_match_recompute_and_follow_template_changes():
         fresh.run(); torch.cuda.synchronize()
         assert torch.equal(fresh.verts, step.verts) and torch.equal(fresh.loss3, step.loss3)
         assert not torch.equal(step.verts, first[1])
+
+
+@pytest.mark.parametrize("use_graph", [False, True])
+def test_pipelined_host_feed_matches_serial_steps(use_graph):
+    """iterate_from_host (batch k+1 staged on a copy stream while step k runs) gives, batch for batch, the losses and the
+    gradients of step_from_host; staging more than two batches ahead is refused."""
+    from find_b200 import synthetic as syn
+    from find_b200.step import TrainStep
+    B, V, P2, n_rows = 3, 700, 600, 9
+    dev, model, p, tv, tables, idx, target, colt = _setup(B, V, P2, n_rows, seed=71)
+    batches = []
+    for k in range(4):
+        g = torch.Generator().manual_seed(100 + k)
+        batches.append((torch.randperm(n_rows, generator=g)[:B].pin_memory(), syn.make_targets(B, P2, 10 * k).pin_memory(),
+                        syn.make_col_target(B, V, 10 * k).pin_memory()))
+    step = TrainStep(model, B, P2, with_colour=True, use_graph=use_graph)
+    serial, grads = [], []
+    for b in batches:
+        serial.append(step.step_from_host(*b))
+        grads.append(step.flat_grad.clone())
+    assert len({round(s["loss"], 6) for s in serial}) == 4                 # the batches really differ
+    piped = list(step.iterate_from_host(batches))
+    assert len(piped) == 4
+    for a, b in zip(serial, piped):
+        for k in ("loss", "chamf", "tex"):
+            assert abs(a[k] - b[k]) <= 1e-6 * abs(a[k])
+    assert rel_l2(step.flat_grad, grads[-1]) < 1e-5
+    step.prefetch_from_host(*batches[0]); step.prefetch_from_host(*batches[1])
+    with pytest.raises(RuntimeError):
+        step.prefetch_from_host(*batches[2])
+    assert abs(step.step_prefetched()["loss"] - serial[0]["loss"]) <= 1e-6 * serial[0]["loss"]
+    assert abs(step.step_prefetched()["loss"] - serial[1]["loss"]) <= 1e-6 * serial[1]["loss"]
+    with pytest.raises(RuntimeError):
+        step.step_prefetched()
