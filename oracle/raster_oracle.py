@@ -57,7 +57,8 @@ def _seg_dist2(px, py, ax, ay, bx, by):
 
 
 def silhouette(verts: torch.Tensor, faces: torch.Tensor, H: int, W: int, blur_radius: float | None = None,
-               sigma: float = 1e-4, faces_per_pixel: int = 100, perspective_correct: bool = True, return_aux: bool = False):
+               sigma: float = 1e-4, faces_per_pixel: int = 100, perspective_correct: bool = True, return_aux: bool = False,
+               rows: tuple | None = None):
     """verts [V,3] in NDC (x left, y up, z depth; any float dtype, autograd flows to x, y), faces [F,3] int64 -> alpha [H,W].
     Dense [H*W, F] evaluation: small cases only."""
     if blur_radius is None:
@@ -68,6 +69,9 @@ def silhouette(verts: torch.Tensor, faces: torch.Tensor, H: int, W: int, blur_ra
     x1, y1, z1 = fv[:, 1, 0], fv[:, 1, 1], fv[:, 1, 2]
     x2, y2, z2 = fv[:, 2, 0], fv[:, 2, 1], fv[:, 2, 2]
     xs, ys = pixel_centres(H, W, dt)
+    if rows is not None:                                                # only rows [r0, r1) of the H-row image
+        ys = ys[rows[0]:rows[1]]
+        H = ys.shape[0]
     px = xs[None, :].expand(H, W).reshape(-1, 1)
     py = ys[:, None].expand(H, W).reshape(-1, 1)
     area = _edge(x2, y2, x0, y0, x1, y1)                                # [F]
@@ -110,6 +114,26 @@ def silhouette(verts: torch.Tensor, faces: torch.Tensor, H: int, W: int, blur_ra
         return alpha, dict(count=cand.sum(1).reshape(H, W), keep=keep, prod=prod.reshape(H, W), pix_to_face=nearest.reshape(H, W),
                            zbuf=znear.reshape(H, W))
     return alpha
+
+
+def silhouette_blocked(verts: torch.Tensor, faces: torch.Tensor, H: int, W: int, rows_per_block: int = 4, **kw) -> torch.Tensor:
+    """The same image evaluated in row blocks, each against only the faces whose grown box reaches the block (dropping the
+    others cannot change a pixel: they fail its bounding-box test; the face order, hence the tie rule, is preserved; only the
+    rounding order of the fp32 product may differ, by ~1e-7).
+    Makes full-size images (256 x 256, 20 480 faces) affordable: seconds instead of a 1.3 G-pair dense evaluation."""
+    blur_radius = kw.get("blur_radius")
+    if blur_radius is None:
+        blur_radius = blur_radius_for(kw.get("sigma", 1e-4))
+    blur = math.sqrt(blur_radius)
+    _, ys = pixel_centres(H, W, verts.dtype)
+    fy = verts.detach()[faces][:, :, 1]
+    fmin, fmax = fy.min(1).values - blur, fy.max(1).values + blur
+    out = []
+    for r0 in range(0, H, rows_per_block):
+        r1 = min(r0 + rows_per_block, H)
+        keep = (fmax >= ys[r1 - 1]) & (fmin <= ys[r0])                   # y decreases with the row index
+        out.append(silhouette(verts, faces[keep], H, W, rows=(r0, r1), **kw))
+    return torch.cat(out, 0)
 
 
 def silhouette_batch(verts: torch.Tensor, faces: torch.Tensor, H: int, W: int, **kw) -> torch.Tensor:

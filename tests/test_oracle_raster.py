@@ -96,3 +96,14 @@ def test_look_at_view_transform_known_answers():
     assert torch.allclose(R[0].T @ R[0], torch.eye(3, dtype=torch.float64), atol=1e-12)
     p = ro.fov_project(torch.tensor([[0.1, 0.0, 0.0]], dtype=torch.float64), R[0], T[0])
     assert torch.allclose(p[0], torch.tensor([0.0, 0.0, 0.35], dtype=torch.float64), atol=1e-12)
+
+
+def test_blocked_evaluation_equals_dense():
+    torch.manual_seed(3)
+    v = torch.rand(60, 3) * torch.tensor([1.8, 1.8, 1.0]) - torch.tensor([0.9, 0.9, -0.5])
+    f = torch.randint(0, 60, (80, 3))
+    kw = dict(blur_radius=0.01, sigma=0.05, faces_per_pixel=6)
+    dense = ro.silhouette(v, f, 40, 24, **kw)
+    # equal up to the rounding order of the fp32 product (torch.prod reduces rows of different length differently)
+    assert float((ro.silhouette_blocked(v, f, 40, 24, rows_per_block=7, **kw) - dense).abs().max()) < 3e-7
+    assert torch.equal(ro.silhouette(v, f, 40, 24, rows=(8, 19), **kw), dense[8:19])

@@ -47,6 +47,19 @@ def main():
     images = feet * 4
     out.update(images=images, image_size=size, faces=int(tf.shape[0]), mpix_per_s_fwd=images * size * size / out["fwd_ms"] / 1e3,
                images_per_s_fwd_bwd=images / out["fwd_bwd_ms"] * 1e3)
+    if os.environ.get("CPU", "1") != "0":           # CPU port (oracle/raster_oracle.py, row-blocked) on ONE image of the same workload
+        import time
+        from oracle import raster_oracle as ro
+        ndc = r.project(verts[:1].cpu(), R[:1], T[:1])
+        t0 = time.perf_counter()
+        want = ro.silhouette_blocked(ndc[0], tf, size, size)
+        cpu_s = time.perf_counter() - t0
+        with torch.no_grad():
+            got = r(Meshes(verts[:1], mesh_faces), R[:1], T[:1])["mask"][0, 0].cpu()
+        err = (got - want).abs()
+        out["cpu_port"] = dict(s_per_image_fwd=cpu_s, images_per_s_fwd=1.0 / cpu_s, cores=torch.get_num_threads(), kind="port",
+                               sample="1 of the 32 images, forward only, oracle/raster_oracle.py::silhouette_blocked (torch CPU)")
+        out["parity_full_image"] = dict(max_abs_err=float(err.max()), mean_abs_err=float(err.mean()))
     print(json.dumps(out))
 
 
