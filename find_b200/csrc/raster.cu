@@ -45,6 +45,9 @@ struct SilParams {
     uint2* sel;                           // [N, H, W]   (depth-threshold bits, ties allowed); (0xffffffff, 0) = all kept
     int* pix_to_face;                     // [N, H, W]   optional: nearest candidate face of the pixel (per-mesh index), -1 = none
     float* zbuf;                          // [N, H, W]   optional: its depth, -1 = none
+    float* bary;                          // [N, H, W, 3] optional: its barycentrics, -1 = none
+    float* dists;                         // [N, H, W]   optional: its signed squared distance (negative inside), -1 = none
+    int clip;                             // clip + renormalise the barycentrics (PyTorch3D: blur_radius > 0)
     const float* grad_alpha;              // backward
     float* grad_verts;                    // [N, V, 3]
     const int* faces;                     // [F, 3] (backward: vertex ids)
@@ -109,11 +112,12 @@ struct Eval {
     bool inside;
     float d2;           // squared distance to the nearest edge
     float pz;           // interpolated depth (>= 0 for a candidate)
+    float w[3], wsum;   // barycentrics the depth was interpolated with, before the division by wsum (1 when not clipped)
     int edge;           // nearest edge: 0 = v0v1, 1 = v0v2, 2 = v1v2
     float t;            // its clamped parameter
 };
 
-FB_DEVINL Eval eval_face(const FaceRec& r, const float4& bx, float px, float py, float blur_radius, int perspective) {
+FB_DEVINL Eval eval_face(const FaceRec& r, const float4& bx, float px, float py, float blur_radius, int perspective, int clip = 1) {
     Eval e;
     e.cand = false;
     // bounding-box test of THIS pixel against the grown box of face_setup_kernel (the tile test only said the face touches the tile)
@@ -140,9 +144,15 @@ FB_DEVINL Eval eval_face(const FaceRec& r, const float4& bx, float px, float py,
         const float dn = fmaxf(__fadd_rn(__fadd_rn(t0, t1), t2), kEps);
         b0 = __fdiv_rn(t0, dn); b1 = __fdiv_rn(t1, dn); b2 = __fdiv_rn(t2, dn);
     }
-    const float c0 = fminf(fmaxf(b0, 0.f), 1.f), c1 = fminf(fmaxf(b1, 0.f), 1.f), c2 = fminf(fmaxf(b2, 0.f), 1.f);
-    const float cs = fmaxf(__fadd_rn(__fadd_rn(c0, c1), c2), 1e-5f);
-    e.pz = __fdiv_rn(__fadd_rn(__fadd_rn(__fmul_rn(c0, r.z0), __fmul_rn(c1, r.z1)), __fmul_rn(c2, r.z2)), cs);
+    if (clip) {
+        const float c0 = fminf(fmaxf(b0, 0.f), 1.f), c1 = fminf(fmaxf(b1, 0.f), 1.f), c2 = fminf(fmaxf(b2, 0.f), 1.f);
+        const float cs = fmaxf(__fadd_rn(__fadd_rn(c0, c1), c2), 1e-5f);
+        e.pz = __fdiv_rn(__fadd_rn(__fadd_rn(__fmul_rn(c0, r.z0), __fmul_rn(c1, r.z1)), __fmul_rn(c2, r.z2)), cs);
+        e.w[0] = c0; e.w[1] = c1; e.w[2] = c2; e.wsum = cs;
+    } else {
+        e.pz = __fadd_rn(__fadd_rn(__fmul_rn(b0, r.z0), __fmul_rn(b1, r.z1)), __fmul_rn(b2, r.z2));
+        e.w[0] = b0; e.w[1] = b1; e.w[2] = b2; e.wsum = 1.f;
+    }
     if (!(e.pz >= 0.f)) return e;
     e.cand = e.inside || (e.d2 < blur_radius);
     return e;
@@ -212,7 +222,8 @@ FB_DEVINL void build_tile_list(const SilParams& P, int n, float txmin, float txm
 
 // Evaluate the first `count` faces of the tile list for this thread's pixel: fn(j_in_list, face_id, rec, eval).
 template <bool kNeedVid, typename Fn>
-FB_DEVINL void for_each_listed(const SilParams& P, int n, int count, float px, float py, float blur, bool active, TileShared& sh, Fn fn) {
+FB_DEVINL void for_each_listed(const SilParams& P, int n, int count, float px, float py, float blur, bool active, TileShared& sh, Fn fn,
+                               int clip = 1) {
     const int tid = threadIdx.x;
     const FaceRec* rec = P.rec + (size_t)n * P.F;
     const bool warp_active = __any_sync(0xffffffffu, active);      // a warp with no pixel to serve only helps staging
@@ -232,7 +243,7 @@ FB_DEVINL void for_each_listed(const SilParams& P, int n, int count, float px, f
             for (int j = 0; j < m; ++j) {
                 Eval e;
                 e.cand = false;
-                if (active) e = eval_face(sh.rec[j], sh.box[j], px, py, P.blur_radius, P.perspective);
+                if (active) e = eval_face(sh.rec[j], sh.box[j], px, py, P.blur_radius, P.perspective, clip);
                 fn(j, sh.rec[j], e);
             }
     }
@@ -241,6 +252,9 @@ FB_DEVINL void for_each_listed(const SilParams& P, int n, int count, float px, f
 
 FB_DEVINL uint32_t depth_bits(float pz) { return __float_as_uint(pz) & 0x7fffffffu; }
 
+// kFragments: also keep the nearest candidate's barycentrics and signed distance (hard rasterisation); the silhouette
+// instantiation does not carry those registers.
+template <bool kFragments>
 __global__ void __launch_bounds__(kThreads, 4) sil_tile_fwd_kernel(const __grid_constant__ SilParams P) {
     pdl_wait_trigger();
     __shared__ TileShared sh;
@@ -274,24 +288,28 @@ __global__ void __launch_bounds__(kThreads, 4) sil_tile_fwd_kernel(const __grid_
     uint2 sel = make_uint2(0xffffffffu, 0u);
     uint32_t zlo = 0xffffffffu, zhi = 0u;           // depth range of this pixel's candidates (bit patterns)
     int near_face = -1;
+    float near_w0 = -1.f, near_w1 = -1.f, near_w2 = -1.f, near_ws = 1.f, near_d = -1.f;
     auto accumulate = [&](int, const FaceRec& r, const Eval& e) {
         if (e.cand) {
             const float fac = 1.f - sigmoidf_((e.inside ? e.d2 : -e.d2) * inv_sigma);
             const uint32_t b = depth_bits(e.pz);
-            if (cnt < P.cap) { cbits[(size_t)cnt * kThreads + tid] = b; cfac[(size_t)cnt * kThreads + tid] = fac; }
+            if (cnt < P.cap && P.alpha) { cbits[(size_t)cnt * kThreads + tid] = b; cfac[(size_t)cnt * kThreads + tid] = fac; }
             ++cnt;
             prod = __fmul_rn(prod, fac);
-            if (b < zlo) near_face = __float_as_int(r.pad0);      // strict: the earlier face wins a depth tie (faces arrive in order)
+            if (b < zlo) {                                        // strict: the earlier face wins a depth tie (faces arrive in order)
+                near_face = __float_as_int(r.pad0);
+                if (kFragments) { near_w0 = e.w[0]; near_w1 = e.w[1]; near_w2 = e.w[2]; near_ws = e.wsum; near_d = e.inside ? -e.d2 : e.d2; }
+            }
             zlo = min(zlo, b); zhi = max(zhi, b);
         }
     };
     build_tile_list(P, n, txmin, txmax, tymin, tymax, sh,
-                    [&](int count) { for_each_listed<false>(P, n, count, px, py, blur, in_img, sh, accumulate); });
+                    [&](int count) { for_each_listed<false>(P, n, count, px, py, blur, in_img, sh, accumulate, kFragments ? P.clip : 1); });
     const int nlist = sh.nlist;
     const bool spilled = sh.overflow != 0;
-    for_each_listed<false>(P, n, nlist, px, py, blur, in_img, sh, accumulate);
+    for_each_listed<false>(P, n, nlist, px, py, blur, in_img, sh, accumulate, kFragments ? P.clip : 1);   // the silhouette always clips
 
-    const bool sat_any = in_img && cnt > P.K;
+    const bool sat_any = in_img && P.alpha && cnt > P.K;
     if (sat_any && cnt <= P.cap) {
         // thread-local: K-th smallest depth of the stored list by 16-ary search on the bit pattern, then the product of the kept
         uint32_t lo = zlo, hi = zhi;
@@ -392,11 +410,18 @@ __global__ void __launch_bounds__(kThreads, 4) sil_tile_fwd_kernel(const __grid_
     }
     if (in_img) {
         const size_t o = ((size_t)n * P.H + row) * P.W + col;
-        P.alpha[o] = 1.f - prod;
+        if (P.alpha) P.alpha[o] = 1.f - prod;
         if (P.prod) P.prod[o] = prod;
         if (P.sel) P.sel[o] = sel;
         if (P.pix_to_face) P.pix_to_face[o] = near_face;
         if (P.zbuf) P.zbuf[o] = near_face >= 0 ? __uint_as_float(zlo) : -1.f;
+        if (kFragments && P.bary) {
+            const bool hit = near_face >= 0 && near_ws != 1.f;
+            P.bary[3 * o] = hit ? __fdiv_rn(near_w0, near_ws) : near_w0;
+            P.bary[3 * o + 1] = hit ? __fdiv_rn(near_w1, near_ws) : near_w1;
+            P.bary[3 * o + 2] = hit ? __fdiv_rn(near_w2, near_ws) : near_w2;
+        }
+        if (kFragments && P.dists) P.dists[o] = near_d;
     }
     __syncthreads();
     }   // tile loop
@@ -475,7 +500,8 @@ struct WsLayout { size_t box, rec, flag, cbits, cfac, total; };
 constexpr int kFwdCtas = 148 * 4;             // persistent CTAs of the forward kernel (4 per SM: 64 registers, 36 KB shared)
 int prefer_shared() {                         // 4 x 36 KB of static shared memory per SM needs the larger carve-out
     static int rc = [] {
-        cudaError_t e = cudaFuncSetAttribute(sil_tile_fwd_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+        cudaError_t e = cudaFuncSetAttribute(sil_tile_fwd_kernel<false>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(sil_tile_fwd_kernel<true>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
         if (e == cudaSuccess) e = cudaFuncSetAttribute(sil_tile_bwd_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
         return (int)e;
     }();
@@ -513,7 +539,7 @@ int fill(SilParams& P, void* ws, size_t ws_bytes, int N, int V, int F, int H, in
     P.cand_fac = (float*)((char*)ws + L.cfac);
     P.cap = cand_cap();
     P.N = N; P.F = F; P.H = H; P.W = W; P.V = V;
-    P.blur_radius = blur_radius; P.sigma = sigma; P.K = K; P.perspective = perspective;
+    P.blur_radius = blur_radius; P.sigma = sigma; P.K = K; P.perspective = perspective; P.clip = 1;
     return 0;
 }
 }  // namespace
@@ -542,7 +568,35 @@ extern "C" int findb200_silhouette_forward(const float* verts_ndc, const int32_t
     FB_CUDA((cudaError_t)prefer_shared());
     FB_MARK("sil_tile_fwd", st);
     const long long n_tiles = (long long)N * ((W + kTile - 1) / kTile) * ((H + kTile - 1) / kTile);
-    FB_CUDA(launch_pdl(sil_tile_fwd_kernel, dim3((unsigned)(n_tiles < kFwdCtas ? n_tiles : kFwdCtas)), dim3(kThreads), 0, st, P));
+    FB_CUDA(launch_pdl(sil_tile_fwd_kernel<false>, dim3((unsigned)(n_tiles < kFwdCtas ? n_tiles : kFwdCtas)), dim3(kThreads), 0, st, P));
+    FB_MARK_END(st);
+    return 0;
+}
+
+// Hard rasterisation (faces_per_pixel = 1): the nearest candidate face of every pixel with its depth, barycentrics and signed
+// squared distance — PyTorch3D's Fragments of rasterize_meshes(faces_per_pixel=1), as the image rasteriser of
+// renderer.py:116-120 produces them (blur_radius = 0: a candidate is a face that contains the pixel centre).
+extern "C" int findb200_rasterize_nearest(const float* verts_ndc, const int32_t* faces, int N, int V, int F, int H, int W,
+                                          float blur_radius, int perspective_correct, int clip_barycentric_coords,
+                                          int32_t* pix_to_face, float* zbuf, float* bary, float* dists, void* ws, size_t ws_bytes, void* stream) {
+    cudaStream_t st = (cudaStream_t)stream;
+    SilParams P;
+    int rc = fill(P, ws, ws_bytes, N, V, F, H, W, blur_radius, 1.f, 1, perspective_correct, true);
+    if (rc) return rc;
+    FB_REQUIRE(verts_ndc && (faces || F == 0) && pix_to_face, FINDB200_ERR_ARG, "rasterize_nearest: null argument");
+    if (N == 0) return 0;
+    P.pix_to_face = pix_to_face; P.zbuf = zbuf; P.bary = bary; P.dists = dists; P.clip = clip_barycentric_coords ? 1 : 0;
+    FB_CUDA(cudaMemsetAsync(P.overflow, 0, 2 * sizeof(unsigned int), st));
+    if (F > 0) {
+        FB_MARK("face_setup", st);
+        const long long tot = (long long)N * F;
+        FB_CUDA(launch_pdl(face_setup_kernel, dim3((unsigned)((tot + 255) / 256)), dim3(256), 0, st, verts_ndc, faces, N, V, F,
+                           sqrtf(blur_radius), (float4*)P.box, (FaceRec*)P.rec));
+    }
+    FB_CUDA((cudaError_t)prefer_shared());
+    FB_MARK("raster_nearest", st);
+    const long long n_tiles = (long long)N * ((W + kTile - 1) / kTile) * ((H + kTile - 1) / kTile);
+    FB_CUDA(launch_pdl(sil_tile_fwd_kernel<true>, dim3((unsigned)(n_tiles < kFwdCtas ? n_tiles : kFwdCtas)), dim3(kThreads), 0, st, P));
     FB_MARK_END(st);
     return 0;
 }

@@ -110,6 +110,32 @@ def rasterize_silhouette(verts_ndc: torch.Tensor, faces: torch.Tensor, image_siz
     return (alpha, p2f, zbuf) if return_fragments else alpha
 
 
+def rasterize_nearest(verts_ndc: torch.Tensor, faces: torch.Tensor, image_size, blur_radius: float = 0.0,
+                      perspective_correct: bool = True, clip_barycentric_coords: bool = None):
+    """``pytorch3d.renderer.mesh.rasterize_meshes(faces_per_pixel=1)`` for a batch sharing one topology: -> (pix_to_face [N,H,W,1]
+    int64, index within the mesh, -1 = none; zbuf [N,H,W,1]; bary_coords [N,H,W,1,3]; dists [N,H,W,1]) — the Fragments of the
+    image rasteriser (renderer.py:116-120).  Forward only: the outputs carry no autograd history."""
+    lib = _lib.load()
+    dev = _lib.require_cuda(verts_ndc)
+    H, W = (image_size, image_size) if isinstance(image_size, int) else image_size
+    if clip_barycentric_coords is None:
+        clip_barycentric_coords = blur_radius > 0.0
+    v = verts_ndc.detach().contiguous().float()
+    f = (faces if faces.dtype == torch.int32 else faces.to(torch.int32)).contiguous()
+    N, V, F = v.shape[0], v.shape[1], f.shape[0]
+    p2f = torch.empty(N, H, W, dtype=torch.int32, device=dev)
+    zbuf = torch.empty(N, H, W, dtype=torch.float32, device=dev)
+    bary = torch.empty(N, H, W, 3, dtype=torch.float32, device=dev)
+    dists = torch.empty(N, H, W, dtype=torch.float32, device=dev)
+    ws = torch.empty(int(lib.findb200_silhouette_workspace_bytes(N, F)), dtype=torch.uint8, device=dev)
+    with torch.cuda.device(dev):
+        rc = lib.findb200_rasterize_nearest(_lib.ptr(v), _lib.ptr(f), N, V, F, int(H), int(W), float(blur_radius), int(bool(perspective_correct)),
+                                            int(bool(clip_barycentric_coords)), _lib.ptr(p2f), _lib.ptr(zbuf), _lib.ptr(bary), _lib.ptr(dists),
+                                            _lib.ptr(ws), ws.numel(), _lib.stream_ptr(dev))
+    _lib.check(rc, "findb200_rasterize_nearest")
+    return p2f.long().unsqueeze(-1), zbuf.unsqueeze(-1), bary.unsqueeze(-2), dists.unsqueeze(-1)
+
+
 class FootRenderer(nn.Module):
     def __init__(self, image_size, device="cuda", background_color=(1.0, 1.0, 1.0), bin_size=None, z_clip_value=None,
                  max_faces_per_bin=None):

@@ -201,6 +201,14 @@ int findb200_silhouette_backward(const float* grad_alpha, const int32_t* faces, 
                                  const float* prod, const void* sel, float* grad_verts_ndc, void* workspace,
                                  size_t workspace_bytes, void* stream);
 int findb200_silhouette_status(const void* workspace, int N, int F, void* stream);
+/* Hard rasterisation, faces_per_pixel = 1 (the image rasteriser of src/model/renderer.py:116-120, called at :208-245): for every
+ * pixel the nearest candidate face (index within the mesh, -1 = none), its depth, barycentrics [N,H,W,3] (perspective-correct
+ * when asked, clipped + renormalised when asked) and signed squared distance (negative inside).  Same workspace size as the
+ * silhouette.  Forward only. */
+int findb200_rasterize_nearest(const float* verts_ndc, const int32_t* faces, int N, int V, int F, int H, int W,
+                               float blur_radius, int perspective_correct, int clip_barycentric_coords,
+                               int32_t* pix_to_face, float* zbuf, float* bary, float* dists, void* workspace,
+                               size_t workspace_bytes, void* stream);
 
 /* ------------------------------------------------------------------------------------------------------
  * Optimiser updates: torch.optim.Adam(main_params / latent_params) and

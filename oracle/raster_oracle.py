@@ -58,7 +58,7 @@ def _seg_dist2(px, py, ax, ay, bx, by):
 
 def silhouette(verts: torch.Tensor, faces: torch.Tensor, H: int, W: int, blur_radius: float | None = None,
                sigma: float = 1e-4, faces_per_pixel: int = 100, perspective_correct: bool = True, return_aux: bool = False,
-               rows: tuple | None = None):
+               rows: tuple | None = None, clip_barycentric_coords: bool | None = None):
     """verts [V,3] in NDC (x left, y up, z depth; any float dtype, autograd flows to x, y), faces [F,3] int64 -> alpha [H,W].
     Dense [H*W, F] evaluation: small cases only."""
     if blur_radius is None:
@@ -92,9 +92,16 @@ def silhouette(verts: torch.Tensor, faces: torch.Tensor, H: int, W: int, blur_ra
         b0, b1, b2 = t0 / dn, t1 / dn, t2 / dn
     else:
         b0, b1, b2 = w0, w1, w2
-    c0, c1, c2 = b0.clamp(0, 1), b1.clamp(0, 1), b2.clamp(0, 1)
-    cs = (c0 + c1 + c2).clamp(min=1e-5)
-    pz = (c0 * z0 + c1 * z1 + c2 * z2) / cs
+    if clip_barycentric_coords is None:                                 # renderer.py:219-221
+        clip_barycentric_coords = blur_radius > 0.0
+    if clip_barycentric_coords:
+        c0, c1, c2 = b0.clamp(0, 1), b1.clamp(0, 1), b2.clamp(0, 1)
+        cs = (c0 + c1 + c2).clamp(min=1e-5)
+        pz = (c0 * z0 + c1 * z1 + c2 * z2) / cs
+        u0, u1, u2 = c0 / cs, c1 / cs, c2 / cs
+    else:
+        pz = b0 * z0 + b1 * z1 + b2 * z2
+        u0, u1, u2 = b0, b1, b2
     d2 = torch.minimum(torch.minimum(_seg_dist2(px, py, x0, y0, x1, y1), _seg_dist2(px, py, x0, y0, x2, y2)),
                        _seg_dist2(px, py, x1, y1, x2, y2))
     cand = face_ok[None, :] & in_box & (pz >= 0) & (inside | (d2 < blur_radius))
@@ -111,9 +118,23 @@ def silhouette(verts: torch.Tensor, faces: torch.Tensor, H: int, W: int, blur_ra
     if return_aux:
         nearest = torch.where(cand.any(1), order[:, 0], torch.full_like(order[:, 0], -1))       # pix_to_face[..., 0]
         znear = torch.where(cand.any(1), key.gather(1, order[:, :1])[:, 0], torch.full_like(key[:, 0], -1.0))
+        first = order[:, :1]
+        hit = cand.any(1)
+        bary = torch.stack([u.gather(1, first)[:, 0] for u in (u0, u1, u2)], -1)
+        bary = torch.where(hit[:, None], bary, torch.full_like(bary, -1.0))
+        dist = torch.where(hit, sd.gather(1, first)[:, 0], torch.full_like(sd[:, 0], -1.0))
         return alpha, dict(count=cand.sum(1).reshape(H, W), keep=keep, prod=prod.reshape(H, W), pix_to_face=nearest.reshape(H, W),
-                           zbuf=znear.reshape(H, W))
+                           zbuf=znear.reshape(H, W), bary=bary.reshape(H, W, 3), dists=dist.reshape(H, W))
     return alpha
+
+
+def rasterize_nearest(verts: torch.Tensor, faces: torch.Tensor, H: int, W: int, blur_radius: float = 0.0,
+                      perspective_correct: bool = True, clip_barycentric_coords: bool | None = None):
+    """rasterize_meshes(faces_per_pixel=1) Fragments of one mesh: pix_to_face [H,W] (-1 = none), zbuf, bary [H,W,3], dists
+    (signed squared distance, negative inside) — the image rasteriser of renderer.py:116-120."""
+    _, aux = silhouette(verts, faces, H, W, blur_radius=blur_radius, sigma=1.0, faces_per_pixel=1, return_aux=True,
+                        perspective_correct=perspective_correct, clip_barycentric_coords=clip_barycentric_coords)
+    return aux["pix_to_face"], aux["zbuf"], aux["bary"], aux["dists"]
 
 
 def silhouette_blocked(verts: torch.Tensor, faces: torch.Tensor, H: int, W: int, rows_per_block: int = 4, **kw) -> torch.Tensor:

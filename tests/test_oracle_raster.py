@@ -107,3 +107,23 @@ def test_blocked_evaluation_equals_dense():
     # equal up to the rounding order of the fp32 product (torch.prod reduces rows of different length differently)
     assert float((ro.silhouette_blocked(v, f, 40, 24, rows_per_block=7, **kw) - dense).abs().max()) < 3e-7
     assert torch.equal(ro.silhouette(v, f, 40, 24, rows=(8, 19), **kw), dense[8:19])
+
+
+def test_hard_rasterisation_known_barycentrics_and_depth():
+    # pixel (x, y) = (-0.25, -0.25) in TRI: plain barycentrics w0 = 0.5 (vertex (-.5,-.5)), w1 = w2 = 0.25
+    r, c = _pix(4, 4, -0.25, -0.25)
+    p2f, z, bary, d = ro.rasterize_nearest(TRI, FACE, 4, 4, perspective_correct=False)
+    assert int(p2f[r, c]) == 0 and torch.allclose(bary[r, c], torch.tensor([0.5, 0.25, 0.25], dtype=torch.float64), atol=1e-7)
+    assert abs(float(z[r, c]) - 1.0) < 1e-7 and abs(float(d[r, c]) + 0.0625) < 1e-12          # inside: minus the squared distance
+    rr, cc = _pix(4, 4, 0.25, 0.25)
+    assert int(p2f[rr, cc]) == -1 and float(z[rr, cc]) == -1.0 and float(bary[rr, cc, 0]) == -1.0   # blur 0: outside pixels are empty
+    # perspective correction with depths (1, 2, 4): b_i = (w_i / z_i) / sum_j (w_j / z_j), depth = 1 / sum_j (w_j / z_j)
+    tri = TRI.clone(); tri[:, 2] = torch.tensor([1.0, 2.0, 4.0], dtype=torch.float64)
+    p2f, z, bary, d = ro.rasterize_nearest(tri, FACE, 4, 4, perspective_correct=True)
+    s = 0.5 / 1 + 0.25 / 2 + 0.25 / 4
+    want = torch.tensor([0.5 / 1 / s, 0.25 / 2 / s, 0.25 / 4 / s], dtype=torch.float64)
+    assert torch.allclose(bary[r, c], want, atol=1e-6) and abs(float(z[r, c]) - 1 / s) < 1e-6
+    # the nearer of two stacked faces wins
+    v = torch.cat([tri + torch.tensor([0.0, 0.0, 5.0]), TRI]); f = torch.tensor([[0, 1, 2], [3, 4, 5]])
+    p2f, z, _, _ = ro.rasterize_nearest(v, f, 4, 4)
+    assert int(p2f[r, c]) == 1 and abs(float(z[r, c]) - 1.0) < 1e-7

@@ -177,3 +177,27 @@ def test_nearest_face_fragments_and_mask_out_faces():
     assert torch.isfinite(vw.grad).all() and float(vw.grad.abs().max()) > 0
     lst = r(mesh, R, T, mask_out_faces=True, masked_faces=[masked, masked[:5]], return_mask_out_masks=True)
     assert torch.equal(lst["mask_out_masks"][0], mm[0]) and int(lst["mask_out_masks"][1].sum()) < int(mm[1].sum())
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("perspective", [True, False])
+def test_hard_rasterisation_fragments_match_oracle(perspective):
+    """faces_per_pixel = 1, blur 0 (the image rasteriser): nearest containing face, depth, barycentrics, signed distance."""
+    from find_b200.renderer import rasterize_nearest
+    dev, verts, tf, r, R, T = _scene(642, ["topdown", "60"], seed=6)
+    ndc = r.project(verts, R, T)
+    p2f, zbuf, bary, dists = rasterize_nearest(ndc.to(dev), tf.to(dev), (72, 56), perspective_correct=perspective)
+    assert p2f.shape == (2, 72, 56, 1) and bary.shape == (2, 72, 56, 1, 3) and p2f.dtype == torch.int64
+    for k in range(2):
+        wp, wz, wb, wd = ro.rasterize_nearest(ndc[k], tf, 72, 56, perspective_correct=perspective)
+        gp = p2f[k, ..., 0].cpu()
+        same = gp == wp
+        assert float(same.float().mean()) > 0.999 and torch.equal(gp < 0, wp < 0)
+        hit = same & (wp >= 0)
+        assert 0.1 < float(hit.float().mean()) < 0.9
+        assert float((zbuf[k, ..., 0].cpu() - wz)[same].abs().max()) < 1e-6
+        assert float((bary[k, ..., 0, :].cpu() - wb)[same].abs().max()) < 2e-5
+        assert float((dists[k, ..., 0].cpu() - wd)[same].abs().max()) < 1e-7
+        b = bary[k, ..., 0, :].cpu()[hit]
+        assert float((b.sum(-1) - 1).abs().max()) < 1e-4 and float(b.min()) > 0
+        assert float(dists[k, ..., 0].cpu()[hit].max()) <= 0.0               # inside: negative squared distance
