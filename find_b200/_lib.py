@@ -66,6 +66,8 @@ SIGNATURES = {
     "findb200_silhouette_status": (c_int, [c_void_p, c_int, c_int, c_void_p]),
     "findb200_rasterize_nearest": (c_int, [c_void_p, c_void_p] + [c_int] * 5 + [c_float, c_int, c_int] + [c_void_p] * 5
                                    + [c_size_t, c_void_p]),
+    "findb200_vertex_normals": (c_int, [c_void_p, c_int, c_int] + [c_void_p] * 6),
+    "findb200_phong_shade": (c_int, [c_void_p] * 4 + [c_int] * 4 + [c_void_p] * 4 + [c_int] + [c_void_p] * 4),
     "findb200_adam_step": (c_int, [c_void_p, c_int] + [ctypes.c_double] * 5 + [c_void_p, c_void_p]),
     "findb200_sgd_momentum_step": (c_int, [c_void_p, c_int] + [ctypes.c_double] * 3 + [c_void_p, c_void_p]),
     "findb200_allreduce_p2p_flag_bytes": (c_size_t, []),

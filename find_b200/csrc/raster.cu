@@ -628,3 +628,131 @@ extern "C" int findb200_silhouette_status(const void* ws, int N, int F, void* st
     FB_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
     return (int)flag;
 }
+
+// ------------------------------------------------------------------------------------------------------------------------
+// Phong image of the hard fragments (forward only): pytorch3d SoftPhongShader = TexturesVertex sampling + phong_shading
+// (PointLights, default Materials) + softmax_rgb_blend, as FootRenderer sets it up (renderer.py:110-115, 133) and calls it
+// (:273-275).  Restated in oracle/raster_oracle.py::phong_image.
+namespace fb {
+namespace raster {
+
+// area-weighted vertex normals, PyTorch3D's per-corner cross products, gathered over the vertex -> (face, corner) CSR list
+__global__ void vert_normals_kernel(const float* __restrict__ verts, const int* __restrict__ faces, const int* __restrict__ vf_ptr,
+                                    const int* __restrict__ vf_face, const int* __restrict__ vf_corner, int N, int V, float* __restrict__ out) {
+    pdl_wait_trigger();
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= (long long)N * V) return;
+    const int n = (int)(i / V), v = (int)(i - (long long)n * V);
+    const float* vb = verts + (size_t)n * V * 3;
+    float nx = 0.f, ny = 0.f, nz = 0.f;
+    for (int k = vf_ptr[v]; k < vf_ptr[v + 1]; ++k) {
+        const int f = vf_face[k], c = vf_corner[k];
+        const int ia = faces[3 * f + c], ib = faces[3 * f + (c + 1) % 3], ic = faces[3 * f + (c + 2) % 3];
+        const float ax = vb[3 * ia], ay = vb[3 * ia + 1], az = vb[3 * ia + 2];
+        const float ux = vb[3 * ib] - ax, uy = vb[3 * ib + 1] - ay, uz = vb[3 * ib + 2] - az;     // next corner - this corner
+        const float wx = vb[3 * ic] - ax, wy = vb[3 * ic + 1] - ay, wz = vb[3 * ic + 2] - az;     // previous corner - this corner
+        nx += uy * wz - uz * wy; ny += uz * wx - ux * wz; nz += ux * wy - uy * wx;
+    }
+    const float len = fmaxf(sqrtf(nx * nx + ny * ny + nz * nz), 1e-6f);
+    out[3 * i] = nx / len; out[3 * i + 1] = ny / len; out[3 * i + 2] = nz / len;
+}
+
+struct PhongParams {
+    const int* p2f; const float* bary; const float* zbuf; const float* dists;      // [I, H, W (,3)]
+    const float* verts; const float* normals; const float* colours;               // [M, V, 3]
+    const int* faces;
+    const float* cam;                                                              // [views, 3] camera centres (world)
+    long long n_pix; int HW, V, views;
+    float light[3], amb[3], dif[3], spec[3], bg[3];
+    float shininess, sigma, gamma, znear, zfar;
+    float* out;                                                                    // [I, H, W, 3]
+};
+
+FB_DEVINL void normalize3(float& x, float& y, float& z) {
+    const float l = fmaxf(sqrtf(x * x + y * y + z * z), 1e-6f);
+    x /= l; y /= l; z /= l;
+}
+
+__global__ void phong_shade_kernel(const __grid_constant__ PhongParams P) {
+    pdl_wait_trigger();
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= P.n_pix) return;
+    const int f = P.p2f[i];
+    float r = P.bg[0], g = P.bg[1], b = P.bg[2];
+    if (f >= 0) {
+        const int img = (int)(i / P.HW), m = img / P.views, view = img - m * P.views;
+        const float w0 = P.bary[3 * i], w1 = P.bary[3 * i + 1], w2 = P.bary[3 * i + 2];
+        const int i0 = P.faces[3 * f], i1 = P.faces[3 * f + 1], i2 = P.faces[3 * f + 2];
+        const size_t o = (size_t)m * P.V * 3;
+        float p[3], nrm[3], tex[3];
+#pragma unroll
+        for (int d = 0; d < 3; ++d) {
+            p[d] = w0 * P.verts[o + 3 * i0 + d] + w1 * P.verts[o + 3 * i1 + d] + w2 * P.verts[o + 3 * i2 + d];
+            nrm[d] = w0 * P.normals[o + 3 * i0 + d] + w1 * P.normals[o + 3 * i1 + d] + w2 * P.normals[o + 3 * i2 + d];
+            tex[d] = w0 * P.colours[o + 3 * i0 + d] + w1 * P.colours[o + 3 * i1 + d] + w2 * P.colours[o + 3 * i2 + d];
+        }
+        normalize3(nrm[0], nrm[1], nrm[2]);
+        float lx = P.light[0] - p[0], ly = P.light[1] - p[1], lz = P.light[2] - p[2];
+        normalize3(lx, ly, lz);
+        const float cosang = nrm[0] * lx + nrm[1] * ly + nrm[2] * lz;
+        const float diff = fmaxf(cosang, 0.f);
+        float vx = P.cam[3 * view] - p[0], vy = P.cam[3 * view + 1] - p[1], vz = P.cam[3 * view + 2] - p[2];
+        normalize3(vx, vy, vz);
+        const float rx = -lx + 2.f * cosang * nrm[0], ry = -ly + 2.f * cosang * nrm[1], rz = -lz + 2.f * cosang * nrm[2];
+        const float al = (cosang > 0.f) ? fmaxf(vx * rx + vy * ry + vz * rz, 0.f) : 0.f;
+        const float sp = powf(al, P.shininess);
+        const float eps = 1e-10f;
+        const float prob = __fdiv_rn(1.f, 1.f + expf(P.dists[i] / P.sigma));          // sigmoid(-dist / sigma)
+        const float z_inv = (P.zfar - P.zbuf[i]) / (P.zfar - P.znear);
+        const float z_max = fmaxf(z_inv, eps);
+        const float wnum = prob * expf((z_inv - z_max) / P.gamma);
+        const float delta = fmaxf(expf((eps - z_max) / P.gamma), eps);
+        const float den = wnum + delta;
+        const float c0 = (P.amb[0] + P.dif[0] * diff) * tex[0] + P.spec[0] * sp;
+        const float c1 = (P.amb[1] + P.dif[1] * diff) * tex[1] + P.spec[1] * sp;
+        const float c2 = (P.amb[2] + P.dif[2] * diff) * tex[2] + P.spec[2] * sp;
+        r = (wnum * c0 + delta * P.bg[0]) / den; g = (wnum * c1 + delta * P.bg[1]) / den; b = (wnum * c2 + delta * P.bg[2]) / den;
+    }
+    P.out[3 * i] = r; P.out[3 * i + 1] = g; P.out[3 * i + 2] = b;
+}
+
+}  // namespace raster
+}  // namespace fb
+
+extern "C" int findb200_vertex_normals(const float* verts, int N, int V, const int32_t* faces, const int32_t* vf_ptr,
+                                       const int32_t* vf_face, const int32_t* vf_corner, float* normals, void* stream) {
+    cudaStream_t st = (cudaStream_t)stream;
+    FB_REQUIRE(N >= 0 && V >= 1, FINDB200_ERR_SHAPE, "vertex_normals: bad shape N=%d V=%d", N, V);
+    FB_REQUIRE(verts && faces && vf_ptr && vf_face && vf_corner && normals, FINDB200_ERR_ARG, "vertex_normals: null argument");
+    if (N == 0) return 0;
+    FB_MARK("vert_normals", st);
+    const long long tot = (long long)N * V;
+    FB_CUDA(launch_pdl(fb::raster::vert_normals_kernel, dim3((unsigned)((tot + 255) / 256)), dim3(256), 0, st, verts, faces, vf_ptr, vf_face,
+                       vf_corner, N, V, normals));
+    FB_MARK_END(st);
+    return 0;
+}
+
+// shading[20] (host): light xyz, ambient rgb, diffuse rgb, specular rgb, background rgb, shininess, sigma, gamma, znear, zfar
+extern "C" int findb200_phong_shade(const int32_t* pix_to_face, const float* bary, const float* zbuf, const float* dists,
+                                    int n_images, int H, int W, int num_views, const float* verts_world, const float* vert_normals,
+                                    const float* vert_colours, const int32_t* faces, int V, const float* cam_centres,
+                                    const float* shading, float* image, void* stream) {
+    cudaStream_t st = (cudaStream_t)stream;
+    FB_REQUIRE(n_images >= 0 && H >= 1 && W >= 1 && num_views >= 1 && V >= 1 && n_images % num_views == 0, FINDB200_ERR_SHAPE,
+               "phong_shade: bad shape images=%d views=%d", n_images, num_views);
+    FB_REQUIRE(pix_to_face && bary && zbuf && dists && verts_world && vert_normals && vert_colours && faces && cam_centres && shading && image,
+               FINDB200_ERR_ARG, "phong_shade: null argument");
+    if (n_images == 0) return 0;
+    fb::raster::PhongParams P;
+    P.p2f = pix_to_face; P.bary = bary; P.zbuf = zbuf; P.dists = dists; P.verts = verts_world; P.normals = vert_normals;
+    P.colours = vert_colours; P.faces = faces; P.cam = cam_centres; P.HW = H * W; P.n_pix = (long long)n_images * H * W;
+    P.V = V; P.views = num_views; P.out = image;
+    for (int d = 0; d < 3; ++d) { P.light[d] = shading[d]; P.amb[d] = shading[3 + d]; P.dif[d] = shading[6 + d]; P.spec[d] = shading[9 + d]; P.bg[d] = shading[12 + d]; }
+    P.shininess = shading[15]; P.sigma = shading[16]; P.gamma = shading[17]; P.znear = shading[18]; P.zfar = shading[19];
+    FB_REQUIRE(P.sigma > 0.f && P.gamma > 0.f && P.zfar > P.znear, FINDB200_ERR_ARG, "phong_shade: sigma, gamma > 0 and zfar > znear required");
+    FB_MARK("phong_shade", st);
+    FB_CUDA(launch_pdl(fb::raster::phong_shade_kernel, dim3((unsigned)((P.n_pix + 255) / 256)), dim3(256), 0, st, P));
+    FB_MARK_END(st);
+    return 0;
+}

@@ -16,6 +16,7 @@ backward are libfindb200.so (``findb200_silhouette_forward/backward``).  There i
 """
 from __future__ import annotations
 
+import ctypes
 import math
 
 import numpy as np
@@ -136,6 +137,20 @@ def rasterize_nearest(verts_ndc: torch.Tensor, faces: torch.Tensor, image_size, 
     return p2f.long().unsqueeze(-1), zbuf.unsqueeze(-1), bary.unsqueeze(-2), dists.unsqueeze(-1)
 
 
+def vertex_normals(verts: torch.Tensor, topo) -> torch.Tensor:
+    """``Meshes.verts_normals_padded()``: verts [M,V,3] -> area-weighted unit normals [M,V,3] (forward only)."""
+    lib = _lib.load()
+    dev = _lib.require_cuda(verts)
+    v = verts.detach().contiguous().float()
+    topo = topo.to(dev)
+    out = torch.empty_like(v)
+    with torch.cuda.device(dev):
+        rc = lib.findb200_vertex_normals(_lib.ptr(v), v.shape[0], v.shape[1], _lib.ptr(topo.faces), _lib.ptr(topo.vf_ptr),
+                                         _lib.ptr(topo.vf_face), _lib.ptr(topo.vf_corner), _lib.ptr(out), _lib.stream_ptr(dev))
+    _lib.check(rc, "findb200_vertex_normals")
+    return out
+
+
 class FootRenderer(nn.Module):
     def __init__(self, image_size, device="cuda", background_color=(1.0, 1.0, 1.0), bin_size=None, z_clip_value=None,
                  max_faces_per_bin=None):
@@ -146,6 +161,9 @@ class FootRenderer(nn.Module):
         self.sigma = SIGMA
         self.blur_radius = float(np.log(1.0 / 1e-4 - 1.0) * self.sigma)   # renderer.py:124
         self.faces_per_pixel = 100                                   # renderer.py:125
+        self.background_color = tuple(float(c) for c in background_color)
+        self.light_location = (0.0, 0.0, 100.0)                      # PointLights(location=[[0, 0, 100]]), renderer.py:111
+        self.light_ambient, self.light_diffuse, self.light_specular, self.shininess = 0.5, 0.3, 0.2, 64.0   # PyTorch3D defaults
 
     # ---- view helpers (host-side numpy / torch, as in the reference) ---------------------------------------------------
     def sample_views(self, nviews=1, dist_mean=0.25, dist_std=0.05, elev_min=-90, elev_max=90, azim_min=0, azim_max=360,
@@ -198,14 +216,23 @@ class FootRenderer(nn.Module):
     def forward(self, input_meshes: Meshes, R, T, return_images=False, return_depth=False, return_mask=True, mask_with_grad=True,
                 mask_out_faces=False, masked_faces=None, keypoints=None, keypoints_blend=False, lights=None,
                 return_mask_out_masks=False, return_features=False, features=None) -> dict:
-        if return_images or return_features or return_depth or keypoints is not None:
-            raise NotImplementedError("find_b200.renderer: only the soft-silhouette mask (return_mask=True, return_images=False) is "
-                                      "built; Phong / feature / depth / keypoint rendering is the rest of SURVEY.md §8(f) row 4")
+        if return_features or return_depth or keypoints is not None:
+            raise NotImplementedError("find_b200.renderer: feature / depth / keypoint rendering is the rest of SURVEY.md §8(f) row 4")
+        if return_images and torch.is_grad_enabled() and (input_meshes.verts_padded().requires_grad
+                                                          or getattr(self._colours(input_meshes, False), "requires_grad", False)):
+            raise NotImplementedError("find_b200.renderer: the Phong image is forward-only so far (ground-truth / evaluation renders "
+                                      "under torch.no_grad()); its backward is the rest of SURVEY.md §8(f) row 4")
         if mask_out_faces and masked_faces is None:
             raise NotImplementedError("find_b200.renderer: mask_out_faces needs masked_faces (the TexturesUV u = v = 0 convention of "
                                       "renderer.py:337-345 is not built)")
-        if not return_mask:
+        if not return_mask and not return_images:
             return {}
+        if return_images:
+            images, img_p2f = self._render_images(input_meshes, R, T)
+            if not return_mask:
+                if mask_out_faces:
+                    images = self._mask_images(images, img_p2f, masked_faces)[0]
+                return {"image": images}
         verts = input_meshes.verts_padded()
         faces, shared = _as_i32_faces(input_meshes)
         if not shared:
@@ -216,9 +243,11 @@ class FootRenderer(nn.Module):
         alpha, p2f, _ = rasterize_silhouette(ndc, faces, S, self.blur_radius, self.sigma, self.faces_per_pixel, True, return_fragments=True)
         mask = alpha.reshape(num_meshes, num_views, S, S)
         out = {}
+        if return_images:
+            out["image"] = images
         if mask_out_faces:
             # renderer.py:318-365: the closest face of every pixel; pixels whose closest face is in masked_faces are zeroed
-            p2f = p2f.reshape(num_meshes, num_views, S, S)
+            p2f = (img_p2f if return_images else p2f).reshape(num_meshes, num_views, S, S)   # the image fragments when rendered
             masks = []
             mask = mask.clone()
             for n in range(num_meshes):
@@ -226,7 +255,59 @@ class FootRenderer(nn.Module):
                 mpix = torch.isin(p2f[n], mf.to(p2f.device, p2f.dtype))
                 masks.append(mpix)
                 mask[n, mpix] = 0.0
+                if return_images:
+                    out["image"][n, mpix] = 1.0
             if return_mask_out_masks:
                 out["mask_out_masks"] = torch.stack(masks).reshape(num_meshes, num_views, S, S)
         out["mask"] = mask
         return out
+
+
+    # ---- Phong image (forward only) -----------------------------------------------------------------------------------
+    def _colours(self, meshes: Meshes, required=True):
+        tex = meshes.textures
+        if tex is None:
+            if required:
+                raise ValueError("Meshes do not contain textures (TexturesVertex features [N,V,3] expected).")
+            return None
+        c = tex.verts_features_padded() if hasattr(tex, "verts_features_padded") else tex
+        return c
+
+    def _render_images(self, meshes: Meshes, R, T):
+        from .mesh import _topology_of
+        lib = _lib.load()
+        verts = meshes.verts_padded().detach().contiguous().float()
+        dev = _lib.require_cuda(verts)
+        topo = _topology_of(meshes).to(dev)
+        M, V = verts.shape[0], verts.shape[1]
+        nv, S = R.shape[0], self.image_size
+        colours = self._colours(meshes).detach().to(dev, torch.float32)
+        if colours.dim() == 2:
+            colours = colours.unsqueeze(0).expand(M, -1, -1)
+        colours = colours.contiguous()
+        ndc = self.project(verts, R, T)
+        p2f, zbuf, bary, dists = rasterize_nearest(ndc, topo.faces, S, blur_radius=0.0, perspective_correct=True)
+        normals = vertex_normals(verts, topo)
+        cam = (-torch.einsum("kj,kij->ki", T.to(torch.float32), R.to(torch.float32))).to(dev).contiguous()   # C = -T R^T
+        shading = (ctypes.c_float * 20)(*self.light_location, *([self.light_ambient] * 3), *([self.light_diffuse] * 3),
+                                        *([self.light_specular] * 3), *self.background_color, self.shininess, 1e-4, 1e-4,
+                                        self.znear, self.zfar)
+        image = torch.empty(M * nv, S, S, 3, dtype=torch.float32, device=dev)
+        p32 = p2f[..., 0].to(torch.int32).contiguous()
+        with torch.cuda.device(dev):
+            rc = lib.findb200_phong_shade(_lib.ptr(p32), _lib.ptr(bary.contiguous()), _lib.ptr(zbuf.contiguous()), _lib.ptr(dists.contiguous()),
+                                          M * nv, S, S, nv, _lib.ptr(verts), _lib.ptr(normals), _lib.ptr(colours), _lib.ptr(topo.faces), V,
+                                          _lib.ptr(cam), ctypes.cast(shading, ctypes.c_void_p), _lib.ptr(image), _lib.stream_ptr(dev))
+        _lib.check(rc, "findb200_phong_shade")
+        return image.reshape(M, nv, S, S, 3), p32
+
+    def _mask_images(self, images, p2f, masked_faces):
+        M, nv, S = images.shape[0], images.shape[1], images.shape[2]
+        p2f = p2f.reshape(M, nv, S, S)
+        masks = []
+        for n in range(M):
+            mf = masked_faces[n] if isinstance(masked_faces, list) else masked_faces
+            mpix = torch.isin(p2f[n], mf.to(p2f.device, p2f.dtype))
+            masks.append(mpix)
+            images[n, mpix] = 1.0
+        return images, masks

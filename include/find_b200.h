@@ -210,6 +210,18 @@ int findb200_rasterize_nearest(const float* verts_ndc, const int32_t* faces, int
                                int32_t* pix_to_face, float* zbuf, float* bary, float* dists, void* workspace,
                                size_t workspace_bytes, void* stream);
 
+/* Phong image of the hard fragments, forward only: SoftPhongShader (TexturesVertex + phong_shading with PointLights and default
+ * Materials + softmax_rgb_blend) as FootRenderer builds it (src/model/renderer.py:110-115, 133) and calls it (:273-275).
+ * findb200_vertex_normals = Meshes.verts_normals_padded() (area-weighted, normalised) over the vertex -> (face, corner) CSR list.
+ * Images are mesh-major (image = mesh * num_views + view); verts / normals / colours are per mesh [M,V,3]; cam_centres
+ * [num_views,3]; shading = 20 HOST floats: light xyz, ambient rgb, diffuse rgb, specular rgb, background rgb, shininess, sigma,
+ * gamma, znear, zfar. */
+int findb200_vertex_normals(const float* verts, int N, int V, const int32_t* faces, const int32_t* vf_ptr, const int32_t* vf_face,
+                            const int32_t* vf_corner, float* normals, void* stream);
+int findb200_phong_shade(const int32_t* pix_to_face, const float* bary, const float* zbuf, const float* dists, int n_images, int H,
+                         int W, int num_views, const float* verts_world, const float* vert_normals, const float* vert_colours,
+                         const int32_t* faces, int V, const float* cam_centres, const float* shading, float* image, void* stream);
+
 /* ------------------------------------------------------------------------------------------------------
  * Optimiser updates: torch.optim.Adam(main_params / latent_params) and
  * torch.optim.SGD(reg_params, momentum=0.9) as stepped at src/train/train.py:161-168, src/train/trainer.py:122-123.

@@ -195,3 +195,43 @@ def fov_project(verts_world: torch.Tensor, R: torch.Tensor, T: torch.Tensor, fov
     s = 1.0 / math.tan(math.radians(fov_deg) / 2.0)
     z = v[:, 2]
     return torch.stack([s * v[:, 0] / z, s * v[:, 1] / z, z], dim=1)
+
+
+# ---- Phong image of the hard fragments (SoftPhongShader as FootRenderer uses it, renderer.py:110-115, 133, 273-275) -------------
+def vertex_normals(verts: torch.Tensor, faces: torch.Tensor) -> torch.Tensor:
+    """Meshes.verts_normals_packed(): per-corner cross products accumulated on the vertices, then normalised (eps 1e-6)."""
+    vf = verts[faces]
+    n = torch.zeros_like(verts)
+    n = n.index_add(0, faces[:, 1], torch.cross(vf[:, 2] - vf[:, 1], vf[:, 0] - vf[:, 1], dim=1))
+    n = n.index_add(0, faces[:, 2], torch.cross(vf[:, 0] - vf[:, 2], vf[:, 1] - vf[:, 2], dim=1))
+    n = n.index_add(0, faces[:, 0], torch.cross(vf[:, 1] - vf[:, 0], vf[:, 2] - vf[:, 0], dim=1))
+    return torch.nn.functional.normalize(n, eps=1e-6, dim=1)
+
+
+def phong_image(p2f, bary, zbuf, dists, verts_world, faces, colours, cam_centre, light=(0.0, 0.0, 100.0), ambient=0.5, diffuse=0.3,
+                specular=0.2, shininess=64.0, background=(1.0, 1.0, 1.0), sigma=1e-4, gamma=1e-4, znear=0.02, zfar=100.0):
+    """p2f [H,W] (-1 = none), bary [H,W,3], zbuf / dists [H,W]; verts_world / colours [V,3] -> rgb [H,W,3].
+    phong_shading: colour = (ambient + diffuse * relu(n.l)) * texel + specular * relu(v.r)^shininess [n.l > 0], with the pixel's
+    position / normal / texel interpolated by the barycentrics; softmax_rgb_blend with one face per pixel."""
+    dt = verts_world.dtype
+    hit = p2f >= 0
+    f = faces[p2f.clamp(min=0)]                                           # [H,W,3]
+    vn = vertex_normals(verts_world, faces)
+    interp = lambda a: (bary[..., None] * a[f]).sum(-2)                    # noqa: E731
+    p, n, tex = interp(verts_world), interp(vn), interp(colours)
+    n = torch.nn.functional.normalize(n, eps=1e-6, dim=-1)
+    l = torch.nn.functional.normalize(torch.as_tensor(light, dtype=dt) - p, eps=1e-6, dim=-1)
+    cosang = (n * l).sum(-1)
+    v = torch.nn.functional.normalize(torch.as_tensor(cam_centre, dtype=dt) - p, eps=1e-6, dim=-1)
+    r = -l + 2 * cosang[..., None] * n
+    al = torch.relu((v * r).sum(-1)) * (cosang > 0).to(dt)
+    colour = (ambient + diffuse * torch.relu(cosang))[..., None] * tex + specular * torch.pow(al, shininess)[..., None]
+    eps = 1e-10
+    mask = hit.to(dt)
+    prob = torch.sigmoid(-dists / sigma) * mask
+    z_inv = (zfar - zbuf) / (zfar - znear) * mask
+    z_max = z_inv.clamp(min=eps)
+    wnum = prob * torch.exp((z_inv - z_max) / gamma)
+    delta = torch.exp((eps - z_max) / gamma).clamp(min=eps)
+    bg = torch.as_tensor(background, dtype=dt)
+    return (wnum[..., None] * colour + delta[..., None] * bg) / (wnum + delta)[..., None]

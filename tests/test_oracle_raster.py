@@ -127,3 +127,22 @@ def test_hard_rasterisation_known_barycentrics_and_depth():
     v = torch.cat([tri + torch.tensor([0.0, 0.0, 5.0]), TRI]); f = torch.tensor([[0, 1, 2], [3, 4, 5]])
     p2f, z, _, _ = ro.rasterize_nearest(v, f, 4, 4)
     assert int(p2f[r, c]) == 1 and abs(float(z[r, c]) - 1.0) < 1e-7
+
+
+def test_phong_known_answer_and_background():
+    v = torch.tensor([[0.0, 0.0, 0.0], [1.0, 0.0, 0.0], [0.0, 1.0, 0.0]], dtype=torch.float64)
+    f = torch.tensor([[0, 1, 2]])
+    assert torch.allclose(ro.vertex_normals(v, f), torch.tensor([[0.0, 0.0, 1.0]] * 3, dtype=torch.float64))
+    p2f = torch.tensor([[0, -1]]); bary = torch.full((1, 2, 3), 1 / 3, dtype=torch.float64)
+    zbuf = torch.tensor([[0.3, -1.0]], dtype=torch.float64); dists = torch.tensor([[-1.0, -1.0]], dtype=torch.float64)
+    col = torch.full((3, 3), 0.5, dtype=torch.float64)
+    img = ro.phong_image(p2f, bary, zbuf, dists, v, f, col, cam_centre=(1 / 3, 1 / 3, 5.0))
+    ln = math.sqrt(2 / 9 + 100.0 ** 2)
+    cosang = 100.0 / ln                                                    # n = (0,0,1), l = normalize((-1/3, -1/3, 100))
+    spec = (2 * cosang * 1.0 - cosang) ** 64                                # v = (0,0,1): v.r = -l_z + 2 cos = cos
+    want = (0.5 + 0.3 * cosang) * 0.5 + 0.2 * spec
+    assert torch.allclose(img[0, 0], torch.full((3,), want, dtype=torch.float64), atol=1e-9)
+    assert torch.equal(img[0, 1], torch.ones(3, dtype=torch.float64))       # empty pixel: the background colour
+    # a face turned away from the light gets ambient only
+    img2 = ro.phong_image(p2f, bary, zbuf, dists, v, f[:, [0, 2, 1]], col, cam_centre=(1 / 3, 1 / 3, 5.0))
+    assert torch.allclose(img2[0, 0], torch.full((3,), 0.25, dtype=torch.float64), atol=1e-9)

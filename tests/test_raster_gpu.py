@@ -33,7 +33,7 @@ def test_camera_helpers_match_the_oracle_cpu():
     for k in range(2):
         assert torch.allclose(ndc[k], ro.fov_project(tv, R[k], T[k]), atol=1e-6)
     with pytest.raises(NotImplementedError):
-        r(Meshes(tv[None], torch.zeros(1, 3, dtype=torch.int64)), R, T, return_images=True)
+        r(Meshes(tv[None], torch.zeros(1, 3, dtype=torch.int64)), R, T, return_features=True)
 
 
 def _scene(V, views, B=1, seed=0):
@@ -201,3 +201,48 @@ def test_hard_rasterisation_fragments_match_oracle(perspective):
         b = bary[k, ..., 0, :].cpu()[hit]
         assert float((b.sum(-1) - 1).abs().max()) < 1e-4 and float(b.min()) > 0
         assert float(dists[k, ..., 0].cpu()[hit].max()) <= 0.0               # inside: negative squared distance
+
+
+@pytest.mark.gpu
+def test_phong_image_forward_matches_oracle():
+    """FootRenderer.forward(return_images=True) under no_grad (ground-truth / evaluation renders): vertex normals, Phong shading
+    and softmax_rgb_blend on the hard fragments, against the oracle evaluated on the SAME fragments; 1e-4 absolute (powf(., 64))."""
+    from find_b200.mesh import MeshTopology
+    from find_b200.renderer import rasterize_nearest, vertex_normals
+    dev, verts, tf, _, _, _ = _scene(642, ["topdown"], B=2, seed=8)
+    S = 80
+    r = FootRenderer(S, device=dev)
+    R, T = r.view_from(["topdown", "side1", "45"])
+    g = torch.Generator().manual_seed(9)
+    colours = torch.rand(2, verts.shape[1], 3, generator=g)
+    topo = MeshTopology(tf.to(dev), verts.shape[1])
+    vn = vertex_normals(verts.to(dev), topo).cpu()
+    for m in range(2):
+        assert float((vn[m] - ro.vertex_normals(verts[m], tf)).abs().max()) < 1e-5
+    mesh = Meshes(verts.to(dev), tf.to(dev), textures=colours.to(dev))
+    with torch.no_grad():
+        out = r(mesh, R, T, return_images=True, return_mask=True)
+    img = out["image"].cpu()
+    assert img.shape == (2, 3, S, S, 3) and out["mask"].shape == (2, 3, S, S)
+    ndc = r.project(verts, R, T)
+    p2f, zbuf, bary, dists = (t.cpu() for t in rasterize_nearest(ndc.to(dev), tf.to(dev), S))
+    cam = -torch.einsum("kj,kij->ki", T, R)
+    for m in range(2):
+        for k in range(3):
+            i = m * 3 + k
+            want = ro.phong_image(p2f[i, ..., 0], bary[i, ..., 0, :], zbuf[i, ..., 0], dists[i, ..., 0], verts[m], tf, colours[m], cam[k])
+            err = (img[m, k] - want).abs()
+            assert float(err.max()) < 1e-4
+            empty = p2f[i, ..., 0] < 0
+            assert float((img[m, k][empty] - 1.0).abs().max()) == 0.0 and 0.1 < float((~empty).float().mean()) < 0.9
+            assert float(img[m, k][~empty].std()) > 0.02                  # shaded, not flat
+    # images only; masked faces paint the image white; gradients are refused (forward only)
+    with torch.no_grad():
+        only = r(mesh, R, T, return_images=True, return_mask=False)
+        masked = r(mesh, R, T, return_images=True, return_mask=True, mask_out_faces=True, masked_faces=torch.arange(0, tf.shape[0], 2, device=dev),
+                   return_mask_out_masks=True)
+    assert torch.equal(only["image"].cpu(), img)
+    mm = masked["mask_out_masks"]
+    assert float((masked["image"][mm] - 1.0).abs().max()) == 0.0 and float(masked["mask"][mm].abs().max()) == 0.0
+    with pytest.raises(NotImplementedError):
+        r(Meshes(verts.to(dev).requires_grad_(True), tf.to(dev), textures=colours.to(dev)), R, T, return_images=True)
