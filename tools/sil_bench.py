@@ -36,6 +36,9 @@ def main():
     out = {}
     with torch.no_grad():
         out["fwd_ms"] = timed(lambda: r(Meshes(verts, mesh_faces), R, T))
+    colours = torch.rand(feet, tv.shape[0], 3, device=dev)
+    with torch.no_grad():                           # Phong image (hard rasterisation + vertex normals + shading), forward only
+        out["image_fwd_ms"] = timed(lambda: r(Meshes(verts, mesh_faces, textures=colours), R, T, return_images=True, return_mask=False))
     vg = verts.clone().requires_grad_(True)
     target = torch.rand(feet, 4, size, size, device=dev)
 
