@@ -59,3 +59,27 @@ def test_no_cpu_fallback():
     import find_b200
     with pytest.raises(RuntimeError, match="CUDA"):
         find_b200.chamfer_distance(torch.zeros(1, 4, 3), torch.zeros(1, 4, 3))
+
+
+def test_product_path_never_touches_the_oracle_and_fails_loudly_without_cuda():
+    """The oracle is test infrastructure: nothing under find_b200/ may import or execute it; CPU tensors raise instead of
+    falling back (the renderer, the mesh ops and the step all go through _lib.require_cuda)."""
+    import os
+    import re
+    import pytest
+    import torch
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    pkg = os.path.join(root, "find_b200")
+    for dirpath, _, files in os.walk(pkg):
+        for name in files:
+            if name.endswith((".py", ".cu", ".cuh", ".h")):
+                text = open(os.path.join(dirpath, name), encoding="utf-8").read()
+                assert not re.search(r"^\s*(from|import)\s+oracle\b", text, re.M), f"{name} imports the oracle"
+                assert "oracle/_ref" not in text and "/root/reference/" not in text.replace("/root/reference/src", "").replace("/root/reference/cfgs", ""), name
+    from find_b200.renderer import rasterize_silhouette, rasterize_nearest
+    from find_b200.mesh import Meshes, sample_points_from_meshes
+    v = torch.zeros(1, 3, 3); f = torch.tensor([[0, 1, 2]])
+    for call in (lambda: rasterize_silhouette(v, f, 8), lambda: rasterize_nearest(v, f, 8),
+                 lambda: sample_points_from_meshes(Meshes(v, f), 4)):
+        with pytest.raises(RuntimeError):
+            call()
