@@ -44,12 +44,17 @@ FB_DEVINL float4 ld_peer(const float4* p) {       // peer data: never serve it f
 }
 
 // CTA b of this rank <-> CTA b of every rank.  Bounded: a rank that never arrives traps the launch instead of hanging the GPU.
+// kPublish: this CTA's threads have written peer memory in this kernel and those writes must be visible system-wide before the
+// flag (barrier B).  Barrier A publishes nothing of this kernel: the bucket was written by EARLIER kernels into local memory,
+// which a peer reads through this GPU's L2 — the kernel boundary already ordered those writes — so it skips the system fences
+// (each costs an NVLink round trip while remote traffic is outstanding; dropping the 256 per-thread fences of barrier A took
+// 9.5 us off the N = 2 step).
+template <bool kPublish>
 FB_DEVINL void cross_rank_barrier(const P2PParams& p, uint32_t epoch) {
-    __threadfence_system();          // this thread's remote stores are visible system-wide before the CTA signals
-    __syncthreads();
+    if (kPublish) __syncthreads();   // every thread's remote stores happen-before the flag threads' release below: st.release.sys is
+                                     // cumulative over them (the pattern of a grid barrier: bar.sync, then ONE thread fences + signals)
     const int t = threadIdx.x;
     if (t < p.world) {
-        __threadfence_system();
         st_release_sys(p.flags[t] + blockIdx.x * kMaxRanks + p.rank, epoch);
         const uint32_t* mine = p.flags[p.rank] + blockIdx.x * kMaxRanks + t;
         const long long t0 = clock64();
@@ -65,7 +70,7 @@ FB_DEVINL void cross_rank_barrier(const P2PParams& p, uint32_t epoch) {
 
 __global__ void __launch_bounds__(256) allreduce_p2p_kernel(const __grid_constant__ P2PParams p) {
     const uint32_t e = *p.epoch;
-    cross_rank_barrier(p, 2u * e + 1u);
+    cross_rank_barrier<false>(p, 2u * e + 1u);
     // slice of this rank, in float4 units
     const long long per = (p.n4 + p.world - 1) / p.world;
     const long long lo = per * p.rank, hi = min(lo + per, p.n4);
@@ -102,7 +107,7 @@ __global__ void __launch_bounds__(256) allreduce_p2p_kernel(const __grid_constan
             for (int q = 0; q < p.world; ++q) reinterpret_cast<float4*>(p.buf[q])[i] = a;
         }
     }
-    cross_rank_barrier(p, 2u * e + 2u);
+    cross_rank_barrier<true>(p, 2u * e + 2u);
     // the last CTA out bumps the epoch (every CTA read it before its first barrier; the next launch starts after this one ends)
     if (threadIdx.x == 0) {
         __threadfence();
