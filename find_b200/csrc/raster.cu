@@ -6,17 +6,23 @@
 // candidates of smallest depth.  The arithmetic is restated in oracle/raster_oracle.py (header there lists the rules).
 //
 // Design (no graphics API: plain CUDA):
-//   face_setup_kernel   one thread per (mesh, face): the 9 vertex floats and the blur-grown bounding box, as two float4-
-//                       aligned records; a degenerate or behind-the-camera face gets an empty box
-//   sil_tile_kernel     one CTA per 16 x 16 pixel tile of one mesh, one thread per pixel.  The CTA streams the mesh's boxes
-//                       (coalesced float4), compacts the faces that touch the tile IN FACE ORDER into shared memory and
-//                       evaluates them for all 256 pixels from shared memory.  No global binning pass, no per-pixel lists.
-//                       K truncation is exact and needs no per-pixel heap: a pixel with more than K candidates finds the
-//                       K-th smallest depth by bisection on the float bit pattern over the tile's face list (re-evaluation
-//                       instead of storage), then multiplies the candidates below it and the first ties in face order.
-//   backward            the same tile walk; d alpha / d signed_dist_k = prod * p_k / sigma needs only the saved product.
-//                       Per face the 256 pixels' contributions are reduced in the warp before 6 atomics per warp.
-// Bound: FP32 latency / FMA (about 70 flop per pixel-face evaluation); HBM traffic is 64 B per face per tile row.
+//   face_setup_kernel     one thread per (mesh x view, face): the 9 vertex floats + face id (48 B record) and the blur-grown
+//                         bounding box (float4); a degenerate or behind-the-camera face gets an empty box
+//   sil_tile_fwd_kernel   persistent CTAs (4 per SM) pull 16 x 16 pixel tiles from a device queue (boundary tiles cost ~10x a
+//                         background tile); one thread per pixel, a warp covers 8 x 4 pixels.  The CTA streams the mesh's boxes
+//                         (1024 per round, two barriers), compacts the faces that touch the tile IN FACE ORDER into shared memory
+//                         and evaluates them for its 256 pixels from shared memory.  No global binning pass.
+//                         K truncation is exact without a per-pixel heap: every candidate's depth bits and blend factor go to a
+//                         per-CTA store [cap][256]; a pixel with more than K candidates finds its K-th smallest depth by a 16-ary
+//                         search on the float bit pattern over its own list and multiplies the kept factors (earlier face on
+//                         ties).  A list longer than the capacity falls back to a block-wide search that re-evaluates the tile's
+//                         faces.  The same walk yields the nearest candidate (pix_to_face / zbuf) and, in the <kFragments = true>
+//                         instantiation used for hard rasterisation, its barycentrics and signed distance.
+//   sil_tile_bwd_kernel   the same tile walk; d alpha / d d2_k = +-prod p_k / sigma needs only the saved product and selection.
+//                         Per face the 256 pixels' contributions are reduced in the warp before 6 atomics per (warp, face).
+//   vert_normals / phong_shade   Phong image of the hard fragments, forward only (end of this file).
+// Bound: latency / issue (divergent point-triangle evaluations, ~18 of 32 lanes active; profiles/r1_silhouette.md); DRAM
+// traffic (the candidate store) is ~160 GB/s.
 #include "common.cuh"
 #include "../../include/find_b200.h"
 
