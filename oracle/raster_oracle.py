@@ -235,3 +235,16 @@ def phong_image(p2f, bary, zbuf, dists, verts_world, faces, colours, cam_centre,
     delta = torch.exp((eps - z_max) / gamma).clamp(min=eps)
     bg = torch.as_tensor(background, dtype=dt)
     return (wnum[..., None] * colour + delta[..., None] * bg) / (wnum + delta)[..., None]
+
+
+def render_image(verts_world: torch.Tensor, faces: torch.Tensor, colours: torch.Tensor, R: torch.Tensor, T: torch.Tensor, H: int, W: int,
+                 **shading) -> torch.Tensor:
+    """One view of FootRenderer.forward(return_images=True) end to end, differentiable by autograd w.r.t. the world vertices and
+    the vertex colours exactly where PyTorch3D is: through the barycentrics (position, normal, texel), the vertex normals and the
+    signed distance of the blend; pix_to_face and the depth ordering carry no gradient.  The reference for the image BACKWARD
+    that the CUDA path does not have yet."""
+    ndc = fov_project(verts_world, R, T)
+    _, aux = silhouette(ndc, faces, H, W, blur_radius=0.0, sigma=1.0, faces_per_pixel=1, return_aux=True, perspective_correct=True,
+                        clip_barycentric_coords=False)
+    cam = -(T.to(verts_world.dtype) @ R.to(verts_world.dtype).T)
+    return phong_image(aux["pix_to_face"], aux["bary"], aux["zbuf"], aux["dists"], verts_world, faces, colours, cam, **shading)

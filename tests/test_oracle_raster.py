@@ -146,3 +146,27 @@ def test_phong_known_answer_and_background():
     # a face turned away from the light gets ambient only
     img2 = ro.phong_image(p2f, bary, zbuf, dists, v, f[:, [0, 2, 1]], col, cam_centre=(1 / 3, 1 / 3, 5.0))
     assert torch.allclose(img2[0, 0], torch.full((3,), 0.25, dtype=torch.float64), atol=1e-9)
+
+
+def test_image_oracle_is_differentiable_end_to_end():
+    """render_image (projection -> hard fragments -> Phong -> blend) in fp64: autograd vs central differences for vertices and
+    colours; pixels that change face under the perturbation are avoided by a small step on a coarse image."""
+    torch.manual_seed(4)
+    v = torch.tensor([[-0.05, -0.04, 0.0], [0.06, -0.05, 0.01], [0.0, 0.06, -0.01], [0.07, 0.05, 0.02]], dtype=torch.float64)
+    f = torch.tensor([[0, 1, 2], [1, 3, 2]])
+    col = torch.rand(4, 3, dtype=torch.float64)
+    R, T = ro.look_at_view_transform(dist=0.3, elev=20.0, azim=10.0)
+    w = torch.rand(12, 12, 3, dtype=torch.float64)
+    fn = lambda vv, cc: (ro.render_image(vv, f, cc, R[0], T[0], 12, 12) * w).sum()      # noqa: E731
+    vg, cg = v.clone().requires_grad_(True), col.clone().requires_grad_(True)
+    fn(vg, cg).backward()
+    assert float(vg.grad.abs().max()) > 0 and float(cg.grad.abs().max()) > 0
+    h = 1e-7
+    for (i, d) in [(0, 0), (1, 1), (2, 2), (3, 0)]:
+        e = torch.zeros_like(v); e[i, d] = h
+        num = (fn(v + e, col) - fn(v - e, col)) / (2 * h)
+        assert abs(float(num) - float(vg.grad[i, d])) < 1e-4 * max(1.0, abs(float(num)))
+    for (i, d) in [(0, 1), (3, 2)]:
+        e = torch.zeros_like(col); e[i, d] = 1e-6
+        num = (fn(v, col + e) - fn(v, col - e)) / 2e-6
+        assert abs(float(num) - float(cg.grad[i, d])) < 1e-6 * max(1.0, abs(float(num)))
