@@ -124,7 +124,8 @@ def silhouette(verts: torch.Tensor, faces: torch.Tensor, H: int, W: int, blur_ra
         bary = torch.where(hit[:, None], bary, torch.full_like(bary, -1.0))
         dist = torch.where(hit, sd.gather(1, first)[:, 0], torch.full_like(sd[:, 0], -1.0))
         return alpha, dict(count=cand.sum(1).reshape(H, W), keep=keep, prod=prod.reshape(H, W), pix_to_face=nearest.reshape(H, W),
-                           zbuf=znear.reshape(H, W), bary=bary.reshape(H, W, 3), dists=dist.reshape(H, W))
+                           zbuf=znear.reshape(H, W), bary=bary.reshape(H, W, 3), dists=dist.reshape(H, W),
+                           pair=dict(prob=prob, pz=pz, u=(u0, u1, u2)))
     return alpha
 
 
@@ -248,3 +249,28 @@ def render_image(verts_world: torch.Tensor, faces: torch.Tensor, colours: torch.
                         clip_barycentric_coords=False)
     cam = -(T.to(verts_world.dtype) @ R.to(verts_world.dtype).T)
     return phong_image(aux["pix_to_face"], aux["bary"], aux["zbuf"], aux["dists"], verts_world, faces, colours, cam, **shading)
+
+
+def feature_blend(verts_ndc: torch.Tensor, faces: torch.Tensor, features: torch.Tensor, H: int, W: int, sigma: float = 1e-4,
+                  gamma: float = 1e-4, background=None, znear: float = 1.0, zfar: float = 100.0, faces_per_pixel: int = 100,
+                  blur_radius: float | None = None) -> torch.Tensor:
+    """FeatureShader (renderer.py:74-105) = the reference's own ``softmax_blend`` (renderer.py:23-72, called with its default
+    znear = 1, zfar = 100) over the silhouette Fragments: features [V,C] interpolated with the clipped barycentrics of each of the K
+    kept faces, weights prob_k * exp((z_inv_k - max z_inv) / gamma), background weight exp((eps - max z_inv) / gamma) clamped at
+    eps.  -> [H,W,C].  Dense: small cases only.  Reference for the feature rendering of the next round."""
+    _, aux = silhouette(verts_ndc, faces, H, W, blur_radius=blur_radius, sigma=sigma, faces_per_pixel=faces_per_pixel, return_aux=True)
+    dt = verts_ndc.dtype
+    keep = aux["keep"].to(dt)
+    prob, pz, (u0, u1, u2) = aux["pair"]["prob"], aux["pair"]["pz"], aux["pair"]["u"]
+    C = features.shape[1]
+    bg = torch.zeros(C, dtype=dt) if background is None else torch.as_tensor(background, dtype=dt)
+    eps = 1e-10
+    z_inv = (zfar - pz) / (zfar - znear) * keep
+    z_max = z_inv.max(dim=1, keepdim=True).values.clamp(min=eps)
+    wnum = prob * torch.exp((z_inv - z_max) / gamma)                       # prob already carries the keep mask
+    delta = torch.exp((eps - z_max) / gamma).clamp(min=eps)
+    denom = wnum.sum(1, keepdim=True) + delta
+    ff = features[faces]                                                    # [F,3,C]
+    texel = u0[..., None] * ff[None, :, 0] + u1[..., None] * ff[None, :, 1] + u2[..., None] * ff[None, :, 2]   # [P,F,C]
+    out = ((wnum[..., None] * texel).sum(1) + delta * bg) / denom
+    return out.reshape(H, W, C)

@@ -170,3 +170,22 @@ def test_image_oracle_is_differentiable_end_to_end():
         e = torch.zeros_like(col); e[i, d] = 1e-6
         num = (fn(v, col + e) - fn(v, col - e)) / 2e-6
         assert abs(float(num) - float(cg.grad[i, d])) < 1e-6 * max(1.0, abs(float(num)))
+
+
+def test_feature_blend_known_answers():
+    feats = torch.tensor([[1.0, 0.0], [0.0, 1.0], [0.0, 0.0]], dtype=torch.float64)
+    r, c = _pix(4, 4, -0.25, -0.25)                                       # inside TRI: barycentrics (0.5, 0.25, 0.25), depth 1
+    out = ro.feature_blend(TRI, FACE, feats, 4, 4, sigma=0.1, gamma=0.5, blur_radius=1.0)
+    prob = 1 / (1 + math.exp(-0.0625 / 0.1))
+    z_inv = (100.0 - 1.0) / 99.0                                          # = 1: the face sits on the near plane of the blend
+    delta = math.exp((1e-10 - z_inv) / 0.5)
+    want = prob * torch.tensor([0.5, 0.25], dtype=torch.float64) / (prob + delta)
+    assert torch.allclose(out[r, c], want, atol=1e-12)
+    rr, cc = _pix(4, 4, 0.75, 0.75)                                       # no candidate: background (zeros) over delta = 1
+    assert torch.equal(out[rr, cc], torch.zeros(2, dtype=torch.float64))
+    # the nearer of two stacked faces dominates as gamma -> 0
+    far = TRI.clone(); far[:, 2] = 3.0
+    v = torch.cat([far, TRI]); f = torch.tensor([[0, 1, 2], [3, 4, 5]])
+    fe = torch.cat([torch.zeros(3, 1, dtype=torch.float64), torch.ones(3, 1, dtype=torch.float64)])
+    sharp = ro.feature_blend(v, f, fe, 4, 4, sigma=0.1, gamma=1e-4, blur_radius=1.0)
+    assert abs(float(sharp[r, c, 0]) - 1.0) < 1e-6
