@@ -356,26 +356,39 @@ def run_ours(args, wl, rank, world, local_rank):
     math_k = [k for k in kernels if "tflops" in k]
     dom = max(math_k, key=lambda k: k["ms_per_step"]) if math_k else None
     roofline = None
-    traffic = None
+    traffic_all = {}
     try:       # dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed `ncu --set full` capture
         with open(os.path.join(ROOT, "profiles", "ncu_traffic.json")) as fh:
-            traffic = json.load(fh).get(args.workload, {}).get(dom["name"] if dom else "", None)
+            traffic_all = json.load(fh).get(args.workload, {})
     except (OSError, ValueError):
         pass
+    traffic = traffic_all.get(dom["name"] if dom else "", None)
+    # whole-step fractions: EXECUTED tensor-core FLOPs of all GEMM kernels / step time / tensor peak, and the DRAM traffic of
+    # all kernels (ncu capture, per launch) / step time / HBM peak.  Neither roof binds the step as a whole.
+    tensor_flops_step = sum(kernel_flops(k["name"], wl) * k["launches_per_step"] for k in kernels
+                            if k.get("bound") == "tensor")
+    step_tensor_frac = tensor_flops_step / (ms_per_step * 1e-3) / 1e12 / peaks["bf16_sustained"]
+    dram_step = sum(v for v in traffic_all.values() if isinstance(v, (int, float)))
+    step_hbm_frac = (dram_step / (ms_per_step * 1e-3) / 1e9 / peaks["hbm_gbs"]) if dram_step else None
     if dom is not None:
-        if dom.get("hbm_frac") is not None and dom["hbm_frac"] > (dom["frac"] or 0):
-            # the binding roof of this kernel is HBM (its tensor-pipe fraction is reported in `kernels`)
-            roofline = dict(kernel=dom["name"], bound="hbm", achieved=round(dom["hbm_gbs"], 1), peak=peaks["hbm_gbs"],
-                            unit="GB/s", frac=round(dom["hbm_frac"], 4), traffic=traffic,
-                            algorithmic_bytes=dom["hbm_bytes_algorithmic"], tensor_frac=round(dom["frac"], 4),
-                            kernel_ms=round(dom["ms_per_step"], 4), share_of_step=round(dom["share"], 3),
-                            peak_source=peaks["source"] + " hbm_gbs (burst copy bandwidth)")
-        else:
-            roofline = dict(kernel=dom["name"], bound=dom["bound"], achieved=round(dom["tflops"], 2), peak=dom["peak"],
-                            unit="TFLOP/s", frac=round(dom["frac"], 4) if dom["frac"] else None, traffic=traffic,
-                            kernel_ms=round(dom["ms_per_step"], 4), share_of_step=round(dom["share"], 3),
-                            peak_source=("findb200_fp32_peak FFMA2 probe, same run" if dom["bound"] == "fp32"
-                                         else peaks["source"] + " bf16_tflops_sustained (fp16 operands, same tensor rate)"))
+        # SURVEY.md §8(d) puts the MLP GEMMs on the TENSOR roof (1.7 MFLOP per 36 B of unavoidable I/O): that fraction is the
+        # primary `frac`.  The dW launch streams the saved fp16 tile images once (this design's traffic, not algorithmic I/O);
+        # its HBM rate is reported beside it as `design_traffic_*`.
+        roofline = dict(kernel=dom["name"], bound="tensor" if dom["bound"] == "tensor" else "hbm",
+                        achieved=round(dom["tflops"], 2), peak=dom["peak"], unit="TFLOP/s",
+                        frac=round(dom["frac"], 4) if dom["frac"] else None, traffic=traffic,
+                        kernel_ms=round(dom["ms_per_step"], 4), share_of_step=round(dom["share"], 3),
+                        step_tensor_frac=round(step_tensor_frac, 4),
+                        step_hbm_frac=round(step_hbm_frac, 4) if step_hbm_frac is not None else None,
+                        step_tensor_tflops=round(tensor_flops_step / (ms_per_step * 1e-3) / 1e12, 1),
+                        peak_source=("findb200_fp32_peak FFMA2 probe, same run (FP32 pipe; reported under 'hbm' only because the "
+                                     "contract has two labels)" if dom["bound"] == "fp32"
+                                     else peaks["source"] + " bf16_tflops_sustained (fp16 operands, same tensor rate)"))
+        if dom.get("hbm_frac") is not None:
+            roofline.update(design_traffic_bytes=dom["hbm_bytes_algorithmic"], design_traffic_gbs=round(dom["hbm_gbs"], 1),
+                            design_traffic_hbm_frac=round(dom["hbm_frac"], 4),
+                            design_traffic_note="bytes of the saved fp16 tile images this design streams through the dW launch "
+                                                "(not algorithmic I/O); HBM peak = " + str(peaks["hbm_gbs"]) + " GB/s measured")
 
     out = {
         "metric": METRIC, "value": fv_global / (ms_per_step * 1e-3), "unit": UNIT, "n_gpus": world,
@@ -401,9 +414,155 @@ def run_ours(args, wl, rank, world, local_rank):
     }
     if world == 1 and not wl["frozen"]:
         out["shipped_3d_step"] = measure_shipped_step(model, step, wl, host, device, flush, min(args.steps, 50))
+    if world == 1 and not args.skip_eager:
+        out["gpu_eager_baseline"] = gpu_eager_baseline(wl, device, flush)
+    # BASELINE.json's other configurations at this N (per-GPU shapes, weak scaling), a few steps each, so that the driver's
+    # BENCH / SCALE records carry a value for every config
+    if not args.skip_other_workloads and args.workload == "cfg2":
+        del sharded, step, model
+        torch.cuda.empty_cache()
+        out["other_workloads"] = {}
+        for name in ("cfg3", "cfg4", "cfg5"):
+            out["other_workloads"][name] = measure_workload_brief(name, rank, world, device, flush, barrier, max_over_ranks,
+                                                                  steps=min(args.steps, 10))
     if rank == 0 and world == 1 and not args.skip_cpu_baseline:
         out["cpu_baseline"] = cpu_baseline(wl, budget_s=args.cpu_budget)
     return out
+
+
+def measure_workload_brief(name, rank, world, device, flush, barrier, max_over_ranks, steps=10, warmup=3):
+    """Device-timed value of another BASELINE.json configuration at this N: same protocol as the headline (graph replay, CUDA
+    events per step, L2 flushed between steps, max over ranks), fewer steps."""
+    from find_b200.parallel import ShardedTrainStep
+    wl = WORKLOADS[name]
+    model, step, host = build_job(wl, rank, world, device)
+    sharded = ShardedTrainStep(step, wl["feet"] * world, collective=os.environ.get("FINDB200_COLLECTIVE", "auto"))
+    step.load_inputs(host["idx"], host["target"], host["col_target"])
+    for _ in range(warmup):
+        sharded.run()
+    barrier()
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
+    for a, b in ev:
+        flush.zero_()
+        a.record()
+        sharded.run()
+        b.record()
+    barrier()
+    ms = max_over_ranks(sum(a.elapsed_time(b) for a, b in ev)) / steps
+    loss3 = step.loss3.tolist()
+    res = {"workload": f"{name}: {wl['desc']}", "feet_per_gpu": wl["feet"], "global_feet": wl["feet"] * world, "verts": wl["V"],
+           "target_points": wl["P2"], "frozen_mlp": wl["frozen"], "ms_per_step": ms, "steps": steps, "warmup": warmup,
+           "value": wl["feet"] * world * wl["V"] / (ms * 1e-3), "unit": UNIT, "collective": sharded.collective,
+           "loss": {"total": loss3[0], "chamfer": loss3[1], "colour_mse": loss3[2]}}
+    del sharded, step, model
+    torch.cuda.empty_cache()
+    return res
+
+
+def gpu_eager_baseline(wl, device, flush, steps=5):
+    """The comparators BASELINE.md §4 promises ("the kernel to beat"): the reference's own module arithmetic
+    (model.py:393-453 + the registration transform 481-488) as torch-eager ops on THIS GPU — cuBLAS GEMMs + autograd — with
+    an eager chunked Chamfer (the brute-force distance matrix PyTorch3D's knn kernel walks, here through torch.cdist-free
+    broadcast + min), in fp32, with allow_tf32, and under bf16 autocast.  Library code end to end: none of this repo's
+    kernels.  Same batch, same loss, forward + backward, optimiser excluded; median of `steps` after 2 warm-ups."""
+    import torch.nn.functional as F
+    from find_b200 import synthetic as syn
+    from find_b200.field import NeuralDisplacementField
+    feet, V, P2 = wl["feet"], wl["V"], wl["P2"]
+    model = NeuralDisplacementField(use_shapevec=True, use_texvec=True, use_posevec=True, train_size=feet, val_size=1,
+                                    shapevec_size=100, texvec_size=100, posevec_size=100, device=device)
+    syn.randomise_last_disp_layer(model.mlp_disp[-1], seed=0)
+    tv, _ = syn.make_template(V)
+    tv = tv.to(device)
+    lat = {k: v.to(device).requires_grad_(True) for k, v in syn.make_latents(feet, 0).items()}
+    target = syn.make_targets(feet, P2, 0).to(device)
+    colt = syn.make_col_target(feet, V, 0).to(device)
+    Bm = model.encoder[0].B_on(device)
+    params = [p for p in model.mlp_parameters()]
+    for p in params:
+        p.requires_grad_(not wl["frozen"])
+
+    def mlp(seq, x):
+        for m in seq:
+            x = F.relu(x) if isinstance(m, torch.nn.ReLU) else F.linear(x, m.weight, m.bias)
+        return x
+
+    def euler(e):
+        a, b, c = e.unbind(-1)
+        one, zero = torch.ones_like(a), torch.zeros_like(a)
+        ca, sa, cb, sb, cc, sc = a.cos(), a.sin(), b.cos(), b.sin(), c.cos(), c.sin()
+        Rx = torch.stack([one, zero, zero, zero, ca, -sa, zero, sa, ca], -1).reshape(-1, 3, 3)
+        Ry = torch.stack([cb, zero, sb, zero, one, zero, -sb, zero, cb], -1).reshape(-1, 3, 3)
+        Rz = torch.stack([cc, -sc, zero, sc, cc, zero, zero, zero, one], -1).reshape(-1, 3, 3)
+        return Rx @ Ry @ Rz
+
+    def nn_sq(x, y, chunk=2048):
+        """min_j |x_i - y_j|^2: the argmin over chunks of the exact-difference distance matrix under no_grad (what knn_points
+        computes), then the differentiable distance to the gathered neighbours (what its autograd differentiates)."""
+        with torch.no_grad():
+            idx = []
+            for i in range(0, x.shape[1], chunk):
+                d = x[:, i:i + chunk, None, :] - y[:, None, :, :]
+                idx.append((d * d).sum(-1).argmin(-1))
+            idx = torch.cat(idx, 1)
+        nb = torch.gather(y, 1, idx[..., None].expand(-1, -1, 3))
+        return ((x - nb) ** 2).sum(-1)
+
+    def step_fn():
+        pos = tv[None].expand(feet, -1, -1)
+        proj = 2 * torch.pi * (pos @ Bm)                                    # fourier_feature_transform.py:41-52
+        x = torch.cat([pos, torch.sin(proj), torch.cos(proj)], -1)
+        x = mlp(model.base, x)
+        ex = lambda z: z[:, None, :].expand(-1, V, -1)
+        disp = 0.1 * torch.tanh(mlp(model.mlp_disp, torch.cat([x, ex(lat["shapevec"]), ex(lat["posevec"])], -1)))
+        col = 0.5 * (1 + torch.tanh(mlp(model.mlp_col, torch.cat([x, ex(lat["texvec"])], -1))))
+        reg = lat["reg"]
+        verts = ((pos + disp).float() * reg[:, None, 6:9]) @ euler(reg[:, 3:6]) + reg[:, None, 0:3]
+        verts = verts.float()
+        chamf = (nn_sq(verts, target).mean(1) + nn_sq(target, verts).mean(1)).mean()
+        loss = 1e4 * chamf + F.mse_loss(col.float(), colt)
+        for t in params + list(lat.values()):
+            t.grad = None
+        loss.backward()
+        return loss
+
+    res = {"what": "torch-eager (cuBLAS + autograd) field fwd+bwd + registration transform + chunked broadcast Chamfer on this GPU; "
+                   "same batch / loss as the headline, optimiser excluded, L2 flushed between steps, median of %d steps" % steps,
+           "feet": feet, "verts": V, "target_points": P2}
+    old_tf32 = (torch.backends.cuda.matmul.allow_tf32, torch.backends.cudnn.allow_tf32)
+    try:
+        for mode in ("fp32", "tf32", "bf16_autocast"):
+            torch.backends.cuda.matmul.allow_tf32 = mode == "tf32"
+            torch.backends.cudnn.allow_tf32 = mode == "tf32"
+            ctx = torch.autocast("cuda", dtype=torch.bfloat16) if mode == "bf16_autocast" else torch.autocast("cuda", enabled=False)
+
+            def run():
+                with ctx:
+                    return step_fn()
+            try:
+                for _ in range(2):
+                    run()
+                torch.cuda.synchronize(device)
+                times = []
+                for _ in range(steps):
+                    flush.zero_()
+                    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                    e0.record(); loss = run(); e1.record()
+                    torch.cuda.synchronize(device)
+                    times.append(e0.elapsed_time(e1))
+                ms = statistics.median(times)
+                res[mode] = {"ms_per_step": ms, "vertices_per_s": feet * V / (ms * 1e-3), "loss": float(loss)}
+            except Exception as e:                      # noqa: BLE001 — e.g. out of memory on the distance matrix chunks
+                res[mode] = {"error": str(e)[:200]}
+                torch.cuda.empty_cache()
+    finally:
+        torch.backends.cuda.matmul.allow_tf32, torch.backends.cudnn.allow_tf32 = old_tf32
+    for t in params:
+        t.grad = None
+        t.requires_grad_(True)
+    del model
+    torch.cuda.empty_cache()
+    return res
 
 
 def measure_shipped_step(model, base_step, wl, host, device, flush, steps):
@@ -422,11 +581,8 @@ def measure_shipped_step(model, base_step, wl, host, device, flush, steps):
     opt_reg = FusedSGD([model.reg.data], lr=0.0, momentum=0.9)
 
     def iteration():
-        step.run()
-        for t in tables:
-            if t.grad is not None:
-                t.grad.zero_()
-        step.populate_grads()
+        step.run()                      # incl. the dense latent-table gradient scatter (part of the enqueue)
+        step.populate_grads()           # attaches the gradient buffers, no launch
         opt_net.step(); opt_lat.step(); opt_reg.step()
 
     for _ in range(3):
@@ -476,8 +632,17 @@ def cpu_step_fn(wl, feet_sample):
     return run, threads
 
 
+def cpu_feet_sample(wl):
+    """Feet per CPU step: the WHOLE per-GPU batch when one step stays around a second (cfg2 / cfg3: 8 feet = 0.4 s on 16
+    cores), otherwise a bounded sample so that the arm ends within minutes (cfg4: 1 of 4 feet; cfg5: 8 of 32)."""
+    cost = wl["feet"] * (wl["V"] * 5.0e-6 + 2.0 * wl["V"] * wl["P2"] * 2.0e-11)      # rough seconds on ~16 cores
+    if cost <= 2.0:
+        return wl["feet"]
+    return max(1, min(wl["feet"], int(wl["feet"] * 2.0 / cost)))
+
+
 def cpu_baseline(wl, budget_s=20.0, steps=None, warmup=1):
-    feet_sample = 1 if wl["V"] <= 20000 else 1
+    feet_sample = cpu_feet_sample(wl)
     run, threads = cpu_step_fn(wl, feet_sample)
     for _ in range(warmup):
         run()
@@ -489,14 +654,18 @@ def cpu_baseline(wl, budget_s=20.0, steps=None, warmup=1):
         times.append(time.perf_counter() - t0)
         if steps is not None and len(times) >= steps:
             break
-        if steps is None and (time.perf_counter() - t_start > budget_s or len(times) >= 20):
+        if steps is None and (time.perf_counter() - t_start > budget_s or len(times) >= 30):
             break
     med = statistics.median(times)
+    whole = feet_sample == wl["feet"]
     return {"value": feet_sample * wl["V"] / med, "unit": UNIT, "cores": threads, "kind": "port",
-            "sample": f"{feet_sample} foot of the {wl['V']}-vertex / {wl['P2']}-target workload per step "
-                      f"(same per-foot work as the GPU arm), median of {len(times)} steps after {warmup} warm-up; "
-                      f"oracle/step_oracle.py: torch CPU autograd (field) + OpenMP C Chamfer",
-            "s_per_step": med}
+            "sample": (f"the whole batch of the GPU arm ({feet_sample} feet x {wl['V']} verts x {wl['P2']} targets) per step"
+                       if whole else
+                       f"{feet_sample} of the {wl['feet']} feet of the {wl['V']}-vertex / {wl['P2']}-target batch per step "
+                       f"(the step is linear in feet)")
+                      + f", median of {len(times)} steps after {warmup} warm-up; "
+                        f"oracle/step_oracle.py: torch CPU autograd (field) + OpenMP C Chamfer",
+            "feet_per_step": feet_sample, "s_per_step": med}
 
 
 def run_reference(args, wl, rank, world):
@@ -507,13 +676,13 @@ def run_reference(args, wl, rank, world):
     return {"metric": METRIC, "value": base["value"], "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": base["s_per_step"] * 1e3, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "fp32", "data": "synthetic", "impl": "reference",
-            "config": {"workload": f"{args.workload}: {wl['desc']}", "feet_per_step": 1, "verts": wl["V"],
-                       "target_points": wl["P2"], "frozen_mlp": wl["frozen"]},
+            "config": {"workload": f"{args.workload}: {wl['desc']}", "feet_per_gpu": wl["feet"], "feet_per_step": base["feet_per_step"],
+                       "verts": wl["V"], "target_points": wl["P2"], "frozen_mlp": wl["frozen"]},
             "cpu_baseline": base,
             "e2e": {"value": base["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0,
-            "note": "reference = pure Python on torch + PyTorch3D (absent, not installable offline): timed arm is the "
-                    "oracle port of its algorithm on the host cores"}
+            "note": "reference = pure Python on torch + PyTorch3D (absent, not installable offline): this arm times the "
+                    "oracle PORT of its algorithm (cpu_baseline.kind = 'port') on the host cores, same batch per step"}
 
 
 def main():
@@ -524,6 +693,8 @@ def main():
     ap.add_argument("--impl", default="find_b200", choices=["find_b200", "reference"])
     ap.add_argument("--workload", default=None, choices=sorted(WORKLOADS))
     ap.add_argument("--skip-cpu-baseline", action="store_true")
+    ap.add_argument("--skip-eager", action="store_true", help="skip the torch-eager GPU comparators (gpu_eager_baseline)")
+    ap.add_argument("--skip-other-workloads", action="store_true", help="skip the brief cfg3 / cfg4 / cfg5 lines")
     ap.add_argument("--cpu-budget", type=float, default=20.0)
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
@@ -534,9 +705,7 @@ def main():
     wl = WORKLOADS[args.workload]
 
     if args.impl == "reference":
-        if args.steps > 5:
-            args.steps = 5                      # each CPU step is seconds: keep the arm within minutes
-        out = run_reference(args, wl, rank, world)
+        out = run_reference(args, wl, rank, world)    # the same batch as the GPU arm per step (0.4 s for cfg2 on 16 cores)
         if out is not None:
             print(json.dumps(out), flush=True)
         return

@@ -40,6 +40,7 @@ SIGNATURES = {
     "findb200_gather_rows": (c_int, [c_void_p, c_int, c_int, c_void_p, c_int, c_void_p, c_void_p]),
     "findb200_gather_rows_multi": (c_int, [c_void_p, c_int, c_void_p, c_int, c_void_p]),
     "findb200_scatter_add_rows": (c_int, [c_void_p, c_int, c_int, c_void_p, c_int, c_void_p, c_void_p]),
+    "findb200_scatter_rows_multi": (c_int, [c_void_p, c_int, c_void_p, c_int, c_int, c_void_p]),
     "findb200_chain_trace": (c_int, [c_void_p]),
     "findb200_profile_enable": (c_int, [c_int]),
     "findb200_profile_read": (c_int, [c_char_p, c_size_t]),

@@ -15,6 +15,8 @@
 // per rank at NVLink speed and costs two flag round trips.
 #include "common.cuh"
 #include "../../include/find_b200.h"
+#include <cstdlib>
+#include <cstring>
 
 namespace fb {
 namespace comm {
@@ -28,7 +30,10 @@ struct P2PParams {
     int rank, world;
     long long n4;                   // bucket length in float4 units (padded by the host)
     float scale;
-    uint32_t* epoch;                // device: [0] number of completed calls, [1] CTAs of this launch that are done
+    uint32_t* epoch;                // device: [0] number of completed calls, [1] CTAs of this launch that are done,
+                                    //         [2] error code (0 ok, 1 a rank never arrived, 2 ranks out of lock-step), [3] culprit rank
+    long long timeout_cycles;       // bound of one flag wait (FINDB200_P2P_TIMEOUT_S, default 600 s: rank skew of a checkpoint
+                                    // save or a validation pass is ordinary; NCCL would simply wait)
 };
 
 FB_DEVINL void st_release_sys(uint32_t* p, uint32_t v) { asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory"); }
@@ -43,7 +48,11 @@ FB_DEVINL float4 ld_peer(const float4* p) {       // peer data: never serve it f
     return v;
 }
 
-// CTA b of this rank <-> CTA b of every rank.  Bounded: a rank that never arrives traps the launch instead of hanging the GPU.
+// CTA b of this rank <-> CTA b of every rank.  Bounded: a rank that never arrives within `timeout_cycles` makes the kernel give
+// up WITHOUT trapping — it records an error code in epoch[2] (host-visible through P2PAllReduce.check()) and every later wait of
+// this and of following launches returns at once, so the CUDA context survives and the job can fall back to NCCL or stop cleanly.
+// Ranks must enqueue the call in lock-step: barrier A also verifies that no peer is a whole call ahead (flag > epoch + 1 means
+// that rank enqueued one call more than this one) and reports it as error 2 instead of silently pairing different steps.
 // kPublish: this CTA's threads have written peer memory in this kernel and those writes must be visible system-wide before the
 // flag (barrier B).  Barrier A publishes nothing of this kernel: the bucket was written by EARLIER kernels into local memory,
 // which a peer reads through this GPU's L2 — the kernel boundary already ordered those writes — so it skips the system fences
@@ -58,11 +67,22 @@ FB_DEVINL void cross_rank_barrier(const P2PParams& p, uint32_t epoch) {
         st_release_sys(p.flags[t] + blockIdx.x * kMaxRanks + p.rank, epoch);
         const uint32_t* mine = p.flags[p.rank] + blockIdx.x * kMaxRanks + t;
         const long long t0 = clock64();
-        while ((int32_t)(ld_acquire_sys(mine) - epoch) < 0) {
-            if (clock64() - t0 > FB_WAIT_TIMEOUT_CYCLES) {
-                printf("find_b200: allreduce_p2p rank %d cta %d: rank %d never reached epoch %u\n", p.rank, (int)blockIdx.x, t, epoch);
-                __trap();
+        uint32_t seen;
+        while ((int32_t)((seen = ld_acquire_sys(mine)) - epoch) < 0) {
+            if (*(volatile uint32_t*)(p.epoch + 2) != 0u) break;                  // an earlier wait already failed
+            if (clock64() - t0 > p.timeout_cycles) {
+                if (atomicCAS(p.epoch + 2, 0u, 1u) == 0u) {
+                    p.epoch[3] = (uint32_t)t;
+                    printf("find_b200: allreduce_p2p rank %d cta %d: rank %d never reached epoch %u (gave up, error flag set)\n", p.rank,
+                           (int)blockIdx.x, t, epoch);
+                }
+                break;
             }
+        }
+        if (!kPublish && (int32_t)(seen - epoch) >= 2 && atomicCAS(p.epoch + 2, 0u, 2u) == 0u) {
+            p.epoch[3] = (uint32_t)t;
+            printf("find_b200: allreduce_p2p rank %d: rank %d is a call ahead (flag %u, expected %u): ranks must enqueue in lock-step\n",
+                   p.rank, t, seen, epoch);
         }
     }
     __syncthreads();
@@ -121,6 +141,17 @@ __global__ void __launch_bounds__(256) allreduce_p2p_kernel(const __grid_constan
 using namespace fb;
 using namespace fb::comm;
 
+static long long p2p_timeout_cycles() {
+    static long long cyc = 0;
+    if (!cyc) {
+        const char* e = getenv("FINDB200_P2P_TIMEOUT_S");
+        double s = e ? atof(e) : 600.0;
+        if (!(s > 0.0)) s = 600.0;
+        cyc = (long long)(s * 2.0e9);           // clock64 ticks at <= ~2 GHz: the bound is generous, not exact
+    }
+    return cyc;
+}
+
 extern "C" int findb200_allreduce_p2p(void* const* peer_bufs, void* const* peer_flags, int rank, int world, long long n_floats,
                                       float scale, unsigned int* epoch_dev, int n_ctas, void* stream) {
     cudaStream_t st = (cudaStream_t)stream;
@@ -138,6 +169,7 @@ extern "C" int findb200_allreduce_p2p(void* const* peer_bufs, void* const* peer_
         p.flags[q] = (uint32_t*)peer_flags[q];
     }
     p.rank = rank; p.world = world; p.n4 = n_floats / 4; p.scale = scale; p.epoch = epoch_dev;
+    p.timeout_cycles = p2p_timeout_cycles();
     FB_MARK("allreduce_p2p", st);
     allreduce_p2p_kernel<<<n_ctas, 256, 0, st>>>(p);
     FB_CUDA(cudaGetLastError());

@@ -33,6 +33,7 @@ constexpr int kTile = 16;
 constexpr int kThreads = kTile * kTile;
 constexpr int kListCap = 4096;           // faces touching one tile that the CTA keeps for the K-truncation passes
 constexpr float kEps = 1e-8f;
+constexpr float kZClip = 0.01f;          // znear / 2 of the reference's cameras (renderer.py:258, 228-236)
 
 struct FaceRec {                          // 48 B, three float4 loads
     float x0, y0, z0, x1;
@@ -80,8 +81,11 @@ __global__ void face_setup_kernel(const float* __restrict__ verts, const int* __
     r.pad0 = __int_as_float(f);              // face id travels with the record (pix_to_face output)
     r.pad1 = r.pad2 = 0.f;
     const float area = __fsub_rn(__fmul_rn(r.x2 - r.x0, r.y1 - r.y0), __fmul_rn(r.y2 - r.y0, r.x1 - r.x0));
-    const float zmax = fmaxf(fmaxf(r.z0, r.z1), r.z2);
-    const bool ok = (fabsf(area) > kEps) && (zmax >= 0.f);     // NaN coordinates fail both tests
+    // PyTorch3D clips faces against z_clip = znear / 2 = 0.01 (renderer.py:228-236, znear = 0.02 renderer.py:258); here a face with
+    // ANY vertex nearer than that is culled whole (conservative, no new vertices): a face that straddles the camera plane would
+    // otherwise keep wrapped x/z, y/z coordinates and rasterise as garbage.  Feet seen from 0.1-0.35 m never come that close.
+    const float zmin = fminf(fminf(r.z0, r.z1), r.z2);
+    const bool ok = (fabsf(area) > kEps) && (zmin >= kZClip);  // NaN coordinates fail both tests
     float4 b;
     if (ok) {
         b.x = fminf(fminf(r.x0, r.x1), r.x2) - blur; b.y = fmaxf(fmaxf(r.x0, r.x1), r.x2) + blur;

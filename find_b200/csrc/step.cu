@@ -231,48 +231,89 @@ int findb200_train_step_knn_stats(const void* workspace, int nfeet, int V, int P
 // ---- latent-table row gather / gradient scatter (LatentVector.__getitem__, model.py:130-152, and its autograd) ----
 namespace fb {
 namespace step {
-__global__ void gather_rows_kernel(const float* __restrict__ table, int width, const int64_t* __restrict__ idx, int B,
+// torch's `self.data[idx]` raises a device-side assert for an index outside the table; so do these kernels
+__device__ __forceinline__ long long checked_row(const int64_t* idx, int b, int n_rows, const char* what) {
+    const long long r = idx[b];
+    if (r < 0 || r >= (long long)n_rows) {
+        if (threadIdx.x == 0) printf("find_b200: %s: index %lld of batch entry %d is outside the table [0, %d)\n", what, r, b, n_rows);
+        __trap();
+    }
+    return r;
+}
+__global__ void gather_rows_kernel(const float* __restrict__ table, int n_rows, int width, const int64_t* __restrict__ idx, int B,
                                    float* __restrict__ out) {
     fb::pdl_wait_trigger();
     const int b = blockIdx.x;
-    const float* src = table + (size_t)idx[b] * width;
+    const float* src = table + (size_t)checked_row(idx, b, n_rows, "gather_rows") * width;
     for (int j = threadIdx.x; j < width; j += blockDim.x) out[(size_t)b * width + j] = src[j];
 }
-__global__ void scatter_add_rows_kernel(float* __restrict__ grad_table, int width, const int64_t* __restrict__ idx, int B,
+__global__ void scatter_add_rows_kernel(float* __restrict__ grad_table, int n_rows, int width, const int64_t* __restrict__ idx, int B,
                                         const float* __restrict__ g) {
     fb::pdl_wait_trigger();
     const int b = blockIdx.x;
-    float* dst = grad_table + (size_t)idx[b] * width;
+    float* dst = grad_table + (size_t)checked_row(idx, b, n_rows, "scatter_add_rows") * width;
     for (int j = threadIdx.x; j < width; j += blockDim.x) atomicAdd(dst + j, g[(size_t)b * width + j]);   // duplicates accumulate
 }
-}  // namespace step
-}  // namespace fb
-
-namespace fb {
-namespace step {
-struct GatherJobs { const float* table[8]; float* out[8]; int width[8]; };
-__global__ void gather_rows_multi_kernel(const GatherJobs J, const int64_t* __restrict__ idx) {
+struct GatherJobs { const float* table[8]; float* out[8]; int width[8]; int n_rows[8]; const int64_t* idx[8]; };
+__global__ void gather_rows_multi_kernel(const GatherJobs J) {
     fb::pdl_wait_trigger();
     const int b = blockIdx.x, k = blockIdx.y;
     const int width = J.width[k];
-    const float* src = J.table[k] + (size_t)idx[b] * width;
+    const float* src = J.table[k] + (size_t)checked_row(J.idx[k], b, J.n_rows[k], "gather_rows_multi") * width;
     float* dst = J.out[k] + (size_t)b * width;
     for (int j = threadIdx.x; j < width; j += blockDim.x) dst[j] = src[j];
+}
+// Dense table gradient of one step, WITHOUT atomics: block (r, k) owns row r of table k and adds, in batch order, the
+// gradient rows of every batch entry that indexed it (feet sharing a label, dataset.py:191-201) — what autograd's
+// index_put_(accumulate=True) gives after zero_grad, but bit-reproducible.  accumulate != 0 adds to what is there.
+struct ScatterJobs { const float* g[8]; float* grad_table[8]; int width[8]; int n_rows[8]; const int64_t* idx[8]; };
+__global__ void scatter_rows_multi_kernel(const ScatterJobs J, int B, int accumulate) {
+    fb::pdl_wait_trigger();
+    const int r = blockIdx.x, k = blockIdx.y;
+    if (r >= J.n_rows[k]) return;
+    const int width = J.width[k];
+    const int64_t* idx = J.idx[k];
+    float* dst = J.grad_table[k] + (size_t)r * width;
+    for (int j = threadIdx.x; j < width; j += blockDim.x) {
+        float acc = accumulate ? dst[j] : 0.f;
+        for (int b = 0; b < B; ++b)
+            if (idx[b] == (int64_t)r) acc += J.g[k][(size_t)b * width + j];
+        dst[j] = acc;
+    }
 }
 }  // namespace step
 }  // namespace fb
 
 extern "C" {
 int findb200_gather_rows_multi(const findb200_gather_job* jobs, int n_jobs, const int64_t* idx, int B, void* stream) {
-    FB_REQUIRE(jobs && idx && n_jobs >= 1 && n_jobs <= 8 && B >= 1, FINDB200_ERR_ARG, "gather_rows_multi: bad argument (1..8 jobs)");
+    FB_REQUIRE(jobs && n_jobs >= 1 && n_jobs <= 8 && B >= 1, FINDB200_ERR_ARG, "gather_rows_multi: bad argument (1..8 jobs)");
     fb::step::GatherJobs J{};
     for (int k = 0; k < n_jobs; ++k) {
-        FB_REQUIRE(jobs[k].table && jobs[k].out && jobs[k].width >= 1 && jobs[k].n_rows >= 1, FINDB200_ERR_ARG,
+        FB_REQUIRE(jobs[k].table && jobs[k].out && jobs[k].width >= 1 && jobs[k].n_rows >= 1 && (jobs[k].idx || idx), FINDB200_ERR_ARG,
                    "gather_rows_multi: job %d is incomplete", k);
-        J.table[k] = jobs[k].table; J.out[k] = jobs[k].out; J.width[k] = jobs[k].width;
+        J.table[k] = jobs[k].table; J.out[k] = jobs[k].out; J.width[k] = jobs[k].width; J.n_rows[k] = jobs[k].n_rows;
+        J.idx[k] = jobs[k].idx ? jobs[k].idx : idx;
     }
     FB_MARK("gather_rows", (cudaStream_t)stream);
-    FB_CUDA(fb::launch_pdl(fb::step::gather_rows_multi_kernel, dim3(B, n_jobs), 128, 0, (cudaStream_t)stream, J, idx));
+    FB_CUDA(fb::launch_pdl(fb::step::gather_rows_multi_kernel, dim3(B, n_jobs), 128, 0, (cudaStream_t)stream, J));
+    FB_CUDA(cudaGetLastError());
+    FB_MARK_END((cudaStream_t)stream);
+    return 0;
+}
+int findb200_scatter_rows_multi(const findb200_scatter_job* jobs, int n_jobs, const int64_t* idx, int B, int accumulate,
+                                void* stream) {
+    FB_REQUIRE(jobs && n_jobs >= 1 && n_jobs <= 8 && B >= 1, FINDB200_ERR_ARG, "scatter_rows_multi: bad argument (1..8 jobs)");
+    fb::step::ScatterJobs J{};
+    int max_rows = 1;
+    for (int k = 0; k < n_jobs; ++k) {
+        FB_REQUIRE(jobs[k].g && jobs[k].grad_table && jobs[k].width >= 1 && jobs[k].n_rows >= 1 && (jobs[k].idx || idx), FINDB200_ERR_ARG,
+                   "scatter_rows_multi: job %d is incomplete", k);
+        J.g[k] = jobs[k].g; J.grad_table[k] = jobs[k].grad_table; J.width[k] = jobs[k].width; J.n_rows[k] = jobs[k].n_rows;
+        J.idx[k] = jobs[k].idx ? jobs[k].idx : idx;
+        if (jobs[k].n_rows > max_rows) max_rows = jobs[k].n_rows;
+    }
+    FB_MARK("scatter_rows", (cudaStream_t)stream);
+    FB_CUDA(fb::launch_pdl(fb::step::scatter_rows_multi_kernel, dim3(max_rows, n_jobs), 128, 0, (cudaStream_t)stream, J, B, accumulate));
     FB_CUDA(cudaGetLastError());
     FB_MARK_END((cudaStream_t)stream);
     return 0;
@@ -280,7 +321,7 @@ int findb200_gather_rows_multi(const findb200_gather_job* jobs, int n_jobs, cons
 int findb200_gather_rows(const float* table, int n_rows, int width, const int64_t* idx, int B, float* out, void* stream) {
     FB_REQUIRE(table && idx && out && n_rows >= 1 && width >= 1 && B >= 1, FINDB200_ERR_ARG, "gather_rows: bad argument");
     FB_MARK("gather_rows", (cudaStream_t)stream);
-    FB_CUDA(fb::launch_pdl(fb::step::gather_rows_kernel, B, 128, 0, (cudaStream_t)stream, table, width, idx, B, out));
+    FB_CUDA(fb::launch_pdl(fb::step::gather_rows_kernel, B, 128, 0, (cudaStream_t)stream, table, n_rows, width, idx, B, out));
     FB_CUDA(cudaGetLastError());
     FB_MARK_END((cudaStream_t)stream);
     return 0;
@@ -289,7 +330,7 @@ int findb200_scatter_add_rows(float* grad_table, int n_rows, int width, const in
                               void* stream) {
     FB_REQUIRE(grad_table && idx && g && n_rows >= 1 && width >= 1 && B >= 1, FINDB200_ERR_ARG, "scatter_add_rows: bad argument");
     FB_MARK("scatter_add_rows", (cudaStream_t)stream);
-    FB_CUDA(fb::launch_pdl(fb::step::scatter_add_rows_kernel, B, 128, 0, (cudaStream_t)stream, grad_table, width, idx, B, g));
+    FB_CUDA(fb::launch_pdl(fb::step::scatter_add_rows_kernel, B, 128, 0, (cudaStream_t)stream, grad_table, n_rows, width, idx, B, g));
     FB_CUDA(cudaGetLastError());
     FB_MARK_END((cudaStream_t)stream);
     return 0;

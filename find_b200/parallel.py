@@ -91,7 +91,7 @@ class P2PAllReduce:
             raise RuntimeError("symmetric-memory rendezvous did not map every peer")
         self._bufs = (ctypes.c_void_p * self.world)(*bp)
         self._flags = (ctypes.c_void_p * self.world)(*fp)
-        self.epoch = torch.zeros(2, dtype=torch.int32, device=device)
+        self.epoch = torch.zeros(4, dtype=torch.int32, device=device)   # [calls done, CTAs done, error code, culprit rank]
         self.bucket = self.buf[: self.n]
         dist.barrier(group)                       # every rank's flag page is zero before anyone signals
         torch.cuda.synchronize(device)
@@ -102,6 +102,15 @@ class P2PAllReduce:
         rc = self.lib.findb200_allreduce_p2p(self._bufs, self._flags, self.rank, self.world, self.n_pad, float(scale),
                                              _lib.ptr(self.epoch), self.n_ctas, _lib.stream_ptr(self.dev))
         _lib.check(rc, "findb200_allreduce_p2p")
+
+    def check(self):
+        """Synchronising health check: raises if a wait of the kernel gave up (a rank missing for FINDB200_P2P_TIMEOUT_S seconds,
+        default 600) or if the ranks were found out of lock-step.  The context stays usable, so a caller may switch the
+        ShardedTrainStep to NCCL (``collective="nccl"``) for skew-prone loops."""
+        code, who = (int(x) for x in self.epoch[2:4].tolist())
+        if code:
+            what = {1: f"rank {who} never arrived", 2: f"rank {who} enqueued one call more than rank {self.rank}"}.get(code, "unknown")
+            raise RuntimeError(f"findb200_allreduce_p2p failed on rank {self.rank}: {what}")
 
 
 class ShardedTrainStep:
@@ -122,6 +131,10 @@ class ShardedTrainStep:
         self.graph: Optional[torch.cuda.CUDAGraph] = None
         self.p2p: Optional[P2PAllReduce] = None
         self.collective = "none"
+        if self.world > 1 and getattr(step, "mesh_terms", None) is not None:
+            # every rank must draw its OWN surface samples: fold the rank into the key of the Philox stream
+            rank = dist.get_rank(group)
+            step.mesh_terms.seed = (int(step.mesh_terms.seed) + 0x9E3779B97F4A7C15 * (rank + 1)) & (2 ** 64 - 1)
         if self.world > 1 and not step.frozen:
             self.collective = "nccl"
             if collective in ("auto", "p2p") and step.flat_grad.is_cuda:
@@ -193,6 +206,8 @@ class ShardedTrainStep:
         """Latent / reg row gradients are rank-local; scale them to the global mean as well."""
         if self.weight != 1.0:
             for g in self.step.grows.values():
+                g.mul_(self.weight)
+            for g in self.step.table_grads.values():
                 g.mul_(self.weight)
 
 

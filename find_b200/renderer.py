@@ -18,6 +18,7 @@ from __future__ import annotations
 
 import ctypes
 import math
+import os
 
 import numpy as np
 import torch
@@ -73,6 +74,13 @@ class _Silhouette(torch.autograd.Function):
                                                  int(K), int(bool(perspective)), _lib.ptr(alpha), _lib.ptr(prod), _lib.ptr(sel),
                                                  _lib.ptr(p2f), _lib.ptr(zbuf), _lib.ptr(ws), ws.numel(), _lib.stream_ptr(dev))
         _lib.check(rc, "findb200_silhouette_forward")
+        # K truncation could not be applied exactly on some tile (> 4096 faces on a 16 x 16 tile AND a pixel with more than K
+        # candidates): never accept that silently where a sync is affordable — evaluation / no-grad renders, or when asked to
+        if not torch.is_grad_enabled() or os.environ.get("FINDB200_RASTER_CHECK", "0") == "1":
+            with torch.cuda.device(dev):
+                if lib.findb200_silhouette_status(_lib.ptr(ws), N, F, _lib.stream_ptr(dev)) == 1:
+                    raise RuntimeError("rasterize_silhouette: faces_per_pixel truncation was inexact on at least one tile "
+                                       "(more than 4096 faces on a 16 x 16 pixel tile); lower the mesh density per tile or raise kListCap")
         if ctx.needs_input_grad[0]:                        # the backward reads the face records only: drop the scratch part
             ws = ws[: int(lib.findb200_silhouette_saved_bytes(N, F))].clone()
         ctx.save_for_backward(faces_i32, prod, sel, ws)
@@ -213,7 +221,7 @@ class FootRenderer(nn.Module):
         ndc = torch.stack([s * view[..., 0] / z, s * view[..., 1] / z, z], dim=-1)
         return ndc.reshape(M * nv, V, 3)
 
-    def forward(self, input_meshes: Meshes, R, T, return_images=False, return_depth=False, return_mask=True, mask_with_grad=True,
+    def forward(self, input_meshes: Meshes, R, T, return_images=True, return_depth=False, return_mask=False, mask_with_grad=True,
                 mask_out_faces=False, masked_faces=None, keypoints=None, keypoints_blend=False, lights=None,
                 return_mask_out_masks=False, return_features=False, features=None) -> dict:
         if return_features or return_depth or keypoints is not None:
@@ -225,14 +233,28 @@ class FootRenderer(nn.Module):
         if mask_out_faces and masked_faces is None:
             raise NotImplementedError("find_b200.renderer: mask_out_faces needs masked_faces (the TexturesUV u = v = 0 convention of "
                                       "renderer.py:337-345 is not built)")
+        """Same defaults as the reference (renderer.py:247-253: ``return_images=True, return_mask=False``), so the call sites that
+        rely on them keep their meaning: ``renderer(mesh, R, T)['image']`` (mesh_turntable.py:57, model.py:1074,1089),
+        ``return_mask=False`` (eval_2d.py:89-90)."""
         if not return_mask and not return_images:
             return {}
         if return_images:
             images, img_p2f = self._render_images(input_meshes, R, T)
-            if not return_mask:
+            if not return_mask or not mask_with_grad:
+                out = {}
+                if return_mask:
+                    # renderer.py:311-312: hard mask from the image render — any channel below the white background
+                    M_, nv_, S_ = images.shape[0], images.shape[1], images.shape[2]
+                    out["mask"] = torch.any(images < 1, dim=-1).reshape(M_, nv_, S_, S_).float()
                 if mask_out_faces:
-                    images = self._mask_images(images, img_p2f, masked_faces)[0]
-                return {"image": images}
+                    images, mpix = self._mask_images(images, img_p2f, masked_faces)
+                    if return_mask:
+                        for n, m in enumerate(mpix):
+                            out["mask"][n, m] = 0.0
+                    if return_mask_out_masks:
+                        out["mask_out_masks"] = torch.stack(mpix).reshape(images.shape[:4])
+                out["image"] = images
+                return out
         verts = input_meshes.verts_padded()
         faces, shared = _as_i32_faces(input_meshes)
         if not shared:

@@ -26,7 +26,16 @@ SMOOTH_WEIGHT = 1000.0   # opts.py:97 (--weight_smooth default)
 
 
 class GatherJobC(ctypes.Structure):             # findb200_gather_job (include/find_b200.h)
-    _fields_ = [("table", ctypes.c_void_p), ("n_rows", ctypes.c_int), ("width", ctypes.c_int), ("out", ctypes.c_void_p)]
+    _fields_ = [("table", ctypes.c_void_p), ("n_rows", ctypes.c_int), ("width", ctypes.c_int), ("out", ctypes.c_void_p),
+                ("idx", ctypes.c_void_p)]
+
+
+class ScatterJobC(ctypes.Structure):            # findb200_scatter_job (include/find_b200.h)
+    _fields_ = [("g", ctypes.c_void_p), ("n_rows", ctypes.c_int), ("width", ctypes.c_int), ("grad_table", ctypes.c_void_p),
+                ("idx", ctypes.c_void_p)]
+
+
+TABLE_KEYS = ("shapevec", "posevec", "texvec", "reg")
 
 
 class MeshTermsC(ctypes.Structure):             # findb200_mesh_terms (include/find_b200.h)
@@ -55,16 +64,22 @@ class TrainStep:
         self.with_colour, self.frozen = bool(with_colour), bool(frozen_mlp)
         self.w_chamf, self.w_tex = float(weight_chamf), float(weight_tex)
         sfx = "" if is_train else "_val"
-        self.tables = {k: getattr(model, k + sfx) for k in ("shapevec", "posevec", "texvec", "reg")}
+        self.tables = {k: getattr(model, k + sfx) for k in TABLE_KEYS}
         f32 = dict(dtype=torch.float32, device=dev)
         B, V = self.B, self.V
-        # per-step inputs (static addresses)
-        self.idx = torch.zeros(B, dtype=torch.int64, device=dev)
+        # per-step inputs (static addresses).  One index row per table: tables with labels are indexed by batch[vec.key],
+        # the others by batch['idx'] (sample_latent_vectors, trainer.py:29-46); load_inputs() fills all four from `idx`
+        # unless told otherwise.
+        self.idx4 = torch.zeros(len(TABLE_KEYS), B, dtype=torch.int64, device=dev)
+        self.idx = self.idx4[0]                    # the batch['idx'] row (kept under its old name)
         self.target = torch.zeros(B, self.P2, 3, **f32)
         self.col_target = torch.zeros(B, V, 3, **f32) if with_colour else None
         # gathered rows, outputs, gradients
         self.rows = {k: torch.zeros(B, t.data.shape[1], **f32) for k, t in self.tables.items() if t is not None}
         self.grows = {k: torch.zeros_like(v) for k, v in self.rows.items()}
+        # dense table gradients, written (not accumulated) by the scatter at the end of every enqueue: what
+        # loss.backward() leaves in LatentVector.data.grad after zero_grad() (trainer.py:99-100,121)
+        self.table_grads = {k: torch.zeros_like(t.data) for k, t in self.tables.items() if t is not None}
         self.loss3 = torch.zeros(3, **f32)
         self.disp, self.col, self.verts = (torch.empty(B, V, 3, **f32) for _ in range(3))
         self.mlp_params = model.mlp_parameters()
@@ -102,6 +117,7 @@ class TrainStep:
         self._cparams = None
         self._cgrads = None
         self._gather = None
+        self._scatter = None
         self._cache_key = None           # what the cached tiles in the workspace were computed from
 
     # ---- the enqueue ---------------------------------------------------------------------------------------
@@ -132,10 +148,15 @@ class TrainStep:
         if self._gather is None:
             live = [(k, t) for k, t in self.tables.items() if t is not None]
             jobs = (GatherJobC * len(live))()
+            sjobs = (ScatterJobC * len(live))()
             for j, (k, t) in enumerate(live):
+                irow = self.idx4[TABLE_KEYS.index(k)].data_ptr()
                 jobs[j].table, jobs[j].n_rows, jobs[j].width = t.data.data_ptr(), t.data.shape[0], t.data.shape[1]
-                jobs[j].out = self.rows[k].data_ptr()
+                jobs[j].out, jobs[j].idx = self.rows[k].data_ptr(), irow
+                sjobs[j].g, sjobs[j].n_rows, sjobs[j].width = self.grows[k].data_ptr(), t.data.shape[0], t.data.shape[1]
+                sjobs[j].grad_table, sjobs[j].idx = self.table_grads[k].data_ptr(), irow
             self._gather = (jobs, len(live))
+            self._scatter = (sjobs, len(live))
         if self._gather[1]:
             rc = lib.findb200_gather_rows_multi(self._gather[0], self._gather[1], _lib.ptr(self.idx), self.B, st)
             _lib.check(rc, "findb200_gather_rows_multi")
@@ -161,6 +182,10 @@ class TrainStep:
         else:
             rc = lib.findb200_train_step_mesh(*args, ctypes.byref(self.mesh_terms), _lib.ptr(self.ws), self.ws.numel(), st)
             _lib.check(rc, "findb200_train_step_mesh")
+        if self._scatter[1]:
+            # autograd of the gather (trainer.py:121): dense table gradients, part of the step (and of its CUDA graph)
+            rc = lib.findb200_scatter_rows_multi(self._scatter[0], self._scatter[1], _lib.ptr(self.idx), self.B, 0, st)
+            _lib.check(rc, "findb200_scatter_rows_multi")
         self._cache_key = key
 
     def _current_cache_key(self):
@@ -189,27 +214,52 @@ class TrainStep:
         return self.loss3
 
     # ---- host-facing conveniences --------------------------------------------------------------------------
-    def load_inputs(self, idx: torch.Tensor, target: torch.Tensor, col_target: Optional[torch.Tensor] = None):
-        """Copy one batch (host pinned or device tensors) into the static input buffers, asynchronously."""
-        self.idx.copy_(idx, non_blocking=True)
+    def _check_rows(self, idx: torch.Tensor, key: str = "idx"):
+        """Host-resident indices are validated here (torch's `self.data[idx]` would raise); device-resident ones by the kernels."""
+        if idx.is_cuda:
+            return
+        if idx.numel() != self.B:
+            raise RuntimeError(f"TrainStep: {key} has {idx.numel()} entries, the step was built for {self.B} feet")
+        lo, hi = int(idx.min()), int(idx.max())
+        tabs = [(k, t) for k, t in self.tables.items() if t is not None and (key == "idx" or k == key)]
+        for k, t in tabs:
+            if lo < 0 or hi >= t.data.shape[0]:
+                raise IndexError(f"TrainStep: {key} range [{lo}, {hi}] is outside table '{k}' with {t.data.shape[0]} rows")
+
+    def load_inputs(self, idx: torch.Tensor, target: torch.Tensor, col_target: Optional[torch.Tensor] = None,
+                    table_idx: Optional[Dict[str, torch.Tensor]] = None):
+        """Copy one batch (host pinned or device tensors) into the static input buffers, asynchronously.  ``table_idx``:
+        per-table row indices for tables that are indexed by label rather than by batch['idx'] (see ``rows_of_batch``)."""
+        self._check_rows(idx)
+        for r in range(len(TABLE_KEYS)):
+            self.idx4[r].copy_(idx, non_blocking=True)
+        for k, v in (table_idx or {}).items():
+            self._check_rows(v, k)
+            self.idx4[TABLE_KEYS.index(k)].copy_(v, non_blocking=True)
         self.target.copy_(target, non_blocking=True)
         if self.with_colour and col_target is not None:
             self.col_target.copy_(col_target, non_blocking=True)
 
+    def rows_of_batch(self, batch) -> Dict[str, torch.Tensor]:
+        """sample_latent_vectors (trainer.py:29-46) as row indices: a labelled table is indexed by batch[vec.key] through
+        its label list, every other table by batch['idx'].  -> {table: int64 [B]} for ``load_inputs(table_idx=...)``."""
+        out = {}
+        for k, t in self.tables.items():
+            if t is not None and t.labels is not None:
+                assert t.key in batch, f"Trying to sample from latent vector {t.key} using keys, but not found in dataset"
+                out[k] = torch.tensor([t._lookup(lab) for lab in batch[t.key]], dtype=torch.int64)
+        return out
+
     def populate_grads(self):
-        """Make ``.grad`` of every parameter what autograd would have produced (dense table grads, trainer.py:121)."""
-        st = _lib.stream_ptr(self.dev)
+        """Make ``.grad`` of every parameter what autograd would have produced (dense table grads, trainer.py:121).  The
+        gradients were already written by the enqueue (MLP bucket by the backward kernels, tables by the in-step scatter);
+        this only attaches the buffers — no launch."""
         if not self.frozen:
             for p, gv in zip(self.mlp_params, self.grad_views):
                 p.grad = gv
         for k, t in self.tables.items():
-            if t is None:
-                continue
-            if t.data.grad is None:
-                t.data.grad = torch.zeros_like(t.data)
-            rc = self.lib.findb200_scatter_add_rows(_lib.ptr(t.data.grad), t.data.shape[0], t.data.shape[1],
-                                                    _lib.ptr(self.idx), self.B, _lib.ptr(self.grows[k]), st)
-            _lib.check(rc, "findb200_scatter_add_rows")
+            if t is not None:
+                t.data.grad = self.table_grads[k]
 
     # ---- pipelined host feed: the NEXT batch crosses PCIe on a copy stream while the current step computes ---------------
     def prefetch_from_host(self, idx: torch.Tensor, target: torch.Tensor, col_target: Optional[torch.Tensor] = None):
@@ -224,6 +274,7 @@ class TrainStep:
             self._staged, self._stage_next = [], 0
         if len(self._staged) >= 2:
             raise RuntimeError("prefetch_from_host: two batches are already staged; call step_prefetched() first")
+        self._check_rows(idx)
         k = self._stage_next
         st = self._stage[k]
         with torch.cuda.stream(self._copy_stream):
@@ -248,7 +299,7 @@ class TrainStep:
         st = self._stage[k]
         cur = torch.cuda.current_stream(self.dev)
         cur.wait_event(self._ready[k])
-        self.idx.copy_(st["idx"], non_blocking=True)                 # device -> device into the graph's static inputs
+        self.idx4.copy_(st["idx"].unsqueeze(0).expand_as(self.idx4), non_blocking=True)   # device -> device into the graph's static inputs
         self.target.copy_(st["target"], non_blocking=True)
         if st["col_target"] is not None:
             self.col_target.copy_(st["col_target"], non_blocking=True)

@@ -288,19 +288,32 @@ int findb200_train_step_knn_stats(const void* workspace, int nfeet, int V, int P
 
 /* Latent-table access (replaces LatentVector.__getitem__ with an index tensor, src/model/model.py:130-152 as called
  * from sample_latent_vectors src/train/trainer.py:29-46, and the index scatter-add of its autograd).
- * table / grad_table: [n_rows,width]; idx: int64 [B] (device); out / g: [B,width].  Duplicate rows accumulate. */
+ * table / grad_table: [n_rows,width]; idx: int64 [B] (device); out / g: [B,width].  Duplicate rows accumulate.
+ * An index outside [0, n_rows) traps the kernel with a message, like torch's device-side assert for `self.data[idx]`. */
 int findb200_gather_rows(const float* table, int n_rows, int width, const int64_t* idx, int B, float* out, void* stream);
 int findb200_scatter_add_rows(float* grad_table, int n_rows, int width, const int64_t* idx, int B, const float* g,
                               void* stream);
-/* the same gather for up to 8 tables in one launch (shapevec / posevec / texvec / reg rows of a batch) */
-typedef struct findb200_gather_job { const float* table; int n_rows; int width; float* out; } findb200_gather_job;
+/* the same gather for up to 8 tables in one launch (shapevec / posevec / texvec / reg rows of a batch).  A job's own `idx`
+ * (non-NULL) overrides the common one: labelled tables are indexed by batch[vec.key], the others by batch['idx']
+ * (sample_latent_vectors, src/train/trainer.py:29-46). */
+typedef struct findb200_gather_job { const float* table; int n_rows; int width; float* out; const int64_t* idx; } findb200_gather_job;
 int findb200_gather_rows_multi(const findb200_gather_job* jobs, int n_jobs, const int64_t* idx, int B, void* stream);
+/* Dense table gradients of one step for up to 8 tables in one launch, WITHOUT atomics (bit-reproducible): row r of
+ * grad_table = (accumulate ? itself : 0) + the sum, in batch order, of g[b] over the batch entries with idx[b] == r — what
+ * loss.backward() leaves in LatentVector.data.grad after optimiser.zero_grad() (src/train/trainer.py:99-100,121). */
+typedef struct findb200_scatter_job { const float* g; int n_rows; int width; float* grad_table; const int64_t* idx; } findb200_scatter_job;
+int findb200_scatter_rows_multi(const findb200_scatter_job* jobs, int n_jobs, const int64_t* idx, int B, int accumulate,
+                                void* stream);
 
 
 /* ------------------------------------------------------------------------------------------------------
  * Diagnostics: one-CTA tcgen05 self-test of the shared-memory image / descriptor / TMEM conventions used by
- * the field kernels (mode 0: K-major operands, forward and dX shape; mode 1: MN-major operands, dW shape).
- * a_img / b_img are fp16 swizzled tile images (see csrc/umma_selftest.cu); d_out is fp32 [128][256].
+ * the field kernels (mode 0: K-major operands, forward and dX shape; mode 1: MN-major operands, dW shape;
+ * modes 2 / 3: the CTA-pair form, one tcgen05.mma.cta_group::2 stream with M = 256 over a cluster of two CTAs,
+ * each staging half of the weight operand — 2: peer -> leader relay by remote mbarrier arrive, 3: the peer's bulk
+ * copies signal the leader's mbarrier directly).
+ * a_img / b_img are fp16 swizzled tile images (see csrc/umma_selftest.cu); d_out is fp32 [128][256]
+ * ([256][256] for modes 2 / 3).
  * ------------------------------------------------------------------------------------------------------ */
 int findb200_umma_selftest(int mode, const void* a_img, const void* b_img, float* d_out, void* stream);
 

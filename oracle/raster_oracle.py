@@ -25,6 +25,7 @@ import math
 
 import torch
 
+Z_CLIP = 0.01
 K_EPS = 1e-8
 
 
@@ -78,8 +79,10 @@ def silhouette(verts: torch.Tensor, faces: torch.Tensor, H: int, W: int, blur_ra
     blur = math.sqrt(blur_radius)
     xmin, xmax = torch.minimum(torch.minimum(x0, x1), x2) - blur, torch.maximum(torch.maximum(x0, x1), x2) + blur
     ymin, ymax = torch.minimum(torch.minimum(y0, y1), y2) - blur, torch.maximum(torch.maximum(y0, y1), y2) + blur
-    zmax = torch.maximum(torch.maximum(z0, z1), z2)
-    face_ok = (area.abs() > K_EPS) & (zmax >= 0)
+    # PyTorch3D clips faces against z_clip = znear / 2 = 0.01 (renderer.py:228-236, 258); restated conservatively as a cull of
+    # every face with a vertex nearer than that (no face of a foot seen from 0.1-0.35 m gets there) — same rule as csrc/raster.cu
+    zmin = torch.minimum(torch.minimum(z0, z1), z2)
+    face_ok = (area.abs() > K_EPS) & (zmin >= Z_CLIP)
     in_box = (px >= xmin) & (px <= xmax) & (py >= ymin) & (py <= ymax)
     den = area + K_EPS
     w0 = _edge(px, py, x1, y1, x2, y2) / den

@@ -1,0 +1,306 @@
+"""GPU parity at BASELINE.json's FULL sizes and over a training trajectory.
+
+  * cfg2 (8 feet x 10 242 verts x 10 000 targets) and cfg5's per-GPU shape (32 feet, frozen MLP): every gradient of the fused
+    step — 13 W, 13 b, the three latent tables, reg — against oracle/step_oracle.py (fp32 torch autograd + C Chamfer).
+    Stated tolerance: rel-L2 <= 5e-2 per tensor vs the fp32 reference (ReLU-mask flips of the fp16-operand forward, see
+    tests/test_field_gpu.py); outputs / losses <= 1e-3.  The per-tensor table is written to gpurun_out/ for profiles/.
+  * trajectory: 50 optimiser steps (Adam lr 5e-5 on the MLP, Adam lr 1e-4 on the latent tables, SGD momentum lr 1e-5 on reg —
+    /root/reference/src/train/train.py:161-168, opts.py:54-57) from identical state on the GPU (TrainStep + FusedAdam /
+    FusedSGD) and on the CPU oracle (torch.optim): the loss curves must agree to 2e-3 at every step and the parameter UPDATE
+    (final - initial) to 0.1 rel-L2.  This is the evidence that the mask-flip gradient noise is benign for training.
+  * duplicate latent rows in one batch (shared labels, /root/reference/src/data/dataset.py:191-201), the z_cutoff both-sides
+    branch against the oracle, kNN / field forward at cfg4's size (50 000 x 100 000), run-to-run determinism.
+"""
+import json
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import chamfer_oracle as co
+from oracle import field_oracle as fo
+from oracle import step_oracle as so
+
+pytestmark = pytest.mark.gpu
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+THREADS = os.cpu_count() or 1
+
+
+def rel_l2(a, b):
+    a = torch.as_tensor(a).detach().double().cpu().reshape(-1)
+    b = torch.as_tensor(b).detach().double().cpu().reshape(-1)
+    return float((a - b).norm() / b.norm().clamp_min(1e-30))
+
+
+def _record(name, obj):
+    d = os.path.join(ROOT, "gpurun_out")
+    try:
+        os.makedirs(d, exist_ok=True)
+        with open(os.path.join(d, name), "w") as fh:
+            json.dump(obj, fh, indent=1)
+    except OSError:
+        pass
+
+
+def _setup(B, V, P2, n_rows, seed, idx=None):
+    from find_b200 import synthetic as syn
+    from find_b200.field import NeuralDisplacementField
+    dev = torch.device("cuda:0")
+    model = NeuralDisplacementField(use_shapevec=True, use_texvec=True, use_posevec=True, train_size=n_rows, val_size=1,
+                                    shapevec_size=100, texvec_size=100, posevec_size=100, device=dev)
+    p = fo.random_params(seed)
+    sd = model.state_dict()
+    with torch.no_grad():
+        for k, v in p.items():
+            sd[k].copy_(v)
+    tv, tf = syn.make_template(V)
+    model.set_template(tv, tf)
+    lat = syn.make_latents(n_rows, 0)
+    with torch.no_grad():
+        for k in ("shapevec", "posevec", "texvec", "reg"):
+            getattr(model, k).data.copy_(lat[k])
+    if idx is None:
+        idx = torch.arange(B)
+    target = syn.make_targets(B, P2, 0)
+    colt = syn.make_col_target(B, V, 0)
+    tables = {k: lat[k] for k in ("shapevec", "posevec", "texvec", "reg")}
+    return dev, model, p, tv, tables, idx, target, colt
+
+
+def _grad_table(step, model, ref, p, frozen):
+    """-> {tensor name: rel-L2 of the GPU gradient vs the oracle's}"""
+    out = {}
+    for k in ("shapevec", "posevec", "texvec", "reg"):
+        out["table/" + k] = rel_l2(getattr(model, k).data.grad, ref["table_grads"][k])
+    if not frozen:
+        for name, prm in model.named_parameters():
+            if name in p:
+                out[name] = rel_l2(prm.grad, ref["grads"][name])
+    return out
+
+
+@pytest.mark.parametrize("cfg", ["cfg2", "cfg5"])
+def test_full_size_gradients_vs_oracle(cfg):
+    from find_b200.step import TrainStep
+    B, V, P2, frozen = {"cfg2": (8, 10242, 10000, False), "cfg5": (32, 10242, 10000, True)}[cfg]
+    dev, model, p, tv, tables, idx, target, colt = _setup(B, V, P2, B, seed=81)
+    ref = so.train_step(p, fo.fourier_B(), tv, tables, idx, target, colt, threads=THREADS, need_param_grads=not frozen)
+    step = TrainStep(model, B, P2, with_colour=True, frozen_mlp=frozen, use_graph=False)
+    step.load_inputs(idx, target, colt)
+    step.run()
+    step.populate_grads()
+    torch.cuda.synchronize()
+    total, chamf, tex = step.loss3.tolist()
+    errs = {"loss": abs(total - ref["loss"]) / ref["loss"], "chamf": abs(chamf - ref["chamf"]) / ref["chamf"],
+            "tex": abs(tex - ref["tex"]) / ref["tex"], "verts": rel_l2(step.verts, ref["verts"]),
+            "disp": rel_l2(step.disp, ref["disp"]), "col": rel_l2(step.col, ref["col"])}
+    grads = _grad_table(step, model, ref, p, frozen)
+    _record(f"parity_r2_{cfg}_full_size.json", {"shape": [B, V, P2], "frozen": frozen, "outputs": errs, "grad_rel_l2": grads})
+    for k, e in errs.items():
+        assert e < 1e-3, (k, e)
+    for k, e in grads.items():
+        assert e < 5e-2, (k, e)
+    # the Chamfer index contract at full size, on the GPU's own vertices: bit-exact
+    ch = co.chamfer(step.verts.cpu().numpy(), target.numpy(), with_grad=False, threads=THREADS)
+    from find_b200 import knn_points
+    k1 = knn_points(step.verts, target.to(dev))
+    assert np.array_equal(k1.idx[..., 0].cpu().numpy(), ch["idx_x"])
+    assert np.array_equal(k1.dists[..., 0].cpu().numpy(), ch["dist_x"])
+
+
+def test_training_trajectory_matches_cpu_oracle():
+    from find_b200.optim import FusedAdam, FusedSGD
+    from find_b200.step import TrainStep
+    B, V, P2, n_rows, n_steps = 4, 2562, 2500, 4, 50
+    dev, model, p, tv, tables, idx, target, colt = _setup(B, V, P2, n_rows, seed=82)
+    Bm = fo.fourier_B()
+    # ---- CPU oracle trajectory (torch.optim IS what the reference steps)
+    cp = {k: v.clone() for k, v in p.items()}
+    ct = {k: v.clone() for k, v in tables.items()}
+    params_c = [cp[k] for k in sorted(cp)]
+    lat_c = [ct[k] for k in ("shapevec", "posevec", "texvec")]
+    for t in params_c + lat_c + [ct["reg"]]:
+        t.requires_grad_(True)
+    o_net, o_lat = torch.optim.Adam(params_c, lr=5e-5), torch.optim.Adam(lat_c, lr=1e-4)
+    o_reg = torch.optim.SGD([ct["reg"]], lr=1e-5, momentum=0.9)
+    cpu_losses = []
+    for _ in range(n_steps):
+        ref = so.train_step({k: v.detach() for k, v in cp.items()}, Bm, tv, {k: v.detach() for k, v in ct.items()}, idx, target,
+                            colt, threads=THREADS)
+        cpu_losses.append(ref["loss"])
+        for k in cp:
+            cp[k].grad = ref["grads"][k]
+        for k in ct:
+            ct[k].grad = ref["table_grads"][k]
+        o_net.step(); o_lat.step(); o_reg.step()
+    # ---- GPU trajectory
+    step = TrainStep(model, B, P2, with_colour=True, use_graph=False)
+    step.load_inputs(idx, target, colt)
+    g_net = FusedAdam(step.mlp_params, lr=5e-5)
+    g_lat = FusedAdam([model.shapevec.data, model.posevec.data, model.texvec.data], lr=1e-4)
+    g_reg = FusedSGD([model.reg.data], lr=1e-5, momentum=0.9)
+    gpu_losses = []
+    for _ in range(n_steps):
+        step.run()
+        step.populate_grads()
+        gpu_losses.append(float(step.loss3[0]))
+        g_net.step(); g_lat.step(); g_reg.step()
+    torch.cuda.synchronize()
+    curve = [abs(a - b) / abs(b) for a, b in zip(gpu_losses, cpu_losses)]
+    p0 = fo.random_params(82)
+    upd = {}
+    for name, prm in model.named_parameters():
+        if name in p0:
+            d_ref = (cp[name].detach() - p0[name]).double()
+            d_gpu = (prm.detach().cpu() - p0[name]).double()
+            upd[name] = float((d_gpu - d_ref).norm() / d_ref.norm().clamp_min(1e-30))
+    for k in ("shapevec", "posevec", "texvec", "reg"):
+        d_ref = (ct[k].detach() - tables[k]).double()
+        d_gpu = (getattr(model, k).data.detach().cpu() - tables[k]).double()
+        upd["table/" + k] = float((d_gpu - d_ref).norm() / d_ref.norm().clamp_min(1e-30))
+    wrel = {n: rel_l2(prm, cp[n]) for n, prm in model.named_parameters() if n in p0}
+    _record("parity_r2_trajectory.json", {"steps": n_steps, "shape": [B, V, P2], "loss_first_last_cpu": [cpu_losses[0], cpu_losses[-1]],
+                                           "loss_first_last_gpu": [gpu_losses[0], gpu_losses[-1]], "loss_rel_diff_max": max(curve),
+                                           "loss_rel_diff_per_step": curve, "update_rel_l2": upd, "weights_rel_l2_max": max(wrel.values())})
+    assert cpu_losses[-1] < cpu_losses[0]                      # the trajectory really descends
+    assert max(curve) < 2e-3, max(curve)
+    assert max(upd.values()) < 0.1, upd
+    assert max(wrel.values()) < 1e-4, wrel
+
+
+def test_duplicate_latent_rows_accumulate():
+    """Feet that share a label index the SAME latent row (dataset.py:191-201): the row's gradient is the sum over those feet."""
+    from find_b200.step import TrainStep
+    B, V, P2, n_rows = 5, 700, 600, 4
+    idx = torch.tensor([2, 0, 2, 3, 2])
+    dev, model, p, tv, tables, idx, target, colt = _setup(B, V, P2, n_rows, seed=83, idx=idx)
+    ref = so.train_step(p, fo.fourier_B(), tv, tables, idx, target, colt)
+    step = TrainStep(model, B, P2, with_colour=True, use_graph=False)
+    step.load_inputs(idx, target, colt)
+    step.run()
+    step.populate_grads()
+    torch.cuda.synchronize()
+    for k in ("shapevec", "posevec", "texvec", "reg"):
+        g = getattr(model, k).data.grad
+        assert rel_l2(g, ref["table_grads"][k]) < 5e-2, k
+        assert float(g[1].abs().max()) == 0.0                      # row 1 is not in the batch
+        # the duplicated row really is the sum of three feet's gradients
+        assert rel_l2(g[2], step.grows[k][[0, 2, 4]].sum(0)) < 1e-6, k
+
+
+def test_row_index_out_of_range_is_refused():
+    from find_b200.step import TrainStep
+    B, V, P2, n_rows = 2, 300, 200, 3
+    dev, model, p, tv, tables, idx, target, colt = _setup(B, V, P2, n_rows, seed=84)
+    step = TrainStep(model, B, P2, with_colour=True, use_graph=False)
+    with pytest.raises((RuntimeError, IndexError)):
+        step.load_inputs(torch.tensor([0, 3]), target, colt)
+    with pytest.raises((RuntimeError, IndexError)):
+        step.load_inputs(torch.tensor([-1, 0]), target, colt)
+
+
+def test_z_cutoff_both_sides_matches_oracle():
+    """losses.py:69-77: both clouds cut at z <= z_cutoff -> ragged Chamfer; oracle = C Chamfer on the same padded clouds."""
+    from find_b200.losses import DisplacementLoss
+    dev = torch.device("cuda:0")
+    g = torch.Generator().manual_seed(6)
+    verts = torch.randn(3, 400, 3, generator=g) * 0.05
+    pts = torch.randn(3, 350, 3, generator=g) * 0.05
+    zc = 0.01
+    xv = verts.to(dev).requires_grad_(True)
+    loss = DisplacementLoss()(None, {"verts": xv}, {"points": pts.to(dev)}, 0, num_samples=None, z_cutoff=zc)["loss"]
+    loss.backward()
+
+    def cut(c):
+        lens = (c[..., 2] <= zc).sum(1)
+        pad = torch.zeros_like(c)
+        for b in range(c.shape[0]):
+            pad[b, : int(lens[b])] = c[b][c[b, :, 2] <= zc]
+        return pad, lens
+    xp, xl = cut(verts)
+    yp, yl = cut(pts)
+    ref = co.chamfer(xp.numpy(), yp.numpy(), xl.numpy(), yl.numpy())
+    assert abs(float(loss) - ref["loss"]) <= 2e-6 * ref["loss"]
+    gref = torch.zeros_like(verts)                               # scatter the padded-cloud gradient back to the kept rows
+    for b in range(3):
+        gref[b][verts[b, :, 2] <= zc] = torch.from_numpy(ref["grad_x"][b, : int(xl[b])])
+    np.testing.assert_allclose(xv.grad.cpu().numpy(), gref.numpy(), rtol=1e-5, atol=1e-9)
+
+
+def test_cfg4_size_knn_bit_exact_and_field_forward():
+    """BASELINE.json configs[3]: 50 000-vertex template vs 100 000 target points (one foot): kNN bit-exact both directions,
+    field forward vs the fp32 oracle."""
+    from find_b200 import knn_points
+    from find_b200 import synthetic as syn
+    from find_b200.step import TrainStep
+    B, V, P2 = 1, 50000, 100000
+    dev, model, p, tv, tables, idx, target, colt = _setup(B, V, P2, 1, seed=85)
+    step = TrainStep(model, B, P2, with_colour=True, use_graph=False)
+    step.load_inputs(idx, target, colt)
+    step.run()
+    torch.cuda.synchronize()
+    ref = so.train_step(p, fo.fourier_B(), tv, tables, idx, target, colt, forward_only=True, threads=THREADS)
+    assert rel_l2(step.verts, ref["verts"]) < 1e-3 and rel_l2(step.disp, ref["disp"]) < 1e-3 and rel_l2(step.col, ref["col"]) < 1e-3
+    assert abs(float(step.loss3[1]) - ref["chamf"]) <= 1e-3 * ref["chamf"]
+    v = step.verts.cpu().numpy()
+    ch = co.chamfer(v, target.numpy(), with_grad=False, threads=THREADS)
+    k1 = knn_points(step.verts, target.to(dev))
+    k2 = knn_points(target.to(dev), step.verts)
+    assert np.array_equal(k1.idx[..., 0].cpu().numpy(), ch["idx_x"])
+    assert np.array_equal(k2.idx[..., 0].cpu().numpy(), ch["idx_y"])
+    assert np.array_equal(k1.dists[..., 0].cpu().numpy(), ch["dist_x"])
+    assert np.array_equal(k2.dists[..., 0].cpu().numpy(), ch["dist_y"])
+
+
+def test_outputs_and_weight_gradients_are_run_to_run_identical():
+    """Two enqueues of the same step: outputs, losses' Chamfer term and the MLP-gradient bucket (deterministic dW fold) are
+    bit-identical; the atomically accumulated pieces (latent / reg gradients, Chamfer distance gradient) agree to 1e-6."""
+    from find_b200.step import TrainStep
+    B, V, P2, n_rows = 4, 3000, 2500, 4
+    dev, model, p, tv, tables, idx, target, colt = _setup(B, V, P2, n_rows, seed=86)
+    step = TrainStep(model, B, P2, with_colour=True, use_graph=False)
+    step.load_inputs(idx, target, colt)
+    step.run(); torch.cuda.synchronize()
+    a = (step.verts.clone(), step.col.clone(), step.loss3.clone(), step.flat_grad.clone(), {k: v.clone() for k, v in step.grows.items()})
+    step.run(); torch.cuda.synchronize()
+    assert torch.equal(a[0], step.verts) and torch.equal(a[1], step.col)
+    assert rel_l2(step.loss3, a[2]) < 1e-6
+    assert rel_l2(step.flat_grad, a[3]) < 1e-5
+    for k, v in a[4].items():
+        assert rel_l2(step.grows[k], v) < 1e-5, k
+
+
+def test_texture_loss_gt_space_matches_oracle():
+    """losses.py:22-57: masked colour MSE at surface samples of the GT mesh, through the field's per-foot-points call site.
+    The oracle evaluates the fp32 field at the SAME samples (the draw is injected from the GPU call)."""
+    from find_b200 import synthetic as syn
+    from find_b200.losses import TextureLossGTSpace
+    from find_b200.mesh import Meshes, sample_points_from_meshes
+    B, V, S = 3, 2562, 1000
+    dev, model, p, tv, tables, idx, target, colt = _setup(B, V, 16, B, seed=87)
+    _, tf = syn.make_template(V)
+    g = torch.Generator().manual_seed(3)
+    gt_verts = tv[None] * (1 + 0.05 * torch.randn(B, 1, 1, generator=g)) + 0.002 * torch.randn(B, V, 3, generator=g)
+    gt_col = torch.rand(B, V, 3, generator=g)
+    gt_col[:, ::3] = 1.0                                            # white (= unobserved) vertices: samples near them are masked
+    mesh = Meshes(gt_verts.to(dev), tf.to(dev), textures=gt_col.to(dev))
+    zs, zp, zt = (tables[k][idx].to(dev).requires_grad_(True) for k in ("shapevec", "posevec", "texvec"))
+    batch = {"mesh": mesh, "shapevec": zs, "posevec": zp, "texvec": zt}
+    loss = TextureLossGTSpace()(model, batch, num_samples=S, seed=11)
+    loss.backward()
+    pts, cols = sample_points_from_meshes(mesh, num_samples=S, return_textures=True, seed=11)
+    pts, cols = pts.cpu(), cols.cpu()
+    zo = [tables[k][idx].clone().requires_grad_(True) for k in ("shapevec", "posevec", "texvec")]
+    po = {k: v.clone().requires_grad_(True) for k, v in p.items()}
+    res = fo.field_forward(po, fo.fourier_B(), pts, shapevec=zo[0], posevec=zo[1], texvec=zo[2])
+    mask = (cols < 1).any(-1, keepdim=True).expand(-1, -1, 3)
+    ref = (torch.nn.functional.mse_loss(res["col"], cols, reduction="none") * mask).mean()
+    ref.backward()
+    assert 0.3 < float(mask.float().mean()) < 1.0
+    assert abs(float(loss) - float(ref)) <= 1e-3 * float(ref)
+    assert rel_l2(zt.grad, zo[2].grad) < 5e-2
+    for name, prm in model.named_parameters():
+        if name.startswith("mlp_col") and name in p:
+            assert rel_l2(prm.grad, po[name].grad) < 5e-2, name

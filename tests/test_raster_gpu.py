@@ -166,8 +166,9 @@ def test_nearest_face_fragments_and_mask_out_faces():
     masked = torch.arange(0, tf.shape[0], 3, device=dev)
     vw = verts.to(dev).requires_grad_(True)
     mesh = Meshes(vw, tf.to(dev))
-    plain = r(mesh, R, T)["mask"]
-    out = r(mesh, R, T, mask_out_faces=True, masked_faces=masked, return_mask_out_masks=True)
+    mk = dict(return_images=False, return_mask=True)     # reference defaults are images on / mask off (renderer.py:247-249)
+    plain = r(mesh, R, T, **mk)["mask"]
+    out = r(mesh, R, T, mask_out_faces=True, masked_faces=masked, return_mask_out_masks=True, **mk)
     mm = out["mask_out_masks"]
     assert mm.shape == (2, 2, S, S) and mm.dtype == torch.bool and 0.05 < float(mm.float().mean()) < 0.5
     assert float(out["mask"][mm].abs().max()) == 0.0 and torch.equal(out["mask"][~mm], plain[~mm])
@@ -175,7 +176,7 @@ def test_nearest_face_fragments_and_mask_out_faces():
     assert torch.equal(mm, expect)
     out["mask"].sum().backward()
     assert torch.isfinite(vw.grad).all() and float(vw.grad.abs().max()) > 0
-    lst = r(mesh, R, T, mask_out_faces=True, masked_faces=[masked, masked[:5]], return_mask_out_masks=True)
+    lst = r(mesh, R, T, mask_out_faces=True, masked_faces=[masked, masked[:5]], return_mask_out_masks=True, **mk)
     assert torch.equal(lst["mask_out_masks"][0], mm[0]) and int(lst["mask_out_masks"][1].sum()) < int(mm[1].sum())
 
 
@@ -242,6 +243,13 @@ def test_phong_image_forward_matches_oracle():
         masked = r(mesh, R, T, return_images=True, return_mask=True, mask_out_faces=True, masked_faces=torch.arange(0, tf.shape[0], 2, device=dev),
                    return_mask_out_masks=True)
     assert torch.equal(only["image"].cpu(), img)
+    # reference defaults: renderer(mesh, R, T) returns the IMAGE only (mesh_turntable.py:57); mask_with_grad=False with images
+    # gives the hard mask any(image < 1) (renderer.py:311-312)
+    with torch.no_grad():
+        dflt = r(mesh, R, T)
+        hard = r(mesh, R, T, return_mask=True, mask_with_grad=False)
+    assert set(dflt) == {"image"} and torch.equal(dflt["image"].cpu(), img)
+    assert torch.equal(hard["mask"].cpu(), torch.any(img < 1, dim=-1).float()) and torch.equal(hard["image"].cpu(), img)
     mm = masked["mask_out_masks"]
     assert float((masked["image"][mm] - 1.0).abs().max()) == 0.0 and float(masked["mask"][mm].abs().max()) == 0.0
     with pytest.raises(NotImplementedError):

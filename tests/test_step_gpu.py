@@ -144,18 +144,21 @@ def test_displacement_loss_z_cutoff_variants_run_ragged():
     verts = (torch.randn(2, 300, 3, generator=g) * 0.05).to(dev)
     pts = (torch.randn(2, 250, 3, generator=g) * 0.05).to(dev)
     L = DisplacementLoss()
-    full = L(None, {"verts": verts}, {"points": pts}, 0)["loss"]
+    full = L(None, {"verts": verts}, {"points": pts}, 0, num_samples=None)["loss"]      # explicit opt-out of the 5000-sample default
     ref = co.chamfer(verts.cpu().numpy(), pts.cpu().numpy(), with_grad=False)["loss"]
     assert abs(float(full) - ref) <= 1e-6 * ref
-    cut = L(None, {"verts": verts}, {"points": pts}, 0, gt_z_cutoff=0.0)["loss"]
+    cut = L(None, {"verts": verts}, {"points": pts}, 0, num_samples=None, gt_z_cutoff=0.0)["loss"]
     lens = (pts[..., 2] <= 0).sum(1)
     padded = torch.zeros_like(pts)
     for b in range(2):
         padded[b, : int(lens[b])] = pts[b][pts[b, :, 2] <= 0]
     ref2 = co.chamfer(verts.cpu().numpy(), padded.cpu().numpy(), y_lengths=lens.cpu().numpy(), with_grad=False)["loss"]
     assert abs(float(cut) - ref2) <= 1e-6 * ref2
-    both = L(None, {"verts": verts}, {"points": pts}, 0, z_cutoff=0.0)["loss"]
-    assert torch.isfinite(both)
+    both = L(None, {"verts": verts}, {"points": pts}, 0, num_samples=None, z_cutoff=0.0)["loss"]
+    assert torch.isfinite(both)                    # vs the oracle: tests/test_parity_full_gpu.py::test_z_cutoff_both_sides_matches_oracle
+    # the reference default (losses.py:61) is 5000 surface samples: without meshes in res / batch it must not silently fall back
+    import inspect
+    assert inspect.signature(L.forward).parameters["num_samples"].default == 5000
 
 
 @pytest.mark.parametrize("use_graph", [False, True])

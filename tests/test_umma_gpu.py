@@ -51,3 +51,28 @@ def test_mnmajor_dw_shape():
     D = _run(1, to_image(G), to_image(H))
     ref = G.astype(np.float32).T @ H.astype(np.float32)
     np.testing.assert_allclose(D, ref, rtol=1e-3, atol=2e-3)
+
+
+def _run_pair(mode, A, W):
+    """CTA-pair self-test (modes 2 / 3): A [256,256], W [256,256] fp16 -> D [256,256] through tcgen05.mma.cta_group::2."""
+    from find_b200 import _lib
+    lib = _lib.load()
+    a_img = np.concatenate([to_image(A[r * 128:(r + 1) * 128]) for r in range(2)])
+    b_img = np.concatenate([to_image(W[:, kc * 64:(kc + 1) * 64]) for kc in range(4)])
+    a = torch.from_numpy(a_img.view(np.int16)).cuda()
+    b = torch.from_numpy(b_img.view(np.int16)).cuda()
+    d = torch.zeros(256, 256, device="cuda")
+    rc = lib.findb200_umma_selftest(mode, _lib.ptr(a), _lib.ptr(b), _lib.ptr(d), _lib.stream_ptr(d.device))
+    _lib.check(rc, "findb200_umma_selftest")
+    torch.cuda.synchronize()
+    return d.cpu().numpy()
+
+
+def test_cta_pair_m256_relay():
+    """cta_group::2: each CTA stages its 128 rows of A and HALF of every weight chunk; peer -> leader relay."""
+    rng = np.random.RandomState(2)
+    A = (rng.randn(256, 256) * 0.5).astype(np.float16)
+    W = (rng.randn(256, 256) * 0.1).astype(np.float16)
+    D = _run_pair(2, A, W)
+    ref = A.astype(np.float32) @ W.astype(np.float32).T
+    np.testing.assert_allclose(D, ref, rtol=1e-3, atol=1e-3)
