@@ -17,7 +17,7 @@ CSRC = os.path.join(_HERE, "csrc")
 LIB = os.path.join(_HERE, "libfindb200.so")
 _STAMP = os.path.join(_HERE, ".libfindb200.stamp")
 
-SOURCES = ["capi.cu", "chamfer.cu", "field.cu", "field_chain.cu", "field_dw.cu", "step.cu", "mesh.cu", "optim.cu", "allreduce.cu", "raster.cu", "umma_selftest.cu", "diag.cu"]
+SOURCES = ["capi.cu", "chamfer.cu", "field.cu", "field_chain.cu", "field_chain2.cu", "field_dw.cu", "step.cu", "mesh.cu", "optim.cu", "allreduce.cu", "raster.cu", "umma_selftest.cu", "diag.cu"]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",
     "-O3", "-lineinfo", "-std=c++17",

@@ -200,32 +200,15 @@ FB_DEVINL uint32_t mapa_u32(uint32_t local_smem_addr, uint32_t rank) {
     asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(local_smem_addr), "r"(rank));
     return r;
 }
-// arrive on an mbarrier anywhere in the cluster (address from mapa_u32); release at cluster scope
+// arrive on an mbarrier anywhere in the cluster (address from mapa_u32).  Default semantics (.release at CTA scope), as
+// CUTLASS's ClusterBarrier::arrive(cta_id) does: the explicit .release.cluster form makes ptxas emit MEMBAR.ALL.GPU before every
+// arrive and the .acquire.cluster wait a CCTL.IVALL (L1 invalidate) after every wait — measured: the pair kernels ran 25 %
+// SLOWER than the single-CTA ones with them.  What travels through these barriers is shared-memory data that is already in
+// place (bulk-copy completions, or st.shared + fence.proxy.async + bar.sync by the writers), consumed by the async proxy.
 FB_DEVINL void mbar_arrive_cluster(uint32_t cluster_addr) {
-    asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+    asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
 }
-FB_DEVINL bool mbar_try_wait_cluster(uint64_t* bar, uint32_t parity) {   // acquire at cluster scope (remote arrivals)
-    uint32_t ok;
-    asm volatile(
-        "{\n\t.reg .pred p;\n\t"
-        "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2;\n\t"
-        "selp.u32 %0, 1, 0, p;\n\t}"
-        : "=r"(ok)
-        : "r"(smem_u32(bar)), "r"(parity)
-        : "memory");
-    return ok != 0;
-}
-FB_DEVINL void mbar_wait_cluster(uint64_t* bar, uint32_t parity) {
-    if (mbar_try_wait_cluster(bar, parity)) return;
-    long long t0 = clock64();
-    while (!mbar_try_wait_cluster(bar, parity)) {
-        if (clock64() - t0 > FB_WAIT_TIMEOUT_CYCLES) {
-            printf("find_b200: cluster mbarrier wait timeout block %d thread %d bar@%u parity %u\n", (int)blockIdx.x,
-                   (int)threadIdx.x, smem_u32(bar), parity);
-            __trap();
-        }
-    }
-}
+FB_DEVINL void mbar_wait_cluster(uint64_t* bar, uint32_t parity) { mbar_wait(bar, parity); }
 FB_DEVINL void tmem_alloc2(uint32_t* smem_dst, uint32_t ncols) {   // one warp in EACH CTA of the pair
     asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(smem_dst)),
                  "r"(ncols)

@@ -1,5 +1,6 @@
 // find_b200/csrc/diag.cu — FP32 CUDA-core peak microbenchmarks (roofline denominators for the Chamfer kernel;
 // MEASURED_PEAKS.json carries no fp32 entry).  mode 0: scalar FFMA chains, mode 1: packed FFMA2 chains.
+#include <cstdlib>
 #include "common.cuh"
 #include "../../include/find_b200.h"
 
@@ -94,8 +95,12 @@ extern "C" int findb200_l2_stream(const void* src, size_t region_bytes, int chun
 
 // Diagnostics: dev_buf (>= 256 x u64, zeroed by the caller) receives %globaltimer stamps of CTA 0's first head_fwd item
 // (slots: field_chain.cu dbg_stamp call sites); NULL turns the trace off.
-namespace fb { namespace field { extern unsigned long long* g_chain_dbg; } }
+namespace fb { namespace field { extern unsigned long long* g_chain_dbg; extern int g_chain_dbg_flags; } }
 extern "C" int findb200_chain_trace(void* dev_buf) {
-    fb::field::g_chain_dbg = (unsigned long long*)dev_buf;
+    // a pointer with bit 0 set asks for the cycle accounting only (no per-chunk stamps, which slow the issuing thread down)
+    const uintptr_t v = (uintptr_t)dev_buf;
+    fb::field::g_chain_dbg_flags = (v & 1) ? 0 : 1;
+    if (const char* e = getenv("FINDB200_CHAIN_DBG")) fb::field::g_chain_dbg_flags |= atoi(e) & ~1;   // timing experiments, see field_chain2.cu
+    fb::field::g_chain_dbg = (unsigned long long*)(v & ~(uintptr_t)1);
     return 0;
 }

@@ -20,6 +20,12 @@ namespace field {
 static inline size_t align1k(size_t x) { return (x + 1023) & ~(size_t)1023; }
 static inline int cdiv(int a, int b) { return (a + b - 1) / b; }
 
+bool chain_pairs_enabled() {
+    static int on = -1;
+    if (on < 0) { const char* e = getenv("FINDB200_CHAIN"); on = (e && e[0] == '1') ? 0 : 1; }
+    return on != 0;
+}
+
 static int g_sms = 0;
 static int num_sms() {
     if (!g_sms) {
@@ -517,6 +523,7 @@ static void fill_chain_common(ChainParams& C, const findb200_field_params* p, co
     C.dovals = (const float*)(ws + w.dovals);
     C.maxabs = (const uint32_t*)(ws + w.scal);
     C.dbg = g_chain_dbg;
+    C.dbg_flags = g_chain_dbg_flags;
 }
 
 static int run_pack(const findb200_field_params* p, const Workspace& w, uint8_t* ws, cudaStream_t st) {
@@ -594,7 +601,7 @@ int findb200_field_forward(const findb200_field_params* p, const float* pos, int
     if (!(save_for_backward && (p->flags & FINDB200_FIELD_TRUNK_CACHED))) {
         const int nt = (w.trunk_tiles <= 2 * sms) ? 1 : 2;
         C.n_items = w.trunk_tiles / nt;
-        rc = launch_chain(0, nt, C, sms, st);
+        rc = chain_pairs_enabled() ? launch_chain2(0, C, sms, st) : launch_chain(0, nt, C, sms, st);
         if (rc) return rc;
     }
     {
@@ -602,7 +609,7 @@ int findb200_field_forward(const findb200_field_params* p, const float* pos, int
         C.n_heads = col ? 2 : 1;
         const int nt = 2;
         C.n_items = C.n_heads * B * (w.tpf2 / nt);
-        rc = launch_chain(1, nt, C, sms, st);
+        rc = chain_pairs_enabled() ? launch_chain2(1, C, sms, st) : launch_chain(1, nt, C, sms, st);
         if (rc) return rc;
     }
     FB_MARK_END(st);
@@ -650,7 +657,7 @@ int findb200_field_backward(const findb200_field_params* p, const float* pos, in
     {
         const int nt = 2;
         C.n_items = n_heads * B * (w.tpf2 / nt);
-        rc = launch_chain(2, nt, C, sms, st);
+        rc = chain_pairs_enabled() ? launch_chain2(2, C, sms, st) : launch_chain(2, nt, C, sms, st);
         if (rc) return rc;
     }
     float* colsum = (float*)(ws + w.colsum);
@@ -684,7 +691,7 @@ int findb200_field_backward(const findb200_field_params* p, const float* pos, in
             for (int hd = 0; hd < 2; ++hd) C.tsrc[hd] = ws + w.hdz + (size_t)hd * 3 * head_tiles * kTileBytes;
         }
         C.n_items = w.trunk_tiles / ((w.trunk_tiles <= 2 * sms) ? 1 : 2);
-        rc = launch_chain(3, (w.trunk_tiles <= 2 * sms) ? 1 : 2, C, sms, st);
+        rc = chain_pairs_enabled() ? launch_chain2(3, C, sms, st) : launch_chain(3, (w.trunk_tiles <= 2 * sms) ? 1 : 2, C, sms, st);
         if (rc) return rc;
     }
     for (int head = 0; head < 2; ++head) {

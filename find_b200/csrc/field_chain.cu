@@ -19,6 +19,7 @@ namespace fb {
 namespace field {
 
 unsigned long long* g_chain_dbg = nullptr;
+int g_chain_dbg_flags = 1;
 
 FB_DEVINL void dbg_stamp(const ChainParams& P, bool first, int slot) {
     if (P.dbg && first && blockIdx.x == 0) {
@@ -314,7 +315,12 @@ __global__ void __launch_bounds__(64 + 128 * NT, 1) chain_kernel(const __grid_co
                 decode(it, head, b, t0);
                 // weights are streamed once per (layer, tile), in the order the MMA warp consumes them
                 if (MODE == TRUNK_FWD) {
-                    for (int l = 0; l < 5; ++l)
+                    // base.0 is consumed in three passes over the 9 encoded-input chunks, tile by tile within a pass: the ring
+                    // must carry the chunks in exactly that order (with NT = 2 a per-tile order would hand tile 1 the wrong ones)
+                    for (int p = 0; p < 3; ++p)
+                        for (int t = 0; t < NT; ++t)
+                            produce_gemm(P, P.lay.fwd[P_T0], ring, bar_full, bar_empty, pcount, 4 * p, min(4 * p + 4, kEncChunks));
+                    for (int l = 1; l < 5; ++l)
                         for (int t = 0; t < NT; ++t)
                             produce_gemm(P, P.lay.fwd[P_T0 + l], ring, bar_full, bar_empty, pcount, 0, P.lay.fwd[P_T0 + l].n_chunks);
                 } else if (MODE == HEAD_FWD) {

@@ -26,12 +26,17 @@ struct ChainParams {
     const float* dovals;         // [2][B][V][4]
     const uint32_t* maxabs;      // bits of max |d(pre-tanh)|
     unsigned long long* dbg;     // optional timeline of CTA 0's first item (findb200_chain_trace; diagnostics only)
+    int dbg_flags;               // bit 0: per-chunk %globaltimer stamps (slow); cycle accounting of the issuing thread is always on with dbg
 };
 
 extern unsigned long long* g_chain_dbg;
+extern int g_chain_dbg_flags;
 
 
 int launch_chain(int mode, int nt, const ChainParams& P, int sms, cudaStream_t st);
+// CTA-pair build (field_chain2.cu, tcgen05 cta_group::2): chooses its own tiles-per-item and item count from the shapes in P
+int launch_chain2(int mode, const ChainParams& P, int sms, cudaStream_t st);
+bool chain_pairs_enabled();      // FINDB200_CHAIN=1 selects the single-CTA kernels of field_chain.cu (A/B)
 
 }  // namespace field
 }  // namespace fb

@@ -161,6 +161,105 @@ umma_selftest2_kernel(int mode, const uint8_t* __restrict__ a_img, const uint8_t
     if (warp == 0) tmem_dealloc2(tmem, 256);
 }
 
+// ---- tensor-pipe rate probe -------------------------------------------------------------------------------------------
+// How many SM cycles does ONE K = 16 MMA of the shapes the chain kernels issue really take, with nothing else running on
+// the SM?  Operands are whatever bytes sit in shared memory / TMEM (values are irrelevant for timing).
+//   mode 0: cta_group::1, M = 128, N = 256, A and B from shared memory (SS)      — field_chain.cu
+//   mode 1: cta_group::1, M = 128, N = 128, SS
+//   mode 2: cta_group::2, M = 256, N = 256, SS (each CTA: 128 rows of A, 128 rows of B) — field_chain2.cu
+//   mode 3: cta_group::1, M = 128, N = 256, A from TMEM (TS), B from shared memory
+//   mode 4: cta_group::2, M = 256, N = 256, TS
+// out[0] = cycles (clock64) from the first issue to the commit arriving, out[1] = MMAs issued.
+template <int CG>
+__global__ void __launch_bounds__(128) umma_rate_kernel(int mode, int iters, int flags, const uint8_t* __restrict__ gsrc,
+                                                        unsigned long long* __restrict__ out) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+    uint8_t* sA = smem;                 // 64 KB
+    uint8_t* sB = smem + 65536;         // 128 KB (CG = 1) / 64 KB (CG = 2)
+    // flags (what the chain kernels do around the MMAs): 1 = tcgen05.commit to a ring barrier after every 4 MMAs, 2 = tcgen05.fence
+    // ::after_thread_sync before every 4, 4 = an (already satisfied) mbarrier wait before every 4, 8 = a second warp streams 16 KB
+    // bulk copies from global memory into a spare shared-memory ring all the while, 16 = two warps keep writing shared memory
+    __shared__ __align__(8) uint64_t bar_mma, bar_ring[8], bar_done_dummy, bar_bg[4];
+    __shared__ uint32_t tmem_base_s;
+    __shared__ volatile int stop_flag;
+    const int tid = threadIdx.x, warp = tid >> 5;
+    const uint32_t rank = CG == 2 ? cluster_ctarank() : 0u;
+    for (int i = tid; i < (65536 + (CG == 2 ? 65536 : 131072)) / 4; i += 128) reinterpret_cast<uint32_t*>(smem)[i] = 0x3c003c00u;
+    if (tid == 0) {
+        mbar_init(&bar_mma, 1); mbar_init(&bar_done_dummy, 1);
+        for (int i = 0; i < 8; ++i) mbar_init(&bar_ring[i], 1);
+        for (int i = 0; i < 4; ++i) mbar_init(&bar_bg[i], 1);
+        stop_flag = 0;
+        fence_barrier_init();
+    }
+    if (warp == 0) { if (CG == 2) tmem_alloc2(&tmem_base_s, 512); else tmem_alloc(&tmem_base_s, 512); }
+    fence_proxy_async();
+    tc_fence_before();
+    if (CG == 2) cluster_sync_all(); else __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = tmem_base_s;
+    const bool ts = mode >= 3;
+    const int N = mode == 1 ? 128 : 256;
+    if (tid == 0 && rank == 0) {
+        const uint32_t idesc = umma_idesc_f16(CG == 2 ? 256 : 128, N, false, false);
+        const long long t0 = clock64();
+        unsigned long long n = 0;
+        for (int it = 0; it < iters; ++it)
+            for (int kc = 0; kc < 4; ++kc) {
+                if (flags & 4) mbar_wait(&bar_done_dummy, 1);          // fresh barrier, parity 1: satisfied at once
+                if (flags & 2) tc_fence_after();
+                for (int k16 = 0; k16 < 4; ++k16, ++n) {
+                    const uint64_t ad = umma_desc(smem_u32(sA) + kc * 16384 + k16 * 32, 16, 1024);
+                    const uint64_t bd = umma_desc(smem_u32(sB) + kc * (CG == 2 ? 16384 : 32768) + k16 * 32, 16, 1024);
+                    if (!ts) {
+                        if (CG == 2) umma2_f16(tmem, ad, bd, idesc, 1u); else umma_f16(tmem, ad, bd, idesc, 1u);
+                    } else {
+                        const uint32_t a_t = tmem + 256 + (uint32_t)(kc * 4 + k16) * 8;     // [128 lanes x 16 fp16] = 8 columns
+                        if (CG == 2)
+                            asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+                                         "tcgen05.mma.cta_group::2.kind::f16 [%0], [%1], %2, %3, p;\n\t}"
+                                         ::"r"(tmem), "r"(a_t), "l"(bd), "r"(idesc), "r"(1u) : "memory");
+                        else
+                            asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+                                         "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}"
+                                         ::"r"(tmem), "r"(a_t), "l"(bd), "r"(idesc), "r"(1u) : "memory");
+                    }
+                }
+                if (flags & 1) { if (CG == 2) umma2_commit_mc(&bar_ring[(it * 4 + kc) & 7], 3); else umma_commit(&bar_ring[(it * 4 + kc) & 7]); }
+            }
+        if (CG == 2) umma2_commit_mc(&bar_mma, 3); else umma_commit(&bar_mma);
+        mbar_wait(&bar_mma, 0);
+        out[0] = (unsigned long long)(clock64() - t0);
+        out[1] = n;
+        stop_flag = 1;
+    } else if (warp == 1 && (tid & 31) == 0 && (flags & 8) && gsrc && CG == 2) {
+        // background weight stream: 16 KB bulk copies into the upper 64 KB of the B region (unused by the pair's MMAs)
+        uint8_t* bg = sB + 65536;
+        uint32_t i = 0;
+        while (!stop_flag && i < (1u << 20)) {          // bounded: a protocol slip must not hang the GPU
+            const uint32_t sl = i & 3, use = i >> 2;
+            if (use > 0) mbar_wait(&bar_bg[sl], (use - 1) & 1);
+            mbar_expect_tx(&bar_bg[sl], 16384u);
+            bulk_g2s(bg + sl * 16384, gsrc + (size_t)((i * 2 + rank) & 63) * 16384, 16384u, &bar_bg[sl]);
+            ++i;
+        }
+        for (uint32_t k = (i >= 4 ? i - 4 : 0); k < i; ++k) mbar_wait(&bar_bg[k & 3], (k >> 2) & 1);
+    } else if (warp >= 2 && (flags & 16) && CG == 2) {
+        uint8_t* bg = sB + 65536;
+        uint32_t i = 0;
+        while (!stop_flag && i < (1u << 24)) {
+            *reinterpret_cast<uint4*>(bg + (((tid - 64) * 16 + i * 1024) & 65535)) = make_uint4(i, i, i, i);
+            ++i;
+        }
+    }
+    __syncwarp();
+    if (CG == 2 && !(tid == 0 && rank == 0)) { if (tid == 0) { mbar_wait(&bar_mma, 0); stop_flag = 1; } }   // the peer's own flag
+    tc_fence_before();
+    if (CG == 2) cluster_sync_all(); else __syncthreads();
+    if (warp == 0) { if (CG == 2) tmem_dealloc2(tmem, 512); else tmem_dealloc(tmem, 512); }
+}
+
 }  // namespace fb
 
 extern "C" int findb200_umma_selftest(int mode, const void* a_img, const void* b_img, float* d_out, void* stream) {
@@ -176,6 +275,28 @@ extern "C" int findb200_umma_selftest(int mode, const void* a_img, const void* b
     const int smem = 65536 + 131072 + 1024;
     FB_CUDA(cudaFuncSetAttribute(umma_selftest_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     umma_selftest_kernel<<<1, 128, smem, (cudaStream_t)stream>>>(mode, (const __half*)a_img, (const __half*)b_img, d_out);
+    FB_CUDA(cudaGetLastError());
+    return 0;
+}
+
+extern "C" int findb200_umma_rate(int mode, int iters, int flags, const void* gsrc_1mb, unsigned long long* out2_dev, void* stream) {
+    using namespace fb;
+    FB_REQUIRE(mode >= 0 && mode <= 4 && iters >= 1 && out2_dev, FINDB200_ERR_ARG, "umma_rate: mode 0..4, iters >= 1");
+    const bool pair = (mode == 2 || mode == 4);
+    const int smem = 65536 + 131072 + 1024;
+    if (pair) {
+        FB_CUDA(cudaFuncSetAttribute(umma_rate_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3(2); cfg.blockDim = dim3(128); cfg.dynamicSmemBytes = smem; cfg.stream = (cudaStream_t)stream;
+        cudaLaunchAttribute at[1];
+        at[0].id = cudaLaunchAttributeClusterDimension;
+        at[0].val.clusterDim.x = 2; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+        cfg.attrs = at; cfg.numAttrs = 1;
+        FB_CUDA(cudaLaunchKernelEx(&cfg, umma_rate_kernel<2>, mode, iters, flags, (const uint8_t*)gsrc_1mb, out2_dev));
+    } else {
+        FB_CUDA(cudaFuncSetAttribute(umma_rate_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        umma_rate_kernel<1><<<1, 128, smem, (cudaStream_t)stream>>>(mode, iters, flags, (const uint8_t*)gsrc_1mb, out2_dev);
+    }
     FB_CUDA(cudaGetLastError());
     return 0;
 }

@@ -316,6 +316,12 @@ int findb200_scatter_rows_multi(const findb200_scatter_job* jobs, int n_jobs, co
  * ([256][256] for modes 2 / 3).
  * ------------------------------------------------------------------------------------------------------ */
 int findb200_umma_selftest(int mode, const void* a_img, const void* b_img, float* d_out, void* stream);
+/* Tensor-pipe rate probe (csrc/umma_selftest.cu): one CTA (pair) issues iters x 16 K = 16 MMAs of the chain kernels' shapes
+ * back to back; out2_dev[0] = SM cycles from first issue to completion, [1] = MMAs issued.  mode 0: cta_group::1 M128 N256
+ * operands from shared memory, 1: N128, 2: cta_group::2 M256 N256, 3 / 4: as 0 / 2 with A from TMEM.  flags add what the chain
+ * kernels do around the MMAs (1 commit per 4 MMAs, 2 tcgen05 fence per 4, 4 mbarrier wait per 4, 8 background bulk-copy stream from
+ * gsrc_1mb (>= 1 MiB, pair modes), 16 background shared-memory writers). */
+int findb200_umma_rate(int mode, int iters, int flags, const void* gsrc_1mb, unsigned long long* out2_dev, void* stream);
 
 /* Launch profiler used by bench.py for the live roofline: after findb200_profile_enable(1) every kernel launch of the
  * library is bracketed by CUDA events on its launching stream (do not enable during CUDA-graph capture);

@@ -166,6 +166,12 @@ def test_field_many_tiles_multi_wave():
     _oracle_case(B=24, V=1500, shared=True, seed=15)
 
 
+def test_field_many_trunk_tiles_two_per_cta():
+    # per-foot points with more trunk tiles than 2 x SMs: the trunk kernels run TWO tiles per CTA (pair), which changes the
+    # order in which base.0's nine weight chunks travel through the ring
+    _oracle_case(B=8, V=4800, shared=False, seed=16)
+
+
 def test_field_no_cpu_fallback():
     from find_b200.field_ops import field_apply
     p = fo.random_params(0)
