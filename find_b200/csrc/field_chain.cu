@@ -273,7 +273,8 @@ __global__ void __launch_bounds__(64 + 128 * NT, 1) chain_kernel(const __grid_co
     uint32_t& tmem_base_s = *reinterpret_cast<uint32_t*>(bar_act_free + NT);
     if ((smem_u32(smem) & 1023u) != 0u) __trap();
 
-    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int tid = threadIdx.x, lane = tid & 31;
+    const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);    // warp-uniform: keeps the issue path in uniform registers (see field_chain2.cu)
     if (tid == 0) {
         for (int s = 0; s < kRing; ++s) { mbar_init(&bar_full[s], 1); mbar_init(&bar_empty[s], 1); }
         for (int t = 0; t < NT; ++t) {
@@ -306,7 +307,7 @@ __global__ void __launch_bounds__(64 + 128 * NT, 1) chain_kernel(const __grid_co
 
     if (warp == 0) {
         // ===================================== producer ===========================================
-        if (lane == 0) {
+        if (elect_one()) {
             uint32_t pcount = 0, icount = 0;
             uint32_t n_free[NT];
             for (int t = 0; t < NT; ++t) n_free[t] = 0;
@@ -359,7 +360,7 @@ __global__ void __launch_bounds__(64 + 128 * NT, 1) chain_kernel(const __grid_co
         }
     } else if (warp == 1) {
         // ===================================== MMA issuer =========================================
-        if (lane == 0) {
+        if (elect_one()) {
             uint32_t ccount = 0, icount = 0;
             uint32_t n_act[NT], n_in[NT];
             for (int t = 0; t < NT; ++t) n_act[t] = n_in[t] = 0;

@@ -200,7 +200,10 @@ __global__ void __launch_bounds__(kThreads2, 1) chain2_kernel(const __grid_const
     uint32_t& ready_cnt = *(&tmem_base_s + 1);          // events (landings of both CTAs) the scout has seen complete
     if ((smem_u32(smem) & 1023u) != 0u) __trap();
 
-    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int tid = threadIdx.x, lane = tid & 31;
+    // warp index as a warp-UNIFORM value: with it and elect.sync as the single-thread guard ptxas keeps the issue path (descriptors,
+    // loop counters) in uniform registers — UTCHMMA back to back — instead of wrapping every MMA in an R2UR waterfall loop
+    const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);
     const uint32_t rank = cluster_ctarank();
     const bool leader_cta = rank == 0;
     constexpr bool kTrunk = (MODE == TRUNK_FWD || MODE == TRUNK_BWD);
@@ -246,7 +249,7 @@ __global__ void __launch_bounds__(kThreads2, 1) chain2_kernel(const __grid_const
 
     if (warp == 0) {
         // ===================================== producer (both CTAs: own halves / own tiles) ========================
-        if (lane == 0) {
+        if (elect_one()) {
             uint32_t pcount = 0, icount = 0;
             uint32_t n_free[NT];
             for (int t = 0; t < NT; ++t) n_free[t] = 0;
@@ -315,7 +318,7 @@ __global__ void __launch_bounds__(kThreads2, 1) chain2_kernel(const __grid_const
         //           mbarrier wait costs ~170-200 cycles even when already satisfied and the issue path is the kernel's critical
         //           path (measured: 363 of 1256 cycles per weight chunk went to the two waits) — it only reads `ready_cnt`
         const bool is_issuer = warp == 2 + kEpiWarps;
-        if (lane == 0 && (leader_cta || !is_issuer)) {
+        if ((leader_cta || !is_issuer) && elect_one()) {
             uint32_t ccount = 0, icount = 0, ev = 0;
             uint32_t n_act[NT], n_in[NT];
             for (int t = 0; t < NT; ++t) n_act[t] = n_in[t] = 0;
@@ -376,6 +379,7 @@ __global__ void __launch_bounds__(kThreads2, 1) chain2_kernel(const __grid_const
                     const uint32_t s = ccount % kRing2, use = ccount / kRing2;
                     if (is_issuer) {
                         await_event();
+                        stamp(P, MODE == HEAD_FWD && cluster_id == 0 && ccount < 48 && (P.dbg_flags & 1), 208 + (int)ccount);
                         const long long tc = prof ? clock64() : 0;
                         for (int sub = 0; sub < grp && c + sub < c1; ++sub) {
                             const int cc = c + sub;
@@ -389,8 +393,10 @@ __global__ void __launch_bounds__(kThreads2, 1) chain2_kernel(const __grid_const
                         umma2_commit_mc(&bar_empty[s], 3);
                         if (prof) cy_issue += clock64() - tc;
                     } else {
+                        const bool tr = MODE == HEAD_FWD && cluster_id == 0 && ccount < 48 && (P.dbg_flags & 1);
                         mbar_wait(&bar_full[s], use & 1);
-                        if (leader_cta) { mbar_wait(&bar_peer_full[s], use & 1); publish_event(); }
+                        stamp(P, tr, (leader_cta ? 112 : 368) + (int)ccount);
+                        if (leader_cta) { mbar_wait(&bar_peer_full[s], use & 1); stamp(P, tr, 160 + (int)ccount); publish_event(); }
                         else mbar_arrive_cluster(r_peer_full + s * 8u);
                     }
                     ++ccount;

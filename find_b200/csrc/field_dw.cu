@@ -24,7 +24,8 @@ __global__ void __launch_bounds__(kDwThreads, 1) dw_kernel(const __grid_constant
     __shared__ __align__(8) uint64_t bar_full[kDwStages], bar_empty[kDwStages], bar_done;
     __shared__ uint32_t tmem_base_s;
 
-    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int tid = threadIdx.x, lane = tid & 31;
+    const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);    // warp-uniform: the MMA issue path stays in uniform registers
     if (tid == 0) {
         for (int s = 0; s < kDwStages; ++s) { mbar_init(&bar_full[s], 1); mbar_init(&bar_empty[s], 1 + 128); }
         mbar_init(&bar_done, 1);
@@ -68,7 +69,7 @@ __global__ void __launch_bounds__(kDwThreads, 1) dw_kernel(const __grid_constant
         }
     } else if (warp == 1) {
         // ---- MMA issuer ------------------------------------------------------------------------------------------
-        if (lane == 0) {
+        if (elect_one()) {
             const uint32_t idesc = umma_idesc_f16(128, G.N, true, true);
             const uint32_t a_lbo = G.a_imgs > 1 ? 8192u : 0u;
             for (int i = 0; i < n_stages_total; ++i) {

@@ -183,7 +183,8 @@ __global__ void __launch_bounds__(128) umma_rate_kernel(int mode, int iters, int
     __shared__ __align__(8) uint64_t bar_mma, bar_ring[8], bar_done_dummy, bar_bg[4];
     __shared__ uint32_t tmem_base_s;
     __shared__ volatile int stop_flag;
-    const int tid = threadIdx.x, warp = tid >> 5;
+    const int tid = threadIdx.x;
+    const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);     // warp-uniform (uniform-register issue path, as in the chain kernels)
     const uint32_t rank = CG == 2 ? cluster_ctarank() : 0u;
     for (int i = tid; i < (65536 + (CG == 2 ? 65536 : 131072)) / 4; i += 128) reinterpret_cast<uint32_t*>(smem)[i] = 0x3c003c00u;
     if (tid == 0) {
@@ -201,7 +202,8 @@ __global__ void __launch_bounds__(128) umma_rate_kernel(int mode, int iters, int
     const uint32_t tmem = tmem_base_s;
     const bool ts = mode >= 3;
     const int N = mode == 1 ? 128 : 256;
-    if (tid == 0 && rank == 0) {
+    if (warp == 0 && rank == 0) {
+      if (elect_one()) {
         const uint32_t idesc = umma_idesc_f16(CG == 2 ? 256 : 128, N, false, false);
         const long long t0 = clock64();
         unsigned long long n = 0;
@@ -233,6 +235,7 @@ __global__ void __launch_bounds__(128) umma_rate_kernel(int mode, int iters, int
         out[0] = (unsigned long long)(clock64() - t0);
         out[1] = n;
         stop_flag = 1;
+      }
     } else if (warp == 1 && (tid & 31) == 0 && (flags & 8) && gsrc && CG == 2) {
         // background weight stream: 16 KB bulk copies into the upper 64 KB of the B region (unused by the pair's MMAs)
         uint8_t* bg = sB + 65536;

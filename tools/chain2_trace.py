@@ -56,4 +56,5 @@ print("leader producer, half-chunk issued :", " ".join(f"{r(64+i):.2f}" for i in
 print("peer   producer, half-chunk issued :", " ".join(f"{r(320+i):.2f}" for i in range(n)))
 print("leader MMA, own half landed        :", " ".join(f"{r(112+i):.2f}" for i in range(n)))
 print("peer relay, its half landed        :", " ".join(f"{r(368+i):.2f}" for i in range(n)))
-print("leader MMA, peer half known landed :", " ".join(f"{r(160+i):.2f}" for i in range(n)))
+print("leader scout, peer half known landed:", " ".join(f"{r(160+i):.2f}" for i in range(n)))
+print("leader issuer, chunk event seen     :", " ".join(f"{r(208+i):.2f}" for i in range(n)))
