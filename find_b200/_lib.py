@@ -46,6 +46,7 @@ SIGNATURES = {
     "findb200_profile_read": (c_int, [c_char_p, c_size_t]),
     "findb200_umma_selftest": (c_int, [c_int, c_void_p, c_void_p, c_void_p, c_void_p]),
     "findb200_umma_rate": (c_int, [c_int, c_int, c_int, c_void_p, c_void_p, c_void_p]),
+    "findb200_sync_probe": (c_int, [c_int, c_int, c_void_p, c_void_p]),
     "findb200_fp32_peak": (c_int, [c_int, c_int, c_int, c_void_p, c_void_p]),
     "findb200_l2_stream": (c_int, [c_void_p, c_size_t] + [c_int] * 5 + [c_void_p, c_void_p]),
     "findb200_set_knn_mode": (c_int, [c_int, c_int]),

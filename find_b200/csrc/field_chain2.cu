@@ -29,6 +29,8 @@
 //   bar_act_ready[t] leader     both CTAs' epilogues have written activation tile t (count 2, one elected arrive per CTA)
 //   bar_acc_ready[t] both       accumulator t is complete (commit multicast)
 //   bar_act_free[t]  local      activation buffer / accumulator t may be reused by the next item
+#include <type_traits>
+
 #include "field.cuh"
 #include "field_chain_params.cuh"
 
@@ -177,9 +179,13 @@ FB_DEVINL void bulk_wait_read(int pending) {       // this thread's bulk stores:
     else asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
 }
 
-template <int MODE, int NT>
+// DIAG = true compiles the %globaltimer stamps and the timing-experiment switches in (findb200_chain_trace); the production
+// instantiation carries none of them.
+template <int MODE, int NT, bool DIAG>
 __global__ void __launch_bounds__(kThreads2, 1) chain2_kernel(const __grid_constant__ ChainParams P) {
     fb::pdl_wait_trigger();
+    auto stamp = [](const ChainParams& Pp, bool on, int slot) { if constexpr (DIAG) c2::stamp(Pp, on, slot); };
+    const int dflags = DIAG ? P.dbg_flags : 0;
     if (threadIdx.x == 0 && blockIdx.x == 0) stamp(P, true, 500 + MODE * 2);
     // dynamic shared memory only, identical carve-up in both CTAs of the pair:
     // [NT activation tiles 64 KB][ring 6 x 16 KB][NT x 256 fp32 bias][mbarriers][tmem base]
@@ -260,7 +266,8 @@ __global__ void __launch_bounds__(kThreads2, 1) chain2_kernel(const __grid_const
                     const uint32_t s = pcount % kRing2, use = pcount / kRing2;
                     const int n = min(grp, c1 - c);
                     if (use > 0) mbar_wait_cluster(&bar_empty[s], (use - 1) & 1);
-                    stamp(P, MODE == HEAD_FWD && cluster_id == 0 && pcount < 48 && (P.dbg_flags & 1), (leader_cta ? 64 : 320) + (int)pcount);
+                    stamp(P, MODE == HEAD_FWD && cluster_id == 0 && pcount < 48 && (dflags & 1), (leader_cta ? 64 : 320) + (int)pcount);
+                    if (dflags & 256) { mbar_arrive(&bar_full[s]); ++pcount; continue; }     // timing experiment: no weight traffic
                     mbar_expect_tx(&bar_full[s], (uint32_t)n * half);
                     for (int q = 0; q < n; ++q)
                         bulk_g2s(ring + s * kSlotBytes + q * half, P.wpack + g.off + (size_t)(c + q) * g.chunk_bytes + rank * half, half,
@@ -314,146 +321,193 @@ __global__ void __launch_bounds__(kThreads2, 1) chain2_kernel(const __grid_const
         //   scout   (leader CTA, warp 1): waits for "input tile landed" / "weight half landed" of BOTH CTAs and publishes the number
         //           of events that are complete in `ready_cnt` (shared memory)
         //   relay   (peer CTA, warp 1):   waits for its own CTA's landings and forwards them to the leader's mbarriers
-        //   issuer  (leader CTA, warp 10): tcgen05.mma.cta_group::2 + commits; it never waits on a landing mbarrier itself — an
-        //           mbarrier wait costs ~170-200 cycles even when already satisfied and the issue path is the kernel's critical
-        //           path (measured: 363 of 1256 cycles per weight chunk went to the two waits) — it only reads `ready_cnt`
+        //   issuer  (leader CTA, warp 10): tcgen05.mma.cta_group::2 + commits; it never waits on a landing mbarrier itself, it only
+        //           polls `ready_cnt`.
+        // The issuer is the kernel's critical path, and one warp alone pays ~20 cycles for every taken branch and ~40 for every
+        // dependent constant-bank load, so its code is straight-line: layer shapes are compile-time (they mirror make_layout() in
+        // field.cu: [256 x 64] chunks, the N = 16 output layer as four 2 KB sub-chunks in one slot), every loop is unrolled, the
+        // descriptors are a base plus an immediate, the role is a template argument, and diagnostics exist only in the DIAG build.
         const bool is_issuer = warp == 2 + kEpiWarps;
         if ((leader_cta || !is_issuer) && elect_one()) {
-            uint32_t ccount = 0, icount = 0, ev = 0;
-            uint32_t n_act[NT], n_in[NT];
-            for (int t = 0; t < NT; ++t) n_act[t] = n_in[t] = 0;
             const uint32_t act_s = smem_u32(act), ring_s = smem_u32(ring);
             const uint32_t ready_s = smem_u32(&ready_cnt);
-            // diagnostics: where the issuing thread's cycles go (written to P.dbg[448..] by cluster 0's leader at the end)
-            const bool prof_total = P.dbg != nullptr && cluster_id == 0 && leader_cta && is_issuer;
-            const bool prof = prof_total && !(P.dbg_flags & 64);      // 64: total only (the per-chunk clock reads cost cycles)
-            const bool free_run = P.dbg != nullptr && (P.dbg_flags & 32);   // timing experiment: the issuer waits for nothing
-            long long cy_ready = 0, cy_issue = 0, cy_act = 0, cy_total0 = prof_total ? clock64() : 0;
+            const uint32_t full_s = smem_u32(bar_full), pfull_s = smem_u32(bar_peer_full), empty_s = smem_u32(bar_empty);
+            const uint32_t in_s = smem_u32(bar_in_full), pin_s = smem_u32(bar_peer_in), actr_s = smem_u32(bar_act_ready);
+            const uint32_t accr_s = smem_u32(bar_acc_ready), actf_s = smem_u32(bar_act_free);
             // leader's mbarriers as seen from the peer
-            const uint32_t r_peer_full = mapa_u32(smem_u32(bar_peer_full), 0), r_peer_in = mapa_u32(smem_u32(bar_peer_in), 0);
-            auto publish_event = [&]() {          // scout
-                ++ev;
-                asm volatile("st.volatile.shared.u32 [%0], %1;" ::"r"(ready_s), "r"(ev) : "memory");
-            };
-            auto await_event = [&]() {            // issuer
-                ++ev;
-                const long long c0 = prof ? clock64() : 0;
-                uint32_t v;
-                long long t0 = 0;
-                for (;;) {
-                    asm volatile("ld.volatile.shared.u32 %0, [%1];" : "=r"(v) : "r"(ready_s) : "memory");
-                    if ((int32_t)(v - ev) >= 0 || free_run) break;
-                    if (t0 == 0) t0 = clock64();
-                    else if (clock64() - t0 > FB_WAIT_TIMEOUT_CYCLES) {
-                        printf("find_b200: chain2 issuer timeout block %d event %u (ready %u)\n", (int)blockIdx.x, ev, v);
+            const uint32_t r_peer_full = mapa_u32(pfull_s, 0), r_peer_in = mapa_u32(pin_s, 0);
+            auto wait_bar = [&](uint32_t bar_addr, uint32_t parity, int role, uint32_t ev_now) {   // bounded spin, no clock reads
+                uint32_t ok, spins = 0;
+                do {
+                    asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                                 : "=r"(ok) : "r"(bar_addr), "r"(parity) : "memory");
+                    if (!ok && ++spins > (1u << 22)) {
+                        printf("find_b200: chain2 issue-path wait timeout mode %d block %d role %d event %u bar+%u parity %u\n", MODE, (int)blockIdx.x, role, ev_now,
+                               bar_addr - full_s, parity);
                         __trap();
                     }
-                }
-                tc_fence_after();
-                if (prof) cy_ready += clock64() - c0;
+                } while (!ok);
             };
-            auto wait_act = [&](int t) {
-                if (is_issuer) {
-                    const long long c0 = prof ? clock64() : 0;
-                    if (!free_run) mbar_wait(&bar_act_ready[t], n_act[t] & 1);
+            auto commit_to = [&](uint32_t bar_addr) {
+                asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+                             ::"r"(bar_addr), "h"((uint16_t)3) : "memory");
+            };
+            auto walk = [&](auto role_tag) {
+                constexpr int ROLE = decltype(role_tag)::value;            // 0 issuer, 1 scout, 2 relay
+                uint32_t slot = 0, sphase = 0, ev = 0;
+                uint32_t act_ph[NT], in_ph[NT];
+#pragma unroll
+                for (int t = 0; t < NT; ++t) act_ph[t] = in_ph[t] = 0;
+                const uint64_t adesc0 = umma_desc(act_s, 16, 1024), bdesc0 = umma_desc(ring_s, 16, 1024);
+                constexpr uint32_t idesc256 = umma_idesc_f16(256, 256, false, false), idesc16 = umma_idesc_f16(256, 16, false, false);
+                long long cy_total0 = 0;
+                if constexpr (DIAG) cy_total0 = clock64();
+                // one landing event (a ring slot, or an input tile); after it `slot` still names the slot
+                auto event_seen = [&]() {                                  // issuer: the scout has published event `ev`
+                    ++ev;
+                    uint32_t v, spins = 0;
+                    for (;;) {
+                        asm volatile("ld.volatile.shared.u32 %0, [%1];" : "=r"(v) : "r"(ready_s) : "memory");
+                        if ((int32_t)(v - ev) >= 0) break;
+                        if (++spins > (1u << 23)) { printf("find_b200: chain2 issuer timeout mode %d block %d event %u (ready %u)\n", MODE, (int)blockIdx.x, ev, v); __trap(); }
+                    }
                     tc_fence_after();
-                    if (prof) cy_act += clock64() - c0;
-                }
-                ++n_act[t];
-            };
-            auto wait_in = [&](int t) {
-                if (is_issuer) await_event();
-                else {
-                    mbar_wait(&bar_in_full[t], n_in[t] & 1);
-                    if (leader_cta) { mbar_wait(&bar_peer_in[t], n_in[t] & 1); publish_event(); }
-                    else mbar_arrive_cluster(r_peer_in + (uint32_t)t * 8u);
-                }
-                ++n_in[t];
-            };
-            // D[tile t] (+)= A[tile t] * W for chunks [c0, c1)
-            auto gemm = [&](int t, const GemmW& g, int c0, int c1, bool acc_init) {
-                const uint32_t idesc = umma_idesc_f16(256, g.N, false, false);
-                const int grp = g.group ? g.group : 1;
-                const uint32_t half = g.chunk_bytes >> 1;
-                for (int c = c0; c < c1; c += grp) {
-                    const uint32_t s = ccount % kRing2, use = ccount / kRing2;
-                    if (is_issuer) {
-                        await_event();
-                        stamp(P, MODE == HEAD_FWD && cluster_id == 0 && ccount < 48 && (P.dbg_flags & 1), 208 + (int)ccount);
-                        const long long tc = prof ? clock64() : 0;
-                        for (int sub = 0; sub < grp && c + sub < c1; ++sub) {
-                            const int cc = c + sub;
-                            const int nk = (cc == g.n_chunks - 1) ? g.k16_last : 4;
-                            for (int k = 0; k < nk; ++k) {
-                                const uint64_t ad = umma_desc(act_s + t * kTileBytes + (cc - c0) * kImgBytes + k * 32, 16, 1024);
-                                const uint64_t bd = umma_desc(ring_s + s * kSlotBytes + sub * half + k * 32, 16, 1024);
-                                umma2_f16(tmem + t * 256, ad, bd, idesc, (acc_init || cc > c0 || k > 0) ? 1u : 0u);
+                };
+                auto publish_event = [&]() {                               // scout
+                    ++ev;
+                    asm volatile("st.volatile.shared.u32 [%0], %1;" ::"r"(ready_s), "r"(ev) : "memory");
+                };
+                auto slot_landed = [&]() {
+                    if constexpr (ROLE == 0) event_seen();
+                    else {
+                        wait_bar(full_s + slot * 8u, sphase, ROLE, ev);
+                        if constexpr (ROLE == 1) { wait_bar(pfull_s + slot * 8u, sphase, ROLE, ev); publish_event(); }
+                        else mbar_arrive_cluster(r_peer_full + slot * 8u);
+                    }
+                };
+                auto next_slot = [&]() { if (++slot == (uint32_t)kRing2) { slot = 0; sphase ^= 1u; } };
+                auto wait_in = [&](int t) {
+                    if constexpr (ROLE == 0) event_seen();
+                    else {
+                        wait_bar(in_s + (uint32_t)t * 8u, in_ph[t], ROLE, ev);
+                        if constexpr (ROLE == 1) { wait_bar(pin_s + (uint32_t)t * 8u, in_ph[t], ROLE, ev); publish_event(); }
+                        else mbar_arrive_cluster(r_peer_in + (uint32_t)t * 8u);
+                    }
+                    in_ph[t] ^= 1u;
+                };
+                auto wait_act = [&](int t) {
+                    if constexpr (ROLE == 0) { wait_bar(actr_s + (uint32_t)t * 8u, act_ph[t], ROLE, ev); tc_fence_after(); }
+                    act_ph[t] ^= 1u;
+                };
+                auto commit = [&](uint32_t bar_addr) { if constexpr (ROLE == 0) commit_to(bar_addr); };
+                // D[tile t] (+)= A[tile t, images 0..NCH-1] * W chunks: NCH ring slots of one [256 n x 64 k] chunk (halves), NKLAST k-steps
+                // in the last one
+                auto block = [&](int t, auto nch_c, auto nklast_c, bool acc) {
+                    constexpr int NCH = decltype(nch_c)::value, NKLAST = decltype(nklast_c)::value;
+#pragma unroll
+                    for (int c = 0; c < NCH; ++c) {
+                        slot_landed();
+                        if constexpr (ROLE == 0) {
+                            const uint64_t ad = adesc0 + (uint64_t)(((uint32_t)t * kTileBytes + (uint32_t)c * kImgBytes) >> 4);
+                            const uint64_t bd = bdesc0 + (uint64_t)((slot * (uint32_t)kSlotBytes) >> 4);
+#pragma unroll
+                            for (int k = 0; k < ((c == NCH - 1) ? NKLAST : 4); ++k)
+                                umma2_f16(tmem + (uint32_t)t * 256u, ad + (uint64_t)(k * 2), bd + (uint64_t)(k * 2), idesc256, (acc || c > 0 || k > 0) ? 1u : 0u);
+                            commit_to(empty_s + slot * 8u);
+                        }
+                        next_slot();
+                    }
+                };
+                // the 256 -> 3 output layer: four [16 n x 64 k] sub-chunks (1 KB halves) in ONE slot, N = 16
+                auto block_out = [&](int t) {
+                    slot_landed();
+                    if constexpr (ROLE == 0) {
+                        const uint64_t ad = adesc0 + (uint64_t)(((uint32_t)t * kTileBytes) >> 4);
+                        const uint64_t bd = bdesc0 + (uint64_t)((slot * (uint32_t)kSlotBytes) >> 4);
+#pragma unroll
+                        for (int sub = 0; sub < 4; ++sub)
+#pragma unroll
+                            for (int k = 0; k < 4; ++k)
+                                umma2_f16(tmem + (uint32_t)t * 256u, ad + (uint64_t)(sub * (kImgBytes >> 4) + k * 2),
+                                          bd + (uint64_t)(sub * ((kWSmallChunkBytes / 2) >> 4) + k * 2), idesc16, (sub > 0 || k > 0) ? 1u : 0u);
+                        commit_to(empty_s + slot * 8u);
+                    }
+                    next_slot();
+                };
+                using I1 = std::integral_constant<int, 1>;
+                using I4 = std::integral_constant<int, 4>;
+                uint32_t icount = 0;
+                for (int it = cluster_id; it < n_items; it += n_clusters, ++icount) {
+                    if constexpr (MODE == TRUNK_FWD) {
+#pragma unroll
+                        for (int p = 0; p < 3; ++p)
+#pragma unroll
+                            for (int j = 0; j < NT; ++j) {
+                                wait_act(j);
+                                if (p < 2) block(j, I4{}, I4{}, p > 0); else block(j, I1{}, I1{}, true);
+                                commit(accr_s + j * 8u);
+                            }
+#pragma unroll
+                        for (int l = 1; l < 5; ++l)
+#pragma unroll
+                            for (int j = 0; j < NT; ++j) { wait_act(j); block(j, I4{}, I4{}, false); commit(accr_s + j * 8u); }
+                    } else if constexpr (MODE == HEAD_FWD) {
+#pragma unroll
+                        for (int l = 0; l < 3; ++l)
+#pragma unroll
+                            for (int j = 0; j < NT; ++j) {
+                                if (l == 0) wait_in(j); else wait_act(j);
+                                if constexpr (DIAG) stamp(P, ROLE == 0 && cluster_id == 0 && icount == 0, (l * 2 + j) * 2);
+                                block(j, I4{}, I4{}, false);
+                                commit(accr_s + j * 8u);
+                                if constexpr (DIAG) stamp(P, ROLE == 0 && cluster_id == 0 && icount == 0, (l * 2 + j) * 2 + 1);
+                            }
+#pragma unroll
+                        for (int j = 0; j < NT; ++j) {
+                            wait_act(j);
+                            if constexpr (DIAG) stamp(P, ROLE == 0 && cluster_id == 0 && icount == 0, (6 + j) * 2);
+                            block_out(j);
+                            commit(accr_s + j * 8u);
+                            commit(actf_s + j * 8u);
+                            if constexpr (DIAG) stamp(P, ROLE == 0 && cluster_id == 0 && icount == 0, (6 + j) * 2 + 1);
+                        }
+                    } else if constexpr (MODE == HEAD_BWD) {
+#pragma unroll
+                        for (int j = 0; j < NT; ++j) { wait_act(j); block(j, I1{}, I1{}, false); commit(accr_s + j * 8u); }
+#pragma unroll
+                        for (int l = 2; l >= 1; --l)
+#pragma unroll
+                            for (int j = 0; j < NT; ++j) { wait_act(j); block(j, I4{}, I4{}, false); commit(accr_s + j * 8u); }
+                    } else {
+                        const int last_hd = (P.heads_mask & 2) ? 1 : 0;
+#pragma unroll
+                        for (int hd = 0; hd < 2; ++hd) {
+                            if (!(P.heads_mask & (1 << hd))) continue;
+#pragma unroll
+                            for (int j = 0; j < NT; ++j) {
+                                wait_in(j);
+                                block(j, I4{}, I4{}, hd == 1 && (P.heads_mask & 1));
+                                // not the last head: the buffer goes back to the producers; last: the accumulator to the epilogues
+                                commit((hd == last_hd ? accr_s : actf_s) + j * 8u);
                             }
                         }
-                        umma2_commit_mc(&bar_empty[s], 3);
-                        if (prof) cy_issue += clock64() - tc;
-                    } else {
-                        const bool tr = MODE == HEAD_FWD && cluster_id == 0 && ccount < 48 && (P.dbg_flags & 1);
-                        mbar_wait(&bar_full[s], use & 1);
-                        stamp(P, tr, (leader_cta ? 112 : 368) + (int)ccount);
-                        if (leader_cta) { mbar_wait(&bar_peer_full[s], use & 1); stamp(P, tr, 160 + (int)ccount); publish_event(); }
-                        else mbar_arrive_cluster(r_peer_full + s * 8u);
+#pragma unroll
+                        for (int l = 4; l >= 1; --l)
+#pragma unroll
+                            for (int j = 0; j < NT; ++j) { wait_act(j); block(j, I4{}, I4{}, false); commit(accr_s + j * 8u); }
                     }
-                    ++ccount;
+                }
+                if constexpr (DIAG && ROLE == 0) {
+                    if (P.dbg != nullptr && cluster_id == 0) {
+                        unsigned long long* o = P.dbg + 448 + MODE * 8;
+                        o[0] = (unsigned long long)(clock64() - cy_total0); o[1] = 0ull; o[2] = 0ull; o[3] = 0ull; o[4] = 0ull;
+                        o[5] = ev; o[6] = icount;
+                    }
                 }
             };
-            auto commit = [&](uint64_t* bar) { if (is_issuer) umma2_commit_mc(bar, 3); };
-            for (int it = cluster_id; it < n_items; it += n_clusters, ++icount) {
-                int head, b, t;
-                decode(it, 0, head, b, t);
-                if (MODE == TRUNK_FWD) {
-                    for (int p = 0; p < 3; ++p)
-                        for (int j = 0; j < NT; ++j) {
-                            wait_act(j);
-                            gemm(j, P.lay.fwd[P_T0], 4 * p, min(4 * p + 4, kEncChunks), p > 0);
-                            commit(&bar_acc_ready[j]);
-                        }
-                    for (int l = 1; l < 5; ++l)
-                        for (int j = 0; j < NT; ++j) { wait_act(j); gemm(j, P.lay.fwd[P_T0 + l], 0, 4, false); commit(&bar_acc_ready[j]); }
-                } else if (MODE == HEAD_FWD) {
-                    const int base = head ? P_C1 : P_D1;
-                    for (int l = 0; l < 4; ++l)
-                        for (int j = 0; j < NT; ++j) {
-                            if (l == 0) wait_in(j); else wait_act(j);
-                            stamp(P, is_issuer && cluster_id == 0 && icount == 0, (l * 2 + j) * 2);
-                            gemm(j, P.lay.fwd[base + l], 0, 4, false);
-                            commit(&bar_acc_ready[j]);
-                            if (l == 3) commit(&bar_act_free[j]);
-                            stamp(P, is_issuer && cluster_id == 0 && icount == 0, (l * 2 + j) * 2 + 1);
-                        }
-                } else if (MODE == HEAD_BWD) {
-                    const int base = head ? P_C1 : P_D1;
-                    for (int l = 3; l >= 1; --l)
-                        for (int j = 0; j < NT; ++j) {
-                            wait_act(j);
-                            gemm(j, P.lay.bwd[base + l], 0, P.lay.bwd[base + l].n_chunks, false);
-                            commit(&bar_acc_ready[j]);
-                        }
-                } else {
-                    const int last_hd = (P.heads_mask & 2) ? 1 : 0;
-                    for (int hd = 0; hd < 2; ++hd) {
-                        if (!(P.heads_mask & (1 << hd))) continue;
-                        for (int j = 0; j < NT; ++j) {
-                            wait_in(j);
-                            gemm(j, P.lay.bwd[hd ? P_C1 : P_D1], 0, 4, hd == 1 && (P.heads_mask & 1));
-                            // not the last head: the buffer goes back to the producers; last: the accumulator to the epilogues
-                            commit(hd == last_hd ? &bar_acc_ready[j] : &bar_act_free[j]);
-                        }
-                    }
-                    for (int l = 4; l >= 1; --l)
-                        for (int j = 0; j < NT; ++j) { wait_act(j); gemm(j, P.lay.bwd[P_T0 + l], 0, 4, false); commit(&bar_acc_ready[j]); }
-                }
-            }
-            if (prof_total) {
-                unsigned long long* o = P.dbg + 448 + MODE * 8;
-                o[0] = (unsigned long long)(clock64() - cy_total0); o[1] = (unsigned long long)cy_ready; o[2] = 0ull;
-                o[3] = (unsigned long long)cy_issue; o[4] = (unsigned long long)cy_act; o[5] = ccount; o[6] = icount;
-            }
+            if (is_issuer) walk(std::integral_constant<int, 0>{});
+            else if (leader_cta) walk(std::integral_constant<int, 1>{});
+            else walk(std::integral_constant<int, 2>{});
         }
     } else {
         // ===================================== epilogue warps (8 per CTA, one tile at a time) ==============================
@@ -481,7 +535,7 @@ __global__ void __launch_bounds__(kThreads2, 1) chain2_kernel(const __grid_const
             tc_fence_before();
             named_bar_sync(1, kEpiThreads);          // also: every thread is done with bias_s of this layer
             if (elected) {
-                if (gdst && !(P.dbg_flags & 2)) { bulk_s2g(gdst, act + j * kTileBytes, kTileBytes); bulk_commit(); last_store = j; }
+                if (gdst && !(dflags & 2)) { bulk_s2g(gdst, act + j * kTileBytes, kTileBytes); bulk_commit(); last_store = j; }
                 if (signal) mbar_arrive_cluster(r_act_ready + (uint32_t)j * 8u);
             }
         };
@@ -495,7 +549,7 @@ __global__ void __launch_bounds__(kThreads2, 1) chain2_kernel(const __grid_const
             uint32_t va[32], vb[32], m[4] = {0u, 0u, 0u, 0u};
             // timing experiments only (findb200_chain_trace + FINDB200_CHAIN_DBG; results are garbage): 16 = no TMEM loads,
             // 8 = no conversion / shared-memory stores, 4 = no sign-word stores, 2 = no bulk stores of the tiles
-            const bool no_ld = P.dbg_flags & 16, no_cv = P.dbg_flags & 8;
+            const bool no_ld = dflags & 16, no_cv = dflags & 8;
             if (!no_ld) tmem_ld32(taddr, va);
 #pragma unroll
             for (int cc = 0; cc < 4; cc += 2) {
@@ -504,7 +558,7 @@ __global__ void __launch_bounds__(kThreads2, 1) chain2_kernel(const __grid_const
                 if (!no_ld) { tmem_ld_wait(); if (cc + 2 < 4) tmem_ld32(taddr + (cc + 2) * 32, va); }
                 if (!no_cv) m[cc + 1] = relu_chunk(vb, h * 4 + cc + 1, act_tile, row, bias_s);
             }
-            if (mask_row && !(P.dbg_flags & 4)) reinterpret_cast<uint4*>(mask_row)[h] = make_uint4(m[0], m[1], m[2], m[3]);
+            if (mask_row && !(dflags & 4)) reinterpret_cast<uint4*>(mask_row)[h] = make_uint4(m[0], m[1], m[2], m[3]);
         };
         auto epi_mask = [&](int j, const uint4& mw) {
             const uint32_t taddr = tmem + ((uint32_t)(q * 32) << 16) + j * 256 + h * 128;
@@ -601,8 +655,13 @@ __global__ void __launch_bounds__(kThreads2, 1) chain2_kernel(const __grid_const
                 // output layer: 3 of the 16 accumulator columns; warps of column half j read tile j (half 0 when NT = 1)
                 if (elected) { bulk_wait_read(0); for (int j = 0; j < NT; ++j) mbar_arrive(&bar_act_free[j]); }
                 for (int j = 0; j < NT; ++j) {
+                    // Only the warps that READ accumulator j wait for it.  Nothing gates the next item's first MMA on tile j on the
+                    // other 128 threads (bar_act_free counts the readers), so if they waited here too, a fast issuer could complete
+                    // the NEXT phase of bar_acc_ready[j] before a slow one of them had looked — and it would wait for ever (seen
+                    // once the issue path went straight-line).  They stay in step through the named barrier of the next item's
+                    // first epilogue, which the readers only reach after this phase.
+                    if (h != (j & 1)) { ++n_acc[j]; continue; }
                     wait_acc(j);
-                    if (h != (j & 1)) continue;
                     const uint32_t taddr = tmem + ((uint32_t)(q * 32) << 16) + j * 256;
                     uint32_t v[32];
                     tmem_ld32(taddr, v);
@@ -704,12 +763,12 @@ __global__ void __launch_bounds__(kThreads2, 1) chain2_kernel(const __grid_const
     if (threadIdx.x == 0 && blockIdx.x == 0) stamp(P, true, 500 + MODE * 2 + 1);
 }
 
-template <int MODE, int NT>
+template <int MODE, int NT, bool DIAG>
 static int launch_t(const ChainParams& P, int n_items, int sms, cudaStream_t st) {
     const int smem = NT * kTileBytes + kRing2 * kSlotBytes + NT * kW * 4 + (3 * kRing2 + 5 * NT + 1) * 8;
     static bool attr_set = false;      // one process drives one GPU (one rank per GPU)
     if (!attr_set) {
-        FB_CUDA(cudaFuncSetAttribute(chain2_kernel<MODE, NT>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        FB_CUDA(cudaFuncSetAttribute(chain2_kernel<MODE, NT, DIAG>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
         attr_set = true;
     }
     int clusters = sms / 2;
@@ -726,7 +785,7 @@ static int launch_t(const ChainParams& P, int n_items, int sms, cudaStream_t st)
     at[1].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = at;
     cfg.numAttrs = fb::pdl_enabled() ? 2 : 1;
-    FB_CUDA(cudaLaunchKernelEx(&cfg, chain2_kernel<MODE, NT>, P));
+    FB_CUDA(cudaLaunchKernelEx(&cfg, chain2_kernel<MODE, NT, DIAG>, P));
     FB_CUDA(cudaGetLastError());
     return 0;
 }
@@ -745,12 +804,12 @@ int launch_chain2(int mode, const ChainParams& P, int sms, cudaStream_t st) {
     const int per_head = (n_tiles + 2 * nt - 1) / (2 * nt);
     const int n_items = trunk ? per_head : P.n_heads * per_head;
     switch (mode * 2 + (nt - 1)) {
-        case 0: return launch_t<TRUNK_FWD, 1>(P, n_items, sms, st);
-        case 1: return launch_t<TRUNK_FWD, 2>(P, n_items, sms, st);
-        case 3: return launch_t<HEAD_FWD, 2>(P, n_items, sms, st);
-        case 5: return launch_t<HEAD_BWD, 2>(P, n_items, sms, st);
-        case 6: return launch_t<TRUNK_BWD, 1>(P, n_items, sms, st);
-        case 7: return launch_t<TRUNK_BWD, 2>(P, n_items, sms, st);
+        case 0: return launch_t<TRUNK_FWD, 1, false>(P, n_items, sms, st);
+        case 1: return launch_t<TRUNK_FWD, 2, false>(P, n_items, sms, st);
+        case 3: return P.dbg ? launch_t<HEAD_FWD, 2, true>(P, n_items, sms, st) : launch_t<HEAD_FWD, 2, false>(P, n_items, sms, st);
+        case 5: return launch_t<HEAD_BWD, 2, false>(P, n_items, sms, st);
+        case 6: return launch_t<TRUNK_BWD, 1, false>(P, n_items, sms, st);
+        case 7: return launch_t<TRUNK_BWD, 2, false>(P, n_items, sms, st);
     }
     set_error("launch_chain2: bad mode %d nt %d", mode, nt);
     return FINDB200_ERR_ARG;

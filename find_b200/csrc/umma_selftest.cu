@@ -263,6 +263,78 @@ __global__ void __launch_bounds__(128) umma_rate_kernel(int mode, int iters, int
     if (warp == 0) { if (CG == 2) tmem_dealloc2(tmem, 512); else tmem_dealloc(tmem, 512); }
 }
 
+// ---- synchronisation-primitive cost probe --------------------------------------------------------------------------------
+// What does ONE elected thread of the leader CTA of a pair pay for each primitive of the chain kernels' issue path?  op:
+//   0 tcgen05.commit cta_group::1 (nothing pending)        1 tcgen05.commit cta_group::2 multicast to both CTAs (nothing pending)
+//   2 mbarrier.try_wait, phase already complete            3 ld.volatile.shared                  4 mbarrier.arrive (own CTA)
+//   5 mbarrier.arrive on the PEER's barrier                6 fence.proxy.async                   7 tcgen05.fence::after_thread_sync
+//   8 4 x MMA (cg2 M256 N256) + multicast commit + wait for that commit (round trip, pipe empty at the start)
+//   9 4 x MMA (cg2) + multicast commit, no wait (issue-side cost with the pipe kept busy)
+//  10 S2R of the cluster CTA id (what cvta.shared costs inside a cluster kernel)    11 clock64 read
+// out[0] = cycles for `iters` repetitions, out[1] = iters.
+__global__ void __launch_bounds__(64) sync_probe_kernel(int op, int iters, unsigned long long* __restrict__ out) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+    __shared__ __align__(8) uint64_t bar[4];
+    __shared__ uint32_t tmem_base_s;
+    __shared__ volatile uint32_t word;
+    const int tid = threadIdx.x;
+    const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);
+    const uint32_t rank = cluster_ctarank();
+    for (int i = tid; i < 131072 / 4; i += 64) reinterpret_cast<uint32_t*>(smem)[i] = 0x3c003c00u;
+    if (tid == 0) {
+        for (int i = 0; i < 4; ++i) mbar_init(&bar[i], 1);
+        word = 1;
+        fence_barrier_init();
+    }
+    if (warp == 0) tmem_alloc2(&tmem_base_s, 512);
+    fence_proxy_async();
+    tc_fence_before();
+    cluster_sync_all();
+    tc_fence_after();
+    const uint32_t tmem = tmem_base_s;
+    if (warp == 1 && rank == 0) {
+        if (elect_one()) {
+            const uint32_t idesc = umma_idesc_f16(256, 256, false, false);
+            const uint32_t sa = smem_u32(smem), sb = sa + 65536;
+            const uint32_t peer_bar = mapa_u32(smem_u32(&bar[1]), 1);
+            uint32_t acc = 0;
+            const long long t0 = clock64();
+            for (int it = 0; it < iters; ++it) {
+                switch (op) {
+                    case 0: umma_commit(&bar[0]); break;
+                    case 1: umma2_commit_mc(&bar[0], 3); break;
+                    case 2: acc += mbar_try_wait(&bar[2], 1) ? 1u : 0u; break;          // fresh barrier: parity 1 is "complete"
+                    case 3: acc += word; break;
+                    case 4: mbar_arrive(&bar[3]); break;
+                    case 5: mbar_arrive_cluster(peer_bar); break;
+                    case 6: fence_proxy_async(); break;
+                    case 7: tc_fence_after(); break;
+                    case 8:
+                    case 9:
+#pragma unroll
+                        for (int k = 0; k < 4; ++k)
+                            umma2_f16(tmem, umma_desc(sa + (it & 3) * 16384 + k * 32, 16, 1024), umma_desc(sb + (it & 3) * 16384 + k * 32, 16, 1024),
+                                      idesc, 1u);
+                        umma2_commit_mc(&bar[0], 3);
+                        if (op == 8) mbar_wait(&bar[0], it & 1);
+                        break;
+                    case 10: { uint32_t r; asm volatile("mov.u32 %0, %%cluster_ctaid.x;" : "=r"(r)); acc += r; } break;
+                    default: acc += (uint32_t)clock64(); break;
+                }
+            }
+            const long long t1 = clock64();
+            if (op == 9 || op == 1 || op == 0) { umma2_commit_mc(&bar[1], 3); mbar_wait(&bar[1], 0); }
+            out[0] = (unsigned long long)(t1 - t0);
+            out[1] = (unsigned long long)iters + (acc == 0xdeadbeefu ? 1ull : 0ull);
+        }
+    }
+    __syncwarp();
+    tc_fence_before();
+    cluster_sync_all();
+    if (warp == 0) tmem_dealloc2(tmem, 512);
+}
+
 }  // namespace fb
 
 extern "C" int findb200_umma_selftest(int mode, const void* a_img, const void* b_img, float* d_out, void* stream) {
@@ -300,6 +372,22 @@ extern "C" int findb200_umma_rate(int mode, int iters, int flags, const void* gs
         FB_CUDA(cudaFuncSetAttribute(umma_rate_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
         umma_rate_kernel<1><<<1, 128, smem, (cudaStream_t)stream>>>(mode, iters, flags, (const uint8_t*)gsrc_1mb, out2_dev);
     }
+    FB_CUDA(cudaGetLastError());
+    return 0;
+}
+
+extern "C" int findb200_sync_probe(int op, int iters, unsigned long long* out2_dev, void* stream) {
+    using namespace fb;
+    FB_REQUIRE(op >= 0 && op <= 11 && iters >= 1 && out2_dev, FINDB200_ERR_ARG, "sync_probe: op 0..11, iters >= 1");
+    const int smem = 131072 + 1024;
+    FB_CUDA(cudaFuncSetAttribute(sync_probe_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(2); cfg.blockDim = dim3(64); cfg.dynamicSmemBytes = smem; cfg.stream = (cudaStream_t)stream;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = 2; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+    cfg.attrs = at; cfg.numAttrs = 1;
+    FB_CUDA(cudaLaunchKernelEx(&cfg, sync_probe_kernel, op, iters, out2_dev));
     FB_CUDA(cudaGetLastError());
     return 0;
 }

@@ -322,6 +322,9 @@ int findb200_umma_selftest(int mode, const void* a_img, const void* b_img, float
  * kernels do around the MMAs (1 commit per 4 MMAs, 2 tcgen05 fence per 4, 4 mbarrier wait per 4, 8 background bulk-copy stream from
  * gsrc_1mb (>= 1 MiB, pair modes), 16 background shared-memory writers). */
 int findb200_umma_rate(int mode, int iters, int flags, const void* gsrc_1mb, unsigned long long* out2_dev, void* stream);
+/* Cost of one synchronisation primitive of the chain kernels' issue path for one elected thread (csrc/umma_selftest.cu lists
+ * the ops); out2_dev[0] = cycles for `iters` repetitions, out2_dev[1] = iters.  Diagnostics only. */
+int findb200_sync_probe(int op, int iters, unsigned long long* out2_dev, void* stream);
 
 /* Launch profiler used by bench.py for the live roofline: after findb200_profile_enable(1) every kernel launch of the
  * library is bracketed by CUDA events on its launching stream (do not enable during CUDA-graph capture);
