@@ -37,6 +37,7 @@ static int g_prof_n = 0;
 static cudaEvent_t g_prof_ev[kProfMax];
 static const char* g_prof_name[kProfMax];
 static int g_prof_created = 0;
+static bool g_prof_keep = false;
 
 void prof_mark(const char* name, cudaStream_t st) {
     if (!g_prof_on || g_prof_n >= kProfMax) return;
@@ -44,7 +45,12 @@ void prof_mark(const char* name, cudaStream_t st) {
         if (cudaEventCreate(&g_prof_ev[g_prof_created]) != cudaSuccess) return;
         ++g_prof_created;
     }
-    cudaEventRecord(g_prof_ev[g_prof_n], st);
+    // inside a stream capture a plain record is only a dependency edge; the External flag makes it an event-record NODE that
+    // every replay re-records and that cudaEventElapsedTime accepts
+    cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
+    if (cudaStreamIsCapturing(st, &cs) != cudaSuccess) cs = cudaStreamCaptureStatusNone;
+    if (cs == cudaStreamCaptureStatusActive) cudaEventRecordWithFlags(g_prof_ev[g_prof_n], st, cudaEventRecordExternal);
+    else cudaEventRecord(g_prof_ev[g_prof_n], st);
     g_prof_name[g_prof_n] = name;
     ++g_prof_n;
 }
@@ -53,7 +59,11 @@ void prof_mark(const char* name, cudaStream_t st) {
 
 extern "C" {
 int findb200_profile_enable(int on) {
+    // 1: start recording (drops earlier marks); 0: off; 2: stop recording but KEEP the marks — for marks that were captured
+    // into a CUDA graph as event-record nodes: every replay re-records them and findb200_profile_read can be called after each
+    if (on == 2) { fb::g_prof_on = false; fb::g_prof_keep = true; return 0; }
     fb::g_prof_on = on != 0;
+    fb::g_prof_keep = false;
     if (on) fb::g_prof_n = 0;
     return 0;
 }
@@ -73,7 +83,7 @@ int findb200_profile_read(char* buf, size_t cap) {
     for (int i = 0; i + 1 < n; ++i) {
         if (!g_prof_name[i]) continue;
         float ms = 0.f;
-        if (cudaEventElapsedTime(&ms, g_prof_ev[i], g_prof_ev[i + 1]) != cudaSuccess) continue;
+        if (cudaEventElapsedTime(&ms, g_prof_ev[i], g_prof_ev[i + 1]) != cudaSuccess) { (void)cudaGetLastError(); continue; }
         int k = 0;
         while (k < nn && strcmp(names[k], g_prof_name[i]) != 0) ++k;
         if (k == nn) { if (nn == 256) continue; names[nn] = g_prof_name[i]; tot[nn] = 0; cnt[nn] = 0; ++nn; }
@@ -85,7 +95,7 @@ int findb200_profile_read(char* buf, size_t cap) {
         if (w < 0 || (size_t)w >= cap - off) break;
         off += (size_t)w;
     }
-    g_prof_n = 0;
+    if (!g_prof_keep) g_prof_n = 0;
     return (int)off;
 }
 const char* findb200_last_error(void) { return fb::g_err; }

@@ -7,6 +7,7 @@
 //             | HEAD_BWD | TRUNK_BWD | dw_kernel (all weight-gradient GEMMs in one launch) | reduce_dw | finish_small
 // With per-foot distinct points (TextureLossGTSpace call site, losses.py:50) the trunk runs per foot as well.
 #include "field.cuh"
+#include <cstdio>
 #include <cstdlib>
 #include "field_dw.cuh"
 #include <math.h>
@@ -730,38 +731,77 @@ int findb200_field_backward(const findb200_field_params* p, const float* pos, in
                 w.trunk_feet, w.tpf2, w.tpf2, kb == 0 ? colsum + cs_trunk(0, B) : nullptr, kb == 0 ? 1 : 0, 256, P_T0, kb);
     }
     D.n_gemms = ng;
-    // CTA allocation: the launch is HBM-bound (profiles/r1_math_kernels_ncu_full.md), so the cost of a GEMM is the bytes it
-    // streams; one CTA per SM, every GEMM at least one, then each further CTA goes to the GEMM whose CTAs carry the most
-    // bytes (greedy min-max), so that all CTAs finish together.
-    long long bytes[kMaxDwGemms];
-    // operands that were written by the kernels just before this one (the trunk's activations / dZ, 5 MB each) or that are
-    // re-read by every foot (the shared trunk output h5) mostly hit the 126 MB L2: they cost a fraction of an HBM byte
-    static float l2w = -1.f;
-    if (l2w < 0.f) { const char* e = getenv("FINDB200_DW_L2W"); l2w = e ? (float)atof(e) : 0.6f; }
+    D.dbg = g_chain_dbg;
+    // Work split.  Every GEMM streams its tiles through a 3-stage ring; under load a stage costs a fixed part (ring round trip)
+    // plus its bytes, and bytes that were written by the kernels just before this one (the trunk's activations / dZ, 5 MB each)
+    // or that every foot re-reads (the shared trunk output h5) come from the 126 MB L2 (measured per stage on cfg2, all CTAs
+    // streaming: 1.25 us for 64 KB from HBM, 0.97 us for 40 KB, 1.14 us for 32 KB HBM + 32 KB L2, 0.75 us for 40 KB from L2:
+    // profiles/r2_dw_cta_lifetimes.txt).  The cost-weighted unit lists of all GEMMs are laid end to end and cut into one equal
+    // piece per CTA; a piece that crosses a GEMM border becomes two segments, each with its own partial (deterministic: the
+    // cut depends only on the shapes).
+    static float c_fix = -1.f, c_hbm = 0.f, c_l2 = 0.f;
+    if (c_fix < 0.f) {
+        const char* e = getenv("FINDB200_DW_COST");        // "fixed_us,us_per_64KB_hbm,us_per_64KB_l2" (tuning)
+        float a = 0.45f, b = 0.80f, c = 0.75f;
+        if (e) sscanf(e, "%f,%f,%f", &a, &b, &c);
+        c_fix = a; c_hbm = b; c_l2 = c;
+    }
+    (void)cost;
+    long long unit_cost[kMaxDwGemms], total_cost = 0;      // in ns per unit (one tile = two stages)
     for (int i = 0; i < ng; ++i) {
         const DwGemm& g = D.g[i];
         const bool trunk = g.feet == w.trunk_feet && g.A >= ws + w.tdz && g.A < ws + w.tdz + (size_t)5 * w.trunk_tiles * kTileBytes;
-        const float fa = trunk ? l2w : 1.f;
-        const float fb = (trunk || (g.b_foot_stride == 0 && g.feet > 1)) ? l2w : 1.f;
-        bytes[i] = (long long)((double)g.feet * g.tpf * ((double)g.a_imgs * fa + (double)g.b_imgs * fb) * kImgBytes);
-        if (bytes[i] < 1) bytes[i] = 1;
+        const bool b_l2 = trunk || (g.b_foot_stride == 0 && g.feet > 1);
+        const double a_kb = g.a_imgs * 8.0, b_kb = g.b_imgs * 8.0;                      // per stage
+        const double hbm = (trunk ? 0.0 : a_kb) + (b_l2 ? 0.0 : b_kb), l2 = (trunk ? a_kb : 0.0) + (b_l2 ? b_kb : 0.0);
+        double us = c_fix + hbm / 64.0 * c_hbm + l2 / 64.0 * c_l2;
+        const double mma_us = g.mhalves * 4 * 0.09;                                     // 172 cycles per K = 16 MMA
+        if (us < mma_us) us = mma_us;
+        unit_cost[i] = (long long)(2.0 * us * 1000.0);
+        if (unit_cost[i] < 1) unit_cost[i] = 1;
+        total_cost += unit_cost[i] * g.feet * g.tpf;
     }
-    (void)cost;
-    int budget = sms < kMaxDwCtas ? sms : kMaxDwCtas;
-    int n_ctas = 0;
-    for (int i = 0; i < ng; ++i) { D.g[i].ncta = 1; ++n_ctas; }
-    FB_REQUIRE(n_ctas <= kMaxDwCtas, FINDB200_ERR_UNSUPPORTED, "field_backward: too many weight-gradient GEMMs");
-    while (n_ctas < budget) {
-        int big = -1;
-        double worst = 0.0;
-        for (int i = 0; i < ng; ++i) {
-            const int units = D.g[i].feet * D.g[i].tpf;
-            if (D.g[i].ncta >= units) continue;
-            const double per = (double)bytes[i] / D.g[i].ncta;
-            if (per > worst) { worst = per; big = i; }
+    int n_ctas = sms < kMaxDwCtas ? sms : kMaxDwCtas;
+    {
+        long long total_units = 0;
+        for (int i = 0; i < ng; ++i) total_units += (long long)D.g[i].feet * D.g[i].tpf;
+        if (total_units < n_ctas) n_ctas = (int)total_units;
+        if (n_ctas < 1) n_ctas = 1;
+    }
+    FB_REQUIRE(n_ctas + ng <= kMaxDwSegs, FINDB200_ERR_UNSUPPORTED, "field_backward: too many weight-gradient GEMMs");
+    int n_seg = 0;
+    {
+        // walk the timeline: CTA b ends at cost tick total * (b + 1) / n_ctas, rounded to a unit boundary of the GEMM it falls in
+        int gi = 0, u = 0;                      // current position: GEMM gi, unit u
+        long long pos = 0;                      // cost tick of the current position
+        int slot[kMaxDwGemms];
+        for (int i = 0; i < ng; ++i) { slot[i] = 0; D.g[i].ncta = 0; }
+        for (int b = 0; b < n_ctas; ++b) {
+            D.cta_seg[b] = (unsigned short)n_seg;
+            const long long target = (b == n_ctas - 1) ? total_cost : total_cost * (b + 1) / n_ctas;
+            while (gi < ng) {
+                const int units = D.g[gi].feet * D.g[gi].tpf;
+                const long long end_g = pos + (long long)(units - u) * unit_cost[gi];
+                int u_end;
+                if (end_g <= target) u_end = units;
+                else {
+                    u_end = u + (int)((target - pos + unit_cost[gi] / 2) / unit_cost[gi]);       // nearest unit boundary
+                    if (u_end > units) u_end = units;
+                }
+                if (u_end > u) {
+                    DwSeg& sg = D.seg[n_seg++];
+                    sg.gemm = (short)gi; sg.slot = (short)slot[gi]++; sg.u0 = u; sg.u1 = u_end;
+                    ++D.g[gi].ncta;
+                    pos += (long long)(u_end - u) * unit_cost[gi];
+                    u = u_end;
+                }
+                if (u < units) break;                   // this CTA's share ends inside GEMM gi
+                ++gi; u = 0;
+                if (pos >= target && b < n_ctas - 1) break;
+            }
         }
-        if (big < 0) break;
-        ++D.g[big].ncta; ++n_ctas;
+        D.cta_seg[n_ctas] = (unsigned short)n_seg;
+        FB_REQUIRE(gi == ng, FINDB200_ERR_UNSUPPORTED, "field_backward: internal: dW work split did not cover every GEMM");
     }
     int c0 = 0;
     for (int i = 0; i < ng; ++i) {
@@ -769,6 +809,11 @@ int findb200_field_backward(const findb200_field_params* p, const float* pos, in
         D.g[i].partial = partial + (size_t)c0 * kW * kW;
         c0 += D.g[i].ncta;
     }
+    FB_REQUIRE(c0 <= w.n_partials, FINDB200_ERR_UNSUPPORTED, "field_backward: internal: more dW partials than workspace slots");
+    if (g_chain_dbg && (g_chain_dbg_flags & 512))             // diagnostics (tools/dw_trace.py): the static CTA allocation
+        for (int i = 0; i < ng; ++i)
+            fprintf(stderr, "dw gemm %d: param %d kblock %d feet %d a_imgs %d b_imgs %d N %d cta0 %d ncta %d\n", i, gemm_param[i], gemm_kblock[i],
+                    D.g[i].feet, D.g[i].a_imgs, D.g[i].b_imgs, D.g[i].N, D.g[i].cta0, D.g[i].ncta);
     rc = launch_dw(D, n_ctas, st);
     if (rc) return rc;
 

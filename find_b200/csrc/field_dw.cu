@@ -21,7 +21,7 @@ __global__ void __launch_bounds__(kDwThreads, 1) dw_kernel(const __grid_constant
     fb::pdl_wait_trigger();
     extern __shared__ uint8_t smem_raw[];
     uint8_t* ring = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
-    __shared__ __align__(8) uint64_t bar_full[kDwStages], bar_empty[kDwStages], bar_done;
+    __shared__ __align__(8) uint64_t bar_full[kDwStages], bar_empty[kDwStages], bar_done, bar_tmem_free;
     __shared__ uint32_t tmem_base_s;
 
     const int tid = threadIdx.x, lane = tid & 31;
@@ -29,6 +29,7 @@ __global__ void __launch_bounds__(kDwThreads, 1) dw_kernel(const __grid_constant
     if (tid == 0) {
         for (int s = 0; s < kDwStages; ++s) { mbar_init(&bar_full[s], 1); mbar_init(&bar_empty[s], 1 + 128); }
         mbar_init(&bar_done, 1);
+        mbar_init(&bar_tmem_free, 128);
         fence_barrier_init();
     }
     if (warp == 0) tmem_alloc(&tmem_base_s, 512);
@@ -37,117 +38,125 @@ __global__ void __launch_bounds__(kDwThreads, 1) dw_kernel(const __grid_constant
     tc_fence_after();
     const uint32_t tmem = tmem_base_s;
 
-    // which GEMM / slice is this CTA
-    int gi = 0;
-    while (gi < P.n_gemms - 1 && (int)blockIdx.x >= P.g[gi].cta0 + P.g[gi].ncta) ++gi;
-    const DwGemm& G = P.g[gi];
-    const int slice = blockIdx.x - G.cta0;
-    const int units = G.feet * G.tpf;
-    const int u0 = (int)(((long long)units * slice) / G.ncta), u1 = (int)(((long long)units * (slice + 1)) / G.ncta);
-    const int n_stages_total = (u1 - u0) * 2;
+    // this CTA's segments
+    const int s0 = P.cta_seg[blockIdx.x], s1 = P.cta_seg[blockIdx.x + 1];
+    if (P.dbg && tid == 0 && blockIdx.x < 240) { unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); P.dbg[2 * blockIdx.x] = t; }
 
     if (warp == 0) {
         // ---- producer: 64-row halves of the A and B tiles, one 8 KB bulk copy per image -----------------------
         uint32_t cnt = 0;
-        for (int u = u0; u < u1; ++u) {
-            const int b = u / G.tpf, t = u % G.tpf;
-            const uint8_t* At = G.A + ((size_t)b * G.a_foot_stride + t) * G.a_tile_bytes;
-            const uint8_t* Bt = G.Bm + ((size_t)b * G.b_foot_stride + t) * G.b_tile_bytes + G.b_img_off;
-            for (int hh = 0; hh < 2; ++hh, ++cnt) {
-                const uint32_t s = cnt % kDwStages, use = cnt / kDwStages;
-                uint8_t* st = ring + s * kDwStageBytes;
-                if (lane == 0) {
-                    if (use > 0) mbar_wait(&bar_empty[s], (use - 1) & 1);
-                    mbar_expect_tx(&bar_full[s], (uint32_t)(G.a_imgs + G.b_imgs) * 8192u);
+        for (int si = s0; si < s1; ++si) {
+            const DwSeg sg = P.seg[si];
+            const DwGemm& G = P.g[sg.gemm];
+            for (int u = sg.u0; u < sg.u1; ++u) {
+                const int b = u / G.tpf, t = u % G.tpf;
+                const uint8_t* At = G.A + ((size_t)b * G.a_foot_stride + t) * G.a_tile_bytes;
+                const uint8_t* Bt = G.Bm + ((size_t)b * G.b_foot_stride + t) * G.b_tile_bytes + G.b_img_off;
+                for (int hh = 0; hh < 2; ++hh, ++cnt) {
+                    const uint32_t s = cnt % kDwStages, use = cnt / kDwStages;
+                    uint8_t* st = ring + s * kDwStageBytes;
+                    if (lane == 0) {
+                        if (use > 0) mbar_wait(&bar_empty[s], (use - 1) & 1);
+                        mbar_expect_tx(&bar_full[s], (uint32_t)(G.a_imgs + G.b_imgs) * 8192u);
+                    }
+                    __syncwarp();
+                    if (lane < G.a_imgs) bulk_g2s(st + lane * 8192, At + (size_t)lane * kImgBytes + hh * 8192, 8192u, &bar_full[s]);
+                    else if (lane >= 8 && lane < 8 + G.b_imgs)
+                        bulk_g2s(st + 32768 + (lane - 8) * 8192, Bt + (size_t)(lane - 8) * kImgBytes + hh * 8192, 8192u, &bar_full[s]);
+                    __syncwarp();
                 }
-                __syncwarp();
-                if (lane < G.a_imgs) bulk_g2s(st + lane * 8192, At + (size_t)lane * kImgBytes + hh * 8192, 8192u, &bar_full[s]);
-                else if (lane >= 8 && lane < 8 + G.b_imgs)
-                    bulk_g2s(st + 32768 + (lane - 8) * 8192, Bt + (size_t)(lane - 8) * kImgBytes + hh * 8192, 8192u, &bar_full[s]);
-                __syncwarp();
             }
         }
     } else if (warp == 1) {
         // ---- MMA issuer ------------------------------------------------------------------------------------------
         if (elect_one()) {
-            const uint32_t idesc = umma_idesc_f16(128, G.N, true, true);
-            const uint32_t a_lbo = G.a_imgs > 1 ? 8192u : 0u;
-            for (int i = 0; i < n_stages_total; ++i) {
-                const uint32_t s = i % kDwStages, use = i / kDwStages;
-                mbar_wait(&bar_full[s], use & 1);
-                tc_fence_after();
-                const uint32_t sa = smem_u32(ring + s * kDwStageBytes), sb = sa + 32768;
-                for (int mh = 0; mh < G.mhalves; ++mh)
-                    for (int ks = 0; ks < 4; ++ks) {
-                        const uint64_t ad = umma_desc(sa + mh * 2 * 8192 + ks * 2048, a_lbo, 1024);
-                        const uint64_t bd = umma_desc(sb + ks * 2048, 8192, 1024);
-                        umma_f16(tmem + mh * 256, ad, bd, idesc, (i > 0 || ks > 0) ? 1u : 0u);
-                    }
-                umma_commit(&bar_empty[s]);
+            uint32_t cnt = 0;
+            for (int si = s0; si < s1; ++si) {
+                const DwSeg sg = P.seg[si];
+                const DwGemm& G = P.g[sg.gemm];
+                const uint32_t idesc = umma_idesc_f16(128, G.N, true, true);
+                const uint32_t a_lbo = G.a_imgs > 1 ? 8192u : 0u;
+                const int n_st = (sg.u1 - sg.u0) * 2;
+                if (si > s0) { mbar_wait(&bar_tmem_free, (uint32_t)(si - s0 - 1) & 1u); tc_fence_after(); }   // the previous partial has left TMEM
+                for (int i = 0; i < n_st; ++i, ++cnt) {
+                    const uint32_t s = cnt % kDwStages, use = cnt / kDwStages;
+                    mbar_wait(&bar_full[s], use & 1);
+                    tc_fence_after();
+                    const uint32_t sa = smem_u32(ring + s * kDwStageBytes), sb = sa + 32768;
+                    for (int mh = 0; mh < G.mhalves; ++mh)
+                        for (int ks = 0; ks < 4; ++ks) {
+                            const uint64_t ad = umma_desc(sa + mh * 2 * 8192 + ks * 2048, a_lbo, 1024);
+                            const uint64_t bd = umma_desc(sb + ks * 2048, 8192, 1024);
+                            umma_f16(tmem + mh * 256, ad, bd, idesc, (i > 0 || ks > 0) ? 1u : 0u);
+                        }
+                    umma_commit(&bar_empty[s]);
+                }
+                umma_commit(&bar_done);
             }
-            umma_commit(&bar_done);
         }
     } else {
-        // ---- column sums of the A operand (dZ), then the TMEM -> HBM epilogue ------------------------------------
+        // ---- column sums of the A operand (dZ), then the TMEM -> HBM epilogue, per segment ------------------------
         const int ct = (warp - 2) * 32 + lane;           // column pair 2ct, 2ct+1
         const int img = ct >> 5, w = ct & 31;
-        const bool active = G.colsum_mode != 0 && (2 * ct < G.colsum_cols) && img < G.a_imgs;
-        float s0 = 0.f, s1 = 0.f;
-        int cur_foot = -1;
-        uint32_t cnt = 0;
-        auto flush = [&](int foot) {
-            if (active && foot >= 0) {
-                float* dst = G.colsum + (G.colsum_mode == 2 ? (size_t)foot * kW : 0) + 2 * ct;
-                atomicAdd(dst, s0);
-                atomicAdd(dst + 1, s1);
-            }
-            s0 = s1 = 0.f;
-        };
-        for (int u = u0; u < u1; ++u) {
-            const int b = u / G.tpf;
-            if (G.colsum_mode == 2 && b != cur_foot) { flush(cur_foot); }
-            cur_foot = b;
-            for (int hh = 0; hh < 2; ++hh, ++cnt) {
-                const uint32_t s = cnt % kDwStages, use = cnt / kDwStages;
-                mbar_wait(&bar_full[s], use & 1);
-                if (active) {
-                    const uint8_t* base = ring + s * kDwStageBytes + img * 8192 + (w & 3) * 4;
-#pragma unroll 8
-                    for (int r = 0; r < 64; ++r) {
-                        const uint32_t x = *reinterpret_cast<const uint32_t*>(base + r * 128 + (((w >> 2) ^ (r & 7)) << 4));
-                        const float2 f = __half22float2(*reinterpret_cast<const __half2*>(&x));
-                        s0 += f.x;
-                        s1 += f.y;
-                    }
-                }
-                mbar_arrive(&bar_empty[s]);
-            }
-        }
-        flush(cur_foot);
-
-        mbar_wait(&bar_done, 0);
-        tc_fence_after();
         const int q = warp & 3, row = q * 32 + lane;
-        float* out = G.partial + (size_t)slice * kW * kW;
-        for (int mh = 0; mh < G.mhalves; ++mh)
-            for (int cc = 0; cc < G.N / 32; ++cc) {
-                uint32_t v[32];
-                if (n_stages_total > 0) {
+        uint32_t cnt = 0;
+        for (int si = s0; si < s1; ++si) {
+            const DwSeg sg = P.seg[si];
+            const DwGemm& G = P.g[sg.gemm];
+            const bool active = G.colsum_mode != 0 && (2 * ct < G.colsum_cols) && img < G.a_imgs;
+            float c0 = 0.f, c1 = 0.f;
+            int cur_foot = -1;
+            auto flush = [&](int foot) {
+                if (active && foot >= 0) {
+                    float* dst = G.colsum + (G.colsum_mode == 2 ? (size_t)foot * kW : 0) + 2 * ct;
+                    atomicAdd(dst, c0);
+                    atomicAdd(dst + 1, c1);
+                }
+                c0 = c1 = 0.f;
+            };
+            for (int u = sg.u0; u < sg.u1; ++u) {
+                const int b = u / G.tpf;
+                if (G.colsum_mode == 2 && b != cur_foot) { flush(cur_foot); }
+                cur_foot = b;
+                for (int hh = 0; hh < 2; ++hh, ++cnt) {
+                    const uint32_t s = cnt % kDwStages, use = cnt / kDwStages;
+                    mbar_wait(&bar_full[s], use & 1);
+                    if (active) {
+                        const uint8_t* base = ring + s * kDwStageBytes + img * 8192 + (w & 3) * 4;
+#pragma unroll 8
+                        for (int r = 0; r < 64; ++r) {
+                            const uint32_t x = *reinterpret_cast<const uint32_t*>(base + r * 128 + (((w >> 2) ^ (r & 7)) << 4));
+                            const float2 f = __half22float2(*reinterpret_cast<const __half2*>(&x));
+                            c0 += f.x;
+                            c1 += f.y;
+                        }
+                    }
+                    mbar_arrive(&bar_empty[s]);
+                }
+            }
+            flush(cur_foot);
+
+            mbar_wait(&bar_done, (uint32_t)(si - s0) & 1u);
+            tc_fence_after();
+            float* out = G.partial + (size_t)sg.slot * kW * kW;
+            for (int mh = 0; mh < G.mhalves; ++mh)
+                for (int cc = 0; cc < G.N / 32; ++cc) {
+                    uint32_t v[32];
                     tmem_ld32(tmem + ((uint32_t)(q * 32) << 16) + mh * 256 + cc * 32, v);
                     tmem_ld_wait();
-                } else {
+                    float4* o = reinterpret_cast<float4*>(out + (size_t)(mh * 128 + row) * kW + cc * 32);
 #pragma unroll
-                    for (int j = 0; j < 32; ++j) v[j] = 0u;
+                    for (int j = 0; j < 8; ++j)
+                        o[j] = make_float4(__uint_as_float(v[4 * j]), __uint_as_float(v[4 * j + 1]), __uint_as_float(v[4 * j + 2]),
+                                           __uint_as_float(v[4 * j + 3]));
                 }
-                float4* o = reinterpret_cast<float4*>(out + (size_t)(mh * 128 + row) * kW + cc * 32);
-#pragma unroll
-                for (int j = 0; j < 8; ++j)
-                    o[j] = make_float4(__uint_as_float(v[4 * j]), __uint_as_float(v[4 * j + 1]), __uint_as_float(v[4 * j + 2]),
-                                       __uint_as_float(v[4 * j + 3]));
-            }
+            tc_fence_before();
+            mbar_arrive(&bar_tmem_free);                 // the accumulators may be overwritten by the next segment
+        }
     }
     tc_fence_before();
     __syncthreads();
+    if (P.dbg && tid == 0 && blockIdx.x < 240) { unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); P.dbg[2 * blockIdx.x + 1] = t; }
     if (warp == 0) tmem_dealloc(tmem, 512);
 }
 

@@ -17,14 +17,25 @@ struct DwGemm {
     float* colsum;           // column sums of A (nullable)
     int colsum_mode;         // 0 none, 1 one vector [256], 2 per foot [feet][256]
     int colsum_cols;         // 256 or 16
-    int cta0, ncta;          // CTAs [cta0, cta0 + ncta) split the units of this GEMM
+    int cta0, ncta;          // partial slots [cta0, cta0 + ncta) hold the row-slices of this GEMM (one per segment, see DwSeg)
     float* partial;          // [ncta][256][256] fp32
 };
+
+// One contiguous run of units (tiles) of one GEMM, accumulated into one partial.  The host cuts the concatenated, cost-weighted
+// unit list of all GEMMs into equal pieces, one piece per CTA; a piece that crosses a GEMM border is two (or more) segments.
+struct DwSeg {
+    short gemm, slot;        // slot = index of the partial inside the GEMM
+    int u0, u1;
+};
+constexpr int kMaxDwSegs = 192;      // = kMaxDwCtas partial slots
 
 constexpr int kMaxDwGemms = 24;
 struct DwParams {
     DwGemm g[kMaxDwGemms];
     int n_gemms;
+    DwSeg seg[kMaxDwSegs];
+    unsigned short cta_seg[kMaxDwCtas + 1];   // CTA b owns segments [cta_seg[b], cta_seg[b + 1])
+    unsigned long long* dbg;   // diagnostics (findb200_chain_trace): %globaltimer at the start / end of every CTA, [2 * cta]
 };
 
 int launch_dw(const DwParams& P, int n_ctas, cudaStream_t st);

@@ -327,9 +327,11 @@ int findb200_umma_rate(int mode, int iters, int flags, const void* gsrc_1mb, uns
 int findb200_sync_probe(int op, int iters, unsigned long long* out2_dev, void* stream);
 
 /* Launch profiler used by bench.py for the live roofline: after findb200_profile_enable(1) every kernel launch of the
- * library is bracketed by CUDA events on its launching stream (do not enable during CUDA-graph capture);
- * findb200_profile_read synchronises and writes "kernel,launches,total_ms" lines into the HOST buffer buf
- * (returns bytes written) and clears the record. */
+ * library is bracketed by CUDA events on its launching stream; findb200_profile_read synchronises and writes
+ * "kernel,launches,total_ms" lines into the HOST buffer buf (returns bytes written) and clears the record.
+ * In-graph timing: enable(1) just before capturing a step into a CUDA graph makes the marks event-record NODES of the graph;
+ * enable(2) after the capture stops recording but keeps the marks, and findb200_profile_read after every replay (it
+ * synchronises) returns that replay's kernel durations without the host's launch gaps.  enable(0) ends either mode. */
 int findb200_chain_trace(void* dev_buf_256_u64);   /* diagnostics: timeline of one head_fwd item (csrc/diag.cu) */
 int findb200_profile_enable(int on);
 int findb200_profile_read(char* buf, size_t cap);
