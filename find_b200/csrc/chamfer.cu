@@ -449,7 +449,7 @@ static int g_knn_mode = -1;
 static int knn_mode() {
     if (g_knn_mode < 0) {
         const char* e = getenv("FINDB200_KNN_MODE");
-        g_knn_mode = (e && e[0] == '1') ? 1 : 0;
+        g_knn_mode = (e && e[0] >= '0' && e[0] <= '2') ? e[0] - '0' : 0;
     }
     return g_knn_mode;
 }
@@ -494,6 +494,24 @@ static int launch_cull(CullParams& prm, int N, int P1, int P2, bool both, cudaSt
     return 0;
 }
 
+template <int kQ>
+static int launch_cull_cta(CullParams& prm, int N, int P1, int P2, bool both, cudaStream_t st) {
+    prm.dir[0].n_groups = (P1 + 32 * kQ - 1) / (32 * kQ);
+    prm.dir[1].n_groups = (P2 + 32 * kQ - 1) / (32 * kQ);
+    prm.items_dir0 = N * prm.dir[0].n_groups;
+    prm.total_items = prm.items_dir0 + (both ? N * prm.dir[1].n_groups : 0);
+    static int per_sm = 0;
+    if (!per_sm) {
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, knn_cull_cta_kernel<kQ>, 128, 0) != cudaSuccess || per_sm < 1) per_sm = 4;
+    }
+    int grid = num_sms() * per_sm;
+    if (grid > prm.total_items) grid = prm.total_items;
+    FB_MARK("knn_main", st);
+    FB_CUDA(fb::launch_pdl(knn_cull_cta_kernel<kQ>, grid, 128, 0, st, prm));
+    FB_CUDA(cudaGetLastError());
+    return 0;
+}
+
 static int run_knn_cull(const float* x, const float* y, const int64_t* lx, const int64_t* ly, int N, int P1, int P2,
                         bool both, Workspace& w, cudaStream_t st) {
     SortParams sp{};
@@ -520,6 +538,10 @@ static int run_knn_cull(const float* x, const float* y, const int64_t* lx, const
     prm.dir[0] = CullDir{w.soa_x, w.perm_x, w.soa_y, w.perm_y, w.box_y, w.sbox_y, lx, ly, w.keys_x, P1, w.P1p, P2, w.P2p, w.C2p, w.S2p, 0};
     prm.dir[1] = CullDir{w.soa_y, w.perm_y, w.soa_x, w.perm_x, w.box_x, w.sbox_x, ly, lx, w.keys_y, P2, w.P2p, P1, w.P1p, w.C1p, w.S1p, 0};
     const int kq = g_cull_kq ? g_cull_kq : 2;   // 2 queries per lane measured best on cfg2-cfg4 shapes (tools/knn_bench.py)
+    if (knn_mode() == 2) {             // CTA-cooperative groups (knn_cull.cuh)
+        if (kq == 1) return launch_cull_cta<1>(prm, N, P1, P2, both, st);
+        return kq == 4 ? launch_cull_cta<4>(prm, N, P1, P2, both, st) : launch_cull_cta<2>(prm, N, P1, P2, both, st);
+    }
     if (kq == 1) return launch_cull<1>(prm, N, P1, P2, both, st);
     return kq == 4 ? launch_cull<4>(prm, N, P1, P2, both, st) : launch_cull<2>(prm, N, P1, P2, both, st);
 }
@@ -550,7 +572,7 @@ using namespace fb::chamfer;
 extern "C" {
 
 int findb200_set_knn_mode(int mode, int kq) {
-    FB_REQUIRE((mode == 0 || mode == 1) && (kq == 0 || kq == 1 || kq == 2 || kq == 4), FINDB200_ERR_ARG, "set_knn_mode: mode 0/1, kq 0/1/2/4");
+    FB_REQUIRE((mode == 0 || mode == 1 || mode == 2) && (kq == 0 || kq == 1 || kq == 2 || kq == 4), FINDB200_ERR_ARG, "set_knn_mode: mode 0/1/2, kq 0/1/2/4");
     g_knn_mode = mode; g_cull_kq = kq;
     return 0;
 }

@@ -558,5 +558,286 @@ __global__ void __launch_bounds__(128) knn_cull_kernel(const CullParams prm) {
     }
 }
 
+// ---- CTA-cooperative variant ----------------------------------------------------------------------------------
+// Same walk, but ONE group of 32*kQ queries is worked on by the four warps of a CTA: every warp keeps all the group's queries
+// in registers, evaluates the seed chunk (a tight first bound for everyone) and then only the target chunks whose index is
+// its own residue mod 4; the four partial results are merged through shared memory before the index resolution.  A launch
+// of the one-warp-per-group kernel lasts as long as its slowest group (cfg2: 53 chunk evaluations against an average of 17,
+// SMs 46 % busy); here the slowest group is four times shorter and the 2 560 groups are pulled from the queue by ~740
+// resident CTAs, so the tail evens out.  Exactness is unchanged: a chunk is skipped by warp w only if it cannot beat or tie
+// w's own best, which is >= the merged best.
+template <int kQ>
+__global__ void __launch_bounds__(128) knn_cull_cta_kernel(const CullParams prm) {
+    fb::pdl_wait_trigger();
+    __shared__ float4 s_stage[4][24];      // per warp: one target chunk (x row | y row | z row)
+    __shared__ float s_best[4][kQ][32];    // per warp: its best distance / chunk / tie bits for the group's queries
+    __shared__ int s_chunk[4][kQ][32];
+    __shared__ uint32_t s_tie[4][32];
+    __shared__ int s_item;
+    const int lane = threadIdx.x & 31, wq = threadIdx.x >> 5;
+    float4* stage = s_stage[wq];
+    unsigned long long n_eval = 0, n_slow = 0, n_eval_max = 0, n_items = 0;
+
+    for (;;) {
+        __syncthreads();                   // the previous item's merged results have been read
+        if (threadIdx.x == 0) s_item = (int)atomicAdd(prm.counter, 1u);
+        __syncthreads();
+        const int item = s_item;
+        if (item >= prm.total_items) break;
+
+        const int d = item >= prm.items_dir0 ? 1 : 0;
+        const CullDir& D = prm.dir[d];
+        const int r = item - (d ? prm.items_dir0 : 0);
+        const int grp = r % D.n_groups, n = r / D.n_groups;
+        const int len_q = D.len_q ? min((int)D.len_q[n], D.Pq) : D.Pq;
+        const int len_t = D.len_t ? min((int)D.len_t[n], D.Pt) : D.Pt;
+        const int q0 = grp * 32 * kQ;
+        if (q0 >= len_q || len_t <= 0) continue;
+
+        const float* qsoa = D.q_soa + (size_t)n * 3 * D.Pq_pad;
+        const float* tsoa = D.t_soa + (size_t)n * 3 * D.Pt_pad;
+        const int* tperm = D.t_perm + (size_t)n * D.Pt_pad;
+        const float* box = D.t_box + (size_t)n * 6 * D.Ct_pad;
+        const int nchunk = (len_t + kCullChunk - 1) / kCullChunk;
+
+        // queries -> registers; lanes past the end of the cloud repeat the group's first query (never published)
+        float fx[kQ], fy[kQ], fz[kQ], best[kQ];
+        uint64_t qx[kQ], qy[kQ], qz[kQ];
+        int bchunk[kQ];
+        uint32_t tie = 0;
+        float glo[3] = {CUDART_INF_F, CUDART_INF_F, CUDART_INF_F}, ghi[3] = {-CUDART_INF_F, -CUDART_INF_F, -CUDART_INF_F};
+#pragma unroll
+        for (int q = 0; q < kQ; ++q) {
+            int i = q0 + q * 32 + lane;
+            if (i >= len_q) i = q0;
+            fx[q] = __ldg(qsoa + i); fy[q] = __ldg(qsoa + D.Pq_pad + i); fz[q] = __ldg(qsoa + 2 * D.Pq_pad + i);
+            qx[q] = pack2(fx[q], fx[q]); qy[q] = pack2(fy[q], fy[q]); qz[q] = pack2(fz[q], fz[q]);
+            best[q] = CUDART_INF_F; bchunk[q] = 0;
+            glo[0] = fminf(glo[0], fx[q]); ghi[0] = fmaxf(ghi[0], fx[q]);
+            glo[1] = fminf(glo[1], fy[q]); ghi[1] = fmaxf(ghi[1], fy[q]);
+            glo[2] = fminf(glo[2], fz[q]); ghi[2] = fmaxf(ghi[2], fz[q]);
+        }
+#pragma unroll
+        for (int k = 0; k < 3; ++k) { glo[k] = warp_min(glo[k]); ghi[k] = warp_max(ghi[k]); }
+
+        const unsigned long long n_eval_before = n_eval;
+        ++n_items;
+        // a chunk travels global -> one float4 per lane (24 lanes) -> the warp's shared-memory stage -> broadcast reads:
+        // one LDG per chunk, issued one chunk ahead of its use
+        auto load_part = [&](int c) -> float4 {
+            float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (lane < 24)
+                v = __ldg(reinterpret_cast<const float4*>(tsoa + (size_t)(lane >> 3) * D.Pt_pad + (size_t)c * kCullChunk) + (lane & 7));
+            return v;
+        };
+        auto evaluate = [&](int c, const float4& part) {
+            __syncwarp();
+            if (lane < 24) stage[lane] = part;
+            __syncwarp();
+            const float4 *sx = stage, *sy = stage + 8, *sz = stage + 16;
+            float cmin[kQ];
+#pragma unroll
+            for (int q = 0; q < kQ; ++q) cmin[q] = CUDART_INF_F;
+#pragma unroll
+            for (int g = 0; g < kCullChunk / 4; ++g) {
+                const float4 X = sx[g], Y = sy[g], Z = sz[g];
+                const uint64_t x01 = pack2(X.x, X.y), x23 = pack2(X.z, X.w);
+                const uint64_t y01 = pack2(Y.x, Y.y), y23 = pack2(Y.z, Y.w);
+                const uint64_t z01 = pack2(Z.x, Z.y), z23 = pack2(Z.z, Z.w);
+#pragma unroll
+                for (int q = 0; q < kQ; ++q) {
+                    uint64_t dx = sub2(qx[q], x01), dy = sub2(qy[q], y01), dz = sub2(qz[q], z01);
+                    uint64_t dd = fma2(dz, dz, fma2(dy, dy, mul2(dx, dx)));
+                    float lo, hi;
+                    unpack2(dd, lo, hi);
+                    cmin[q] = min3(cmin[q], lo, hi);
+                    dx = sub2(qx[q], x23); dy = sub2(qy[q], y23); dz = sub2(qz[q], z23);
+                    dd = fma2(dz, dz, fma2(dy, dy, mul2(dx, dx)));
+                    unpack2(dd, lo, hi);
+                    cmin[q] = min3(cmin[q], lo, hi);
+                }
+            }
+#pragma unroll
+            for (int q = 0; q < kQ; ++q) {
+                if (cmin[q] < best[q]) { best[q] = cmin[q]; bchunk[q] = c; tie &= ~(1u << q); }
+                else if (cmin[q] == best[q]) tie |= 1u << q;
+            }
+            ++n_eval;
+        };
+
+        // seed: nearest super-chunk (32 chunks) by box centre, then the nearest chunk inside it
+        const float* sbox = D.t_sbox + (size_t)n * 6 * D.St_pad;
+        const int nsuper = (nchunk + 31) / 32;
+        auto nearest = [&](const float* bxs, int pad, int first, int last) -> int {
+            const float cx = 0.5f * (glo[0] + ghi[0]), cy = 0.5f * (glo[1] + ghi[1]), cz = 0.5f * (glo[2] + ghi[2]);
+            unsigned long long bk = ~0ull;
+            for (int c = first + lane; c < last; c += 32) {
+                const float dx = 0.5f * (bxs[c] + bxs[3 * pad + c]) - cx;
+                const float dy = 0.5f * (bxs[pad + c] + bxs[4 * pad + c]) - cy;
+                const float dz = 0.5f * (bxs[2 * pad + c] + bxs[5 * pad + c]) - cz;
+                const float k2 = dx * dx + dy * dy + dz * dz;        // >= 0 or NaN
+                const unsigned long long key = ((unsigned long long)__float_as_uint(k2) << 32) | (unsigned)c;
+                if (k2 >= 0.f && key < bk) bk = key;
+            }
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) {
+                const unsigned long long other = __shfl_xor_sync(0xffffffffu, bk, o);
+                bk = other < bk ? other : bk;
+            }
+            return bk != ~0ull ? (int)(bk & 0xffffffffu) : first;
+        };
+        const int seed_super = nearest(sbox, D.St_pad, 0, nsuper);
+        const int seed = nearest(box, D.Ct_pad, seed_super * 32, min(nchunk, seed_super * 32 + 32));
+        evaluate(seed, load_part(seed));
+
+        // cull passes over a two-level box hierarchy (super-chunk = 32 chunks = 1024 targets; chunk = 32 targets), one box
+        // per lane at either level.  Level 1 tests the group's box: pass 0 takes the chunks whose box overlaps it (LB == 0:
+        // where the neighbours almost always are), pass 1 the remaining chunks with LB <= U, U = max over the group's
+        // queries of their best so far; a super-chunk is opened when its own box passes the same test.  Level 2, for the
+        // level-1 survivors in ascending chunk order: every lane tests its own kQ queries against the chunk box
+        // (point-to-box bound vs that query's best); the chunk is evaluated if any query may gain or tie.
+        // Survivors' box rows and target rows are prefetched into L1 while the tests run.
+        auto group_U = [&]() -> float {
+            float mb = 0.f;
+#pragma unroll
+            for (int q = 0; q < kQ; ++q) mb = fmaxf(mb, best[q]);
+            return warp_max(mb);
+        };
+#pragma unroll 1
+        for (int pass = 0; pass < 2; ++pass) {
+#pragma unroll 1
+            for (int s0 = 0; s0 < nsuper; s0 += 32) {
+                const int sidx = s0 + lane;
+                float slb = CUDART_INF_F;
+                if (sidx < nsuper) {
+                    slb = lb_dist(gap(glo[0], ghi[0], sbox[sidx], sbox[3 * D.St_pad + sidx]),
+                                  gap(glo[1], ghi[1], sbox[D.St_pad + sidx], sbox[4 * D.St_pad + sidx]),
+                                  gap(glo[2], ghi[2], sbox[2 * D.St_pad + sidx], sbox[5 * D.St_pad + sidx]));
+                    if (!(slb >= 0.f)) slb = 0.f;
+                }
+                bool scand = slb == 0.f;
+                if (pass) { const float U = group_U(); scand = slb <= U; }
+                uint32_t ms = __ballot_sync(0xffffffffu, scand);
+                if (lane < 6) {
+                    for (uint32_t t = ms; t; t &= t - 1) prefetch_l1(box + lane * D.Ct_pad + (s0 + __ffs(t) - 1) * 32);
+                }
+                while (ms) {
+                    const int sb = __ffs(ms) - 1;
+                    ms &= ms - 1;
+                    const int c0 = (s0 + sb) * 32;
+                    const int c = c0 + lane;
+                    float lb = CUDART_INF_F;
+                    float bx[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+                    if (c < nchunk && c != seed) {
+#pragma unroll
+                        for (int k = 0; k < 6; ++k) bx[k] = box[k * D.Ct_pad + c];
+                        lb = lb_dist(gap(glo[0], ghi[0], bx[0], bx[3]), gap(glo[1], ghi[1], bx[1], bx[4]),
+                                     gap(glo[2], ghi[2], bx[2], bx[5]));
+                        if (!(lb >= 0.f)) lb = 0.f;          // NaN box -> always a candidate
+                    }
+                    bool cand = lb == 0.f;
+                    if (pass) { const float U = group_U(); cand = lb > 0.f && lb <= U; }   // U first: all lanes shuffle
+                    cand = cand && ((c & 3) == wq);          // this warp's quarter of the target chunks
+                    uint32_t m = __ballot_sync(0xffffffffu, cand);
+                    float4 cur = make_float4(0.f, 0.f, 0.f, 0.f);
+                    if (m) cur = load_part(c0 + __ffs(m) - 1);
+                    while (m) {
+                        const int b = __ffs(m) - 1;
+                        m &= m - 1;
+                        float4 nxt = make_float4(0.f, 0.f, 0.f, 0.f);
+                        if (m) nxt = load_part(c0 + __ffs(m) - 1);
+                        float cb[6];
+#pragma unroll
+                        for (int k = 0; k < 6; ++k) cb[k] = __shfl_sync(0xffffffffu, bx[k], b);
+                        bool want = false;
+#pragma unroll
+                        for (int q = 0; q < kQ; ++q) {
+                            const float lq = lb_dist(gap(fx[q], fx[q], cb[0], cb[3]), gap(fy[q], fy[q], cb[1], cb[4]),
+                                                     gap(fz[q], fz[q], cb[2], cb[5]));
+                            want |= !(lq > best[q]);           // NaN -> evaluate
+                        }
+                        if (__any_sync(0xffffffffu, want)) evaluate(c0 + b, cur);
+                        cur = nxt;
+                    }
+                }
+            }
+        }
+
+        if (n_eval - n_eval_before > n_eval_max) n_eval_max = n_eval - n_eval_before;
+
+        // merge the four warps' results: the minimum distance; a tie when a warp that attains it saw one, or when two warps
+        // attain it in different chunks (every warp evaluates the seed chunk, so the same chunk twice is not a tie)
+#pragma unroll
+        for (int q = 0; q < kQ; ++q) { s_best[wq][q][lane] = best[q]; s_chunk[wq][q][lane] = bchunk[q]; }
+        s_tie[wq][lane] = tie;
+        __syncthreads();
+#pragma unroll
+        for (int q = 0; q < kQ; ++q) {
+            float m = s_best[0][q][lane];
+            int mc = s_chunk[0][q][lane];
+            bool t = (s_tie[0][lane] >> q) & 1u;
+#pragma unroll
+            for (int w2 = 1; w2 < 4; ++w2) {
+                const float b2 = s_best[w2][q][lane];
+                const int c2 = s_chunk[w2][q][lane];
+                const bool t2 = (s_tie[w2][lane] >> q) & 1u;
+                if (b2 < m) { m = b2; mc = c2; t = t2; }
+                else if (b2 == m) { t = t || t2 || (c2 != mc); if (c2 < mc) mc = c2; }
+            }
+            best[q] = m; bchunk[q] = mc;
+            tie = t ? (tie | (1u << q)) : (tie & ~(1u << q));
+        }
+
+        // resolve the lowest original index among the targets at distance best[q], publish (query slot q by warp q mod 4)
+#pragma unroll
+        for (int q = 0; q < kQ; ++q) {
+            const int i = q0 + q * 32 + lane;
+            if ((q & 3) != wq) continue;
+            if (i >= len_q) continue;
+            int bj = 0x7fffffff;
+            auto scan_chunk = [&](int c) {
+                const int j0 = c * kCullChunk;
+                const float4* sx = reinterpret_cast<const float4*>(tsoa + j0);
+                const float4* sy = reinterpret_cast<const float4*>(tsoa + D.Pt_pad + j0);
+                const float4* sz = reinterpret_cast<const float4*>(tsoa + 2 * (size_t)D.Pt_pad + j0);
+                for (int g = 0; g < kCullChunk / 4; ++g) {
+                    const float4 X = __ldg(sx + g), Y = __ldg(sy + g), Z = __ldg(sz + g);
+                    const float tx[4] = {X.x, X.y, X.z, X.w}, ty[4] = {Y.x, Y.y, Y.z, Y.w}, tz[4] = {Z.x, Z.y, Z.z, Z.w};
+#pragma unroll
+                    for (int e = 0; e < 4; ++e) {
+                        const float dd = dist_exact(fx[q], fy[q], fz[q], tx[e], ty[e], tz[e]);
+                        if (dd == best[q] && j0 + g * 4 + e < len_t) bj = min(bj, __ldg(tperm + j0 + g * 4 + e));
+                    }
+                }
+            };
+            if (!((tie >> q) & 1u)) {
+                scan_chunk(bchunk[q]);
+            } else {
+                ++n_slow;
+                for (int c = 0; c < nchunk; ++c) {
+                    const float gx = gap(fx[q], fx[q], box[c], box[3 * D.Ct_pad + c]);
+                    const float gy = gap(fy[q], fy[q], box[D.Ct_pad + c], box[4 * D.Ct_pad + c]);
+                    const float gz = gap(fz[q], fz[q], box[2 * D.Ct_pad + c], box[5 * D.Ct_pad + c]);
+                    const float lb = lb_dist(gx, gy, gz);
+                    if (!(lb > best[q])) scan_chunk(c);
+                }
+            }
+            if (bj == 0x7fffffff) bj = 0;   // no finite distance at all (NaN / inf input)
+            const int orig = __ldg(D.q_perm + (size_t)n * D.Pq_pad + i);
+            D.keys[(size_t)n * D.Pq + orig] =
+                ((unsigned long long)__float_as_uint(best[q]) << 32) | (unsigned long long)(unsigned)bj;
+        }
+    }
+    if (prm.stats) {
+        n_slow = __reduce_add_sync(0xffffffffu, (unsigned)n_slow);
+        if (lane == 0) {
+            if (n_eval) atomicAdd(prm.stats, n_eval * (unsigned long long)(32 * kQ * kCullChunk));
+            if (n_slow) atomicAdd(prm.stats + 1, n_slow);
+            atomicMax(prm.stats + 2, n_eval_max);
+            atomicAdd(prm.stats + 3, n_items);
+        }
+    }
+}
+
 }  // namespace chamfer
 }  // namespace fb
