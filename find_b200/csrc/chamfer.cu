@@ -367,6 +367,143 @@ __global__ void chamfer_bwd_scatter_kernel(const float* __restrict__ a, const fl
     atomicAdd(o + 2, -2.0f * w * (pa[2] - pb[2]));
 }
 
+// ---- fused tail of the training step -------------------------------------------------------------------------------
+// One launch after the kNN: keys -> indices + per-block distance sums (both directions, as knn_finalize), d(w * chamfer)/dx
+// (direct term of the x -> y direction and scatter term of the y -> x direction, both as fp32 atomics into the pre-zeroed
+// grad_x), the colour MSE with its gradient, and — by the last block to finish — the ordered reduction of the block sums
+// and the weighted total (chamfer_reduce_kernel + combine of step.cu, same arithmetic, deterministic order).
+constexpr int kTailSlice = 512;    // points per block of the fused tail (finer than knn_finalize's: one launch does everything)
+static inline int tail_blocks(int P) { return P > 0 ? (P + kTailSlice - 1) / kTailSlice : 1; }
+struct TailParams {
+    FinalizeDir dir[2];
+    const float *x, *y;
+    float* grad_x;
+    float grad_scale;             // w_chamf (upstream gradient of the Chamfer term)
+    int N, P1, P2;
+    const float *col, *col_target;
+    float* grad_col;
+    unsigned long long n_col;     // elements of col (0: no colour term)
+    float w_tex;
+    double* mse_part;             // [gridDim.x * gridDim.y] block sums of (col - target)^2
+    const double *sum_x, *sum_y;
+    float* loss3;                 // [w_chamf * chamfer + w_tex * mse, chamfer, mse]
+    unsigned int* done;           // block counter (zeroed with the kNN work queue)
+};
+
+__global__ void __launch_bounds__(256) chamfer_tail_kernel(const TailParams prm) {
+    fb::pdl_wait_trigger();
+    __shared__ double s_acc[8];
+    __shared__ bool s_last;
+    const int z = blockIdx.z;
+    if (z < 2) {
+        const FinalizeDir& D = prm.dir[z];
+        const int n = blockIdx.y;
+        const int nblk = (D.Pq + kTailSlice - 1) / kTailSlice;
+        if ((int)blockIdx.x < nblk) {
+            const int len_q = D.len_q ? (int)D.len_q[n] : D.Pq;
+            const int len_t = D.len_t ? (int)D.len_t[n] : D.Pt;
+            const int i_end = min(D.Pq, ((int)blockIdx.x + 1) * kTailSlice);
+            const float* a = (z == 0 ? prm.x : prm.y) + (size_t)n * D.Pq * 3;
+            const float* b = (z == 0 ? prm.y : prm.x) + (size_t)n * D.Pt * 3;
+            float* gx = prm.grad_x + (size_t)n * prm.P1 * 3;
+            const float w = prm.grad_scale / ((float)(len_q < 1 ? 1 : len_q) * (float)(prm.N < 1 ? 1 : prm.N));
+            double acc = 0.0;
+            for (int i = blockIdx.x * kTailSlice + threadIdx.x; i < i_end; i += 256) {
+                long long j = 0;
+                if (i < len_q && len_t > 0) {
+                    const unsigned long long k = D.keys[(size_t)n * D.Pq + i];
+                    acc += (double)__uint_as_float((unsigned)(k >> 32));
+                    j = (long long)(k & 0xffffffffull);
+                    const float* pa = a + (size_t)i * 3;
+                    const float* pb = b + (size_t)j * 3;
+                    const float g0 = 2.0f * w * (pa[0] - pb[0]), g1 = 2.0f * w * (pa[1] - pb[1]), g2 = 2.0f * w * (pa[2] - pb[2]);
+                    if (z == 0) { float* o = gx + (size_t)i * 3; atomicAdd(o, g0); atomicAdd(o + 1, g1); atomicAdd(o + 2, g2); }
+                    else { float* o = gx + (size_t)j * 3; atomicAdd(o, -g0); atomicAdd(o + 1, -g1); atomicAdd(o + 2, -g2); }
+                }
+                if (D.idx) D.idx[(size_t)n * D.Pq + i] = j;
+            }
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+            if ((threadIdx.x & 31) == 0) s_acc[threadIdx.x >> 5] = acc;
+            __syncthreads();
+            if (threadIdx.x == 0) {
+                double t = 0.0;
+                for (int wv = 0; wv < 8; ++wv) t += s_acc[wv];
+                D.sums[(size_t)n * nblk + blockIdx.x] = t;
+            }
+        }
+    } else {
+        // colour term: block b of gridDim.x * gridDim.y, grid-stride
+        const unsigned nb = gridDim.x * gridDim.y, bid = blockIdx.x + gridDim.x * blockIdx.y;
+        double acc = 0.0;
+        if (prm.n_col) {
+            const float w2 = 2.0f * (prm.w_tex / (float)prm.n_col);
+            for (unsigned long long i = (unsigned long long)bid * 256 + threadIdx.x; i < prm.n_col; i += (unsigned long long)nb * 256) {
+                const float d = prm.col[i] - prm.col_target[i];
+                prm.grad_col[i] = w2 * d;
+                acc += (double)d * (double)d;
+            }
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+        if ((threadIdx.x & 31) == 0) s_acc[threadIdx.x >> 5] = acc;
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            double t = 0.0;
+            for (int wv = 0; wv < 8; ++wv) t += s_acc[wv];
+            prm.mse_part[bid] = t;
+        }
+    }
+    // last block out: ordered reduction + weighted total
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        __threadfence();
+        const unsigned total = gridDim.x * gridDim.y * gridDim.z;
+        s_last = atomicAdd(prm.done, 1u) == total - 1;
+    }
+    __syncthreads();
+    if (!s_last) return;
+    __threadfence();
+    // The block partials are summed in a FIXED shape (deterministic), with all 256 threads so that the loads overlap: warp wv takes
+    // clouds wv, wv + 8, ...; inside a cloud lane l adds blocks l, l + 32, ..., then a butterfly; warps are combined in order.
+    __shared__ double s_cx[8], s_cy[8], s_m[8];
+    const int lane = threadIdx.x & 31, wv = threadIdx.x >> 5;
+    const int nb1 = (prm.P1 + kTailSlice - 1) / kTailSlice, nb2 = (prm.P2 + kTailSlice - 1) / kTailSlice;
+    const int64_t *lx = prm.dir[0].len_q, *ly = prm.dir[1].len_q;
+    double cx = 0.0, cy = 0.0;
+    for (int n = wv; n < prm.N; n += 8) {
+        double a = 0.0, b = 0.0;
+        for (int k = lane; k < nb1; k += 32) a += __ldcg(prm.sum_x + (size_t)n * nb1 + k);
+        for (int k = lane; k < nb2; k += 32) b += __ldcg(prm.sum_y + (size_t)n * nb2 + k);
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            a += __shfl_xor_sync(0xffffffffu, a, o);
+            b += __shfl_xor_sync(0xffffffffu, b, o);
+        }
+        const long long la = lx ? lx[n] : prm.P1, lb = ly ? ly[n] : prm.P2;
+        cx += a / (double)(la < 1 ? 1 : la);
+        cy += b / (double)(lb < 1 ? 1 : lb);
+    }
+    double m = 0.0;
+    if (prm.n_col) {
+        const unsigned nb = gridDim.x * gridDim.y;
+        for (unsigned k = threadIdx.x; k < nb; k += 256) m += __ldcg(prm.mse_part + k);
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) m += __shfl_xor_sync(0xffffffffu, m, o);
+    }
+    if (lane == 0) { s_cx[wv] = cx; s_cy[wv] = cy; s_m[wv] = m; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double tx = 0.0, ty = 0.0, tm = 0.0;
+        for (int k = 0; k < 8; ++k) { tx += s_cx[k]; ty += s_cy[k]; tm += s_m[k]; }
+        const float c = (float)((tx + ty) / (double)(prm.N < 1 ? 1 : prm.N));
+        const float t = prm.n_col ? (float)(tm / (double)prm.n_col) : 0.f;
+        prm.loss3[0] = prm.grad_scale * c + prm.w_tex * t;
+        prm.loss3[1] = c;
+        prm.loss3[2] = t;
+    }
+}
+
 // ---- host side ------------------------------------------------------------------------------------------
 static inline int round_up(int a, int b) { return (a + b - 1) / b * b; }
 static inline size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }
@@ -413,7 +550,7 @@ static Workspace carve(void* base, int N, int P1, int P2) {
     w.sbox_x = (float*)take((size_t)N * 6 * w.S1p * 4); w.sbox_y = (float*)take((size_t)N * 6 * w.S2p * 4);
     w.cell_x = (int*)take((size_t)N * P1 * 4); w.cell_y = (int*)take((size_t)N * P2 * 4);
     w.rank_x = (int*)take((size_t)N * P1 * 4); w.rank_y = (int*)take((size_t)N * P2 * 4);
-    w.sum_x = (double*)take((size_t)N * fin_blocks(P1) * 8); w.sum_y = (double*)take((size_t)N * fin_blocks(P2) * 8);
+    w.sum_x = (double*)take((size_t)N * tail_blocks(P1) * 8); w.sum_y = (double*)take((size_t)N * tail_blocks(P2) * 8);   // >= fin_blocks
     w.bytes = off;
     return w;
 }
@@ -512,9 +649,13 @@ static int launch_cull_cta(CullParams& prm, int N, int P1, int P2, bool both, cu
     return 0;
 }
 
+struct ZeroJobs { void* ptr[2]; size_t bytes[2]; };      // multiples of 4 bytes
+
 static int run_knn_cull(const float* x, const float* y, const int64_t* lx, const int64_t* ly, int N, int P1, int P2,
-                        bool both, Workspace& w, cudaStream_t st) {
+                        bool both, Workspace& w, cudaStream_t st, const ZeroJobs* zj = nullptr) {
     SortParams sp{};
+    if (zj)
+        for (int k = 0; k < 2; ++k) { sp.zero_ptr[k] = (unsigned*)zj->ptr[k]; sp.zero_words[k] = (unsigned)(zj->bytes[k] / 4); }
     sp.set[0] = SortSet{x, lx, w.soa_x, w.perm_x, w.box_x, w.sbox_x, w.bbmin_x, w.bbmax_x, w.hist_x, w.cell_x, w.rank_x,
                         P1, w.P1p, w.C1p, w.S1p, w.gl1};
     sp.set[1] = SortSet{y, ly, w.soa_y, w.perm_y, w.box_y, w.sbox_y, w.bbmin_y, w.bbmax_y, w.hist_y, w.cell_y, w.rank_y,
@@ -548,7 +689,7 @@ static int run_knn_cull(const float* x, const float* y, const int64_t* lx, const
 
 // Core: runs 1 or 2 directions.  dir 0: queries x (P1) vs targets y (P2); dir 1: queries y vs targets x.
 static int run_knn(const float* x, const float* y, const int64_t* lx, const int64_t* ly, int N, int P1, int P2,
-                   bool both, void* ws_base, size_t ws_bytes, Workspace& w, cudaStream_t st) {
+                   bool both, void* ws_base, size_t ws_bytes, Workspace& w, cudaStream_t st, const ZeroJobs* zj = nullptr) {
     FB_REQUIRE(N >= 0 && P1 >= 0 && P2 >= 0, FINDB200_ERR_SHAPE, "knn: negative size N=%d P1=%d P2=%d", N, P1, P2);
     w = carve(ws_base, N, P1, P2);
     FB_REQUIRE(ws_base != nullptr && ws_bytes >= w.bytes, FINDB200_ERR_WORKSPACE,
@@ -558,9 +699,14 @@ static int run_knn(const float* x, const float* y, const int64_t* lx, const int6
     FB_MARK("knn_memsets", st);
     FB_CUDA(cudaMemsetAsync(w.counter, 0, w.zero_bytes, st));
     FB_CUDA(cudaMemsetAsync(w.bbmin_x, 0xFF, w.ff_bytes, st));
+    if (zj && (P1 == 0 || P2 == 0 || knn_mode() == 1)) {        // no sort kernels on this path: plain memsets
+        for (int k = 0; k < 2; ++k)
+            if (zj->ptr[k] && zj->bytes[k]) FB_CUDA(cudaMemsetAsync(zj->ptr[k], 0, zj->bytes[k], st));
+        zj = nullptr;
+    }
     if (P1 == 0 || P2 == 0) return 0;
     return knn_mode() == 1 ? run_knn_brute(x, y, lx, ly, N, P1, P2, both, w, st)
-                           : run_knn_cull(x, y, lx, ly, N, P1, P2, both, w, st);
+                           : run_knn_cull(x, y, lx, ly, N, P1, P2, both, w, st, zj);
 }
 
 }  // namespace chamfer
@@ -637,6 +783,34 @@ int findb200_chamfer_forward(const float* x, const float* y, const int64_t* x_le
     FB_CUDA(fb::launch_pdl(knn_finalize_kernel, dim3(fin_blocks(P1 > P2 ? P1 : P2), N, 2), 256, 0, st, fp));
     FB_MARK("chamfer_reduce", st);
     FB_CUDA(fb::launch_pdl(chamfer_reduce_kernel, 1, 32, 0, st, w.sum_x, w.sum_y, x_len, y_len, N, P1, P2, loss, nullptr));
+    FB_CUDA(cudaGetLastError());
+    FB_MARK_END(st);
+    return 0;
+}
+
+int findb200_chamfer_train(const float* x, const float* y, const int64_t* x_len, const int64_t* y_len, int N, int P1, int P2,
+                           float w_chamf, const float* col, const float* col_target, size_t n_col, float w_tex, float* grad_x,
+                           float* grad_col, int64_t* idx_x, int64_t* idx_y, float* loss3, double* mse_part, size_t mse_part_bytes,
+                           void* zero_extra, size_t zero_extra_bytes, void* ws, size_t ws_bytes, void* stream) {
+    cudaStream_t st = (cudaStream_t)stream;
+    FB_REQUIRE(x && y && grad_x && loss3 && N >= 1 && P1 >= 1 && P2 >= 1, FINDB200_ERR_ARG, "chamfer_train: bad argument");
+    const bool tex = col && col_target && grad_col && n_col > 0 && w_tex != 0.f;
+    const dim3 grid(tail_blocks(P1 > P2 ? P1 : P2), N, 3);
+    FB_REQUIRE(!tex || (mse_part && mse_part_bytes >= (size_t)grid.x * grid.y * 8), FINDB200_ERR_WORKSPACE, "chamfer_train: mse_part too small");
+    FB_REQUIRE(((size_t)N * P1 * 12) % 4 == 0 && zero_extra_bytes % 4 == 0, FINDB200_ERR_ARG, "chamfer_train: zero regions must be multiples of 4 bytes");
+    ZeroJobs zj{{grad_x, zero_extra}, {(size_t)N * P1 * 12, zero_extra ? zero_extra_bytes : 0}};
+    Workspace w;
+    int rc = run_knn(x, y, x_len, y_len, N, P1, P2, true, ws, ws_bytes, w, st, &zj);
+    if (rc) return rc;
+    TailParams tp{};
+    tp.dir[0] = FinalizeDir{w.keys_x, x_len, y_len, nullptr, idx_x, nullptr, w.sum_x, P1, P2};
+    tp.dir[1] = FinalizeDir{w.keys_y, y_len, x_len, nullptr, idx_y, nullptr, w.sum_y, P2, P1};
+    tp.x = x; tp.y = y; tp.grad_x = grad_x; tp.grad_scale = w_chamf; tp.N = N; tp.P1 = P1; tp.P2 = P2;
+    tp.col = col; tp.col_target = col_target; tp.grad_col = grad_col; tp.n_col = tex ? (unsigned long long)n_col : 0ull; tp.w_tex = tex ? w_tex : 0.f;
+    tp.mse_part = mse_part; tp.sum_x = w.sum_x; tp.sum_y = w.sum_y; tp.loss3 = loss3;
+    tp.done = w.counter + 32;                      // inside the zeroed header of the kNN workspace (queue at +0, stats at +64)
+    FB_MARK("chamfer_tail", st);
+    FB_CUDA(fb::launch_pdl(chamfer_tail_kernel, grid, 256, 0, st, tp));
     FB_CUDA(cudaGetLastError());
     FB_MARK_END(st);
     return 0;

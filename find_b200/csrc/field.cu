@@ -527,6 +527,17 @@ static void fill_chain_common(ChainParams& C, const findb200_field_params* p, co
     C.dbg_flags = g_chain_dbg_flags;
 }
 
+}  // namespace field
+}  // namespace fb
+namespace fb {
+namespace field {
+thread_local bool g_field_bwd_prezeroed = false;
+void field_bwd_zero_region(int nfeet, int V, int pos_shared, size_t* offset, size_t* bytes) {
+    const Workspace w = carve(nfeet, V, pos_shared, 1);
+    *offset = w.scal;
+    *bytes = (w.colsum - w.scal) + cs_total(nfeet) * 4;
+}
+
 static int run_pack(const findb200_field_params* p, const Workspace& w, uint8_t* ws, cudaStream_t st) {
     const PackLayout L = make_layout();
     PackParams PP;
@@ -639,11 +650,13 @@ int findb200_field_backward(const findb200_field_params* p, const float* pos, in
     const size_t head_tiles = (size_t)B * w.tpf2;
 
     // scalars, per-foot sums, column sums, d(pre-tanh) images start from zero
-    FB_MARK("bwd_memsets", st);
     // one memset: global max | per-foot reg sums | column sums (adjacent in the workspace).  The d(pre-tanh) images need no
     // clearing: head_bwd rewrites columns 0..15 of every row each step, and whatever sits in columns 16..63 only reaches
     // rows >= 16 of the 256 -> 3 layers' dW partial, which reduce_dw never reads (J.rows = 3).
-    FB_CUDA(cudaMemsetAsync(ws + w.scal, 0, (w.colsum - w.scal) + cs_total(B) * 4, st));
+    if (!g_field_bwd_prezeroed) {
+        FB_MARK("bwd_memsets", st);
+        FB_CUDA(cudaMemsetAsync(ws + w.scal, 0, (w.colsum - w.scal) + cs_total(B) * 4, st));
+    }
 
     GradPrepParams GP{pos, disp, col, reg, p->avg_col, grad_disp, grad_col, grad_verts, B, V, pos_shared,
                       (float*)(ws + w.dovals), (uint32_t*)(ws + w.scal), (float*)(ws + w.regsums)};

@@ -84,5 +84,11 @@ struct Workspace {
 
 constexpr int kMaxDwCtas = 192;
 
+// step.cu -> field.cu (inside the library, not part of the C ABI): the region of the field workspace that
+// findb200_field_backward clears before it accumulates (global max | per-foot reg sums | column sums), so that a fused step
+// can have an earlier kernel clear it and tell the backward so.
+void field_bwd_zero_region(int nfeet, int V, int pos_shared, size_t* offset, size_t* bytes);
+extern thread_local bool g_field_bwd_prezeroed;
+
 }  // namespace field
 }  // namespace fb

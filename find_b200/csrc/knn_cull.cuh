@@ -41,7 +41,9 @@ struct SortSet {
     int* rank;              // [N][P]         arrival rank of point i inside its cell
     int P, Ppad, Cpad, Spad, glog2;
 };
-struct SortParams { SortSet set[2]; };
+// zero[k]: an optional region the FIRST sort kernel clears (4-byte words) while it computes the bounding boxes: buffers that
+// later kernels of a fused training step accumulate into, cleared here instead of by separate memset nodes
+struct SortParams { SortSet set[2]; unsigned* zero_ptr[2]; unsigned zero_words[2]; };
 
 FB_DEVINL unsigned enc_ord(float f) {       // monotone float -> uint
     const unsigned u = __float_as_uint(f);
@@ -90,6 +92,14 @@ FB_DEVINL int set_len(const SortSet& S, int n) {
 // 1. bounding box per cloud.  grid (ceil(maxP/1024), N, 2), block 256, 4 points per thread.
 __global__ void __launch_bounds__(256) cloud_bbox_kernel(const SortParams prm) {
     fb::pdl_wait_trigger();
+    {
+        const unsigned nthreads = gridDim.x * gridDim.y * gridDim.z * 256u;
+        const unsigned t = (blockIdx.x + gridDim.x * (blockIdx.y + gridDim.y * blockIdx.z)) * 256u + threadIdx.x;
+#pragma unroll
+        for (int k = 0; k < 2; ++k)
+            if (prm.zero_ptr[k])
+                for (unsigned i = t; i < prm.zero_words[k]; i += nthreads) prm.zero_ptr[k][i] = 0u;
+    }
     const SortSet& S = prm.set[blockIdx.z];
     const int n = blockIdx.y;
     const int len = set_len(S, n);

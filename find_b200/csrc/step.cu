@@ -7,6 +7,7 @@
 // It only composes the entry points of chamfer.cu / field.cu; the kernels are theirs.
 #include "common.cuh"
 #include "../../include/find_b200.h"
+#include "field.cuh"
 
 namespace fb {
 namespace step {
@@ -15,7 +16,7 @@ static inline size_t align1k(size_t x) { return (x + 1023) & ~(size_t)1023; }
 
 struct Carve {
     size_t field, knn, idx_x, idx_y, grad_verts, grad_col, sums, total;
-    size_t field_bytes, knn_bytes;
+    size_t field_bytes, knn_bytes, mse_part_bytes;
     // mesh terms (findb200_train_step_mesh): surface samples of the deformed template and the smoothness workspace
     size_t samples, fidx, bary, grad_samples, sample_ws, smooth_ws, smooth2;
     size_t sample_ws_bytes, smooth_ws_bytes;
@@ -33,7 +34,8 @@ static Carve carve(int B, int V, int P2, int S = 0, int nnz = 0, int F = 0) {
     c.idx_y = take((size_t)B * P2 * 8);
     c.grad_verts = take((size_t)B * V * 12);
     c.grad_col = take((size_t)B * V * 12);
-    c.sums = take(1024);
+    c.mse_part_bytes = (size_t)8 * B * (((P1 > P2 ? P1 : P2) + 511) / 512);
+    c.sums = take(1024 + c.mse_part_bytes);     // mse sum | chamfer scalar | block partials of the colour term (fused tail)
     if (S > 0) {
         c.samples = take((size_t)B * S * 12);
         c.fidx = take((size_t)B * S * 8);
@@ -162,6 +164,23 @@ static int run_step(const findb200_field_params* p, const float* template_pos, c
         if (rc) return rc;
         rc = findb200_sample_points_backward(grad_samples, mt->faces, 1, fidx, bary, nfeet, V, mt->F, S, 1.0f, 0, grad_verts, stream);
         if (rc) return rc;
+    } else if (!smooth) {
+        // plain branch (losses.py:87-88), everything after the kNN in ONE launch: indices, loss3, d/d(verts), colour MSE and its
+        // gradient; the sort pass of the kNN also clears grad_verts and the accumulators of the field backward
+        const size_t n = (size_t)nfeet * V * 3;
+        const bool tex = col_target != nullptr && w_tex != 0.f;
+        size_t zoff = 0, zbytes = 0;
+        fb::field::field_bwd_zero_region(nfeet, V, 1, &zoff, &zbytes);
+        rc = findb200_chamfer_train(verts, target, nullptr, target_len, nfeet, V, P2, w_chamf, tex ? col : nullptr, col_target, n,
+                                    tex ? w_tex : 0.f, grad_verts, grad_col, idx_x, idx_y, loss3, (double*)(ws + c.sums + 1024), c.mse_part_bytes,
+                                    ws + c.field + zoff, zbytes, ws + c.knn, c.knn_bytes, stream);
+        if (rc) return rc;
+        fb::field::g_field_bwd_prezeroed = true;
+        rc = findb200_field_backward(p, template_pos, 1, z_shape, z_pose, z_tex, reg, nfeet, V, disp, col, nullptr,
+                                     tex ? grad_col : nullptr, grad_verts, gw, gz_shape, gz_pose, gz_tex, greg,
+                                     ws + c.field, c.field_bytes, stream);
+        fb::field::g_field_bwd_prezeroed = false;
+        return rc;
     } else {
         rc = findb200_chamfer_forward(verts, target, nullptr, target_len, nfeet, V, P2, chamf, nullptr, idx_x, nullptr, idx_y,
                                       ws + c.knn, c.knn_bytes, stream);
