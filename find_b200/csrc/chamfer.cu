@@ -698,7 +698,9 @@ static int run_knn(const float* x, const float* y, const int64_t* lx, const int6
     // queue counter + stats = 0, keys = 0xFF.. (identity of atomicMin; also what an unreachable query keeps)
     FB_MARK("knn_memsets", st);
     FB_CUDA(cudaMemsetAsync(w.counter, 0, w.zero_bytes, st));
-    FB_CUDA(cudaMemsetAsync(w.bbmin_x, 0xFF, w.ff_bytes, st));
+    // the culled kernels store every reachable query's key; only the brute-force split path combines with atomicMin and needs
+    // the keys preset to the identity — for the cull path the 0xFF fill shrinks to the two bounding-box minima
+    FB_CUDA(cudaMemsetAsync(w.bbmin_x, 0xFF, knn_mode() == 1 ? w.ff_bytes : (size_t)((char*)w.keys_x - (char*)w.bbmin_x), st));
     if (zj && (P1 == 0 || P2 == 0 || knn_mode() == 1)) {        // no sort kernels on this path: plain memsets
         for (int k = 0; k < 2; ++k)
             if (zj->ptr[k] && zj->bytes[k]) FB_CUDA(cudaMemsetAsync(zj->ptr[k], 0, zj->bytes[k], st));

@@ -76,9 +76,8 @@ struct PackJob {
 };
 struct PackParams { PackJob j[2 * P_COUNT]; int n; uint8_t* dst; };
 
-__global__ void __launch_bounds__(256) pack_weights_kernel(const __grid_constant__ PackParams P) {
-    fb::pdl_wait_trigger();
-    const PackJob& J = P.j[blockIdx.y];
+__device__ __forceinline__ void pack_weights_body(const PackParams& P, int job) {
+    const PackJob& J = P.j[job];
     const int per_chunk = J.img_rows * 8;
     const int total = per_chunk * J.n_chunks;
     for (int id = blockIdx.x * blockDim.x + threadIdx.x; id < total; id += gridDim.x * blockDim.x) {
@@ -115,11 +114,9 @@ struct LatentBiasParams {
     float* out;
 };
 // one warp per output row n: lanes stride over the latent columns (coalesced weight reads), shuffle-reduce
-__global__ void __launch_bounds__(256) latent_bias_kernel(const LatentBiasParams P) {
-    fb::pdl_wait_trigger();
+__device__ __forceinline__ void latent_bias_body(const LatentBiasParams& P, int b, int head, int zslot) {
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-    const int b = blockIdx.x, head = blockIdx.y;
-    for (int n = blockIdx.z * 8 + wid; n < kW; n += gridDim.z * 8) {
+    for (int n = zslot * 8 + wid; n < kW; n += 8 * 8) {
         float acc = 0.f;
         if (head == 0) {
             const int L = P.S + P.Pz;
@@ -134,6 +131,16 @@ __global__ void __launch_bounds__(256) latent_bias_kernel(const LatentBiasParams
         for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
         if (lane == 0) P.out[((size_t)head * P.B + b) * kW + n] = acc + (head ? P.bc[n] : P.bd[n]);
     }
+}
+
+// pack_weights + latent_bias in one launch (they are independent): blockIdx.y < P.n is a pack job; the remaining rows of the
+// grid are the (foot, head, row-slot) blocks of latent_bias, numbered row-major
+__global__ void __launch_bounds__(256) field_prologue_kernel(const __grid_constant__ PackParams P, const LatentBiasParams L) {
+    fb::pdl_wait_trigger();
+    if ((int)blockIdx.y < P.n) { pack_weights_body(P, blockIdx.y); return; }
+    const int lb = ((int)blockIdx.y - P.n) * gridDim.x + blockIdx.x;
+    if (lb >= L.B * 2 * 8) return;
+    latent_bias_body(L, lb % L.B, (lb / L.B) & 1, lb / (2 * L.B));
 }
 
 __device__ __forceinline__ void euler_xyz_d(const float* e, float (&R)[3][3]) {
@@ -248,9 +255,8 @@ struct ReduceJob {
 constexpr int kMaxReduceJobs = 20;
 struct ReduceParams { ReduceJob j[kMaxReduceJobs]; int n; const uint32_t* maxabs; };
 
-__global__ void __launch_bounds__(256) reduce_dw_kernel(const __grid_constant__ ReduceParams P) {
-    fb::pdl_wait_trigger();
-    const ReduceJob& J = P.j[blockIdx.y];
+__device__ __forceinline__ void reduce_dw_body(const ReduceParams& P, int job) {
+    const ReduceJob& J = P.j[job];
     if (!J.dst) return;
     const float inv = inv_grad_scale(*P.maxabs);
     if ((J.cols & 3) == 0 && (J.src_col0 & 3) == 0) {
@@ -313,10 +319,8 @@ __host__ __device__ inline size_t cs_out(int head, int B) { return (size_t)2 * B
 __host__ __device__ inline size_t cs_trunk(int l, int B) { return (size_t)2 * B * kW + 4 * kW + 32 + (size_t)l * kW; }
 __host__ __device__ inline size_t cs_total(int B) { return (size_t)2 * B * kW + 4 * kW + 32 + 5 * kW; }
 
-__global__ void __launch_bounds__(256) finish_small_kernel(const __grid_constant__ FinishParams P) {
-    fb::pdl_wait_trigger();
+__device__ __forceinline__ void finish_small_body(const FinishParams& P, int sec) {
     const float inv = inv_grad_scale(*P.maxabs);
-    const int sec = blockIdx.y;
     const int id = blockIdx.x * blockDim.x + threadIdx.x;
     if (sec == 0) {
         // bias gradients (13 vectors) : id = param * 256 + n
@@ -457,6 +461,13 @@ __global__ void __launch_bounds__(256) sum_feet_kernel(const uint8_t* __restrict
     reinterpret_cast<uint4*>(hsum + (size_t)hd * tpf2 * kTileBytes)[j] = o;
 }
 
+// reduce_dw + finish_small in one launch: blockIdx.y < R.n is a reduce job, the rest are the sections of finish_small
+__global__ void __launch_bounds__(256) reduce_finish_kernel(const __grid_constant__ ReduceParams R, const __grid_constant__ FinishParams F) {
+    fb::pdl_wait_trigger();
+    if ((int)blockIdx.y < R.n) reduce_dw_body(R, blockIdx.y);
+    else finish_small_body(F, (int)blockIdx.y - R.n);
+}
+
 // ---- workspace --------------------------------------------------------------------------------------------
 static Workspace carve(int B, int V, int shared, int for_backward) {
     Workspace w;
@@ -538,7 +549,7 @@ void field_bwd_zero_region(int nfeet, int V, int pos_shared, size_t* offset, siz
     *bytes = (w.colsum - w.scal) + cs_total(nfeet) * 4;
 }
 
-static int run_pack(const findb200_field_params* p, const Workspace& w, uint8_t* ws, cudaStream_t st) {
+static int run_pack(const findb200_field_params* p, const Workspace& w, uint8_t* ws, const LatentBiasParams& LB, cudaStream_t st) {
     const PackLayout L = make_layout();
     PackParams PP;
     memset(&PP, 0, sizeof(PP));
@@ -559,8 +570,9 @@ static int run_pack(const findb200_field_params* p, const Workspace& w, uint8_t*
         J.transpose = 1; J.perm = 0; J.img_rows = 256; J.n_chunks = L.bwd[i].n_chunks; J.dst_off = L.bwd[i].off;
     }
     PP.n = n;
-    FB_MARK("pack_weights", st);
-    FB_CUDA(fb::launch_pdl(pack_weights_kernel, dim3(36, n), 256, 0, st, PP));
+    FB_MARK("field_prologue", st);
+    const int lb_rows = cdiv(LB.B * 2 * 8, 36);
+    FB_CUDA(fb::launch_pdl(field_prologue_kernel, dim3(36, n + lb_rows), 256, 0, st, PP, LB));
     FB_CUDA(cudaGetLastError());
     return 0;
 }
@@ -595,13 +607,10 @@ int findb200_field_forward(const findb200_field_params* p, const float* pos, int
     uint8_t* ws = (uint8_t*)ws_;
     const int sms = num_sms();
 
-    rc = run_pack(p, w, ws, st);
-    if (rc) return rc;
     LatentBiasParams LB{p->weight[P_D1], p->bias[P_D1], p->weight[P_C1], p->bias[P_C1], z_shape, z_pose, z_tex,
                         p->shapevec_size, p->posevec_size, p->texvec_size, B, (float*)(ws + w.biasfoot)};
-    FB_MARK("latent_bias", st);
-    FB_CUDA(fb::launch_pdl(latent_bias_kernel, dim3(B, 2, 8), 256, 0, st, LB));
-    FB_CUDA(cudaGetLastError());
+    rc = run_pack(p, w, ws, LB, st);
+    if (rc) return rc;
 
     ChainParams C;
     fill_chain_common(C, p, w, ws, B, V, pos_shared);
@@ -830,9 +839,9 @@ int findb200_field_backward(const findb200_field_params* p, const float* pos, in
     rc = launch_dw(D, n_ctas, st);
     if (rc) return rc;
 
+    ReduceParams R;
+    memset(&R, 0, sizeof(R));
     if (!frozen) {
-        ReduceParams R;
-        memset(&R, 0, sizeof(R));
         R.maxabs = (const uint32_t*)(ws + w.scal);
         const int in_dims[P_COUNT] = {kEnc, kW, kW, kW, kW, kW + p->shapevec_size + p->posevec_size, kW, kW, kW,
                                       kW + p->texvec_size, kW, kW, kW};
@@ -857,9 +866,6 @@ int findb200_field_backward(const findb200_field_params* p, const float* pos, in
             }
         }
         R.n = nj;
-        FB_MARK("reduce_dw", st);
-        FB_CUDA(fb::launch_pdl(reduce_dw_kernel, dim3(64, nj), 256, 0, st, R));
-        FB_CUDA(cudaGetLastError());
     }
 
     FinishParams F;
@@ -877,8 +883,12 @@ int findb200_field_backward(const findb200_field_params* p, const float* pos, in
     if (kW * Lmax > maxid) maxid = kW * Lmax;
     if (B * (F.S + F.Pz + F.T) * 8 > maxid) maxid = B * (F.S + F.Pz + F.T) * 8;     // section 3: 32 (b, j) pairs per block
     if (B > maxid) maxid = B;
-    FB_MARK("finish_small", st);
-    FB_CUDA(fb::launch_pdl(finish_small_kernel, dim3(cdiv(maxid, 256), 5), 256, 0, st, F));
+    FB_MARK("reduce_finish", st);
+    {
+        int gx = cdiv(maxid, 256);
+        if (R.n > 0 && gx < 64) gx = 64;
+        FB_CUDA(fb::launch_pdl(reduce_finish_kernel, dim3(gx, R.n + 5), 256, 0, st, R, F));
+    }
     FB_CUDA(cudaGetLastError());
     FB_MARK_END(st);
     return 0;
