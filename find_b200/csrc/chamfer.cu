@@ -73,6 +73,7 @@ FB_DEVINL float dist_exact(float qx, float qy, float qz, float tx, float ty, flo
 
 }  // namespace chamfer
 }  // namespace fb
+namespace fb { namespace field { extern unsigned long long* g_chain_dbg; } }
 #include "knn_cull.cuh"
 namespace fb {
 namespace chamfer {
@@ -651,6 +652,16 @@ static int launch_cull_cta(CullParams& prm, int N, int P1, int P2, bool both, cu
 
 struct ZeroJobs { void* ptr[2]; size_t bytes[2]; };      // multiples of 4 bytes
 
+// clouds up to this many points are sorted by cloud_sort_cluster_kernel (one launch); larger ones by the six-kernel path.
+// Default 0 = never: measured on cfg2 the one-launch sort takes 21-38 us (seven latency-bound phases behind cluster barriers)
+// against ~30 us for the six short kernels inside the step graph, so it only saves launches, not time (profiles/r2_tail_fusion.md).
+static int g_sort_cta_max = -1;
+static bool sort_in_one_cta(int P1, int P2) {
+    if (g_sort_cta_max < 0) { const char* e = getenv("FINDB200_SORT_CTA_MAX"); g_sort_cta_max = e ? atoi(e) : 0; }
+    const int Pm = P1 > P2 ? P1 : P2;
+    return Pm <= g_sort_cta_max && grid_log2(Pm) <= 4;       // the cluster kernel keeps ncell / 8 <= 1024 cells per CTA
+}
+
 static int run_knn_cull(const float* x, const float* y, const int64_t* lx, const int64_t* ly, int N, int P1, int P2,
                         bool both, Workspace& w, cudaStream_t st, const ZeroJobs* zj = nullptr) {
     SortParams sp{};
@@ -661,6 +672,23 @@ static int run_knn_cull(const float* x, const float* y, const int64_t* lx, const
     sp.set[1] = SortSet{y, ly, w.soa_y, w.perm_y, w.box_y, w.sbox_y, w.bbmin_y, w.bbmax_y, w.hist_y, w.cell_y, w.rank_y,
                         P2, w.P2p, w.C2p, w.S2p, w.gl2};
     const int Pm = P1 > P2 ? P1 : P2, Ppm = w.P1p > w.P2p ? w.P1p : w.P2p;
+    if (sort_in_one_cta(P1, P2)) {
+        // small clouds: the whole sort (and the clearing of the header / the caller's regions) in one launch, one cluster per cloud
+        const int gl = w.gl1 > w.gl2 ? w.gl1 : w.gl2;
+        const size_t smem = ((size_t)4 << (3 * gl)) / kSortCluster;
+        FB_MARK("cloud_sort", st);
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3(kSortCluster * N, 2); cfg.blockDim = dim3(1024); cfg.dynamicSmemBytes = smem; cfg.stream = st;
+        cudaLaunchAttribute at[2];
+        at[0].id = cudaLaunchAttributeClusterDimension;
+        at[0].val.clusterDim.x = kSortCluster; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+        at[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        at[1].val.programmaticStreamSerializationAllowed = 1;
+        cfg.attrs = at;
+        cfg.numAttrs = fb::pdl_enabled() ? 2 : 1;
+        FB_CUDA(cudaLaunchKernelEx(&cfg, cloud_sort_cluster_kernel, sp, (unsigned*)w.counter, fb::field::g_chain_dbg));
+        FB_CUDA(cudaGetLastError());
+    } else {
     FB_MARK("sort_bbox", st);
     FB_CUDA(fb::launch_pdl(cloud_bbox_kernel, dim3((Pm + 1023) / 1024, N, 2), 256, 0, st, sp));
     FB_MARK("sort_hist", st);
@@ -673,6 +701,7 @@ static int run_knn_cull(const float* x, const float* y, const int64_t* lx, const
     FB_CUDA(fb::launch_pdl(cloud_boxes_kernel, dim3((Ppm / kCullChunk + 7) / 8, N, 2), 256, 0, st, sp));
     FB_CUDA(fb::launch_pdl(cloud_superboxes_kernel, dim3((Ppm / kCullChunk / 32 + 8) / 8, N, 2), 256, 0, st, sp));
     FB_CUDA(cudaGetLastError());
+    }
 
     CullParams prm{};
     prm.N = N; prm.counter = w.counter; prm.stats = w.stats; prm.ndir = both ? 2 : 1;
@@ -695,6 +724,8 @@ static int run_knn(const float* x, const float* y, const int64_t* lx, const int6
     FB_REQUIRE(ws_base != nullptr && ws_bytes >= w.bytes, FINDB200_ERR_WORKSPACE,
                "knn: workspace too small (%zu < %zu bytes)", ws_bytes, w.bytes);
     if (N == 0 || (P1 == 0 && P2 == 0)) return 0;
+    if (knn_mode() != 1 && P1 > 0 && P2 > 0 && sort_in_one_cta(P1, P2))       // the one-launch sort clears what it needs itself
+        return run_knn_cull(x, y, lx, ly, N, P1, P2, both, w, st, zj);
     // queue counter + stats = 0, keys = 0xFF.. (identity of atomicMin; also what an unreachable query keeps)
     FB_MARK("knn_memsets", st);
     FB_CUDA(cudaMemsetAsync(w.counter, 0, w.zero_bytes, st));
@@ -722,6 +753,11 @@ extern "C" {
 int findb200_set_knn_mode(int mode, int kq) {
     FB_REQUIRE((mode == 0 || mode == 1 || mode == 2) && (kq == 0 || kq == 1 || kq == 2 || kq == 4), FINDB200_ERR_ARG, "set_knn_mode: mode 0/1/2, kq 0/1/2/4");
     g_knn_mode = mode; g_cull_kq = kq;
+    return 0;
+}
+
+int findb200_set_sort_cta_max(int max_points) {        // < 0: default (FINDB200_SORT_CTA_MAX, else 0 = always the six-kernel sort)
+    g_sort_cta_max = max_points;
     return 0;
 }
 

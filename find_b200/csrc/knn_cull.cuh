@@ -289,6 +289,237 @@ __global__ void __launch_bounds__(256) cloud_superboxes_kernel(const SortParams 
     }
 }
 
+// ---- the whole sort of one cloud in ONE launch: a cluster of 8 CTAs per cloud -----------------------------------------
+// Steps 1-6 above need a grid-wide dependency between them, i.e. six launches (plus the memsets of the histogram and the
+// bounding-box cells) of a few microseconds each, all on the critical path of a training step.  For clouds of up to a few
+// ten thousand points one thread-block cluster per (cloud, set) does all of it: 8 x 1024 threads hold one or two points
+// each, the histogram is distributed over the eight shared memories (CTA r owns cells [r, r + 1) * ncell / 8; arrival ranks
+// come from atom.shared::cluster), and barrier.cluster separates the phases.  The result equals the six-kernel path up to
+// the arrival order inside a grid cell, which the kNN does not depend on.  Also clears the caller's zero regions and the
+// 256-byte header of the kNN workspace (work queue, statistics, tail counter).
+// grid (8 N, 2), cluster (8, 1, 1), block 1024, dynamic shared memory = 4 * ncell / 8 bytes; needs glog2 <= 4.
+constexpr int kSortCluster = 8;
+FB_DEVINL int dsmem_atomic_add(uint32_t cluster_addr, int v) {
+    int old;
+    asm volatile("atom.shared::cluster.add.u32 %0, [%1], %2;" : "=r"(old) : "r"(cluster_addr), "r"(v) : "memory");
+    return old;
+}
+FB_DEVINL int dsmem_ld_i32(uint32_t cluster_addr) {
+    int v;
+    asm volatile("ld.shared::cluster.u32 %0, [%1];" : "=r"(v) : "r"(cluster_addr) : "memory");
+    return v;
+}
+FB_DEVINL void dsmem_st_b32(uint32_t cluster_addr, uint32_t v) {
+    asm volatile("st.shared::cluster.u32 [%0], %1;" ::"r"(cluster_addr), "r"(v) : "memory");
+}
+
+__global__ void __launch_bounds__(1024) cloud_sort_cluster_kernel(const SortParams prm, unsigned* __restrict__ header64, unsigned long long* dbg) {
+    fb::pdl_wait_trigger();
+    auto stamp = [&](int k) { if (dbg && blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 0) { unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); dbg[400 + k] = t; } };
+    stamp(0);
+    extern __shared__ int s_hist[];                 // the ncell / 8 cells this CTA owns: counts, then start offsets
+    __shared__ float s_red[32][6];
+    __shared__ float s_bb8[kSortCluster][6];        // every CTA's partial bounding box, broadcast to every CTA
+    __shared__ int s_tot8[kSortCluster];            // every CTA's cell-count total, broadcast to every CTA
+    __shared__ int s_wsum[32];
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    const int crank = (int)cluster_ctarank();
+    const int ctid = crank * 1024 + tid, cthreads = kSortCluster * 1024;
+    {
+        const unsigned nthreads = gridDim.x * gridDim.y * 1024u;
+        const unsigned t = (blockIdx.x + gridDim.x * blockIdx.y) * 1024u + tid;
+#pragma unroll
+        for (int k = 0; k < 2; ++k)
+            if (prm.zero_ptr[k])
+                for (unsigned i = t; i < prm.zero_words[k]; i += nthreads) prm.zero_ptr[k][i] = 0u;
+        if (header64 && t < 64u) header64[t] = 0u;
+    }
+    stamp(1);
+    const SortSet& S = prm.set[blockIdx.y];
+    if (S.P <= 0) return;                            // the whole cluster leaves together
+    const int n = blockIdx.x / kSortCluster;
+    const int len = set_len(S, n);
+    const int ncell = 1 << (3 * S.glog2), G = 1 << S.glog2;
+    const int cells_per = ncell / kSortCluster;      // 64 or 512 (<= 1024 threads)
+    const float* aos = S.aos + (size_t)n * S.P * 3;
+    if (tid < cells_per) s_hist[tid] = 0;
+
+    // 1. bounding box: local reduction, then all-to-all through distributed shared memory
+    float lo[3] = {CUDART_INF_F, CUDART_INF_F, CUDART_INF_F}, hi[3] = {-CUDART_INF_F, -CUDART_INF_F, -CUDART_INF_F};
+    for (int i = ctid; i < len; i += cthreads) {
+#pragma unroll
+        for (int k = 0; k < 3; ++k) { const float v = aos[(size_t)i * 3 + k]; lo[k] = fminf(lo[k], v); hi[k] = fmaxf(hi[k], v); }
+    }
+#pragma unroll
+    for (int k = 0; k < 3; ++k)
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            lo[k] = fminf(lo[k], __shfl_xor_sync(0xffffffffu, lo[k], o));
+            hi[k] = fmaxf(hi[k], __shfl_xor_sync(0xffffffffu, hi[k], o));
+        }
+    if (lane == 0) {
+#pragma unroll
+        for (int k = 0; k < 3; ++k) { s_red[wid][k] = lo[k]; s_red[wid][3 + k] = hi[k]; }
+    }
+    __syncthreads();
+    if (tid < 6 * kSortCluster) {
+        const int k = tid % 6, r = tid / 6;          // value k of this CTA's box -> CTA r
+        float v = s_red[0][k];
+        for (int w = 1; w < 32; ++w) v = k < 3 ? fminf(v, s_red[w][k]) : fmaxf(v, s_red[w][k]);
+        dsmem_st_b32(mapa_u32(smem_u32(&s_bb8[crank][k]), (uint32_t)r), __float_as_uint(v));
+    }
+    cluster_sync_all();
+    CloudGrid g;
+    {
+        float ext = 0.f;
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+            float a = s_bb8[0][k], b = s_bb8[0][3 + k];
+#pragma unroll
+            for (int r = 1; r < kSortCluster; ++r) { a = fminf(a, s_bb8[r][k]); b = fmaxf(b, s_bb8[r][3 + k]); }
+            const float l = a < CUDART_INF_F ? a : 0.f, h = b > -CUDART_INF_F ? b : 0.f;    // empty / NaN-only cloud -> 0, as cloud_grid
+            g.lo[k] = l;
+            ext = fmaxf(ext, h - l);
+        }
+        g.inv_h = (ext > 0.f && ext < CUDART_INF_F) ? (float)G / ext : 0.f;
+        if (!(g.inv_h < CUDART_INF_F)) g.inv_h = 0.f;
+    }
+
+    stamp(2);
+    // 2. cell + arrival rank.  Histogram cell c lives in CTA c / cells_per (atom.shared::cluster).  Neighbouring points of a
+    //    mesh-ordered cloud fall into the same cell, and same-address atomics serialise, so a warp first groups its lanes by
+    //    cell (match.any) and issues ONE atomic per distinct cell; the lanes of a group take consecutive ranks.
+    const uint32_t hist_s = smem_u32(s_hist);
+    int* cellv = S.cell + (size_t)n * S.P;
+    int* rankv = S.rank + (size_t)n * S.P;
+    for (int it = 0; it * cthreads < len; ++it) {
+        const int i = it * cthreads + ctid;
+        const bool valid = i < len;
+        int cell = 0x40000000 | lane;                 // a key of its own for idle lanes
+        if (valid) {
+            const float* p = aos + (size_t)i * 3;
+            const uint32_t cx = cell_coord(p[0], g.lo[0], g.inv_h, G), cy = cell_coord(p[1], g.lo[1], g.inv_h, G),
+                           cz = cell_coord(p[2], g.lo[2], g.inv_h, G);
+            cell = (int)hilbert3(cx, cy, cz, S.glog2);
+        }
+        const unsigned m = __match_any_sync(0xffffffffu, cell);
+        const int leader = __ffs(m) - 1;
+        int base = 0;
+        if (valid && lane == leader)
+            base = dsmem_atomic_add(mapa_u32(hist_s + (uint32_t)(cell % cells_per) * 4u, (uint32_t)(cell / cells_per)), __popc(m));
+        base = __shfl_sync(0xffffffffu, base, leader);
+        if (valid) {
+            cellv[i] = cell;
+            rankv[i] = base + __popc(m & ((1u << lane) - 1u));
+        }
+    }
+    cluster_sync_all();
+
+    stamp(3);
+    // 3. exclusive scan: inside the CTA (one cell per thread), then the CTA totals
+    {
+        const int v = tid < cells_per ? s_hist[tid] : 0;
+        int inc = v;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int u = __shfl_up_sync(0xffffffffu, inc, o);
+            if (lane >= o) inc += u;
+        }
+        if (lane == 31) s_wsum[wid] = inc;
+        __syncthreads();
+        if (wid == 0) {
+            const int t = s_wsum[lane];
+            int w = t;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const int u = __shfl_up_sync(0xffffffffu, w, o);
+                if (lane >= o) w += u;
+            }
+            s_wsum[lane] = w - t;
+            if (lane == 31) {                        // w = this CTA's total -> every CTA
+                for (int r = 0; r < kSortCluster; ++r) dsmem_st_b32(mapa_u32(smem_u32(&s_tot8[crank]), (uint32_t)r), (uint32_t)w);
+            }
+        }
+        cluster_sync_all();
+        int off = 0;
+        for (int r = 0; r < crank; ++r) off += s_tot8[r];
+        if (tid < cells_per) s_hist[tid] = off + s_wsum[wid] + inc - v;
+    }
+    cluster_sync_all();     // start offsets of every CTA are final before anyone reads them remotely
+
+    stamp(4);
+    // 4. scatter into curve order (start offsets read from the owning CTA, once per distinct cell of a warp); +inf padding
+    float* soa = S.soa + (size_t)n * 3 * S.Ppad;
+    int* perm = S.perm + (size_t)n * S.Ppad;
+    for (int it = 0; it * cthreads < len; ++it) {
+        const int i = it * cthreads + ctid;
+        const bool valid = i < len;
+        const int cell = valid ? cellv[i] : (0x40000000 | lane);
+        const unsigned m = __match_any_sync(0xffffffffu, cell);
+        const int leader = __ffs(m) - 1;
+        int start = 0;
+        if (valid && lane == leader) start = dsmem_ld_i32(mapa_u32(hist_s + (uint32_t)(cell % cells_per) * 4u, (uint32_t)(cell / cells_per)));
+        start = __shfl_sync(0xffffffffu, start, leader);
+        if (valid) {
+            const float* p = aos + (size_t)i * 3;
+            const int pos = start + rankv[i];
+            soa[pos] = p[0]; soa[S.Ppad + pos] = p[1]; soa[2 * S.Ppad + pos] = p[2];
+            perm[pos] = i;
+        }
+    }
+    for (int i = len + ctid; i < S.Ppad; i += cthreads) {
+        soa[i] = CUDART_INF_F; soa[S.Ppad + i] = CUDART_INF_F; soa[2 * S.Ppad + i] = CUDART_INF_F;
+        perm[i] = 0;
+    }
+    __threadfence();
+    cluster_sync_all();
+
+    stamp(5);
+    // 5. chunk boxes (warp per chunk, 8 x 32 warps)
+    float* box = S.box + (size_t)n * 6 * S.Cpad;
+    const int nchunk = (len + kCullChunk - 1) / kCullChunk;
+    for (int c = crank * 32 + wid; c < nchunk; c += kSortCluster * 32) {
+        const int i = c * kCullChunk + lane;
+        float a[3], b[3];
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+            const float v = soa[k * S.Ppad + i];
+            a[k] = i < len ? v : CUDART_INF_F;
+            b[k] = i < len ? v : -CUDART_INF_F;
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) {
+                a[k] = fminf(a[k], __shfl_xor_sync(0xffffffffu, a[k], o));
+                b[k] = fmaxf(b[k], __shfl_xor_sync(0xffffffffu, b[k], o));
+            }
+        }
+        if (lane == 0) {
+#pragma unroll
+            for (int k = 0; k < 3; ++k) { box[k * S.Cpad + c] = a[k]; box[(3 + k) * S.Cpad + c] = b[k]; }
+        }
+    }
+    __threadfence();
+    cluster_sync_all();
+
+    stamp(6);
+    // 6. super-chunk boxes (warp per 32 chunks)
+    float* sbox = S.sbox + (size_t)n * 6 * S.Spad;
+    for (int sc = crank * 32 + wid; sc * 32 < nchunk; sc += kSortCluster * 32) {
+        const int c = sc * 32 + lane;
+#pragma unroll
+        for (int k = 0; k < 6; ++k) {
+            float v = k < 3 ? CUDART_INF_F : -CUDART_INF_F;
+            if (c < nchunk) v = box[k * S.Cpad + c];
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) {
+                const float u = __shfl_xor_sync(0xffffffffu, v, o);
+                v = k < 3 ? fminf(v, u) : fmaxf(v, u);
+            }
+            if (lane == 0) sbox[k * S.Spad + sc] = v;
+        }
+    }
+    stamp(7);
+}
+
 // ---- main kernel ------------------------------------------------------------------------------------------
 struct CullDir {
     const float* q_soa;   // sorted [N][3][Pq_pad]

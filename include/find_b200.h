@@ -77,6 +77,9 @@ int findb200_chamfer_backward(const float* x, const float* y, const int64_t* x_l
  * evaluations done for one query group, query groups} of the LAST culled call that used `workspace` into four host
  * uint64 (synchronises `stream`). */
 int findb200_set_knn_mode(int mode, int kq);
+/* Clouds of up to max_points points (and < 40000) are Hilbert-sorted by one 8-CTA cluster each in a single launch instead of
+ * six kernels; 0 = never (the default: the single launch measured slower), negative = back to the default.  A/B measurement. */
+int findb200_set_sort_cta_max(int max_points);
 int findb200_knn_stats(const void* workspace, unsigned long long* out4_host, void* stream);
 
 /* ------------------------------------------------------------------------------------------------------

@@ -32,3 +32,5 @@ print("CTA start spread %.1f us, kernel %.1f us" % ((max(st) - t0) / 1e3, (max(e
 print("per CTA (start, end) us:")
 for i in range(0, n, 8):
     print("  " + "  ".join(f"{i+k:3d}:{(st[i+k]-t0)/1e3:5.1f}-{(en[i+k]-t0)/1e3:5.1f}" for k in range(8) if i + k < n))
+
+print("cloud_sort phases (us from kernel start):", [round((t[400 + k] - t[400]) / 1e3, 2) for k in range(8)])
