@@ -74,6 +74,12 @@ FB_DEVINL float dist_exact(float qx, float qy, float qz, float tx, float ty, flo
 }  // namespace chamfer
 }  // namespace fb
 namespace fb { namespace field { extern unsigned long long* g_chain_dbg; } }
+namespace fb { namespace chamfer {
+// 64-bit fixed-point accumulation (integer adds are associative: bit-identical sums whatever the arrival order); see field.cuh
+FB_DEVINL void fx_add(long long* dst, float v, float scale) {
+    atomicAdd(reinterpret_cast<unsigned long long*>(dst), (unsigned long long)__double2ll_rn((double)v * (double)scale));
+}
+} }
 #include "knn_cull.cuh"
 namespace fb {
 namespace chamfer {
@@ -378,7 +384,8 @@ static inline int tail_blocks(int P) { return P > 0 ? (P + kTailSlice - 1) / kTa
 struct TailParams {
     FinalizeDir dir[2];
     const float *x, *y;
-    float* grad_x;
+    long long* grad_x;            // fixed point, pre-zeroed: d/dx[n][i][k] = grad_x[..] * grad_x_scale[n]
+    float* grad_x_scale;          // [N], written here (a power of two chosen from the cloud's weights)
     float grad_scale;             // w_chamf (upstream gradient of the Chamfer term)
     int N, P1, P2;
     const float *col, *col_target;
@@ -406,8 +413,15 @@ __global__ void __launch_bounds__(256) chamfer_tail_kernel(const TailParams prm)
             const int i_end = min(D.Pq, ((int)blockIdx.x + 1) * kTailSlice);
             const float* a = (z == 0 ? prm.x : prm.y) + (size_t)n * D.Pq * 3;
             const float* b = (z == 0 ? prm.y : prm.x) + (size_t)n * D.Pt * 3;
-            float* gx = prm.grad_x + (size_t)n * prm.P1 * 3;
+            long long* gx = prm.grad_x + (size_t)n * prm.P1 * 3;
             const float w = prm.grad_scale / ((float)(len_q < 1 ? 1 : len_q) * (float)(prm.N < 1 ? 1 : prm.N));
+            // Both directions add into the same fixed-point accumulators (integer adds: any order gives the same bits).  One
+            // quantum = 2^-36 of twice the larger of the cloud's two weights, i.e. 1.5e-11 of a unit coordinate difference.
+            const float w_other = prm.grad_scale / ((float)(len_t < 1 ? 1 : len_t) * (float)(prm.N < 1 ? 1 : prm.N));
+            int e2;
+            frexpf(2.0f * fmaxf(fabsf(w), fabsf(w_other)), &e2);
+            const float q = (e2 > -80 && e2 < 80) ? ldexpf(1.0f, 36 - e2) : 1.0f;        // fixed-point units per unit gradient
+            if (z == 0 && blockIdx.x == 0 && threadIdx.x == 0) prm.grad_x_scale[n] = 1.0f / q;
             double acc = 0.0;
             for (int i = blockIdx.x * kTailSlice + threadIdx.x; i < i_end; i += 256) {
                 long long j = 0;
@@ -418,8 +432,9 @@ __global__ void __launch_bounds__(256) chamfer_tail_kernel(const TailParams prm)
                     const float* pa = a + (size_t)i * 3;
                     const float* pb = b + (size_t)j * 3;
                     const float g0 = 2.0f * w * (pa[0] - pb[0]), g1 = 2.0f * w * (pa[1] - pb[1]), g2 = 2.0f * w * (pa[2] - pb[2]);
-                    if (z == 0) { float* o = gx + (size_t)i * 3; atomicAdd(o, g0); atomicAdd(o + 1, g1); atomicAdd(o + 2, g2); }
-                    else { float* o = gx + (size_t)j * 3; atomicAdd(o, -g0); atomicAdd(o + 1, -g1); atomicAdd(o + 2, -g2); }
+                    long long* o = gx + (size_t)(z == 0 ? i : (int)j) * 3;
+                    const float sg = z == 0 ? q : -q;
+                    fx_add(o, g0, sg); fx_add(o + 1, g1, sg); fx_add(o + 2, g2, sg);
                 }
                 if (D.idx) D.idx[(size_t)n * D.Pq + i] = j;
             }
@@ -827,23 +842,23 @@ int findb200_chamfer_forward(const float* x, const float* y, const int64_t* x_le
 }
 
 int findb200_chamfer_train(const float* x, const float* y, const int64_t* x_len, const int64_t* y_len, int N, int P1, int P2,
-                           float w_chamf, const float* col, const float* col_target, size_t n_col, float w_tex, float* grad_x,
-                           float* grad_col, int64_t* idx_x, int64_t* idx_y, float* loss3, double* mse_part, size_t mse_part_bytes,
-                           void* zero_extra, size_t zero_extra_bytes, void* ws, size_t ws_bytes, void* stream) {
+                           float w_chamf, const float* col, const float* col_target, size_t n_col, float w_tex, long long* grad_x,
+                           float* grad_x_scale, float* grad_col, int64_t* idx_x, int64_t* idx_y, float* loss3, double* mse_part,
+                           size_t mse_part_bytes, void* zero_extra, size_t zero_extra_bytes, void* ws, size_t ws_bytes, void* stream) {
     cudaStream_t st = (cudaStream_t)stream;
-    FB_REQUIRE(x && y && grad_x && loss3 && N >= 1 && P1 >= 1 && P2 >= 1, FINDB200_ERR_ARG, "chamfer_train: bad argument");
+    FB_REQUIRE(x && y && grad_x && grad_x_scale && loss3 && N >= 1 && P1 >= 1 && P2 >= 1, FINDB200_ERR_ARG, "chamfer_train: bad argument");
     const bool tex = col && col_target && grad_col && n_col > 0 && w_tex != 0.f;
     const dim3 grid(tail_blocks(P1 > P2 ? P1 : P2), N, 3);
     FB_REQUIRE(!tex || (mse_part && mse_part_bytes >= (size_t)grid.x * grid.y * 8), FINDB200_ERR_WORKSPACE, "chamfer_train: mse_part too small");
-    FB_REQUIRE(((size_t)N * P1 * 12) % 4 == 0 && zero_extra_bytes % 4 == 0, FINDB200_ERR_ARG, "chamfer_train: zero regions must be multiples of 4 bytes");
-    ZeroJobs zj{{grad_x, zero_extra}, {(size_t)N * P1 * 12, zero_extra ? zero_extra_bytes : 0}};
+    FB_REQUIRE(zero_extra_bytes % 4 == 0, FINDB200_ERR_ARG, "chamfer_train: zero_extra_bytes must be a multiple of 4");
+    ZeroJobs zj{{grad_x, zero_extra}, {(size_t)N * P1 * 24, zero_extra ? zero_extra_bytes : 0}};
     Workspace w;
     int rc = run_knn(x, y, x_len, y_len, N, P1, P2, true, ws, ws_bytes, w, st, &zj);
     if (rc) return rc;
     TailParams tp{};
     tp.dir[0] = FinalizeDir{w.keys_x, x_len, y_len, nullptr, idx_x, nullptr, w.sum_x, P1, P2};
     tp.dir[1] = FinalizeDir{w.keys_y, y_len, x_len, nullptr, idx_y, nullptr, w.sum_y, P2, P1};
-    tp.x = x; tp.y = y; tp.grad_x = grad_x; tp.grad_scale = w_chamf; tp.N = N; tp.P1 = P1; tp.P2 = P2;
+    tp.x = x; tp.y = y; tp.grad_x = grad_x; tp.grad_x_scale = grad_x_scale; tp.grad_scale = w_chamf; tp.N = N; tp.P1 = P1; tp.P2 = P2;
     tp.col = col; tp.col_target = col_target; tp.grad_col = grad_col; tp.n_col = tex ? (unsigned long long)n_col : 0ull; tp.w_tex = tex ? w_tex : 0.f;
     tp.mse_part = mse_part; tp.sum_x = w.sum_x; tp.sum_y = w.sum_y; tp.loss3 = loss3;
     tp.done = w.counter + 32;                      // inside the zeroed header of the kNN workspace (queue at +0, stats at +64)

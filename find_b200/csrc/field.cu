@@ -160,7 +160,9 @@ struct GradPrepParams {
     int B, V, shared;
     float* dovals;       // [2][B][V][4]
     uint32_t* maxabs;
-    float* regsums;      // [B][12]
+    long long* regsums;  // [B][12] fixed point (kRegFx)
+    const long long* grad_verts_fx;    // optional fixed-point form of grad_verts (replaces it when non-null)
+    const float* grad_verts_fx_scale;  // [B]
 };
 __global__ void __launch_bounds__(256) grad_prep_kernel(const GradPrepParams P) {
     fb::pdl_wait_trigger();
@@ -174,8 +176,13 @@ __global__ void __launch_bounds__(256) grad_prep_kernel(const GradPrepParams P) 
         const size_t o = ((size_t)b * P.V + v) * 3;
         float g0 = 0.f, g1 = 0.f, g2 = 0.f;
         if (P.grad_disp) { g0 = P.grad_disp[o]; g1 = P.grad_disp[o + 1]; g2 = P.grad_disp[o + 2]; }
-        if (P.grad_verts) {
-            const float x0 = P.grad_verts[o], x1 = P.grad_verts[o + 1], x2 = P.grad_verts[o + 2];
+        if (P.grad_verts || P.grad_verts_fx) {
+            float x0, x1, x2;
+            if (P.grad_verts_fx) {
+                const double sc = (double)P.grad_verts_fx_scale[b];
+                x0 = (float)((double)P.grad_verts_fx[o] * sc); x1 = (float)((double)P.grad_verts_fx[o + 1] * sc);
+                x2 = (float)((double)P.grad_verts_fx[o + 2] * sc);
+            } else { x0 = P.grad_verts[o]; x1 = P.grad_verts[o + 1]; x2 = P.grad_verts[o + 2]; }
             if (P.reg) {
                 const float* rg = P.reg + (size_t)b * 9;
                 float R[3][3];
@@ -215,7 +222,8 @@ __global__ void __launch_bounds__(256) grad_prep_kernel(const GradPrepParams P) 
     const int lane = threadIdx.x & 31, wp = threadIdx.x >> 5;
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
-    if (P.reg && P.grad_verts) {
+    const bool have_gv = P.grad_verts || P.grad_verts_fx;
+    if (P.reg && have_gv) {
 #pragma unroll
         for (int i = 0; i < 12; ++i) {
             float s = sums[i];
@@ -226,10 +234,10 @@ __global__ void __launch_bounds__(256) grad_prep_kernel(const GradPrepParams P) 
     }
     if (lane == 0) shm[wp] = m;
     __syncthreads();
-    if (threadIdx.x < 12 && P.reg && P.grad_verts) {
+    if (threadIdx.x < 12 && P.reg && have_gv) {
         float s = 0.f;
         for (int w = 0; w < 8; ++w) s += sh[threadIdx.x][w];
-        atomicAdd(P.regsums + (size_t)b * 12 + threadIdx.x, s);
+        fx_add(P.regsums + (size_t)b * 12 + threadIdx.x, s, kRegFx);
     }
     if (threadIdx.x == 0) {
         float mm = 0.f;
@@ -303,8 +311,8 @@ __device__ __forceinline__ void reduce_dw_body(const ReduceParams& P, int job) {
 // gradients, registration gradients.  grid.x = blocks of 256 threads, grid.y = section.
 struct FinishParams {
     const uint32_t* maxabs;
-    const float* colsum;          // see Workspace::colsum
-    const float* regsums;         // [B][12]
+    const long long* colsum;      // see Workspace::colsum (fixed point, kColsumFx)
+    const long long* regsums;     // [B][12] (fixed point, kRegFx)
     const float *Wd, *Wc;         // mlp_disp.0.weight / mlp_col.0.weight (for the latent-code gradients)
     const float *z_shape, *z_pose, *z_tex, *reg;
     int B, S, Pz, T, heads_mask, frozen, have_reg;
@@ -328,14 +336,14 @@ __device__ __forceinline__ void finish_small_body(const FinishParams& P, int sec
         const int prm = id / kW, n = id % kW;
         if (prm >= P_COUNT || !P.gb[prm]) return;
         float v = 0.f;
-        if (prm <= P_T4) v = P.colsum[cs_trunk(prm, P.B) + n];
+        if (prm <= P_T4) v = fx_get(P.colsum + cs_trunk(prm, P.B) + n, kColsumFx);
         else {
             const int head = prm >= P_C1, l = prm - (head ? P_C1 : P_D1);
             if (l == 3 && n >= 3) return;
             if (!(P.heads_mask & (1 << head))) v = 0.f;
-            else if (l == 0) { for (int b = 0; b < P.B; ++b) v += P.colsum[cs_foot(head, P.B) + (size_t)b * kW + n]; }
-            else if (l == 3) v = P.colsum[cs_out(head, P.B) + n];
-            else v = P.colsum[cs_head(head, l - 1, P.B) + n];
+            else if (l == 0) { for (int b = 0; b < P.B; ++b) v += fx_get(P.colsum + cs_foot(head, P.B) + (size_t)b * kW + n, kColsumFx); }
+            else if (l == 3) v = fx_get(P.colsum + cs_out(head, P.B) + n, kColsumFx);
+            else v = fx_get(P.colsum + cs_head(head, l - 1, P.B) + n, kColsumFx);
         }
         P.gb[prm][n] = v * inv;
     } else if (sec == 1 || sec == 2) {
@@ -352,7 +360,7 @@ __device__ __forceinline__ void finish_small_body(const FinishParams& P, int sec
                 float z;
                 if (head) z = P.z_tex[(size_t)b * P.T + j];
                 else z = j < P.S ? P.z_shape[(size_t)b * P.S + j] : P.z_pose[(size_t)b * P.Pz + (j - P.S)];
-                v = fmaf(P.colsum[cs_foot(head, P.B) + (size_t)b * kW + n], z, v);
+                v = fmaf(fx_get(P.colsum + cs_foot(head, P.B) + (size_t)b * kW + n, kColsumFx), z, v);
             }
         }
         g[(size_t)n * (kW + L) + kW + j] = v * inv;
@@ -372,15 +380,15 @@ __device__ __forceinline__ void finish_small_body(const FinishParams& P, int sec
         if (live && (P.heads_mask & (1 << head))) {
             const float* W = head ? P.Wc : P.Wd;
             const int ld = kW + (head ? Lt : Ld);
-            const float* s = P.colsum + cs_foot(head, P.B) + (size_t)b * kW + wq * 32;
+            const long long* s = P.colsum + cs_foot(head, P.B) + (size_t)b * kW + wq * 32;
             const float* Wj = W + (size_t)(wq * 32) * ld + kW + jj;
             float v0 = 0.f, v1 = 0.f, v2 = 0.f, v3 = 0.f;
 #pragma unroll
             for (int n = 0; n < 32; n += 4) {
-                v0 = fmaf(Wj[(size_t)n * ld], s[n], v0);
-                v1 = fmaf(Wj[(size_t)(n + 1) * ld], s[n + 1], v1);
-                v2 = fmaf(Wj[(size_t)(n + 2) * ld], s[n + 2], v2);
-                v3 = fmaf(Wj[(size_t)(n + 3) * ld], s[n + 3], v3);
+                v0 = fmaf(Wj[(size_t)n * ld], fx_get(s + n, kColsumFx), v0);
+                v1 = fmaf(Wj[(size_t)(n + 1) * ld], fx_get(s + n + 1, kColsumFx), v1);
+                v2 = fmaf(Wj[(size_t)(n + 2) * ld], fx_get(s + n + 2, kColsumFx), v2);
+                v3 = fmaf(Wj[(size_t)(n + 3) * ld], fx_get(s + n + 3, kColsumFx), v3);
             }
             v = (v0 + v1) + (v2 + v3);
         }
@@ -401,7 +409,8 @@ __device__ __forceinline__ void finish_small_body(const FinishParams& P, int sec
         const int b = id;
         float* g = P.greg + (size_t)b * 9;
         if (!P.have_reg) { for (int i = 0; i < 9; ++i) g[i] = 0.f; return; }
-        const float* s = P.regsums + (size_t)b * 12;
+        float s[12];
+        for (int i = 0; i < 12; ++i) s[i] = fx_get(P.regsums + (size_t)b * 12 + i, kRegFx);
         const float* rg = P.reg + (size_t)b * 9;
         float sa, ca, sb, cb, sc, cc;
         sincosf(rg[3], &sa, &ca); sincosf(rg[4], &sb, &cb); sincosf(rg[5], &sc, &cc);
@@ -486,8 +495,8 @@ static Workspace carve(int B, int V, int shared, int for_backward) {
     w.scal = take(1024);
     if (for_backward) {
         // scal | regsums | colsum are adjacent: the backward zeroes them with ONE memset node
-        w.regsums = take((size_t)B * 12 * 4);
-        w.colsum = take(cs_total(B) * 4);
+        w.regsums = take((size_t)B * 12 * 8);
+        w.colsum = take(cs_total(B) * 8);
         w.enc = take((size_t)w.trunk_tiles * kEncTileBytes);
         w.hact = take((size_t)2 * 3 * head_tiles * kTileBytes);
         w.hdz = take((size_t)2 * 3 * head_tiles * kTileBytes);
@@ -543,10 +552,12 @@ static void fill_chain_common(ChainParams& C, const findb200_field_params* p, co
 namespace fb {
 namespace field {
 thread_local bool g_field_bwd_prezeroed = false;
+thread_local const long long* g_grad_verts_fx = nullptr;
+thread_local const float* g_grad_verts_fx_scale = nullptr;
 void field_bwd_zero_region(int nfeet, int V, int pos_shared, size_t* offset, size_t* bytes) {
     const Workspace w = carve(nfeet, V, pos_shared, 1);
     *offset = w.scal;
-    *bytes = (w.colsum - w.scal) + cs_total(nfeet) * 4;
+    *bytes = (w.colsum - w.scal) + cs_total(nfeet) * 8;
 }
 
 static int run_pack(const findb200_field_params* p, const Workspace& w, uint8_t* ws, const LatentBiasParams& LB, cudaStream_t st) {
@@ -664,11 +675,12 @@ int findb200_field_backward(const findb200_field_params* p, const float* pos, in
     // rows >= 16 of the 256 -> 3 layers' dW partial, which reduce_dw never reads (J.rows = 3).
     if (!g_field_bwd_prezeroed) {
         FB_MARK("bwd_memsets", st);
-        FB_CUDA(cudaMemsetAsync(ws + w.scal, 0, (w.colsum - w.scal) + cs_total(B) * 4, st));
+        FB_CUDA(cudaMemsetAsync(ws + w.scal, 0, (w.colsum - w.scal) + cs_total(B) * 8, st));
     }
 
     GradPrepParams GP{pos, disp, col, reg, p->avg_col, grad_disp, grad_col, grad_verts, B, V, pos_shared,
-                      (float*)(ws + w.dovals), (uint32_t*)(ws + w.scal), (float*)(ws + w.regsums)};
+                      (float*)(ws + w.dovals), (uint32_t*)(ws + w.scal), (long long*)(ws + w.regsums), g_grad_verts_fx,
+                      g_grad_verts_fx_scale};
     FB_MARK("grad_prep", st);
     FB_CUDA(fb::launch_pdl(grad_prep_kernel, dim3(cdiv(V, 256), B), 256, 0, st, GP));
     FB_CUDA(cudaGetLastError());
@@ -683,7 +695,7 @@ int findb200_field_backward(const findb200_field_params* p, const float* pos, in
         rc = chain_pairs_enabled() ? launch_chain2(2, C, sms, st) : launch_chain(2, nt, C, sms, st);
         if (rc) return rc;
     }
-    float* colsum = (float*)(ws + w.colsum);
+    long long* colsum = (long long*)(ws + w.colsum);
     float* partial = (float*)(ws + w.partial);
 
     DwParams D;
@@ -693,7 +705,7 @@ int findb200_field_backward(const findb200_field_params* p, const float* pos, in
     int gemm_kblock[kMaxDwGemms];
     long long cost[kMaxDwGemms];
     auto add = [&](const uint8_t* A, uint32_t atb, int a_imgs, const uint8_t* Bm, uint32_t btb, uint32_t boff, int b_imgs,
-                   int mh, int N, int feet, int afs, int bfs, float* cs, int csmode, int cscols, int prm, int kblock) {
+                   int mh, int N, int feet, int afs, int bfs, long long* cs, int csmode, int cscols, int prm, int kblock) {
         DwGemm& g = D.g[ng];
         g.A = A; g.Bm = Bm; g.a_tile_bytes = atb; g.b_tile_bytes = btb; g.b_img_off = boff; g.a_imgs = a_imgs; g.b_imgs = b_imgs;
         g.mhalves = mh; g.N = N; g.feet = feet; g.tpf = w.tpf; g.a_foot_stride = afs; g.b_foot_stride = bfs;
@@ -871,11 +883,11 @@ int findb200_field_backward(const findb200_field_params* p, const float* pos, in
     FinishParams F;
     memset(&F, 0, sizeof(F));
     F.maxabs = (const uint32_t*)(ws + w.scal);
-    F.colsum = colsum; F.regsums = (const float*)(ws + w.regsums);
+    F.colsum = colsum; F.regsums = (const long long*)(ws + w.regsums);
     F.Wd = p->weight[P_D1]; F.Wc = p->weight[P_C1];
     F.z_shape = z_shape; F.z_pose = z_pose; F.z_tex = z_tex; F.reg = reg;
     F.B = B; F.S = p->shapevec_size; F.Pz = p->posevec_size; F.T = p->texvec_size;
-    F.heads_mask = heads_mask; F.frozen = frozen; F.have_reg = (reg && grad_verts) ? 1 : 0;
+    F.heads_mask = heads_mask; F.frozen = frozen; F.have_reg = (reg && (grad_verts || g_grad_verts_fx)) ? 1 : 0;
     if (gw) for (int i = 0; i < P_COUNT; ++i) { F.gW[i] = gw->weight[i]; F.gb[i] = gw->bias[i]; }
     F.gz_shape = gz_shape; F.gz_pose = gz_pose; F.gz_tex = gz_tex; F.greg = greg;
     int maxid = P_COUNT * kW;

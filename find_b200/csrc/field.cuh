@@ -89,6 +89,20 @@ constexpr int kMaxDwCtas = 192;
 // can have an earlier kernel clear it and tell the backward so.
 void field_bwd_zero_region(int nfeet, int V, int pos_shared, size_t* offset, size_t* bytes);
 extern thread_local bool g_field_bwd_prezeroed;
+// d loss / d verts handed over as fixed point (see fx_add): grad_verts[b][v][k] = fx[b][v][k] * scale[b].  Set by step.cu around
+// findb200_field_backward when the fused Chamfer tail produced the gradient; null = the float grad_verts argument is used.
+extern thread_local const long long* g_grad_verts_fx;
+extern thread_local const float* g_grad_verts_fx_scale;
+
+// Order-independent accumulation: sums that many CTAs build with atomics (column sums of dZ, registration sums, the Chamfer
+// scatter) are kept as 64-bit fixed point, because integer addition is associative — two runs of a step give bit-identical
+// gradients whatever the arrival order — and at these scales the quantum is far below an fp32 ulp of the result.
+constexpr float kColsumFx = 16777216.f;        // 2^24: |sum of scaled dZ| < 2^39, quantum 6e-8
+constexpr float kRegFx = 4294967296.f;         // 2^32: registration sums, quantum 2.3e-10
+FB_DEVINL void fx_add(long long* dst, float v, float scale) {
+    atomicAdd(reinterpret_cast<unsigned long long*>(dst), (unsigned long long)__double2ll_rn((double)v * (double)scale));
+}
+FB_DEVINL float fx_get(const long long* src, float scale) { return (float)((double)(*src) / (double)scale); }
 
 }  // namespace field
 }  // namespace fb

@@ -108,9 +108,9 @@ __global__ void __launch_bounds__(kDwThreads, 1) dw_kernel(const __grid_constant
             int cur_foot = -1;
             auto flush = [&](int foot) {
                 if (active && foot >= 0) {
-                    float* dst = G.colsum + (G.colsum_mode == 2 ? (size_t)foot * kW : 0) + 2 * ct;
-                    atomicAdd(dst, c0);
-                    atomicAdd(dst + 1, c1);
+                    long long* dst = G.colsum + (G.colsum_mode == 2 ? (size_t)foot * kW : 0) + 2 * ct;
+                    fx_add(dst, c0, kColsumFx);
+                    fx_add(dst + 1, c1, kColsumFx);
                 }
                 c0 = c1 = 0.f;
             };

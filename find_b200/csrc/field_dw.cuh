@@ -14,7 +14,7 @@ struct DwGemm {
     int N;                   // UMMA N (256 or 64)
     int feet, tpf;           // units = feet * tpf tiles
     int a_foot_stride, b_foot_stride;   // in tiles
-    float* colsum;           // column sums of A (nullable)
+    long long* colsum;       // column sums of A (nullable), fixed point (kColsumFx)
     int colsum_mode;         // 0 none, 1 one vector [256], 2 per foot [feet][256]
     int colsum_cols;         // 256 or 16
     int cta0, ncta;          // partial slots [cta0, cta0 + ncta) hold the row-slices of this GEMM (one per segment, see DwSeg)

@@ -15,7 +15,7 @@ namespace step {
 static inline size_t align1k(size_t x) { return (x + 1023) & ~(size_t)1023; }
 
 struct Carve {
-    size_t field, knn, idx_x, idx_y, grad_verts, grad_col, sums, total;
+    size_t field, knn, idx_x, idx_y, grad_verts, gv_scale, grad_col, sums, total;
     size_t field_bytes, knn_bytes, mse_part_bytes;
     // mesh terms (findb200_train_step_mesh): surface samples of the deformed template and the smoothness workspace
     size_t samples, fidx, bary, grad_samples, sample_ws, smooth_ws, smooth2;
@@ -32,7 +32,8 @@ static Carve carve(int B, int V, int P2, int S = 0, int nnz = 0, int F = 0) {
     c.knn = take(c.knn_bytes);
     c.idx_x = take((size_t)B * P1 * 8);
     c.idx_y = take((size_t)B * P2 * 8);
-    c.grad_verts = take((size_t)B * V * 12);
+    c.grad_verts = take((size_t)B * V * 24);       // float [B][V][3], or int64 fixed point on the fused plain path
+    c.gv_scale = take((size_t)B * 4);
     c.grad_col = take((size_t)B * V * 12);
     c.mse_part_bytes = (size_t)8 * B * (((P1 > P2 ? P1 : P2) + 511) / 512);
     c.sums = take(1024 + c.mse_part_bytes);     // mse sum | chamfer scalar | block partials of the colour term (fused tail)
@@ -171,15 +172,21 @@ static int run_step(const findb200_field_params* p, const float* template_pos, c
         const bool tex = col_target != nullptr && w_tex != 0.f;
         size_t zoff = 0, zbytes = 0;
         fb::field::field_bwd_zero_region(nfeet, V, 1, &zoff, &zbytes);
+        long long* gv_fx = (long long*)(ws + c.grad_verts);
+        float* gv_scale = (float*)(ws + c.gv_scale);
         rc = findb200_chamfer_train(verts, target, nullptr, target_len, nfeet, V, P2, w_chamf, tex ? col : nullptr, col_target, n,
-                                    tex ? w_tex : 0.f, grad_verts, grad_col, idx_x, idx_y, loss3, (double*)(ws + c.sums + 1024), c.mse_part_bytes,
-                                    ws + c.field + zoff, zbytes, ws + c.knn, c.knn_bytes, stream);
+                                    tex ? w_tex : 0.f, gv_fx, gv_scale, grad_col, idx_x, idx_y, loss3, (double*)(ws + c.sums + 1024),
+                                    c.mse_part_bytes, ws + c.field + zoff, zbytes, ws + c.knn, c.knn_bytes, stream);
         if (rc) return rc;
         fb::field::g_field_bwd_prezeroed = true;
+        fb::field::g_grad_verts_fx = gv_fx;
+        fb::field::g_grad_verts_fx_scale = gv_scale;
         rc = findb200_field_backward(p, template_pos, 1, z_shape, z_pose, z_tex, reg, nfeet, V, disp, col, nullptr,
-                                     tex ? grad_col : nullptr, grad_verts, gw, gz_shape, gz_pose, gz_tex, greg,
+                                     tex ? grad_col : nullptr, nullptr, gw, gz_shape, gz_pose, gz_tex, greg,
                                      ws + c.field, c.field_bytes, stream);
         fb::field::g_field_bwd_prezeroed = false;
+        fb::field::g_grad_verts_fx = nullptr;
+        fb::field::g_grad_verts_fx_scale = nullptr;
         return rc;
     } else {
         rc = findb200_chamfer_forward(verts, target, nullptr, target_len, nfeet, V, P2, chamf, nullptr, idx_x, nullptr, idx_y,

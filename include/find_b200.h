@@ -57,13 +57,17 @@ int findb200_chamfer_forward(const float* x, const float* y, const int64_t* x_le
 
 /* The Chamfer + colour part of one training step in as few launches as possible (used by findb200_train_step): kNN both
  * ways, then ONE kernel for the indices, loss3 = [w_chamf * chamfer(x, y) + w_tex * mse(col, col_target), chamfer, mse]
- * (losses.py:87-88, model.py:1157-1158), grad_x = d(w_chamf * chamfer)/dx [N,P1,3] and grad_col = d(w_tex * mse)/dcol
- * (col == NULL: no colour term).  mse_part: scratch of >= 8 * ceil(max(P1,P2)/512) * N bytes.  zero_extra: an optional
- * region (multiple of 4 bytes) cleared early in the call for the kernels the caller enqueues next. */
+ * (losses.py:87-88, model.py:1157-1158), d(w_chamf * chamfer)/dx and grad_col = d(w_tex * mse)/dcol (col == NULL: no colour
+ * term).  The gradient with respect to x comes as 64-bit FIXED POINT, d/dx[n][i][k] = grad_x_fx[n][i][k] * grad_x_scale[n]
+ * ([N,P1,3] int64 + [N] float): both Chamfer directions scatter into it with integer atomics, so two runs give the same bits
+ * whatever the arrival order (PyTorch3D's knn_points_backward uses float atomicAdd).  mse_part: scratch of
+ * >= 8 * ceil(max(P1,P2)/512) * N bytes.  zero_extra: an optional region (multiple of 4 bytes) cleared early in the call for
+ * the kernels the caller enqueues next. */
 int findb200_chamfer_train(const float* x, const float* y, const int64_t* x_len, const int64_t* y_len, int N, int P1, int P2,
-                           float w_chamf, const float* col, const float* col_target, size_t n_col, float w_tex, float* grad_x,
-                           float* grad_col, int64_t* idx_x, int64_t* idx_y, float* loss3, double* mse_part, size_t mse_part_bytes,
-                           void* zero_extra, size_t zero_extra_bytes, void* workspace, size_t workspace_bytes, void* stream);
+                           float w_chamf, const float* col, const float* col_target, size_t n_col, float w_tex,
+                           long long* grad_x_fx, float* grad_x_scale, float* grad_col, int64_t* idx_x, int64_t* idx_y,
+                           float* loss3, double* mse_part, size_t mse_part_bytes, void* zero_extra, size_t zero_extra_bytes,
+                           void* workspace, size_t workspace_bytes, void* stream);
 
 /* d loss / d x (and d y if grad_y != NULL); upstream gradient = (*grad_loss if non-NULL else 1) * grad_scale */
 int findb200_chamfer_backward(const float* x, const float* y, const int64_t* x_len, const int64_t* y_len, int N,

@@ -262,22 +262,28 @@ def test_cfg4_size_knn_bit_exact_and_field_forward():
     assert np.array_equal(k2.dists[..., 0].cpu().numpy(), ch["dist_y"])
 
 
-def test_outputs_and_weight_gradients_are_run_to_run_identical():
-    """Two enqueues of the same step: outputs, losses' Chamfer term and the MLP-gradient bucket (deterministic dW fold) are
-    bit-identical; the atomically accumulated pieces (latent / reg gradients, Chamfer distance gradient) agree to 1e-6."""
+def test_step_is_bit_reproducible_at_cfg2_size():
+    """two enqueues of the cfg2 step (8 x 10 242 x 10 000) give bit-identical outputs, losses and EVERY
+    gradient — the MLP bucket (ordered fold of the dW partials), the latent / registration rows (column sums and registration
+    sums accumulated in 64-bit fixed point) and therefore the Chamfer scatter behind them (fixed-point d/d(verts)); the kNN's
+    cell-arrival order may differ between the runs, its result may not.  The dense table gradients are part of the step."""
     from find_b200.step import TrainStep
-    B, V, P2, n_rows = 4, 3000, 2500, 4
+    B, V, P2, n_rows = 8, 10242, 10000, 8
     dev, model, p, tv, tables, idx, target, colt = _setup(B, V, P2, n_rows, seed=86)
     step = TrainStep(model, B, P2, with_colour=True, use_graph=False)
     step.load_inputs(idx, target, colt)
-    step.run(); torch.cuda.synchronize()
-    a = (step.verts.clone(), step.col.clone(), step.loss3.clone(), step.flat_grad.clone(), {k: v.clone() for k, v in step.grows.items()})
-    step.run(); torch.cuda.synchronize()
-    assert torch.equal(a[0], step.verts) and torch.equal(a[1], step.col)
-    assert rel_l2(step.loss3, a[2]) < 1e-6
-    assert rel_l2(step.flat_grad, a[3]) < 1e-5
-    for k, v in a[4].items():
-        assert rel_l2(step.grows[k], v) < 1e-5, k
+
+    def snap():
+        step.run(); torch.cuda.synchronize()
+        return dict(verts=step.verts.clone(), col=step.col.clone(), disp=step.disp.clone(), loss3=step.loss3.clone(),
+                    flat_grad=step.flat_grad.clone(), **{"rows/" + k: v.clone() for k, v in step.grows.items()},
+                    **{"table/" + k: v.clone() for k, v in step.table_grads.items()})
+    a = snap()
+    for _ in range(3):
+        b = snap()
+        for k in a:
+            assert torch.equal(a[k], b[k]), k
+    assert float(a["flat_grad"].abs().max()) > 0 and float(a["rows/reg"].abs().max()) > 0
 
 
 def test_texture_loss_gt_space_matches_oracle():
