@@ -672,7 +672,7 @@ struct PhongParams {
     const float* verts; const float* normals; const float* colours;               // [M, V, 3]
     const int* faces;
     const float* cam;                                                              // [views, 3] camera centres (world)
-    long long n_pix; int HW, V, views;
+    long long n_pix; int HW, V, views, H_;
     float light[3], amb[3], dif[3], spec[3], bg[3];
     float shininess, sigma, gamma, znear, zfar;
     float* out;                                                                    // [I, H, W, 3]
@@ -726,6 +726,269 @@ __global__ void phong_shade_kernel(const __grid_constant__ PhongParams P) {
     P.out[3 * i] = r; P.out[3 * i + 1] = g; P.out[3 * i + 2] = b;
 }
 
+// ---- backward of the Phong image ----------------------------------------------------------------------------------------
+// d(image)/d(world vertices, vertex colours): per pixel, the forward is recomputed and differentiated by hand —
+//   blend (softmax_rgb_blend, one face per pixel)  ->  colour, and the sigmoid of the signed edge distance,
+//   phong_shading                                   ->  interpolated position / normal / texel,
+//   barycentric interpolation                       ->  the three vertices' attributes, and the barycentrics themselves,
+//   rasterize_meshes backward                       ->  the face's NDC vertices: perspective correction, edge functions, and
+//                                                       the squared distance to the nearest edge.
+// pix_to_face and the depth ordering carry no gradient; neither does zbuf here: with gamma = 1e-4 the background weight
+// delta = exp((eps - z_inv) / gamma) is clamped at eps for every visible depth, and (z_inv - max z_inv) is identically 0 with
+// one face per pixel.  Same rules as oracle/raster_oracle.py::render_image under autograd.  Gradients are accumulated with fp32
+// atomics into pre-zeroed buffers (PyTorch3D does the same).
+struct PhongBwdParams {
+    PhongParams f;
+    const float* grad_image;              // [I, H, W, 3]
+    const float* verts_ndc;               // [I, V, 3]
+    float *g_verts, *g_normals, *g_colours;   // [M, V, 3]
+    float* g_ndc;                         // [I, V, 3]
+};
+
+FB_DEVINL void normalize_bwd(const float (&x)[3], const float (&g)[3], float (&out)[3]) {
+    // y = x / max(|x|, 1e-6):  dL/dx = (g - y (y . g)) / |x|   (|x| > eps), g / eps otherwise
+    const float l = sqrtf(x[0] * x[0] + x[1] * x[1] + x[2] * x[2]);
+    if (l > 1e-6f) {
+        const float y0 = x[0] / l, y1 = x[1] / l, y2 = x[2] / l;
+        const float d = y0 * g[0] + y1 * g[1] + y2 * g[2];
+        out[0] = (g[0] - y0 * d) / l; out[1] = (g[1] - y1 * d) / l; out[2] = (g[2] - y2 * d) / l;
+    } else {
+        out[0] = g[0] / 1e-6f; out[1] = g[1] / 1e-6f; out[2] = g[2] / 1e-6f;
+    }
+}
+
+__global__ void __launch_bounds__(128) phong_shade_bwd_kernel(const __grid_constant__ PhongBwdParams B) {
+    pdl_wait_trigger();
+    const PhongParams& P = B.f;
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= P.n_pix) return;
+    const int f = P.p2f[i];
+    if (f < 0) return;
+    const float g[3] = {B.grad_image[3 * i], B.grad_image[3 * i + 1], B.grad_image[3 * i + 2]};
+    if (g[0] == 0.f && g[1] == 0.f && g[2] == 0.f) return;
+    const int img = (int)(i / P.HW), m = img / P.views, view = img - m * P.views;
+    const int pix = (int)(i - (long long)img * P.HW);
+    const float w[3] = {P.bary[3 * i], P.bary[3 * i + 1], P.bary[3 * i + 2]};
+    const int vid[3] = {P.faces[3 * f], P.faces[3 * f + 1], P.faces[3 * f + 2]};
+    const size_t o = (size_t)m * P.V * 3;
+    float Pv[3][3], Nv[3][3], Cv[3][3];
+#pragma unroll
+    for (int k = 0; k < 3; ++k)
+#pragma unroll
+        for (int d = 0; d < 3; ++d) {
+            Pv[k][d] = P.verts[o + 3 * vid[k] + d]; Nv[k][d] = P.normals[o + 3 * vid[k] + d]; Cv[k][d] = P.colours[o + 3 * vid[k] + d];
+        }
+    float p[3], nraw[3], tex[3];
+#pragma unroll
+    for (int d = 0; d < 3; ++d) {
+        p[d] = w[0] * Pv[0][d] + w[1] * Pv[1][d] + w[2] * Pv[2][d];
+        nraw[d] = w[0] * Nv[0][d] + w[1] * Nv[1][d] + w[2] * Nv[2][d];
+        tex[d] = w[0] * Cv[0][d] + w[1] * Cv[1][d] + w[2] * Cv[2][d];
+    }
+    float n[3] = {nraw[0], nraw[1], nraw[2]};
+    normalize3(n[0], n[1], n[2]);
+    const float lraw[3] = {P.light[0] - p[0], P.light[1] - p[1], P.light[2] - p[2]};
+    float l[3] = {lraw[0], lraw[1], lraw[2]};
+    normalize3(l[0], l[1], l[2]);
+    const float cosang = n[0] * l[0] + n[1] * l[1] + n[2] * l[2];
+    const float diff = fmaxf(cosang, 0.f);
+    const float vraw[3] = {P.cam[3 * view] - p[0], P.cam[3 * view + 1] - p[1], P.cam[3 * view + 2] - p[2]};
+    float v[3] = {vraw[0], vraw[1], vraw[2]};
+    normalize3(v[0], v[1], v[2]);
+    const float r[3] = {-l[0] + 2.f * cosang * n[0], -l[1] + 2.f * cosang * n[1], -l[2] + 2.f * cosang * n[2]};
+    const float vr = v[0] * r[0] + v[1] * r[1] + v[2] * r[2];
+    const float al = (cosang > 0.f) ? fmaxf(vr, 0.f) : 0.f;
+    const float sp = powf(al, P.shininess);
+    const float eps = 1e-10f;
+    const float dist = P.dists[i];
+    const float prob = __fdiv_rn(1.f, 1.f + expf(dist / P.sigma));
+    const float z_inv = (P.zfar - P.zbuf[i]) / (P.zfar - P.znear);
+    const float z_max = fmaxf(z_inv, eps);
+    const float ez = expf((z_inv - z_max) / P.gamma);
+    const float wnum = prob * ez;
+    const float delta = fmaxf(expf((eps - z_max) / P.gamma), eps);
+    const float den = wnum + delta;
+    float c[3], outc[3];
+#pragma unroll
+    for (int d = 0; d < 3; ++d) {
+        c[d] = (P.amb[d] + P.dif[d] * diff) * tex[d] + P.spec[d] * sp;
+        outc[d] = (wnum * c[d] + delta * P.bg[d]) / den;
+    }
+    // ---- blend
+    float gc[3], g_wnum = 0.f;
+#pragma unroll
+    for (int d = 0; d < 3; ++d) { gc[d] = g[d] * wnum / den; g_wnum += g[d] * (c[d] - outc[d]) / den; }
+    const float g_prob = g_wnum * ez;
+    const float g_dist = g_prob * (-prob * (1.f - prob) / P.sigma);
+    // ---- shading
+    float g_tex[3], g_diff = 0.f, g_sp = 0.f;
+#pragma unroll
+    for (int d = 0; d < 3; ++d) { g_tex[d] = gc[d] * (P.amb[d] + P.dif[d] * diff); g_diff += gc[d] * P.dif[d] * tex[d]; g_sp += gc[d] * P.spec[d]; }
+    float g_cos = (cosang > 0.f) ? g_diff : 0.f;
+    float g_vr = 0.f;
+    if (cosang > 0.f && vr > 0.f && al > 0.f) g_vr = g_sp * P.shininess * powf(al, P.shininess - 1.f);
+    float g_v[3], g_r[3], g_l[3], g_n[3];
+#pragma unroll
+    for (int d = 0; d < 3; ++d) { g_v[d] = g_vr * r[d]; g_r[d] = g_vr * v[d]; }
+    g_cos += 2.f * (g_r[0] * n[0] + g_r[1] * n[1] + g_r[2] * n[2]);
+#pragma unroll
+    for (int d = 0; d < 3; ++d) { g_l[d] = -g_r[d] + g_cos * n[d]; g_n[d] = 2.f * cosang * g_r[d] + g_cos * l[d]; }
+    float g_vraw[3], g_lraw[3], g_nraw[3], g_p[3];
+    normalize_bwd(vraw, g_v, g_vraw);
+    normalize_bwd(lraw, g_l, g_lraw);
+    normalize_bwd(nraw, g_n, g_nraw);
+#pragma unroll
+    for (int d = 0; d < 3; ++d) g_p[d] = -g_vraw[d] - g_lraw[d];
+    // ---- interpolation: attribute gradients to the three vertices, and d/d(barycentrics)
+    float g_w[3];
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        g_w[k] = 0.f;
+#pragma unroll
+        for (int d = 0; d < 3; ++d) {
+            g_w[k] += g_p[d] * Pv[k][d] + g_nraw[d] * Nv[k][d] + g_tex[d] * Cv[k][d];
+            atomicAdd(B.g_verts + o + 3 * vid[k] + d, w[k] * g_p[d]);
+            atomicAdd(B.g_normals + o + 3 * vid[k] + d, w[k] * g_nraw[d]);
+            atomicAdd(B.g_colours + o + 3 * vid[k] + d, w[k] * g_tex[d]);
+        }
+    }
+    // ---- rasteriser backward on the face's NDC vertices
+    const float* nd = B.verts_ndc + (size_t)img * P.V * 3;
+    float X[3], Y[3], Z[3];
+#pragma unroll
+    for (int k = 0; k < 3; ++k) { X[k] = nd[3 * vid[k]]; Y[k] = nd[3 * vid[k] + 1]; Z[k] = nd[3 * vid[k] + 2]; }
+    const int Wd = P.HW / P.H_;
+    const int row = pix / Wd, col = pix - row * Wd;
+    const float px = 1.f - __fdiv_rn((float)(2 * col + 1), (float)Wd), py = 1.f - __fdiv_rn((float)(2 * row + 1), (float)P.H_);
+    float gX[3] = {0.f, 0.f, 0.f}, gY[3] = {0.f, 0.f, 0.f}, gZ[3] = {0.f, 0.f, 0.f};
+    // perspective correction: b_k = t_k / dn, t0 = w0 z1 z2, t1 = z0 w1 z2, t2 = z0 z1 w2 (w = screen-space barycentrics)
+    const float area = edge_fn(X[2], Y[2], X[0], Y[0], X[1], Y[1]);
+    const float dena = area + kEps;
+    const float e0 = edge_fn(px, py, X[1], Y[1], X[2], Y[2]), e1 = edge_fn(px, py, X[2], Y[2], X[0], Y[0]), e2 = edge_fn(px, py, X[0], Y[0], X[1], Y[1]);
+    const float ws[3] = {e0 / dena, e1 / dena, e2 / dena};
+    const float t0 = ws[0] * Z[1] * Z[2], t1 = Z[0] * ws[1] * Z[2], t2 = Z[0] * Z[1] * ws[2];
+    const float dn_raw = t0 + t1 + t2;
+    float g_ws[3];
+    if (dn_raw > kEps) {
+        const float dn = dn_raw;
+        const float bsum = g_w[0] * (t0 / dn) + g_w[1] * (t1 / dn) + g_w[2] * (t2 / dn);
+        const float g_t0 = (g_w[0] - bsum) / dn, g_t1 = (g_w[1] - bsum) / dn, g_t2 = (g_w[2] - bsum) / dn;
+        g_ws[0] = g_t0 * Z[1] * Z[2]; g_ws[1] = g_t1 * Z[0] * Z[2]; g_ws[2] = g_t2 * Z[0] * Z[1];
+        gZ[0] += g_t1 * ws[1] * Z[2] + g_t2 * Z[1] * ws[2];
+        gZ[1] += g_t0 * ws[0] * Z[2] + g_t2 * Z[0] * ws[2];
+        gZ[2] += g_t0 * ws[0] * Z[1] + g_t1 * Z[0] * ws[1];
+    } else {
+        const float dn = kEps;                     // clamped denominator: a constant
+        g_ws[0] = g_w[0] / dn * Z[1] * Z[2]; g_ws[1] = g_w[1] / dn * Z[0] * Z[2]; g_ws[2] = g_w[2] / dn * Z[0] * Z[1];
+        gZ[0] += g_w[1] / dn * ws[1] * Z[2] + g_w[2] / dn * Z[1] * ws[2];
+        gZ[1] += g_w[0] / dn * ws[0] * Z[2] + g_w[2] / dn * Z[0] * ws[2];
+        gZ[2] += g_w[0] / dn * ws[0] * Z[1] + g_w[1] / dn * Z[0] * ws[1];
+    }
+    // screen-space barycentrics: ws_k = e_k / (area + eps);  edge(p; a, b) = (px - ax)(by - ay) - (py - ay)(bx - ax)
+    const float g_e[3] = {g_ws[0] / dena, g_ws[1] / dena, g_ws[2] / dena};
+    const float g_area = -(g_ws[0] * ws[0] + g_ws[1] * ws[1] + g_ws[2] * ws[2]) / dena;
+    auto edge_bwd = [&](float ge, int a, int b) {       // p = the pixel (no gradient)
+        gX[a] += ge * (py - Y[b]); gY[a] += ge * (X[b] - px);
+        gX[b] += ge * -(py - Y[a]); gY[b] += ge * (px - X[a]);
+    };
+    edge_bwd(g_e[0], 1, 2);
+    edge_bwd(g_e[1], 2, 0);
+    edge_bwd(g_e[2], 0, 1);
+    // area = edge(v2; v0, v1): also a function of its "point" v2
+    gX[0] += g_area * (Y[2] - Y[1]); gY[0] += g_area * (X[1] - X[2]);
+    gX[1] += g_area * -(Y[2] - Y[0]); gY[1] += g_area * (X[2] - X[0]);
+    gX[2] += g_area * (Y[1] - Y[0]); gY[2] += g_area * -(X[1] - X[0]);
+    // signed squared distance to the nearest edge (negative inside): d2 = |p - q|^2, q = a + t (b - a), t clamped
+    if (g_dist != 0.f) {
+        float tt[3];
+        const float d01 = seg_dist2(px, py, X[0], Y[0], X[1], Y[1], tt[0]);
+        const float d02 = seg_dist2(px, py, X[0], Y[0], X[2], Y[2], tt[1]);
+        const float d12 = seg_dist2(px, py, X[1], Y[1], X[2], Y[2], tt[2]);
+        int ed = 0;
+        float dmin = d01;
+        if (d02 < dmin) { dmin = d02; ed = 1; }
+        if (d12 < dmin) { dmin = d12; ed = 2; }
+        const int ia = ed == 2 ? 1 : 0, ib = ed == 0 ? 1 : 2;
+        const bool inside = (ws[0] > 0.f) && (ws[1] > 0.f) && (ws[2] > 0.f);
+        const float gs = inside ? -g_dist : g_dist;                  // d(signed)/d(d2)
+        const float t = tt[ed];
+        if (t == 2.f) {                                              // degenerate segment: distance to b
+            gX[ib] += gs * -2.f * (px - X[ib]); gY[ib] += gs * -2.f * (py - Y[ib]);
+        } else {
+            const float qx = X[ia] + t * (X[ib] - X[ia]), qy = Y[ia] + t * (Y[ib] - Y[ia]);
+            const float cx = px - qx, cy = py - qy;
+            gX[ia] += gs * -2.f * (1.f - t) * cx; gY[ia] += gs * -2.f * (1.f - t) * cy;
+            gX[ib] += gs * -2.f * t * cx; gY[ib] += gs * -2.f * t * cy;
+        }
+    }
+    float* gn = B.g_ndc + (size_t)img * P.V * 3;
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        atomicAdd(gn + 3 * vid[k], gX[k]); atomicAdd(gn + 3 * vid[k] + 1, gY[k]); atomicAdd(gn + 3 * vid[k] + 2, gZ[k]);
+    }
+}
+
+// backward of vert_normals_kernel.  Pass 1 (per vertex): gradient w.r.t. the un-normalised normal.  Pass 2 (per vertex, gather over
+// its incident faces): every face adds three cross products T_c = (P_next - P_c) x (P_prev - P_c), one per corner c, to the raw
+// normal of that corner's vertex; with G = d/d(raw normal of corner c): d/dP_next = w x G, d/dP_prev = G x u, d/dP_c = -(both).
+__global__ void vert_normals_bwd_raw_kernel(const float* __restrict__ verts, const int* __restrict__ faces, const int* __restrict__ vf_ptr,
+                                            const int* __restrict__ vf_face, const int* __restrict__ vf_corner, int N, int V,
+                                            const float* __restrict__ g_normals, float* __restrict__ g_raw) {
+    pdl_wait_trigger();
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= (long long)N * V) return;
+    const int n = (int)(i / V), v = (int)(i - (long long)n * V);
+    const float* vb = verts + (size_t)n * V * 3;
+    float x[3] = {0.f, 0.f, 0.f};
+    for (int k = vf_ptr[v]; k < vf_ptr[v + 1]; ++k) {
+        const int f = vf_face[k], c = vf_corner[k];
+        const int ia = faces[3 * f + c], ib = faces[3 * f + (c + 1) % 3], ic = faces[3 * f + (c + 2) % 3];
+        const float ax = vb[3 * ia], ay = vb[3 * ia + 1], az = vb[3 * ia + 2];
+        const float ux = vb[3 * ib] - ax, uy = vb[3 * ib + 1] - ay, uz = vb[3 * ib + 2] - az;
+        const float wx = vb[3 * ic] - ax, wy = vb[3 * ic + 1] - ay, wz = vb[3 * ic + 2] - az;
+        x[0] += uy * wz - uz * wy; x[1] += uz * wx - ux * wz; x[2] += ux * wy - uy * wx;
+    }
+    const float g[3] = {g_normals[3 * i], g_normals[3 * i + 1], g_normals[3 * i + 2]};
+    float out[3];
+    normalize_bwd(x, g, out);
+    g_raw[3 * i] = out[0]; g_raw[3 * i + 1] = out[1]; g_raw[3 * i + 2] = out[2];
+}
+
+__global__ void vert_normals_bwd_gather_kernel(const float* __restrict__ verts, const int* __restrict__ faces, const int* __restrict__ vf_ptr,
+                                               const int* __restrict__ vf_face, const int* __restrict__ vf_corner, int N, int V,
+                                               const float* __restrict__ g_raw, float* __restrict__ g_verts) {
+    pdl_wait_trigger();
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= (long long)N * V) return;
+    const int n = (int)(i / V), v = (int)(i - (long long)n * V);
+    const float* vb = verts + (size_t)n * V * 3;
+    const float* gr = g_raw + (size_t)n * V * 3;
+    float acc[3] = {0.f, 0.f, 0.f};
+    for (int k = vf_ptr[v]; k < vf_ptr[v + 1]; ++k) {
+        const int f = vf_face[k], c = vf_corner[k];               // this vertex is corner c of face f
+        int id[3];
+        float Pc[3][3];
+#pragma unroll
+        for (int q = 0; q < 3; ++q) {
+            id[q] = faces[3 * f + q];
+            Pc[q][0] = vb[3 * id[q]]; Pc[q][1] = vb[3 * id[q] + 1]; Pc[q][2] = vb[3 * id[q] + 2];
+        }
+#pragma unroll
+        for (int cc = 0; cc < 3; ++cc) {                           // the term that belongs to corner cc
+            const int nx = (cc + 1) % 3, pv = (cc + 2) % 3;
+            const float G[3] = {gr[3 * id[cc]], gr[3 * id[cc] + 1], gr[3 * id[cc] + 2]};
+            const float u[3] = {Pc[nx][0] - Pc[cc][0], Pc[nx][1] - Pc[cc][1], Pc[nx][2] - Pc[cc][2]};
+            const float w[3] = {Pc[pv][0] - Pc[cc][0], Pc[pv][1] - Pc[cc][1], Pc[pv][2] - Pc[cc][2]};
+            const float gu[3] = {w[1] * G[2] - w[2] * G[1], w[2] * G[0] - w[0] * G[2], w[0] * G[1] - w[1] * G[0]};     // w x G
+            const float gw[3] = {G[1] * u[2] - G[2] * u[1], G[2] * u[0] - G[0] * u[2], G[0] * u[1] - G[1] * u[0]};     // G x u
+            if (c == nx) { acc[0] += gu[0]; acc[1] += gu[1]; acc[2] += gu[2]; }
+            else if (c == pv) { acc[0] += gw[0]; acc[1] += gw[1]; acc[2] += gw[2]; }
+            else { acc[0] -= gu[0] + gw[0]; acc[1] -= gu[1] + gw[1]; acc[2] -= gu[2] + gw[2]; }
+        }
+    }
+    g_verts[3 * i] += acc[0]; g_verts[3 * i + 1] += acc[1]; g_verts[3 * i + 2] += acc[2];
+}
+
 }  // namespace raster
 }  // namespace fb
 
@@ -756,13 +1019,63 @@ extern "C" int findb200_phong_shade(const int32_t* pix_to_face, const float* bar
     if (n_images == 0) return 0;
     fb::raster::PhongParams P;
     P.p2f = pix_to_face; P.bary = bary; P.zbuf = zbuf; P.dists = dists; P.verts = verts_world; P.normals = vert_normals;
-    P.colours = vert_colours; P.faces = faces; P.cam = cam_centres; P.HW = H * W; P.n_pix = (long long)n_images * H * W;
+    P.colours = vert_colours; P.faces = faces; P.cam = cam_centres; P.HW = H * W; P.H_ = H; P.n_pix = (long long)n_images * H * W;
     P.V = V; P.views = num_views; P.out = image;
     for (int d = 0; d < 3; ++d) { P.light[d] = shading[d]; P.amb[d] = shading[3 + d]; P.dif[d] = shading[6 + d]; P.spec[d] = shading[9 + d]; P.bg[d] = shading[12 + d]; }
     P.shininess = shading[15]; P.sigma = shading[16]; P.gamma = shading[17]; P.znear = shading[18]; P.zfar = shading[19];
     FB_REQUIRE(P.sigma > 0.f && P.gamma > 0.f && P.zfar > P.znear, FINDB200_ERR_ARG, "phong_shade: sigma, gamma > 0 and zfar > znear required");
     FB_MARK("phong_shade", st);
     FB_CUDA(launch_pdl(fb::raster::phong_shade_kernel, dim3((unsigned)((P.n_pix + 255) / 256)), dim3(256), 0, st, P));
+    FB_MARK_END(st);
+    return 0;
+}
+
+// grad buffers are ACCUMULATED into (the caller zeroes them): grad_verts_world / grad_normals / grad_colours [M, V, 3],
+// grad_verts_ndc [n_images, V, 3]
+extern "C" int findb200_phong_shade_backward(const float* grad_image, const int32_t* pix_to_face, const float* bary, const float* zbuf,
+                                             const float* dists, int n_images, int H, int W, int num_views, const float* verts_ndc,
+                                             const float* verts_world, const float* vert_normals, const float* vert_colours,
+                                             const int32_t* faces, int V, const float* cam_centres, const float* shading,
+                                             float* grad_verts_world, float* grad_normals, float* grad_colours, float* grad_verts_ndc,
+                                             void* stream) {
+    cudaStream_t st = (cudaStream_t)stream;
+    FB_REQUIRE(n_images >= 0 && H >= 1 && W >= 1 && num_views >= 1 && V >= 1 && n_images % num_views == 0, FINDB200_ERR_SHAPE,
+               "phong_shade_backward: bad shape images=%d views=%d", n_images, num_views);
+    FB_REQUIRE(grad_image && pix_to_face && bary && zbuf && dists && verts_ndc && verts_world && vert_normals && vert_colours && faces &&
+               cam_centres && shading && grad_verts_world && grad_normals && grad_colours && grad_verts_ndc, FINDB200_ERR_ARG,
+               "phong_shade_backward: null argument");
+    if (n_images == 0) return 0;
+    fb::raster::PhongBwdParams B;
+    fb::raster::PhongParams& P = B.f;
+    P.p2f = pix_to_face; P.bary = bary; P.zbuf = zbuf; P.dists = dists; P.verts = verts_world; P.normals = vert_normals;
+    P.colours = vert_colours; P.faces = faces; P.cam = cam_centres; P.HW = H * W; P.H_ = H; P.n_pix = (long long)n_images * H * W;
+    P.V = V; P.views = num_views; P.out = nullptr;
+    for (int d = 0; d < 3; ++d) { P.light[d] = shading[d]; P.amb[d] = shading[3 + d]; P.dif[d] = shading[6 + d]; P.spec[d] = shading[9 + d]; P.bg[d] = shading[12 + d]; }
+    P.shininess = shading[15]; P.sigma = shading[16]; P.gamma = shading[17]; P.znear = shading[18]; P.zfar = shading[19];
+    FB_REQUIRE(P.sigma > 0.f && P.gamma > 0.f && P.zfar > P.znear, FINDB200_ERR_ARG, "phong_shade_backward: sigma, gamma > 0 and zfar > znear required");
+    B.grad_image = grad_image; B.verts_ndc = verts_ndc; B.g_verts = grad_verts_world; B.g_normals = grad_normals; B.g_colours = grad_colours;
+    B.g_ndc = grad_verts_ndc;
+    FB_MARK("phong_shade_bwd", st);
+    FB_CUDA(launch_pdl(fb::raster::phong_shade_bwd_kernel, dim3((unsigned)((P.n_pix + 127) / 128)), dim3(128), 0, st, B));
+    FB_MARK_END(st);
+    return 0;
+}
+
+// grad_verts [N, V, 3] += d/d(verts) through Meshes.verts_normals_padded(), given grad_normals [N, V, 3]; scratch: [N, V, 3] floats
+extern "C" int findb200_vertex_normals_backward(const float* verts, int N, int V, const int32_t* faces, const int32_t* vf_ptr,
+                                                const int32_t* vf_face, const int32_t* vf_corner, const float* grad_normals, float* scratch,
+                                                float* grad_verts, void* stream) {
+    cudaStream_t st = (cudaStream_t)stream;
+    FB_REQUIRE(N >= 0 && V >= 1, FINDB200_ERR_SHAPE, "vertex_normals_backward: bad shape N=%d V=%d", N, V);
+    FB_REQUIRE(verts && faces && vf_ptr && vf_face && vf_corner && grad_normals && scratch && grad_verts, FINDB200_ERR_ARG,
+               "vertex_normals_backward: null argument");
+    if (N == 0) return 0;
+    const long long tot = (long long)N * V;
+    FB_MARK("vert_normals_bwd", st);
+    FB_CUDA(launch_pdl(fb::raster::vert_normals_bwd_raw_kernel, dim3((unsigned)((tot + 255) / 256)), dim3(256), 0, st, verts, faces, vf_ptr,
+                       vf_face, vf_corner, N, V, grad_normals, scratch));
+    FB_CUDA(launch_pdl(fb::raster::vert_normals_bwd_gather_kernel, dim3((unsigned)((tot + 255) / 256)), dim3(256), 0, st, verts, faces, vf_ptr,
+                       vf_face, vf_corner, N, V, (const float*)scratch, grad_verts));
     FB_MARK_END(st);
     return 0;
 }

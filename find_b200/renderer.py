@@ -159,6 +159,67 @@ def vertex_normals(verts: torch.Tensor, topo) -> torch.Tensor:
     return out
 
 
+class _PhongImage(torch.autograd.Function):
+    """SoftPhongShader image of the hard fragments with its backward (csrc/raster.cu: findb200_rasterize_nearest,
+    findb200_vertex_normals, findb200_phong_shade / _backward, findb200_vertex_normals_backward).  The camera projection's
+    backward is torch autograd of ``FootRenderer.project`` (a handful of elementwise ops)."""
+
+    @staticmethod
+    def forward(ctx, verts, colours, rdr, topo, R, T):
+        lib = _lib.load()
+        v = verts.detach().contiguous().float()
+        dev = v.device
+        M, V = v.shape[0], v.shape[1]
+        nv, S = R.shape[0], rdr.image_size
+        c = colours.detach().contiguous().float()
+        ndc = rdr.project(v, R, T).contiguous()
+        p2f, zbuf, bary, dists = rasterize_nearest(ndc, topo.faces, S, blur_radius=0.0, perspective_correct=True)
+        normals = vertex_normals(v, topo)
+        cam = (-torch.einsum("kj,kij->ki", T.to(torch.float32), R.to(torch.float32))).to(dev).contiguous()   # C = -T R^T
+        shading = [*rdr.light_location, *([rdr.light_ambient] * 3), *([rdr.light_diffuse] * 3), *([rdr.light_specular] * 3),
+                   *rdr.background_color, rdr.shininess, 1e-4, 1e-4, rdr.znear, rdr.zfar]
+        sh = (ctypes.c_float * 20)(*shading)
+        image = torch.empty(M * nv, S, S, 3, dtype=torch.float32, device=dev)
+        p32 = p2f[..., 0].to(torch.int32).contiguous()
+        bary, zbuf, dists = bary.contiguous(), zbuf.contiguous(), dists.contiguous()
+        with torch.cuda.device(dev):
+            rc = lib.findb200_phong_shade(_lib.ptr(p32), _lib.ptr(bary), _lib.ptr(zbuf), _lib.ptr(dists), M * nv, S, S, nv, _lib.ptr(v),
+                                          _lib.ptr(normals), _lib.ptr(c), _lib.ptr(topo.faces), V, _lib.ptr(cam),
+                                          ctypes.cast(sh, ctypes.c_void_p), _lib.ptr(image), _lib.stream_ptr(dev))
+        _lib.check(rc, "findb200_phong_shade")
+        ctx.save_for_backward(v, c, ndc, p32, bary, zbuf, dists, normals, cam)
+        ctx.misc = (rdr, topo, R, T, shading, M, V, nv, S)
+        ctx.mark_non_differentiable(p32)
+        return image.reshape(M, nv, S, S, 3), p32
+
+    @staticmethod
+    def backward(ctx, g_image, _g_p2f):
+        lib = _lib.load()
+        v, c, ndc, p32, bary, zbuf, dists, normals, cam = ctx.saved_tensors
+        rdr, topo, R, T, shading, M, V, nv, S = ctx.misc
+        dev = v.device
+        g = g_image.contiguous().float()
+        g_verts, g_normals, g_colours = torch.zeros_like(v), torch.zeros_like(v), torch.zeros_like(v)
+        g_ndc = torch.zeros_like(ndc)
+        scratch = torch.empty_like(v)
+        sh = (ctypes.c_float * 20)(*shading)
+        with torch.cuda.device(dev):
+            st = _lib.stream_ptr(dev)
+            rc = lib.findb200_phong_shade_backward(_lib.ptr(g), _lib.ptr(p32), _lib.ptr(bary), _lib.ptr(zbuf), _lib.ptr(dists), M * nv, S, S, nv,
+                                                   _lib.ptr(ndc), _lib.ptr(v), _lib.ptr(normals), _lib.ptr(c), _lib.ptr(topo.faces), V,
+                                                   _lib.ptr(cam), ctypes.cast(sh, ctypes.c_void_p), _lib.ptr(g_verts), _lib.ptr(g_normals),
+                                                   _lib.ptr(g_colours), _lib.ptr(g_ndc), st)
+            _lib.check(rc, "findb200_phong_shade_backward")
+            rc = lib.findb200_vertex_normals_backward(_lib.ptr(v), M, V, _lib.ptr(topo.faces), _lib.ptr(topo.vf_ptr), _lib.ptr(topo.vf_face),
+                                                      _lib.ptr(topo.vf_corner), _lib.ptr(g_normals), _lib.ptr(scratch), _lib.ptr(g_verts), st)
+            _lib.check(rc, "findb200_vertex_normals_backward")
+        with torch.enable_grad():                                     # backward of the camera projection
+            vv = v.detach().requires_grad_(True)
+            (g_proj,) = torch.autograd.grad(rdr.project(vv, R, T), vv, g_ndc)
+        g_verts = g_verts + g_proj
+        return (g_verts if ctx.needs_input_grad[0] else None), (g_colours if ctx.needs_input_grad[1] else None), None, None, None, None
+
+
 class FootRenderer(nn.Module):
     def __init__(self, image_size, device="cuda", background_color=(1.0, 1.0, 1.0), bin_size=None, z_clip_value=None,
                  max_faces_per_bin=None):
@@ -226,10 +287,6 @@ class FootRenderer(nn.Module):
                 return_mask_out_masks=False, return_features=False, features=None) -> dict:
         if return_features or return_depth or keypoints is not None:
             raise NotImplementedError("find_b200.renderer: feature / depth / keypoint rendering is the rest of SURVEY.md §8(f) row 4")
-        if return_images and torch.is_grad_enabled() and (input_meshes.verts_padded().requires_grad
-                                                          or getattr(self._colours(input_meshes, False), "requires_grad", False)):
-            raise NotImplementedError("find_b200.renderer: the Phong image is forward-only so far (ground-truth / evaluation renders "
-                                      "under torch.no_grad()); its backward is the rest of SURVEY.md §8(f) row 4")
         if mask_out_faces and masked_faces is None:
             raise NotImplementedError("find_b200.renderer: mask_out_faces needs masked_faces (the TexturesUV u = v = 0 convention of "
                                       "renderer.py:337-345 is not built)")
@@ -278,6 +335,8 @@ class FootRenderer(nn.Module):
                 masks.append(mpix)
                 mask[n, mpix] = 0.0
                 if return_images:
+                    if out["image"].requires_grad and n == 0:
+                        out["image"] = out["image"].clone()
                     out["image"][n, mpix] = 1.0
             if return_mask_out_masks:
                 out["mask_out_masks"] = torch.stack(masks).reshape(num_meshes, num_views, S, S)
@@ -285,7 +344,7 @@ class FootRenderer(nn.Module):
         return out
 
 
-    # ---- Phong image (forward only) -----------------------------------------------------------------------------------
+    # ---- Phong image -----------------------------------------------------------------------------------
     def _colours(self, meshes: Meshes, required=True):
         tex = meshes.textures
         if tex is None:
@@ -296,34 +355,22 @@ class FootRenderer(nn.Module):
         return c
 
     def _render_images(self, meshes: Meshes, R, T):
+        """-> (image [M,views,S,S,3], pix_to_face int32 [M*views,S,S]).  Differentiable w.r.t. the mesh vertices and the vertex
+        colours (``_PhongImage``); under ``torch.no_grad()`` only the forward kernels run."""
         from .mesh import _topology_of
-        lib = _lib.load()
-        verts = meshes.verts_padded().detach().contiguous().float()
+        verts = meshes.verts_padded()
         dev = _lib.require_cuda(verts)
         topo = _topology_of(meshes).to(dev)
-        M, V = verts.shape[0], verts.shape[1]
-        nv, S = R.shape[0], self.image_size
-        colours = self._colours(meshes).detach().to(dev, torch.float32)
+        M = verts.shape[0]
+        colours = self._colours(meshes).to(dev)
         if colours.dim() == 2:
             colours = colours.unsqueeze(0).expand(M, -1, -1)
-        colours = colours.contiguous()
-        ndc = self.project(verts, R, T)
-        p2f, zbuf, bary, dists = rasterize_nearest(ndc, topo.faces, S, blur_radius=0.0, perspective_correct=True)
-        normals = vertex_normals(verts, topo)
-        cam = (-torch.einsum("kj,kij->ki", T.to(torch.float32), R.to(torch.float32))).to(dev).contiguous()   # C = -T R^T
-        shading = (ctypes.c_float * 20)(*self.light_location, *([self.light_ambient] * 3), *([self.light_diffuse] * 3),
-                                        *([self.light_specular] * 3), *self.background_color, self.shininess, 1e-4, 1e-4,
-                                        self.znear, self.zfar)
-        image = torch.empty(M * nv, S, S, 3, dtype=torch.float32, device=dev)
-        p32 = p2f[..., 0].to(torch.int32).contiguous()
-        with torch.cuda.device(dev):
-            rc = lib.findb200_phong_shade(_lib.ptr(p32), _lib.ptr(bary.contiguous()), _lib.ptr(zbuf.contiguous()), _lib.ptr(dists.contiguous()),
-                                          M * nv, S, S, nv, _lib.ptr(verts), _lib.ptr(normals), _lib.ptr(colours), _lib.ptr(topo.faces), V,
-                                          _lib.ptr(cam), ctypes.cast(shading, ctypes.c_void_p), _lib.ptr(image), _lib.stream_ptr(dev))
-        _lib.check(rc, "findb200_phong_shade")
-        return image.reshape(M, nv, S, S, 3), p32
+        image, p32 = _PhongImage.apply(verts.float(), colours.float(), self, topo, R, T)
+        return image, p32
 
     def _mask_images(self, images, p2f, masked_faces):
+        if images.requires_grad:
+            images = images.clone()                                   # in-place masking below (renderer.py:354-356)
         M, nv, S = images.shape[0], images.shape[1], images.shape[2]
         p2f = p2f.reshape(M, nv, S, S)
         masks = []

@@ -239,6 +239,21 @@ int findb200_phong_shade(const int32_t* pix_to_face, const float* bary, const fl
                          int W, int num_views, const float* verts_world, const float* vert_normals, const float* vert_colours,
                          const int32_t* faces, int V, const float* cam_centres, const float* shading, float* image, void* stream);
 
+/* Backward of the Phong image (FootRenderer.forward(return_images=True) with gradients: the predicted renders of the pixel /
+ * perceptual losses, model.py:1089-1107): d/d(world vertices), d/d(vertex normals), d/d(vertex colours) and d/d(NDC vertices of
+ * every image) from d/d(image), ACCUMULATED into the caller's pre-zeroed buffers.  findb200_vertex_normals_backward then carries
+ * d/d(normals) to the vertices (scratch: N * V * 3 floats), and the camera projection's backward is the caller's (torch autograd
+ * of FootRenderer.project).  Same arguments as the forward plus verts_ndc [n_images, V, 3]. */
+int findb200_phong_shade_backward(const float* grad_image, const int32_t* pix_to_face, const float* bary, const float* zbuf,
+                                  const float* dists, int n_images, int H, int W, int num_views, const float* verts_ndc,
+                                  const float* verts_world, const float* vert_normals, const float* vert_colours,
+                                  const int32_t* faces, int V, const float* cam_centres, const float* shading,
+                                  float* grad_verts_world, float* grad_normals, float* grad_colours, float* grad_verts_ndc,
+                                  void* stream);
+int findb200_vertex_normals_backward(const float* verts, int N, int V, const int32_t* faces, const int32_t* vf_ptr,
+                                     const int32_t* vf_face, const int32_t* vf_corner, const float* grad_normals, float* scratch,
+                                     float* grad_verts, void* stream);
+
 /* ------------------------------------------------------------------------------------------------------
  * Optimiser updates: torch.optim.Adam(main_params / latent_params) and
  * torch.optim.SGD(reg_params, momentum=0.9) as stepped at src/train/train.py:161-168, src/train/trainer.py:122-123.

@@ -252,5 +252,47 @@ def test_phong_image_forward_matches_oracle():
     assert torch.equal(hard["mask"].cpu(), torch.any(img < 1, dim=-1).float()) and torch.equal(hard["image"].cpu(), img)
     mm = masked["mask_out_masks"]
     assert float((masked["image"][mm] - 1.0).abs().max()) == 0.0 and float(masked["mask"][mm].abs().max()) == 0.0
-    with pytest.raises(NotImplementedError):
-        r(Meshes(verts.to(dev).requires_grad_(True), tf.to(dev), textures=colours.to(dev)), R, T, return_images=True)
+
+
+@pytest.mark.gpu
+def test_phong_image_backward_matches_oracle_autograd():
+    """FootRenderer.forward(return_images=True) WITH gradients (the predicted renders of the pixel / perceptual losses,
+    model.py:1089-1107): d/d(world vertices) and d/d(vertex colours) of a weighted sum of the image against torch autograd of
+    oracle/raster_oracle.py::render_image (same rules as PyTorch3D: through the barycentrics of position / normal / texel, the
+    vertex normals, the signed edge distance of the blend; pix_to_face and the depth order carry none).  Tolerance rel-L2 2e-3:
+    fp32 atomics, and the sigmoid(-dist / 1e-4) factor that makes edge pixels 1e4 times more sensitive than interior ones."""
+    dev, verts, tf, _, _, _ = _scene(162, ["topdown"], B=2, seed=11)
+    S = 40
+    r = FootRenderer(S, device=dev)
+    R, T = r.view_from(["topdown", "45"])
+    g = torch.Generator().manual_seed(12)
+    colours = torch.rand(2, verts.shape[1], 3, generator=g)
+    wimg = torch.rand(2, 2, S, S, 3, generator=g)
+    # oracle (CPU, fp32 like the kernels so that the same pixels hit the same faces)
+    vo = verts.clone().requires_grad_(True)
+    co = colours.clone().requires_grad_(True)
+    tot = 0.0
+    imgs_o = []
+    for m in range(2):
+        for k in range(2):
+            im = ro.render_image(vo[m], tf, co[m], R[k], T[k], S, S)
+            imgs_o.append(im.detach())
+            tot = tot + (im * wimg[m, k]).sum()
+    tot.backward()
+    # CUDA
+    vg = verts.to(dev).requires_grad_(True)
+    cg = colours.to(dev).requires_grad_(True)
+    out = r(Meshes(vg, tf.to(dev), textures=cg), R, T, return_images=True)
+    img = out["image"]
+    assert img.requires_grad
+    (img * wimg.to(dev)).sum().backward()
+    same = torch.stack([(img[m, k].detach().cpu() - imgs_o[m * 2 + k]).abs().max() for m in range(2) for k in range(2)])
+    assert float(same.max()) < 2e-3                                         # same fragments on both sides
+    assert float(vo.grad.abs().max()) > 0 and float(co.grad.abs().max()) > 0
+    assert rel_l2(cg.grad.cpu(), co.grad) < 2e-3, rel_l2(cg.grad.cpu(), co.grad)
+    assert rel_l2(vg.grad.cpu(), vo.grad) < 2e-3, rel_l2(vg.grad.cpu(), vo.grad)
+    # the image term composes with the silhouette term in one backward (model.py:1089: both requested together)
+    vg2 = verts.to(dev).requires_grad_(True)
+    both = r(Meshes(vg2, tf.to(dev), textures=colours.to(dev)), R, T, return_images=True, return_mask=True)
+    ((both["image"] * wimg.to(dev)).sum() + both["mask"].sum()).backward()
+    assert torch.isfinite(vg2.grad).all() and float((vg2.grad - vg.grad).abs().max()) > 0
