@@ -101,3 +101,26 @@ def test_two_rank_gloo_matches_single_rank():
             np.testing.assert_allclose(g[lo:hi], ref["table_grads"][k][lo:hi].numpy(), rtol=2e-4, atol=1e-7)
             other = np.delete(g, np.arange(lo, hi), axis=0)
             assert not other.any()                      # rows of feet owned by the other rank are never touched
+
+
+@pytest.mark.gpu
+def test_sharded_step_on_two_gpus_matches_single_rank():
+    """Two real ranks (torchrun, NCCL rendezvous, the library's peer-memory allreduce inside the step graph) against the single-rank
+    step on the concatenated batch: tools/dp_check.py.  Needs >= 2 visible GPUs; skipped otherwise (the driver's GPU box has one)."""
+    import json
+    import subprocess
+    import sys
+    if not torch.cuda.is_available() or torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    port = s.getsockname()[1]
+    s.close()
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr", "127.0.0.1",
+           "--master-port", str(port), os.path.join(root, "tools", "dp_check.py")]
+    res = subprocess.run(cmd, cwd=root, stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True, timeout=600)
+    assert res.returncode == 0, res.stderr[-2000:]
+    line = [ln for ln in res.stdout.splitlines() if ln.startswith("{")][-1]
+    out = json.loads(line)
+    assert out["ok"] and out["all_ranks_identical"] and out["bucket_rel_l2"] < 1e-4 and out["shapevec_rows_rel_l2"] < 1e-4, out
