@@ -537,6 +537,7 @@ struct Workspace {
     float *soa_x, *soa_y;
     int *perm_x, *perm_y;
     float *box_x, *box_y, *sbox_x, *sbox_y;
+    int2 *lut_x, *lut_y;              // grid mode: linear cell -> [start, end) of the sorted cloud
     int *cell_x, *cell_y, *rank_x, *rank_y;
     double *sum_x, *sum_y;
     int P1p, P2p, C1p, C2p, S1p, S2p, gl1, gl2;
@@ -566,6 +567,7 @@ static Workspace carve(void* base, int N, int P1, int P2) {
     w.sbox_x = (float*)take((size_t)N * 6 * w.S1p * 4); w.sbox_y = (float*)take((size_t)N * 6 * w.S2p * 4);
     w.cell_x = (int*)take((size_t)N * P1 * 4); w.cell_y = (int*)take((size_t)N * P2 * 4);
     w.rank_x = (int*)take((size_t)N * P1 * 4); w.rank_y = (int*)take((size_t)N * P2 * 4);
+    w.lut_x = (int2*)take(((size_t)N << (3 * w.gl1)) * 8); w.lut_y = (int2*)take(((size_t)N << (3 * w.gl2)) * 8);
     w.sum_x = (double*)take((size_t)N * tail_blocks(P1) * 8); w.sum_y = (double*)take((size_t)N * tail_blocks(P2) * 8);   // >= fin_blocks
     w.bytes = off;
     return w;
@@ -602,7 +604,7 @@ static int g_knn_mode = -1;
 static int knn_mode() {
     if (g_knn_mode < 0) {
         const char* e = getenv("FINDB200_KNN_MODE");
-        g_knn_mode = (e && e[0] >= '0' && e[0] <= '2') ? e[0] - '0' : 0;
+        g_knn_mode = (e && e[0] >= '0' && e[0] <= '3') ? e[0] - '0' : 0;
     }
     return g_knn_mode;
 }
@@ -674,6 +676,7 @@ static int g_sort_cta_max = -1;
 static bool sort_in_one_cta(int P1, int P2) {
     if (g_sort_cta_max < 0) { const char* e = getenv("FINDB200_SORT_CTA_MAX"); g_sort_cta_max = e ? atoi(e) : 0; }
     const int Pm = P1 > P2 ? P1 : P2;
+    if (knn_mode() == 3) return false;                       // the grid search reads the global histogram (cell table)
     return Pm <= g_sort_cta_max && grid_log2(Pm) <= 4;       // the cluster kernel keeps ncell / 8 <= 1024 cells per CTA
 }
 
@@ -712,6 +715,24 @@ static int run_knn_cull(const float* x, const float* y, const int64_t* lx, const
     FB_CUDA(fb::launch_pdl(cloud_scan_kernel, dim3(N, 2), 1024, 0, st, sp));
     FB_MARK("sort_scatter2", st);
     FB_CUDA(fb::launch_pdl(cloud_scatter_kernel, dim3((Ppm + 255) / 256, N, 2), 256, 0, st, sp));
+    if (knn_mode() == 3) {
+        // grid search (knn_cull.cuh): no box hierarchy, a cell table instead; one thread per query
+        const int ncm = 1 << (3 * (w.gl1 > w.gl2 ? w.gl1 : w.gl2));
+        FB_MARK("sort_boxes", st);
+        FB_CUDA(fb::launch_pdl(cloud_lut_kernel, dim3((ncm + 255) / 256, N, 2), 256, 0, st, sp, w.lut_x, w.lut_y));
+        GridParams gp{};
+        gp.N = N; gp.ndir = both ? 2 : 1; gp.stats = w.stats;
+        gp.dir[0] = GridDir{w.soa_x, w.perm_x, w.soa_y, w.perm_y, w.lut_y, w.bbmin_y, w.bbmax_y, lx, ly, w.keys_x, P1, w.P1p, P2, w.P2p, w.gl2,
+                            (P1 + 255) / 256};
+        gp.dir[1] = GridDir{w.soa_y, w.perm_y, w.soa_x, w.perm_x, w.lut_x, w.bbmin_x, w.bbmax_x, ly, lx, w.keys_y, P2, w.P2p, P1, w.P1p, w.gl1,
+                            (P2 + 255) / 256};
+        gp.blocks_dir0 = N * gp.dir[0].blocks_per_cloud;
+        const int blocks = gp.blocks_dir0 + (both ? N * gp.dir[1].blocks_per_cloud : 0);
+        FB_MARK("knn_main", st);
+        FB_CUDA(fb::launch_pdl(knn_grid_kernel, blocks, 256, 0, st, gp));
+        FB_CUDA(cudaGetLastError());
+        return 0;
+    }
     FB_MARK("sort_boxes", st);
     FB_CUDA(fb::launch_pdl(cloud_boxes_kernel, dim3((Ppm / kCullChunk + 7) / 8, N, 2), 256, 0, st, sp));
     FB_CUDA(fb::launch_pdl(cloud_superboxes_kernel, dim3((Ppm / kCullChunk / 32 + 8) / 8, N, 2), 256, 0, st, sp));
@@ -766,7 +787,7 @@ using namespace fb::chamfer;
 extern "C" {
 
 int findb200_set_knn_mode(int mode, int kq) {
-    FB_REQUIRE((mode == 0 || mode == 1 || mode == 2) && (kq == 0 || kq == 1 || kq == 2 || kq == 4), FINDB200_ERR_ARG, "set_knn_mode: mode 0/1/2, kq 0/1/2/4");
+    FB_REQUIRE(mode >= 0 && mode <= 3 && (kq == 0 || kq == 1 || kq == 2 || kq == 4), FINDB200_ERR_ARG, "set_knn_mode: mode 0..3, kq 0/1/2/4");
     g_knn_mode = mode; g_cull_kq = kq;
     return 0;
 }

@@ -1080,5 +1080,156 @@ __global__ void __launch_bounds__(128) knn_cull_cta_kernel(const CullParams prm)
     }
 }
 
+// ---- grid search: one thread per query --------------------------------------------------------------------------------
+// The same sorted clouds, read through a table of the grid's cells (cloud_lut_kernel: linear cell index -> [start, end) in the
+// sorted order).  A thread owns ONE query: it visits the cell the query falls in, then the shells of cells around it, keeping
+// the lexicographic minimum of (distance, original index), and stops when nothing outside the visited block can beat or tie it:
+//   every point outside the block [x0..x1] x [y0..y1] x [z0..z1] lies beyond one of the block's faces that are interior to the
+//   grid, so its COMPUTED distance is >= the squared gap from the query to the nearest such face — taken with a relative
+//   safety margin that covers the rounding of the cell assignment (p -> floor((p - lo) * inv_h)) and of the distance itself —
+// or when every point of the cloud has been visited (degenerate grids, far-away queries).  A surface cloud of 10 k points in
+// a 16^3 grid has ~2.5 points per occupied cell: a query evaluates the ~30-70 points of its 27-cell neighbourhood instead of
+// the ~540 of the box-hierarchy walk, there is no per-group serial chain, and 160 k independent threads hide the latency.
+// Exactness: same distance expression and tie rule as everywhere else; bit-identical to the other kernels (tests).
+// lower bound of |q - p| along one axis for any point p assigned to cell `cell` of that axis (0 if q may be level with it),
+// with the same safety margins as the block faces below
+FB_DEVINL float cell_gap(float q, float lo, float h, int cell) {
+    const float a = lo + (float)cell * h * (1.0f - 0x1p-18f) - fabsf(lo) * 0x1p-20f;            // cell's points are >= a
+    const float b = lo + (float)(cell + 1) * h * (1.0f + 0x1p-18f) + fabsf(lo) * 0x1p-20f;      // and < b
+    return fmaxf(0.f, fmaxf(a - q, q - b));
+}
+
+struct GridDir {
+    const float* q_soa;   // sorted queries [N][3][Pq_pad]
+    const int* q_perm;
+    const float* t_soa;   // sorted targets [N][3][Pt_pad]
+    const int* t_perm;
+    const int2* t_lut;    // [N][G^3] linear cell -> [start, end)
+    const unsigned *t_bbmin, *t_bbmax;   // [N][3] order-encoded bounding box of the targets
+    const int64_t *len_q, *len_t;
+    unsigned long long* keys;            // [N][Pq] original query order
+    int Pq, Pq_pad, Pt, Pt_pad, glog2, blocks_per_cloud;
+};
+struct GridParams { GridDir dir[2]; int ndir, N, blocks_dir0; unsigned long long* stats; };
+
+// 6. (grid mode) linear cell table.  grid (ceil(ncell / 256), N, 2), block 256; after cloud_scan_kernel (hist = exclusive starts).
+__global__ void __launch_bounds__(256) cloud_lut_kernel(const SortParams prm, int2* __restrict__ lut_x, int2* __restrict__ lut_y) {
+    fb::pdl_wait_trigger();
+    const SortSet& S = prm.set[blockIdx.z];
+    if (S.P <= 0) return;
+    const int n = blockIdx.y, G = 1 << S.glog2, ncell = 1 << (3 * S.glog2);
+    const int lin = blockIdx.x * 256 + threadIdx.x;
+    if (lin >= ncell) return;
+    const int cx = lin & (G - 1), cy = (lin >> S.glog2) & (G - 1), cz = lin >> (2 * S.glog2);
+    const int h = (int)hilbert3((uint32_t)cx, (uint32_t)cy, (uint32_t)cz, S.glog2);
+    const int* hist = S.hist + ((size_t)n << (3 * S.glog2));
+    const int start = hist[h], end = (h + 1 < ncell) ? hist[h + 1] : set_len(S, n);
+    (blockIdx.z ? lut_y : lut_x)[((size_t)n << (3 * S.glog2)) + lin] = make_int2(start, end);
+}
+
+__global__ void __launch_bounds__(256) knn_grid_kernel(const GridParams prm) {
+    fb::pdl_wait_trigger();
+    const int d = (int)blockIdx.x >= prm.blocks_dir0 ? 1 : 0;
+    const GridDir& D = prm.dir[d];
+    const int bl = (int)blockIdx.x - (d ? prm.blocks_dir0 : 0);
+    const int n = bl / D.blocks_per_cloud;
+    const int i = (bl - n * D.blocks_per_cloud) * 256 + threadIdx.x;          // sorted query index
+    const int len_q = D.len_q ? min((int)D.len_q[n], D.Pq) : D.Pq;
+    const int len_t = D.len_t ? min((int)D.len_t[n], D.Pt) : D.Pt;
+    __shared__ unsigned long long s_eval;
+    if (threadIdx.x == 0) s_eval = 0ull;
+    __syncthreads();
+    unsigned long long n_eval = 0;
+    if (i < len_q && len_t > 0) {
+    const float* qs = D.q_soa + (size_t)n * 3 * D.Pq_pad;
+    const float fx = __ldg(qs + i), fy = __ldg(qs + D.Pq_pad + i), fz = __ldg(qs + 2 * D.Pq_pad + i);
+    const float* ts = D.t_soa + (size_t)n * 3 * D.Pt_pad;
+    const int* tperm = D.t_perm + (size_t)n * D.Pt_pad;
+    const int G = 1 << D.glog2;
+    const int2* lut = D.t_lut + ((size_t)n << (3 * D.glog2));
+    // the targets' grid (same arithmetic as cloud_grid)
+    float lo[3], ext = 0.f;
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        const unsigned a = D.t_bbmin[n * 3 + k], b = D.t_bbmax[n * 3 + k];
+        const float l = a == 0xFFFFFFFFu ? 0.f : dec_ord(a), h = b == 0u ? 0.f : dec_ord(b);
+        lo[k] = l;
+        ext = fmaxf(ext, h - l);
+    }
+    float inv_h = (ext > 0.f && ext < CUDART_INF_F) ? (float)G / ext : 0.f;
+    if (!(inv_h < CUDART_INF_F)) inv_h = 0.f;
+    const float hcell = inv_h > 0.f ? 1.0f / inv_h : 0.f;
+    const int cx = cell_coord(fx, lo[0], inv_h, G), cy = cell_coord(fy, lo[1], inv_h, G), cz = cell_coord(fz, lo[2], inv_h, G);
+    const float q[3] = {fx, fy, fz};
+
+    float best = CUDART_INF_F;
+    int bj = 0x7fffffff;
+    int visited = 0;
+    for (int r = 0; r < G; ++r) {
+        const int x0 = max(cx - r, 0), x1 = min(cx + r, G - 1), y0 = max(cy - r, 0), y1 = min(cy + r, G - 1), z0 = max(cz - r, 0),
+                  z1 = min(cz + r, G - 1);
+        for (int z = z0; z <= z1; ++z)
+            for (int y = y0; y <= y1; ++y) {
+                const bool face = (abs(z - cz) == r) || (abs(y - cy) == r);
+                // on a face row every x belongs to the shell; otherwise only the two end cells do
+                // squared gap from the query to this row of cells along y and z (0 when the query is level with the row)
+                float gyz = 0.f;
+                if (r > 0 && inv_h > 0.f) {
+                    const float gy = cell_gap(q[1], lo[1], hcell, y), gz = cell_gap(q[2], lo[2], hcell, z);
+                    gyz = gy * gy + gz * gz;
+                    if (gyz * (1.0f - 0x1p-18f) > best) continue;          // the whole row is farther than the best so far
+                }
+                for (int x = x0; x <= x1; x += (face || r == 0) ? 1 : max(x1 - x0, 1)) {
+                    if (!face && abs(x - cx) != r) continue;
+                    if (r > 0 && inv_h > 0.f) {                                // this cell's box cannot beat or tie the best: skip it
+                        const float gx = cell_gap(q[0], lo[0], hcell, x);
+                        if ((gyz + gx * gx) * (1.0f - 0x1p-18f) > best) continue;
+                    }
+                    const int2 se = __ldg(lut + (((z << D.glog2) + y) << D.glog2) + x);
+                    for (int j = se.x; j < se.y; ++j) {
+                        const float dd = dist_exact(fx, fy, fz, __ldg(ts + j), __ldg(ts + D.Pt_pad + j), __ldg(ts + 2 * D.Pt_pad + j));
+                        if (dd <= best) {                       // NaN never enters
+                            const int oj = __ldg(tperm + j);
+                            if (dd < best || oj < bj) { best = dd; bj = oj; }
+                        }
+                    }
+                    visited += se.y - se.x;
+                    n_eval += (unsigned long long)(se.y - se.x);
+                }
+            }
+        if (visited >= len_t) break;
+        if (inv_h == 0.f) continue;                               // single-cell grid: geometry says nothing
+        // lower bound of the computed distance of any point outside the block
+        float lb = CUDART_INF_F;
+        const int b0[3] = {x0, y0, z0}, b1[3] = {x1, y1, z1};
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+            if (b0[k] > 0) {           // points in cells < b0: p < lo + b0 * h (1 + margin)
+                const float face_hi = lo[k] + (float)b0[k] * hcell * (1.0f + 0x1p-18f) + fabsf(lo[k]) * 0x1p-20f;
+                const float g = q[k] - face_hi;
+                lb = fminf(lb, g > 0.f ? g * g * (1.0f - 0x1p-18f) : 0.f);
+            }
+            if (b1[k] < G - 1) {       // points in cells > b1: p >= lo + (b1 + 1) * h (1 - margin)
+                const float face_lo = lo[k] + (float)(b1[k] + 1) * hcell * (1.0f - 0x1p-18f) - fabsf(lo[k]) * 0x1p-20f;
+                const float g = face_lo - q[k];
+                lb = fminf(lb, g > 0.f ? g * g * (1.0f - 0x1p-18f) : 0.f);
+            }
+        }
+        if (lb > best) break;                                     // strictly: an equal distance outside could carry a lower index
+    }
+    if (bj == 0x7fffffff) bj = 0;                                 // no finite distance at all (NaN / inf input)
+    const int orig = __ldg(D.q_perm + (size_t)n * D.Pq_pad + i);
+    D.keys[(size_t)n * D.Pq + orig] = ((unsigned long long)__float_as_uint(best) << 32) | (unsigned long long)(unsigned)bj;
+    }
+    if (prm.stats) {                                              // executed pair evaluations, one global atomic per block
+        unsigned ne = (unsigned)n_eval;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) ne += __shfl_xor_sync(0xffffffffu, ne, o);
+        if ((threadIdx.x & 31) == 0 && ne) atomicAdd(&s_eval, (unsigned long long)ne);
+        __syncthreads();
+        if (threadIdx.x == 0 && s_eval) atomicAdd(prm.stats, s_eval);
+    }
+}
+
 }  // namespace chamfer
 }  // namespace fb

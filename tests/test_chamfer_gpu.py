@@ -7,13 +7,13 @@ import torch
 pytestmark = pytest.mark.gpu
 
 
-@pytest.fixture(params=["cull_kq1", "cull_kq2", "cull_kq4", "brute", "cta_kq1", "cta_kq2", "cta_kq4", "cull_kq2_sort1"], autouse=True)
+@pytest.fixture(params=["cull_kq1", "cull_kq2", "cull_kq4", "brute", "cta_kq1", "cta_kq2", "cta_kq4", "cull_kq2_sort1", "grid"], autouse=True)
 def knn_mode(request):
     """Every test runs on the culled kernel (1, 2 and 4 queries per lane; one warp per group and the CTA-cooperative variant) and
     on the brute-force tile kernel."""
     from find_b200 import _lib
     mode, kq = {"cull_kq1": (0, 1), "cull_kq2": (0, 2), "cull_kq4": (0, 4), "brute": (1, 0),
-                "cta_kq1": (2, 1), "cta_kq2": (2, 2), "cta_kq4": (2, 4), "cull_kq2_sort1": (0, 2)}[request.param]
+                "cta_kq1": (2, 1), "cta_kq2": (2, 2), "cta_kq4": (2, 4), "cull_kq2_sort1": (0, 2), "grid": (3, 0)}[request.param]
     assert _lib.load().findb200_set_knn_mode(mode, kq) == 0
     # "sort1": clouds below 32768 points are sorted by one cluster per cloud in a single launch instead of six kernels
     _lib.load().findb200_set_sort_cta_max(32768 if request.param.endswith("sort1") else -1)

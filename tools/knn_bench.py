@@ -51,7 +51,7 @@ def run(B, V, P2, mode, kq, iters=int(os.environ.get('KB_ITERS', '20'))):
     prof = {l.split(",")[0]: float(l.split(",")[2]) for l in buf.value.decode().strip().splitlines() if l}
     alg = 2 * B * V * P2
     return {"B": B, "V": V, "P2": P2, "mode": mode, "kq": kq, "ms_median": ts[len(ts) // 2], "ms_min": ts[0],
-            "pairs_alg": alg, "pairs_exec": int(stats[0]) if mode == 0 else alg, "slow_queries": int(stats[1]), "max_evals": int(stats[2]), "groups": int(stats[3]),
+            "pairs_alg": alg, "pairs_exec": int(stats[0]) if mode != 1 else alg, "slow_queries": int(stats[1]), "max_evals": int(stats[2]), "groups": int(stats[3]),
             "kernels_ms": prof, "loss": loss.item(), "idx_sum": int(ix.sum().item() + iy.sum().item())}
 
 
