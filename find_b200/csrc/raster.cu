@@ -499,6 +499,280 @@ __global__ void __launch_bounds__(kThreads, 4) sil_tile_bwd_kernel(const __grid_
     for_each_listed<true>(P, n, sh.nlist, px, py, blur, active, sh, scatter);
 }
 
+// ---- FeatureShader: the reference's own softmax_blend over the silhouette fragments (renderer.py:23-105) -----------------
+// out_c = (sum_i w_i f_ic + delta bg_c) / (sum_i w_i + delta) over the K kept candidates i of a pixel,
+//   w_i = sigmoid(-sd_i / sigma) * exp((zinv_i - max zinv) / gamma),  zinv = (zfar - z) / (zfar - znear)  (softmax_blend's defaults
+//   znear = 1, zfar = 100: the reference passes none), delta = max(exp((eps - max zinv) / gamma), eps), f_ic = the per-vertex
+//   features interpolated with the CLIPPED perspective-correct barycentrics (TexturesVertex.sample_textures on those fragments).
+// Both kernels re-walk the tile's faces like the silhouette backward and keep the same K candidates through the saved (depth
+// threshold, ties) pair; the nearest kept depth (max zinv) is the forward's zbuf.
+struct FeatParams {
+    SilParams s;                          // box / rec / sizes / blur / sigma / perspective; s.sel = saved selection; s.faces
+    const float* zbuf;                    // [N, H, W] nearest kept depth, -1 = none
+    const int* p2f;                       // [N, H, W] its face (backward: the candidate that carries the max-zinv term)
+    const float* feat;                    // [M, V, C]
+    int C, views, c0;                     // channels [c0, c0 + 8) in this launch (forward)
+    float gamma, znear, zfar;
+    const float* bg;                      // [C] or null (zeros)
+    float* out;                           // [N, H, W, C]
+    float* den;                           // [N, H, W]  sum w + delta
+    const float* grad_out;                // backward
+    float* g_feat;                        // [M, V, C]  +=
+    float* g_ndc;                         // [N, V, 3]  +=
+};
+constexpr int kFeatCh = 8;
+
+__global__ void __launch_bounds__(kThreads, 4) feat_tile_fwd_kernel(const __grid_constant__ FeatParams Q) {
+    pdl_wait_trigger();
+    __shared__ TileShared sh;
+    const SilParams& P = Q.s;
+    const int n = blockIdx.z, tid = threadIdx.x;
+    const int col = blockIdx.x * kTile + ((tid >> 5) & 1) * 8 + (tid & 7), row = blockIdx.y * kTile + (tid >> 6) * 4 + ((tid >> 3) & 3);
+    const bool in_img = (col < P.W) && (row < P.H);
+    const float px = 1.f - __fdiv_rn((float)(2 * col + 1), (float)P.W), py = 1.f - __fdiv_rn((float)(2 * row + 1), (float)P.H);
+    const int c_hi = min(blockIdx.x * kTile + kTile - 1, P.W - 1), r_hi = min(blockIdx.y * kTile + kTile - 1, P.H - 1);
+    const float txmax = 1.f - __fdiv_rn((float)(2 * blockIdx.x * kTile + 1), (float)P.W), txmin = 1.f - __fdiv_rn((float)(2 * c_hi + 1), (float)P.W);
+    const float tymax = 1.f - __fdiv_rn((float)(2 * blockIdx.y * kTile + 1), (float)P.H), tymin = 1.f - __fdiv_rn((float)(2 * r_hi + 1), (float)P.H);
+    const float blur = sqrtf(P.blur_radius), inv_sigma = __fdiv_rn(1.f, P.sigma);
+    const float eps = 1e-10f, zr = Q.zfar - Q.znear;
+    const size_t o = in_img ? ((size_t)n * P.H + row) * P.W + col : 0;
+    uint2 sel = make_uint2(0xffffffffu, 0u);
+    float zmax = eps;
+    if (in_img) {
+        sel = P.sel[o];
+        const float zb = Q.zbuf[o];
+        if (zb >= 0.f) zmax = fmaxf((Q.zfar - zb) / zr, eps);
+    }
+    const float* feat = Q.feat + (size_t)(n / Q.views) * P.V * Q.C;
+    const int nch = min(kFeatCh, Q.C - Q.c0);
+    float acc[kFeatCh], wsum = 0.f;
+#pragma unroll
+    for (int c = 0; c < kFeatCh; ++c) acc[c] = 0.f;
+    int seen = 0;
+    auto blend = [&](int j, const FaceRec&, const Eval& e) {
+        if (!e.cand) return;
+        const uint32_t b = depth_bits(e.pz);
+        const bool keep = (sel.x == 0xffffffffu) || (b < sel.x) || (b == sel.x && seen++ < (int)sel.y);
+        if (!keep) return;
+        const float prob = sigmoidf_((e.inside ? e.d2 : -e.d2) * inv_sigma);
+        const float w = prob * expf(((Q.zfar - e.pz) / zr - zmax) / Q.gamma);
+        wsum += w;
+        const float u0 = e.w[0] / e.wsum, u1 = e.w[1] / e.wsum, u2 = e.w[2] / e.wsum;
+        const float* f0 = feat + (size_t)sh.vid[j][0] * Q.C + Q.c0;
+        const float* f1 = feat + (size_t)sh.vid[j][1] * Q.C + Q.c0;
+        const float* f2 = feat + (size_t)sh.vid[j][2] * Q.C + Q.c0;
+#pragma unroll
+        for (int c = 0; c < kFeatCh; ++c)
+            if (c < nch) acc[c] += w * (u0 * __ldg(f0 + c) + u1 * __ldg(f1 + c) + u2 * __ldg(f2 + c));
+    };
+    build_tile_list(P, n, txmin, txmax, tymin, tymax, sh, [&](int count) { for_each_listed<true>(P, n, count, px, py, blur, in_img, sh, blend); });
+    for_each_listed<true>(P, n, sh.nlist, px, py, blur, in_img, sh, blend);
+    if (in_img) {
+        const float delta = fmaxf(expf((eps - zmax) / Q.gamma), eps);
+        const float den = wsum + delta;
+        if (Q.c0 == 0) Q.den[o] = den;
+        for (int c = 0; c < nch; ++c) Q.out[o * Q.C + Q.c0 + c] = (acc[c] + delta * (Q.bg ? Q.bg[Q.c0 + c] : 0.f)) / den;
+    }
+}
+
+// d/d(NDC vertices of one face) from d/d(final barycentrics u), d/d(interpolated depth) and d/d(signed squared edge distance),
+// for the rasteriser's forward as eval_face computes it (clip + renormalise when `clip`, perspective correction when `persp`).
+FB_DEVINL void face_geometry_bwd(const FaceRec& r, float px, float py, int persp, int clip, const float (&g_u)[3], float g_z, float g_sd,
+                                 float (&gX)[3], float (&gY)[3], float (&gZ)[3]) {
+    const float X[3] = {r.x0, r.x1, r.x2}, Y[3] = {r.y0, r.y1, r.y2}, Z[3] = {r.z0, r.z1, r.z2};
+#pragma unroll
+    for (int k = 0; k < 3; ++k) { gX[k] = 0.f; gY[k] = 0.f; gZ[k] = 0.f; }
+    const float area = edge_fn(X[2], Y[2], X[0], Y[0], X[1], Y[1]);
+    const float dena = area + kEps;
+    const float e0 = edge_fn(px, py, X[1], Y[1], X[2], Y[2]), e1 = edge_fn(px, py, X[2], Y[2], X[0], Y[0]), e2 = edge_fn(px, py, X[0], Y[0], X[1], Y[1]);
+    const float ws[3] = {e0 / dena, e1 / dena, e2 / dena};
+    float b[3] = {ws[0], ws[1], ws[2]};
+    float t[3] = {0.f, 0.f, 0.f}, dn_raw = 1.f;
+    if (persp) {
+        t[0] = ws[0] * Z[1] * Z[2]; t[1] = Z[0] * ws[1] * Z[2]; t[2] = Z[0] * Z[1] * ws[2];
+        dn_raw = t[0] + t[1] + t[2];
+        const float dn = fmaxf(dn_raw, kEps);
+        b[0] = t[0] / dn; b[1] = t[1] / dn; b[2] = t[2] / dn;
+    }
+    // final barycentrics u and depth z
+    float g_b[3];
+    if (clip) {
+        float c[3];
+#pragma unroll
+        for (int k = 0; k < 3; ++k) c[k] = fminf(fmaxf(b[k], 0.f), 1.f);
+        const float cs_raw = c[0] + c[1] + c[2];
+        const float cs = fmaxf(cs_raw, 1e-5f);
+        const float z = (c[0] * Z[0] + c[1] * Z[1] + c[2] * Z[2]) / cs;
+        const float u[3] = {c[0] / cs, c[1] / cs, c[2] / cs};
+        float g_c[3];
+        if (cs_raw > 1e-5f) {
+            const float gu_dot = g_u[0] * u[0] + g_u[1] * u[1] + g_u[2] * u[2];
+#pragma unroll
+            for (int k = 0; k < 3; ++k) g_c[k] = (g_u[k] - gu_dot) / cs + g_z * (Z[k] - z) / cs;
+        } else {
+#pragma unroll
+            for (int k = 0; k < 3; ++k) g_c[k] = g_u[k] / cs + g_z * Z[k] / cs;
+        }
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+            gZ[k] += g_z * u[k];
+            g_b[k] = (b[k] > 0.f && b[k] < 1.f) ? g_c[k] : 0.f;
+        }
+    } else {
+#pragma unroll
+        for (int k = 0; k < 3; ++k) { g_b[k] = g_u[k] + g_z * Z[k]; gZ[k] += g_z * b[k]; }
+    }
+    float g_ws[3];
+    if (persp) {
+        if (dn_raw > kEps) {
+            const float dn = dn_raw;
+            const float bsum = g_b[0] * b[0] + g_b[1] * b[1] + g_b[2] * b[2];
+            const float g_t0 = (g_b[0] - bsum) / dn, g_t1 = (g_b[1] - bsum) / dn, g_t2 = (g_b[2] - bsum) / dn;
+            g_ws[0] = g_t0 * Z[1] * Z[2]; g_ws[1] = g_t1 * Z[0] * Z[2]; g_ws[2] = g_t2 * Z[0] * Z[1];
+            gZ[0] += g_t1 * ws[1] * Z[2] + g_t2 * Z[1] * ws[2];
+            gZ[1] += g_t0 * ws[0] * Z[2] + g_t2 * Z[0] * ws[2];
+            gZ[2] += g_t0 * ws[0] * Z[1] + g_t1 * Z[0] * ws[1];
+        } else {
+            const float dn = kEps;
+            g_ws[0] = g_b[0] / dn * Z[1] * Z[2]; g_ws[1] = g_b[1] / dn * Z[0] * Z[2]; g_ws[2] = g_b[2] / dn * Z[0] * Z[1];
+            gZ[0] += g_b[1] / dn * ws[1] * Z[2] + g_b[2] / dn * Z[1] * ws[2];
+            gZ[1] += g_b[0] / dn * ws[0] * Z[2] + g_b[2] / dn * Z[0] * ws[2];
+            gZ[2] += g_b[0] / dn * ws[0] * Z[1] + g_b[1] / dn * Z[0] * ws[1];
+        }
+    } else {
+#pragma unroll
+        for (int k = 0; k < 3; ++k) g_ws[k] = g_b[k];
+    }
+    const float g_e[3] = {g_ws[0] / dena, g_ws[1] / dena, g_ws[2] / dena};
+    const float g_area = -(g_ws[0] * ws[0] + g_ws[1] * ws[1] + g_ws[2] * ws[2]) / dena;
+    auto edge_bwd = [&](float ge, int a, int bb) {
+        gX[a] += ge * (py - Y[bb]); gY[a] += ge * (X[bb] - px);
+        gX[bb] += ge * -(py - Y[a]); gY[bb] += ge * (px - X[a]);
+    };
+    edge_bwd(g_e[0], 1, 2);
+    edge_bwd(g_e[1], 2, 0);
+    edge_bwd(g_e[2], 0, 1);
+    gX[0] += g_area * (Y[2] - Y[1]); gY[0] += g_area * (X[1] - X[2]);
+    gX[1] += g_area * -(Y[2] - Y[0]); gY[1] += g_area * (X[2] - X[0]);
+    gX[2] += g_area * (Y[1] - Y[0]); gY[2] += g_area * -(X[1] - X[0]);
+    if (g_sd != 0.f) {
+        float tt[3];
+        const float d01 = seg_dist2(px, py, X[0], Y[0], X[1], Y[1], tt[0]);
+        const float d02 = seg_dist2(px, py, X[0], Y[0], X[2], Y[2], tt[1]);
+        const float d12 = seg_dist2(px, py, X[1], Y[1], X[2], Y[2], tt[2]);
+        int ed = 0;
+        float dmin = d01;
+        if (d02 < dmin) { dmin = d02; ed = 1; }
+        if (d12 < dmin) { dmin = d12; ed = 2; }
+        const int ia = ed == 2 ? 1 : 0, ib = ed == 0 ? 1 : 2;
+        const bool inside = (ws[0] > 0.f) && (ws[1] > 0.f) && (ws[2] > 0.f);
+        const float gs = inside ? -g_sd : g_sd;
+        const float tp = tt[ed];
+        if (tp == 2.f) {
+            gX[ib] += gs * -2.f * (px - X[ib]); gY[ib] += gs * -2.f * (py - Y[ib]);
+        } else {
+            const float qx = X[ia] + tp * (X[ib] - X[ia]), qy = Y[ia] + tp * (Y[ib] - Y[ia]);
+            const float cx = px - qx, cy = py - qy;
+            gX[ia] += gs * -2.f * (1.f - tp) * cx; gY[ia] += gs * -2.f * (1.f - tp) * cy;
+            gX[ib] += gs * -2.f * tp * cx; gY[ib] += gs * -2.f * tp * cy;
+        }
+    }
+}
+
+__global__ void __launch_bounds__(kThreads, 2) feat_tile_bwd_kernel(const __grid_constant__ FeatParams Q) {
+    pdl_wait_trigger();
+    __shared__ TileShared sh;
+    const SilParams& P = Q.s;
+    const int n = blockIdx.z, tid = threadIdx.x;
+    const int col = blockIdx.x * kTile + ((tid >> 5) & 1) * 8 + (tid & 7), row = blockIdx.y * kTile + (tid >> 6) * 4 + ((tid >> 3) & 3);
+    const bool in_img = (col < P.W) && (row < P.H);
+    const float px = 1.f - __fdiv_rn((float)(2 * col + 1), (float)P.W), py = 1.f - __fdiv_rn((float)(2 * row + 1), (float)P.H);
+    const int c_hi = min(blockIdx.x * kTile + kTile - 1, P.W - 1), r_hi = min(blockIdx.y * kTile + kTile - 1, P.H - 1);
+    const float txmax = 1.f - __fdiv_rn((float)(2 * blockIdx.x * kTile + 1), (float)P.W), txmin = 1.f - __fdiv_rn((float)(2 * c_hi + 1), (float)P.W);
+    const float tymax = 1.f - __fdiv_rn((float)(2 * blockIdx.y * kTile + 1), (float)P.H), tymin = 1.f - __fdiv_rn((float)(2 * r_hi + 1), (float)P.H);
+    const float blur = sqrtf(P.blur_radius), inv_sigma = __fdiv_rn(1.f, P.sigma);
+    const float eps = 1e-10f, zr = Q.zfar - Q.znear;
+    const size_t o = in_img ? ((size_t)n * P.H + row) * P.W + col : 0;
+    uint2 sel = make_uint2(0xffffffffu, 0u);
+    float zmax = eps, den = 1.f, g_zmax = 0.f;
+    int near = -1;
+    bool active = false;
+    if (in_img) {
+        sel = P.sel[o];
+        const float zb = Q.zbuf[o];
+        near = Q.p2f[o];
+        den = Q.den[o];
+        const bool hit = zb >= 0.f;
+        if (hit) zmax = fmaxf((Q.zfar - zb) / zr, eps);
+        // gradient carried by max zinv: -(1/gamma) sum_i gw_i w_i plus delta's own term.  sum_i gw_i w_i collapses to
+        // delta * sum_c g_c (out_c - bg_c) / den, and d(delta)/d(zmax) = -delta / gamma when delta is not clamped:
+        //   G = -(delta / gamma) * sum_c g_c (out_c - bg_c) / den + [delta > eps] * (-(delta / gamma)) * sum_c g_c (bg_c - out_c) / den
+        // so with an unclamped delta the two cancel exactly, and with the clamp only the first stays.
+        float dot = 0.f, gsum = 0.f;
+        for (int c = 0; c < Q.C; ++c) {
+            const float g = Q.grad_out[o * Q.C + c];
+            gsum += fabsf(g);
+            dot += g * (Q.out[o * Q.C + c] - (Q.bg ? Q.bg[c] : 0.f));
+        }
+        active = hit && gsum != 0.f;
+        const float dl_raw = expf((eps - zmax) / Q.gamma);
+        const float delta = fmaxf(dl_raw, eps);
+        if (hit && (Q.zfar - zb) / zr > eps) g_zmax = (dl_raw > eps) ? 0.f : -(delta / Q.gamma) * dot / den;
+    }
+    if (!__syncthreads_or(active)) return;
+    const float* feat = Q.feat + (size_t)(n / Q.views) * P.V * Q.C;
+    float* g_feat = Q.g_feat + (size_t)(n / Q.views) * P.V * Q.C;
+    float* g_ndc = Q.g_ndc + (size_t)n * P.V * 3;
+    const float* gout = Q.grad_out + o * Q.C;
+    const float* outp = Q.out + o * Q.C;
+    int seen = 0;
+    auto scatter = [&](int j, const FaceRec& r, const Eval& e) {
+        if (!e.cand) return;
+        const uint32_t b = depth_bits(e.pz);
+        const bool keep = (sel.x == 0xffffffffu) || (b < sel.x) || (b == sel.x && seen++ < (int)sel.y);
+        if (!keep || !active) return;
+        const float prob = sigmoidf_((e.inside ? e.d2 : -e.d2) * inv_sigma);
+        const float E = expf(((Q.zfar - e.pz) / zr - zmax) / Q.gamma);
+        const float w = prob * E;
+        const float u[3] = {e.w[0] / e.wsum, e.w[1] / e.wsum, e.w[2] / e.wsum};
+        const int v0 = sh.vid[j][0], v1 = sh.vid[j][1], v2 = sh.vid[j][2];
+        const float *f0 = feat + (size_t)v0 * Q.C, *f1 = feat + (size_t)v1 * Q.C, *f2 = feat + (size_t)v2 * Q.C;
+        float gw = 0.f, g_u[3] = {0.f, 0.f, 0.f};
+        const float wd = w / den;
+        for (int c = 0; c < Q.C; ++c) {
+            const float a0 = __ldg(f0 + c), a1 = __ldg(f1 + c), a2 = __ldg(f2 + c);
+            const float g = gout[c];
+            gw += g * ((u[0] * a0 + u[1] * a1 + u[2] * a2) - outp[c]);
+            const float gf = g * wd;                                 // d/d(interpolated feature c)
+            g_u[0] += gf * a0; g_u[1] += gf * a1; g_u[2] += gf * a2;
+            if (gf != 0.f) {
+                atomicAdd(g_feat + (size_t)v0 * Q.C + c, u[0] * gf);
+                atomicAdd(g_feat + (size_t)v1 * Q.C + c, u[1] * gf);
+                atomicAdd(g_feat + (size_t)v2 * Q.C + c, u[2] * gf);
+            }
+        }
+        gw /= den;
+        // w = prob * E:  d/d(prob) = gw E;  d/d(zinv) = gw w / gamma (+ the max-zinv term on the nearest face)
+        const float g_prob = gw * E;
+        float g_zinv = gw * w / Q.gamma;
+        if (__float_as_int(r.pad0) == near && depth_bits(e.pz) == depth_bits(Q.zbuf[o])) g_zinv += g_zmax - 0.f;
+        // every kept candidate's exponent also holds -zmax: that part is inside g_zmax (collapsed sum), see above
+        const float g_z = -g_zinv / zr;
+        const float g_sd = g_prob * (-prob * (1.f - prob) * inv_sigma);      // prob = sigmoid(-sd / sigma)
+        float gX[3], gY[3], gZ[3];
+        face_geometry_bwd(r, px, py, P.perspective, 1, g_u, g_z, g_sd, gX, gY, gZ);
+        const int vv[3] = {v0, v1, v2};
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+            if (gX[k] != 0.f) atomicAdd(g_ndc + (size_t)vv[k] * 3, gX[k]);
+            if (gY[k] != 0.f) atomicAdd(g_ndc + (size_t)vv[k] * 3 + 1, gY[k]);
+            if (gZ[k] != 0.f) atomicAdd(g_ndc + (size_t)vv[k] * 3 + 2, gZ[k]);
+        }
+    };
+    build_tile_list(P, n, txmin, txmax, tymin, tymax, sh, [&](int count) { for_each_listed<true>(P, n, count, px, py, blur, in_img, sh, scatter); });
+    for_each_listed<true>(P, n, sh.nlist, px, py, blur, in_img, sh, scatter);
+}
+
 }  // namespace raster
 }  // namespace fb
 
@@ -625,6 +899,66 @@ extern "C" int findb200_silhouette_backward(const float* grad_alpha, const int32
     FB_CUDA((cudaError_t)prefer_shared());
     FB_MARK("sil_tile_bwd", st);
     FB_CUDA(launch_pdl(sil_tile_bwd_kernel, dim3((W + kTile - 1) / kTile, (H + kTile - 1) / kTile, N), dim3(kThreads), 0, st, P));
+    FB_MARK_END(st);
+    return 0;
+}
+
+// FeatureShader on the fragments of a findb200_silhouette_forward call (same workspace, its sel / zbuf / pix_to_face outputs).
+// features [M, V, C] with M = N / num_views meshes; background [C] on the device or NULL (zeros); out [N, H, W, C], den [N, H, W].
+static int fill_feat(FeatParams& Q, const float* features, int C, int num_views, const int32_t* faces, int N, int V, int F, int H, int W,
+                     float blur_radius, float sigma, int K, int perspective, float gamma, float znear, float zfar, const float* background,
+                     const void* sel, const float* zbuf, void* ws, size_t ws_bytes) {
+    int rc = fill(Q.s, ws, ws_bytes, N, V, F, H, W, blur_radius, sigma, K, perspective, false);
+    if (rc) return rc;
+    FB_REQUIRE(features && faces && sel && zbuf && C >= 1 && num_views >= 1 && N % num_views == 0, FINDB200_ERR_ARG, "feature_blend: bad argument");
+    FB_REQUIRE(gamma > 0.f && zfar > znear, FINDB200_ERR_ARG, "feature_blend: gamma > 0 and zfar > znear required");
+    Q.s.sel = (uint2*)sel; Q.s.faces = faces;
+    Q.zbuf = zbuf; Q.p2f = nullptr; Q.feat = features; Q.C = C; Q.views = num_views; Q.c0 = 0; Q.gamma = gamma; Q.znear = znear; Q.zfar = zfar;
+    Q.bg = background; Q.out = nullptr; Q.den = nullptr; Q.grad_out = nullptr; Q.g_feat = nullptr; Q.g_ndc = nullptr;
+    return 0;
+}
+
+extern "C" int findb200_feature_blend_forward(const float* features, int C, int num_views, const int32_t* faces, int N, int V, int F, int H,
+                                              int W, float blur_radius, float sigma, int faces_per_pixel, int perspective_correct,
+                                              float gamma, float znear, float zfar, const float* background, const void* sel,
+                                              const float* zbuf, float* out, float* den, void* ws, size_t ws_bytes, void* stream) {
+    cudaStream_t st = (cudaStream_t)stream;
+    if (N == 0) return 0;
+    FeatParams Q;
+    int rc = fill_feat(Q, features, C, num_views, faces, N, V, F, H, W, blur_radius, sigma, faces_per_pixel, perspective_correct, gamma, znear,
+                       zfar, background, sel, zbuf, ws, ws_bytes);
+    if (rc) return rc;
+    FB_REQUIRE(out && den, FINDB200_ERR_ARG, "feature_blend_forward: null output");
+    Q.out = out; Q.den = den;
+    FB_CUDA((cudaError_t)prefer_shared());
+    FB_MARK("feat_tile_fwd", st);
+    for (int c0 = 0; c0 < C; c0 += kFeatCh) {            // eight channels per walk (per-pixel accumulators live in registers)
+        Q.c0 = c0;
+        FB_CUDA(launch_pdl(feat_tile_fwd_kernel, dim3((W + kTile - 1) / kTile, (H + kTile - 1) / kTile, N), dim3(kThreads), 0, st, Q));
+    }
+    FB_MARK_END(st);
+    return 0;
+}
+
+// grad_features [M, V, C] and grad_verts_ndc [N, V, 3] are ACCUMULATED into (the caller zeroes them)
+extern "C" int findb200_feature_blend_backward(const float* grad_out, const float* features, int C, int num_views, const int32_t* faces,
+                                               int N, int V, int F, int H, int W, float blur_radius, float sigma, int faces_per_pixel,
+                                               int perspective_correct, float gamma, float znear, float zfar, const float* background,
+                                               const void* sel, const float* zbuf, const int32_t* pix_to_face, const float* out,
+                                               const float* den, float* grad_features, float* grad_verts_ndc, void* ws, size_t ws_bytes,
+                                               void* stream) {
+    cudaStream_t st = (cudaStream_t)stream;
+    if (N == 0 || F == 0) return 0;
+    FeatParams Q;
+    int rc = fill_feat(Q, features, C, num_views, faces, N, V, F, H, W, blur_radius, sigma, faces_per_pixel, perspective_correct, gamma, znear,
+                       zfar, background, sel, zbuf, ws, ws_bytes);
+    if (rc) return rc;
+    FB_REQUIRE(grad_out && pix_to_face && out && den && grad_features && grad_verts_ndc, FINDB200_ERR_ARG, "feature_blend_backward: null argument");
+    Q.p2f = pix_to_face; Q.out = (float*)out; Q.den = (float*)den; Q.grad_out = grad_out; Q.g_feat = grad_features; Q.g_ndc = grad_verts_ndc;
+    static bool carve = false;
+    if (!carve) { cudaFuncSetAttribute(feat_tile_bwd_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared); carve = true; }
+    FB_MARK("feat_tile_bwd", st);
+    FB_CUDA(launch_pdl(feat_tile_bwd_kernel, dim3((W + kTile - 1) / kTile, (H + kTile - 1) / kTile, N), dim3(kThreads), 0, st, Q));
     FB_MARK_END(st);
     return 0;
 }

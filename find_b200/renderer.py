@@ -159,6 +159,74 @@ def vertex_normals(verts: torch.Tensor, topo) -> torch.Tensor:
     return out
 
 
+class _FeatureRender(torch.autograd.Function):
+    """``FeatureShader`` of the reference (renderer.py:74-105: TexturesVertex sampling + its own ``softmax_blend``, :23-72) over the
+    silhouette fragments, forward and backward (csrc/raster.cu: findb200_silhouette_forward for the fragments, then
+    findb200_feature_blend_forward / _backward).  Differentiable w.r.t. the per-vertex features and the NDC vertices."""
+
+    @staticmethod
+    def forward(ctx, verts_ndc, features, faces_i32, H, W, blur_radius, sigma, K, perspective, num_views, gamma, znear, zfar):
+        lib = _lib.load()
+        dev = _lib.require_cuda(verts_ndc)
+        v = verts_ndc.detach().contiguous().float()
+        f = features.detach().contiguous().float()
+        N, V, F, C = v.shape[0], v.shape[1], faces_i32.shape[0], f.shape[-1]
+        alpha = torch.empty(N, H, W, dtype=torch.float32, device=dev)
+        prod = torch.empty_like(alpha)
+        sel = torch.empty(N, H, W, 2, dtype=torch.int32, device=dev)
+        p2f = torch.empty(N, H, W, dtype=torch.int32, device=dev)
+        zbuf = torch.empty(N, H, W, dtype=torch.float32, device=dev)
+        out = torch.empty(N, H, W, C, dtype=torch.float32, device=dev)
+        den = torch.empty(N, H, W, dtype=torch.float32, device=dev)
+        ws = torch.empty(int(lib.findb200_silhouette_workspace_bytes(N, F)), dtype=torch.uint8, device=dev)
+        with torch.cuda.device(dev):
+            st = _lib.stream_ptr(dev)
+            rc = lib.findb200_silhouette_forward(_lib.ptr(v), _lib.ptr(faces_i32), N, V, F, H, W, float(blur_radius), float(sigma), int(K),
+                                                 int(bool(perspective)), _lib.ptr(alpha), _lib.ptr(prod), _lib.ptr(sel), _lib.ptr(p2f),
+                                                 _lib.ptr(zbuf), _lib.ptr(ws), ws.numel(), st)
+            _lib.check(rc, "findb200_silhouette_forward")
+            rc = lib.findb200_feature_blend_forward(_lib.ptr(f), C, int(num_views), _lib.ptr(faces_i32), N, V, F, H, W, float(blur_radius),
+                                                    float(sigma), int(K), int(bool(perspective)), float(gamma), float(znear), float(zfar),
+                                                    None, _lib.ptr(sel), _lib.ptr(zbuf), _lib.ptr(out), _lib.ptr(den), _lib.ptr(ws),
+                                                    ws.numel(), st)
+            _lib.check(rc, "findb200_feature_blend_forward")
+        ws = ws[: int(lib.findb200_silhouette_saved_bytes(N, F))].clone()
+        ctx.save_for_backward(f, faces_i32, sel, zbuf, p2f, out, den, ws)
+        ctx.cfg = (N, V, F, C, H, W, float(blur_radius), float(sigma), int(K), int(bool(perspective)), int(num_views), float(gamma),
+                   float(znear), float(zfar))
+        ctx.mark_non_differentiable(p2f)
+        return out, p2f
+
+    @staticmethod
+    def backward(ctx, g_out, _g_p2f):
+        lib = _lib.load()
+        f, faces_i32, sel, zbuf, p2f, out, den, ws = ctx.saved_tensors
+        N, V, F, C, H, W, blur_radius, sigma, K, perspective, num_views, gamma, znear, zfar = ctx.cfg
+        dev = g_out.device
+        g = g_out.contiguous().float()
+        g_feat = torch.zeros_like(f)
+        g_ndc = torch.zeros(N, V, 3, dtype=torch.float32, device=dev)
+        with torch.cuda.device(dev):
+            rc = lib.findb200_feature_blend_backward(_lib.ptr(g), _lib.ptr(f), C, num_views, _lib.ptr(faces_i32), N, V, F, H, W, blur_radius,
+                                                     sigma, K, perspective, gamma, znear, zfar, None, _lib.ptr(sel), _lib.ptr(zbuf),
+                                                     _lib.ptr(p2f), _lib.ptr(out), _lib.ptr(den), _lib.ptr(g_feat), _lib.ptr(g_ndc),
+                                                     _lib.ptr(ws), ws.numel(), _lib.stream_ptr(dev))
+        _lib.check(rc, "findb200_feature_blend_backward")
+        return g_ndc, g_feat, None, None, None, None, None, None, None, None, None, None, None
+
+
+def render_features(verts_ndc: torch.Tensor, faces: torch.Tensor, features: torch.Tensor, image_size, num_views: int = 1,
+                    blur_radius: float = None, sigma: float = SIGMA, gamma: float = 1e-4, faces_per_pixel: int = 100,
+                    perspective_correct: bool = True, znear: float = 1.0, zfar: float = 100.0):
+    """verts_ndc [N,V,3], features [N // num_views, V, C] -> feature image [N,H,W,C] (+ pix_to_face [N,H,W]); background 0."""
+    H, W = (image_size, image_size) if isinstance(image_size, int) else image_size
+    if blur_radius is None:
+        blur_radius = math.log(1.0 / 1e-4 - 1.0) * sigma
+    f = (faces if faces.dtype == torch.int32 else faces.to(torch.int32)).contiguous()
+    return _FeatureRender.apply(verts_ndc, features, f, int(H), int(W), blur_radius, sigma, faces_per_pixel, perspective_correct, int(num_views),
+                                gamma, znear, zfar)
+
+
 class _PhongImage(torch.autograd.Function):
     """SoftPhongShader image of the hard fragments with its backward (csrc/raster.cu: findb200_rasterize_nearest,
     findb200_vertex_normals, findb200_phong_shade / _backward, findb200_vertex_normals_backward).  The camera projection's
@@ -285,19 +353,24 @@ class FootRenderer(nn.Module):
     def forward(self, input_meshes: Meshes, R, T, return_images=True, return_depth=False, return_mask=False, mask_with_grad=True,
                 mask_out_faces=False, masked_faces=None, keypoints=None, keypoints_blend=False, lights=None,
                 return_mask_out_masks=False, return_features=False, features=None) -> dict:
-        if return_features or return_depth or keypoints is not None:
-            raise NotImplementedError("find_b200.renderer: feature / depth / keypoint rendering is the rest of SURVEY.md §8(f) row 4")
+        if return_depth:
+            raise NotImplementedError("find_b200.renderer: return_depth cannot run in the reference either (renderer.py:296-301 reads "
+                                      "`fragments.zbuf` of a dict); the nearest depth is rasterize_nearest(...)[1] / rasterize_silhouette(..., return_fragments=True)[2]")
+        if keypoints is not None:
+            raise NotImplementedError("find_b200.renderer: the keypoint point-cloud overlay (a debug visualisation, renderer.py:367-377) is not built")
+        if return_features and features is None:
+            raise AssertionError("Requires features to be passed for rendering")        # renderer.py:278
         if mask_out_faces and masked_faces is None:
             raise NotImplementedError("find_b200.renderer: mask_out_faces needs masked_faces (the TexturesUV u = v = 0 convention of "
                                       "renderer.py:337-345 is not built)")
         """Same defaults as the reference (renderer.py:247-253: ``return_images=True, return_mask=False``), so the call sites that
         rely on them keep their meaning: ``renderer(mesh, R, T)['image']`` (mesh_turntable.py:57, model.py:1074,1089),
         ``return_mask=False`` (eval_2d.py:89-90)."""
-        if not return_mask and not return_images:
+        if not return_mask and not return_images and not return_features:
             return {}
         if return_images:
             images, img_p2f = self._render_images(input_meshes, R, T)
-            if not return_mask or not mask_with_grad:
+            if (not return_mask or not mask_with_grad) and not return_features:
                 out = {}
                 if return_mask:
                     # renderer.py:311-312: hard mask from the image render — any channel below the white background
@@ -319,28 +392,51 @@ class FootRenderer(nn.Module):
         num_views, num_meshes = R.shape[0], len(input_meshes)
         S = self.image_size
         ndc = self.project(verts, R, T)
-        alpha, p2f, _ = rasterize_silhouette(ndc, faces, S, self.blur_radius, self.sigma, self.faces_per_pixel, True, return_fragments=True)
-        mask = alpha.reshape(num_meshes, num_views, S, S)
         out = {}
+        mask, p2f = None, None
+        if return_mask:
+            if mask_with_grad or not return_images:
+                alpha, p2f, _ = rasterize_silhouette(ndc, faces, S, self.blur_radius, self.sigma, self.faces_per_pixel, True, return_fragments=True)
+                mask = alpha.reshape(num_meshes, num_views, S, S)
+            else:                                                  # renderer.py:311-312: hard mask from the image render
+                mask = torch.any(images < 1, dim=-1).reshape(num_meshes, num_views, S, S).float()
+        feat_renders = None
+        if return_features:
+            # renderer.py:277-284: TexturesVertex(features) on the SILHOUETTE fragments, background 0, default BlendParams
+            feats = features if features.dim() == 3 else features.unsqueeze(0).expand(num_meshes, -1, -1)
+            fr, fp2f = render_features(ndc, faces, feats.to(ndc.device), S, num_views=num_views, blur_radius=self.blur_radius, sigma=self.sigma,
+                                       gamma=1e-4, faces_per_pixel=self.faces_per_pixel)
+            feat_renders = fr.reshape(num_meshes, num_views, S, S, -1)
+            if p2f is None:
+                p2f = fp2f
         if return_images:
             out["image"] = images
         if mask_out_faces:
             # renderer.py:318-365: the closest face of every pixel; pixels whose closest face is in masked_faces are zeroed
             p2f = (img_p2f if return_images else p2f).reshape(num_meshes, num_views, S, S)   # the image fragments when rendered
             masks = []
-            mask = mask.clone()
+            if mask is not None:
+                mask = mask.clone()
+            if feat_renders is not None:
+                feat_renders = feat_renders.clone()
             for n in range(num_meshes):
                 mf = masked_faces[n] if isinstance(masked_faces, list) else masked_faces
                 mpix = torch.isin(p2f[n], mf.to(p2f.device, p2f.dtype))
                 masks.append(mpix)
-                mask[n, mpix] = 0.0
+                if mask is not None:
+                    mask[n, mpix] = 0.0
+                if feat_renders is not None:
+                    feat_renders[n, mpix] = 0.0
                 if return_images:
                     if out["image"].requires_grad and n == 0:
                         out["image"] = out["image"].clone()
                     out["image"][n, mpix] = 1.0
             if return_mask_out_masks:
                 out["mask_out_masks"] = torch.stack(masks).reshape(num_meshes, num_views, S, S)
-        out["mask"] = mask
+        if mask is not None:
+            out["mask"] = mask
+        if feat_renders is not None:
+            out["features"] = feat_renders
         return out
 
 

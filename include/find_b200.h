@@ -254,6 +254,21 @@ int findb200_vertex_normals_backward(const float* verts, int N, int V, const int
                                      const int32_t* vf_face, const int32_t* vf_corner, const float* grad_normals, float* scratch,
                                      float* grad_verts, void* stream);
 
+/* FeatureShader (renderer.py:74-105) = the reference's own softmax_blend (renderer.py:23-72, default znear = 1, zfar = 100) over the
+ * fragments of a findb200_silhouette_forward call: per-vertex features [M, V, C] (M = N / num_views) interpolated with the clipped
+ * barycentrics of each kept face and blended with weights sigmoid(-dist / sigma) * exp((zinv - max zinv) / gamma).  `ws`, `sel`,
+ * `zbuf`, `pix_to_face` are that call's workspace and outputs.  Forward: out [N, H, W, C], den [N, H, W] (kept for the backward).
+ * Backward: d/d(features) and d/d(NDC vertices), ACCUMULATED into pre-zeroed buffers.  background: [C] on the device or NULL. */
+int findb200_feature_blend_forward(const float* features, int C, int num_views, const int32_t* faces, int N, int V, int F, int H, int W,
+                                   float blur_radius, float sigma, int faces_per_pixel, int perspective_correct, float gamma,
+                                   float znear, float zfar, const float* background, const void* sel, const float* zbuf, float* out,
+                                   float* den, void* workspace, size_t workspace_bytes, void* stream);
+int findb200_feature_blend_backward(const float* grad_out, const float* features, int C, int num_views, const int32_t* faces, int N,
+                                    int V, int F, int H, int W, float blur_radius, float sigma, int faces_per_pixel,
+                                    int perspective_correct, float gamma, float znear, float zfar, const float* background,
+                                    const void* sel, const float* zbuf, const int32_t* pix_to_face, const float* out, const float* den,
+                                    float* grad_features, float* grad_verts_ndc, void* workspace, size_t workspace_bytes, void* stream);
+
 /* ------------------------------------------------------------------------------------------------------
  * Optimiser updates: torch.optim.Adam(main_params / latent_params) and
  * torch.optim.SGD(reg_params, momentum=0.9) as stepped at src/train/train.py:161-168, src/train/trainer.py:122-123.

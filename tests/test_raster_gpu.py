@@ -296,3 +296,40 @@ def test_phong_image_backward_matches_oracle_autograd():
     both = r(Meshes(vg2, tf.to(dev), textures=colours.to(dev)), R, T, return_images=True, return_mask=True)
     ((both["image"] * wimg.to(dev)).sum() + both["mask"].sum()).backward()
     assert torch.isfinite(vg2.grad).all() and float((vg2.grad - vg.grad).abs().max()) > 0
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("K", [100, 3])
+def test_feature_render_matches_oracle_forward_and_backward(K):
+    """FootRenderer(return_features=True) = FeatureShader over the silhouette fragments (renderer.py:74-105, 277-284): forward and
+    the gradients w.r.t. the per-vertex features and the NDC vertices against oracle/raster_oracle.py::feature_blend under autograd
+    (K = 3 exercises the faces-per-pixel truncation).  Tolerances: 2e-4 absolute forward, rel-L2 2e-3 on the gradients."""
+    from find_b200.renderer import render_features
+    dev, verts, tf, r, R, T = _scene(162, ["topdown", "side1"], seed=21)
+    H = W = 40
+    C = 5
+    g = torch.Generator().manual_seed(22)
+    feats = torch.randn(1, verts.shape[1], C, generator=g)
+    wimg = torch.rand(2, H, W, C, generator=g)
+    ndc = r.project(verts, R, T)                                          # [2, V, 3]
+    a = ndc.clone().requires_grad_(True)
+    fo = feats.clone().requires_grad_(True)
+    want = torch.stack([ro.feature_blend(a[i], tf, fo[0], H, W, faces_per_pixel=K) for i in range(2)])
+    (want * wimg).sum().backward()
+    b = ndc.to(dev).requires_grad_(True)
+    fg = feats.to(dev).requires_grad_(True)
+    got, p2f = render_features(b, tf.to(dev), fg, (H, W), num_views=2, faces_per_pixel=K)
+    assert got.shape == (2, H, W, C)
+    assert float((got.detach().cpu() - want.detach()).abs().max()) < 2e-4
+    (got * wimg.to(dev)).sum().backward()
+    assert float(fo.grad.abs().max()) > 0 and float(a.grad.abs().max()) > 0
+    assert rel_l2(fg.grad.cpu(), fo.grad) < 2e-3, rel_l2(fg.grad.cpu(), fo.grad)
+    assert rel_l2(b.grad.cpu(), a.grad) < 2e-3, rel_l2(b.grad.cpu(), a.grad)
+    # through FootRenderer: world vertices, masked faces zero the feature image, shapes as the reference's
+    vg = verts.to(dev).requires_grad_(True)
+    out = r(Meshes(vg, tf.to(dev)), R, T, return_images=False, return_mask=True, return_features=True, features=fg.detach()[0],
+            mask_out_faces=True, masked_faces=torch.arange(0, tf.shape[0], 2, device=dev), return_mask_out_masks=True)
+    assert out["features"].shape == (1, 2, 64, 64, C) and out["mask"].shape == (1, 2, 64, 64)
+    assert float(out["features"][out["mask_out_masks"]].abs().max()) == 0.0
+    out["features"].sum().backward()
+    assert torch.isfinite(vg.grad).all() and float(vg.grad.abs().max()) > 0
