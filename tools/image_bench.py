@@ -54,3 +54,31 @@ for name, fn in (("forward_ms", fwd), ("forward_backward_ms", fwd_bwd)):
     out[name] = sorted(ts)[len(ts) // 2]
 out["images"] = f"{B * nv} x {S} x {S}, {tv.shape[0]} vertices / {tf.shape[0]} faces"
 print(json.dumps(out, indent=1))
+
+# ---- feature rendering (FeatureShader over the 100-face silhouette fragments), C = 21 as the reference's per-vertex clusters
+from find_b200.renderer import render_features
+C = 21
+feats = torch.randn(B, tv.shape[0], C, generator=g).to(dev)
+ndc = r.project(verts, R, T)
+def f_fwd():
+    with torch.no_grad():
+        return render_features(ndc, tf.to(dev), feats, S, num_views=nv)[0]
+def f_fwd_bwd():
+    a = ndc.clone().requires_grad_(True)
+    f = feats.clone().requires_grad_(True)
+    o = render_features(a, tf.to(dev), f, S, num_views=nv)[0]
+    o.square().mean().backward()
+    return a.grad
+res = {}
+for name, fn in (("features_forward_ms", f_fwd), ("features_forward_backward_ms", f_fwd_bwd)):
+    for _ in range(2):
+        fn()
+    torch.cuda.synchronize()
+    ts = []
+    for _ in range(5):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(); fn(); e1.record(); torch.cuda.synchronize()
+        ts.append(e0.elapsed_time(e1))
+    res[name] = sorted(ts)[len(ts) // 2]
+res["channels"] = C
+print(json.dumps(res, indent=1))
