@@ -560,6 +560,26 @@ void field_bwd_zero_region(int nfeet, int V, int pos_shared, size_t* offset, siz
     *bytes = (w.colsum - w.scal) + cs_total(nfeet) * 8;
 }
 
+// The side stream of findb200_field_backward's early dW launch (one per device, created on first use; inside a stream capture
+// the side stream joins the capture through the fork event and leaves it through the join event).
+static int side_stream(cudaStream_t* s, cudaEvent_t* fork, cudaEvent_t* join) {
+    constexpr int kMaxDev = 32;
+    static cudaStream_t streams[kMaxDev];
+    static cudaEvent_t forks[kMaxDev], joins[kMaxDev];
+    static bool made[kMaxDev];
+    int dev = 0;
+    FB_CUDA(cudaGetDevice(&dev));
+    FB_REQUIRE(dev >= 0 && dev < kMaxDev, FINDB200_ERR_UNSUPPORTED, "field_backward: device ordinal out of range");
+    if (!made[dev]) {
+        FB_CUDA(cudaStreamCreateWithFlags(&streams[dev], cudaStreamNonBlocking));
+        FB_CUDA(cudaEventCreateWithFlags(&forks[dev], cudaEventDisableTiming));
+        FB_CUDA(cudaEventCreateWithFlags(&joins[dev], cudaEventDisableTiming));
+        made[dev] = true;
+    }
+    *s = streams[dev]; *fork = forks[dev]; *join = joins[dev];
+    return 0;
+}
+
 static int run_pack(const findb200_field_params* p, const Workspace& w, uint8_t* ws, const LatentBiasParams& LB, cudaStream_t st) {
     const PackLayout L = make_layout();
     PackParams PP;
@@ -714,21 +734,6 @@ int findb200_field_backward(const findb200_field_params* p, const float* pos, in
         cost[ng] = (long long)feet * w.tpf * (mh * 4 * (N >= 256 ? 4 : 1) + 4);
         ++ng;
     };
-    if (!frozen) {
-        rc = 0;
-        if (pos_shared && B > 1) {
-            FB_MARK("sum_feet", st);
-            FB_CUDA(fb::launch_pdl(sum_feet_kernel, dim3(w.tpf2 * (kTileBytes / 16) / 256, n_heads), 256, 0, st, ws + w.hdz, ws + w.hsum, B, w.tpf2,
-                                                                                             heads_mask));
-            FB_CUDA(cudaGetLastError());
-            for (int hd = 0; hd < 2; ++hd) C.tsrc[hd] = ws + w.hsum + (size_t)hd * w.trunk_tiles * kTileBytes;
-        } else {
-            for (int hd = 0; hd < 2; ++hd) C.tsrc[hd] = ws + w.hdz + (size_t)hd * 3 * head_tiles * kTileBytes;
-        }
-        C.n_items = w.trunk_tiles / ((w.trunk_tiles <= 2 * sms) ? 1 : 2);
-        rc = chain_pairs_enabled() ? launch_chain2(3, C, sms, st) : launch_chain(3, (w.trunk_tiles <= 2 * sms) ? 1 : 2, C, sms, st);
-        if (rc) return rc;
-    }
     for (int head = 0; head < 2; ++head) {
         if (!(heads_mask & (1 << head))) continue;
         const int base = head ? P_C1 : P_D1;
@@ -753,6 +758,7 @@ int findb200_field_backward(const findb200_field_params* p, const float* pos, in
         add(doimg, kImgBytes, 1, hact + (size_t)2 * head_tiles * kTileBytes, kTileBytes, 0, 4, 1, 256, B, w.tpf2, w.tpf2,
             colsum + cs_out(head, B), 1, 16, base + 3, 0);
     }
+    const int n_head_gemms = ng;
     if (!frozen) {
         uint8_t* tact = ws + w.tact;
         uint8_t* tdz = ws + w.tdz;
@@ -773,13 +779,16 @@ int findb200_field_backward(const findb200_field_params* p, const float* pos, in
     // profiles/r2_dw_cta_lifetimes.txt).  The cost-weighted unit lists of all GEMMs are laid end to end and cut into one equal
     // piece per CTA; a piece that crosses a GEMM border becomes two segments, each with its own partial (deterministic: the
     // cut depends only on the shapes).
-    static float c_fix = -1.f, c_hbm = 0.f, c_l2 = 0.f;
+    static float c_fix = -1.f, c_hbm = 0.f, c_l2 = 0.f, c_seg = 0.f;
     if (c_fix < 0.f) {
-        const char* e = getenv("FINDB200_DW_COST");        // "fixed_us,us_per_64KB_hbm,us_per_64KB_l2" (tuning)
-        float a = 0.45f, b = 0.80f, c = 0.75f;
-        if (e) sscanf(e, "%f,%f,%f", &a, &b, &c);
-        c_fix = a; c_hbm = b; c_l2 = c;
+        const char* e = getenv("FINDB200_DW_COST");        // "fixed_us,us_per_64KB_hbm,us_per_64KB_l2,us_per_segment" (tuning)
+        float a = 0.70f, b = 0.55f, c = 0.45f, d = 6.0f;
+        if (e) sscanf(e, "%f,%f,%f,%f", &a, &b, &c, &d);
+        c_fix = a; c_hbm = b; c_l2 = c; c_seg = d;
     }
+    // every segment ends with the drain of its MMAs and a 256 KB partial written from TMEM: a CTA whose piece crosses a GEMM
+    // border pays that twice (measured: such CTAs ended 6..8 us after their neighbours, profiles/r2_dw_split.md)
+    const long long seg_cost = (long long)(c_seg * 1000.0f);
     (void)cost;
     long long unit_cost[kMaxDwGemms], total_cost = 0;      // in ns per unit (one tile = two stages)
     for (int i = 0; i < ng; ++i) {
@@ -802,8 +811,29 @@ int findb200_field_backward(const findb200_field_params* p, const float* pos, in
         if (total_units < n_ctas) n_ctas = (int)total_units;
         if (n_ctas < 1) n_ctas = 1;
     }
+    total_cost += (long long)(n_ctas + ng - 1) * seg_cost;
     FB_REQUIRE(n_ctas + ng <= kMaxDwSegs, FINDB200_ERR_UNSUPPORTED, "field_backward: too many weight-gradient GEMMs");
+    // Early / late launch.  The trunk's backward chain is a latency chain on trunk_tiles CTAs that moves no HBM bytes, and this
+    // kernel is bound by HBM: the CTAs that do not fit beside the trunk chain's would otherwise idle, and so would the HBM.  So
+    // the first n_early CTAs of the plan are launched on a side stream as soon as the heads' backward has finished (they run
+    // beside sum_feet and the trunk chain, as 2-CTA clusters so that they fill whole TPCs and leave whole TPCs to the trunk's
+    // CTA pairs), the others after the trunk chain; an early CTA runs longer and with fewer competitors, so its share of the
+    // timeline is early_weight times a late CTA's.  The head GEMMs come first in the timeline; the plan is only split when
+    // the early CTAs' share ends inside them (the trunk GEMMs need the trunk chain's output).
+    static float early_weight = -1.f;
+    if (early_weight < 0.f) {
+        const char* e = getenv("FINDB200_DW_SPLIT");        // early CTA's share relative to a late CTA's; 0 = one launch
+        early_weight = e ? (float)atof(e) : 1.65f;
+        if (early_weight < 0.f) early_weight = 0.f;
+    }
+    int n_early = 0;
+    if (!frozen && early_weight > 0.f && chain_pairs_enabled() && n_ctas == sms && w.trunk_tiles <= 2 * sms) {
+        n_early = (sms - w.trunk_tiles) & ~1;
+        if (n_early < 16 || n_early > n_ctas - 16) n_early = 0;
+    }
     int n_seg = 0;
+  plan_again:
+    n_seg = 0;
     {
         // walk the timeline: CTA b ends at cost tick total * (b + 1) / n_ctas, rounded to a unit boundary of the GEMM it falls in
         int gi = 0, u = 0;                      // current position: GEMM gi, unit u
@@ -812,21 +842,31 @@ int findb200_field_backward(const findb200_field_params* p, const float* pos, in
         for (int i = 0; i < ng; ++i) { slot[i] = 0; D.g[i].ncta = 0; }
         for (int b = 0; b < n_ctas; ++b) {
             D.cta_seg[b] = (unsigned short)n_seg;
-            const long long target = (b == n_ctas - 1) ? total_cost : total_cost * (b + 1) / n_ctas;
+            long long target = (b == n_ctas - 1) ? total_cost : total_cost * (b + 1) / n_ctas;
+            if (n_early > 0 && b < n_ctas - 1) {
+                const double sumw = (double)n_early * early_weight + (n_ctas - n_early);
+                const double cum = b + 1 <= n_early ? (double)(b + 1) * early_weight : (double)n_early * early_weight + (b + 1 - n_early);
+                target = (long long)((double)total_cost * cum / sumw);
+            }
+            const bool last = b == n_ctas - 1;
             while (gi < ng) {
                 const int units = D.g[gi].feet * D.g[gi].tpf;
-                const long long end_g = pos + (long long)(units - u) * unit_cost[gi];
+                const bool first = n_seg == (int)D.cta_seg[b];                // this CTA has no segment yet
+                const long long p0 = pos + seg_cost;                          // opening a segment costs its epilogue
+                if (!first && !last && p0 + unit_cost[gi] / 2 >= target) break;     // no room for another segment
+                const long long end_g = p0 + (long long)(units - u) * unit_cost[gi];
                 int u_end;
-                if (end_g <= target) u_end = units;
+                if (end_g <= target || last) u_end = units;
                 else {
-                    u_end = u + (int)((target - pos + unit_cost[gi] / 2) / unit_cost[gi]);       // nearest unit boundary
+                    u_end = u + (int)((target - p0 + unit_cost[gi] / 2) / unit_cost[gi]);       // nearest unit boundary
+                    if (u_end <= u) u_end = u + 1;
                     if (u_end > units) u_end = units;
                 }
                 if (u_end > u) {
                     DwSeg& sg = D.seg[n_seg++];
                     sg.gemm = (short)gi; sg.slot = (short)slot[gi]++; sg.u0 = u; sg.u1 = u_end;
                     ++D.g[gi].ncta;
-                    pos += (long long)(u_end - u) * unit_cost[gi];
+                    pos = p0 + (long long)(u_end - u) * unit_cost[gi];
                     u = u_end;
                 }
                 if (u < units) break;                   // this CTA's share ends inside GEMM gi
@@ -836,6 +876,11 @@ int findb200_field_backward(const findb200_field_params* p, const float* pos, in
         }
         D.cta_seg[n_ctas] = (unsigned short)n_seg;
         FB_REQUIRE(gi == ng, FINDB200_ERR_UNSUPPORTED, "field_backward: internal: dW work split did not cover every GEMM");
+        if (n_early > 0) {
+            bool ok = true;
+            for (int sgi = 0; sgi < D.cta_seg[n_early]; ++sgi) ok = ok && D.seg[sgi].gemm < n_head_gemms;
+            if (!ok) { n_early = 0; goto plan_again; }
+        }
     }
     int c0 = 0;
     for (int i = 0; i < ng; ++i) {
@@ -848,8 +893,42 @@ int findb200_field_backward(const findb200_field_params* p, const float* pos, in
         for (int i = 0; i < ng; ++i)
             fprintf(stderr, "dw gemm %d: param %d kblock %d feet %d a_imgs %d b_imgs %d N %d cta0 %d ncta %d\n", i, gemm_param[i], gemm_kblock[i],
                     D.g[i].feet, D.g[i].a_imgs, D.g[i].b_imgs, D.g[i].N, D.g[i].cta0, D.g[i].ncta);
-    rc = launch_dw(D, n_ctas, st);
+    if (g_chain_dbg && (g_chain_dbg_flags & 512))
+        for (int b = 0; b < n_ctas; ++b)
+            for (int sgi = D.cta_seg[b]; sgi < D.cta_seg[b + 1]; ++sgi)
+                fprintf(stderr, "dw cta %d: gemm %d units %d %d cost %lld early %d\n", b, D.seg[sgi].gemm, D.seg[sgi].u0, D.seg[sgi].u1,
+                        unit_cost[D.seg[sgi].gemm], b < n_early ? 1 : 0);
+    cudaStream_t side = nullptr;
+    cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+    if (n_early > 0) {
+        rc = side_stream(&side, &ev_fork, &ev_join);
+        if (rc) return rc;
+        FB_CUDA(cudaEventRecord(ev_fork, st));
+        FB_CUDA(cudaStreamWaitEvent(side, ev_fork, 0));
+        D.cta_base = 0;
+        rc = launch_dw(D, n_early, side, true);
+        if (rc) return rc;
+        FB_CUDA(cudaEventRecord(ev_join, side));
+    }
+    if (!frozen) {
+        rc = 0;
+        if (pos_shared && B > 1) {
+            FB_MARK("sum_feet", st);
+            FB_CUDA(fb::launch_pdl(sum_feet_kernel, dim3(w.tpf2 * (kTileBytes / 16) / 256, n_heads), 256, 0, st, ws + w.hdz, ws + w.hsum, B, w.tpf2,
+                                                                                             heads_mask));
+            FB_CUDA(cudaGetLastError());
+            for (int hd = 0; hd < 2; ++hd) C.tsrc[hd] = ws + w.hsum + (size_t)hd * w.trunk_tiles * kTileBytes;
+        } else {
+            for (int hd = 0; hd < 2; ++hd) C.tsrc[hd] = ws + w.hdz + (size_t)hd * 3 * head_tiles * kTileBytes;
+        }
+        C.n_items = w.trunk_tiles / ((w.trunk_tiles <= 2 * sms) ? 1 : 2);
+        rc = chain_pairs_enabled() ? launch_chain2(3, C, sms, st) : launch_chain(3, (w.trunk_tiles <= 2 * sms) ? 1 : 2, C, sms, st);
+        if (rc) return rc;
+    }
+    D.cta_base = n_early;
+    rc = launch_dw(D, n_ctas - n_early, st);
     if (rc) return rc;
+    if (n_early > 0) FB_CUDA(cudaStreamWaitEvent(st, ev_join, 0));
 
     ReduceParams R;
     memset(&R, 0, sizeof(R));

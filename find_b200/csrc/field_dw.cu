@@ -39,8 +39,9 @@ __global__ void __launch_bounds__(kDwThreads, 1) dw_kernel(const __grid_constant
     const uint32_t tmem = tmem_base_s;
 
     // this CTA's segments
-    const int s0 = P.cta_seg[blockIdx.x], s1 = P.cta_seg[blockIdx.x + 1];
-    if (P.dbg && tid == 0 && blockIdx.x < 240) { unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); P.dbg[2 * blockIdx.x] = t; }
+    const int cta = (int)blockIdx.x + P.cta_base;          // the early / late launches of one plan share the CTA numbering
+    const int s0 = P.cta_seg[cta], s1 = P.cta_seg[cta + 1];
+    if (P.dbg && tid == 0 && cta < 240) { unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); P.dbg[2 * cta] = t; }
 
     if (warp == 0) {
         // ---- producer: 64-row halves of the A and B tiles, one 8 KB bulk copy per image -----------------------
@@ -156,11 +157,11 @@ __global__ void __launch_bounds__(kDwThreads, 1) dw_kernel(const __grid_constant
     }
     tc_fence_before();
     __syncthreads();
-    if (P.dbg && tid == 0 && blockIdx.x < 240) { unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); P.dbg[2 * blockIdx.x + 1] = t; }
+    if (P.dbg && tid == 0 && cta < 240) { unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); P.dbg[2 * cta + 1] = t; }
     if (warp == 0) tmem_dealloc(tmem, 512);
 }
 
-int launch_dw(const DwParams& P, int n_ctas, cudaStream_t st) {
+int launch_dw(const DwParams& P, int n_ctas, cudaStream_t st, bool tpc_pairs) {
     if (n_ctas <= 0) return 0;
     const int smem = kDwStages * kDwStageBytes + 1024;
     static bool attr_set = false;
@@ -168,8 +169,23 @@ int launch_dw(const DwParams& P, int n_ctas, cudaStream_t st) {
         FB_CUDA(cudaFuncSetAttribute(dw_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
         attr_set = true;
     }
-    FB_MARK("dw_gemms", st);
-    FB_CUDA(fb::launch_pdl(dw_kernel, n_ctas, kDwThreads, smem, st, P));
+    // launch profiler: with the early / late split the early launch (side stream) is not marked; the late mark is named apart so
+    // that a reader of the marks knows that the dW kernel's span starts at the fork (the sum_feet mark), see bench.py
+    if (!tpc_pairs) FB_MARK(P.cta_base > 0 ? "dw_gemms_late" : "dw_gemms", st);
+    if (tpc_pairs) {
+        // the early launch runs beside the trunk's CTA-pair kernel: launched as 2-CTA clusters its CTAs fill whole TPCs and leave
+        // whole TPCs free for the pairs (the kernel itself makes no use of the cluster)
+        FB_REQUIRE(n_ctas % 2 == 0, FINDB200_ERR_UNSUPPORTED, "launch_dw: a TPC-paired launch needs an even number of CTAs");
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3(n_ctas); cfg.blockDim = dim3(kDwThreads); cfg.dynamicSmemBytes = smem; cfg.stream = st;
+        cudaLaunchAttribute at[1];
+        at[0].id = cudaLaunchAttributeClusterDimension;
+        at[0].val.clusterDim.x = 2; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+        cfg.attrs = at; cfg.numAttrs = 1;
+        FB_CUDA(cudaLaunchKernelEx(&cfg, dw_kernel, P));
+    } else {
+        FB_CUDA(fb::launch_pdl(dw_kernel, n_ctas, kDwThreads, smem, st, P));
+    }
     FB_CUDA(cudaGetLastError());
     return 0;
 }

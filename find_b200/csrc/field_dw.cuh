@@ -36,9 +36,10 @@ struct DwParams {
     DwSeg seg[kMaxDwSegs];
     unsigned short cta_seg[kMaxDwCtas + 1];   // CTA b owns segments [cta_seg[b], cta_seg[b + 1])
     unsigned long long* dbg;   // diagnostics (findb200_chain_trace): %globaltimer at the start / end of every CTA, [2 * cta]
+    int cta_base;              // blockIdx.x + cta_base = the CTA's number in the plan (the plan may be launched in two parts)
 };
 
-int launch_dw(const DwParams& P, int n_ctas, cudaStream_t st);
+int launch_dw(const DwParams& P, int n_ctas, cudaStream_t st, bool tpc_pairs = false);
 
 }  // namespace field
 }  // namespace fb

@@ -32,8 +32,13 @@ def test_camera_helpers_match_the_oracle_cpu():
     ndc = r.project(tv[None], R[:2], T[:2])
     for k in range(2):
         assert torch.allclose(ndc[k], ro.fov_project(tv, R[k], T[k]), atol=1e-6)
+    m = Meshes(tv[None], torch.zeros(1, 3, dtype=torch.int64))
+    with pytest.raises(AssertionError):          # renderer.py:278: features must come with return_features
+        r(m, R, T, return_features=True)
+    with pytest.raises(NotImplementedError):     # the debug overlays are not built and say so
+        r(m, R, T, keypoints=torch.zeros(1, 4, 3))
     with pytest.raises(NotImplementedError):
-        r(Meshes(tv[None], torch.zeros(1, 3, dtype=torch.int64)), R, T, return_features=True)
+        r(m, R, T, return_depth=True)
 
 
 def _scene(V, views, B=1, seed=0):
