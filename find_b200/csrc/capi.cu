@@ -36,6 +36,7 @@ static bool g_prof_on = false;
 static int g_prof_n = 0;
 static cudaEvent_t g_prof_ev[kProfMax];
 static const char* g_prof_name[kProfMax];
+static cudaStream_t g_prof_stream[kProfMax];      // a mark's time runs to the next mark on the SAME stream
 static int g_prof_created = 0;
 static bool g_prof_keep = false;
 
@@ -52,7 +53,31 @@ void prof_mark(const char* name, cudaStream_t st) {
     if (cs == cudaStreamCaptureStatusActive) cudaEventRecordWithFlags(g_prof_ev[g_prof_n], st, cudaEventRecordExternal);
     else cudaEventRecord(g_prof_ev[g_prof_n], st);
     g_prof_name[g_prof_n] = name;
+    g_prof_stream[g_prof_n] = st;
     ++g_prof_n;
+}
+
+// A side stream per device for the two places where a training step runs kernels beside its main stream (chamfer_hooks.cuh):
+// created on first use; inside a stream capture the side stream joins the capture through the fork event and leaves it through
+// the join event.
+int side_stream(int which, cudaStream_t* s, cudaEvent_t* fork, cudaEvent_t* join) {
+    constexpr int kMaxDev = 32;
+    static cudaStream_t streams[kMaxDev];
+    static cudaEvent_t forks[kMaxDev][2], joins[kMaxDev][2];
+    static bool made[kMaxDev];
+    int dev = 0;
+    FB_CUDA(cudaGetDevice(&dev));
+    FB_REQUIRE(dev >= 0 && dev < kMaxDev && which >= 0 && which < 2, FINDB200_ERR_UNSUPPORTED, "side_stream: device ordinal out of range");
+    if (!made[dev]) {
+        FB_CUDA(cudaStreamCreateWithFlags(&streams[dev], cudaStreamNonBlocking));
+        for (int k = 0; k < 2; ++k) {
+            FB_CUDA(cudaEventCreateWithFlags(&forks[dev][k], cudaEventDisableTiming));
+            FB_CUDA(cudaEventCreateWithFlags(&joins[dev][k], cudaEventDisableTiming));
+        }
+        made[dev] = true;
+    }
+    *s = streams[dev]; *fork = forks[dev][which]; *join = joins[dev][which];
+    return 0;
 }
 
 }  // namespace fb
@@ -76,22 +101,30 @@ int findb200_profile_read(char* buf, size_t cap) {
     buf[0] = 0;
     const int n = g_prof_n;
     if (n < 2) return 0;
-    if (cudaEventSynchronize(g_prof_ev[n - 1]) != cudaSuccess) return FINDB200_ERR_CUDA;
+    if (cudaDeviceSynchronize() != cudaSuccess) return FINDB200_ERR_CUDA;
     const char* names[256];
     double tot[256];
     int cnt[256], nn = 0;
+    bool side[256];
+    // marks of a side stream (the presort of a training step, chamfer_hooks.cuh) are timed along their own stream and reported
+    // as "side:<name>": they run beside the main stream's kernels
+    const cudaStream_t main_stream = g_prof_stream[0];
     for (int i = 0; i + 1 < n; ++i) {
         if (!g_prof_name[i]) continue;
+        int j = i + 1;
+        while (j < n && g_prof_stream[j] != g_prof_stream[i]) ++j;
+        if (j == n) continue;
         float ms = 0.f;
-        if (cudaEventElapsedTime(&ms, g_prof_ev[i], g_prof_ev[i + 1]) != cudaSuccess) { (void)cudaGetLastError(); continue; }
+        if (cudaEventElapsedTime(&ms, g_prof_ev[i], g_prof_ev[j]) != cudaSuccess) { (void)cudaGetLastError(); continue; }
+        const bool sd = g_prof_stream[i] != main_stream;
         int k = 0;
-        while (k < nn && strcmp(names[k], g_prof_name[i]) != 0) ++k;
-        if (k == nn) { if (nn == 256) continue; names[nn] = g_prof_name[i]; tot[nn] = 0; cnt[nn] = 0; ++nn; }
+        while (k < nn && (side[k] != sd || strcmp(names[k], g_prof_name[i]) != 0)) ++k;
+        if (k == nn) { if (nn == 256) continue; names[nn] = g_prof_name[i]; tot[nn] = 0; cnt[nn] = 0; side[nn] = sd; ++nn; }
         tot[k] += ms; cnt[k] += 1;
     }
     size_t off = 0;
     for (int k = 0; k < nn; ++k) {
-        int w = snprintf(buf + off, cap - off, "%s,%d,%.6f\n", names[k], cnt[k], tot[k]);
+        int w = snprintf(buf + off, cap - off, "%s%s,%d,%.6f\n", side[k] ? "side:" : "", names[k], cnt[k], tot[k]);
         if (w < 0 || (size_t)w >= cap - off) break;
         off += (size_t)w;
     }

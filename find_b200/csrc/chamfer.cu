@@ -20,6 +20,7 @@
 //     an atomic counter; splits combine with one 64-bit atomicMin on (dist_bits << 32 | idx), which orders
 //     exactly like (dist, idx) lexicographically because dist >= +0.
 #include "common.cuh"
+#include "chamfer_hooks.cuh"
 #include "../../include/find_b200.h"
 #include <math_constants.h>
 #include <cstdlib>
@@ -536,6 +537,7 @@ struct Workspace {
     unsigned long long *keys_x, *keys_y;
     float *soa_x, *soa_y;
     int *perm_x, *perm_y;
+    int* perm_t;                      // curve order of the template cloud (presorted training step), [P1p]
     float *box_x, *box_y, *sbox_x, *sbox_y;
     int2 *lut_x, *lut_y;              // grid mode: linear cell -> [start, end) of the sorted cloud
     int *cell_x, *cell_y, *rank_x, *rank_y;
@@ -569,6 +571,7 @@ static Workspace carve(void* base, int N, int P1, int P2) {
     w.rank_x = (int*)take((size_t)N * P1 * 4); w.rank_y = (int*)take((size_t)N * P2 * 4);
     w.lut_x = (int2*)take(((size_t)N << (3 * w.gl1)) * 8); w.lut_y = (int2*)take(((size_t)N << (3 * w.gl2)) * 8);
     w.sum_x = (double*)take((size_t)N * tail_blocks(P1) * 8); w.sum_y = (double*)take((size_t)N * tail_blocks(P2) * 8);   // >= fin_blocks
+    w.perm_t = (int*)take((size_t)w.P1p * 4);
     w.bytes = off;
     return w;
 }
@@ -680,17 +683,25 @@ static bool sort_in_one_cta(int P1, int P2) {
     return Pm <= g_sort_cta_max && grid_log2(Pm) <= 4;       // the cluster kernel keeps ncell / 8 <= 1024 cells per CTA
 }
 
+// phase: 0 = sort both sets, then the kNN; 1 = presort only: set 0 is ONE cloud (the template `x`), whose curve order goes to
+// w.perm_t, set 1 the N target clouds, no kNN; 2 = after a presort: the N clouds `x` are laid out in the template's order
+// (cloud_apply_order_kernel), then the kNN.
 static int run_knn_cull(const float* x, const float* y, const int64_t* lx, const int64_t* ly, int N, int P1, int P2,
-                        bool both, Workspace& w, cudaStream_t st, const ZeroJobs* zj = nullptr) {
+                        bool both, Workspace& w, cudaStream_t st, const ZeroJobs* zj = nullptr, int phase = 0) {
     SortParams sp{};
     if (zj)
         for (int k = 0; k < 2; ++k) { sp.zero_ptr[k] = (unsigned*)zj->ptr[k]; sp.zero_words[k] = (unsigned)(zj->bytes[k] / 4); }
-    sp.set[0] = SortSet{x, lx, w.soa_x, w.perm_x, w.box_x, w.sbox_x, w.bbmin_x, w.bbmax_x, w.hist_x, w.cell_x, w.rank_x,
-                        P1, w.P1p, w.C1p, w.S1p, w.gl1};
+    sp.set[0] = SortSet{x, lx, w.soa_x, phase == 1 ? w.perm_t : w.perm_x, w.box_x, w.sbox_x, w.bbmin_x, w.bbmax_x, w.hist_x, w.cell_x, w.rank_x,
+                        P1, w.P1p, w.C1p, w.S1p, w.gl1, phase == 1 ? 1 : N};
     sp.set[1] = SortSet{y, ly, w.soa_y, w.perm_y, w.box_y, w.sbox_y, w.bbmin_y, w.bbmax_y, w.hist_y, w.cell_y, w.rank_y,
-                        P2, w.P2p, w.C2p, w.S2p, w.gl2};
+                        P2, w.P2p, w.C2p, w.S2p, w.gl2, N};
     const int Pm = P1 > P2 ? P1 : P2, Ppm = w.P1p > w.P2p ? w.P1p : w.P2p;
-    if (sort_in_one_cta(P1, P2)) {
+    if (phase == 2) {
+        OrderParams op{x, w.perm_t, w.soa_x, w.perm_x, w.box_x, w.sbox_x, P1, w.P1p, w.C1p, w.S1p};
+        FB_MARK("order_boxes", st);
+        FB_CUDA(fb::launch_pdl(cloud_apply_order_kernel, dim3((w.P1p + 1023) / 1024, N), 1024, 0, st, op));
+        FB_CUDA(cudaGetLastError());
+    } else if (sort_in_one_cta(P1, P2)) {
         // small clouds: the whole sort (and the clearing of the header / the caller's regions) in one launch, one cluster per cloud
         const int gl = w.gl1 > w.gl2 ? w.gl1 : w.gl2;
         const size_t smem = ((size_t)4 << (3 * gl)) / kSortCluster;
@@ -738,6 +749,7 @@ static int run_knn_cull(const float* x, const float* y, const int64_t* lx, const
     FB_CUDA(fb::launch_pdl(cloud_superboxes_kernel, dim3((Ppm / kCullChunk / 32 + 8) / 8, N, 2), 256, 0, st, sp));
     FB_CUDA(cudaGetLastError());
     }
+    if (phase == 1) return 0;
 
     CullParams prm{};
     prm.N = N; prm.counter = w.counter; prm.stats = w.stats; prm.ndir = both ? 2 : 1;
@@ -754,12 +766,13 @@ static int run_knn_cull(const float* x, const float* y, const int64_t* lx, const
 
 // Core: runs 1 or 2 directions.  dir 0: queries x (P1) vs targets y (P2); dir 1: queries y vs targets x.
 static int run_knn(const float* x, const float* y, const int64_t* lx, const int64_t* ly, int N, int P1, int P2,
-                   bool both, void* ws_base, size_t ws_bytes, Workspace& w, cudaStream_t st, const ZeroJobs* zj = nullptr) {
+                   bool both, void* ws_base, size_t ws_bytes, Workspace& w, cudaStream_t st, const ZeroJobs* zj = nullptr, int phase = 0) {
     FB_REQUIRE(N >= 0 && P1 >= 0 && P2 >= 0, FINDB200_ERR_SHAPE, "knn: negative size N=%d P1=%d P2=%d", N, P1, P2);
     w = carve(ws_base, N, P1, P2);
     FB_REQUIRE(ws_base != nullptr && ws_bytes >= w.bytes, FINDB200_ERR_WORKSPACE,
                "knn: workspace too small (%zu < %zu bytes)", ws_bytes, w.bytes);
     if (N == 0 || (P1 == 0 && P2 == 0)) return 0;
+    if (phase == 2) return run_knn_cull(x, y, lx, ly, N, P1, P2, both, w, st, nullptr, 2);      // memsets and sorts ran in the presort
     if (knn_mode() != 1 && P1 > 0 && P2 > 0 && sort_in_one_cta(P1, P2))       // the one-launch sort clears what it needs itself
         return run_knn_cull(x, y, lx, ly, N, P1, P2, both, w, st, zj);
     // queue counter + stats = 0, keys = 0xFF.. (identity of atomicMin; also what an unreachable query keeps)
@@ -775,7 +788,28 @@ static int run_knn(const float* x, const float* y, const int64_t* lx, const int6
     }
     if (P1 == 0 || P2 == 0) return 0;
     return knn_mode() == 1 ? run_knn_brute(x, y, lx, ly, N, P1, P2, both, w, st)
-                           : run_knn_cull(x, y, lx, ly, N, P1, P2, both, w, st, zj);
+                           : run_knn_cull(x, y, lx, ly, N, P1, P2, both, w, st, zj, phase);
+}
+
+// ---- presorted training step (hooks for step.cu; see chamfer_hooks.cuh) ---------------------------------------------------
+thread_local bool g_train_presorted = false;
+
+bool presort_supported(int N, int P1, int P2) {
+    static int on = -1;
+    if (on < 0) { const char* e = getenv("FINDB200_PRESORT"); on = (e && e[0] == '0') ? 0 : 1; }
+    const int m = knn_mode();
+    return on && N >= 1 && P1 >= 1 && P2 >= 1 && (m == 0 || m == 2) && !sort_in_one_cta(P1, P2);
+}
+
+int train_presort(const float* x_template, const float* y, const int64_t* y_len, int N, int P1, int P2, void* zero_a, size_t zero_a_bytes,
+                  void* zero_b, size_t zero_b_bytes, void* ws, size_t ws_bytes, cudaStream_t st) {
+    FB_REQUIRE(x_template && y && presort_supported(N, P1, P2), FINDB200_ERR_ARG, "chamfer presort: bad argument");
+    FB_REQUIRE(zero_a_bytes % 4 == 0 && zero_b_bytes % 4 == 0, FINDB200_ERR_ARG, "chamfer presort: zero regions must be multiples of 4 bytes");
+    ZeroJobs zj{{zero_a, zero_b}, {zero_a ? zero_a_bytes : 0, zero_b ? zero_b_bytes : 0}};
+    Workspace w;
+    const int rc = run_knn(x_template, y, nullptr, y_len, N, P1, P2, true, ws, ws_bytes, w, st, &zj, 1);
+    FB_MARK_END(st);          // closes the side stream's marks (the launch profiler times a mark along its own stream)
+    return rc;
 }
 
 }  // namespace chamfer
@@ -874,7 +908,10 @@ int findb200_chamfer_train(const float* x, const float* y, const int64_t* x_len,
     FB_REQUIRE(zero_extra_bytes % 4 == 0, FINDB200_ERR_ARG, "chamfer_train: zero_extra_bytes must be a multiple of 4");
     ZeroJobs zj{{grad_x, zero_extra}, {(size_t)N * P1 * 24, zero_extra ? zero_extra_bytes : 0}};
     Workspace w;
-    int rc = run_knn(x, y, x_len, y_len, N, P1, P2, true, ws, ws_bytes, w, st, &zj);
+    // after fb::chamfer::train_presort (step.cu): the targets are sorted, the template's curve order is known and the zero
+    // regions are cleared; the deformed clouds only have to be laid out in that order
+    const bool presorted = fb::chamfer::g_train_presorted && !x_len && presort_supported(N, P1, P2);
+    int rc = run_knn(x, y, x_len, y_len, N, P1, P2, true, ws, ws_bytes, w, st, &zj, presorted ? 2 : 0);
     if (rc) return rc;
     TailParams tp{};
     tp.dir[0] = FinalizeDir{w.keys_x, x_len, y_len, nullptr, idx_x, nullptr, w.sum_x, P1, P2};

@@ -7,6 +7,7 @@
 //             | HEAD_BWD | TRUNK_BWD | dw_kernel (all weight-gradient GEMMs in one launch) | reduce_dw | finish_small
 // With per-foot distinct points (TextureLossGTSpace call site, losses.py:50) the trunk runs per foot as well.
 #include "field.cuh"
+#include "chamfer_hooks.cuh"
 #include <cstdio>
 #include <cstdlib>
 #include "field_dw.cuh"
@@ -560,26 +561,6 @@ void field_bwd_zero_region(int nfeet, int V, int pos_shared, size_t* offset, siz
     *bytes = (w.colsum - w.scal) + cs_total(nfeet) * 8;
 }
 
-// The side stream of findb200_field_backward's early dW launch (one per device, created on first use; inside a stream capture
-// the side stream joins the capture through the fork event and leaves it through the join event).
-static int side_stream(cudaStream_t* s, cudaEvent_t* fork, cudaEvent_t* join) {
-    constexpr int kMaxDev = 32;
-    static cudaStream_t streams[kMaxDev];
-    static cudaEvent_t forks[kMaxDev], joins[kMaxDev];
-    static bool made[kMaxDev];
-    int dev = 0;
-    FB_CUDA(cudaGetDevice(&dev));
-    FB_REQUIRE(dev >= 0 && dev < kMaxDev, FINDB200_ERR_UNSUPPORTED, "field_backward: device ordinal out of range");
-    if (!made[dev]) {
-        FB_CUDA(cudaStreamCreateWithFlags(&streams[dev], cudaStreamNonBlocking));
-        FB_CUDA(cudaEventCreateWithFlags(&forks[dev], cudaEventDisableTiming));
-        FB_CUDA(cudaEventCreateWithFlags(&joins[dev], cudaEventDisableTiming));
-        made[dev] = true;
-    }
-    *s = streams[dev]; *fork = forks[dev]; *join = joins[dev];
-    return 0;
-}
-
 static int run_pack(const findb200_field_params* p, const Workspace& w, uint8_t* ws, const LatentBiasParams& LB, cudaStream_t st) {
     const PackLayout L = make_layout();
     PackParams PP;
@@ -901,7 +882,7 @@ int findb200_field_backward(const findb200_field_params* p, const float* pos, in
     cudaStream_t side = nullptr;
     cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
     if (n_early > 0) {
-        rc = side_stream(&side, &ev_fork, &ev_join);
+        rc = fb::side_stream(1, &side, &ev_fork, &ev_join);
         if (rc) return rc;
         FB_CUDA(cudaEventRecord(ev_fork, st));
         FB_CUDA(cudaStreamWaitEvent(side, ev_fork, 0));

@@ -40,6 +40,7 @@ struct SortSet {
     int* cell;              // [N][P]         cell of point i
     int* rank;              // [N][P]         arrival rank of point i inside its cell
     int P, Ppad, Cpad, Spad, glog2;
+    int N;                  // clouds of THIS set (the two sets of one launch may differ: kernels return for n >= N)
 };
 // zero[k]: an optional region the FIRST sort kernel clears (4-byte words) while it computes the bounding boxes: buffers that
 // later kernels of a fused training step accumulate into, cleared here instead of by separate memset nodes
@@ -102,6 +103,7 @@ __global__ void __launch_bounds__(256) cloud_bbox_kernel(const SortParams prm) {
     }
     const SortSet& S = prm.set[blockIdx.z];
     const int n = blockIdx.y;
+    if (n >= S.N) return;
     const int len = set_len(S, n);
     const int i0 = blockIdx.x * 1024;
     if (i0 >= len) return;
@@ -160,6 +162,7 @@ __global__ void __launch_bounds__(256) cloud_hist_kernel(const SortParams prm) {
     fb::pdl_wait_trigger();
     const SortSet& S = prm.set[blockIdx.z];
     const int n = blockIdx.y;
+    if (n >= S.N) return;
     const int len = set_len(S, n);
     const int i = blockIdx.x * 256 + threadIdx.x;
     if (i >= len) return;
@@ -179,7 +182,7 @@ __global__ void __launch_bounds__(1024) cloud_scan_kernel(const SortParams prm) 
     fb::pdl_wait_trigger();
     __shared__ int s_wsum[32];
     const SortSet& S = prm.set[blockIdx.y];
-    if (S.P <= 0) return;
+    if (S.P <= 0 || (int)blockIdx.x >= S.N) return;
     const int n = blockIdx.x, lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     const int ncell = 1 << (3 * S.glog2), seg = ncell / 32;
     int* hist = S.hist + ((size_t)n << (3 * S.glog2)) + wid * seg;
@@ -220,6 +223,7 @@ __global__ void __launch_bounds__(256) cloud_scatter_kernel(const SortParams prm
     fb::pdl_wait_trigger();
     const SortSet& S = prm.set[blockIdx.z];
     const int n = blockIdx.y;
+    if (n >= S.N) return;
     const int len = set_len(S, n);
     const int i = blockIdx.x * 256 + threadIdx.x;
     if (i >= S.Ppad || S.P <= 0) return;
@@ -241,6 +245,7 @@ __global__ void __launch_bounds__(256) cloud_boxes_kernel(const SortParams prm) 
     fb::pdl_wait_trigger();
     const SortSet& S = prm.set[blockIdx.z];
     const int n = blockIdx.y, lane = threadIdx.x & 31;
+    if (n >= S.N) return;
     const int len = set_len(S, n);
     const int c = blockIdx.x * 8 + (threadIdx.x >> 5);
     if (c * kCullChunk >= len) return;
@@ -270,6 +275,7 @@ __global__ void __launch_bounds__(256) cloud_superboxes_kernel(const SortParams 
     fb::pdl_wait_trigger();
     const SortSet& S = prm.set[blockIdx.z];
     const int n = blockIdx.y, lane = threadIdx.x & 31;
+    if (n >= S.N) return;
     const int nchunk = (set_len(S, n) + kCullChunk - 1) / kCullChunk;
     const int sc = blockIdx.x * 8 + (threadIdx.x >> 5);
     if (sc * 32 >= nchunk) return;
@@ -286,6 +292,69 @@ __global__ void __launch_bounds__(256) cloud_superboxes_kernel(const SortParams 
             v = k < 3 ? fminf(v, u) : fmaxf(v, u);
         }
         if (lane == 0) sbox[k * S.Spad + sc] = v;
+    }
+}
+
+// ---- a cloud set laid out in a GIVEN order ----------------------------------------------------------------------------
+// The deformed template of a training step moves a little per step and smoothly over the surface: the curve order of the
+// TEMPLATE's vertices (one cloud, sorted once per step beside the forward pass) keeps every 32-point chunk of every deformed foot
+// compact.  This kernel replaces steps 1-6 for such a set: points are gathered in the given order into the SoA rows (+inf
+// padding), the permutation is the order itself, and chunk and super-chunk boxes are taken on the way.  Any permutation gives
+// the same kNN result bit for bit (the boxes are true bounds of their members; ties resolve on ORIGINAL indices): a poor order
+// only costs speed.  grid (ceil(Ppad / 1024), N), block 1024 = one super-chunk of 32 chunks; all clouds are full (no lengths).
+struct OrderParams {
+    const float* aos;       // [N][P][3]
+    const int* order;       // [Ppad] sorted position -> original index, shared by all clouds (entries >= P unused)
+    float* soa; int* perm; float* box; float* sbox;
+    int P, Ppad, Cpad, Spad;
+};
+__global__ void __launch_bounds__(1024) cloud_apply_order_kernel(const OrderParams prm) {
+    fb::pdl_wait_trigger();
+    __shared__ float s_box[32][6];
+    const int n = blockIdx.y, lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const int pos = blockIdx.x * 1024 + threadIdx.x;
+    const int c = blockIdx.x * 32 + wid;                       // chunk
+    const int nchunk = (prm.P + kCullChunk - 1) / kCullChunk;
+    float a[3] = {CUDART_INF_F, CUDART_INF_F, CUDART_INF_F}, b[3] = {-CUDART_INF_F, -CUDART_INF_F, -CUDART_INF_F};
+    if (pos < prm.Ppad) {
+        float* soa = prm.soa + (size_t)n * 3 * prm.Ppad;
+        int src = 0;
+        float v[3] = {CUDART_INF_F, CUDART_INF_F, CUDART_INF_F};
+        if (pos < prm.P) {
+            src = prm.order[pos];
+            const float* p = prm.aos + ((size_t)n * prm.P + src) * 3;
+#pragma unroll
+            for (int k = 0; k < 3; ++k) { v[k] = p[k]; a[k] = v[k]; b[k] = v[k]; }
+        }
+        soa[pos] = v[0]; soa[prm.Ppad + pos] = v[1]; soa[2 * prm.Ppad + pos] = v[2];
+        prm.perm[(size_t)n * prm.Ppad + pos] = src;
+    }
+#pragma unroll
+    for (int k = 0; k < 3; ++k)
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            a[k] = fminf(a[k], __shfl_xor_sync(0xffffffffu, a[k], o));
+            b[k] = fmaxf(b[k], __shfl_xor_sync(0xffffffffu, b[k], o));
+        }
+    if (lane == 0) {
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+            s_box[wid][k] = a[k]; s_box[wid][3 + k] = b[k];
+            if (c < nchunk) {
+                float* box = prm.box + (size_t)n * 6 * prm.Cpad;
+                box[k * prm.Cpad + c] = a[k]; box[(3 + k) * prm.Cpad + c] = b[k];
+            }
+        }
+    }
+    __syncthreads();
+    if (wid < 6 && blockIdx.x * 32 < nchunk) {                 // warp k reduces coordinate k over the 32 chunks
+        float v = s_box[lane][wid];                            // chunks past the end hold the identities
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            const float u = __shfl_xor_sync(0xffffffffu, v, o);
+            v = wid < 3 ? fminf(v, u) : fmaxf(v, u);
+        }
+        if (lane == 0) prm.sbox[(size_t)n * 6 * prm.Spad + wid * prm.Spad + blockIdx.x] = v;
     }
 }
 
@@ -1116,7 +1185,7 @@ struct GridParams { GridDir dir[2]; int ndir, N, blocks_dir0; unsigned long long
 __global__ void __launch_bounds__(256) cloud_lut_kernel(const SortParams prm, int2* __restrict__ lut_x, int2* __restrict__ lut_y) {
     fb::pdl_wait_trigger();
     const SortSet& S = prm.set[blockIdx.z];
-    if (S.P <= 0) return;
+    if (S.P <= 0 || (int)blockIdx.y >= S.N) return;
     const int n = blockIdx.y, G = 1 << S.glog2, ncell = 1 << (3 * S.glog2);
     const int lin = blockIdx.x * 256 + threadIdx.x;
     if (lin >= ncell) return;

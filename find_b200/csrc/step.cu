@@ -8,6 +8,7 @@
 #include "common.cuh"
 #include "../../include/find_b200.h"
 #include "field.cuh"
+#include "chamfer_hooks.cuh"
 
 namespace fb {
 namespace step {
@@ -140,8 +141,27 @@ static int run_step(const findb200_field_params* p, const float* template_pos, c
     double* mse_sum = (double*)(ws + c.sums);
     float* chamf = (float*)(ws + c.sums + 64);
 
-    int rc = findb200_field_forward(p, template_pos, 1, z_shape, z_pose, z_tex, reg, nfeet, V, 1, disp, col, verts,
-                                    ws + c.field, c.field_bytes, stream);
+    // plain branch: the part of the Chamfer that does not depend on the forward pass (sort of the target clouds, curve order of
+    // the template, clearing of the accumulators) runs on a side stream beside the forward kernels (chamfer_hooks.cuh)
+    const bool presort = S == 0 && !smooth && fb::chamfer::presort_supported(nfeet, V, P2);
+    cudaEvent_t ev_join = nullptr;
+    int rc = 0;
+    if (presort) {
+        cudaStream_t side = nullptr;
+        cudaEvent_t ev_fork = nullptr;
+        rc = fb::side_stream(0, &side, &ev_fork, &ev_join);
+        if (rc) return rc;
+        size_t zoff = 0, zbytes = 0;
+        fb::field::field_bwd_zero_region(nfeet, V, 1, &zoff, &zbytes);
+        FB_CUDA(cudaEventRecord(ev_fork, st));
+        FB_CUDA(cudaStreamWaitEvent(side, ev_fork, 0));
+        rc = fb::chamfer::train_presort(template_pos, target, target_len, nfeet, V, P2, ws + c.grad_verts, (size_t)nfeet * V * 24,
+                                        ws + c.field + zoff, zbytes, ws + c.knn, c.knn_bytes, side);
+        if (rc) return rc;
+        FB_CUDA(cudaEventRecord(ev_join, side));
+    }
+    rc = findb200_field_forward(p, template_pos, 1, z_shape, z_pose, z_tex, reg, nfeet, V, 1, disp, col, verts,
+                                ws + c.field, c.field_bytes, stream);
     if (rc) return rc;
     if (S > 0) {
         // losses.py:67: Chamfer is taken on S area-weighted surface samples of the deformed template
@@ -174,9 +194,12 @@ static int run_step(const findb200_field_params* p, const float* template_pos, c
         fb::field::field_bwd_zero_region(nfeet, V, 1, &zoff, &zbytes);
         long long* gv_fx = (long long*)(ws + c.grad_verts);
         float* gv_scale = (float*)(ws + c.gv_scale);
+        if (presort) FB_CUDA(cudaStreamWaitEvent(st, ev_join, 0));
+        fb::chamfer::g_train_presorted = presort;
         rc = findb200_chamfer_train(verts, target, nullptr, target_len, nfeet, V, P2, w_chamf, tex ? col : nullptr, col_target, n,
                                     tex ? w_tex : 0.f, gv_fx, gv_scale, grad_col, idx_x, idx_y, loss3, (double*)(ws + c.sums + 1024),
                                     c.mse_part_bytes, ws + c.field + zoff, zbytes, ws + c.knn, c.knn_bytes, stream);
+        fb::chamfer::g_train_presorted = false;
         if (rc) return rc;
         fb::field::g_field_bwd_prezeroed = true;
         fb::field::g_grad_verts_fx = gv_fx;
