@@ -81,6 +81,7 @@ SIGNATURES = {
     "findb200_allreduce_p2p": (c_int, [c_void_p, c_void_p, c_int, c_int, ctypes.c_longlong, c_float, c_void_p, c_int, c_void_p]),
     "findb200_train_step_knn_stats": (c_int, [c_void_p, c_int, c_int, c_int, c_void_p, c_void_p]),
     "findb200_set_sort_cta_max": (c_int, [c_int]),
+    "findb200_set_step_overlap": (c_int, [c_int, c_float]),
     "findb200_chamfer_train": (c_int, [c_void_p] * 4 + [c_int] * 3 + [c_float] + [c_void_p] * 2 + [c_size_t, c_float] + [c_void_p] * 7 + [c_size_t, c_void_p, c_size_t, c_void_p, c_size_t, c_void_p]),
     "findb200_chamfer_backward": (c_int, [c_void_p] * 4 + [c_int] * 3 + [c_void_p] * 3 + [c_float] + [c_void_p] * 3),
 }

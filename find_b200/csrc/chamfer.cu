@@ -794,11 +794,11 @@ static int run_knn(const float* x, const float* y, const int64_t* lx, const int6
 // ---- presorted training step (hooks for step.cu; see chamfer_hooks.cuh) ---------------------------------------------------
 thread_local bool g_train_presorted = false;
 
+int g_presort = -1;         // -1: FINDB200_PRESORT (default on); findb200_set_step_overlap
 bool presort_supported(int N, int P1, int P2) {
-    static int on = -1;
-    if (on < 0) { const char* e = getenv("FINDB200_PRESORT"); on = (e && e[0] == '0') ? 0 : 1; }
+    if (g_presort < 0) { const char* e = getenv("FINDB200_PRESORT"); g_presort = (e && e[0] == '0') ? 0 : 1; }
     const int m = knn_mode();
-    return on && N >= 1 && P1 >= 1 && P2 >= 1 && (m == 0 || m == 2) && !sort_in_one_cta(P1, P2);
+    return g_presort && N >= 1 && P1 >= 1 && P2 >= 1 && (m == 0 || m == 2) && !sort_in_one_cta(P1, P2);
 }
 
 int train_presort(const float* x_template, const float* y, const int64_t* y_len, int N, int P1, int P2, void* zero_a, size_t zero_a_bytes,

@@ -17,9 +17,11 @@ namespace chamfer {
 bool presort_supported(int N, int P1, int P2);      // culled kNN modes, six-kernel sort, FINDB200_PRESORT != 0
 int train_presort(const float* x_template, const float* y, const int64_t* y_len, int N, int P1, int P2, void* zero_a, size_t zero_a_bytes,
                   void* zero_b, size_t zero_b_bytes, void* ws, size_t ws_bytes, cudaStream_t st);
+extern int g_presort;                                // -1 environment default, 0 off, 1 on (findb200_set_step_overlap)
 extern thread_local bool g_train_presorted;          // consumed by the next findb200_chamfer_train on this thread
 
 }  // namespace chamfer
+namespace field { extern float g_dw_early_weight; }     // < 0 environment default (FINDB200_DW_SPLIT, else 1.65); 0 = one dW launch
 
 // a side stream per device with fork / join event pairs (created on first use): which = 0 presort, 1 early dW launch
 int side_stream(int which, cudaStream_t* s, cudaEvent_t* fork, cudaEvent_t* join);

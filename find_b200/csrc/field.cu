@@ -552,6 +552,7 @@ static void fill_chain_common(ChainParams& C, const findb200_field_params* p, co
 }  // namespace fb
 namespace fb {
 namespace field {
+float g_dw_early_weight = -1.f;
 thread_local bool g_field_bwd_prezeroed = false;
 thread_local const long long* g_grad_verts_fx = nullptr;
 thread_local const float* g_grad_verts_fx_scale = nullptr;
@@ -801,12 +802,12 @@ int findb200_field_backward(const findb200_field_params* p, const float* pos, in
     // CTA pairs), the others after the trunk chain; an early CTA runs longer and with fewer competitors, so its share of the
     // timeline is early_weight times a late CTA's.  The head GEMMs come first in the timeline; the plan is only split when
     // the early CTAs' share ends inside them (the trunk GEMMs need the trunk chain's output).
-    static float early_weight = -1.f;
-    if (early_weight < 0.f) {
+    if (g_dw_early_weight < 0.f) {
         const char* e = getenv("FINDB200_DW_SPLIT");        // early CTA's share relative to a late CTA's; 0 = one launch
-        early_weight = e ? (float)atof(e) : 1.65f;
-        if (early_weight < 0.f) early_weight = 0.f;
+        g_dw_early_weight = e ? (float)atof(e) : 1.65f;
+        if (g_dw_early_weight < 0.f) g_dw_early_weight = 0.f;
     }
+    const float early_weight = g_dw_early_weight;
     int n_early = 0;
     if (!frozen && early_weight > 0.f && chain_pairs_enabled() && n_ctas == sms && w.trunk_tiles <= 2 * sms) {
         n_early = (sms - w.trunk_tiles) & ~1;
@@ -963,6 +964,12 @@ int findb200_field_backward(const findb200_field_params* p, const float* pos, in
     }
     FB_CUDA(cudaGetLastError());
     FB_MARK_END(st);
+    return 0;
+}
+
+int findb200_set_step_overlap(int presort, float dw_early_weight) {
+    fb::chamfer::g_presort = presort < 0 ? -1 : (presort ? 1 : 0);
+    fb::field::g_dw_early_weight = dw_early_weight < 0.f ? -1.f : dw_early_weight;
     return 0;
 }
 

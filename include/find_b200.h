@@ -85,6 +85,13 @@ int findb200_set_knn_mode(int mode, int kq);
  * six kernels; 0 = never (the default: the single launch measured slower), negative = back to the default.  A/B measurement. */
 int findb200_set_sort_cta_max(int max_points);
 int findb200_knn_stats(const void* workspace, unsigned long long* out4_host, void* stream);
+/* Side-stream schedule of the fused training step (A/B measurement and tests; both default on).  presort: 1 = the sort of the
+ * target clouds and the curve order of the template run on a side stream beside the forward kernels and the deformed feet are laid
+ * out in the template's order (bit-identical results), 0 = everything on the caller's stream, negative = environment default
+ * (FINDB200_PRESORT).  dw_early_weight: share of an early CTA of the weight-gradient launch relative to a late one (the early CTAs
+ * start on a side stream beside the trunk's backward chain), 0 = one launch, negative = default (FINDB200_DW_SPLIT, else 1.65); it
+ * changes how the fp32 partial sums of dW are grouped, i.e. the last bits of the weight gradients. */
+int findb200_set_step_overlap(int presort, float dw_early_weight);
 
 /* ------------------------------------------------------------------------------------------------------
  * Neural displacement field   (replaces NeuralDisplacementField.forward + its autograd,

@@ -286,6 +286,42 @@ def test_step_is_bit_reproducible_at_cfg2_size():
     assert float(a["flat_grad"].abs().max()) > 0 and float(a["rows/reg"].abs().max()) > 0
 
 
+def test_step_side_stream_schedules_do_not_change_results():
+    """The presorted step (target sort + template order on a side stream, deformed feet laid out in the template's order) is
+    bit-identical to the in-line sort on every output and gradient; the early / late launch of the dW plan only regroups the
+    per-CTA fp32 partial sums behind the weight / bias / latent gradients (outputs and losses stay bit-identical).  Both with and without the step graph."""
+    from find_b200 import _lib
+    from find_b200.step import TrainStep
+    lib = _lib.load()
+    B, V, P2, n_rows = 8, 10242, 10000, 8
+    dev, model, p, tv, tables, idx, target, colt = _setup(B, V, P2, n_rows, seed=91)
+
+    def snap(presort, weight, graph):
+        lib.findb200_set_step_overlap(presort, weight)
+        try:
+            step = TrainStep(model, B, P2, with_colour=True, use_graph=graph)
+            step.load_inputs(idx, target, colt)
+            for _ in range(2):
+                step.run()
+            torch.cuda.synchronize()
+            return dict(verts=step.verts.clone(), col=step.col.clone(), loss3=step.loss3.clone(), flat_grad=step.flat_grad.clone(),
+                        **{"rows/" + k: v.clone() for k, v in step.grows.items()})
+        finally:
+            lib.findb200_set_step_overlap(-1, -1.0)
+    base = snap(0, 0.0, False)
+    for graph in (False, True):
+        a = snap(1, 0.0, graph)
+        for k in base:
+            assert torch.equal(a[k], base[k]), ("presort", graph, k)
+        b = snap(1, 1.65, graph)
+        for k in base:
+            if k == "flat_grad" or k.startswith("rows/"):     # per-CTA fp32 column sums / dW partials are cut differently
+                assert float((b[k] - base[k]).norm() / base[k].norm()) < 1e-6, ("dw split", graph, k)
+            else:
+                assert torch.equal(b[k], base[k]), ("dw split", graph, k)
+    assert float(base["flat_grad"].abs().max()) > 0
+
+
 def test_texture_loss_gt_space_matches_oracle():
     """losses.py:22-57: masked colour MSE at surface samples of the GT mesh, through the field's per-foot-points call site.
     The oracle evaluates the fp32 field at the SAME samples (the draw is injected from the GPU call)."""
