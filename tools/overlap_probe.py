@@ -100,5 +100,27 @@ def timed_graph(gr, iters=50):
     return ts[len(ts) // 2]
 
 
+# ---- the field BACKWARD (head_bwd, sum_feet, trunk_bwd, dW: store / HBM-bound) beside the kNN
+ws_g = [w.clone().requires_grad_(True) for w in ws_]
+bs_g = [b.clone().requires_grad_(True) for b in bs_]
+zg = [z.clone().requires_grad_(True) for z in (zs, zp, zt)]
+with torch.cuda.stream(sA):
+    outs = field_apply(pos, zg[0], zg[1], zg[2], None, Bm, avg, ws_g, bs_g)
+    gouts = [torch.randn_like(o) * 1e-4 for o in outs]
+torch.cuda.synchronize()
+
+
+def fbwd():
+    with torch.cuda.stream(sA):
+        torch.autograd.backward(list(outs), gouts, retain_graph=True)
+
+
+for _ in range(3):
+    fbwd()
+torch.cuda.synchronize()
+print("backward alone %.4f ms; backward then knn %.4f; knn then backward %.4f ms" % (timed([fbwd]), timed([fbwd, knn]), timed([knn, fbwd])))
+gb, gbk, gkb = graph_of([fbwd]), graph_of([fbwd, knn]), graph_of([knn, fbwd])
+print("graphs: backward %.4f, backward+knn %.4f, knn+backward %.4f ms" % (timed_graph(gb), timed_graph(gbk), timed_graph(gkb)))
+
 gf, gk, gfk, gkf = graph_of([field]), graph_of([knn]), graph_of([field, knn]), graph_of([knn, field])
 print("graphs: field %.4f, chamfer fwd %.4f, field+knn %.4f, knn+field %.4f ms" % (timed_graph(gf), timed_graph(gk), timed_graph(gfk), timed_graph(gkf)))
