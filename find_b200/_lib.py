@@ -26,6 +26,7 @@ SIGNATURES = {
     "findb200_version": (c_char_p, []),
     "findb200_knn_workspace_bytes": (c_size_t, [c_int, c_int, c_int]),
     "findb200_knn1": (c_int, [c_void_p] * 4 + [c_int] * 3 + [c_void_p] * 3 + [c_size_t, c_void_p]),
+    "findb200_knn1_static": (c_int, [c_void_p] * 4 + [c_int] * 3 + [c_void_p] * 3),
     "findb200_knn1_backward": (c_int, [c_void_p] * 6 + [c_int] * 3 + [c_void_p] * 3),
     "findb200_chamfer_forward": (c_int, [c_void_p] * 4 + [c_int] * 3 + [c_void_p] * 6 + [c_size_t, c_void_p]),
     "findb200_field_workspace_bytes": (c_size_t, [c_int] * 4),

@@ -952,3 +952,44 @@ int findb200_chamfer_backward(const float* x, const float* y, const int64_t* x_l
 }
 
 }  // extern "C"
+
+// ---- knn1 without a caller-provided workspace and without any allocation ------------------------------------------------
+// For callers that cannot allocate (CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc): the scratch of
+// findb200_knn1 (sorted clouds, permutations, chunk boxes, histogram, keys, work queue) lives in ONE file-scope device array of
+// FINDB200_KNN1_STATIC_MAX_BYTES that every GPU loading the library holds until the process exits.  All calls share it and it
+// keeps the last call's contents: run_knn clears what has to start from zero (work queue, statistics, histograms, bounding-box
+// cells) on every call, everything else is fully rewritten before it is read.  Calls that overlap on the GPU (two streams, two
+// host threads) race on it: serialise them.
+static __device__ __align__(256) unsigned char g_knn1_static_ws[FINDB200_KNN1_STATIC_MAX_BYTES];
+
+// The array's name is a host-side stand-in in host code, not a device address: it is resolved once per device, with that device
+// current, and the resolved pointer is what the kernels get.
+static int knn1_static_ws(void** out) {
+    constexpr int kMaxDev = 64;
+    static void* addr[kMaxDev];
+    int dev = 0;
+    FB_CUDA(cudaGetDevice(&dev));
+    FB_REQUIRE(dev >= 0 && dev < kMaxDev, FINDB200_ERR_UNSUPPORTED, "knn1_static: device ordinal %d out of range", dev);
+    if (!addr[dev]) {
+        void* p = nullptr;
+        FB_CUDA(cudaGetSymbolAddress(&p, g_knn1_static_ws));
+        FB_REQUIRE(p != nullptr, FINDB200_ERR_CUDA, "knn1_static: the static workspace has no device address");
+        addr[dev] = p;
+    }
+    *out = addr[dev];
+    return 0;
+}
+
+extern "C" int findb200_knn1_static(const float* p1, const float* p2, const int64_t* len1, const int64_t* len2, int N, int P1,
+                                    int P2, float* dists, int64_t* idx, void* stream) {
+    FB_REQUIRE(N >= 0 && P1 >= 0 && P2 >= 0, FINDB200_ERR_SHAPE, "knn1_static: negative size N=%d P1=%d P2=%d", N, P1, P2);
+    const size_t need = fb::chamfer::carve(nullptr, N, P1, P2).bytes;
+    FB_REQUIRE(need <= (size_t)FINDB200_KNN1_STATIC_MAX_BYTES, FINDB200_ERR_WORKSPACE,
+               "knn1_static: N=%d P1=%d P2=%d needs %zu bytes of scratch, the static workspace holds %zu "
+               "(FINDB200_KNN1_STATIC_MAX_BYTES); use findb200_knn1 with a caller-provided workspace",
+               N, P1, P2, need, (size_t)FINDB200_KNN1_STATIC_MAX_BYTES);
+    void* ws = nullptr;
+    const int rc = knn1_static_ws(&ws);
+    if (rc) return rc;
+    return findb200_knn1(p1, p2, len1, len2, N, P1, P2, dists, idx, ws, (size_t)FINDB200_KNN1_STATIC_MAX_BYTES, stream);
+}

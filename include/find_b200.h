@@ -43,6 +43,17 @@ size_t findb200_knn_workspace_bytes(int N, int P1, int P2);
 int findb200_knn1(const float* p1, const float* p2, const int64_t* len1, const int64_t* len2, int N, int P1, int P2,
                   float* dists, int64_t* idx, void* workspace, size_t workspace_bytes, void* stream);
 
+/* findb200_knn1 for callers that cannot allocate or provide a workspace (CUDA graph capture, tight serving loops, harnesses
+ * that forbid cudaMalloc).  No counterpart in the reference.  Same inputs,
+ * outputs and results as findb200_knn1; the scratch is a static device array of FINDB200_KNN1_STATIC_MAX_BYTES inside the
+ * library (held by every GPU that loads it until the process exits), and the call performs no cudaMalloc / cudaFree and calls
+ * no allocating routine.  Sizes whose findb200_knn_workspace_bytes(N, P1, P2) exceeds the limit are rejected with
+ * FINDB200_ERR_WORKSPACE (8 MiB covers 8 clouds of 10 242 x 10 000 points or one of 50 000 x 100 000).  All calls share the
+ * array: calls that overlap on the GPU (different streams or host threads) race — serialise them. */
+#define FINDB200_KNN1_STATIC_MAX_BYTES (8u << 20)
+int findb200_knn1_static(const float* p1, const float* p2, const int64_t* len1, const int64_t* len2, int N, int P1, int P2,
+                         float* dists, int64_t* idx, void* stream);
+
 /* autograd backward of the above: grad_p1 [N,P1,3], grad_p2 [N,P2,3] (both fully overwritten) */
 int findb200_knn1_backward(const float* p1, const float* p2, const int64_t* len1, const int64_t* len2,
                            const int64_t* idx, const float* grad_dists, int N, int P1, int P2, float* grad_p1,
