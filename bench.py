@@ -353,11 +353,20 @@ def run_ours(args, wl, rank, world, local_rank):
     late = next((k for k in kernels if k["name"] == "dw_gemms_late"), None)
     if late is not None:
         span = sum(k["ms_per_step"] for k in kernels if k["name"] in ("sum_feet", "trunk_bwd", "dw_gemms_late"))
-        kernels.append(dict(name="dw_gemms", launches_per_step=1.0, ms_per_step=span, overlapped=True,
-                            note="early launch (side stream, unmarked) + late launch; ms = span from the fork to the join = "
-                                 "sum_feet + trunk_bwd + dw_gemms_late marks, which run beside it and are listed on their own: "
-                                 "shares of the overlapped entries sum to more than the step"))
-        launches += 1
+        merged = dict(name="dw_gemms", launches_per_step=1.0, ms_per_step=span, overlapped=True,
+                      note="one plan = two launches (side:dw_gemms_early + dw_gemms_late, listed on their own and counted in "
+                           "gpu_launches there); ms = span from the fork to the join = sum_feet + trunk_bwd + dw_gemms_late marks, "
+                           "which run beside the early launch: shares of the overlapped entries sum to more than the step")
+        early = next((k for k in kernels if k["name"] == "side:dw_gemms_early"), None)
+        if early is not None:
+            # SM-time of the plan: the early launch holds n_early SMs, the late one the rest (csrc/field.cu: n_early = the SMs the
+            # trunk chain's CTA pairs leave free, even) — the duration the same SM-seconds would take on the whole GPU
+            sms = torch.cuda.get_device_properties(device).multi_processor_count
+            n_early = (sms - 2 * ((V + 255) // 256)) & ~1
+            merged["early_ms"], merged["late_ms"], merged["early_ctas"], merged["late_ctas"] = (
+                early["ms_per_step"], late["ms_per_step"], n_early, sms - n_early)
+            merged["sm_time_ms"] = (n_early * early["ms_per_step"] + (sms - n_early) * late["ms_per_step"]) / sms
+        kernels.append(merged)
     fp32_peak = None
     try:
         scratch = torch.zeros(16, device=device)
@@ -436,6 +445,16 @@ def run_ours(args, wl, rank, world, local_rank):
                             design_traffic_hbm_frac=round(dom["hbm_frac"], 4),
                             design_traffic_note="bytes of the saved fp16 tile images this design streams through the dW launch "
                                                 "(not algorithmic I/O); HBM peak = " + str(peaks["hbm_gbs"]) + " GB/s measured")
+        if dom.get("sm_time_ms"):
+            # the plan shares the GPU with sum_feet / trunk_bwd during its span: `frac` above charges it the whole span on the
+            # whole GPU; these charge it the SM-time it really holds (early CTAs x early duration + late CTAs x late duration)
+            r = dom["ms_per_step"] / dom["sm_time_ms"]
+            roofline.update(overlapped_with=["sum_feet", "trunk_bwd"], sm_time_ms=round(dom["sm_time_ms"], 4),
+                            early_launch_ms=round(dom["early_ms"], 4), late_launch_ms=round(dom["late_ms"], 4),
+                            early_ctas=dom["early_ctas"], late_ctas=dom["late_ctas"],
+                            frac_on_sm_time=round(dom["frac"] * r, 4) if dom["frac"] else None)
+            if dom.get("hbm_frac") is not None:
+                roofline["design_traffic_hbm_frac_on_sm_time"] = round(dom["hbm_frac"] * r, 4)
 
     out = {
         "metric": METRIC, "value": fv_global / (ms_per_step * 1e-3), "unit": UNIT, "n_gpus": world,

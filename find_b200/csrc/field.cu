@@ -890,6 +890,7 @@ int findb200_field_backward(const findb200_field_params* p, const float* pos, in
         D.cta_base = 0;
         rc = launch_dw(D, n_early, side, true);
         if (rc) return rc;
+        FB_MARK_END(side);
         FB_CUDA(cudaEventRecord(ev_join, side));
     }
     if (!frozen) {

@@ -169,9 +169,9 @@ int launch_dw(const DwParams& P, int n_ctas, cudaStream_t st, bool tpc_pairs) {
         FB_CUDA(cudaFuncSetAttribute(dw_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
         attr_set = true;
     }
-    // launch profiler: with the early / late split the early launch (side stream) is not marked; the late mark is named apart so
-    // that a reader of the marks knows that the dW kernel's span starts at the fork (the sum_feet mark), see bench.py
-    if (!tpc_pairs) FB_MARK(P.cta_base > 0 ? "dw_gemms_late" : "dw_gemms", st);
+    // launch profiler: the early launch (side stream) and the late one are named apart; the dW plan's span runs from the fork
+    // (the sum_feet mark of the main stream) to the end of the late launch, see bench.py
+    FB_MARK(tpc_pairs ? "dw_gemms_early" : (P.cta_base > 0 ? "dw_gemms_late" : "dw_gemms"), st);
     if (tpc_pairs) {
         // the early launch runs beside the trunk's CTA-pair kernel: launched as 2-CTA clusters its CTAs fill whole TPCs and leave
         // whole TPCs free for the pairs (the kernel itself makes no use of the cluster)
