@@ -74,6 +74,7 @@ SIGNATURES = {
     "findb200_phong_shade": (c_int, [c_void_p] * 4 + [c_int] * 4 + [c_void_p] * 4 + [c_int] + [c_void_p] * 4),
     "findb200_phong_shade_backward": (c_int, [c_void_p] * 5 + [c_int] * 4 + [c_void_p] * 5 + [c_int] + [c_void_p] * 7),
     "findb200_vertex_normals_backward": (c_int, [c_void_p, c_int, c_int] + [c_void_p] * 8),
+    "findb200_points_render": (c_int, [c_void_p, c_void_p] + [c_int] * 5 + [c_float, c_int, c_void_p, c_void_p]),
     "findb200_feature_blend_forward": (c_int, [c_void_p, c_int, c_int, c_void_p] + [c_int] * 5 + [c_float, c_float, c_int, c_int] + [c_float] * 3 + [c_void_p] * 6 + [c_size_t, c_void_p]),
     "findb200_feature_blend_backward": (c_int, [c_void_p, c_void_p, c_int, c_int, c_void_p] + [c_int] * 5 + [c_float, c_float, c_int, c_int] + [c_float] * 3 + [c_void_p] * 9 + [c_size_t, c_void_p]),
     "findb200_adam_step": (c_int, [c_void_p, c_int] + [ctypes.c_double] * 5 + [c_void_p, c_void_p]),

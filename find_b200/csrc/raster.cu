@@ -1413,3 +1413,91 @@ extern "C" int findb200_vertex_normals_backward(const float* verts, int N, int V
     FB_MARK_END(st);
     return 0;
 }
+
+// ------------------------------------------------------------------------------------------------------------------------
+// Keypoint overlay: PyTorch3D's PointsRenderer (PointsRasterizer radius r, K points per pixel + AlphaCompositor) as used by
+// /root/reference/src/model/renderer.py:139-142, 365-373 (red discs at the keypoints, eval_3d.py:97).  Restated in
+// oracle/raster_oracle.py::render_points.  One thread per pixel walks the cloud's points (staged through shared memory, a few
+// dozen keypoints per cloud) and keeps the K candidates of smallest depth in a sorted register list (the earlier point on
+// ties), then composites them front to back.  Forward only: the overlay is a visualisation of given keypoints.
+namespace fb {
+namespace raster {
+constexpr int kPtsMaxK = 16, kPtsMaxC = 8, kPtsStage = 256;
+
+__global__ void __launch_bounds__(256) points_render_kernel(const float* __restrict__ pts, const float* __restrict__ feats, int P, int C,
+                                                            int H, int W, float r2, int K, float* __restrict__ image) {
+    fb::pdl_wait_trigger();
+    __shared__ float s_p[kPtsStage][3];
+    const int n = blockIdx.y;
+    const int pix = blockIdx.x * 256 + threadIdx.x;
+    const bool live = pix < H * W;
+    const int row = live ? pix / W : 0, col = live ? pix % W : 0;
+    const float cx = 1.f - __fdiv_rn((float)(2 * col + 1), (float)W), cy = 1.f - __fdiv_rn((float)(2 * row + 1), (float)H);
+    float kz[kPtsMaxK], kd[kPtsMaxK];
+    int ki[kPtsMaxK];
+    int cnt = 0;
+    for (int p0 = 0; p0 < P; p0 += kPtsStage) {
+        const int np = min(kPtsStage, P - p0);
+        __syncthreads();
+        for (int i = threadIdx.x; i < np * 3; i += 256) s_p[i / 3][i % 3] = pts[((size_t)n * P + p0) * 3 + i];
+        __syncthreads();
+        if (!live) continue;
+        for (int j = 0; j < np; ++j) {
+            const float z = s_p[j][2];
+            if (!(z >= 0.f)) continue;
+            const float dx = __fsub_rn(cx, s_p[j][0]), dy = __fsub_rn(cy, s_p[j][1]);
+            const float d2 = __fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy));
+            if (!(d2 < r2)) continue;
+            if (cnt == K && !(z < kz[K - 1])) continue;          // full and not nearer than the farthest kept (ties: the earlier stays)
+            int at = cnt < K ? cnt : K - 1;
+#pragma unroll
+            for (int s = kPtsMaxK - 1; s >= 1; --s)              // shift the entries behind the insertion point (z strictly larger)
+                if (s <= at && kz[s - 1] > z) { kz[s] = kz[s - 1]; kd[s] = kd[s - 1]; ki[s] = ki[s - 1]; at = s - 1; }
+            kz[at] = z; kd[at] = d2; ki[at] = p0 + j;
+            if (cnt < K) ++cnt;
+        }
+    }
+    if (!live) return;
+    float out[kPtsMaxC];
+#pragma unroll
+    for (int c = 0; c < kPtsMaxC; ++c) out[c] = 0.f;
+    float trans = 1.f;
+#pragma unroll
+    for (int s = 0; s < kPtsMaxK; ++s) {
+        if (s >= cnt) break;
+        const float w = __fsub_rn(1.f, __fdiv_rn(kd[s], r2));
+        const float tw = __fmul_rn(trans, w);
+        const float* f = feats + ((size_t)n * P + ki[s]) * C;
+#pragma unroll
+        for (int c = 0; c < kPtsMaxC; ++c)
+            if (c < C) out[c] = __fadd_rn(out[c], __fmul_rn(tw, f[c]));
+        trans = __fmul_rn(trans, __fsub_rn(1.f, w));
+    }
+    float* o = image + ((size_t)n * H * W + pix) * C;
+#pragma unroll
+    for (int c = 0; c < kPtsMaxC; ++c)
+        if (c < C) o[c] = out[c];
+}
+}  // namespace raster
+}  // namespace fb
+
+// image [N, H, W, C] <- points_ndc [N, P, 3] (NDC x, y, view-space depth), features [N, P, C]; radius in NDC units
+extern "C" int findb200_points_render(const float* points_ndc, const float* features, int N, int P, int C, int H, int W, float radius,
+                                      int points_per_pixel, float* image, void* stream) {
+    cudaStream_t st = (cudaStream_t)stream;
+    FB_REQUIRE(N >= 0 && P >= 0 && H >= 1 && W >= 1, FINDB200_ERR_SHAPE, "points_render: bad shape N=%d P=%d H=%d W=%d", N, P, H, W);
+    FB_REQUIRE(C >= 1 && C <= fb::raster::kPtsMaxC, FINDB200_ERR_UNSUPPORTED, "points_render: 1..%d feature channels, got %d",
+               fb::raster::kPtsMaxC, C);
+    FB_REQUIRE(points_per_pixel >= 1 && points_per_pixel <= fb::raster::kPtsMaxK, FINDB200_ERR_UNSUPPORTED,
+               "points_render: 1..%d points per pixel, got %d", fb::raster::kPtsMaxK, points_per_pixel);
+    FB_REQUIRE(radius > 0.f, FINDB200_ERR_ARG, "points_render: radius must be positive");
+    FB_REQUIRE(image && (P == 0 || (points_ndc && features)), FINDB200_ERR_ARG, "points_render: null argument");
+    if (N == 0) return 0;
+    const float r2 = (float)((double)radius * (double)radius);
+    FB_MARK("points_render", st);
+    FB_CUDA(launch_pdl(fb::raster::points_render_kernel, dim3((unsigned)((H * W + 255) / 256), (unsigned)N), dim3(256), 0, st, points_ndc,
+                       features, P, C, H, W, r2, points_per_pixel, image));
+    FB_CUDA(cudaGetLastError());
+    FB_MARK_END(st);
+    return 0;
+}

@@ -215,6 +215,25 @@ class _FeatureRender(torch.autograd.Function):
         return g_ndc, g_feat, None, None, None, None, None, None, None, None, None, None, None
 
 
+def render_points(points_ndc: torch.Tensor, features: torch.Tensor, image_size, radius: float = 0.03, points_per_pixel: int = 10):
+    """PyTorch3D's ``PointsRenderer(PointsRasterizer(radius, points_per_pixel), AlphaCompositor())`` as FIND sets it up for its
+    keypoint overlay (/root/reference/src/model/renderer.py:139-142): points_ndc [N,P,3] (NDC x, y, view depth), features [N,P,C]
+    -> image [N,H,W,C], zero where no point lands.  Forward only (a visualisation)."""
+    H, W = (image_size, image_size) if isinstance(image_size, int) else image_size
+    dev = _lib.require_cuda(points_ndc)
+    pts = points_ndc.detach().to(torch.float32).contiguous()
+    f = features.detach().to(dev, torch.float32).contiguous()
+    N, P, C = f.shape
+    if pts.shape != (N, P, 3):
+        raise ValueError(f"points_ndc {tuple(pts.shape)} does not match features {tuple(f.shape)}")
+    image = torch.empty((N, int(H), int(W), C), dtype=torch.float32, device=dev)
+    with torch.cuda.device(dev):
+        rc = _lib.load().findb200_points_render(_lib.ptr(pts), _lib.ptr(f), N, P, C, int(H), int(W), float(radius), int(points_per_pixel),
+                                                _lib.ptr(image), _lib.stream_ptr(dev))
+    _lib.check(rc, "findb200_points_render")
+    return image
+
+
 def render_features(verts_ndc: torch.Tensor, faces: torch.Tensor, features: torch.Tensor, image_size, num_views: int = 1,
                     blur_radius: float = None, sigma: float = SIGMA, gamma: float = 1e-4, faces_per_pixel: int = 100,
                     perspective_correct: bool = True, znear: float = 1.0, zfar: float = 100.0):
@@ -301,6 +320,7 @@ class FootRenderer(nn.Module):
         self.background_color = tuple(float(c) for c in background_color)
         self.light_location = (0.0, 0.0, 100.0)                      # PointLights(location=[[0, 0, 100]]), renderer.py:111
         self.light_ambient, self.light_diffuse, self.light_specular, self.shininess = 0.5, 0.3, 0.2, 64.0   # PyTorch3D defaults
+        self.points_radius, self.points_per_pixel = 0.03, 10         # PointsRasterizationSettings of the keypoint overlay, renderer.py:139
 
     # ---- view helpers (host-side numpy / torch, as in the reference) ---------------------------------------------------
     def sample_views(self, nviews=1, dist_mean=0.25, dist_std=0.05, elev_min=-90, elev_max=90, azim_min=0, azim_max=360,
@@ -357,7 +377,31 @@ class FootRenderer(nn.Module):
             raise NotImplementedError("find_b200.renderer: return_depth cannot run in the reference either (renderer.py:296-301 reads "
                                       "`fragments.zbuf` of a dict); the nearest depth is rasterize_nearest(...)[1] / rasterize_silhouette(..., return_fragments=True)[2]")
         if keypoints is not None:
-            raise NotImplementedError("find_b200.renderer: the keypoint point-cloud overlay (a debug visualisation, renderer.py:367-377) is not built")
+            # renderer.py:365-377: the scene without the overlay, then red discs at the keypoints (PointsRenderer, radius 0.03,
+            # 10 points per pixel, AlphaCompositor) and, with keypoints_blend, the discs pasted over the image
+            out = self.forward(input_meshes, R, T, return_images=return_images, return_mask=return_mask, mask_with_grad=mask_with_grad,
+                               mask_out_faces=mask_out_faces, masked_faces=masked_faces, lights=lights,
+                               return_mask_out_masks=return_mask_out_masks, return_features=return_features, features=features)
+            num_views, num_meshes = R.shape[0], len(input_meshes)
+            if keypoints.dim() != 3 or keypoints.shape[0] != num_meshes or keypoints.shape[-1] != 3:
+                # the reference's own stacking over the views (renderer.py:367) is computed and discarded, so it only runs with one
+                # keypoint cloud per camera; here a cloud per MESH is drawn in every view of that mesh, which is what that line is for
+                raise ValueError(f"keypoints must be [num_meshes = {num_meshes}, K, 3], got {tuple(keypoints.shape)}")
+            dev = _lib.require_cuda(input_meshes.verts_padded())
+            kp = keypoints.detach().to(dev, torch.float32)
+            feats = torch.zeros_like(kp)
+            feats[..., 0] = 1.0
+            pcl = render_points(self.project(kp, R, T), feats.repeat_interleave(num_views, dim=0), self.image_size,
+                                radius=self.points_radius, points_per_pixel=self.points_per_pixel)
+            S = self.image_size
+            pcl = pcl.reshape(num_meshes, num_views, S, S, 3)
+            out["keypoints"] = pcl
+            if keypoints_blend:
+                if not return_images:
+                    raise ValueError("keypoints_blend pastes the keypoints over out['image']: it needs return_images=True")
+                pcl_mask = torch.any(pcl > 0, dim=-1, keepdim=True)
+                out["keypoints_blend"] = (~pcl_mask) * out["image"].clone() + pcl_mask * pcl
+            return out
         if return_features and features is None:
             raise AssertionError("Requires features to be passed for rendering")        # renderer.py:278
         if mask_out_faces and masked_faces is None:

@@ -272,6 +272,14 @@ int findb200_vertex_normals_backward(const float* verts, int N, int V, const int
                                      const int32_t* vf_face, const int32_t* vf_corner, const float* grad_normals, float* scratch,
                                      float* grad_verts, void* stream);
 
+/* Keypoint overlay (FootRenderer.forward(keypoints=...), /root/reference/src/model/renderer.py:139-142, 365-373; call site
+ * src/eval/eval_3d.py:97): PyTorch3D's PointsRenderer — PointsRasterizer(radius, points_per_pixel) + AlphaCompositor without a
+ * background.  points_ndc [N, P, 3] = NDC x, y and view-space depth (FootRenderer.project), features [N, P, C], C <= 8,
+ * points_per_pixel <= 16 -> image [N, H, W, C].  A point covers the pixels whose centre is closer than `radius` (NDC units) and
+ * has depth >= 0; the nearest `points_per_pixel` are composited front to back with weight 1 - d^2 / radius^2.  Forward only. */
+int findb200_points_render(const float* points_ndc, const float* features, int N, int P, int C, int H, int W, float radius,
+                           int points_per_pixel, float* image, void* stream);
+
 /* FeatureShader (renderer.py:74-105) = the reference's own softmax_blend (renderer.py:23-72, default znear = 1, zfar = 100) over the
  * fragments of a findb200_silhouette_forward call: per-vertex features [M, V, C] (M = N / num_views) interpolated with the clipped
  * barycentrics of each kept face and blended with weights sigmoid(-dist / sigma) * exp((zinv - max zinv) / gamma).  `ws`, `sel`,

@@ -277,3 +277,42 @@ def feature_blend(verts_ndc: torch.Tensor, faces: torch.Tensor, features: torch.
     texel = u0[..., None] * ff[None, :, 0] + u1[..., None] * ff[None, :, 1] + u2[..., None] * ff[None, :, 2]   # [P,F,C]
     out = ((wnum[..., None] * texel).sum(1) + delta * bg) / denom
     return out.reshape(H, W, C)
+
+
+def render_points(points_ndc: torch.Tensor, features: torch.Tensor, H: int, W: int, radius: float = 0.03,
+                  points_per_pixel: int = 10) -> torch.Tensor:
+    """The keypoint overlay of /root/reference/src/model/renderer.py:139-142, 365-373: PyTorch3D's ``PointsRenderer`` with
+    ``PointsRasterizationSettings(radius=0.03, points_per_pixel=10)`` and ``AlphaCompositor`` (no background colour).
+    Restated from PyTorch3D @ 1706eb82's published algorithm (renderer/points/rasterize_points.{py,cu}, renderer.py,
+    compositing.py; the package is not on this box, so this function is UNPINNED like the rest of the file):
+
+      * a point (x, y, z) — NDC x, y and view-space depth — is a candidate of the pixel with NDC centre (cx, cy) when z >= 0 and
+        d2 = (cx - x)^2 + (cy - y)^2 < radius^2;
+      * the ``points_per_pixel`` candidates of smallest z are kept, sorted by z (the earlier point on ties);
+      * weight w = 1 - d2 / radius^2; front to back: out += T * w * feature, T *= (1 - w), T starting at 1.
+
+    points_ndc [P, 3], features [P, C] -> [H, W, C] (zero where no point lands)."""
+    P, C = features.shape
+    xs, ys = pixel_centres(H, W, points_ndc.dtype)
+    cx = xs[None, :].expand(H, W)
+    cy = ys[:, None].expand(H, W)
+    out = torch.zeros(H, W, C, dtype=points_ndc.dtype)
+    if P == 0:
+        return out
+    dx = cx[..., None] - points_ndc[:, 0]
+    dy = cy[..., None] - points_ndc[:, 1]
+    d2 = dx * dx + dy * dy                                            # [H, W, P]
+    z = points_ndc[:, 2].expand(H, W, P)
+    cand = (z >= 0) & (d2 < radius * radius)
+    zkey = torch.where(cand, z, torch.full_like(z, float("inf")))
+    order = torch.sort(zkey, dim=-1, stable=True).indices             # stable: the earlier point on ties
+    K = min(points_per_pixel, P)
+    trans = torch.ones(H, W, dtype=points_ndc.dtype)
+    for k in range(K):
+        idx = order[..., k]
+        ok = torch.gather(cand, -1, idx[..., None])[..., 0]
+        w = 1.0 - torch.gather(d2, -1, idx[..., None])[..., 0] / (radius * radius)
+        w = torch.where(ok, w, torch.zeros_like(w))
+        out = out + (trans * w)[..., None] * features[idx]
+        trans = trans * (1.0 - w)
+    return out

@@ -189,3 +189,25 @@ def test_feature_blend_known_answers():
     fe = torch.cat([torch.zeros(3, 1, dtype=torch.float64), torch.ones(3, 1, dtype=torch.float64)])
     sharp = ro.feature_blend(v, f, fe, 4, 4, sigma=0.1, gamma=1e-4, blur_radius=1.0)
     assert abs(float(sharp[r, c, 0]) - 1.0) < 1e-6
+
+
+def test_render_points_known_answers():
+    """renderer.py:139-142, 365-373 (PointsRenderer + AlphaCompositor): disc weights 1 - d^2 / r^2, front-to-back compositing by
+    depth, points behind the camera dropped, K truncation keeps the nearest, the earlier point wins a depth tie."""
+    H = W = 8
+    r = 0.3
+    red, green, blue = torch.eye(3)
+    # pixel (3, 3) has its centre at (0.125, 0.125): d^2 = 2 * 0.125^2 to a point at the origin
+    w = 1.0 - 2 * 0.125 ** 2 / r ** 2
+    pts = torch.tensor([[0.0, 0.0, 0.3], [0.0, 0.0, 0.2], [0.0, 0.0, -0.1]])
+    img = ro.render_points(pts, torch.stack([red, green, blue]), H, W, radius=r)
+    assert torch.allclose(img[3, 3], torch.tensor([(1 - w) * w, w, 0.0]), atol=1e-6)      # green (nearer) first, blue is behind
+    assert float(img[0, 0].abs().sum()) == 0.0                                          # outside every disc: zeros
+    # K = 1 keeps only the nearest point
+    img1 = ro.render_points(pts, torch.stack([red, green, blue]), H, W, radius=r, points_per_pixel=1)
+    assert torch.allclose(img1[3, 3], torch.tensor([0.0, w, 0.0]), atol=1e-6)
+    # equal depths: the earlier point is composited first
+    tie = torch.tensor([[0.0, 0.0, 0.2], [0.0, 0.0, 0.2]])
+    imgt = ro.render_points(tie, torch.stack([red, green]), H, W, radius=r)
+    assert torch.allclose(imgt[3, 3], torch.tensor([w, (1 - w) * w, 0.0]), atol=1e-6)
+    assert ro.render_points(torch.zeros(0, 3), torch.zeros(0, 3), 4, 4).abs().sum() == 0

@@ -35,9 +35,7 @@ def test_camera_helpers_match_the_oracle_cpu():
     m = Meshes(tv[None], torch.zeros(1, 3, dtype=torch.int64))
     with pytest.raises(AssertionError):          # renderer.py:278: features must come with return_features
         r(m, R, T, return_features=True)
-    with pytest.raises(NotImplementedError):     # the debug overlays are not built and say so
-        r(m, R, T, keypoints=torch.zeros(1, 4, 3))
-    with pytest.raises(NotImplementedError):
+    with pytest.raises(NotImplementedError):     # renderer.py:296-301 cannot run in the reference either; refused with the reason
         r(m, R, T, return_depth=True)
 
 
@@ -338,3 +336,58 @@ def test_feature_render_matches_oracle_forward_and_backward(K):
     assert float(out["features"][out["mask_out_masks"]].abs().max()) == 0.0
     out["features"].sum().backward()
     assert torch.isfinite(vg.grad).all() and float(vg.grad.abs().max()) > 0
+
+
+@pytest.mark.gpu
+def test_points_render_matches_oracle():
+    """findb200_points_render (the keypoint overlay's PointsRenderer) against oracle/raster_oracle.py::render_points: clouds with
+    overlapping discs, depth ties, points behind the camera and more than K points over one pixel."""
+    from find_b200.renderer import render_points
+    dev = torch.device("cuda")
+    g = torch.Generator().manual_seed(3)
+    for (N, P, C, S, radius, K) in [(3, 40, 3, 64, 0.15, 10), (2, 300, 5, 48, 0.3, 4), (1, 1, 3, 32, 0.03, 10), (2, 17, 1, (40, 24), 0.2, 16)]:
+        pts = torch.rand(N, P, 3, generator=g) * torch.tensor([2.0, 2.0, 0.5]) - torch.tensor([1.0, 1.0, 0.1])   # some z < 0
+        pts[:, ::5, 2] = 0.25                                           # depth ties
+        if P > 8:
+            pts[:, 1] = pts[:, 0]                                       # a coincident pair: same disc, same depth
+        feats = torch.rand(N, P, C, generator=g)
+        img = render_points(pts.to(dev), feats.to(dev), S, radius=radius, points_per_pixel=K).cpu()
+        H, W = (S, S) if isinstance(S, int) else S
+        assert img.shape == (N, H, W, C)
+        for n in range(N):
+            ref = ro.render_points(pts[n], feats[n], H, W, radius=radius, points_per_pixel=K)
+            assert float((img[n] - ref).abs().max()) < 2e-6, (N, P, C, S, n)
+        assert float(img.abs().max()) > 0
+    # nothing to draw
+    assert float(render_points(torch.zeros(2, 0, 3, device=dev), torch.zeros(2, 0, 3, device=dev), 16).abs().sum()) == 0
+
+
+@pytest.mark.gpu
+def test_foot_renderer_keypoint_overlay():
+    """FootRenderer.forward(keypoints=..., keypoints_blend=True) (renderer.py:365-377, call site eval_3d.py:97): red discs at the
+    projected keypoints, pasted over the image where they land; the overlay equals the oracle's point render of the projected
+    keypoints per (mesh, view)."""
+    dev = torch.device("cuda")
+    tv, tf = syn.make_template(642)
+    B, S = 2, 64
+    verts = torch.stack([tv, tv * 1.05]).to(dev)
+    cols = torch.rand(B, tv.shape[0], 3, generator=torch.Generator().manual_seed(1)).to(dev)
+    r = FootRenderer(S, device=dev)
+    R, T = r.view_from(["topdown", "side1"])
+    kps = verts[:, ::80].contiguous()                                   # 9 keypoints per mesh, on the surface
+    out = r(Meshes(verts, tf.to(dev), textures=cols), R, T, return_images=True, keypoints=kps, keypoints_blend=True)
+    assert out["keypoints"].shape == (B, 2, S, S, 3) and out["keypoints_blend"].shape == (B, 2, S, S, 3)
+    ndc = r.project(kps, R, T).cpu()
+    feats = torch.zeros(kps.shape[1], 3)
+    feats[:, 0] = 1.0
+    for m in range(B):
+        for v in range(2):
+            ref = ro.render_points(ndc[m * 2 + v], feats, S, S, radius=0.03, points_per_pixel=10)
+            assert float((out["keypoints"][m, v].cpu() - ref).abs().max()) < 2e-6
+    kp = out["keypoints"]
+    on = (kp > 0).any(-1)
+    assert on.any() and not on.all()
+    assert torch.equal(out["keypoints_blend"][on], kp[on]) and torch.equal(out["keypoints_blend"][~on], out["image"][~on])
+    assert float(kp[..., 1:].abs().max()) == 0.0                         # red only
+    with pytest.raises(ValueError):
+        r(Meshes(verts, tf.to(dev), textures=cols), R, T, keypoints=kps[:1])
