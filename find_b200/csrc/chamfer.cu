@@ -644,7 +644,9 @@ static int launch_cull(CullParams& prm, int N, int P1, int P2, bool both, cudaSt
     prm.items_dir0 = N * prm.dir[0].n_groups;
     prm.total_items = prm.items_dir0 + (both ? N * prm.dir[1].n_groups : 0);
     int grid = (prm.total_items + 3) / 4;
-    const int cap = num_sms() * 8;
+    static int per_sm = -1;                 // CTAs (of 4 warps) per SM; the groups beyond are pulled from the queue
+    if (per_sm < 0) { const char* e = getenv("FINDB200_KNN_CTAS_PER_SM"); per_sm = e ? atoi(e) : 8; if (per_sm < 1) per_sm = 8; }
+    const int cap = num_sms() * per_sm;
     if (grid > cap) grid = cap;
     FB_MARK("knn_main", st);
     FB_CUDA(fb::launch_pdl(knn_cull_kernel<kQ>, grid, 128, 0, st, prm));
