@@ -290,7 +290,7 @@ def run_ours(args, wl, rank, world, local_rank):
     e2e_s = time.perf_counter() - t0
     barrier()
     e2e_s = max_over_ranks(e2e_s)
-    h2d = host["idx"].numel() * 8 + host["target"].numel() * 4 + host["col_target"].numel() * 4
+    h2d = host["idx"].numel() * 8 * 4 + host["target"].numel() * 4 + host["col_target"].numel() * 4
     clocks = sampler.stop() if rank == 0 else None
 
     # ---- (3) live per-kernel timing (library launch profiler, non-graph enqueue, L2 flushed between steps) -----
@@ -468,7 +468,7 @@ def run_ours(args, wl, rank, world, local_rank):
         "e2e": {"value": fv_global / (e2e_s / args.steps), "unit": UNIT, "h2d_bytes_per_step": h2d,
                 "d2h_bytes_per_step": 12, "ms_per_step": e2e_s / args.steps * 1e3,
                 "isolated_ms_per_step": iso_s * 1e3,
-                "api": "find_b200.step.TrainStep.iterate_from_host (pinned host -> H2D of batch k+1 on a copy stream while step k "
+                "api": "find_b200.step.TrainStep.iterate_from_host (pinned host -> H2D of batch k+1 on a copy stream, straight into the input set that step k does not read (one captured graph per set, no device-to-device copy), while step k "
                        "replays -> losses of every step copied D2H asynchronously and read one step later); isolated_ms_per_step = step_from_host with nothing overlapped, L2 flushed"},
         "gpu_launches": launches * args.steps,
         "gpu_launches_per_step": launches,

@@ -129,6 +129,7 @@ class ShardedTrainStep:
         self.world = dist.get_world_size(group) if dist.is_initialized() else 1
         self.weight = step.B / float(self.global_feet)
         self.graph: Optional[torch.cuda.CUDAGraph] = None
+        self._graphs = {}
         self.p2p: Optional[P2PAllReduce] = None
         self.collective = "none"
         if self.world > 1 and getattr(step, "mesh_terms", None) is not None:
@@ -189,8 +190,10 @@ class ShardedTrainStep:
             self._collective()
             return step.loss3
         with torch.cuda.device(step.dev):
-            if self.graph is None or (step._cache_key is not None and step._cache_key != step._current_cache_key()):
-                step._cache_key = None               # template changed: recompute the cached tiles, re-capture
+            if step.graphs_stale():                  # template changed: recompute the cached tiles, re-capture
+                self._graphs = {}
+            self.graph = self._graphs.get(step._cur)         # one graph per input set of the step (pipelined host feed)
+            if self.graph is None:
                 step._enqueue()                      # warm-up outside capture: function attributes, NCCL communicator
                 self._collective()
                 torch.cuda.synchronize(step.dev)
@@ -198,7 +201,7 @@ class ShardedTrainStep:
                 with torch.cuda.graph(g):
                     step._enqueue()
                     self._collective()
-                self.graph = g
+                self.graph = self._graphs[step._cur] = g
             self.graph.replay()
         return step.loss3
 

@@ -70,10 +70,11 @@ class TrainStep:
         # per-step inputs (static addresses).  One index row per table: tables with labels are indexed by batch[vec.key],
         # the others by batch['idx'] (sample_latent_vectors, trainer.py:29-46); load_inputs() fills all four from `idx`
         # unless told otherwise.
-        self.idx4 = torch.zeros(len(TABLE_KEYS), B, dtype=torch.int64, device=dev)
-        self.idx = self.idx4[0]                    # the batch['idx'] row (kept under its old name)
-        self.target = torch.zeros(B, self.P2, 3, **f32)
-        self.col_target = torch.zeros(B, V, 3, **f32) if with_colour else None
+        # Two input sets can exist (the second is created by prefetch_from_host): the pipelined host feed copies batch k+1
+        # straight into the set that step k is NOT reading, and every set has its own captured graph, so no device-to-device
+        # copy sits between the H2D and the step.  ``idx4`` / ``idx`` / ``target`` / ``col_target`` are the CURRENT set's.
+        self._sets = [self._new_input_set()]
+        self._cur = 0
         # gathered rows, outputs, gradients
         self.rows = {k: torch.zeros(B, t.data.shape[1], **f32) for k, t in self.tables.items() if t is not None}
         self.grows = {k: torch.zeros_like(v) for k, v in self.rows.items()}
@@ -112,12 +113,11 @@ class TrainStep:
             nbytes = int(self.lib.findb200_train_step_workspace_bytes(B, V, self.P2))
         self.ws = torch.empty(nbytes, dtype=torch.uint8, device=dev)
         self.kernel_launches = 0         # filled by the first enqueue (counted from the C ABI's launch list)
-        self.graph: Optional[torch.cuda.CUDAGraph] = None
+        self._graphs = [None, None]      # one captured step per input set
         self.use_graph = use_graph
         self._cparams = None
         self._cgrads = None
-        self._gather = None
-        self._scatter = None
+        self._jobs = [None, None]        # gather / scatter job tables per input set (they hold the index rows' addresses)
         self._cache_key = None           # what the cached tiles in the workspace were computed from
 
     # ---- the enqueue ---------------------------------------------------------------------------------------
@@ -141,11 +141,37 @@ class TrainStep:
                 cg.bias[i] = self.grad_views[N_PARAMS + i].data_ptr()
         return cp, cg
 
+    def _new_input_set(self):
+        f32 = dict(dtype=torch.float32, device=self.dev)
+        return dict(idx4=torch.zeros(len(TABLE_KEYS), self.B, dtype=torch.int64, device=self.dev),
+                    target=torch.zeros(self.B, self.P2, 3, **f32),
+                    col_target=torch.zeros(self.B, self.V, 3, **f32) if self.with_colour else None)
+
+    @property
+    def idx4(self):
+        return self._sets[self._cur]["idx4"]
+
+    @property
+    def idx(self):                                 # the batch['idx'] row (kept under its old name)
+        return self._sets[self._cur]["idx4"][0]
+
+    @property
+    def target(self):
+        return self._sets[self._cur]["target"]
+
+    @property
+    def col_target(self):
+        return self._sets[self._cur]["col_target"]
+
+    @property
+    def graph(self):
+        return self._graphs[self._cur]
+
     def _enqueue(self):
         lib, st = self.lib, _lib.stream_ptr(self.dev)
         if self._cparams is None:
             self._cparams, self._cgrads = self._structs()
-        if self._gather is None:
+        if self._jobs[self._cur] is None:
             live = [(k, t) for k, t in self.tables.items() if t is not None]
             jobs = (GatherJobC * len(live))()
             sjobs = (ScatterJobC * len(live))()
@@ -155,10 +181,10 @@ class TrainStep:
                 jobs[j].out, jobs[j].idx = self.rows[k].data_ptr(), irow
                 sjobs[j].g, sjobs[j].n_rows, sjobs[j].width = self.grows[k].data_ptr(), t.data.shape[0], t.data.shape[1]
                 sjobs[j].grad_table, sjobs[j].idx = self.table_grads[k].data_ptr(), irow
-            self._gather = (jobs, len(live))
-            self._scatter = (sjobs, len(live))
-        if self._gather[1]:
-            rc = lib.findb200_gather_rows_multi(self._gather[0], self._gather[1], _lib.ptr(self.idx), self.B, st)
+            self._jobs[self._cur] = ((jobs, len(live)), (sjobs, len(live)))
+        gather, scatter = self._jobs[self._cur]
+        if gather[1]:
+            rc = lib.findb200_gather_rows_multi(gather[0], gather[1], _lib.ptr(self.idx), self.B, st)
             _lib.check(rc, "findb200_gather_rows_multi")
         # Workspace caches (include/find_b200.h FINDB200_FIELD_*): the template never changes during training, so after the
         # first enqueue the Fourier-encoded tiles are reused; with a frozen MLP the whole trunk output is.  Any in-place
@@ -182,9 +208,9 @@ class TrainStep:
         else:
             rc = lib.findb200_train_step_mesh(*args, ctypes.byref(self.mesh_terms), _lib.ptr(self.ws), self.ws.numel(), st)
             _lib.check(rc, "findb200_train_step_mesh")
-        if self._scatter[1]:
+        if scatter[1]:
             # autograd of the gather (trainer.py:121): dense table gradients, part of the step (and of its CUDA graph)
-            rc = lib.findb200_scatter_rows_multi(self._scatter[0], self._scatter[1], _lib.ptr(self.idx), self.B, 0, st)
+            rc = lib.findb200_scatter_rows_multi(scatter[0], scatter[1], _lib.ptr(self.idx), self.B, 0, st)
             _lib.check(rc, "findb200_scatter_rows_multi")
         self._cache_key = key
 
@@ -200,18 +226,26 @@ class TrainStep:
         with torch.cuda.device(self.dev):
             if not self.use_graph:
                 self._enqueue()
-            elif self.graph is None or (self._cache_key is not None and self._cache_key != self._current_cache_key()):
-                self._cache_key = None               # template (or frozen weights) changed: recompute, then re-capture
+            elif self.graph is None or self.graphs_stale():
                 self._enqueue()                      # warm-up outside capture (sets function attributes)
                 torch.cuda.synchronize(self.dev)
                 g = torch.cuda.CUDAGraph()
                 with torch.cuda.graph(g):
                     self._enqueue()
-                self.graph = g
+                self._graphs[self._cur] = g
                 g.replay()
             else:
                 self.graph.replay()
         return self.loss3
+
+    def graphs_stale(self) -> bool:
+        """True (once) when the template — or the frozen weights — changed since the cached tiles were computed: every captured
+        graph is dropped and the next enqueue recomputes the caches."""
+        if self._cache_key is not None and self._cache_key != self._current_cache_key():
+            self._cache_key = None
+            self._graphs = [None, None]
+            return True
+        return False
 
     # ---- host-facing conveniences --------------------------------------------------------------------------
     def _check_rows(self, idx: torch.Tensor, key: str = "idx"):
@@ -267,8 +301,8 @@ class TrainStep:
         one ``step_prefetched()``; at most two batches may be staged ahead."""
         if getattr(self, "_copy_stream", None) is None:
             self._copy_stream = torch.cuda.Stream(device=self.dev)
-            self._stage = [dict(idx=torch.empty_like(self.idx), target=torch.empty_like(self.target),
-                                col_target=None if self.col_target is None else torch.empty_like(self.col_target)) for _ in range(2)]
+            if len(self._sets) < 2:
+                self._sets.append(self._new_input_set())
             self._ready = [torch.cuda.Event() for _ in range(2)]
             self._consumed = [torch.cuda.Event() for _ in range(2)]
             self._staged, self._stage_next = [], 0
@@ -276,10 +310,11 @@ class TrainStep:
             raise RuntimeError("prefetch_from_host: two batches are already staged; call step_prefetched() first")
         self._check_rows(idx)
         k = self._stage_next
-        st = self._stage[k]
+        st = self._sets[k]
         with torch.cuda.stream(self._copy_stream):
-            self._copy_stream.wait_event(self._consumed[k])          # the step that last used this set has copied it out
-            st["idx"].copy_(idx, non_blocking=True)
+            self._copy_stream.wait_event(self._consumed[k])          # the step that last read this set has finished
+            for r in range(len(TABLE_KEYS)):
+                st["idx4"][r].copy_(idx, non_blocking=True)
             st["target"].copy_(target, non_blocking=True)
             if st["col_target"] is not None and col_target is not None:
                 st["col_target"].copy_(col_target, non_blocking=True)
@@ -296,15 +331,11 @@ class TrainStep:
             self._loss_done = [torch.cuda.Event() for _ in range(2)]
             self._loss_next = 0
         k = self._staged.pop(0)
-        st = self._stage[k]
         cur = torch.cuda.current_stream(self.dev)
         cur.wait_event(self._ready[k])
-        self.idx4.copy_(st["idx"].unsqueeze(0).expand_as(self.idx4), non_blocking=True)   # device -> device into the graph's static inputs
-        self.target.copy_(st["target"], non_blocking=True)
-        if st["col_target"] is not None:
-            self.col_target.copy_(st["col_target"], non_blocking=True)
-        self._consumed[k].record(cur)
+        self._cur = k                                                # the step reads set k in place (its own captured graph)
         (runner or self).run()
+        self._consumed[k].record(cur)
         j = self._loss_next
         self._loss_host[j].copy_(self.loss3, non_blocking=True)
         self._loss_done[j].record(cur)
