@@ -226,7 +226,7 @@ class TrainStep:
         with torch.cuda.device(self.dev):
             if not self.use_graph:
                 self._enqueue()
-            elif self.graph is None or self.graphs_stale():
+            elif self.graphs_stale() or self.graph is None:      # (stale first: it drops the graphs of BOTH input sets)
                 self._enqueue()                      # warm-up outside capture (sets function attributes)
                 torch.cuda.synchronize(self.dev)
                 g = torch.cuda.CUDAGraph()
