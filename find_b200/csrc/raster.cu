@@ -726,47 +726,98 @@ __global__ void __launch_bounds__(kThreads, 2) feat_tile_bwd_kernel(const __grid
     const float* gout = Q.grad_out + o * Q.C;
     const float* outp = Q.out + o * Q.C;
     int seen = 0;
+    const int lane = tid & 31;
+    // Every lane of a warp sees the same face j at the same time (for_each_listed is warp-uniform), so the contributions of the
+    // warp's 32 pixels to that face's three vertices are summed in the warp before they go to memory: up to 3 C + 9 atomics per
+    // (warp, face) instead of per (pixel, face).  The 16-value halving butterfly below leaves value i of the 16 on the lanes
+    // whose upper four bits spell i (31 shuffles per 16 values instead of 80).
     auto scatter = [&](int j, const FaceRec& r, const Eval& e) {
-        if (!e.cand) return;
-        const uint32_t b = depth_bits(e.pz);
-        const bool keep = (sel.x == 0xffffffffu) || (b < sel.x) || (b == sel.x && seen++ < (int)sel.y);
-        if (!keep || !active) return;
-        const float prob = sigmoidf_((e.inside ? e.d2 : -e.d2) * inv_sigma);
-        const float E = expf(((Q.zfar - e.pz) / zr - zmax) / Q.gamma);
-        const float w = prob * E;
-        const float u[3] = {e.w[0] / e.wsum, e.w[1] / e.wsum, e.w[2] / e.wsum};
-        const int v0 = sh.vid[j][0], v1 = sh.vid[j][1], v2 = sh.vid[j][2];
-        const float *f0 = feat + (size_t)v0 * Q.C, *f1 = feat + (size_t)v1 * Q.C, *f2 = feat + (size_t)v2 * Q.C;
-        float gw = 0.f, g_u[3] = {0.f, 0.f, 0.f};
-        const float wd = w / den;
-        for (int c = 0; c < Q.C; ++c) {
-            const float a0 = __ldg(f0 + c), a1 = __ldg(f1 + c), a2 = __ldg(f2 + c);
-            const float g = gout[c];
-            gw += g * ((u[0] * a0 + u[1] * a1 + u[2] * a2) - outp[c]);
-            const float gf = g * wd;                                 // d/d(interpolated feature c)
-            g_u[0] += gf * a0; g_u[1] += gf * a1; g_u[2] += gf * a2;
-            if (gf != 0.f) {
-                atomicAdd(g_feat + (size_t)v0 * Q.C + c, u[0] * gf);
-                atomicAdd(g_feat + (size_t)v1 * Q.C + c, u[1] * gf);
-                atomicAdd(g_feat + (size_t)v2 * Q.C + c, u[2] * gf);
+        bool contributes = false;
+        float wd = 0.f, u[3] = {0.f, 0.f, 0.f};
+        float gnd[16];
+#pragma unroll
+        for (int i = 0; i < 16; ++i) gnd[i] = 0.f;
+        if (e.cand) {
+            const uint32_t b = depth_bits(e.pz);
+            const bool keep = (sel.x == 0xffffffffu) || (b < sel.x) || (b == sel.x && seen++ < (int)sel.y);
+            if (keep && active) {
+                contributes = true;
+                const float prob = sigmoidf_((e.inside ? e.d2 : -e.d2) * inv_sigma);
+                const float E = expf(((Q.zfar - e.pz) / zr - zmax) / Q.gamma);
+                const float w = prob * E;
+                u[0] = e.w[0] / e.wsum; u[1] = e.w[1] / e.wsum; u[2] = e.w[2] / e.wsum;
+                const int v0 = sh.vid[j][0], v1 = sh.vid[j][1], v2 = sh.vid[j][2];
+                const float *f0 = feat + (size_t)v0 * Q.C, *f1 = feat + (size_t)v1 * Q.C, *f2 = feat + (size_t)v2 * Q.C;
+                float gw = 0.f, g_u[3] = {0.f, 0.f, 0.f};
+                wd = w / den;
+                for (int c = 0; c < Q.C; ++c) {
+                    const float a0 = __ldg(f0 + c), a1 = __ldg(f1 + c), a2 = __ldg(f2 + c);
+                    const float g = gout[c];
+                    gw += g * ((u[0] * a0 + u[1] * a1 + u[2] * a2) - outp[c]);
+                    const float gf = g * wd;                                 // d/d(interpolated feature c)
+                    g_u[0] += gf * a0; g_u[1] += gf * a1; g_u[2] += gf * a2;
+                }
+                gw /= den;
+                // w = prob * E:  d/d(prob) = gw E;  d/d(zinv) = gw w / gamma (+ the max-zinv term on the nearest face)
+                const float g_prob = gw * E;
+                float g_zinv = gw * w / Q.gamma;
+                if (__float_as_int(r.pad0) == near && depth_bits(e.pz) == depth_bits(Q.zbuf[o])) g_zinv += g_zmax - 0.f;
+                // every kept candidate's exponent also holds -zmax: that part is inside g_zmax (collapsed sum), see above
+                const float g_z = -g_zinv / zr;
+                const float g_sd = g_prob * (-prob * (1.f - prob) * inv_sigma);      // prob = sigmoid(-sd / sigma)
+                float gX[3], gY[3], gZ[3];
+                face_geometry_bwd(r, px, py, P.perspective, 1, g_u, g_z, g_sd, gX, gY, gZ);
+#pragma unroll
+                for (int k = 0; k < 3; ++k) { gnd[3 * k] = gX[k]; gnd[3 * k + 1] = gY[k]; gnd[3 * k + 2] = gZ[k]; }
             }
         }
-        gw /= den;
-        // w = prob * E:  d/d(prob) = gw E;  d/d(zinv) = gw w / gamma (+ the max-zinv term on the nearest face)
-        const float g_prob = gw * E;
-        float g_zinv = gw * w / Q.gamma;
-        if (__float_as_int(r.pad0) == near && depth_bits(e.pz) == depth_bits(Q.zbuf[o])) g_zinv += g_zmax - 0.f;
-        // every kept candidate's exponent also holds -zmax: that part is inside g_zmax (collapsed sum), see above
-        const float g_z = -g_zinv / zr;
-        const float g_sd = g_prob * (-prob * (1.f - prob) * inv_sigma);      // prob = sigmoid(-sd / sigma)
-        float gX[3], gY[3], gZ[3];
-        face_geometry_bwd(r, px, py, P.perspective, 1, g_u, g_z, g_sd, gX, gY, gZ);
-        const int vv[3] = {v0, v1, v2};
+        if (__ballot_sync(0xffffffffu, contributes) == 0u) return;
+        const int vv[3] = {sh.vid[j][0], sh.vid[j][1], sh.vid[j][2]};
+        // v[0..15] of every lane -> the sum over the warp of v[idx], idx = lane >> 1, on both lanes of the pair
+        auto reduce16 = [&](float (&v)[16]) -> float {
 #pragma unroll
-        for (int k = 0; k < 3; ++k) {
-            if (gX[k] != 0.f) atomicAdd(g_ndc + (size_t)vv[k] * 3, gX[k]);
-            if (gY[k] != 0.f) atomicAdd(g_ndc + (size_t)vv[k] * 3 + 1, gY[k]);
-            if (gZ[k] != 0.f) atomicAdd(g_ndc + (size_t)vv[k] * 3 + 2, gZ[k]);
+            for (int i = 0; i < 8; ++i) {
+                const bool hi = lane & 16;
+                const float send = hi ? v[i] : v[i + 8], keepv = hi ? v[i + 8] : v[i];
+                v[i] = keepv + __shfl_xor_sync(0xffffffffu, send, 16);
+            }
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const bool hi = lane & 8;
+                const float send = hi ? v[i] : v[i + 4], keepv = hi ? v[i + 4] : v[i];
+                v[i] = keepv + __shfl_xor_sync(0xffffffffu, send, 8);
+            }
+#pragma unroll
+            for (int i = 0; i < 2; ++i) {
+                const bool hi = lane & 4;
+                const float send = hi ? v[i] : v[i + 2], keepv = hi ? v[i + 2] : v[i];
+                v[i] = keepv + __shfl_xor_sync(0xffffffffu, send, 4);
+            }
+            {
+                const bool hi = lane & 2;
+                const float send = hi ? v[0] : v[1], keepv = hi ? v[1] : v[0];
+                v[0] = keepv + __shfl_xor_sync(0xffffffffu, send, 2);
+            }
+            return v[0] + __shfl_xor_sync(0xffffffffu, v[0], 1);
+        };
+        const int idx = lane >> 1;
+        const bool writer = (lane & 1) == 0;
+        {
+            const float t = reduce16(gnd);                            // 9 of the 16: (vertex k, axis d) = idx / 3, idx % 3
+            if (writer && idx < 9 && t != 0.f) atomicAdd(g_ndc + (size_t)vv[idx / 3] * 3 + idx % 3, t);
+        }
+        for (int c0 = 0; c0 < Q.C; c0 += 16) {
+            float gf[16];
+#pragma unroll
+            for (int i = 0; i < 16; ++i) gf[i] = (contributes && c0 + i < Q.C) ? gout[c0 + i] * wd : 0.f;
+#pragma unroll
+            for (int k = 0; k < 3; ++k) {
+                float v[16];
+#pragma unroll
+                for (int i = 0; i < 16; ++i) v[i] = u[k] * gf[i];
+                const float t = reduce16(v);
+                if (writer && c0 + idx < Q.C && t != 0.f) atomicAdd(g_feat + (size_t)vv[k] * Q.C + c0 + idx, t);
+            }
         }
     };
     build_tile_list(P, n, txmin, txmax, tymin, tymax, sh, [&](int count) { for_each_listed<true>(P, n, count, px, py, blur, in_img, sh, scatter); });
