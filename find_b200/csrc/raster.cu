@@ -20,7 +20,10 @@
 //                         instantiation used for hard rasterisation, its barycentrics and signed distance.
 //   sil_tile_bwd_kernel   the same tile walk; d alpha / d d2_k = +-prod p_k / sigma needs only the saved product and selection.
 //                         Per face the 256 pixels' contributions are reduced in the warp before 6 atomics per (warp, face).
-//   vert_normals / phong_shade   Phong image of the hard fragments, forward only (end of this file).
+//   feat_tile_fwd / feat_tile_bwd   FeatureShader (the reference's softmax_blend over the silhouette fragments), same walk; the
+//                         backward sums a warp's contributions to a face with a halving butterfly before the atomics.
+//   vert_normals / phong_shade (+ _bwd)   Phong image of the hard fragments and its hand-differentiated backward.
+//   points_render_kernel  the keypoint overlay (PointsRenderer + AlphaCompositor), forward only (end of this file).
 // Bound: latency / issue (divergent point-triangle evaluations, ~18 of 32 lanes active; profiles/r1_silhouette.md); DRAM
 // traffic (the candidate store) is ~160 GB/s.
 #include "common.cuh"
