@@ -81,6 +81,7 @@ SIGNATURES = {
     "findb200_sgd_momentum_step": (c_int, [c_void_p, c_int] + [ctypes.c_double] * 3 + [c_void_p, c_void_p]),
     "findb200_allreduce_p2p_flag_bytes": (c_size_t, []),
     "findb200_allreduce_p2p": (c_int, [c_void_p, c_void_p, c_int, c_int, ctypes.c_longlong, c_float, c_void_p, c_int, c_void_p]),
+    "findb200_allreduce_mc": (c_int, [c_void_p, c_void_p, c_int, c_int, ctypes.c_longlong, c_float, c_void_p, c_int, c_void_p]),
     "findb200_train_step_knn_stats": (c_int, [c_void_p, c_int, c_int, c_int, c_void_p, c_void_p]),
     "findb200_set_sort_cta_max": (c_int, [c_int]),
     "findb200_set_step_overlap": (c_int, [c_int, c_float]),

@@ -34,6 +34,7 @@ struct P2PParams {
                                     //         [2] error code (0 ok, 1 a rank never arrived, 2 ranks out of lock-step), [3] culprit rank
     long long timeout_cycles;       // bound of one flag wait (FINDB200_P2P_TIMEOUT_S, default 600 s: rank skew of a checkpoint
                                     // save or a validation pass is ordinary; NCCL would simply wait)
+    float* mc;                      // multicast mapping of the bucket (NVLS variant), else null
 };
 
 FB_DEVINL void st_release_sys(uint32_t* p, uint32_t v) { asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory"); }
@@ -86,6 +87,51 @@ FB_DEVINL void cross_rank_barrier(const P2PParams& p, uint32_t epoch) {
         }
     }
     __syncthreads();
+}
+
+// NVLS variant: the bucket is also mapped through a multicast object.  multimem.ld_reduce returns the SUM of the addressed 16
+// bytes over every rank's copy, added inside the NVSwitch (one request per rank slice instead of W - 1 peer loads), and
+// multimem.st writes the scaled result into every rank's copy at once.  Same two barriers, same slice ownership: every element
+// is reduced by exactly one rank and broadcast, so all ranks still end with bit-identical buckets.
+FB_DEVINL float4 mc_ld_reduce(const float4* p) {
+    float4 v;
+    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
+                 : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p) : "memory");
+    return v;
+}
+FB_DEVINL void mc_st(float4* p, const float4& v) {
+    asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+
+__global__ void __launch_bounds__(256) allreduce_mc_kernel(const __grid_constant__ P2PParams p) {
+    const uint32_t e = *p.epoch;
+    cross_rank_barrier<false>(p, 2u * e + 1u);
+    const long long per = (p.n4 + p.world - 1) / p.world;
+    const long long lo = per * p.rank, hi = min(lo + per, p.n4);
+    constexpr int kUnroll = 4;
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    float4* mc = reinterpret_cast<float4*>(p.mc);
+    for (long long i0 = lo + (long long)blockIdx.x * blockDim.x + threadIdx.x; i0 < hi; i0 += stride * kUnroll) {
+        float4 v[kUnroll];
+#pragma unroll
+        for (int u = 0; u < kUnroll; ++u) {
+            const long long i = i0 + u * stride;
+            if (i < hi) v[u] = mc_ld_reduce(mc + i);
+        }
+#pragma unroll
+        for (int u = 0; u < kUnroll; ++u) {
+            const long long i = i0 + u * stride;
+            if (i >= hi) continue;
+            float4 a = v[u];
+            a.x *= p.scale; a.y *= p.scale; a.z *= p.scale; a.w *= p.scale;
+            mc_st(mc + i, a);
+        }
+    }
+    cross_rank_barrier<true>(p, 2u * e + 2u);
+    if (threadIdx.x == 0) {
+        __threadfence();
+        if (atomicAdd(p.epoch + 1, 1u) == gridDim.x - 1) { p.epoch[1] = 0u; p.epoch[0] = e + 1u; }
+    }
 }
 
 __global__ void __launch_bounds__(256) allreduce_p2p_kernel(const __grid_constant__ P2PParams p) {
@@ -172,6 +218,32 @@ extern "C" int findb200_allreduce_p2p(void* const* peer_bufs, void* const* peer_
     p.timeout_cycles = p2p_timeout_cycles();
     FB_MARK("allreduce_p2p", st);
     allreduce_p2p_kernel<<<n_ctas, 256, 0, st>>>(p);
+    FB_CUDA(cudaGetLastError());
+    FB_MARK_END(st);
+    return 0;
+}
+
+// Same contract as findb200_allreduce_p2p, with the reduction done inside the NVSwitch: mc_buf = the multicast mapping of the
+// bucket (torch symmetric memory: handle.multicast_ptr); peer_flags as above (the barriers are the same peer-memory flags).
+extern "C" int findb200_allreduce_mc(void* mc_buf, void* const* peer_flags, int rank, int world, long long n_floats, float scale,
+                                     unsigned int* epoch_dev, int n_ctas, void* stream) {
+    cudaStream_t st = (cudaStream_t)stream;
+    FB_REQUIRE(mc_buf && peer_flags && epoch_dev, FINDB200_ERR_ARG, "allreduce_mc: null argument");
+    FB_REQUIRE(world >= 1 && world <= kMaxRanks && rank >= 0 && rank < world, FINDB200_ERR_ARG, "allreduce_mc: bad rank/world %d/%d", rank, world);
+    FB_REQUIRE(n_floats >= 0 && (n_floats & 3) == 0, FINDB200_ERR_SHAPE, "allreduce_mc: the bucket length must be a multiple of 4 floats (pad it)");
+    FB_REQUIRE(((uintptr_t)mc_buf & 15) == 0, FINDB200_ERR_ARG, "allreduce_mc: the multicast pointer is not 16-byte aligned");
+    if (n_ctas < 1) n_ctas = 128;
+    if (n_ctas > kMaxCtas) n_ctas = kMaxCtas;
+    P2PParams p;
+    memset(&p, 0, sizeof(p));
+    for (int q = 0; q < world; ++q) {
+        FB_REQUIRE(peer_flags[q], FINDB200_ERR_ARG, "allreduce_mc: peer %d has no flag mapping", q);
+        p.flags[q] = (uint32_t*)peer_flags[q];
+    }
+    p.rank = rank; p.world = world; p.n4 = n_floats / 4; p.scale = scale; p.epoch = epoch_dev; p.mc = (float*)mc_buf;
+    p.timeout_cycles = p2p_timeout_cycles();
+    FB_MARK("allreduce_mc", st);
+    allreduce_mc_kernel<<<n_ctas, 256, 0, st>>>(p);
     FB_CUDA(cudaGetLastError());
     FB_MARK_END(st);
     return 0;

@@ -91,6 +91,9 @@ class P2PAllReduce:
             raise RuntimeError("symmetric-memory rendezvous did not map every peer")
         self._bufs = (ctypes.c_void_p * self.world)(*bp)
         self._flags = (ctypes.c_void_p * self.world)(*fp)
+        # NVLS: the bucket's multicast mapping, when the ranks share a multicast object (0 otherwise)
+        self.mc_ptr = int(getattr(self._h_buf, "multicast_ptr", 0) or 0)
+        self.use_mc = False                        # set by ShardedTrainStep once EVERY rank has a multicast mapping
         self.epoch = torch.zeros(4, dtype=torch.int32, device=device)   # [calls done, CTAs done, error code, culprit rank]
         self.bucket = self.buf[: self.n]
         dist.barrier(group)                       # every rank's flag page is zero before anyone signals
@@ -99,6 +102,12 @@ class P2PAllReduce:
     def enqueue(self, scale: float = 1.0):
         """bucket <- scale * sum over ranks (in place, on the current stream; graph-capturable)."""
         _lib = self._lib_mod
+        if self.use_mc:                            # the sum is taken inside the NVSwitch (csrc/allreduce.cu, allreduce_mc_kernel)
+            import ctypes
+            rc = self.lib.findb200_allreduce_mc(ctypes.c_void_p(self.mc_ptr), self._flags, self.rank, self.world, self.n_pad,
+                                                float(scale), _lib.ptr(self.epoch), self.n_ctas, _lib.stream_ptr(self.dev))
+            _lib.check(rc, "findb200_allreduce_mc")
+            return
         rc = self.lib.findb200_allreduce_p2p(self._bufs, self._flags, self.rank, self.world, self.n_pad, float(scale),
                                              _lib.ptr(self.epoch), self.n_ctas, _lib.stream_ptr(self.dev))
         _lib.check(rc, "findb200_allreduce_p2p")
@@ -121,8 +130,11 @@ class ShardedTrainStep:
     split is even), which reproduces the single-rank gradient of the concatenated batch."""
 
     def __init__(self, step, global_feet: int, group=None, collective: str = "auto"):
-        """``collective``: "p2p" = the library's own peer-memory allreduce kernel (csrc/allreduce.cu), "nccl" =
-        torch.distributed.all_reduce, "auto" = p2p when every rank can map its peers (symmetric memory), else nccl."""
+        """``collective``: "p2p" = the library's own peer-memory allreduce kernel (csrc/allreduce.cu), "nvls" = the same
+        exchange with the sum taken inside the NVSwitch (multimem.ld_reduce / multimem.st on the bucket's multicast mapping;
+        falls back to "p2p" when a rank has no multicast mapping), "nccl" = torch.distributed.all_reduce, "auto" = p2p when
+        every rank can map its peers (symmetric memory; nvls from 8 ranks on when every rank has the multicast mapping), else
+        nccl."""
         self.step = step
         self.group = group
         self.global_feet = int(global_feet)
@@ -138,7 +150,7 @@ class ShardedTrainStep:
             step.mesh_terms.seed = (int(step.mesh_terms.seed) + 0x9E3779B97F4A7C15 * (rank + 1)) & (2 ** 64 - 1)
         if self.world > 1 and not step.frozen:
             self.collective = "nccl"
-            if collective in ("auto", "p2p") and step.flat_grad.is_cuda:
+            if collective in ("auto", "p2p", "nvls") and step.flat_grad.is_cuda:
                 err = None
                 try:
                     self.p2p = P2PAllReduce(step.flat_grad.numel(), step.dev, group)
@@ -149,9 +161,17 @@ class ShardedTrainStep:
                 if int(ok.item()) == 1:
                     self._adopt_bucket()
                     self.collective = "p2p"
+                    # "auto": the in-switch sum pays from 8 ranks on (isolated 22.4 us against 25.2 us at N = 8, equal at N = 4,
+                    # 23.1 against 19.5 us at N = 2: profiles/r2_allreduce_nvls.md)
+                    if collective == "nvls" or (collective == "auto" and self.world >= 8):
+                        mc = torch.tensor([1 if self.p2p.mc_ptr else 0], device=step.dev)
+                        dist.all_reduce(mc, op=dist.ReduceOp.MIN, group=group)
+                        if int(mc.item()) == 1:
+                            self.p2p.use_mc = True
+                            self.collective = "nvls"
                 else:
                     self.p2p = None
-                    if collective == "p2p":
+                    if collective in ("p2p", "nvls"):
                         raise RuntimeError(f"peer-memory allreduce unavailable: {err}")
 
     def _adopt_bucket(self):

@@ -353,6 +353,12 @@ int findb200_train_step_mesh(const findb200_field_params* p, const float* templa
 size_t findb200_allreduce_p2p_flag_bytes(void);
 int findb200_allreduce_p2p(void* const* peer_bufs, void* const* peer_flags, int rank, int world, long long n_floats,
                            float scale, unsigned int* epoch_dev, int n_ctas, void* stream);
+/* The same exchange with the sum taken inside the NVSwitch (NVLS): mc_buf is the MULTICAST mapping of the bucket
+ * (multimem.ld_reduce adds the addressed bytes over every rank's copy, multimem.st writes the result into all of them); the
+ * barriers use the same peer flag pages.  Needs a multicast object over the ranks (torch symmetric memory reports it as
+ * handle.multicast_ptr != 0); results are bit-identical on every rank, the order of the additions is the switch's. */
+int findb200_allreduce_mc(void* mc_buf, void* const* peer_flags, int rank, int world, long long n_floats, float scale,
+                          unsigned int* epoch_dev, int n_ctas, void* stream);
 
 /* Kernel counters of the last findb200_train_step that used this workspace: same four numbers as findb200_knn_stats
  * ({pair evaluations executed, cross-chunk-tie queries, most chunk evaluations of one group, groups}); synchronises. */

@@ -45,7 +45,7 @@ def main():
     target, colt = syn.make_targets(G, P2, 0), syn.make_col_target(G, V, 0)
     lo = rank * per
     step = TrainStep(model, per, P2, with_colour=True, use_graph=True)
-    sh = ShardedTrainStep(step, G)
+    sh = ShardedTrainStep(step, G, collective=os.environ.get("FINDB200_COLLECTIVE", "auto"))
     step.load_inputs(torch.arange(lo, lo + per), target[lo:lo + per], colt[lo:lo + per])
     for _ in range(3):                                       # capture + replays
         sh.run()
