@@ -104,8 +104,10 @@ def test_two_rank_gloo_matches_single_rank():
 
 
 @pytest.mark.gpu
-def test_sharded_step_on_two_gpus_matches_single_rank():
-    """Two real ranks (torchrun, NCCL rendezvous, the library's peer-memory allreduce inside the step graph) against the single-rank
+@pytest.mark.parametrize("collective", ["p2p", "nvls", "nccl"])
+def test_sharded_step_on_two_gpus_matches_single_rank(collective):
+    """Two real ranks (torchrun, NCCL rendezvous, the exchange inside the step graph: the library's peer-memory kernel, its NVLS
+    variant — which falls back to the peer-memory kernel when the ranks share no multicast object — or NCCL) against the single-rank
     step on the concatenated batch: tools/dp_check.py.  Needs >= 2 visible GPUs; skipped otherwise (the driver's GPU box has one)."""
     import json
     import subprocess
@@ -119,8 +121,10 @@ def test_sharded_step_on_two_gpus_matches_single_rank():
     s.close()
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr", "127.0.0.1",
            "--master-port", str(port), os.path.join(root, "tools", "dp_check.py")]
-    res = subprocess.run(cmd, cwd=root, stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True, timeout=600)
+    res = subprocess.run(cmd, cwd=root, stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True, timeout=600,
+                         env=dict(os.environ, FINDB200_COLLECTIVE=collective))
     assert res.returncode == 0, res.stderr[-2000:]
     line = [ln for ln in res.stdout.splitlines() if ln.startswith("{")][-1]
     out = json.loads(line)
     assert out["ok"] and out["all_ranks_identical"] and out["bucket_rel_l2"] < 1e-4 and out["shapevec_rows_rel_l2"] < 1e-4, out
+    assert out["collective"] in ((collective, "p2p") if collective == "nvls" else (collective,)), out
