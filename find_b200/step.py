@@ -81,7 +81,6 @@ class TrainStep:
         # dense table gradients, written (not accumulated) by the scatter at the end of every enqueue: what
         # loss.backward() leaves in LatentVector.data.grad after zero_grad() (trainer.py:99-100,121)
         self.table_grads = {k: torch.zeros_like(t.data) for k, t in self.tables.items() if t is not None}
-        self.loss3 = torch.zeros(3, **f32)
         self.disp, self.col, self.verts = (torch.empty(B, V, 3, **f32) for _ in range(3))
         self.mlp_params = model.mlp_parameters()
         n_flat = sum(p.numel() for p in self.mlp_params)
@@ -145,7 +144,8 @@ class TrainStep:
         f32 = dict(dtype=torch.float32, device=self.dev)
         return dict(idx4=torch.zeros(len(TABLE_KEYS), self.B, dtype=torch.int64, device=self.dev),
                     target=torch.zeros(self.B, self.P2, 3, **f32),
-                    col_target=torch.zeros(self.B, self.V, 3, **f32) if self.with_colour else None)
+                    col_target=torch.zeros(self.B, self.V, 3, **f32) if self.with_colour else None,
+                    loss3=torch.zeros(3, **f32))       # [total, chamfer, colour]: written by the step that reads this set
 
     @property
     def idx4(self):
@@ -162,6 +162,10 @@ class TrainStep:
     @property
     def col_target(self):
         return self._sets[self._cur]["col_target"]
+
+    @property
+    def loss3(self):
+        return self._sets[self._cur]["loss3"]
 
     @property
     def graph(self):
@@ -329,18 +333,20 @@ class TrainStep:
         if getattr(self, "_loss_host", None) is None:
             self._loss_host = [torch.empty(3, dtype=torch.float32).pin_memory() for _ in range(2)]
             self._loss_done = [torch.cuda.Event() for _ in range(2)]
-            self._loss_next = 0
+            self._d2h_stream = torch.cuda.Stream(device=self.dev)
         k = self._staged.pop(0)
         cur = torch.cuda.current_stream(self.dev)
         cur.wait_event(self._ready[k])
+        cur.wait_event(self._loss_done[k])                           # set k's losses of two steps ago have left the device
         self._cur = k                                                # the step reads set k in place (its own captured graph)
         (runner or self).run()
         self._consumed[k].record(cur)
-        j = self._loss_next
-        self._loss_host[j].copy_(self.loss3, non_blocking=True)
-        self._loss_done[j].record(cur)
-        self._loss_next = j ^ 1
-        return j
+        # the losses go home on their own stream (every set has its own loss3), so the next step's graph follows this one directly
+        self._d2h_stream.wait_event(self._consumed[k])
+        with torch.cuda.stream(self._d2h_stream):
+            self._loss_host[k].copy_(self._sets[k]["loss3"], non_blocking=True)
+            self._loss_done[k].record(self._d2h_stream)
+        return k
 
     def _collect(self, j: int) -> Dict[str, float]:
         self._loss_done[j].synchronize()
