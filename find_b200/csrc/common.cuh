@@ -35,7 +35,9 @@ void prof_mark(const char* name, cudaStream_t st);
 // Programmatic dependent launch: every kernel of the step starts with pdl_wait_trigger() and is launched through
 // launch_pdl(), so kernel N+1 is scheduled (launch latency, CTA ramp) while kernel N drains.  griddepcontrol.wait blocks
 // until the previous grid has COMPLETED and its memory is visible, so data hazards are exactly those of plain stream
-// order; launch_dependents comes after the wait, which keeps at most two kernels of the chain resident.
+// order; launch_dependents comes after the wait, which keeps at most two kernels of the chain resident.  The tensor-core kernels
+// (chain2_kernel, dw_kernel) call it AFTER their set-up (mbarrier init, TMEM allocation, cluster sync: shared memory and TMEM only),
+// so that part overlaps the previous kernel's tail wherever an SM is already free: 0.4518 -> 0.4461 ms per cfg2 step.
 FB_DEVINL void pdl_wait_trigger() {
     asm volatile("griddepcontrol.wait;" ::: "memory");
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");

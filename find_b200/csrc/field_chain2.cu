@@ -183,7 +183,6 @@ FB_DEVINL void bulk_wait_read(int pending) {       // this thread's bulk stores:
 // instantiation carries none of them.
 template <int MODE, int NT, bool DIAG>
 __global__ void __launch_bounds__(kThreads2, 1) chain2_kernel(const __grid_constant__ ChainParams P) {
-    fb::pdl_wait_trigger();
     auto stamp = [](const ChainParams& Pp, bool on, int slot) { if constexpr (DIAG) c2::stamp(Pp, on, slot); };
     const int dflags = DIAG ? P.dbg_flags : 0;
     if (threadIdx.x == 0 && blockIdx.x == 0) stamp(P, true, 500 + MODE * 2);
@@ -232,6 +231,9 @@ __global__ void __launch_bounds__(kThreads2, 1) chain2_kernel(const __grid_const
     cluster_sync_all();
     tc_fence_after();
     const uint32_t tmem = tmem_base_s;
+    // Everything above touches only this CTA pair's shared memory and TMEM: with a programmatic launch it runs while the previous
+    // kernel of the stream is still finishing (where an SM is free for it); global memory is first touched below.
+    fb::pdl_wait_trigger();
 
     // ---- work decomposition: flat tile list, 2 tiles per pair-tile (one per CTA), NT pair-tiles per item --------------------
     const int n_tiles = (kTrunk ? P.trunk_feet : P.B) * P.tpf;                  // per head for the head kernels

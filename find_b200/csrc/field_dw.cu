@@ -18,7 +18,6 @@ constexpr int kDwStageBytes = 65536;   // A half-tile (<= 4 x 8 KB) | B half-til
 constexpr int kDwThreads = 192;        // warp 0 producer, warp 1 MMA, warps 2..5 column sums + final epilogue
 
 __global__ void __launch_bounds__(kDwThreads, 1) dw_kernel(const __grid_constant__ DwParams P) {
-    fb::pdl_wait_trigger();
     extern __shared__ uint8_t smem_raw[];
     uint8_t* ring = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
     __shared__ __align__(8) uint64_t bar_full[kDwStages], bar_empty[kDwStages], bar_done, bar_tmem_free;
@@ -37,6 +36,7 @@ __global__ void __launch_bounds__(kDwThreads, 1) dw_kernel(const __grid_constant
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem = tmem_base_s;
+    fb::pdl_wait_trigger();            // the set-up above needs nothing from the previous kernel of the stream
 
     // this CTA's segments
     const int cta = (int)blockIdx.x + P.cta_base;          // the early / late launches of one plan share the CTA numbering
