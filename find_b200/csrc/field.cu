@@ -705,7 +705,6 @@ int findb200_field_backward(const findb200_field_params* p, const float* pos, in
     int ng = 0;
     int gemm_param[kMaxDwGemms];     // which parameter the GEMM feeds, and which K block of base.0
     int gemm_kblock[kMaxDwGemms];
-    long long cost[kMaxDwGemms];
     auto add = [&](const uint8_t* A, uint32_t atb, int a_imgs, const uint8_t* Bm, uint32_t btb, uint32_t boff, int b_imgs,
                    int mh, int N, int feet, int afs, int bfs, long long* cs, int csmode, int cscols, int prm, int kblock) {
         DwGemm& g = D.g[ng];
@@ -713,7 +712,6 @@ int findb200_field_backward(const findb200_field_params* p, const float* pos, in
         g.mhalves = mh; g.N = N; g.feet = feet; g.tpf = w.tpf; g.a_foot_stride = afs; g.b_foot_stride = bfs;
         g.colsum = cs; g.colsum_mode = csmode; g.colsum_cols = cscols;
         gemm_param[ng] = prm; gemm_kblock[ng] = kblock;
-        cost[ng] = (long long)feet * w.tpf * (mh * 4 * (N >= 256 ? 4 : 1) + 4);
         ++ng;
     };
     for (int head = 0; head < 2; ++head) {
@@ -771,7 +769,6 @@ int findb200_field_backward(const findb200_field_params* p, const float* pos, in
     // every segment ends with the drain of its MMAs and a 256 KB partial written from TMEM: a CTA whose piece crosses a GEMM
     // border pays that twice (measured: such CTAs ended 6..8 us after their neighbours, profiles/r2_dw_split.md)
     const long long seg_cost = (long long)(c_seg * 1000.0f);
-    (void)cost;
     long long unit_cost[kMaxDwGemms], total_cost = 0;      // in ns per unit (one tile = two stages)
     for (int i = 0; i < ng; ++i) {
         const DwGemm& g = D.g[i];
